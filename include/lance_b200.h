@@ -1,0 +1,164 @@
+/*
+ * lance_b200.h -- C ABI of the B200-native IVF_PQ query path (liblance_b200.so).
+ *
+ * This is the drop-in boundary of SURVEY.md 8(b): every entry point replaces one method of
+ * Lance's `trait VectorIndex` (rust/lance-index/src/vector.rs:117-217) or the flat-kNN free
+ * function `compute_distance` (rust/lance-index/src/vector/flat.rs:28), batched over Q
+ * queries.  Signatures carry only plain pointers and sizes (no torch / Arrow types).
+ *
+ * Conventions
+ *  - return 0 = OK, negative = error (LB200_E*); message via lb200_last_error() (thread-local).
+ *  - pointers are HOST memory unless the function name ends in `_device`.
+ *  - nothing is retained after return except what lb200_index_create copies to the GPU.
+ *  - a handle may be used from several host threads; calls serialise on the handle.
+ *  - there is NO CPU fallback: without a usable CUDA device every call fails with
+ *    LB200_ECUDA.
+ *
+ * Numerics: all distances are IEEE f32 computed in the reference's own operation order
+ * (see DESIGN.md "Numerics"), so results are bit-identical to the CPU reference wherever the
+ * reference itself is deterministic; equal distances are ordered by row id.
+ */
+#ifndef LANCE_B200_H
+#define LANCE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lb200_index lb200_index; /* opaque, device-resident IVF_PQ index */
+
+/* DistanceType, rust/lance-linalg/src/distance.rs:36-43 */
+enum { LB200_L2 = 0, LB200_COSINE = 1, LB200_DOT = 2 };
+
+enum {
+  LB200_OK = 0,
+  LB200_EINVAL = -1,   /* Error::InvalidInput  (lance-core/src/error.rs:19)  */
+  LB200_ECUDA = -2,    /* CUDA runtime failure / no device                   */
+  LB200_ENOMEM = -3,
+  LB200_EUNSUPPORTED = -4 /* Error::Index "not supported" (e.g. num_bits != 8) */
+};
+
+/* Replaces IVFIndex::try_new + load_partition + ProductQuantizationStorage::new
+ * (rust/lance/src/index/vector/ivf/v2.rs:110-275, rust/lance-index/src/vector/storage.rs:271-298,
+ * pq/storage.rs:147-211): eager upload of the whole index.
+ *   centroids    [nlist][dim] f32 row-major                (IvfModel, ivf/storage.rs)
+ *   codebook     [M][256][dim/M] f32                       (pq/utils.rs:54-71)
+ *   part_offsets [nlist+1] rows, prefix sum                (pb::Ivf offsets/lengths)
+ *   codes        concat over p of [M][n_p] u8, transposed  (pq/storage.rs:357-377,455-470)
+ *   row_ids      [N] u64 in index order                    (`_rowid` column of auxiliary.idx)
+ *   raw_vectors  [N][dim] f32 in index order, or NULL      (only for device-side refine)
+ * num_bits must be 8 (4-bit PQ: LB200_EUNSUPPORTED). */
+int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist,
+                           const float* centroids, uint32_t num_sub_vectors, uint32_t num_bits,
+                           const float* codebook, const uint64_t* part_offsets,
+                           const uint8_t* codes, const uint64_t* row_ids,
+                           const float* raw_vectors_or_null, lb200_index** out);
+void lb200_index_destroy(lb200_index* ix);
+
+/* VectorIndex::find_partitions (vector.rs:146; ivf/v2.rs:403-411 ->
+ * kmeans_find_partitions, rust/lance-linalg/src/kmeans.rs:624-644), batched.
+ * As in the reference, the key is used AS GIVEN: for a cosine index the caller passes the
+ * already-normalised key (exec node does that, rust/lance/src/io/exec/knn.rs:366-369).
+ * out_part_ids [Q][min(nprobes,nlist)] ascending by (distance, id); out_part_dists optional. */
+int32_t lb200_find_partitions(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes,
+                              uint32_t* out_part_ids, float* out_part_dists_or_null);
+
+/* VectorIndex::search_in_partition (vector.rs:165; ivf/v2.rs:414-433 -> FlatIndex::search,
+ * rust/lance-index/src/vector/flat/index.rs:76-137) for explicit (query, partition) pairs.
+ * part_ids [Q][P]; key used as given (already normalised for cosine).
+ * lower/upper: distance range [lower, upper), NULL = unbounded (flat/index.rs:97-101).
+ * part_bitmask_or_null: per PARTITION pointer (nlist entries, NULL entry = all rows) to a
+ *   bitmask over that partition's rows, bit i of word i/64 set = row allowed (PreFilter,
+ *   lance-index/src/prefilter.rs:26-51).
+ * out_dist/out_rowid [Q][P][k_prime] ascending by (distance,row id); out_count [Q][P]. */
+int32_t lb200_search_partitions(lb200_index* ix, const float* queries, uint32_t Q,
+                                const uint32_t* part_ids, uint32_t P, uint32_t k_prime,
+                                const float* lower_or_null, const float* upper_or_null,
+                                const uint64_t* const* part_bitmask_or_null, float* out_dist,
+                                uint64_t* out_rowid, uint32_t* out_count);
+
+/* VectorIndex::search (vector.rs:133; ivf/v2.rs:368-401): normalise (cosine) ->
+ * find_partitions -> search_in_partition per probe -> merge to k' = k*max(refine_factor,1).
+ * If refine_factor > 0 and the index holds raw vectors, also runs the scanner's refine
+ * (rust/lance/src/dataset/scanner.rs:1706-1721,2066-2136): exact index-metric distance on
+ * raw vectors with the original query, bounds re-applied, top-k.
+ * Output stride is k (refined) or k' (not refined, refine_factor==0 -> k'=k); out_count [Q]. */
+int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes,
+                     uint32_t k, uint32_t refine_factor, const float* lower_or_null,
+                     const float* upper_or_null, float* out_dist, uint64_t* out_rowid,
+                     uint32_t* out_count);
+
+/* Same as lb200_search with DEVICE pointers on the index's device, asynchronous on `stream`
+ * (a cudaStream_t; NULL = the handle's own stream, synchronised before return).
+ * Shard mode (multi-GPU): when d_out_exact_or_null != NULL the call stops before
+ * the final cut and returns the k' merged ANN candidates of THIS shard -- d_out_dist [Q][k']
+ * PQ distances, d_out_rowid [Q][k'], d_out_count [Q] -- plus their exact (refine) distances
+ * in d_out_exact [Q][k'] (NaN when refine_factor==0 or no raw vectors), so that
+ * lb200_merge_topk_device can reproduce the single-index result exactly. */
+int32_t lb200_search_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
+                            uint32_t k, uint32_t refine_factor, const float* lower_or_null,
+                            const float* upper_or_null, float* d_out_dist, uint64_t* d_out_rowid,
+                            uint32_t* d_out_count, float* d_out_exact_or_null, void* stream);
+
+/* compute_distance (flat.rs:28-86; KNNVectorDistanceExec, io/exec/knn.rs:156-183): one
+ * distance per (query,row); validity = Arrow validity bitmap (bit set = valid) or NULL;
+ * null rows yield NaN.  out [Q][n]. */
+int32_t lb200_flat_distance(int32_t device_id, int32_t metric, uint32_t dim, const float* queries,
+                            uint32_t Q, const float* vectors, const uint8_t* validity_or_null,
+                            uint64_t n, float* out);
+
+/* compute_distance + SortExec(fetch=k) + NOT NULL filter (scanner.rs:2066-2136).
+ * out_idx are row positions 0..n-1; out_count [Q] (<k when fewer valid rows). */
+int32_t lb200_flat_topk(int32_t device_id, int32_t metric, uint32_t dim, const float* queries,
+                        uint32_t Q, const float* vectors, const uint8_t* validity_or_null,
+                        uint64_t n, uint32_t k, const float* lower_or_null,
+                        const float* upper_or_null, float* out_dist, uint64_t* out_idx,
+                        uint32_t* out_count);
+/* Device-pointer variant (vectors resident in HBM), asynchronous on `stream`. */
+int32_t lb200_flat_topk_device(int32_t device_id, int32_t metric, uint32_t dim,
+                               const float* d_queries, uint32_t Q, const float* d_vectors,
+                               const uint8_t* d_validity_or_null, uint64_t n, uint32_t k,
+                               float* d_out_dist, uint64_t* d_out_idx, uint32_t* d_out_count,
+                               void* stream);
+
+/* Multi-GPU merge step of SURVEY 8(e): G gathered per-shard candidate lists -> global result.
+ * d_dist/d_rowid/d_exact [G][Q][stride], d_count [G][Q]; device pointers.
+ * Selects the kprime smallest by (dist,row id) (== the merge of ivf/v2.rs:395-400); if
+ * d_exact_or_null != NULL then re-ranks those by (exact,row id) with [lower,upper) applied and
+ * keeps k (== the refine of scanner.rs:1706-1721), writing exact distances to d_out_dist;
+ * otherwise keeps min(k,kprime).  Output stride k. */
+int32_t lb200_merge_topk_device(int32_t device_id, const float* d_dist, const uint64_t* d_rowid,
+                                const float* d_exact_or_null, const uint32_t* d_count, uint32_t G,
+                                uint32_t Q, uint32_t stride, uint32_t kprime, uint32_t k,
+                                const float* lower_or_null, const float* upper_or_null,
+                                float* d_out_dist, uint64_t* d_out_rowid, uint32_t* d_out_count,
+                                void* stream);
+
+/* Instrumentation (not part of the reference surface): per-handle counters of the last
+ * search / search_partitions call, used by bench.py for the roofline line. */
+typedef struct {
+  double scan_ms;          /* CUDA-event time of the PQ scan kernel (0 if profiling off)  */
+  double coarse_ms;        /* CUDA-event time of the coarse distance + select kernels      */
+  double total_ms;         /* CUDA-event time of the whole device pipeline                 */
+  uint64_t scan_code_bytes;/* algorithmic code bytes: sum over (q,p) pairs of n_p * M      */
+  uint64_t pairs;          /* (query, partition) pairs scanned                             */
+  uint32_t kernel_launches;/* kernels launched by the call                                 */
+  uint32_t scan_variant;   /* 1 = generic kernel, 2 = bank-skewed multi-query kernel       */
+  uint32_t scan_ql;        /* queries per CTA of the scan kernel                           */
+  uint32_t scan_items;     /* work items of the scan kernel                                */
+} lb200_stats;
+int32_t lb200_set_profiling(lb200_index* ix, int32_t enabled);
+int32_t lb200_get_stats(const lb200_index* ix, lb200_stats* out);
+/* Force a scan kernel variant (0 = auto, 1 = generic, 2 = bank-skewed); for A/B tests. */
+int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant);
+
+const char* lb200_last_error(void);
+const char* lb200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LANCE_B200_H */

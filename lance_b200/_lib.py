@@ -1,0 +1,55 @@
+"""ctypes loader for liblance_b200.so (the C ABI declared in include/lance_b200.h).
+
+There is no fallback of any kind: if the shared library is missing the import fails with an
+explicit build hint, and every compute call fails loudly when no CUDA device is usable.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "liblance_b200.so")
+
+EXPORTS = [
+    "lb200_index_create", "lb200_index_destroy", "lb200_find_partitions", "lb200_search_partitions",
+    "lb200_search", "lb200_search_device", "lb200_flat_distance", "lb200_flat_topk",
+    "lb200_flat_topk_device", "lb200_merge_topk_device", "lb200_set_profiling", "lb200_get_stats",
+    "lb200_set_scan_variant", "lb200_last_error", "lb200_version",
+]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("scan_ms", C.c_double), ("coarse_ms", C.c_double), ("total_ms", C.c_double),
+        ("scan_code_bytes", C.c_uint64), ("pairs", C.c_uint64), ("kernel_launches", C.c_uint32),
+        ("scan_variant", C.c_uint32), ("scan_ql", C.c_uint32), ("scan_items", C.c_uint32),
+    ]
+
+
+class LanceB200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"lance_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError(
+                f"{SO_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "or `make -C lance_b200/csrc` (nvcc, sm_100a). lance_b200 has no CPU fallback.")
+        _lib = C.CDLL(SO_PATH)
+        _lib.lb200_last_error.restype = C.c_char_p
+        _lib.lb200_version.restype = C.c_char_p
+        _lib.lb200_index_destroy.restype = None
+        for name in EXPORTS:
+            getattr(_lib, name)  # raises AttributeError if a declared symbol is missing
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise LanceB200Error(rc, lib().lb200_last_error().decode())

@@ -1,0 +1,247 @@
+// api.cu -- host side of liblance_b200.so: the device-resident index object and the C ABI.
+//
+// `B200IvfPq` mirrors IVFIndex<FlatIndex, ProductQuantizer> (rust/lance/src/index/vector/ivf/v2.rs:76)
+// behind `trait VectorIndex` (rust/lance-index/src/vector.rs:117-217): find_partitions,
+// search_in_partition (batched as search_partitions) and search.  No CPU fallback exists:
+// every entry point fails with LB200_ECUDA when no CUDA device is usable.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/lance_b200.h"
+#include "coarse.cuh"
+#include "flat.cuh"
+#include "scan.cuh"
+#include "worklist.cuh"
+
+using namespace lb200;
+
+static thread_local std::string g_err;
+static int set_err(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return set_err(e_ == cudaErrorMemoryAllocation ? LB200_ENOMEM : LB200_ECUDA,            \
+                     "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+extern "C" const char* lb200_last_error(void) { return g_err.c_str(); }
+extern "C" const char* lb200_version(void) { return "lance_b200 0.1 (sm_100a)"; }
+
+static inline uint32_t next_pow2(uint32_t v) {
+  uint32_t p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// Grow-only device arena; one per handle, carved per call.
+struct Arena {
+  char* base = nullptr;
+  size_t cap = 0, used = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (base) cudaFree(base);
+    base = nullptr;
+    cap = 0;
+    size_t want = bytes + (bytes >> 3);
+    cudaError_t e = cudaMalloc((void**)&base, want);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      e = cudaMalloc((void**)&base, bytes);
+      want = bytes;
+    }
+    if (e != cudaSuccess) return set_err(LB200_ENOMEM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    cap = want;
+    return 0;
+  }
+  void reset() { used = 0; }
+  template <typename T>
+  T* take(size_t n) {
+    size_t off = (used + 255) & ~(size_t)255;
+    used = off + n * sizeof(T);
+    return reinterpret_cast<T*>(base + off);
+  }
+  static size_t pad(size_t b) { return (b + 255) & ~(size_t)255; }
+};
+
+struct lb200_index {
+  int device = 0, metric = 0;
+  uint32_t dim = 0, nlist = 0, M = 0, dsub = 0;
+  uint64_t N = 0, ntiles = 0, max_part = 0;
+  float *d_centroids = nullptr, *d_codebook = nullptr, *d_raw = nullptr;
+  uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
+  uint8_t* d_codes = nullptr;
+  std::vector<uint64_t> h_part_off;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6] = {};
+  std::mutex mu;
+  bool profiling = false;
+  int force_variant = 0;
+  lb200_stats stats = {};
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  Arena arena;
+  const uint64_t** d_bitmask_ptrs = nullptr;  // scratch for prefilter pointers
+};
+
+static int select_device(int device_id) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return set_err(LB200_ECUDA, "no CUDA device available (%s); lance_b200 has no CPU fallback",
+                   e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device_id < 0 || device_id >= n) return set_err(LB200_EINVAL, "device_id %d out of range [0,%d)", device_id, n);
+  CK(cudaSetDevice(device_id));
+  return 0;
+}
+
+extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist,
+                                      const float* centroids, uint32_t M, uint32_t num_bits,
+                                      const float* codebook, const uint64_t* part_offsets,
+                                      const uint8_t* codes, const uint64_t* row_ids,
+                                      const float* raw_vectors_or_null, lb200_index** out) {
+  if (!out) return set_err(LB200_EINVAL, "out is null");
+  *out = nullptr;
+  if (num_bits != 8)
+    return set_err(LB200_EUNSUPPORTED, "num_bits=%u: only 8-bit PQ is supported (4-bit: SURVEY 8f-4)", num_bits);
+  if (metric != LB200_L2 && metric != LB200_COSINE && metric != LB200_DOT)
+    return set_err(LB200_EINVAL, "unknown metric %d", metric);
+  if (!dim || !nlist || !M || dim % M) return set_err(LB200_EINVAL, "bad shape dim=%u nlist=%u M=%u", dim, nlist, M);
+  if (!centroids || !codebook || !part_offsets) return set_err(LB200_EINVAL, "null index buffers");
+  if (M > 192) return set_err(LB200_EUNSUPPORTED, "num_sub_vectors=%u > 192 (ADC table would exceed shared memory)", M);
+  for (uint32_t p = 0; p < nlist; p++)
+    if (part_offsets[p + 1] < part_offsets[p]) return set_err(LB200_EINVAL, "part_offsets not monotone at %u", p);
+  if (part_offsets[0] != 0) return set_err(LB200_EINVAL, "part_offsets[0] must be 0");
+  uint64_t N = part_offsets[nlist];
+  if (N >= (1ull << 32)) return set_err(LB200_EUNSUPPORTED, "N=%llu rows >= 2^32", (unsigned long long)N);
+  if (N && (!codes || !row_ids)) return set_err(LB200_EINVAL, "null codes/row_ids");
+  int rc = select_device(device_id);
+  if (rc) return rc;
+
+  lb200_index* ix = new lb200_index();
+  ix->device = device_id;
+  ix->metric = metric;
+  ix->dim = dim;
+  ix->nlist = nlist;
+  ix->M = M;
+  ix->dsub = dim / M;
+  ix->N = N;
+  ix->h_part_off.assign(part_offsets, part_offsets + nlist + 1);
+  std::vector<uint64_t> tile_off(nlist + 1);
+  uint64_t t = 0;
+  for (uint32_t p = 0; p < nlist; p++) {
+    tile_off[p] = t;
+    uint64_t n = part_offsets[p + 1] - part_offsets[p];
+    ix->max_part = std::max(ix->max_part, n);
+    if (n >= (1ull << 31)) { delete ix; return set_err(LB200_EUNSUPPORTED, "partition %u too large", p); }
+    t += (n + 15) >> 4;
+  }
+  tile_off[nlist] = t;
+  ix->ntiles = t;
+  cudaDeviceProp prop;
+  auto fail = [&](int code) {
+    lb200_index_destroy(ix);
+    return code;
+  };
+#define CKF(call)                                                                                  \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return fail(set_err(e_ == cudaErrorMemoryAllocation ? LB200_ENOMEM : LB200_ECUDA,            \
+                          "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__)); \
+  } while (0)
+  CKF(cudaGetDeviceProperties(&prop, device_id));
+  ix->sm_count = prop.multiProcessorCount;
+  ix->smem_optin = prop.sharedMemPerBlockOptin;
+  CKF(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+  for (auto& e : ix->ev) CKF(cudaEventCreate(&e));
+  size_t cent_b = (size_t)nlist * dim * 4, cb_b = (size_t)M * 256 * ix->dsub * 4;
+  CKF(cudaMalloc(&ix->d_centroids, cent_b));
+  CKF(cudaMalloc(&ix->d_codebook, cb_b));
+  CKF(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
+  CKF(cudaMalloc(&ix->d_tile_off, (nlist + 1) * 8));
+  CKF(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));
+  // tile16 codes, padded by one extra block of tiles so clamped loads stay in bounds
+  size_t codes_b = (size_t)(t + 64) * 16 * M;
+  CKF(cudaMalloc(&ix->d_codes, codes_b));
+  CKF(cudaMemcpyAsync(ix->d_centroids, centroids, cent_b, cudaMemcpyHostToDevice, ix->stream));
+  CKF(cudaMemcpyAsync(ix->d_codebook, codebook, cb_b, cudaMemcpyHostToDevice, ix->stream));
+  CKF(cudaMemcpyAsync(ix->d_part_off, part_offsets, (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
+  CKF(cudaMemcpyAsync(ix->d_tile_off, tile_off.data(), (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
+  CKF(cudaMemsetAsync(ix->d_codes, 0, codes_b, ix->stream));
+  if (N) {
+    CKF(cudaMemcpyAsync(ix->d_row_ids, row_ids, N * 8, cudaMemcpyHostToDevice, ix->stream));
+    uint8_t* d_src = nullptr;
+    CKF(cudaMalloc(&d_src, (size_t)N * M));
+    cudaError_t e1 = cudaMemcpyAsync(d_src, codes, (size_t)N * M, cudaMemcpyHostToDevice, ix->stream);
+    if (e1 == cudaSuccess) {
+      dim3 grid(nlist, 8);
+      repack_codes_kernel<<<grid, 256, 0, ix->stream>>>(d_src, ix->d_part_off, ix->d_tile_off, nlist, M, ix->d_codes);
+      e1 = cudaGetLastError();
+    }
+    if (e1 == cudaSuccess) e1 = cudaStreamSynchronize(ix->stream);
+    cudaFree(d_src);
+    CKF(e1);
+    if (raw_vectors_or_null) {
+      CKF(cudaMalloc(&ix->d_raw, (size_t)N * dim * 4));
+      CKF(cudaMemcpyAsync(ix->d_raw, raw_vectors_or_null, (size_t)N * dim * 4, cudaMemcpyHostToDevice, ix->stream));
+    }
+  }
+  CKF(cudaStreamSynchronize(ix->stream));
+#undef CKF
+  *out = ix;
+  return 0;
+}
+
+extern "C" void lb200_index_destroy(lb200_index* ix) {
+  if (!ix) return;
+  cudaSetDevice(ix->device);
+  cudaFree(ix->d_centroids);
+  cudaFree(ix->d_codebook);
+  cudaFree(ix->d_raw);
+  cudaFree(ix->d_part_off);
+  cudaFree(ix->d_tile_off);
+  cudaFree(ix->d_row_ids);
+  cudaFree(ix->d_codes);
+  cudaFree(ix->arena.base);
+  cudaFree((void*)ix->d_bitmask_ptrs);
+  for (auto& e : ix->ev)
+    if (e) cudaEventDestroy(e);
+  if (ix->stream) cudaStreamDestroy(ix->stream);
+  delete ix;
+}
+
+extern "C" int32_t lb200_set_profiling(lb200_index* ix, int32_t enabled) {
+  if (!ix) return set_err(LB200_EINVAL, "null index");
+  ix->profiling = enabled != 0;
+  return 0;
+}
+extern "C" int32_t lb200_get_stats(const lb200_index* ix, lb200_stats* out) {
+  if (!ix || !out) return set_err(LB200_EINVAL, "null argument");
+  *out = ix->stats;
+  return 0;
+}
+extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
+  if (!ix || variant < 0 || variant > 2) return set_err(LB200_EINVAL, "variant must be 0, 1 or 2");
+  ix->force_variant = variant;
+  return 0;
+}
+
+#include "api_search.inl"
+#include "api_flat.inl"

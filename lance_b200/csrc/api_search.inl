@@ -1,0 +1,530 @@
+// api_search.inl -- the batched IVF_PQ query pipeline (included by api.cu).
+
+namespace {
+
+struct ScanConfig {
+  int variant, ql, dsub_t;
+  uint32_t capw;
+  size_t smem;
+};
+constexpr int SCAN_NW = 8;
+
+static size_t scan_smem_bytes(int variant, int ql, uint32_t M, uint32_t dim, uint32_t capw) {
+  int vg = 32 / ql;
+  size_t lut = variant == 1 ? (size_t)M * 256 * 4 : (size_t)(M / vg) * 256 * 32 * 4;
+  return lut + (size_t)ql * dim * 4 + (size_t)SCAN_NW * ql * capw * 8 + (size_t)SCAN_NW * ql * 4 +
+         (size_t)ql * 8 + 16;
+}
+
+// Choose the scan kernel: the bank-skewed multi-query variant when the table layout allows it
+// (M % (32/QL) == 0) and the batch brings enough queries per partition, else the generic one.
+static int choose_scan(const lb200_index* ix, uint32_t kprime, double avg_q_per_part, ScanConfig* out) {
+  const uint32_t need_cap = std::max(2 * kprime, kprime + 32);
+  const size_t limit = ix->smem_optin;
+  auto fit = [&](int variant, int ql, ScanConfig* c) {
+    if (variant == 2 && ix->M % (32 / ql)) return false;
+    size_t fixed = scan_smem_bytes(variant, ql, ix->M, ix->dim, 0);
+    if (fixed >= limit) return false;
+    size_t capw = (limit - fixed) / ((size_t)SCAN_NW * ql * 8);
+    capw = std::min<size_t>(capw, 1024);
+    if (capw < need_cap) return false;
+    if (capw > 4 * (size_t)need_cap) capw = 4 * (size_t)need_cap;  // enough; keep L1 for the codes
+    c->variant = variant;
+    c->ql = ql;
+    c->capw = (uint32_t)capw;
+    c->smem = scan_smem_bytes(variant, ql, ix->M, ix->dim, (uint32_t)capw);
+    c->dsub_t = ix->dsub == 8 ? 8 : ix->dsub == 16 ? 16 : 0;
+    return true;
+  };
+  if (ix->force_variant != 1) {
+    int want = avg_q_per_part >= 6 ? 8 : avg_q_per_part >= 3 ? 4 : avg_q_per_part >= 1.5 ? 2 : 1;
+    if (ix->force_variant == 2 && want < 2) want = 8;
+    for (int ql = want; ql >= 1; ql >>= 1)
+      if ((ql > 1 || ix->force_variant == 2 || ix->M % 32 == 0) && fit(2, ql, out)) return 0;
+    if (ix->force_variant == 2)
+      for (int ql = 8; ql > want; ql >>= 1)
+        if (fit(2, ql, out)) return 0;
+  }
+  if (fit(1, 1, out)) return 0;
+  return set_err(LB200_EUNSUPPORTED, "k'=%u does not fit the shared-memory candidate buffers (M=%u, dim=%u)",
+                 kprime, ix->M, ix->dim);
+}
+
+template <int VARIANT, int QL>
+static cudaError_t launch_scan_d(int dsub_t, int grid, size_t smem, cudaStream_t st, const ScanParams& sp,
+                                 const uint32_t* total_items) {
+#define LB200_LAUNCH(D)                                                                           \
+  do {                                                                                            \
+    auto kern = scan_kernel<VARIANT, QL, SCAN_NW, D>;                                             \
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    if (e != cudaSuccess) return e;                                                               \
+    kern<<<grid, SCAN_NW * 32, smem, st>>>(sp, total_items);                                      \
+    return cudaGetLastError();                                                                    \
+  } while (0)
+  if (dsub_t == 8) LB200_LAUNCH(8);
+  if (dsub_t == 16) LB200_LAUNCH(16);
+  LB200_LAUNCH(0);
+#undef LB200_LAUNCH
+}
+
+static cudaError_t launch_scan(const ScanConfig& c, int grid, cudaStream_t st, const ScanParams& sp,
+                               const uint32_t* total_items) {
+  if (c.variant == 1) return launch_scan_d<1, 1>(c.dsub_t, grid, c.smem, st, sp, total_items);
+  switch (c.ql) {
+    case 8: return launch_scan_d<2, 8>(c.dsub_t, grid, c.smem, st, sp, total_items);
+    case 4: return launch_scan_d<2, 4>(c.dsub_t, grid, c.smem, st, sp, total_items);
+    case 2: return launch_scan_d<2, 2>(c.dsub_t, grid, c.smem, st, sp, total_items);
+    default: return launch_scan_d<2, 1>(c.dsub_t, grid, c.smem, st, sp, total_items);
+  }
+}
+
+struct SearchArgs {
+  const float* d_queries;      // [Q][dim] device, as given by the caller
+  uint32_t Q;
+  uint32_t nprobes;            // used when d_part_ids == nullptr
+  const uint32_t* d_part_ids;  // [Q][P] device (search_partitions) or nullptr (search)
+  uint32_t P;                  // partitions per query (search_partitions)
+  uint32_t k, refine_factor;
+  bool normalize;              // cosine + VectorIndex::search entry
+  bool per_pair_output;        // search_partitions: [Q][P][k'] instead of merged [Q][k']
+  bool shard_mode;             // stop before the final cut, also return exact distances
+  bool has_lower, has_upper;
+  float lower, upper;
+  const uint64_t* const* d_bitmask;  // device array [nlist] of device pointers, or nullptr
+  float* d_out_dist;
+  uint64_t* d_out_rowid;
+  uint32_t* d_out_count;
+  float* d_out_exact;          // shard mode only
+};
+
+// find_partitions on device: distances [Q][nlist] + per-query sort.  Output [Q][P].
+static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint32_t P, float* d_D,
+                         uint32_t* d_probes, float* d_pdists, cudaStream_t st, uint32_t* launches) {
+  if (ix->nlist > 8192)
+    return set_err(LB200_EUNSUPPORTED, "nlist=%u > 8192 not supported by the coarse select kernel yet", ix->nlist);
+  dim3 grid((ix->nlist + COARSE_THREADS - 1) / COARSE_THREADS, (Q + COARSE_TQ - 1) / COARSE_TQ);
+  size_t smem = (size_t)COARSE_TQ * ix->dim * 4;
+  if (ix->metric == LB200_DOT)
+    coarse_dist_kernel<false><<<grid, COARSE_THREADS, smem, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
+  else
+    coarse_dist_kernel<true><<<grid, COARSE_THREADS, smem, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
+  CK(cudaGetLastError());
+  uint32_t np2 = next_pow2(ix->nlist);
+  size_t ssm = (size_t)np2 * 8;
+  if (ssm > 48 * 1024)
+    CK(cudaFuncSetAttribute(coarse_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm));
+  coarse_select_kernel<<<Q, 256, ssm, st>>>(d_D, ix->nlist, np2, P, d_probes, d_pdists);
+  CK(cudaGetLastError());
+  *launches += 2;
+  return 0;
+}
+
+static int launch_merge(const float* in_dist, const uint64_t* in_rowid, const uint64_t* in_pos, const float* in_aux,
+                        const uint32_t* in_cnt, uint32_t groups, uint32_t L, uint32_t stride, size_t group_stride,
+                        size_t list_stride, size_t cnt_gs, size_t cnt_ls, uint32_t kout, uint32_t out_stride,
+                        float* out_dist, uint64_t* out_rowid, uint64_t* out_pos, float* out_aux, uint32_t* out_cnt,
+                        cudaStream_t st) {
+  uint64_t tot = (uint64_t)L * stride;
+  if (tot > 16384) return set_err(LB200_EUNSUPPORTED, "merge of %llu candidates per query exceeds 16384", (unsigned long long)tot);
+  uint32_t np2 = std::max(2u, next_pow2((uint32_t)tot));
+  size_t smem = (size_t)np2 * 8;
+  if (smem > 48 * 1024)
+    CK(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  merge_lists_kernel<<<groups, 256, smem, st>>>(in_dist, in_rowid, in_pos, in_aux, in_cnt, L, stride, group_stride,
+                                                list_stride, cnt_gs, cnt_ls, np2, kout, out_stride, out_dist,
+                                                out_rowid, out_pos, out_aux, out_cnt);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// The whole device pipeline for one batch of queries; asynchronous on `st`.
+static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st) {
+  const uint32_t Q = a.Q, dim = ix->dim, nlist = ix->nlist;
+  const uint32_t P = a.d_part_ids ? a.P : std::min(a.nprobes, nlist);
+  const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);
+  if (a.k == 0) return set_err(LB200_EINVAL, "k must be > 0");       // scanner.rs:642 validation
+  if (kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", kprime);
+  if (P == 0 || Q == 0) return 0;
+  const bool refine = a.refine_factor > 0 && ix->d_raw != nullptr && !a.per_pair_output;
+  if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output && !a.shard_mode)
+    return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
+  uint32_t launches = 0;
+  lb200_stats stats = {};
+
+  ScanConfig sc;
+  double avg_q = (double)Q * P / std::max(1u, nlist);
+  int rc = choose_scan(ix, kprime, avg_q, &sc);
+  if (rc) return rc;
+  // chunking: enough work items to fill the SMs even for tiny batches
+  uint64_t est_items = std::max<uint64_t>(1, (uint64_t)Q * P / sc.ql);
+  uint64_t want_items = 4ull * ix->sm_count;
+  uint32_t chunk_vecs = (uint32_t)std::max<uint64_t>(16, (ix->max_part + 15) / 16 * 16);
+  if (est_items < want_items) {
+    uint64_t nch = (want_items + est_items - 1) / est_items;
+    uint64_t cv = (ix->max_part + nch - 1) / nch;
+    cv = std::max<uint64_t>(2048, (cv + 511) / 512 * 512);
+    chunk_vecs = (uint32_t)std::min<uint64_t>(chunk_vecs, cv);
+  }
+  const uint32_t max_chunks = (uint32_t)std::max<uint64_t>(1, (ix->max_part + chunk_vecs - 1) / chunk_vecs);
+
+  // ---- workspace -----------------------------------------------------------------------
+  const size_t npairs = (size_t)Q * P, nslots = npairs * max_chunks;
+  if (npairs >= (1ull << 31)) return set_err(LB200_EUNSUPPORTED, "Q*P too large");
+  size_t need = 0;
+  auto add = [&](size_t b) { need += Arena::pad(b) + 256; };
+  add((size_t)Q * dim * 4);         // normalised keys
+  add((size_t)Q * nlist * 4);       // coarse distances
+  add(npairs * 4);                  // probes
+  add((size_t)nlist * 4);           // cnt
+  add(npairs * 4);                  // rank
+  add((size_t)(nlist + 1) * 4 * 2); // pair_off, item_off
+  add(npairs * 4);                  // pair_list
+  add(64);                          // counter + stats
+  add(nslots * kprime * 4); add(nslots * kprime * 8); add(nslots * kprime * 8); add(nslots * 4);
+  add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
+  add((size_t)Q * kprime * 4);      // exact
+  rc = ix->arena.reserve(need);
+  if (rc) return rc;
+  ix->arena.reset();
+  float* d_keys = ix->arena.take<float>((size_t)Q * dim);
+  float* d_D = ix->arena.take<float>((size_t)Q * nlist);
+  uint32_t* d_probes = ix->arena.take<uint32_t>(npairs);
+  uint32_t* d_cnt = ix->arena.take<uint32_t>(nlist);
+  uint32_t* d_rank = ix->arena.take<uint32_t>(npairs);
+  uint32_t* d_pair_off = ix->arena.take<uint32_t>(nlist + 1);
+  uint32_t* d_item_off = ix->arena.take<uint32_t>(nlist + 1);
+  uint32_t* d_pair_list = ix->arena.take<uint32_t>(npairs);
+  unsigned long long* d_stats = ix->arena.take<unsigned long long>(4);
+  uint32_t* d_counter = reinterpret_cast<uint32_t*>(d_stats + 2);
+  float* d_sdist = ix->arena.take<float>(nslots * kprime);
+  uint64_t* d_spos = ix->arena.take<uint64_t>(nslots * kprime);
+  uint64_t* d_srow = ix->arena.take<uint64_t>(nslots * kprime);
+  uint32_t* d_scnt = ix->arena.take<uint32_t>(nslots);
+  float* d_mdist = ix->arena.take<float>((size_t)Q * kprime);
+  uint64_t* d_mrow = ix->arena.take<uint64_t>((size_t)Q * kprime);
+  uint64_t* d_mpos = ix->arena.take<uint64_t>((size_t)Q * kprime);
+  uint32_t* d_mcnt = ix->arena.take<uint32_t>(Q);
+  float* d_exact = ix->arena.take<float>((size_t)Q * kprime);
+
+  const bool prof = ix->profiling;
+  if (prof) CK(cudaEventRecord(ix->ev[0], st));
+
+  // ---- A1 normalise (VectorIndex::search on a cosine index, ivf/v2.rs:370-373) ----------
+  const float* keys = a.d_queries;
+  if (a.normalize && ix->metric == LB200_COSINE) {
+    normalize_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(a.d_queries, d_keys, Q, dim);
+    CK(cudaGetLastError());
+    launches++;
+    keys = d_keys;
+  }
+  // ---- A2 find_partitions ---------------------------------------------------------------
+  const uint32_t* probes = a.d_part_ids;
+  if (!probes) {
+    rc = coarse_device(ix, keys, Q, P, d_D, d_probes, nullptr, st, &launches);
+    if (rc) return rc;
+    probes = d_probes;
+  }
+  if (prof) CK(cudaEventRecord(ix->ev[1], st));
+  // ---- work list ------------------------------------------------------------------------
+  CK(cudaMemsetAsync(d_cnt, 0, (size_t)nlist * 4, st));
+  CK(cudaMemsetAsync(d_stats, 0, 32, st));
+  CK(cudaMemsetAsync(d_scnt, 0, nslots * 4, st));
+  count_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, (uint32_t)npairs, d_cnt, d_rank);
+  offsets_kernel<<<1, 1024, 0, st>>>(d_cnt, ix->d_part_off, nlist, (uint32_t)sc.ql, chunk_vecs, ix->M, d_pair_off,
+                                     d_item_off, d_stats);
+  scatter_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, d_rank, d_pair_off, (uint32_t)npairs,
+                                                                        d_pair_list);
+  CK(cudaGetLastError());
+  launches += 3;
+  // ---- A3-A6 scan -----------------------------------------------------------------------
+  ScanParams sp = {};
+  sp.codes = ix->d_codes; sp.tile_off = ix->d_tile_off; sp.part_off = ix->d_part_off; sp.row_ids = ix->d_row_ids;
+  sp.centroids = ix->d_centroids; sp.codebook = ix->d_codebook;
+  sp.dim = dim; sp.M = ix->M; sp.dsub = ix->dsub; sp.nlist = nlist;
+  sp.residual = ix->metric != LB200_DOT;
+  sp.queries = keys; sp.Q = Q; sp.P = P; sp.kprime = kprime;
+  sp.pair_list = d_pair_list; sp.part_pair_off = d_pair_off; sp.item_off = d_item_off; sp.item_counter = d_counter;
+  sp.chunk_vecs = chunk_vecs; sp.max_chunks = max_chunks; sp.capw = sc.capw;
+  sp.lower = a.lower; sp.upper = a.upper; sp.has_lower = a.has_lower; sp.has_upper = a.has_upper;
+  sp.bitmask = a.d_bitmask;
+  sp.out_dist = d_sdist; sp.out_pos = d_spos; sp.out_rowid = d_srow; sp.out_count = d_scnt;
+  if (prof) CK(cudaEventRecord(ix->ev[2], st));
+  CK(launch_scan(sc, ix->sm_count, st, sp, d_item_off + nlist));
+  launches++;
+  if (prof) CK(cudaEventRecord(ix->ev[3], st));
+  // ---- A7 merge ---------------------------------------------------------------------------
+  if (a.per_pair_output) {
+    // search_in_partition semantics: one list per (query, partition); merge only the chunks
+    rc = launch_merge(d_sdist, d_srow, nullptr, nullptr, d_scnt, (uint32_t)npairs, max_chunks, kprime,
+                      (size_t)max_chunks * kprime, kprime, max_chunks, 1, kprime, kprime, a.d_out_dist,
+                      a.d_out_rowid, nullptr, nullptr, a.d_out_count, st);
+    if (rc) return rc;
+    launches++;
+  } else {
+    const uint32_t L = P * max_chunks;
+    const bool direct = !refine && !a.shard_mode;  // merged list is the final answer
+    rc = launch_merge(d_sdist, d_srow, d_spos, nullptr, d_scnt, Q, L, kprime, (size_t)L * kprime, kprime, L, 1,
+                      kprime, kprime, direct ? a.d_out_dist : d_mdist, direct ? a.d_out_rowid : d_mrow, d_mpos,
+                      nullptr, direct ? a.d_out_count : d_mcnt, st);
+    if (rc) return rc;
+    launches++;
+    if (!direct) {
+      // ---- A8 refine ------------------------------------------------------------------------
+      float* exact = a.shard_mode ? a.d_out_exact : d_exact;
+      if (a.refine_factor > 0 && ix->d_raw) {
+        refine_distance_kernel<<<(uint32_t)(((size_t)Q * kprime + 127) / 128), 128, 0, st>>>(
+            ix->metric, a.d_queries, ix->d_raw, dim, d_mpos, d_mcnt, Q, kprime, exact);
+        CK(cudaGetLastError());
+        launches++;
+      } else if (a.shard_mode) {
+        CK(cudaMemsetAsync(exact, 0xff, (size_t)Q * kprime * 4, st));  // NaN
+      }
+      if (a.shard_mode) {
+        CK(cudaMemcpyAsync(a.d_out_dist, d_mdist, (size_t)Q * kprime * 4, cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpyAsync(a.d_out_rowid, d_mrow, (size_t)Q * kprime * 8, cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpyAsync(a.d_out_count, d_mcnt, (size_t)Q * 4, cudaMemcpyDeviceToDevice, st));
+      } else {
+        rerank_kernel<<<(Q * 32 + 127) / 128, 128, 0, st>>>(exact, d_mrow, d_mcnt, Q, kprime, a.k, a.has_lower, a.lower,
+                                                          a.has_upper, a.upper, a.d_out_dist, a.d_out_rowid,
+                                                          a.d_out_count);
+        CK(cudaGetLastError());
+        launches++;
+      }
+    }
+  }
+  if (prof) {
+    CK(cudaEventRecord(ix->ev[4], st));
+    CK(cudaStreamSynchronize(st));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ix->ev[0], ix->ev[1])); stats.coarse_ms = ms;
+    CK(cudaEventElapsedTime(&ms, ix->ev[2], ix->ev[3])); stats.scan_ms = ms;
+    CK(cudaEventElapsedTime(&ms, ix->ev[0], ix->ev[4])); stats.total_ms = ms;
+    unsigned long long hs[2];
+    uint32_t items = 0;
+    CK(cudaMemcpy(hs, d_stats, 16, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&items, d_item_off + nlist, 4, cudaMemcpyDeviceToHost));
+    stats.scan_code_bytes = hs[0];
+    stats.pairs = hs[1];
+    stats.scan_items = items;
+  }
+  stats.kernel_launches = launches;
+  stats.scan_variant = sc.variant;
+  stats.scan_ql = sc.ql;
+  ix->stats = stats;
+  return 0;
+}
+
+static int check_queries(const lb200_index* ix, const void* q, uint32_t Q) {
+  if (!ix) return set_err(LB200_EINVAL, "null index");
+  if (Q && !q) return set_err(LB200_EINVAL, "null queries");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int32_t lb200_find_partitions(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes,
+                                         uint32_t* out_part_ids, float* out_part_dists_or_null) {
+  int rc = check_queries(ix, queries, Q);
+  if (rc) return rc;
+  if (!out_part_ids) return set_err(LB200_EINVAL, "null output");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  const uint32_t P = std::min(nprobes, ix->nlist);
+  if (!Q || !P) return 0;
+  size_t need = Arena::pad((size_t)Q * ix->dim * 4) + Arena::pad((size_t)Q * ix->nlist * 4) +
+                Arena::pad((size_t)Q * P * 4) * 2 + 2048;
+  rc = ix->arena.reserve(need);
+  if (rc) return rc;
+  ix->arena.reset();
+  float* d_q = ix->arena.take<float>((size_t)Q * ix->dim);
+  float* d_D = ix->arena.take<float>((size_t)Q * ix->nlist);
+  uint32_t* d_p = ix->arena.take<uint32_t>((size_t)Q * P);
+  float* d_pd = ix->arena.take<float>((size_t)Q * P);
+  cudaStream_t st = ix->stream;
+  CK(cudaMemcpyAsync(d_q, queries, (size_t)Q * ix->dim * 4, cudaMemcpyHostToDevice, st));
+  uint32_t launches = 0;
+  rc = coarse_device(ix, d_q, Q, P, d_D, d_p, d_pd, st, &launches);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(out_part_ids, d_p, (size_t)Q * P * 4, cudaMemcpyDeviceToHost, st));
+  if (out_part_dists_or_null)
+    CK(cudaMemcpyAsync(out_part_dists_or_null, d_pd, (size_t)Q * P * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+namespace {
+// Host-pointer front end shared by lb200_search and lb200_search_partitions: stages inputs in
+// device scratch (separate from the pipeline arena), runs the pipeline, copies results back.
+struct HostStage {
+  void* p = nullptr;
+  ~HostStage() { if (p) cudaFree(p); }
+};
+}  // namespace
+
+extern "C" int32_t lb200_search_partitions(lb200_index* ix, const float* queries, uint32_t Q,
+                                           const uint32_t* part_ids, uint32_t P, uint32_t k_prime,
+                                           const float* lower_or_null, const float* upper_or_null,
+                                           const uint64_t* const* part_bitmask_or_null, float* out_dist,
+                                           uint64_t* out_rowid, uint32_t* out_count) {
+  int rc = check_queries(ix, queries, Q);
+  if (rc) return rc;
+  if (Q && P && (!part_ids || !out_dist || !out_rowid || !out_count)) return set_err(LB200_EINVAL, "null argument");
+  if (k_prime == 0) return set_err(LB200_EINVAL, "k must be > 0");
+  if (!Q || !P) return 0;
+  for (size_t i = 0; i < (size_t)Q * P; i++)
+    if (part_ids[i] >= ix->nlist)  // ivf/v2.rs:288-293 "partition centroid {} does not exist"
+      return set_err(LB200_EINVAL, "partition centroid %u does not exist", part_ids[i]);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  cudaStream_t st = ix->stream;
+  const size_t nq = (size_t)Q * ix->dim * 4, np = (size_t)Q * P * 4, no = (size_t)Q * P * k_prime;
+  HostStage hs;
+  size_t total = Arena::pad(nq) + Arena::pad(np) + Arena::pad(no * 4) + Arena::pad(no * 8) + Arena::pad(np) +
+                 Arena::pad((size_t)ix->nlist * 8);
+  CK(cudaMalloc(&hs.p, total));
+  char* b = (char*)hs.p;
+  float* d_q = (float*)b; b += Arena::pad(nq);
+  uint32_t* d_p = (uint32_t*)b; b += Arena::pad(np);
+  float* d_od = (float*)b; b += Arena::pad(no * 4);
+  uint64_t* d_or = (uint64_t*)b; b += Arena::pad(no * 8);
+  uint32_t* d_oc = (uint32_t*)b; b += Arena::pad(np);
+  const uint64_t** d_bmp = (const uint64_t**)b;
+  CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(d_p, part_ids, np, cudaMemcpyHostToDevice, st));
+  // prefilter bitmasks: upload each partition's mask, then the pointer table
+  std::vector<void*> mask_bufs;
+  std::vector<const uint64_t*> h_ptrs;
+  struct Cleanup { std::vector<void*>& v; ~Cleanup() { for (void* p : v) cudaFree(p); } } cleanup{mask_bufs};
+  if (part_bitmask_or_null) {
+    h_ptrs.assign(ix->nlist, nullptr);
+    for (uint32_t p = 0; p < ix->nlist; p++) {
+      if (!part_bitmask_or_null[p]) continue;
+      uint64_t n = ix->h_part_off[p + 1] - ix->h_part_off[p];
+      size_t words = (size_t)((n + 63) / 64) + 1;
+      void* dm = nullptr;
+      CK(cudaMalloc(&dm, words * 8));
+      mask_bufs.push_back(dm);
+      CK(cudaMemsetAsync(dm, 0, words * 8, st));
+      CK(cudaMemcpyAsync(dm, part_bitmask_or_null[p], (words - 1) * 8, cudaMemcpyHostToDevice, st));
+      h_ptrs[p] = (const uint64_t*)dm;
+    }
+    CK(cudaMemcpyAsync((void*)d_bmp, h_ptrs.data(), (size_t)ix->nlist * 8, cudaMemcpyHostToDevice, st));
+  }
+  SearchArgs a = {};
+  a.d_queries = d_q; a.Q = Q; a.d_part_ids = d_p; a.P = P; a.k = k_prime; a.refine_factor = 0;
+  a.normalize = false; a.per_pair_output = true;
+  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
+  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
+  a.d_bitmask = part_bitmask_or_null ? d_bmp : nullptr;
+  a.d_out_dist = d_od; a.d_out_rowid = d_or; a.d_out_count = d_oc;
+  rc = search_pipeline(ix, a, st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(out_dist, d_od, no * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_rowid, d_or, no * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_count, d_oc, np, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int32_t lb200_search_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
+                                       uint32_t k, uint32_t refine_factor, const float* lower_or_null,
+                                       const float* upper_or_null, float* d_out_dist, uint64_t* d_out_rowid,
+                                       uint32_t* d_out_count, float* d_out_exact_or_null, void* stream) {
+  int rc = check_queries(ix, d_queries, Q);
+  if (rc) return rc;
+  if (Q && (!d_out_dist || !d_out_rowid || !d_out_count)) return set_err(LB200_EINVAL, "null output");
+  if (nprobes == 0) return set_err(LB200_EINVAL, "nprobes must be > 0");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+  SearchArgs a = {};
+  a.d_queries = d_queries; a.Q = Q; a.nprobes = nprobes; a.k = k; a.refine_factor = refine_factor;
+  a.normalize = true; a.shard_mode = d_out_exact_or_null != nullptr;
+  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
+  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
+  a.d_out_dist = d_out_dist; a.d_out_rowid = d_out_rowid; a.d_out_count = d_out_count;
+  a.d_out_exact = d_out_exact_or_null;
+  rc = search_pipeline(ix, a, st);
+  if (rc) return rc;
+  if (!stream) CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
+                                uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
+                                float* out_dist, uint64_t* out_rowid, uint32_t* out_count) {
+  int rc = check_queries(ix, queries, Q);
+  if (rc) return rc;
+  if (Q && (!out_dist || !out_rowid || !out_count)) return set_err(LB200_EINVAL, "null output");
+  if (k == 0) return set_err(LB200_EINVAL, "k must be > 0");
+  if (nprobes == 0) return set_err(LB200_EINVAL, "nprobes must be > 0");
+  if (!Q) return 0;
+  const bool refined = refine_factor > 0 && ix->d_raw;
+  if (refine_factor > 0 && !ix->d_raw) return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
+  const uint32_t ostride = refined ? k : k * std::max(refine_factor, 1u);
+  HostStage hs;
+  {
+    std::lock_guard<std::mutex> lk(ix->mu);
+    CK(cudaSetDevice(ix->device));
+  }
+  const size_t nq = (size_t)Q * ix->dim * 4, no = (size_t)Q * ostride;
+  CK(cudaMalloc(&hs.p, Arena::pad(nq) + Arena::pad(no * 4) + Arena::pad(no * 8) + Arena::pad((size_t)Q * 4)));
+  char* b = (char*)hs.p;
+  float* d_q = (float*)b; b += Arena::pad(nq);
+  float* d_od = (float*)b; b += Arena::pad(no * 4);
+  uint64_t* d_or = (uint64_t*)b; b += Arena::pad(no * 8);
+  uint32_t* d_oc = (uint32_t*)b;
+  cudaStream_t st = ix->stream;
+  CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
+  rc = lb200_search_device(ix, d_q, Q, nprobes, k, refine_factor, lower_or_null, upper_or_null, d_od, d_or, d_oc,
+                           nullptr, (void*)st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(out_dist, d_od, no * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_rowid, d_or, no * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_count, d_oc, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int32_t lb200_merge_topk_device(int32_t device_id, const float* d_dist, const uint64_t* d_rowid,
+                                           const float* d_exact_or_null, const uint32_t* d_count, uint32_t G,
+                                           uint32_t Q, uint32_t stride, uint32_t kprime, uint32_t k,
+                                           const float* lower_or_null, const float* upper_or_null,
+                                           float* d_out_dist, uint64_t* d_out_rowid, uint32_t* d_out_count,
+                                           void* stream) {
+  int rc = select_device(device_id);
+  if (rc) return rc;
+  if (!G || !Q) return 0;
+  if (!d_dist || !d_rowid || !d_count || !d_out_dist || !d_out_rowid || !d_out_count)
+    return set_err(LB200_EINVAL, "null argument");
+  if (kprime == 0 || k == 0 || kprime > stride * G) kprime = std::min(std::max(kprime, 1u), stride * G);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!d_exact_or_null) {
+    uint32_t kout = std::min(k, kprime);
+    rc = launch_merge(d_dist, d_rowid, nullptr, nullptr, d_count, Q, G, stride, stride, (size_t)Q * stride, 1, Q,
+                      kout, k, d_out_dist, d_out_rowid, nullptr, nullptr, d_out_count, st);
+    if (rc) return rc;
+  } else {
+    float *t_dist = nullptr, *t_exact = nullptr;
+    uint64_t* t_row = nullptr;
+    uint32_t* t_cnt = nullptr;
+    HostStage hs;
+    size_t n = (size_t)Q * kprime;
+    CK(cudaMalloc(&hs.p, Arena::pad(n * 4) * 2 + Arena::pad(n * 8) + Arena::pad((size_t)Q * 4)));
+    char* b = (char*)hs.p;
+    t_dist = (float*)b; b += Arena::pad(n * 4);
+    t_exact = (float*)b; b += Arena::pad(n * 4);
+    t_row = (uint64_t*)b; b += Arena::pad(n * 8);
+    t_cnt = (uint32_t*)b;
+    rc = launch_merge(d_dist, d_rowid, nullptr, d_exact_or_null, d_count, Q, G, stride, stride, (size_t)Q * stride, 1,
+                      Q, kprime, kprime, t_dist, t_row, nullptr, t_exact, t_cnt, st);
+    if (rc) return rc;
+    rerank_kernel<<<(Q * 32 + 127) / 128, 128, 0, st>>>(t_exact, t_row, t_cnt, Q, kprime, k, lower_or_null != nullptr,
+                                                      lower_or_null ? *lower_or_null : 0.f,
+                                                      upper_or_null != nullptr, upper_or_null ? *upper_or_null : 0.f,
+                                                      d_out_dist, d_out_rowid, d_out_count);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));  // scratch is freed on return
+  }
+  return 0;
+}

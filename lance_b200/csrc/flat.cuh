@@ -1,0 +1,176 @@
+// flat.cuh -- K7 flat brute-force kNN (KNNVectorDistanceExec path, BASELINE config 2).
+//
+// Replaces compute_distance (rust/lance-index/src/vector/flat.rs:28-86) ->
+// {l2,cosine,dot}_distance_arrow_batch (rust/lance-linalg/src/distance/l2.rs:288,
+// cosine.rs:315, dot.rs:270) and the SortExec(fetch=k) + NOT NULL filter that follows it
+// (rust/lance/src/dataset/scanner.rs:2066-2136).
+#pragma once
+#include "coarse.cuh"
+
+namespace lb200 {
+
+constexpr int FLAT_TQ = 4;
+constexpr int FLAT_THREADS = 128;
+
+// out[q][row] = metric distance (exact reference order); NaN for null rows.
+__global__ void __launch_bounds__(FLAT_THREADS)
+flat_dist_kernel(int metric, const float* __restrict__ queries, uint32_t Q, const float* __restrict__ vectors,
+                 const uint8_t* __restrict__ validity, uint64_t n, uint32_t d, float* __restrict__ out,
+                 size_t out_stride) {
+  extern __shared__ float sq[];  // [TQ][d] + [TQ] norms
+  float* snorm = sq + FLAT_TQ * d;
+  const uint32_t q0 = blockIdx.y * FLAT_TQ;
+  for (uint32_t i = threadIdx.x; i < FLAT_TQ * d; i += FLAT_THREADS) {
+    uint32_t qq = q0 + i / d;
+    sq[i] = qq < Q ? queries[(size_t)qq * d + (i % d)] : 0.0f;
+  }
+  __syncthreads();
+  if (threadIdx.x < FLAT_TQ) snorm[threadIdx.x] = metric == 1 ? norm_l2(sq + threadIdx.x * d, (int)d) : 0.0f;
+  __syncthreads();
+  uint64_t row = (uint64_t)blockIdx.x * FLAT_THREADS + threadIdx.x;
+  if (row >= n) return;
+  const bool valid = !validity || ((validity[row >> 3] >> (row & 7)) & 1);
+  const float* y = vectors + row * d;
+#pragma unroll
+  for (int t = 0; t < FLAT_TQ; t++) {
+    if (q0 + t >= Q) break;
+    float v = __int_as_float(0x7fc00000);
+    if (valid) v = exact_distance(metric, sq + t * d, snorm[t], y, (int)d);
+    out[(size_t)(q0 + t) * out_stride + row] = v;
+  }
+}
+
+// Per-query top-k of a distance row by (total-order key, row index): 3-level radix select on
+// the 32-bit ordered key, then an unordered gather of keys < T plus an index-ordered gather of
+// the ties, then a small bitonic sort.  One block (256 threads) per query.  k <= 1024.
+__global__ void __launch_bounds__(256)
+flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t n, uint32_t k, uint32_t kpow2,
+                   int has_lower, float lower, int has_upper, float upper, float* __restrict__ out_dist,
+                   uint64_t* __restrict__ out_idx, uint32_t* __restrict__ out_cnt) {
+  extern __shared__ unsigned long long sl[];  // [kpow2] result list
+  __shared__ uint32_t hist[4096];
+  __shared__ uint32_t s_prefix, s_mask, s_kk, s_less, s_fill, s_tiebase, s_wsum[8];
+  const uint32_t q = blockIdx.x;
+  const float* drow = dist + (size_t)q * dist_stride;
+  auto admissible = [&](float v) {
+    bool ok = v == v;
+    if (has_lower) ok = ok && v >= lower;
+    if (has_upper) ok = ok && v < upper;
+    return ok;
+  };
+  if (threadIdx.x == 0) {
+    s_prefix = 0;
+    s_mask = 0;
+    s_kk = k;  // rank still to be located inside the current prefix bucket
+    s_less = 0;
+  }
+  __syncthreads();
+  // total admissible count decides whether a k-th element exists
+  const int shifts[3] = {20, 8, 0};
+  const int widths[3] = {12, 12, 8};
+  bool have_kth = true;
+  for (int lvl = 0; lvl < 3 && have_kth; lvl++) {
+    for (uint32_t i = threadIdx.x; i < 4096; i += 256) hist[i] = 0;
+    __syncthreads();
+    const uint32_t prefix = s_prefix, mask = s_mask;
+    for (uint64_t i = threadIdx.x; i < n; i += 256) {
+      float v = drow[i];
+      if (!admissible(v)) continue;
+      uint32_t key = ordered_key(v);
+      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shifts[lvl]) & ((1u << widths[lvl]) - 1u)], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t kk = s_kk, cum = 0, b = 0, nb = 1u << widths[lvl];
+      for (; b < nb; b++) {
+        if (cum + hist[b] >= kk) break;
+        cum += hist[b];
+      }
+      if (b == nb) {
+        s_kk = 0xffffffffu;  // fewer than k admissible rows: take everything
+      } else {
+        s_less += cum;
+        s_kk = kk - cum;
+        s_prefix = prefix | (b << shifts[lvl]);
+        s_mask = mask | (((1u << widths[lvl]) - 1u) << shifts[lvl]);
+      }
+    }
+    __syncthreads();
+    have_kth = s_kk != 0xffffffffu;
+  }
+  const uint32_t T = have_kth ? s_prefix : 0xffffffffu;  // k-th smallest key
+  const uint32_t nless = have_kth ? s_less : 0;          // #keys < T (when have_kth)
+  const uint32_t need_ties = have_kth ? k - nless : 0;
+  for (uint32_t i = threadIdx.x; i < kpow2; i += 256) sl[i] = ~0ull;
+  if (threadIdx.x == 0) {
+    s_fill = 0;
+    s_tiebase = 0;
+  }
+  __syncthreads();
+  if (!have_kth) {
+    // fewer than k admissible rows: gather all of them (count < k <= kpow2)
+    for (uint64_t i = threadIdx.x; i < n; i += 256) {
+      float v = drow[i];
+      if (!admissible(v)) continue;
+      uint32_t o = atomicAdd(&s_fill, 1u);
+      sl[o] = ((unsigned long long)ordered_key(v) << 32) | (uint32_t)i;
+    }
+  } else {
+    // keys < T: unordered; keys == T: first need_ties in index order (block-ordered compaction)
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (uint64_t base = 0; base < n; base += 256) {
+      uint64_t i = base + threadIdx.x;
+      bool tie = false;
+      if (i < n) {
+        float v = drow[i];
+        if (admissible(v)) {
+          uint32_t key = ordered_key(v);
+          if (key < T) {
+            uint32_t o = atomicAdd(&s_fill, 1u);
+            sl[o] = ((unsigned long long)key << 32) | (uint32_t)i;
+          }
+          tie = key == T;
+        }
+      }
+      uint32_t bal = __ballot_sync(0xffffffffu, tie);
+      if (lane == 0) s_wsum[w] = __popc(bal);
+      __syncthreads();
+      uint32_t before = s_tiebase;
+      for (uint32_t ww = 0; ww < w; ww++) before += s_wsum[ww];
+      uint32_t r = before + __popc(bal & ((1u << lane) - 1u));
+      if (tie && r < need_ties) sl[nless + r] = ((unsigned long long)T << 32) | (uint32_t)i;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+        for (int ww = 0; ww < 8; ww++) tot += s_wsum[ww];
+        s_tiebase += tot;
+      }
+      __syncthreads();
+      if (s_tiebase >= need_ties && base + 256 < n) {
+        // ties satisfied: finish the (key < T) gather without the ordered machinery
+        for (uint64_t j = base + 256 + threadIdx.x; j < n; j += 256) {
+          float v = drow[j];
+          if (!admissible(v)) continue;
+          uint32_t key = ordered_key(v);
+          if (key < T) {
+            uint32_t o = atomicAdd(&s_fill, 1u);
+            sl[o] = ((unsigned long long)key << 32) | (uint32_t)j;
+          }
+        }
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t cnt = have_kth ? k : s_fill;
+  block_bitonic_sort_u64(sl, kpow2);
+  for (uint32_t i = threadIdx.x; i < k; i += 256) {
+    unsigned long long v = sl[i];
+    bool ok = i < cnt;
+    out_dist[(size_t)q * k + i] = ok ? key_to_float((uint32_t)(v >> 32)) : __int_as_float(0x7f800000);
+    out_idx[(size_t)q * k + i] = ok ? (uint64_t)(uint32_t)v : ~0ull;
+  }
+  if (threadIdx.x == 0) out_cnt[q] = cnt;
+}
+
+}  // namespace lb200

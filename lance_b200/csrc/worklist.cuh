@@ -1,0 +1,262 @@
+// worklist.cuh -- device-side scheduling of (query, partition) pairs, K5 merge and K6 refine.
+#pragma once
+#include "select.cuh"
+
+namespace lb200 {
+
+// Repack the reference layout (concat over p of transposed [M][n_p], pq/storage.rs:357-377)
+// into tile16 layout: partition p starts at tile tile_off[p]; tile t = [M][16] bytes.
+__global__ void repack_codes_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ part_off,
+                                    const uint64_t* __restrict__ tile_off, uint32_t nlist, uint32_t M,
+                                    uint8_t* __restrict__ dst) {
+  // one block per partition-slice: blockIdx.x = partition, blockIdx.y strides over tiles
+  uint32_t p = blockIdx.x;
+  uint64_t o = part_off[p], n = part_off[p + 1] - o;
+  uint64_t ntile = (n + 15) >> 4;
+  const uint8_t* s = src + o * M;
+  uint8_t* d = dst + tile_off[p] * 16 * M;
+  uint64_t total = ntile * 16 * M;
+  for (uint64_t i = (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; i < total;
+       i += (uint64_t)gridDim.y * blockDim.x) {
+    uint64_t t = i / (16 * M);
+    uint32_t r = (uint32_t)(i - t * 16 * M);
+    uint32_t m = r >> 4, k = r & 15;
+    uint64_t row = t * 16 + k;
+    d[i] = row < n ? s[(uint64_t)m * n + row] : 0;
+  }
+}
+
+// Step 1: histogram of probed partitions; rank[e] = arrival order of pair e in its partition.
+__global__ void count_pairs_kernel(const uint32_t* __restrict__ probes, uint32_t npairs,
+                                   uint32_t* __restrict__ cnt, uint32_t* __restrict__ rank) {
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < npairs) rank[e] = atomicAdd(&cnt[probes[e]], 1u);
+}
+
+// Step 2 (single block): exclusive scans over partitions -> pair offsets and item offsets.
+// items(p) = ceil(cnt[p]/QL) * ceil(n_p/chunk_vecs).  Also accumulates the algorithmic scan
+// bytes sum_pairs n_p * M and the pair count into stats[0..1].
+__global__ void __launch_bounds__(1024)
+offsets_kernel(const uint32_t* __restrict__ cnt, const uint64_t* __restrict__ part_off, uint32_t nlist,
+               uint32_t QL, uint32_t chunk_vecs, uint32_t M, uint32_t* __restrict__ pair_off,
+               uint32_t* __restrict__ item_off, unsigned long long* __restrict__ stats) {
+  __shared__ uint32_t s_pairs[1024], s_items[1024];
+  __shared__ uint32_t carry_pairs, carry_items;
+  __shared__ unsigned long long s_bytes;
+  if (threadIdx.x == 0) {
+    carry_pairs = 0;
+    carry_items = 0;
+    s_bytes = 0;
+  }
+  __syncthreads();
+  unsigned long long bytes = 0;
+  for (uint32_t base = 0; base < nlist; base += 1024) {
+    uint32_t p = base + threadIdx.x;
+    uint32_t c = 0, it = 0;
+    if (p < nlist) {
+      c = cnt[p];
+      uint64_t n = part_off[p + 1] - part_off[p];
+      uint32_t nch = (uint32_t)((n + chunk_vecs - 1) / chunk_vecs);
+      it = ((c + QL - 1) / QL) * nch;
+      bytes += (unsigned long long)c * n * M;
+    }
+    s_pairs[threadIdx.x] = c;
+    s_items[threadIdx.x] = it;
+    __syncthreads();
+    // Hillis-Steele inclusive scan over 1024 entries
+    for (uint32_t off = 1; off < 1024; off <<= 1) {
+      uint32_t a = 0, b = 0;
+      if (threadIdx.x >= off) {
+        a = s_pairs[threadIdx.x - off];
+        b = s_items[threadIdx.x - off];
+      }
+      __syncthreads();
+      s_pairs[threadIdx.x] += a;
+      s_items[threadIdx.x] += b;
+      __syncthreads();
+    }
+    if (p < nlist) {
+      pair_off[p] = carry_pairs + s_pairs[threadIdx.x] - c;
+      item_off[p] = carry_items + s_items[threadIdx.x] - it;
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) {
+      carry_pairs += s_pairs[1023];
+      carry_items += s_items[1023];
+    }
+    __syncthreads();
+  }
+  atomicAdd(&s_bytes, bytes);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pair_off[nlist] = carry_pairs;
+    item_off[nlist] = carry_items;
+    stats[0] = s_bytes;
+    stats[1] = carry_pairs;
+  }
+}
+
+// Step 3: scatter pair ids into partition-grouped order.
+__global__ void scatter_pairs_kernel(const uint32_t* __restrict__ probes, const uint32_t* __restrict__ rank,
+                                     const uint32_t* __restrict__ pair_off, uint32_t npairs,
+                                     uint32_t* __restrict__ pair_list) {
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < npairs) pair_list[pair_off[probes[e]] + rank[e]] = e;
+}
+
+// ---------------------------------------------------------------------------------------
+// K5 merge: for each output group g, the `L` candidate lists [g*L, (g+1)*L) (each <= stride
+// valid entries, count in cnt[]) are merged to the `kout` smallest by (distance,row id).
+// == concat_batches + sort_to_indices(limit) of ivf/v2.rs:383-400 (and the DataFusion
+// SortExec fetch=k' of scanner.rs:2147-2157).  One block per group; block-wide bitonic sort of
+// (key<<32 | src index) with a row-id tie-break inside the comparator.
+__device__ __forceinline__ bool merge_less(unsigned long long a, unsigned long long b,
+                                           const uint64_t* __restrict__ rowid) {
+  uint32_t ka = (uint32_t)(a >> 32), kb = (uint32_t)(b >> 32);
+  if (ka != kb) return ka < kb;
+  if (ka == 0xffffffffu) return (uint32_t)a < (uint32_t)b;  // padding
+  uint64_t ra = rowid[(uint32_t)a], rb = rowid[(uint32_t)b];
+  if (ra != rb) return ra < rb;
+  return (uint32_t)a < (uint32_t)b;
+}
+
+// Addressing: entry r of list l of group g lives at g*group_stride + l*list_stride + r;
+// its count at g*cnt_gs + l*cnt_ls (covers both [group][list][r] and [list][group][r] inputs).
+__global__ void __launch_bounds__(256)
+merge_lists_kernel(const float* __restrict__ in_dist, const uint64_t* __restrict__ in_rowid,
+                   const uint64_t* __restrict__ in_pos /*or null*/, const float* __restrict__ in_aux /*or null*/,
+                   const uint32_t* __restrict__ in_cnt, uint32_t L, uint32_t stride,
+                   size_t group_stride, size_t list_stride, size_t cnt_gs, size_t cnt_ls,
+                   uint32_t npow2, uint32_t kout, uint32_t out_stride, float* __restrict__ out_dist,
+                   uint64_t* __restrict__ out_rowid, uint64_t* __restrict__ out_pos /*or null*/,
+                   float* __restrict__ out_aux /*or null*/, uint32_t* __restrict__ out_cnt) {
+  extern __shared__ unsigned long long sk[];
+  __shared__ uint32_t s_n;
+  const uint32_t g = blockIdx.x;
+  const size_t base = (size_t)g * group_stride;
+  if (threadIdx.x == 0) s_n = 0;
+  __syncthreads();
+  // the low word of a sort key is the entry's offset from `base` (must fit 32 bits)
+  for (uint32_t i = threadIdx.x; i < npow2; i += blockDim.x) {
+    unsigned long long v = ~0ull;
+    if (i < L * stride) {
+      uint32_t l = i / stride, r = i - l * stride;
+      if (r < in_cnt[(size_t)g * cnt_gs + (size_t)l * cnt_ls]) {
+        size_t off = (size_t)l * list_stride + r;
+        v = ((unsigned long long)ordered_key(in_dist[base + off]) << 32) | (uint32_t)off;
+        atomicAdd(&s_n, 1u);
+      }
+    }
+    sk[i] = v;
+  }
+  __syncthreads();
+  const uint64_t* rid = in_rowid + base;
+  for (uint32_t k = 2; k <= npow2; k <<= 1) {
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t i = threadIdx.x; i < npow2; i += blockDim.x) {
+        uint32_t ixj = i ^ j;
+        if (ixj > i) {
+          unsigned long long a = sk[i], b = sk[ixj];
+          bool up = (i & k) == 0;
+          bool a_gt_b = merge_less(b, a, rid);
+          if (a_gt_b == up) {
+            sk[i] = b;
+            sk[ixj] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  const uint32_t n = min(s_n, kout);
+  for (uint32_t i = threadIdx.x; i < kout; i += blockDim.x) {
+    size_t o = (size_t)g * out_stride + i;
+    if (i < n) {
+      uint32_t src = (uint32_t)sk[i];
+      out_dist[o] = in_dist[base + src];
+      out_rowid[o] = in_rowid[base + src];
+      if (out_pos) out_pos[o] = in_pos[base + src];
+      if (out_aux) out_aux[o] = in_aux[base + src];
+    } else {
+      out_dist[o] = __int_as_float(0x7f800000);
+      out_rowid[o] = ~0ull;
+      if (out_pos) out_pos[o] = ~0ull;
+      if (out_aux) out_aux[o] = __int_as_float(0x7fc00000);
+    }
+  }
+  if (threadIdx.x == 0) out_cnt[g] = n;
+}
+
+// ---------------------------------------------------------------------------------------
+// K6 refine, part 1: exact distance of every merged ANN candidate on the raw vectors with the
+// ORIGINAL query and the INDEX metric (scanner.rs:1706-1721 -> flat_knn -> compute_distance,
+// flat.rs:28-86).  One thread per candidate keeps the reference's lane structure exactly.
+__global__ void refine_distance_kernel(int metric, const float* __restrict__ queries /*original*/,
+                                       const float* __restrict__ raw, uint32_t dim,
+                                       const uint64_t* __restrict__ pos, const uint32_t* __restrict__ cnt,
+                                       uint32_t Q, uint32_t kprime, float* __restrict__ exact) {
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= Q * kprime) return;
+  uint32_t q = e / kprime, r = e - q * kprime;
+  float out = __int_as_float(0x7fc00000);
+  if (r < cnt[q]) {
+    const float* x = queries + (size_t)q * dim;
+    float xn = metric == 1 ? norm_l2(x, (int)dim) : 0.0f;
+    out = exact_distance(metric, x, xn, raw + (size_t)pos[e] * dim, (int)dim);
+  }
+  exact[e] = out;
+}
+
+// K6 part 2 (and the re-rank half of the multi-GPU merge): among the first cnt[q] candidates
+// keep those with lower <= exact < upper, order by (exact,row id), emit the first k.
+// == FilterExec(bounds) + SortExec(fetch=k) + NOT NULL of scanner.rs:2066-2136.
+// One warp per query; kprime <= 1024.
+__global__ void rerank_kernel(const float* __restrict__ exact, const uint64_t* __restrict__ rowid,
+                              const uint32_t* __restrict__ cnt, uint32_t Q, uint32_t kprime,
+                              uint32_t k, int has_lower, float lower, int has_upper, float upper,
+                              float* __restrict__ out_dist, uint64_t* __restrict__ out_rowid,
+                              uint32_t* __restrict__ out_cnt) {
+  uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (q >= Q) return;
+  const float* ex = exact + (size_t)q * kprime;
+  const uint64_t* rid = rowid + (size_t)q * kprime;
+  uint32_t n = cnt[q];
+  uint32_t nvalid = 0;
+  for (uint32_t i = lane; i < k; i += 32) {
+    out_dist[(size_t)q * k + i] = __int_as_float(0x7f800000);
+    out_rowid[(size_t)q * k + i] = ~0ull;
+  }
+  __syncwarp();
+  for (uint32_t i = lane; i < ((n + 31) & ~31u); i += 32) {
+    bool ok = false;
+    float di = 0.0f;
+    uint64_t ri = 0;
+    if (i < n) {
+      di = ex[i];
+      ri = rid[i];
+      ok = di == di;  // IS NOT NULL
+      if (has_lower) ok = ok && (di >= lower);
+      if (has_upper) ok = ok && (di < upper);
+    }
+    if (ok) {
+      uint32_t ki = ordered_key(di), r = 0;
+      for (uint32_t j = 0; j < n; j++) {
+        float dj = ex[j];
+        bool okj = dj == dj;
+        if (has_lower) okj = okj && (dj >= lower);
+        if (has_upper) okj = okj && (dj < upper);
+        if (!okj || j == i) continue;
+        uint32_t kj = ordered_key(dj);
+        if (kj < ki || (kj == ki && (rid[j] < ri || (rid[j] == ri && j < i)))) r++;
+      }
+      if (r < k) {
+        out_dist[(size_t)q * k + r] = di;
+        out_rowid[(size_t)q * k + r] = ri;
+      }
+    }
+    nvalid += __popc(__ballot_sync(FULL, ok));
+  }
+  if (lane == 0) out_cnt[q] = min(nvalid, k);
+}
+
+}  // namespace lb200

@@ -1,0 +1,218 @@
+"""Host-side mirror of the reference's operator surface for the IVF_PQ query path.
+
+Names, argument meaning and error behaviour follow `trait VectorIndex`
+(rust/lance-index/src/vector.rs:117-217), `Query` (vector.rs:59-91), `DistanceType`
+(rust/lance-linalg/src/distance.rs:36-43) and `compute_distance`
+(rust/lance-index/src/vector/flat.rs:28-86); every method is a thin call into the C ABI
+(include/lance_b200.h) and is batched over queries.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from . import _lib
+from ._lib import Stats, check
+
+
+class DistanceType:
+    L2 = "l2"
+    Cosine = "cosine"
+    Dot = "dot"
+    _CODE = {"l2": 0, "cosine": 1, "dot": 2}
+
+    @staticmethod
+    def code(m):
+        try:
+            return DistanceType._CODE[str(m).lower()]
+        except KeyError:
+            # DistanceType::try_from (distance.rs:87-103)
+            raise ValueError(f"Metric type '{m}' is not supported") from None
+
+
+@dataclass
+class Query:
+    """vector.rs:59-91.  `key` may be one vector [d] or a batch [Q][d]."""
+    key: np.ndarray
+    k: int = 10
+    nprobes: int = 1
+    refine_factor: Optional[int] = None
+    lower_bound: Optional[float] = None
+    upper_bound: Optional[float] = None
+    column: str = "vector"
+    metric_type: str = "l2"
+    use_index: bool = True
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fptr(v):
+    return None if v is None else C.byref(C.c_float(float(v)))
+
+
+class IvfPqIndex:
+    """Device-resident IVFIndex<FlatIndex, ProductQuantizer> (lance/src/index/vector/ivf/v2.rs:76)."""
+
+    def __init__(self, data, device_id=0):
+        L = _lib.lib()
+        self._L = L
+        self.metric = data.metric
+        self.dim, self.nlist, self.M = int(data.dim), int(data.nlist), int(data.M)
+        self.part_offsets = np.ascontiguousarray(data.part_offsets, dtype=np.uint64)
+        self.has_raw = data.raw_vectors is not None
+        self.device_id = device_id
+        h = C.c_void_p()
+        cents, cb = _f32(data.centroids), _f32(data.codebook)
+        codes = np.ascontiguousarray(data.codes, dtype=np.uint8)
+        rids = np.ascontiguousarray(data.row_ids, dtype=np.uint64)
+        raw = None if data.raw_vectors is None else _f32(data.raw_vectors)
+        check(L.lb200_index_create(
+            C.c_int32(device_id), C.c_int32(DistanceType.code(data.metric)), C.c_uint32(self.dim),
+            C.c_uint32(self.nlist), _p(cents), C.c_uint32(self.M), C.c_uint32(8), _p(cb),
+            _p(self.part_offsets), _p(codes), _p(rids), _p(raw), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lb200_index_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # -- VectorIndex surface ----------------------------------------------------------------
+    def metric_type(self):
+        return self.metric
+
+    def find_partitions(self, key, nprobes, return_distances=False):
+        """VectorIndex::find_partitions (vector.rs:146), batched.  Key used as given."""
+        key = np.atleast_2d(_f32(key))
+        self._check_dim(key)
+        Q = key.shape[0]
+        P = min(int(nprobes), self.nlist)
+        ids = np.zeros((Q, P), dtype=np.uint32)
+        d = np.zeros((Q, P), dtype=np.float32) if return_distances else None
+        check(self._L.lb200_find_partitions(self._h, _p(key), C.c_uint32(Q), C.c_uint32(nprobes), _p(ids), _p(d)))
+        return (ids, d) if return_distances else ids
+
+    def search_in_partition(self, part_ids, key, k, lower_bound=None, upper_bound=None, prefilter=None):
+        """VectorIndex::search_in_partition (vector.rs:165) for [Q][P] explicit partitions.
+        prefilter: optional dict {partition id: bool/0-1 array over that partition's rows}."""
+        key = np.atleast_2d(_f32(key))
+        self._check_dim(key)
+        Q = key.shape[0]
+        part_ids = np.ascontiguousarray(np.asarray(part_ids, dtype=np.uint32).reshape(Q, -1))
+        P = part_ids.shape[1]
+        od = np.full((Q, P, max(k, 1)), np.inf, dtype=np.float32)
+        oi = np.full((Q, P, max(k, 1)), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros((Q, P), dtype=np.uint32)
+        bm_arr, keep = None, []
+        if prefilter is not None:
+            ptrs = (C.c_void_p * self.nlist)()
+            for p, mask in prefilter.items():
+                n = int(self.part_offsets[p + 1] - self.part_offsets[p])
+                bits = np.zeros(((n + 63) // 64) * 8 + 8, dtype=np.uint8)
+                packed = np.packbits(np.asarray(mask, dtype=bool)[:n], bitorder="little")
+                bits[:packed.size] = packed
+                keep.append(bits)
+                ptrs[p] = bits.ctypes.data
+            bm_arr = ptrs
+        check(self._L.lb200_search_partitions(
+            self._h, _p(key), C.c_uint32(Q), _p(part_ids), C.c_uint32(P), C.c_uint32(k), _fptr(lower_bound),
+            _fptr(upper_bound), bm_arr, _p(od), _p(oi), _p(oc)))
+        return od, oi, oc
+
+    def search(self, query: Query):
+        """VectorIndex::search (vector.rs:133) + the scanner's refine when refine_factor is set.
+        Returns (distances [Q][k_out], row ids [Q][k_out], counts [Q])."""
+        key = np.atleast_2d(_f32(query.key))
+        self._check_dim(key)
+        if query.k <= 0:
+            raise ValueError("k must be positive")  # scanner.rs:642 nearest() validation
+        Q = key.shape[0]
+        rf = int(query.refine_factor or 0)
+        kout = query.k if (rf and self.has_raw) else query.k * max(rf, 1)
+        od = np.full((Q, kout), np.inf, dtype=np.float32)
+        oi = np.full((Q, kout), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros(Q, dtype=np.uint32)
+        check(self._L.lb200_search(
+            self._h, _p(key), C.c_uint32(Q), C.c_uint32(query.nprobes), C.c_uint32(query.k), C.c_uint32(rf),
+            _fptr(query.lower_bound), _fptr(query.upper_bound), _p(od), _p(oi), _p(oc)))
+        return od, oi, oc
+
+    # -- device-pointer entry (benchmark / multi-GPU plumbing) -------------------------------
+    def search_device(self, d_queries_ptr, Q, nprobes, k, refine_factor, d_out_dist, d_out_rowid, d_out_count,
+                      d_out_exact=None, stream=None, lower=None, upper=None):
+        check(self._L.lb200_search_device(
+            self._h, C.c_void_p(d_queries_ptr), C.c_uint32(Q), C.c_uint32(nprobes), C.c_uint32(k),
+            C.c_uint32(refine_factor), _fptr(lower), _fptr(upper), C.c_void_p(d_out_dist), C.c_void_p(d_out_rowid),
+            C.c_void_p(d_out_count), C.c_void_p(d_out_exact) if d_out_exact else None,
+            C.c_void_p(stream) if stream else None))
+
+    def set_profiling(self, on=True):
+        check(self._L.lb200_set_profiling(self._h, C.c_int32(1 if on else 0)))
+
+    def set_scan_variant(self, v):
+        check(self._L.lb200_set_scan_variant(self._h, C.c_int32(v)))
+
+    def stats(self):
+        s = Stats()
+        check(self._L.lb200_get_stats(self._h, C.byref(s)))
+        return {f: getattr(s, f) for f, _ in Stats._fields_}
+
+    def _check_dim(self, key):
+        if key.shape[1] != self.dim:
+            # scanner.rs:642-700: "query dim({}) doesn't match the column {} vector dim({})"
+            raise ValueError(f"query dim({key.shape[1]}) doesn't match the index vector dim({self.dim})")
+
+
+def merge_topk_device(device_id, d_dist, d_rowid, d_exact, d_count, G, Q, stride, kprime, k, d_out_dist,
+                      d_out_rowid, d_out_count, lower=None, upper=None, stream=None):
+    check(_lib.lib().lb200_merge_topk_device(
+        C.c_int32(device_id), C.c_void_p(d_dist), C.c_void_p(d_rowid), C.c_void_p(d_exact) if d_exact else None,
+        C.c_void_p(d_count), C.c_uint32(G), C.c_uint32(Q), C.c_uint32(stride), C.c_uint32(kprime), C.c_uint32(k),
+        _fptr(lower), _fptr(upper), C.c_void_p(d_out_dist), C.c_void_p(d_out_rowid), C.c_void_p(d_out_count),
+        C.c_void_p(stream) if stream else None))
+
+
+def compute_distance(key, metric, vectors, validity=None, device_id=0):
+    """compute_distance (flat.rs:28-86): `_distance` column for a batch; NaN where null.
+    key [d] or [Q][d]; vectors [n][d]; validity: Arrow bitmap bytes (bit set = valid) or None."""
+    key2 = np.atleast_2d(_f32(key))
+    vectors = _f32(vectors)
+    if vectors.ndim != 2 or key2.shape[1] != vectors.shape[1]:
+        raise ValueError("dimension mismatch between key and vectors")
+    Q, n = key2.shape[0], vectors.shape[0]
+    out = np.zeros((Q, n), dtype=np.float32)
+    v = None if validity is None else np.ascontiguousarray(validity, dtype=np.uint8)
+    check(_lib.lib().lb200_flat_distance(C.c_int32(device_id), C.c_int32(DistanceType.code(metric)),
+                                         C.c_uint32(vectors.shape[1]), _p(key2), C.c_uint32(Q), _p(vectors), _p(v),
+                                         C.c_uint64(n), _p(out)))
+    return out[0] if np.ndim(key) == 1 else out
+
+
+def flat_knn(key, metric, vectors, k, validity=None, lower_bound=None, upper_bound=None, device_id=0):
+    """Scanner::flat_knn (scanner.rs:2066-2136): KNNVectorDistanceExec -> bounds -> SortExec(fetch=k)
+    -> NOT NULL.  Returns (distances [Q][k], row positions [Q][k], counts [Q])."""
+    key2 = np.atleast_2d(_f32(key))
+    vectors = _f32(vectors)
+    if vectors.ndim != 2 or key2.shape[1] != vectors.shape[1]:
+        raise ValueError("dimension mismatch between key and vectors")
+    if k <= 0:
+        raise ValueError("k must be positive")
+    Q, n = key2.shape[0], vectors.shape[0]
+    od = np.full((Q, k), np.inf, dtype=np.float32)
+    oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+    oc = np.zeros(Q, dtype=np.uint32)
+    v = None if validity is None else np.ascontiguousarray(validity, dtype=np.uint8)
+    check(_lib.lib().lb200_flat_topk(C.c_int32(device_id), C.c_int32(DistanceType.code(metric)),
+                                     C.c_uint32(vectors.shape[1]), _p(key2), C.c_uint32(Q), _p(vectors), _p(v),
+                                     C.c_uint64(n), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound), _p(od),
+                                     _p(oi), _p(oc)))
+    return od, oi, oc

@@ -1,0 +1,217 @@
+"""ctypes binding of the CPU oracle (oracle/lance_oracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py.  Nothing under lance_b200/ imports it.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liblance_oracle.so")
+
+L2, COSINE, DOT = 0, 1, 2
+METRICS = {"l2": L2, "cosine": COSINE, "dot": DOT}
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "lance_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-B"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+class _Index(C.Structure):
+    _fields_ = [
+        ("metric", C.c_int32), ("dim", C.c_uint32), ("nlist", C.c_uint32), ("M", C.c_uint32),
+        ("centroids", C.c_void_p), ("codebook", C.c_void_p), ("part_offsets", C.c_void_p),
+        ("codes", C.c_void_p), ("row_ids", C.c_void_p), ("raw_vectors", C.c_void_p),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_SO)
+        f = _lib
+        f.lo_l2.restype = C.c_float
+        f.lo_dot.restype = C.c_float
+        f.lo_dot_distance.restype = C.c_float
+        f.lo_norm_l2.restype = C.c_float
+        f.lo_cosine_fast.restype = C.c_float
+        f.lo_pq_distance_one.restype = C.c_float
+        f.lo_find_partitions.restype = C.c_uint32
+        f.lo_search_in_partition.restype = C.c_uint32
+        f.lo_search_one.restype = C.c_uint32
+        f.lo_flat_knn_one.restype = C.c_uint32
+        f.lo_max_threads.restype = C.c_int
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def l2(x, y):
+    x, y = _f32(x), _f32(y)
+    return float(lib().lo_l2(_p(x), _p(y), C.c_size_t(x.size)))
+
+
+def dot(x, y):
+    x, y = _f32(x), _f32(y)
+    return float(lib().lo_dot(_p(x), _p(y), C.c_size_t(x.size)))
+
+
+def norm_l2(x):
+    x = _f32(x)
+    return float(lib().lo_norm_l2(_p(x), C.c_size_t(x.size)))
+
+
+def normalize(x):
+    x = _f32(x)
+    out = np.empty_like(x)
+    lib().lo_normalize(_p(x), C.c_size_t(x.size), _p(out))
+    return out
+
+
+def distance_batch(metric, q, vectors):
+    """DistanceType::arrow_batch_func: one query against [n][d] rows -> [n] f32."""
+    q, vectors = _f32(q), _f32(vectors)
+    n, d = vectors.shape
+    out = np.empty(n, dtype=np.float32)
+    lib().lo_distance_batch(C.c_int(METRICS[metric]), _p(q), _p(vectors), C.c_size_t(n),
+                            C.c_size_t(d), _p(out))
+    return out
+
+
+def find_partitions(centroids, query, nprobes, metric):
+    centroids, query = _f32(centroids), _f32(query)
+    nlist, d = centroids.shape
+    lim = min(nprobes, nlist)
+    ids = np.empty(max(lim, 1), dtype=np.uint32)
+    dists = np.empty(max(lim, 1), dtype=np.float32)
+    m = METRICS[metric]
+    n = lib().lo_find_partitions(_p(centroids), C.c_uint32(nlist), C.c_uint32(d), _p(query),
+                                 C.c_uint32(nprobes), C.c_int(DOT if m == DOT else L2), _p(ids),
+                                 _p(dists))
+    return ids[:n], dists[:n]
+
+
+def build_distance_table(metric, codebook, query):
+    """codebook [M][256][dsub]; returns [M][256]."""
+    codebook, query = _f32(codebook), _f32(query)
+    M = codebook.shape[0]
+    out = np.empty((M, 256), dtype=np.float32)
+    m = METRICS[metric]
+    lib().lo_build_distance_table(C.c_int(DOT if m == DOT else L2), _p(codebook), C.c_uint32(M),
+                                  C.c_uint32(query.size), _p(query), _p(out))
+    return out
+
+
+def compute_pq_distance(table, codes_t):
+    """table [M][256], codes_t transposed [M][n] u8 -> [n] f32."""
+    table = _f32(table)
+    codes_t = np.ascontiguousarray(codes_t, dtype=np.uint8)
+    M, n = codes_t.shape
+    out = np.empty(n, dtype=np.float32)
+    lib().lo_compute_pq_distance(_p(table), C.c_uint32(M), _p(codes_t), C.c_size_t(n), _p(out))
+    return out
+
+
+def pq_distance_one(table, codes_t, i):
+    table = _f32(table)
+    codes_t = np.ascontiguousarray(codes_t, dtype=np.uint8)
+    M, n = codes_t.shape
+    return float(lib().lo_pq_distance_one(_p(table), C.c_uint32(M), _p(codes_t), C.c_size_t(n),
+                                          C.c_size_t(i)))
+
+
+def pq_quantize(metric, codebook, vecs):
+    codebook, vecs = _f32(codebook), _f32(vecs)
+    M = codebook.shape[0]
+    n, d = vecs.shape
+    out = np.empty((n, M), dtype=np.uint8)
+    m = METRICS[metric]
+    lib().lo_pq_quantize(C.c_int(DOT if m == DOT else L2), _p(codebook), C.c_uint32(M),
+                         C.c_uint32(d), _p(vecs), C.c_size_t(n), _p(out))
+    return out
+
+
+class OracleIndex:
+    """Mirror of IVFIndex<FlatIndex, ProductQuantizer> (lance/src/index/vector/ivf/v2.rs:76)
+    over the exchange format of lance_b200.synth.IvfPqData."""
+
+    def __init__(self, data):
+        self.data = data
+        self._keep = [
+            _f32(data.centroids), _f32(data.codebook),
+            np.ascontiguousarray(data.part_offsets, dtype=np.uint64),
+            np.ascontiguousarray(data.codes, dtype=np.uint8),
+            np.ascontiguousarray(data.row_ids, dtype=np.uint64),
+            None if data.raw_vectors is None else _f32(data.raw_vectors),
+        ]
+        k = self._keep
+        self.ix = _Index(METRICS[data.metric], data.dim, data.nlist, data.M, k[0].ctypes.data,
+                         k[1].ctypes.data, k[2].ctypes.data, k[3].ctypes.data, k[4].ctypes.data,
+                         None if k[5] is None else k[5].ctypes.data)
+
+    def preprocess_query(self, part, key):
+        key = _f32(key)
+        out = np.empty_like(key)
+        lib().lo_preprocess_query(C.byref(self.ix), C.c_uint32(part), _p(key), _p(out))
+        return out
+
+    def search_in_partition(self, part, key, kprime, lower=None, upper=None, bitmask=None):
+        key = _f32(key)
+        od = np.empty(max(kprime, 1), dtype=np.float32)
+        oi = np.empty(max(kprime, 1), dtype=np.uint64)
+        n = lib().lo_search_in_partition(
+            C.byref(self.ix), C.c_uint32(part), _p(key), C.c_uint32(kprime),
+            C.c_int(lower is not None), C.c_float(lower or 0.0), C.c_int(upper is not None),
+            C.c_float(upper or 0.0), _p(bitmask), _p(od), _p(oi), None)
+        return od[:n], oi[:n]
+
+    def search(self, queries, k, nprobes, refine_factor=0, lower=None, upper=None, threads=0):
+        """Batched VectorIndex::search (+ scanner refine when refine_factor>0).
+        Returns (dist [Q][k'], rowid [Q][k'], count [Q], probes [Q][P])."""
+        queries = _f32(queries)
+        Q = queries.shape[0]
+        kp = k * (refine_factor if refine_factor else 1)
+        P = min(nprobes, self.data.nlist)
+        od = np.full((Q, max(kp, 1)), np.inf, dtype=np.float32)
+        oi = np.full((Q, max(kp, 1)), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros(Q, dtype=np.uint32)
+        pr = np.zeros((Q, max(nprobes, 1)), dtype=np.uint32)
+        lib().lo_search_batch(
+            C.byref(self.ix), _p(queries), C.c_uint32(Q), C.c_uint32(k), C.c_uint32(nprobes),
+            C.c_uint32(refine_factor), C.c_int(lower is not None), C.c_float(lower or 0.0),
+            C.c_int(upper is not None), C.c_float(upper or 0.0), C.c_int(threads), _p(od), _p(oi),
+            _p(oc), _p(pr))
+        return od, oi, oc, pr[:, :P]
+
+
+def flat_knn(metric, queries, vectors, k, validity=None, row_ids=None, threads=0):
+    queries, vectors = _f32(queries), _f32(vectors)
+    Q, d = queries.shape
+    n = vectors.shape[0]
+    od = np.full((Q, k), np.inf, dtype=np.float32)
+    oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+    oc = np.zeros(Q, dtype=np.uint32)
+    lib().lo_flat_knn_batch(C.c_int(METRICS[metric]), _p(queries), C.c_uint32(Q), _p(vectors),
+                            _p(validity), _p(row_ids), C.c_size_t(n), C.c_size_t(d), C.c_uint32(k),
+                            C.c_int(threads), _p(od), _p(oi), _p(oc))
+    return od, oi, oc
+
+
+def max_threads():
+    return int(lib().lo_max_threads())
