@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""bench.py -- IVF_PQ batched query throughput on B200 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload cfg4|cfg1|cfg5|cfg3]
+
+A "step" is one pass of the whole hot path (coarse probe selection -> ADC tables -> PQ code
+scan -> top-k -> merge [-> refine]) over one batch of synthetic queries.  Default workload is
+BASELINE.json's target config: bigann-shaped 100M x 128, IVF4096, PQ16, L2, k=10, nprobes=32,
+10k queries (fits one B200).  With N>1 the IVF partitions are sharded over the ranks
+(SURVEY 8e): each rank scans its partitions, one NCCL all_gather of the local top-k lists and a
+device-side merge produce the result; total work is fixed, so scaling is "strong".
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port of the reference
+path (the Rust reference cannot be built in this image) on all host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (N, dim, nlist, M, metric, nprobes, k, refine, Q, description)
+    "cfg4": (100_000_000, 128, 4096, 16, "l2", 32, 10, 0, 10_000,
+             "bigann-shaped 100Mx128 f32, IVF4096,PQ16, L2, k=10, nprobes=32, 10k queries (BASELINE configs[3])"),
+    "cfg1": (1_000_000, 128, 256, 16, "l2", 20, 10, 0, 10_000,
+             "SIFT-shaped 1Mx128 f32, IVF256,PQ16, L2, k=10, nprobes=20, 10k queries (BASELINE configs[0])"),
+    "cfg5": (10_000_000, 768, 2048, 48, "dot", 32, 10, 0, 4096,
+             "10Mx768 dot IVF2048,PQ48, k=10, nprobes=32, 4096 queries (BASELINE configs[4])"),
+    "cfg3": (1_000_000, 1536, 1024, 96, "cosine", 102, 10, 5, 1000,
+             "dbpedia-openai-shaped 1Mx1536 cosine IVF1024,PQ96, k=10, refine_factor=5, nprobes=102 (BASELINE configs[2])"),
+    "tiny": (200_000, 128, 64, 16, "l2", 8, 10, 0, 512, "tiny CI workload"),
+}
+
+
+def partition_sizes(N, nlist, seed, sigma=0.5):
+    rng = np.random.default_rng(seed)
+    w = rng.lognormal(0.0, sigma, size=nlist)
+    sizes = np.floor(w / w.sum() * N).astype(np.int64)
+    sizes[: N - sizes.sum()] += 1
+    return sizes
+
+
+def assign_partitions(sizes, world):
+    """Greedy bin-packing (largest first) of partitions onto ranks by row count."""
+    order = np.argsort(-sizes, kind="stable")
+    load = np.zeros(world, dtype=np.int64)
+    owner = np.zeros(len(sizes), dtype=np.int64)
+    for p in order:
+        r = int(np.argmin(load))
+        owner[p] = r
+        load[r] += sizes[p]
+    return owner
+
+
+def make_shard(wl, seed, rank, world, keep_raw=False):
+    """Synthetic index (SURVEY 8d cfg 4 recipe): log-normal partition sizes, uniform u8 codes
+    (scan cost is value independent), seeded per partition so every rank builds only its shard."""
+    from lance_b200.synth import IvfPqData
+    N, d, nlist, M, metric = wl[0], wl[1], wl[2], wl[3], wl[4]
+    sizes = partition_sizes(N, nlist, seed)
+    owner = assign_partitions(sizes, world)
+    rng = np.random.default_rng(seed + 1)
+    if metric == "dot":
+        cents = rng.normal(size=(nlist, d)).astype(np.float32)
+        codebook = rng.normal(size=(M, 256, d // M)).astype(np.float32)
+    elif metric == "cosine":
+        cents = rng.normal(size=(nlist, d)).astype(np.float32)
+        cents /= np.linalg.norm(cents, axis=1, keepdims=True)
+        codebook = (rng.normal(size=(M, 256, d // M)) * 0.02).astype(np.float32)
+    else:
+        cents = rng.uniform(0, 128, size=(nlist, d)).astype(np.float32)
+        codebook = rng.normal(0, 16, size=(M, 256, d // M)).astype(np.float32)
+    goffs = np.zeros(nlist + 1, dtype=np.int64)
+    goffs[1:] = np.cumsum(sizes)
+    mine = owner == rank
+    lsizes = sizes * mine
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(lsizes)
+    n_local = int(offs[-1])
+    codes = np.empty(n_local * M, dtype=np.uint8)
+    rids = np.empty(n_local, dtype=np.uint64)
+    raw = np.empty((n_local, d), dtype=np.float32) if keep_raw else None
+    for p in np.nonzero(mine)[0]:
+        prng = np.random.default_rng([seed, int(p)])
+        o, n = int(offs[p]), int(sizes[p])
+        codes[o * M:(o + n) * M] = prng.integers(0, 256, size=n * M, dtype=np.uint8)
+        gpos = np.arange(goffs[p], goffs[p] + n, dtype=np.uint64)
+        rids[o:o + n] = (gpos * np.uint64(2654435761)) % np.uint64(1 << 32)  # bijection on u32
+        if keep_raw:
+            raw[o:o + n] = cents[p] + prng.normal(0, 0.05 if metric == "cosine" else 8.0, size=(n, d)).astype(np.float32)
+    data = IvfPqData(metric, d, nlist, M, cents, codebook, offs, codes, rids, raw)
+    return data, sizes, owner
+
+
+def make_queries(wl, cents, seed):
+    Q, metric = wl[8], wl[4]
+    rng = np.random.default_rng(seed + 2)
+    c = cents[rng.integers(0, cents.shape[0], size=Q)]
+    s = 0.05 if metric == "cosine" else (0.5 if metric == "dot" else 16.0)
+    return (c + rng.normal(0, s, size=c.shape)).astype(np.float32)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(wl, data, queries, nq, threads):
+    """The reference's CPU algorithm (oracle port) on a bounded sample of the workload."""
+    import oracle
+    o = oracle.OracleIndex(data)
+    k, nprobes, refine = wl[6], wl[5], wl[7]
+    t0 = time.perf_counter()
+    o.search(queries[:nq], k=k, nprobes=nprobes, refine_factor=refine, threads=threads)
+    dt = time.perf_counter() - t0
+    return nq / dt, dt
+
+
+def run_reference(args, wl):
+    """--impl reference: the CPU path on the host cores, same config/metric/unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    seed = 77
+    data, sizes, _ = make_shard(wl, seed, 0, 1, keep_raw=wl[7] > 0)
+    queries = make_queries(wl, data.centroids, seed)
+    cores = oracle.max_threads()
+    # bounded sample per step: sized from a probe so the whole run stays within a few minutes
+    qps0, _ = cpu_reference_run(wl, data, queries, min(64, len(queries)), cores)
+    budget_s = 120.0 / max(1, args.steps + args.warmup)
+    nq = int(max(16, min(len(queries), qps0 * min(budget_s, 10.0))))
+    for _ in range(args.warmup):
+        cpu_reference_run(wl, data, queries, nq, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_reference_run(wl, data, queries, nq, cores)
+    dt = time.perf_counter() - t0
+    qps = nq * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "IVF_PQ queries/sec (batched)", "value": qps, "unit": "queries/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl[9], "queries_per_step": nq},
+        "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
+                         "sample": f"{nq} queries per step of the same workload, queries spread over {cores} threads"},
+        "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("LB200_WORKLOAD", "cfg4"), choices=sorted(WORKLOADS))
+    ap.add_argument("--scan-variant", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from lance_b200 import IvfPqIndex
+    from lance_b200.index import merge_topk_device
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    seed = 77
+    N, d, nlist, M, metric, nprobes, k, refine, Q, desc = wl
+    kprime = k * max(refine, 1)
+    t_build = time.perf_counter()
+    data, sizes, owner = make_shard(wl, seed, rank, world, keep_raw=refine > 0)
+    queries = make_queries(wl, data.centroids, seed)
+    ix = IvfPqIndex(data, device_id=local)
+    if args.scan_variant:
+        ix.set_scan_variant(args.scan_variant)
+    t_build = time.perf_counter() - t_build
+
+    stream = torch.cuda.Stream(device=dev)  # everything (our kernels, copies, NCCL) is ordered on it
+    torch.cuda.set_stream(stream)
+    sp = stream.cuda_stream
+    d_q = torch.from_numpy(queries).to(dev)
+    shard_mode = world > 1
+    ks = kprime if shard_mode else (k if refine else kprime)
+    d_od = torch.empty((Q, ks), dtype=torch.float32, device=dev)
+    d_oi = torch.empty((Q, ks), dtype=torch.int64, device=dev)
+    d_oc = torch.empty((Q,), dtype=torch.int32, device=dev)
+    d_ex = torch.empty((Q, ks), dtype=torch.float32, device=dev) if shard_mode else None
+    if shard_mode:
+        g_od = torch.empty((world, Q, ks), dtype=torch.float32, device=dev)
+        g_oi = torch.empty((world, Q, ks), dtype=torch.int64, device=dev)
+        g_oc = torch.empty((world, Q), dtype=torch.int32, device=dev)
+        g_ex = torch.empty((world, Q, ks), dtype=torch.float32, device=dev)
+        f_od = torch.empty((Q, k), dtype=torch.float32, device=dev)
+        f_oi = torch.empty((Q, k), dtype=torch.int64, device=dev)
+        f_oc = torch.empty((Q,), dtype=torch.int32, device=dev)
+    h_q = torch.from_numpy(queries).pin_memory()
+    h_od = torch.empty((Q, k if (refine or shard_mode) else kprime), dtype=torch.float32).pin_memory()
+    h_oi = torch.empty(h_od.shape, dtype=torch.int64).pin_memory()
+    h_oc = torch.empty((Q,), dtype=torch.int32).pin_memory()
+
+    def device_step():
+        ix.search_device(d_q.data_ptr(), Q, nprobes, k, refine, d_od.data_ptr(), d_oi.data_ptr(), d_oc.data_ptr(),
+                         d_out_exact=d_ex.data_ptr() if shard_mode else None, stream=sp)
+        if shard_mode:
+            dist.all_gather_into_tensor(g_od, d_od)
+            dist.all_gather_into_tensor(g_oi, d_oi)
+            dist.all_gather_into_tensor(g_oc, d_oc)
+            if refine:
+                dist.all_gather_into_tensor(g_ex, d_ex)
+            if rank == 0:
+                merge_topk_device(local, g_od.data_ptr(), g_oi.data_ptr(), g_ex.data_ptr() if refine else None,
+                                  g_oc.data_ptr(), world, Q, ks, kprime, k, f_od.data_ptr(), f_oi.data_ptr(),
+                                  f_oc.data_ptr(), stream=sp)
+
+    def e2e_step():
+        d_q.copy_(h_q, non_blocking=True)
+        device_step()
+        if rank == 0:
+            src = (f_od, f_oi, f_oc) if shard_mode else (d_od, d_oi, d_oc)
+            h_od.copy_(src[0], non_blocking=True)
+            h_oi.copy_(src[1], non_blocking=True)
+            h_oc.copy_(src[2], non_blocking=True)
+        stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        device_step()
+    barrier()
+    ix.set_profiling(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    scan_ms, scan_bytes, launches = [], [], 0
+
+    def profiled_step():
+        nonlocal launches
+        device_step()
+        st = ix.stats()
+        scan_ms.append(st["scan_ms"])
+        scan_bytes.append(st["scan_code_bytes"])
+        launches += st["kernel_launches"] + (1 if (shard_mode and rank == 0) else 0)
+
+    ms_total = timed(profiled_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    st = ix.stats()
+    ix.set_profiling(False)
+    for _ in range(2):
+        e2e_step()
+    e2e_steps = max(3, min(args.steps, 10))
+    ms_e2e = timed(e2e_step, e2e_steps)
+
+    # scan bytes / time across ranks (sum of bytes, max of time): whole-job scan bandwidth
+    agg = torch.tensor([float(np.mean(scan_ms)), float(np.mean(scan_bytes))], device=dev, dtype=torch.float64)
+    if world > 1:
+        tmax = agg[:1].clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        bsum = agg[1:].clone()
+        dist.all_reduce(bsum, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+    else:
+        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+    my_scan_ms = float(np.mean(scan_ms))
+    my_bytes = float(np.mean(scan_bytes))
+    achieved = my_bytes / (my_scan_ms * 1e-3) / 1e9 if my_scan_ms > 0 else 0.0
+    qps = Q * args.steps / (ms_total * 1e-3)
+    e2e_qps = Q * e2e_steps / (ms_e2e * 1e-3)
+    line = {
+        "metric": "IVF_PQ queries/sec (batched)", "value": qps, "unit": "queries/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "queries_per_step": Q, "k": k, "nprobes": nprobes, "refine_factor": refine,
+                   "parallelism": f"ivf-partitions sharded over {world} GPU(s)",
+                   "l2_policy": "inputs larger than L2 (PQ codes %.2f GB per GPU)" % (data.codes.nbytes / 1e9),
+                   "scan_variant": st["scan_variant"], "scan_queries_per_cta": st["scan_ql"],
+                   "index_build_s": round(t_build, 1)},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "kernel": "scan_kernel (rank 0)",
+                     "peak_source": peak_src, "scan_ms_per_launch": my_scan_ms,
+                     "algorithmic_bytes_per_launch": my_bytes,
+                     "note": "algorithmic bytes = sum over (query,partition) pairs of n_p*M code bytes; QL queries "
+                             "share each code load, so the figure can exceed DRAM traffic (SURVEY 8d)"},
+        "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": int(h_q.numel() * 4) * world,
+                "d2h_bytes_per_step": int(h_od.numel() * 4 + h_oi.numel() * 8 + h_oc.numel() * 4),
+                "ms_per_step": ms_e2e / e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    if world > 1:
+        line["roofline"]["all_ranks_achieved"] = float(bsum.item()) / (float(tmax.item()) * 1e-3) / 1e9
+    if world == 1 and not args.no_cpu_baseline:
+        import oracle
+        cores = oracle.max_threads()
+        qps0, _ = cpu_reference_run(wl, data, queries, min(32, Q), cores)
+        nq = int(max(32, min(Q, qps0 * 15.0)))
+        cqps, cdt = cpu_reference_run(wl, data, queries, nq, cores)
+        line["cpu_baseline"] = {"value": cqps, "unit": "queries/s", "cores": cores, "kind": "port",
+                                "sample": f"first {nq} queries of the same batch, {cdt:.1f} s, queries spread over "
+                                          f"{cores} threads (oracle port of the Rust reference)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,318 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
+
+Bar (BASELINE.json north_star): identical probed partitions; row ids identical except for
+distance ties within 1e-5 relative; distances within 1e-5 relative.  Because the kernels keep
+the reference's operation order, these tests assert the stronger property: BIT-IDENTICAL
+distances and identical row ids (ties ordered by row id on both sides); REL_TOL documents the
+contract the bit-exact check implies.
+"""
+import numpy as np
+import pytest
+import torch
+
+from lance_b200.synth import IvfPqData, build_ivf_pq, random_index, queries_near_centroids
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-5  # the stated tolerance; every check below is exact, which is stricter
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_gpu():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from lance_b200 import _lib
+    assert _lib.lib() is not None  # the in-tree .so is what runs; no fallback exists
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def _assert_same(d_gpu, i_gpu, c_gpu, d_ref, i_ref, c_ref, what=""):
+    assert c_gpu.tolist() == c_ref.tolist(), f"{what}: counts differ"
+    for q in range(len(c_ref)):
+        n = int(c_ref[q])
+        assert i_gpu[q, :n].tolist() == i_ref[q, :n].tolist(), f"{what}: row ids differ for query {q}"
+        assert _bits(d_gpu[q, :n]).tolist() == _bits(d_ref[q, :n]).tolist(), f"{what}: distances differ for query {q}"
+
+
+def _ragged_index(metric, d, nlist, M, sizes, seed, keep_raw=False):
+    """Index with explicit partition sizes (incl. empty / tiny / non-multiple-of-16), random
+    codes, unique row ids in random order."""
+    rng = np.random.default_rng(seed)
+    sizes = np.asarray(sizes, dtype=np.int64)
+    N = int(sizes.sum())
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    cents = rng.normal(size=(nlist, d)).astype(np.float32)
+    cb = rng.normal(size=(M, 256, d // M)).astype(np.float32)
+    codes = rng.integers(0, 256, size=N * M, dtype=np.uint8)
+    rid = rng.permutation(N * 3)[:N].astype(np.uint64)
+    raw = rng.normal(size=(N, d)).astype(np.float32) if keep_raw else None
+    return IvfPqData(metric, d, nlist, M, cents, cb, offs, codes, rid, raw)
+
+
+# ---- A1/A2: find_partitions -------------------------------------------------------------
+@pytest.mark.parametrize("metric,d,nlist", [("l2", 128, 256), ("l2", 8, 33), ("l2", 16, 64), ("l2", 100, 50),
+                                            ("dot", 768, 128), ("dot", 70, 20), ("cosine", 1536, 64)])
+def test_find_partitions_parity(oracle, metric, d, nlist):
+    from lance_b200 import IvfPqIndex
+    rng = np.random.default_rng(d + nlist)
+    data = _ragged_index(metric, d, nlist, 1 if d % 2 else 2, [3] * nlist, seed=1)
+    q = rng.normal(size=(37, d)).astype(np.float32)
+    if metric == "cosine":
+        q = np.stack([oracle.normalize(x) for x in q])
+    ix = IvfPqIndex(data)
+    for nprobes in (1, 7, nlist, nlist + 5):
+        ids, dist = ix.find_partitions(q, nprobes, return_distances=True)
+        for i in range(q.shape[0]):
+            rid, rd = oracle.find_partitions(data.centroids, q[i], nprobes, metric)
+            assert ids[i].tolist() == rid.tolist()
+            assert _bits(dist[i]).tolist() == _bits(rd).tolist()
+    ix.close()
+
+
+# ---- A3-A6: search_in_partition ------------------------------------------------------------
+CASES = [
+    # metric, d, M (dsub), variant
+    ("l2", 128, 16, 1), ("l2", 128, 16, 2), ("cosine", 128, 16, 2), ("dot", 128, 16, 2),
+    ("l2", 64, 4, 1), ("l2", 64, 4, 2),        # dsub 16
+    ("dot", 96, 8, 2), ("l2", 96, 8, 2),       # dsub 12: generic table path
+    ("l2", 32, 16, 2), ("l2", 24, 2, 1),       # dsub 2 / 12, M=2 only fits variant 1
+    ("l2", 256, 32, 2), ("dot", 768, 48, 2),   # QL sweeps through VG=32/16/8/4
+]
+
+
+@pytest.mark.parametrize("metric,d,M,variant", CASES)
+def test_search_in_partition_parity(oracle, metric, d, M, variant):
+    from lance_b200 import IvfPqIndex
+    sizes = [0, 1, 5, 15, 16, 17, 100, 1000, 33, 0, 2049, 64, 7, 300, 4100, 9]
+    nlist = len(sizes)
+    data = _ragged_index(metric, d, nlist, M, sizes, seed=d + M)
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    ix.set_scan_variant(variant)
+    rng = np.random.default_rng(5)
+    Q, P = 19, nlist
+    q = rng.normal(size=(Q, d)).astype(np.float32)
+    if metric == "cosine":
+        q = np.stack([oracle.normalize(x) for x in q])
+    parts = np.stack([rng.permutation(nlist) for _ in range(Q)]).astype(np.uint32)
+    for k in (1, 10, 50):
+        od, oi, oc = ix.search_in_partition(parts, q, k)
+        assert ix.stats()["scan_variant"] == variant
+        for qi in range(Q):
+            for pi in range(P):
+                rd, ri = o.search_in_partition(int(parts[qi, pi]), q[qi], k)
+                n = len(rd)
+                assert oc[qi, pi] == n == min(k, sizes[parts[qi, pi]])
+                assert oi[qi, pi, :n].tolist() == ri.tolist()
+                assert _bits(od[qi, pi, :n]).tolist() == _bits(rd).tolist()
+    ix.close()
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+def test_bounds_and_prefilter(oracle, variant):
+    from lance_b200 import IvfPqIndex
+    sizes = [500, 0, 77, 1300]
+    data = _ragged_index("l2", 64, 4, 16, sizes, seed=3)
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    ix.set_scan_variant(variant)
+    rng = np.random.default_rng(8)
+    q = rng.normal(size=(6, 64)).astype(np.float32)
+    parts = np.tile(np.arange(4, dtype=np.uint32), (6, 1))
+    base_d, _, _ = ix.search_in_partition(parts, q, 20)
+    lo, hi = float(np.median(base_d[np.isfinite(base_d)])), float(np.max(base_d[np.isfinite(base_d)]))
+    masks = {p: rng.random(sizes[p]) < 0.3 for p in (0, 3)}
+    for lower, upper, pf in [(lo, None, None), (None, hi, None), (lo, hi, None), (None, None, masks), (lo, hi, masks)]:
+        od, oi, oc = ix.search_in_partition(parts, q, 20, lower_bound=lower, upper_bound=upper, prefilter=pf)
+        for qi in range(6):
+            for p in range(4):
+                bm = None
+                if pf is not None and p in pf:
+                    bm = np.zeros((sizes[p] + 63) // 64 + 1, dtype=np.uint64)
+                    packed = np.packbits(pf[p], bitorder="little")
+                    bm.view(np.uint8)[:packed.size] = packed
+                rd, ri = o.search_in_partition(p, q[qi], 20, lower=lower, upper=upper, bitmask=bm)
+                n = len(rd)
+                assert oc[qi, p] == n
+                assert oi[qi, p, :n].tolist() == ri.tolist()
+                assert _bits(od[qi, p, :n]).tolist() == _bits(rd).tolist()
+    ix.close()
+
+
+def test_distance_ties_ordered_by_row_id(oracle):
+    """All rows share one code -> every distance ties; both sides must order by row id."""
+    from lance_b200 import IvfPqIndex
+    data = _ragged_index("l2", 32, 2, 4, [700, 45], seed=4)
+    data.codes[:] = 7
+    o = oracle.OracleIndex(data)
+    q = np.random.default_rng(1).normal(size=(3, 32)).astype(np.float32)
+    for variant in (1, 2):
+        ix = IvfPqIndex(data)
+        ix.set_scan_variant(variant)
+        od, oi, oc = ix.search_in_partition(np.tile(np.arange(2, dtype=np.uint32), (3, 1)), q, 10)
+        for qi in range(3):
+            for p in range(2):
+                rd, ri = o.search_in_partition(p, q[qi], 10)
+                assert oi[qi, p, :len(ri)].tolist() == ri.tolist()
+        ix.close()
+
+
+# ---- whole path: VectorIndex::search (+ refine) ---------------------------------------------
+@pytest.mark.parametrize("metric,d,nlist,M,refine", [("l2", 128, 64, 16, 0), ("l2", 128, 64, 16, 5),
+                                                     ("cosine", 96, 32, 6, 5), ("dot", 64, 16, 8, 2),
+                                                     ("cosine", 64, 16, 16, 0)])
+def test_search_parity_trained_index(oracle, metric, d, nlist, M, refine):
+    from lance_b200 import IvfPqIndex, Query
+    rng = np.random.default_rng(nlist)
+    vecs = rng.normal(size=(20000, d)).astype(np.float32) + rng.normal(size=(1, d)).astype(np.float32)
+    data = build_ivf_pq(vecs, metric, nlist, M, seed=1, keep_raw=True, ivf_iters=4, pq_iters=3, sample=8192)
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    q = vecs[rng.integers(0, len(vecs), 64)] + 0.05 * rng.normal(size=(64, d)).astype(np.float32)
+    for nprobes in (1, 8, nlist):
+        rd, ri, rc, rp = o.search(q, k=10, nprobes=nprobes, refine_factor=refine)
+        probes = ix.find_partitions(np.stack([oracle.normalize(x) for x in q]) if metric == "cosine" else q, nprobes)
+        assert probes.tolist() == rp.tolist(), "probed partitions differ"
+        gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=nprobes, refine_factor=refine or None))
+        kout = gd.shape[1]
+        _assert_same(gd, gi, gc, rd[:, :kout], ri[:, :kout], rc, f"{metric} nprobes={nprobes}")
+    # batched == one at a time (the reference has no inter-query batching)
+    gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=8, refine_factor=refine or None))
+    for i in (0, 17, 63):
+        d1, i1, c1 = ix.search(Query(key=q[i], k=10, nprobes=8, refine_factor=refine or None))
+        assert i1[0].tolist() == gi[i].tolist() and _bits(d1[0]).tolist() == _bits(gd[i]).tolist()
+    ix.close()
+
+
+def test_variants_agree_and_bounds_in_search(oracle):
+    from lance_b200 import IvfPqIndex, Query
+    data = random_index(60000, 128, 32, 16, "l2", seed=2)
+    q = queries_near_centroids(data, 200, seed=3)
+    o = oracle.OracleIndex(data)
+    rd, ri, rc, _ = o.search(q, k=10, nprobes=8)
+    mid = float(np.median(rd[:, 5]))
+    rdb, rib, rcb, _ = o.search(q, k=10, nprobes=8, lower=mid * 0.9, upper=mid * 1.1)
+    for variant in (1, 2):
+        ix = IvfPqIndex(data)
+        ix.set_scan_variant(variant)
+        gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=8))
+        _assert_same(gd, gi, gc, rd, ri, rc, f"variant {variant}")
+        gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=8, lower_bound=mid * 0.9, upper_bound=mid * 1.1))
+        _assert_same(gd, gi, gc, rdb, rib, rcb, f"variant {variant} bounds")
+        ix.close()
+
+
+def test_golden_test_vector_dataset(oracle):
+    """scanner.rs:2758-2816 test_knn_nodes: ivf_pq(2,8,2,L2,2) + refine(5) -> {1,81,161,241,321}."""
+    from lance_b200 import IvfPqIndex, Query, flat_knn
+    base = np.arange(32 * 80, dtype=np.float32).reshape(80, 32)
+    rows = np.concatenate([base] * 5, axis=0)
+    key = np.arange(32, 64, dtype=np.float32)
+    data = build_ivf_pq(rows, "l2", nlist=2, M=2, seed=0, keep_raw=True)
+    ix = IvfPqIndex(data)
+    d, ids, cnt = ix.search(Query(key=key, k=5, nprobes=2, refine_factor=5))
+    assert cnt[0] == 5 and set(ids[0].tolist()) == {1, 81, 161, 241, 321} and d[0].tolist() == [0.0] * 5
+    d, ids, cnt = flat_knn(key, "l2", rows, 5)
+    assert cnt[0] == 5 and set(ids[0].tolist()) == {1, 81, 161, 241, 321}
+    ix.close()
+
+
+def test_committed_golden_fixture():
+    """tests/golden/ivfpq_small.npz was produced by tests/golden/make_golden.py (oracle output at
+    commit time); the GPU must reproduce it bit for bit."""
+    import os
+    from lance_b200 import IvfPqIndex, Query
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ivfpq_small.npz"))
+    for metric in ("l2", "cosine", "dot"):
+        data = IvfPqData(metric, int(g["dim"]), int(g["nlist"]), int(g["M"]), g[f"{metric}_centroids"],
+                         g[f"{metric}_codebook"], g[f"{metric}_part_offsets"], g[f"{metric}_codes"],
+                         g[f"{metric}_row_ids"], g[f"{metric}_raw"])
+        ix = IvfPqIndex(data)
+        for refine in (0, 3):
+            gd, gi, gc = ix.search(Query(key=g["queries"], k=10, nprobes=6, refine_factor=refine or None))
+            _assert_same(gd, gi, gc, g[f"{metric}_r{refine}_dist"][:, :gd.shape[1]],
+                         g[f"{metric}_r{refine}_ids"][:, :gd.shape[1]], g[f"{metric}_r{refine}_cnt"], metric)
+        ix.close()
+
+
+# ---- flat kNN (KNNVectorDistanceExec) -----------------------------------------------------------
+@pytest.mark.parametrize("metric,d", [("l2", 128), ("cosine", 128), ("dot", 128), ("l2", 8), ("cosine", 16),
+                                      ("l2", 100), ("cosine", 1536), ("dot", 70)])
+def test_flat_parity(oracle, metric, d):
+    from lance_b200 import compute_distance, flat_knn
+    rng = np.random.default_rng(d)
+    n = 3001
+    vecs = rng.normal(size=(n, d)).astype(np.float32)
+    q = rng.normal(size=(9, d)).astype(np.float32)
+    valid = rng.random(n) < 0.9
+    vbits = np.packbits(valid, bitorder="little")
+    dist = compute_distance(q, metric, vecs, validity=vbits)
+    for i in range(9):
+        ref = oracle.distance_batch(metric, q[i], vecs)
+        assert _bits(dist[i][valid]).tolist() == _bits(ref[valid]).tolist()
+        assert np.all(np.isnan(dist[i][~valid]))
+    for k in (1, 10, 100):
+        gd, gi, gc = flat_knn(q, metric, vecs, k, validity=vbits)
+        rd, ri, rc = oracle.flat_knn(metric, q, vecs, k, validity=vbits)
+        _assert_same(gd, gi, gc, rd, ri, rc, f"flat {metric} k={k}")
+
+
+def test_flat_edge_cases(oracle):
+    from lance_b200 import flat_knn
+    rng = np.random.default_rng(0)
+    vecs = rng.normal(size=(40, 32)).astype(np.float32)
+    vecs[10:30] = vecs[5]  # 21 identical rows: ties resolved by row position
+    q = vecs[5:6]
+    gd, gi, gc = flat_knn(q, "l2", vecs, 8)
+    rd, ri, rc = oracle.flat_knn("l2", q, vecs, 8)
+    _assert_same(gd, gi, gc, rd, ri, rc, "ties")
+    gd, gi, gc = flat_knn(q, "l2", vecs, 64)  # k > n
+    assert gc[0] == 40 and sorted(gi[0, :40].tolist()) == list(range(40))
+    mid = float(rd[0, 7]) + 1.0
+    gd, gi, gc = flat_knn(q, "l2", vecs, 8, lower_bound=0.5, upper_bound=mid)
+    assert np.all(gd[0, :gc[0]] >= 0.5) and np.all(gd[0, :gc[0]] < mid)
+
+
+# ---- reference-style error behaviour ---------------------------------------------------------------
+def test_error_behaviour():
+    from lance_b200 import IvfPqIndex, LanceB200Error, Query
+    data = _ragged_index("l2", 32, 4, 4, [10, 20, 30, 40], seed=1)
+    ix = IvfPqIndex(data)
+    with pytest.raises(ValueError):  # scanner.rs:642: dim mismatch
+        ix.search(Query(key=np.zeros(16, np.float32), k=5))
+    with pytest.raises(ValueError):  # k must be positive
+        ix.search(Query(key=np.zeros(32, np.float32), k=0))
+    with pytest.raises(LanceB200Error, match="does not exist"):  # ivf/v2.rs:288-293
+        ix.search_in_partition(np.array([[9]], np.uint32), np.zeros(32, np.float32), 5)
+    with pytest.raises(LanceB200Error, match="raw vectors"):
+        ix.search(Query(key=np.zeros(32, np.float32), k=5, nprobes=2, refine_factor=2))
+    # k' larger than the partition: short result, like the reference's short batches
+    od, oi, oc = ix.search_in_partition(np.array([[0]], np.uint32), np.zeros(32, np.float32), 50)
+    assert oc[0, 0] == 10
+    ix.close()
+
+
+# ---- full-size properties (BASELINE cfg 1 scale; oracle on a sample) ---------------------------------
+def test_full_size_properties(oracle):
+    from lance_b200 import IvfPqIndex, Query
+    data = random_index(1_000_000, 128, 256, 16, "l2", seed=11)
+    q = queries_near_centroids(data, 2000, seed=12)
+    ix = IvfPqIndex(data)
+    gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=20))
+    assert np.all(gc == 10)
+    assert np.all(np.diff(gd, axis=1) >= 0), "distances must be sorted ascending"
+    assert all(len(set(r.tolist())) == 10 for r in gi), "row ids must be unique per query"
+    # idempotence / batch-composition independence
+    gd2, gi2, _ = ix.search(Query(key=q[::-1].copy(), k=10, nprobes=20))
+    assert gi2[::-1].tolist() == gi.tolist() and _bits(gd2[::-1]).tolist() == _bits(gd).tolist()
+    # nprobes monotonicity: more probes can only improve the k-th distance
+    gd3, _, _ = ix.search(Query(key=q[:200], k=10, nprobes=40))
+    assert np.all(gd3[:, -1] <= gd[:200, -1])
+    # oracle on a sample
+    o = oracle.OracleIndex(data)
+    sel = np.arange(0, 2000, 40)
+    rd, ri, rc, _ = o.search(q[sel], k=10, nprobes=20)
+    _assert_same(gd[sel], gi[sel], gc[sel], rd, ri, rc, "cfg1-size sample")
+    ix.close()
