@@ -146,13 +146,14 @@ typedef struct {
   uint64_t scan_code_bytes;/* algorithmic code bytes: sum over (q,p) pairs of n_p * M      */
   uint64_t pairs;          /* (query, partition) pairs scanned                             */
   uint32_t kernel_launches;/* kernels launched by the call                                 */
-  uint32_t scan_variant;   /* 1 = generic kernel, 2 = bank-skewed multi-query kernel       */
+  uint32_t scan_variant;   /* 1 = generic, 2 = bank-skewed tile16, 3 = skew-stream lane=row  */
   uint32_t scan_ql;        /* queries per CTA of the scan kernel                           */
   uint32_t scan_items;     /* work items of the scan kernel                                */
 } lb200_stats;
 int32_t lb200_set_profiling(lb200_index* ix, int32_t enabled);
 int32_t lb200_get_stats(const lb200_index* ix, lb200_stats* out);
-/* Force a scan kernel variant (0 = auto, 1 = generic, 2 = bank-skewed); for A/B tests. */
+/* Force a scan kernel variant (0 = auto, 1 = generic, 2 = bank-skewed tile16, 3 = skew
+ * streams); 1/2 need the tile16 layout (env LB200_LAYOUTS=all at create when M % 16 == 0). */
 int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant);
 
 const char* lb200_last_error(void);

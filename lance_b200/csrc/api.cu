@@ -19,6 +19,7 @@
 #include "coarse.cuh"
 #include "flat.cuh"
 #include "scan.cuh"
+#include "scan3.cuh"
 #include "worklist.cuh"
 
 using namespace lb200;
@@ -86,7 +87,10 @@ struct lb200_index {
   uint64_t N = 0, ntiles = 0, max_part = 0;
   float *d_centroids = nullptr, *d_codebook = nullptr, *d_raw = nullptr;
   uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
-  uint8_t* d_codes = nullptr;
+  uint8_t* d_codes = nullptr;          // tile16 layout (variants 1/2), or null
+  uint8_t* d_codes3 = nullptr;         // skew-stream layout (variant 3), or null
+  uint64_t* d_sb_off = nullptr;        // [nlist+1] first superblock per partition
+  uint32_t skew_L = 0, skew_D = 0;     // superblock = 32*skew_L rows; lane delay period
   std::vector<uint64_t> h_part_off;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[6] = {};
@@ -95,7 +99,7 @@ struct lb200_index {
   int force_variant = 0;
   lb200_stats stats = {};
   int sm_count = 148;
-  size_t smem_optin = 0;
+  size_t smem_optin = 0, smem_per_sm = 0;
   Arena arena;
   const uint64_t** d_bitmask_ptrs = nullptr;  // scratch for prefilter pointers
 };
@@ -169,6 +173,7 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   CKF(cudaGetDeviceProperties(&prop, device_id));
   ix->sm_count = prop.multiProcessorCount;
   ix->smem_optin = prop.sharedMemPerBlockOptin;
+  ix->smem_per_sm = prop.sharedMemPerMultiprocessor;
   CKF(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
   for (auto& e : ix->ev) CKF(cudaEventCreate(&e));
   size_t cent_b = (size_t)nlist * dim * 4, cb_b = (size_t)M * 256 * ix->dsub * 4;
@@ -177,22 +182,63 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   CKF(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
   CKF(cudaMalloc(&ix->d_tile_off, (nlist + 1) * 8));
   CKF(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));
-  // tile16 codes, padded by one extra block of tiles so clamped loads stay in bounds
+  // Device code layouts.  Variant 3 (skew streams) serves every M that is a multiple of 16; the
+  // tile16 layout of variants 1/2 is built otherwise, or when LB200_LAYOUTS=all asks for both
+  // (A/B runs of the scan variants).
+  const char* lay = getenv("LB200_LAYOUTS");
+  const bool want_all = lay && !strcmp(lay, "all");
+  // QL=4 tables (M*4 KB) fit up to M=48; beyond that QL=2 tables (M*2 KB) up to M=96.
+  const bool want_skew = (M % 16 == 0) && M <= 96 && !(lay && !strcmp(lay, "tile16"));
+  const bool want_tile = !want_skew || want_all;
+  std::vector<uint64_t> sb_off(nlist + 1, 0);
+  if (want_skew) {
+    // rows per lane per superblock: ~2 superblocks per warp of an 8-warp CTA on an average
+    // partition, clamped to [4, 32] (drain overhead is 0.5/L of the lookups).
+    double avg = (double)N / nlist;
+    uint32_t L = 4;
+    while (L < 32 && avg >= 768.0 * L) L <<= 1;
+    if (const char* el = getenv("LB200_SKEW_L")) {  // test hook: force the superblock depth
+      int v = atoi(el);
+      if (v >= 1 && v <= 256) L = (uint32_t)v;
+    }
+    ix->skew_L = L;
+    ix->skew_D = M <= 48 ? 8 : 16;
+    uint64_t sb = 0;
+    for (uint32_t p = 0; p < nlist; p++) {
+      sb_off[p] = sb;
+      sb += (part_offsets[p + 1] - part_offsets[p] + 32 * L - 1) / (32 * L);
+    }
+    sb_off[nlist] = sb;
+    CKF(cudaMalloc(&ix->d_sb_off, (nlist + 1) * 8));
+    CKF(cudaMemcpyAsync(ix->d_sb_off, sb_off.data(), (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
+    size_t units = (size_t)L * (M / 16) + 1;
+    size_t b3 = std::max<size_t>((size_t)sb * units * 512, 512);
+    CKF(cudaMalloc(&ix->d_codes3, b3));
+  }
   size_t codes_b = (size_t)(t + 64) * 16 * M;
-  CKF(cudaMalloc(&ix->d_codes, codes_b));
+  if (want_tile) {
+    // tile16 codes, padded by one extra block of tiles so clamped loads stay in bounds
+    CKF(cudaMalloc(&ix->d_codes, codes_b));
+    CKF(cudaMemsetAsync(ix->d_codes, 0, codes_b, ix->stream));
+  }
   CKF(cudaMemcpyAsync(ix->d_centroids, centroids, cent_b, cudaMemcpyHostToDevice, ix->stream));
   CKF(cudaMemcpyAsync(ix->d_codebook, codebook, cb_b, cudaMemcpyHostToDevice, ix->stream));
   CKF(cudaMemcpyAsync(ix->d_part_off, part_offsets, (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
   CKF(cudaMemcpyAsync(ix->d_tile_off, tile_off.data(), (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
-  CKF(cudaMemsetAsync(ix->d_codes, 0, codes_b, ix->stream));
   if (N) {
     CKF(cudaMemcpyAsync(ix->d_row_ids, row_ids, N * 8, cudaMemcpyHostToDevice, ix->stream));
     uint8_t* d_src = nullptr;
     CKF(cudaMalloc(&d_src, (size_t)N * M));
     cudaError_t e1 = cudaMemcpyAsync(d_src, codes, (size_t)N * M, cudaMemcpyHostToDevice, ix->stream);
-    if (e1 == cudaSuccess) {
+    if (e1 == cudaSuccess && want_tile) {
       dim3 grid(nlist, 8);
       repack_codes_kernel<<<grid, 256, 0, ix->stream>>>(d_src, ix->d_part_off, ix->d_tile_off, nlist, M, ix->d_codes);
+      e1 = cudaGetLastError();
+    }
+    if (e1 == cudaSuccess && want_skew) {
+      dim3 grid(nlist, 8);
+      repack_skew_kernel<<<grid, 256, 0, ix->stream>>>(d_src, ix->d_part_off, ix->d_sb_off, M, ix->skew_L,
+                                                       ix->skew_D, ix->d_codes3);
       e1 = cudaGetLastError();
     }
     if (e1 == cudaSuccess) e1 = cudaStreamSynchronize(ix->stream);
@@ -219,6 +265,8 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_tile_off);
   cudaFree(ix->d_row_ids);
   cudaFree(ix->d_codes);
+  cudaFree(ix->d_codes3);
+  cudaFree(ix->d_sb_off);
   cudaFree(ix->arena.base);
   cudaFree((void*)ix->d_bitmask_ptrs);
   for (auto& e : ix->ev)
@@ -238,7 +286,10 @@ extern "C" int32_t lb200_get_stats(const lb200_index* ix, lb200_stats* out) {
   return 0;
 }
 extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
-  if (!ix || variant < 0 || variant > 2) return set_err(LB200_EINVAL, "variant must be 0, 1 or 2");
+  if (!ix || variant < 0 || variant > 3) return set_err(LB200_EINVAL, "variant must be 0..3");
+  if ((variant == 1 || variant == 2) && !ix->d_codes)
+    return set_err(LB200_EINVAL, "variant %d needs the tile16 layout (create the index with LB200_LAYOUTS=all)", variant);
+  if (variant == 3 && !ix->d_codes3) return set_err(LB200_EINVAL, "variant 3 needs num_sub_vectors %% 16 == 0");
   ix->force_variant = variant;
   return 0;
 }

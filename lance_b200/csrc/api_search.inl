@@ -6,6 +6,7 @@ struct ScanConfig {
   int variant, ql, dsub_t;
   uint32_t capw;
   size_t smem;
+  int minb;  // variant 3: CTAs per SM the kernel is compiled for
 };
 constexpr int SCAN_NW = 8;
 
@@ -36,6 +37,26 @@ static int choose_scan(const lb200_index* ix, uint32_t kprime, double avg_q_per_
     c->dsub_t = ix->dsub == 8 ? 8 : ix->dsub == 16 ? 16 : 0;
     return true;
   };
+  out->minb = 1;
+  if (ix->d_codes3 && (ix->force_variant == 0 || ix->force_variant == 3)) {
+    // variant 3: QL is tied to the layout's lane-delay period (8 -> LDS.128/QL 4, 16 -> LDS.64/QL 2)
+    const int ql = ix->skew_D == 8 ? 4 : 2;
+    uint32_t capw = std::max(64u, (kprime + 32 + 3) & ~3u);
+    size_t smem = scan3_smem_bytes(ql, SCAN_NW, ix->M, ix->dim, capw);
+    if (smem <= limit) {
+      out->variant = 3;
+      out->ql = ql;
+      out->capw = capw;
+      out->smem = smem;
+      out->dsub_t = ix->dsub == 8 ? 8 : ix->dsub == 16 ? 16 : 0;
+      out->minb = (2 * (smem + 1024) <= ix->smem_per_sm) ? 2 : 1;
+      return 0;
+    }
+    if (ix->force_variant == 3 || !ix->d_codes)
+      return set_err(LB200_EUNSUPPORTED, "k'=%u does not fit the shared-memory candidate buffers (M=%u, dim=%u)",
+                     kprime, ix->M, ix->dim);
+  }
+  if (!ix->d_codes) return set_err(LB200_EUNSUPPORTED, "tile16 layout missing (LB200_LAYOUTS=all)");
   if (ix->force_variant != 1) {
     int want = avg_q_per_part >= 6 ? 8 : avg_q_per_part >= 3 ? 4 : avg_q_per_part >= 1.5 ? 2 : 1;
     if (ix->force_variant == 2 && want < 2) want = 8;
@@ -76,6 +97,37 @@ static cudaError_t launch_scan(const ScanConfig& c, int grid, cudaStream_t st, c
     case 2: return launch_scan_d<2, 2>(c.dsub_t, grid, c.smem, st, sp, total_items);
     default: return launch_scan_d<2, 1>(c.dsub_t, grid, c.smem, st, sp, total_items);
   }
+}
+
+template <int QL, int D, int MINB>
+static cudaError_t launch_scan3_d(int dsub_t, int sm_count, size_t smem, cudaStream_t st, const Scan3Params& sp,
+                                  const uint32_t* total_items) {
+#define LB200_LAUNCH3(DS)                                                                         \
+  do {                                                                                            \
+    auto kern = scan3_kernel<QL, D, SCAN_NW, MINB, DS>;                                           \
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    if (e != cudaSuccess) return e;                                                               \
+    int nb = 0;                                                                                   \
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, SCAN_NW * 32, smem);             \
+    if (e != cudaSuccess) return e;                                                               \
+    if (nb < 1) return cudaErrorLaunchOutOfResources;                                             \
+    kern<<<sm_count * nb, SCAN_NW * 32, smem, st>>>(sp, total_items);                             \
+    return cudaGetLastError();                                                                    \
+  } while (0)
+  if (dsub_t == 8) LB200_LAUNCH3(8);
+  if (dsub_t == 16) LB200_LAUNCH3(16);
+  LB200_LAUNCH3(0);
+#undef LB200_LAUNCH3
+}
+
+static cudaError_t launch_scan3(const ScanConfig& c, int sm_count, cudaStream_t st, const Scan3Params& sp,
+                                const uint32_t* total_items) {
+  if (c.ql == 4) {
+    if (c.minb == 2) return launch_scan3_d<4, 8, 2>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+    return launch_scan3_d<4, 8, 1>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+  }
+  if (c.minb == 2) return launch_scan3_d<2, 16, 2>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+  return launch_scan3_d<2, 16, 1>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
 }
 
 struct SearchArgs {
@@ -165,6 +217,10 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     cv = std::max<uint64_t>(2048, (cv + 511) / 512 * 512);
     chunk_vecs = (uint32_t)std::min<uint64_t>(chunk_vecs, cv);
   }
+  if (sc.variant == 3) {  // chunks are whole superblocks
+    const uint32_t sbr = 32 * ix->skew_L;
+    chunk_vecs = (chunk_vecs + sbr - 1) / sbr * sbr;
+  }
   const uint32_t max_chunks = (uint32_t)std::max<uint64_t>(1, (ix->max_part + chunk_vecs - 1) / chunk_vecs);
 
   // ---- workspace -----------------------------------------------------------------------
@@ -183,6 +239,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   add(nslots * kprime * 4); add(nslots * kprime * 8); add(nslots * kprime * 8); add(nslots * 4);
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
   add((size_t)Q * kprime * 4);      // exact
+  add((size_t)Q * 4);               // per-query thresholds
   rc = ix->arena.reserve(need);
   if (rc) return rc;
   ix->arena.reset();
@@ -205,6 +262,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   uint64_t* d_mpos = ix->arena.take<uint64_t>((size_t)Q * kprime);
   uint32_t* d_mcnt = ix->arena.take<uint32_t>(Q);
   float* d_exact = ix->arena.take<float>((size_t)Q * kprime);
+  uint32_t* d_qthr = ix->arena.take<uint32_t>(Q);
 
   const bool prof = ix->profiling;
   if (prof) CK(cudaEventRecord(ix->ev[0], st));
@@ -237,6 +295,30 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   CK(cudaGetLastError());
   launches += 3;
   // ---- A3-A6 scan -----------------------------------------------------------------------
+  if (sc.variant == 3) {
+    Scan3Params sp = {};
+    sp.codes = ix->d_codes3; sp.sb_off = ix->d_sb_off; sp.part_off = ix->d_part_off; sp.row_ids = ix->d_row_ids;
+    sp.centroids = ix->d_centroids; sp.codebook = ix->d_codebook;
+    sp.dim = dim; sp.M = ix->M; sp.dsub = ix->dsub; sp.nlist = nlist; sp.L = ix->skew_L;
+    sp.residual = ix->metric != LB200_DOT;
+    sp.queries = keys; sp.Q = Q; sp.P = P; sp.kprime = kprime;
+    sp.pair_list = d_pair_list; sp.part_pair_off = d_pair_off; sp.item_off = d_item_off; sp.item_counter = d_counter;
+    sp.chunk_vecs = chunk_vecs; sp.max_chunks = max_chunks; sp.capw = sc.capw;
+    // merged searches share one running k'-th-best bound per query across all its partitions;
+    // search_in_partition semantics (one full list per pair) must not.
+    sp.qthr = a.per_pair_output ? nullptr : d_qthr;
+    sp.lower = a.lower; sp.upper = a.upper; sp.has_lower = a.has_lower; sp.has_upper = a.has_upper;
+    sp.bitmask = a.d_bitmask;
+    sp.out_dist = d_sdist; sp.out_pos = d_spos; sp.out_rowid = d_srow; sp.out_count = d_scnt;
+    if (sp.qthr) {
+      fill_u32_kernel<<<(Q + 255) / 256, 256, 0, st>>>(d_qthr, KEY_PINF, Q);
+      CK(cudaGetLastError());
+      launches++;
+    }
+    if (prof) CK(cudaEventRecord(ix->ev[2], st));
+    CK(launch_scan3(sc, ix->sm_count, st, sp, d_item_off + nlist));
+    launches++;
+  } else {
   ScanParams sp = {};
   sp.codes = ix->d_codes; sp.tile_off = ix->d_tile_off; sp.part_off = ix->d_part_off; sp.row_ids = ix->d_row_ids;
   sp.centroids = ix->d_centroids; sp.codebook = ix->d_codebook;
@@ -251,6 +333,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   if (prof) CK(cudaEventRecord(ix->ev[2], st));
   CK(launch_scan(sc, ix->sm_count, st, sp, d_item_off + nlist));
   launches++;
+  }
   if (prof) CK(cudaEventRecord(ix->ev[3], st));
   // ---- A7 merge ---------------------------------------------------------------------------
   if (a.per_pair_output) {

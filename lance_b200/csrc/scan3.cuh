@@ -1,0 +1,463 @@
+// scan3.cuh -- VARIANT 3 of K2+K3+K4: lane = row, QL queries per CTA, skewed code streams.
+//
+// Same arithmetic as scan.cuh (A3 residual, A4 ADC table, A5 ascending-m f32 accumulation, A6
+// per-pair top-k'); what changes is how the work is laid on the SM so that the shared-memory
+// gather -- the real limiter of the scan (SURVEY 7 "hard parts") -- runs conflict-free at one
+// wide LDS per code byte:
+//
+//  * The ADC tables of the CTA's QL queries are interleaved: T[chunk][code][slot][q], slot = m%16,
+//    chunk = m/16, so ONE LDS.128 (QL=4) / LDS.64 (QL=2) returns T_q[m][code] for all QL queries.
+//    The word address is chunk*CB + code*(64*QL) + slot*(4*QL) bytes: the bank group of an access
+//    depends only on the slot, never on the (random) code.
+//  * A wide LDS is served in phases of 8 (128-bit) / 16 (64-bit) consecutive lanes.  Lane l runs
+//    d = l % D bytes BEHIND in its own code stream, so at any step the lanes of a phase sit on D
+//    consecutive sub-vectors m -> D distinct slots -> distinct bank groups: no conflicts, although
+//    every lane still adds its row's M table entries in ASCENDING m order (bit-exact with
+//    pq/distance.rs:102-135).
+//  * The skew is baked into the device layout ("skew stream"): a partition is cut into
+//    superblocks of 32*L rows; lane l of superblock s owns rows s*32L + i*32 + l (i < L), its
+//    stream is the concatenation of those rows' M code bytes delayed by d zero bytes, stored as
+//    16-byte units interleaved over the 32 lanes (unit g of lane l at (g*32 + l)*16): every
+//    LDG.128 of a warp is one fully coalesced 512-byte line group.  L*M/16 + 1 units per
+//    superblock (the last one drains the d delayed bytes).
+//  * A lane finishes row i-1 and starts row i at step d of macro-iteration i ("switch").  The
+//    finished sum is captured and the accumulator cleared either with selects (SAFE) or, when
+//    every table entry is finite and small enough that no partial sum can overflow, with exact
+//    FMAs by 0.0/1.0 on the FMA pipe (acc*1+v == acc+v, acc*0+v == v bit for bit).
+//  * Candidates are filtered against a running k'-th-best threshold that is shared by the warps
+//    of the CTA and -- for merged searches -- by all work items of the same query (global
+//    atomicMin), so that after a query's first partition almost nothing reaches the buffers.
+#pragma once
+#include "scan.cuh"
+
+namespace lb200 {
+
+struct Scan3Params {
+  // index (device)
+  const uint8_t* codes;           // skew-stream layout
+  const uint64_t* sb_off;         // [nlist+1] first superblock of each partition
+  const uint64_t* part_off;       // [nlist+1] first row of each partition
+  const uint64_t* row_ids;        // [N]
+  const float* centroids;         // [nlist][dim]
+  const float* codebook;          // [M][256][dsub]
+  uint32_t dim, M, dsub, nlist;
+  uint32_t L;                     // rows per lane per superblock
+  int32_t residual;               // 1: L2/cosine, 0: dot
+  // queries
+  const float* queries;           // [Q][dim], already normalised for cosine
+  uint32_t Q, P, kprime;
+  // work list
+  const uint32_t* pair_list;
+  const uint32_t* part_pair_off;
+  const uint32_t* item_off;
+  uint32_t* item_counter;
+  uint32_t chunk_vecs;            // rows per chunk (multiple of 32*L)
+  uint32_t max_chunks;
+  uint32_t capw;                  // candidate buffer entries per (warp, query slot)
+  uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
+  // bounds / prefilter
+  float lower, upper;
+  int32_t has_lower, has_upper;
+  const uint64_t* const* bitmask;
+  // outputs, slot = pair * max_chunks + chunk
+  float* out_dist;
+  uint64_t* out_pos;
+  uint64_t* out_rowid;
+  uint32_t* out_count;
+};
+
+constexpr uint32_t KEY_PINF = 0xff800000u;  // ordered_key(+inf)
+
+// Reference layout (concat over p of transposed [M][n_p]) -> skew streams.
+// grid = (nlist, Y); one thread per 16-byte unit-lane.
+__global__ void repack_skew_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ part_off,
+                                   const uint64_t* __restrict__ sb_off, uint32_t M, uint32_t L, uint32_t D,
+                                   uint8_t* __restrict__ dst) {
+  const uint32_t p = blockIdx.x;
+  const uint64_t o = part_off[p], n = part_off[p + 1] - o;
+  const uint64_t sb0 = sb_off[p], nsb = sb_off[p + 1] - sb0;
+  const uint32_t units = L * (M / 16) + 1;
+  const uint8_t* s = src + o * M;
+  const uint64_t total = nsb * units * 32;  // 16-byte records
+  for (uint64_t rec = (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; rec < total;
+       rec += (uint64_t)gridDim.y * blockDim.x) {
+    const uint32_t lane = (uint32_t)(rec & 31);
+    const uint64_t ug = rec >> 5;
+    const uint64_t sb = ug / units;
+    const uint32_t g = (uint32_t)(ug - sb * units);
+    const uint32_t d = lane % D;
+    uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int b = 0; b < 16; b++) {
+      int64_t t = (int64_t)g * 16 + b - (int64_t)d;
+      if (t >= 0 && t < (int64_t)L * M) {
+        uint32_t ri = (uint32_t)(t / M), m = (uint32_t)(t % M);
+        uint64_t row = sb * 32 * L + (uint64_t)ri * 32 + lane;
+        if (row < n) w[b >> 2] |= (uint32_t)s[(uint64_t)m * n + row] << (8 * (b & 3));
+      }
+    }
+    reinterpret_cast<uint4*>(dst)[(sb0 * units) * 32 + rec] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+__global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+template <int QL>
+struct LutVec;
+template <>
+struct LutVec<4> { using T = float4; };
+template <>
+struct LutVec<2> { using T = float2; };
+
+template <int QL>
+__device__ __forceinline__ void lut_load(const unsigned char* lut, uint32_t off, float (&v)[QL]) {
+  if (QL == 4) {
+    float4 t = *reinterpret_cast<const float4*>(lut + off);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  } else {
+    float2 t = *reinterpret_cast<const float2*>(lut + off);
+    v[0] = t.x; v[1] = t.y;
+  }
+}
+
+// byte k of `word` times the table row pitch (64*QL bytes), merged with / added to `b`.
+template <int QL>
+__device__ __forceinline__ uint32_t code_addr(uint32_t word, int k, uint32_t b) {
+  if (QL == 4) {
+    // pitch 256: result = {b.byte0, word.byte_k, b.byte2, b.byte3}; b.byte1 is 0 by construction
+    return __byte_perm(word, b, 0x7604u | ((uint32_t)k << 4));
+  } else {
+    return __dp4a(word, 128u << (8 * k), b);
+  }
+}
+
+// One 16-byte unit of the lane's stream = 16 lookups for each of the QL queries.
+// SWITCH: this is unit 0 of a row (steps 0..15 of the macro-iteration): lanes with d == j finish
+// the previous row at step j.  NSTEP < 16 only for the drain unit.
+template <int QL, int D, bool SWITCH, bool SAFE, int NSTEP>
+__device__ __forceinline__ void scan_unit(const uint4 W, const unsigned char* lut_u /*lut + (u-1)*CB*/,
+                                          const uint32_t (&Bp)[16], const uint32_t (&B0)[D],
+                                          const float (&keepf)[D], const float (&swf)[D], uint32_t d,
+                                          float (&acc)[QL], float (&done)[QL]) {
+  const uint32_t ww[4] = {W.x, W.y, W.z, W.w};
+#pragma unroll
+  for (int j = 0; j < NSTEP; j++) {
+    const uint32_t b = (SWITCH && j < D) ? B0[j < D ? j : 0] : Bp[j];
+    // B0 is relative to the table start, Bp to (chunk u-1): the caller passes lut_u accordingly.
+    float v[QL];
+    if (SWITCH && j < D) {
+      lut_load<QL>(lut_u + (size_t)(256 * 64 * QL), code_addr<QL>(ww[j >> 2], j & 3, b), v);
+    } else {
+      lut_load<QL>(lut_u, code_addr<QL>(ww[j >> 2], j & 3, b), v);
+    }
+    if (SWITCH && j < D) {
+      if (SAFE) {
+        const bool sw = d == (uint32_t)j;
+#pragma unroll
+        for (int q = 0; q < QL; q++) {
+          done[q] = sw ? acc[q] : done[q];
+          acc[q] = __fadd_rn(sw ? 0.0f : acc[q], v[q]);
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < QL; q++) {
+          done[q] = j == 0 ? __fmul_rn(acc[q], swf[0]) : __fmaf_rn(acc[q], swf[j < D ? j : 0], done[q]);
+          acc[q] = __fmaf_rn(acc[q], keepf[j < D ? j : 0], v[q]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < QL; q++) acc[q] = __fadd_rn(acc[q], v[q]);
+    }
+  }
+}
+
+// Append the warp's passing rows for query slot q to its (query, warp) buffer; prune first when
+// it would overflow.  Warp-uniform call.
+__device__ __forceinline__ void append_rows(bool pass, float dist, uint32_t pos, uint32_t lane, uint32_t capw,
+                                            uint32_t kprime, uint32_t* kb, uint32_t* pb, uint32_t* cnt_p,
+                                            uint32_t* sthr_q, float* sthrf_q, uint32_t* gthr_q,
+                                            const uint64_t* prow) {
+  uint32_t mask = __ballot_sync(FULL, pass);
+  if (mask == 0) return;
+  uint32_t np = __popc(mask);
+  uint32_t cnt = *cnt_p;
+  if (cnt + np > capw) {  // capw >= k'+32, so cnt > k' here
+    uint32_t T = warp_select_k(kb, pb, cnt, kprime, prow);
+    cnt = kprime;
+    if (lane == 0) {
+      uint32_t old = atomicMin(sthr_q, T);
+      *sthrf_q = key_to_float(min(old, T));
+      if (gthr_q) atomicMin(gthr_q, T);
+    }
+    __syncwarp();
+    pass = pass && ordered_key(dist) <= *sthr_q;
+    mask = __ballot_sync(FULL, pass);
+    np = __popc(mask);
+  }
+  if (pass) {
+    uint32_t r = __popc(mask & ((1u << lane) - 1u));
+    kb[cnt + r] = ordered_key(dist);
+    pb[cnt + r] = pos;
+  }
+  if (lane == 0) *cnt_p = cnt + np;
+  __syncwarp();
+}
+
+// The thresholds change under the scanning warps' feet (other warps tighten them): volatile.
+template <int QL>
+__device__ __forceinline__ void lds_volatile(uint32_t saddr, float (&v)[QL]) {
+  if (QL == 4)
+    asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(saddr));
+  else
+    asm volatile("ld.volatile.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v[0]), "=f"(v[1]) : "r"(saddr));
+}
+
+// Shared-memory footprint of scan3_kernel (host + device agree through this one function).
+__host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, uint32_t dim, uint32_t capw) {
+  size_t lut = (size_t)(M / 16) * 256 * 64 * QL;
+  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 12 + 32;
+}
+
+template <int QL, int D, int NW, int MINB, int DSUB>
+__global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params p,
+                                                              const uint32_t* __restrict__ total_items_p) {
+  constexpr int NT = NW * 32;
+  constexpr uint32_t CB = 256u * 64u * QL;  // bytes per table chunk (16 sub-vectors)
+  constexpr uint32_t SLOTB = 4u * QL;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned char* lut = smem_raw;
+  const uint32_t C16 = p.M >> 4;
+  float* resid = reinterpret_cast<float*>(smem_raw + (size_t)C16 * CB);
+  uint32_t* ckey = reinterpret_cast<uint32_t*>(resid + QL * p.dim);
+  uint32_t* cpos = ckey + (size_t)QL * NW * p.capw;
+  uint32_t* ccnt = cpos + (size_t)QL * NW * p.capw;
+  float* sthrf = reinterpret_cast<float*>(ccnt + QL * NW);  // 16-byte aligned (all sizes are multiples of 16)
+  uint32_t* sthr = reinterpret_cast<uint32_t*>(sthrf + QL);
+  uint32_t* spair = sthr + QL;
+  uint32_t* sitem = spair + QL;
+  const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
+
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t d = lane % D;
+  const uint32_t M = p.M, dsub = p.dsub, dim = p.dim, kprime = p.kprime, capw = p.capw, L = p.L;
+  const uint32_t units = L * C16 + 1;
+  const uint32_t total_items = *total_items_p;
+
+  // per-lane table offsets for static step j (see header): slot = (j-d) mod 16;
+  //   Bp[j]: relative to chunk (u-1): + CB when the lane is already on chunk u (j >= d)
+  //   B0[j]: unit 0 of a row, relative to the table start: lanes with j < d are on the LAST chunk
+  uint32_t Bp[16], B0[D];
+  float keepf[D], swf[D];
+#pragma unroll
+  for (int j = 0; j < 16; j++) Bp[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? CB : 0u);
+#pragma unroll
+  for (int j = 0; j < D; j++) {
+    B0[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? 0u : (C16 - 1) * CB);
+    keepf[j] = d == (uint32_t)j ? 0.0f : 1.0f;
+    swf[j] = d == (uint32_t)j ? 1.0f : 0.0f;
+  }
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) *sitem = atomicAdd(p.item_counter, 1u);
+    __syncthreads();
+    const uint32_t item = *sitem;
+    if (item >= total_items) break;
+    uint32_t lo = 0, hi = p.nlist;
+    while (hi - lo > 1) {
+      uint32_t mid = (lo + hi) >> 1;
+      if (p.item_off[mid] <= item) lo = mid; else hi = mid;
+    }
+    const uint32_t part = lo;
+    const uint64_t row_base = p.part_off[part];
+    const uint32_t n_p = (uint32_t)(p.part_off[part + 1] - row_base);
+    const uint32_t nch = (n_p + p.chunk_vecs - 1) / p.chunk_vecs;
+    const uint32_t local = item - p.item_off[part];
+    const uint32_t g = local / nch, c = local % nch;
+    const uint32_t pbase = p.part_pair_off[part] + g * QL;
+    const uint32_t nq = min((uint32_t)QL, p.part_pair_off[part + 1] - pbase);
+    const uint64_t* prow = p.row_ids + row_base;
+    const uint64_t* bm = p.bitmask ? p.bitmask[part] : nullptr;
+
+    if (tid < QL) {
+      uint32_t pr = tid < nq ? p.pair_list[pbase + tid] : 0xffffffffu;
+      spair[tid] = pr;
+      uint32_t t0 = KEY_PINF;
+      if (p.qthr && tid < nq) t0 = __ldcg(p.qthr + pr / p.P);
+      sthr[tid] = t0;
+      sthrf[tid] = key_to_float(t0);
+    }
+    if (tid < NW * QL) ccnt[tid] = 0;
+    for (uint32_t i = tid; i < QL * dim; i += NT) {
+      uint32_t qq = i / dim, e = i - qq * dim;
+      float val = 0.0f;
+      if (qq < nq) {
+        uint32_t qidx = p.pair_list[pbase + qq] / p.P;
+        float x = p.queries[(size_t)qidx * dim + e];
+        val = p.residual ? __fsub_rn(x, p.centroids[(size_t)part * dim + e]) : x;
+      }
+      resid[i] = val;
+    }
+    __syncthreads();
+
+    // ---- A4: ADC tables, interleaved over the QL queries --------------------------------
+    // thread -> (slot = tid%16, code = tid/16 + k*NT/16): a quarter/half warp writes consecutive
+    // slots of one code row -> conflict-free wide stores.
+    uint32_t maxbits = 0;
+    {
+      const uint32_t slot = tid & 15;
+#pragma unroll 1
+      for (uint32_t ch = 0; ch < C16; ch++) {
+        const uint32_t m = ch * 16 + slot;
+        float xr[QL][DSUB > 0 ? DSUB : 1];
+        if (DSUB > 0) {
+#pragma unroll
+          for (int q = 0; q < QL; q++)
+#pragma unroll
+            for (int i = 0; i < DSUB; i++) xr[q][i] = resid[q * dim + m * DSUB + i];
+        }
+#pragma unroll 1
+        for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
+          const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
+          float yr[DSUB > 0 ? DSUB : 1];
+          if (DSUB > 0) {
+#pragma unroll
+            for (int i = 0; i < DSUB / 4; i++) {
+              float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
+              yr[4 * i] = v4.x; yr[4 * i + 1] = v4.y; yr[4 * i + 2] = v4.z; yr[4 * i + 3] = v4.w;
+            }
+          }
+          float val[QL];
+#pragma unroll
+          for (int q = 0; q < QL; q++) {
+            if (DSUB > 0)
+              val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr, dsub);
+            else
+              val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub, y, dsub);
+            maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
+          }
+          unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
+          if (QL == 4)
+            *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
+          else
+            *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
+        }
+      }
+    }
+    // exact-FMA switch only if no partial sum of <=256 entries can overflow: |T| < 2^118
+    const bool unsafe = __syncthreads_or(maxbits >= 0x7a800000u) != 0;
+
+    // ---- A5 + A6: scan the chunk's superblocks ---------------------------------------------
+    const uint32_t v0 = c * p.chunk_vecs;
+    const uint32_t vend = min(n_p, v0 + p.chunk_vecs);
+    const uint32_t sb_lo = v0 / (32 * L), sb_hi = (vend + 32 * L - 1) / (32 * L);
+    const float lower = p.lower, upper = p.upper;
+    const bool has_lower = p.has_lower != 0, has_upper = p.has_upper != 0;
+    const uint8_t* cbase = p.codes + (size_t)p.sb_off[part] * units * 512 + lane * 16;
+
+#pragma unroll 1
+    for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
+      const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
+      uint4 cur = __ldg(up), n1 = __ldg(up + 32);
+      uint32_t gi = 0;  // unit index of `cur`
+      float acc[QL], done[QL];
+#pragma unroll
+      for (int q = 0; q < QL; q++) acc[q] = done[q] = 0.0f;
+      const uint32_t row0 = sb * 32 * L + lane;
+#pragma unroll 1
+      for (uint32_t i = 0; i <= L; i++) {
+        uint4 n2 = make_uint4(0, 0, 0, 0);
+        if (gi + 2 < units) n2 = __ldg(up + (size_t)(gi + 2) * 32);
+        if (i < L) {
+          if (unsafe) scan_unit<QL, D, true, true, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+          else scan_unit<QL, D, true, false, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+        } else {
+          if (unsafe) scan_unit<QL, D, true, true, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+          else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+        }
+        cur = n1; n1 = n2; gi++;
+        if (i >= 1) {
+          // `done` = distance of row i-1 of this lane
+          const uint32_t r = row0 + (i - 1) * 32;
+          float thr[QL];
+          lds_volatile<QL>(sthrf_saddr, thr);
+          uint32_t pm = 0;
+#pragma unroll
+          for (int q = 0; q < QL; q++) {
+            bool ok = done[q] <= thr[q];
+            if (has_lower) ok = ok && (lower <= done[q]);
+            if (has_upper) ok = ok && (done[q] < upper);
+            pm |= ok ? (1u << q) : 0u;
+          }
+          if (r >= vend) pm = 0;
+          pm &= (1u << nq) - 1u;
+          if (__any_sync(FULL, pm != 0)) {
+            if (bm && pm) {
+              if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
+            }
+#pragma unroll
+            for (int q = 0; q < QL; q++) {
+              const uint32_t b = (uint32_t)q * NW + w;
+              uint32_t pr = spair[q];
+              append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
+                          cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
+                          (p.qthr && pr != 0xffffffffu) ? p.qthr + pr / p.P : nullptr, prow);
+            }
+          }
+        }
+        if (i == L) break;
+#pragma unroll 1
+        for (uint32_t u = 1; u < C16; u++) {
+          uint4 n3 = make_uint4(0, 0, 0, 0);
+          if (gi + 2 < units) n3 = __ldg(up + (size_t)(gi + 2) * 32);
+          scan_unit<QL, D, false, true, 16>(cur, lut + (size_t)(u - 1) * CB, Bp, B0, keepf, swf, d, acc, done);
+          cur = n1; n1 = n3; gi++;
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- finalize: one warp per query: gather the warps' buffers, select k', sorted emit ----
+#pragma unroll 1
+    for (uint32_t qq = w; qq < nq; qq += NW) {
+      uint32_t* dk = ckey + (size_t)qq * NW * capw;
+      uint32_t* dp = cpos + (size_t)qq * NW * capw;
+      uint32_t n = ccnt[qq * NW];
+#pragma unroll 1
+      for (uint32_t w2 = 1; w2 < NW; w2++) {
+        const uint32_t n2 = ccnt[qq * NW + w2];
+        const uint32_t* sk = dk + (size_t)w2 * capw;
+        const uint32_t* sp = dp + (size_t)w2 * capw;
+        for (uint32_t i0 = 0; i0 < n2; i0 += 32) {
+          uint32_t i = i0 + lane, kk = 0, pp = 0;
+          if (i < n2) { kk = sk[i]; pp = sp[i]; }
+          __syncwarp();
+          if (i < n2) { dk[n + i] = kk; dp[n + i] = pp; }
+          __syncwarp();
+        }
+        n += n2;
+      }
+      if (n > kprime) {
+        uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
+        n = kprime;
+        if (p.qthr && lane == 0) atomicMin(p.qthr + spair[qq] / p.P, T);
+      } else if (n == kprime && p.qthr) {
+        uint32_t mx = 0;
+        for (uint32_t i = lane; i < n; i += 32) mx = max(mx, dk[i]);
+        mx = __reduce_max_sync(FULL, mx);
+        if (lane == 0) atomicMin(p.qthr + spair[qq] / p.P, mx);
+      }
+      const size_t slot = (size_t)spair[qq] * p.max_chunks + c;
+      warp_sort_emit(dk, dp, n, prow, row_base, p.out_dist + slot * kprime, p.out_pos + slot * kprime,
+                     p.out_rowid + slot * kprime);
+      if (lane == 0) p.out_count[slot] = n;
+    }
+  }
+}
+
+}  // namespace lb200

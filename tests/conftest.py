@@ -3,6 +3,9 @@ import sys
 
 import pytest
 
+# build every device code layout so the tests can force each scan variant (A/B parity)
+os.environ.setdefault("LB200_LAYOUTS", "all")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -79,6 +79,10 @@ CASES = [
     ("dot", 96, 8, 2), ("l2", 96, 8, 2),       # dsub 12: generic table path
     ("l2", 32, 16, 2), ("l2", 24, 2, 1),       # dsub 2 / 12, M=2 only fits variant 1
     ("l2", 256, 32, 2), ("dot", 768, 48, 2),   # QL sweeps through VG=32/16/8/4
+    # variant 3 (skew streams): D=8/QL=4 for M<=48, D=16/QL=2 for M in (48,96]
+    ("l2", 128, 16, 3), ("cosine", 128, 16, 3), ("dot", 128, 16, 3), ("l2", 32, 16, 3),
+    ("l2", 256, 32, 3), ("dot", 768, 48, 3), ("l2", 576, 48, 3), ("l2", 1024, 64, 3),
+    ("cosine", 192, 96, 3), ("dot", 1536, 96, 3),
 ]
 
 
@@ -110,7 +114,7 @@ def test_search_in_partition_parity(oracle, metric, d, M, variant):
     ix.close()
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 def test_bounds_and_prefilter(oracle, variant):
     from lance_b200 import IvfPqIndex
     sizes = [500, 0, 77, 1300]
@@ -148,7 +152,7 @@ def test_distance_ties_ordered_by_row_id(oracle):
     data.codes[:] = 7
     o = oracle.OracleIndex(data)
     q = np.random.default_rng(1).normal(size=(3, 32)).astype(np.float32)
-    for variant in (1, 2):
+    for variant in (1, 2):  # M=4: variant 3 needs M % 16 == 0, see the M=16 tie test below
         ix = IvfPqIndex(data)
         ix.set_scan_variant(variant)
         od, oi, oc = ix.search_in_partition(np.tile(np.arange(2, dtype=np.uint32), (3, 1)), q, 10)
@@ -157,6 +161,61 @@ def test_distance_ties_ordered_by_row_id(oracle):
                 rd, ri = o.search_in_partition(p, q[qi], 10)
                 assert oi[qi, p, :len(ri)].tolist() == ri.tolist()
         ix.close()
+
+
+def test_variant3_ties_and_nonfinite(oracle):
+    """Variant 3: all-equal distances are ordered by row id (whole search and per partition), and
+    a table with non-finite / huge entries takes the select-based switch path with results
+    still bit-identical."""
+    from lance_b200 import IvfPqIndex, Query
+    data = _ragged_index("l2", 64, 2, 16, [2100, 300], seed=4)
+    data.codes[:] = 7
+    o = oracle.OracleIndex(data)
+    q = np.random.default_rng(1).normal(size=(5, 64)).astype(np.float32)
+    ix = IvfPqIndex(data)
+    ix.set_scan_variant(3)
+    od, oi, oc = ix.search_in_partition(np.tile(np.arange(2, dtype=np.uint32), (5, 1)), q, 10)
+    for qi in range(5):
+        for p in range(2):
+            rd, ri = o.search_in_partition(p, q[qi], 10)
+            assert oi[qi, p, :len(ri)].tolist() == ri.tolist()
+    gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=2))
+    rd, ri, rc, _ = o.search(q, k=10, nprobes=2)
+    _assert_same(gd, gi, gc, rd, ri, rc, "ties")
+    ix.close()
+    # huge codebook entries: partial sums overflow to +inf for some rows
+    data = _ragged_index("l2", 64, 3, 16, [1500, 40, 700], seed=9)
+    data.codebook[3, 5, :] = 3e19   # (3e19)^2*4 ~ 3.6e39 -> +inf table entry
+    data.codebook[7, 9, :] = 1e18
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    ix.set_scan_variant(3)
+    parts = np.tile(np.arange(3, dtype=np.uint32), (5, 1))
+    od, oi, oc = ix.search_in_partition(parts, q, 20)
+    for qi in range(5):
+        for p in range(3):
+            rd, ri = o.search_in_partition(p, q[qi], 20)
+            n = len(rd)
+            assert oc[qi, p] == n
+            assert oi[qi, p, :n].tolist() == ri.tolist()
+            assert _bits(od[qi, p, :n]).tolist() == _bits(rd).tolist()
+    ix.close()
+
+
+@pytest.mark.parametrize("L", [1, 4, 32])
+def test_variant3_superblock_depths(oracle, L, monkeypatch):
+    from lance_b200 import IvfPqIndex, Query
+    monkeypatch.setenv("LB200_SKEW_L", str(L))
+    data = random_index(30000, 64, 8, 16, "l2", seed=12)
+    q = queries_near_centroids(data, 50, seed=5)
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    ix.set_scan_variant(3)
+    for Q in (1, 3, 50):   # small batches chunk the partitions across CTAs
+        rd, ri, rc, _ = o.search(q[:Q], k=10, nprobes=4)
+        gd, gi, gc = ix.search(Query(key=q[:Q], k=10, nprobes=4))
+        _assert_same(gd, gi, gc, rd, ri, rc, f"L={L} Q={Q}")
+    ix.close()
 
 
 # ---- whole path: VectorIndex::search (+ refine) ---------------------------------------------
@@ -194,7 +253,7 @@ def test_variants_agree_and_bounds_in_search(oracle):
     rd, ri, rc, _ = o.search(q, k=10, nprobes=8)
     mid = float(np.median(rd[:, 5]))
     rdb, rib, rcb, _ = o.search(q, k=10, nprobes=8, lower=mid * 0.9, upper=mid * 1.1)
-    for variant in (1, 2):
+    for variant in (1, 2, 3):
         ix = IvfPqIndex(data)
         ix.set_scan_variant(variant)
         gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=8))
