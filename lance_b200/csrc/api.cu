@@ -212,8 +212,9 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
     CKF(cudaMalloc(&ix->d_sb_off, (nlist + 1) * 8));
     CKF(cudaMemcpyAsync(ix->d_sb_off, sb_off.data(), (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
     size_t units = (size_t)L * (M / 16) + 1;
-    size_t b3 = std::max<size_t>((size_t)sb * units * 512, 512);
+    size_t b3 = (size_t)sb * units * 512 + 2 * 512;  // + 2 units: the scan prefetches 2 units ahead
     CKF(cudaMalloc(&ix->d_codes3, b3));
+    CKF(cudaMemsetAsync(ix->d_codes3 + (b3 - 1024), 0, 1024, ix->stream));
   }
   size_t codes_b = (size_t)(t + 64) * 16 * M;
   if (want_tile) {

@@ -220,7 +220,7 @@ __device__ __forceinline__ void lds_volatile(uint32_t saddr, float (&v)[QL]) {
 // Shared-memory footprint of scan3_kernel (host + device agree through this one function).
 __host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, uint32_t dim, uint32_t capw) {
   size_t lut = (size_t)(M / 16) * 256 * 64 * QL;
-  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 12 + 32;
+  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32;
 }
 
 template <int QL, int D, int NW, int MINB, int DSUB>
@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   float* sthrf = reinterpret_cast<float*>(ccnt + QL * NW);  // 16-byte aligned (all sizes are multiples of 16)
   uint32_t* sthr = reinterpret_cast<uint32_t*>(sthrf + QL);
   uint32_t* spair = sthr + QL;
-  uint32_t* sitem = spair + QL;
+  uint32_t* sqidx = spair + QL;
+  uint32_t* sitem = sqidx + QL;
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -260,6 +261,16 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     B0[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? 0u : (C16 - 1) * CB);
     keepf[j] = d == (uint32_t)j ? 0.0f : 1.0f;
     swf[j] = d == (uint32_t)j ? 1.0f : 0.0f;
+  }
+  // Keep these per-lane constants in registers: left alone, ptxas rematerialises them inside the
+  // hot loop (ISETP+FSEL per switch step; r01 profile) which costs more issue slots than the FMAs.
+#pragma unroll
+  for (int j = 0; j < 16; j++) asm volatile("" : "+r"(Bp[j]));
+#pragma unroll
+  for (int j = 0; j < D; j++) {
+    asm volatile("" : "+r"(B0[j]));
+    asm volatile("" : "+f"(keepf[j]));
+    asm volatile("" : "+f"(swf[j]));
   }
 
   for (;;) {
@@ -287,10 +298,13 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     if (tid < QL) {
       uint32_t pr = tid < nq ? p.pair_list[pbase + tid] : 0xffffffffu;
       spair[tid] = pr;
+      const uint32_t qi = tid < nq ? pr / p.P : 0u;
+      sqidx[tid] = qi;
       uint32_t t0 = KEY_PINF;
-      if (p.qthr && tid < nq) t0 = __ldcg(p.qthr + pr / p.P);
+      if (p.qthr && tid < nq) t0 = __ldcg(p.qthr + qi);
       sthr[tid] = t0;
-      sthrf[tid] = key_to_float(t0);
+      // unused query slots never pass the fast test
+      sthrf[tid] = tid < nq ? key_to_float(t0) : __int_as_float(0xff800000);
     }
     if (tid < NW * QL) ccnt[tid] = 0;
     for (uint32_t i = tid; i < QL * dim; i += NT) {
@@ -364,15 +378,26 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
       const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
       uint4 cur = __ldg(up), n1 = __ldg(up + 32);
-      uint32_t gi = 0;  // unit index of `cur`
+      const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
       float acc[QL], done[QL];
 #pragma unroll
       for (int q = 0; q < QL; q++) acc[q] = done[q] = 0.0f;
       const uint32_t row0 = sb * 32 * L + lane;
+      // pick up bounds found meanwhile by other work items of the same queries
+      if (p.qthr) {
+        if (lane < nq) {
+          uint32_t t = __ldcg(p.qthr + sqidx[lane]);
+          if (t < sthr[lane]) {
+            uint32_t old = atomicMin(sthr + lane, t);
+            sthrf[lane] = key_to_float(min(old, t));
+          }
+        }
+        __syncwarp();
+      }
 #pragma unroll 1
       for (uint32_t i = 0; i <= L; i++) {
-        uint4 n2 = make_uint4(0, 0, 0, 0);
-        if (gi + 2 < units) n2 = __ldg(up + (size_t)(gi + 2) * 32);
+        const uint4 n2 = __ldg(pf);
+        pf += 32;
         if (i < L) {
           if (unsafe) scan_unit<QL, D, true, true, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
           else scan_unit<QL, D, true, false, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
@@ -380,43 +405,48 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           if (unsafe) scan_unit<QL, D, true, true, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
           else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
         }
-        cur = n1; n1 = n2; gi++;
+        cur = n1; n1 = n2;
         if (i >= 1) {
-          // `done` = distance of row i-1 of this lane
-          const uint32_t r = row0 + (i - 1) * 32;
+          // `done` = distance of row i-1 of this lane.  Fast test: running threshold only; bounds,
+          // tail rows and the prefilter are applied on the (rare) slow path.
           float thr[QL];
           lds_volatile<QL>(sthrf_saddr, thr);
-          uint32_t pm = 0;
+          bool anyp = done[0] <= thr[0];
 #pragma unroll
-          for (int q = 0; q < QL; q++) {
-            bool ok = done[q] <= thr[q];
-            if (has_lower) ok = ok && (lower <= done[q]);
-            if (has_upper) ok = ok && (done[q] < upper);
-            pm |= ok ? (1u << q) : 0u;
-          }
-          if (r >= vend) pm = 0;
-          pm &= (1u << nq) - 1u;
-          if (__any_sync(FULL, pm != 0)) {
+          for (int q = 1; q < QL; q++) anyp = anyp || (done[q] <= thr[q]);
+          if (__any_sync(FULL, anyp)) {
+            const uint32_t r = row0 + (i - 1) * 32;
+            uint32_t pm = 0;
+#pragma unroll
+            for (int q = 0; q < QL; q++) {
+              bool ok = done[q] <= thr[q];
+              if (has_lower) ok = ok && (lower <= done[q]);
+              if (has_upper) ok = ok && (done[q] < upper);
+              pm |= ok ? (1u << q) : 0u;
+            }
+            if (r >= vend) pm = 0;
+            pm &= (1u << nq) - 1u;
             if (bm && pm) {
               if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
             }
+            if (__any_sync(FULL, pm != 0)) {
 #pragma unroll
-            for (int q = 0; q < QL; q++) {
-              const uint32_t b = (uint32_t)q * NW + w;
-              uint32_t pr = spair[q];
-              append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
-                          cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
-                          (p.qthr && pr != 0xffffffffu) ? p.qthr + pr / p.P : nullptr, prow);
+              for (int q = 0; q < QL; q++) {
+                const uint32_t b = (uint32_t)q * NW + w;
+                append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
+                            cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
+                            (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
+              }
             }
           }
         }
         if (i == L) break;
 #pragma unroll 1
         for (uint32_t u = 1; u < C16; u++) {
-          uint4 n3 = make_uint4(0, 0, 0, 0);
-          if (gi + 2 < units) n3 = __ldg(up + (size_t)(gi + 2) * 32);
+          const uint4 n3 = __ldg(pf);
+          pf += 32;
           scan_unit<QL, D, false, true, 16>(cur, lut + (size_t)(u - 1) * CB, Bp, B0, keepf, swf, d, acc, done);
-          cur = n1; n1 = n3; gi++;
+          cur = n1; n1 = n3;
         }
       }
     }
@@ -445,12 +475,12 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       if (n > kprime) {
         uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
         n = kprime;
-        if (p.qthr && lane == 0) atomicMin(p.qthr + spair[qq] / p.P, T);
+        if (p.qthr && lane == 0) atomicMin(p.qthr + sqidx[qq], T);
       } else if (n == kprime && p.qthr) {
         uint32_t mx = 0;
         for (uint32_t i = lane; i < n; i += 32) mx = max(mx, dk[i]);
         mx = __reduce_max_sync(FULL, mx);
-        if (lane == 0) atomicMin(p.qthr + spair[qq] / p.P, mx);
+        if (lane == 0) atomicMin(p.qthr + sqidx[qq], mx);
       }
       const size_t slot = (size_t)spair[qq] * p.max_chunks + c;
       warp_sort_emit(dk, dp, n, prow, row_base, p.out_dist + slot * kprime, p.out_pos + slot * kprime,
