@@ -48,16 +48,7 @@ def partition_sizes(N, nlist, seed, sigma=0.5):
     return sizes
 
 
-def assign_partitions(sizes, world):
-    """Greedy bin-packing (largest first) of partitions onto ranks by row count."""
-    order = np.argsort(-sizes, kind="stable")
-    load = np.zeros(world, dtype=np.int64)
-    owner = np.zeros(len(sizes), dtype=np.int64)
-    for p in order:
-        r = int(np.argmin(load))
-        owner[p] = r
-        load[r] += sizes[p]
-    return owner
+from lance_b200.shard import assign_partitions  # noqa: E402  (greedy bin-packing)
 
 
 def make_shard(wl, seed, rank, world, keep_raw=False):
@@ -277,7 +268,18 @@ def main():
                                   g_oc.data_ptr(), world, Q, ks, kprime, k, f_od.data_ptr(), f_oi.data_ptr(),
                                   f_oc.data_ptr(), stream=sp)
 
+    from lance_b200 import Query
+    hq_np = h_q.numpy()
+    e2e_out = (h_od.numpy(), h_oi.numpy().view(np.uint64), h_oc.numpy().view(np.uint32))
+
+    def e2e_host_abi_step():
+        # the call a Lance host makes: lb200_search with HOST buffers (pinned), blocking; the H2D of
+        # the queries and the D2H of the results happen inside the library call
+        ix.search(Query(key=hq_np, k=k, nprobes=nprobes, refine_factor=refine or None), out=e2e_out)
+
     def e2e_step():
+        if not shard_mode:
+            return e2e_host_abi_step()
         d_q.copy_(h_q, non_blocking=True)
         device_step()
         if rank == 0:
@@ -329,7 +331,16 @@ def main():
     for _ in range(2):
         e2e_step()
     e2e_steps = max(3, min(args.steps, 10))
-    ms_e2e = timed(e2e_step, e2e_steps)
+    if shard_mode:
+        ms_e2e = timed(e2e_step, e2e_steps)
+    else:
+        # blocking host call: host wall clock between two device syncs is the end-to-end time
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        ms_e2e = (time.perf_counter() - t0) * 1e3
 
     # scan bytes / time across ranks (sum of bytes, max of time): whole-job scan bandwidth
     agg = torch.tensor([float(np.mean(scan_ms)), float(np.mean(scan_bytes))], device=dev, dtype=torch.float64)
@@ -351,6 +362,13 @@ def main():
     my_scan_ms = float(np.mean(scan_ms))
     my_bytes = float(np.mean(scan_bytes))
     achieved = my_bytes / (my_scan_ms * 1e-3) / 1e9 if my_scan_ms > 0 else 0.0
+    kname = "scan3_kernel" if st["scan_variant"] == 3 else "scan_kernel"
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "ncu_scan_traffic.json")
+    if os.path.exists(tpath):
+        for rec in json.load(open(tpath)):
+            if rec["workload"] == args.workload and rec["scan_variant"] == st["scan_variant"] and rec["n_gpus"] == world:
+                traffic, traffic_src = rec["dram_bytes_per_launch"] / 1e9, rec["source"]
     qps = Q * args.steps / (ms_total * 1e-3)
     e2e_qps = Q * e2e_steps / (ms_e2e * 1e-3)
     line = {
@@ -363,14 +381,17 @@ def main():
                    "scan_variant": st["scan_variant"], "scan_queries_per_cta": st["scan_ql"],
                    "index_build_s": round(t_build, 1)},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "kernel": "scan_kernel (rank 0)",
+                     "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu dram read+write)",
+                     "traffic_source": traffic_src, "kernel": kname + " (rank 0)",
                      "peak_source": peak_src, "scan_ms_per_launch": my_scan_ms,
                      "algorithmic_bytes_per_launch": my_bytes,
                      "note": "algorithmic bytes = sum over (query,partition) pairs of n_p*M code bytes; QL queries "
                              "share each code load, so the figure can exceed DRAM traffic (SURVEY 8d)"},
         "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": int(h_q.numel() * 4) * world,
                 "d2h_bytes_per_step": int(h_od.numel() * 4 + h_oi.numel() * 8 + h_oc.numel() * 4),
-                "ms_per_step": ms_e2e / e2e_steps},
+                "ms_per_step": ms_e2e / e2e_steps,
+                "path": "torch pinned copies + lb200_search_device + NCCL all_gather + merge" if shard_mode else
+                        "lb200_search (host-pointer C ABI, pinned host buffers, blocking; host wall clock)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
     }

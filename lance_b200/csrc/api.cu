@@ -94,13 +94,14 @@ struct lb200_index {
   std::vector<uint64_t> h_part_off;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[6] = {};
-  std::mutex mu;
+  std::mutex mu, stage_mu;
   bool profiling = false;
   int force_variant = 0;
   lb200_stats stats = {};
   int sm_count = 148;
   size_t smem_optin = 0, smem_per_sm = 0;
   Arena arena;
+  Arena stage;  // host<->device staging of lb200_search (queries in, results out)
   const uint64_t** d_bitmask_ptrs = nullptr;  // scratch for prefilter pointers
 };
 
@@ -269,6 +270,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_codes3);
   cudaFree(ix->d_sb_off);
   cudaFree(ix->arena.base);
+  cudaFree(ix->stage.base);
   cudaFree((void*)ix->d_bitmask_ptrs);
   for (auto& e : ix->ev)
     if (e) cudaEventDestroy(e);

@@ -545,14 +545,17 @@ extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t 
   const bool refined = refine_factor > 0 && ix->d_raw;
   if (refine_factor > 0 && !ix->d_raw) return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
   const uint32_t ostride = refined ? k : k * std::max(refine_factor, 1u);
-  HostStage hs;
+  // staging for queries/results: a grow-only buffer owned by the handle (no cudaMalloc per call)
+  const size_t nq = (size_t)Q * ix->dim * 4, no = (size_t)Q * ostride;
+  char* b = nullptr;
+  std::lock_guard<std::mutex> slk(ix->stage_mu);  // whole call: the staging buffer is per handle
   {
     std::lock_guard<std::mutex> lk(ix->mu);
     CK(cudaSetDevice(ix->device));
+    int rs = ix->stage.reserve(Arena::pad(nq) + Arena::pad(no * 4) + Arena::pad(no * 8) + Arena::pad((size_t)Q * 4));
+    if (rs) return rs;
+    b = ix->stage.base;
   }
-  const size_t nq = (size_t)Q * ix->dim * 4, no = (size_t)Q * ostride;
-  CK(cudaMalloc(&hs.p, Arena::pad(nq) + Arena::pad(no * 4) + Arena::pad(no * 8) + Arena::pad((size_t)Q * 4)));
-  char* b = (char*)hs.p;
   float* d_q = (float*)b; b += Arena::pad(nq);
   float* d_od = (float*)b; b += Arena::pad(no * 4);
   uint64_t* d_or = (uint64_t*)b; b += Arena::pad(no * 8);

@@ -128,9 +128,10 @@ class IvfPqIndex:
             _fptr(upper_bound), bm_arr, _p(od), _p(oi), _p(oc)))
         return od, oi, oc
 
-    def search(self, query: Query):
+    def search(self, query: Query, out=None):
         """VectorIndex::search (vector.rs:133) + the scanner's refine when refine_factor is set.
-        Returns (distances [Q][k_out], row ids [Q][k_out], counts [Q])."""
+        Returns (distances [Q][k_out], row ids [Q][k_out], counts [Q]).  `out` = caller-owned
+        (f32 [Q][k_out], u64 [Q][k_out], u32 [Q]) arrays, e.g. views of pinned host memory."""
         key = np.atleast_2d(_f32(query.key))
         self._check_dim(key)
         if query.k <= 0:
@@ -138,9 +139,15 @@ class IvfPqIndex:
         Q = key.shape[0]
         rf = int(query.refine_factor or 0)
         kout = query.k if (rf and self.has_raw) else query.k * max(rf, 1)
-        od = np.full((Q, kout), np.inf, dtype=np.float32)
-        oi = np.full((Q, kout), np.iinfo(np.uint64).max, dtype=np.uint64)
-        oc = np.zeros(Q, dtype=np.uint32)
+        if out is not None:
+            od, oi, oc = out
+            assert od.shape == (Q, kout) and od.dtype == np.float32 and od.flags.c_contiguous
+            assert oi.shape == (Q, kout) and oi.dtype == np.uint64 and oi.flags.c_contiguous
+            assert oc.shape == (Q,) and oc.dtype == np.uint32
+        else:
+            od = np.full((Q, kout), np.inf, dtype=np.float32)
+            oi = np.full((Q, kout), np.iinfo(np.uint64).max, dtype=np.uint64)
+            oc = np.zeros(Q, dtype=np.uint32)
         check(self._L.lb200_search(
             self._h, _p(key), C.c_uint32(Q), C.c_uint32(query.nprobes), C.c_uint32(query.k), C.c_uint32(rf),
             _fptr(query.lower_bound), _fptr(query.upper_bound), _p(od), _p(oi), _p(oc)))

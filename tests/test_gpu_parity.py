@@ -375,3 +375,44 @@ def test_full_size_properties(oracle):
     rd, ri, rc, _ = o.search(q[sel], k=10, nprobes=20)
     _assert_same(gd[sel], gi[sel], gc[sel], rd, ri, rc, "cfg1-size sample")
     ix.close()
+
+
+# ---- multi-GPU protocol on one device: G shard handles + lb200_merge_topk_device --------------
+@pytest.mark.parametrize("metric,refine,G", [("l2", 0, 2), ("l2", 4, 3), ("cosine", 3, 2), ("dot", 0, 4)])
+def test_sharded_search_merge_equals_single_index(oracle, metric, refine, G):
+    """every shard returns its k' candidates (+ exact distances), the gathered lists
+    are merged on the device; the result must be bit-identical to the unsharded oracle search."""
+    from lance_b200 import IvfPqIndex
+    from lance_b200.index import merge_topk_device
+    from lance_b200.shard import assign_partitions
+    rng = np.random.default_rng(G)
+    d, nlist, M, k, nprobes, Q = 64, 24, 16, 10, 9, 40
+    vecs = rng.normal(size=(12000, d)).astype(np.float32)
+    data = build_ivf_pq(vecs, metric, nlist, M, seed=2, keep_raw=True, ivf_iters=3, pq_iters=2, sample=4096)
+    q = vecs[rng.integers(0, len(vecs), Q)] + 0.05 * rng.normal(size=(Q, d)).astype(np.float32)
+    rd, ri, rc, _ = oracle.OracleIndex(data).search(q, k=k, nprobes=nprobes, refine_factor=refine)
+    owner = assign_partitions(np.diff(data.part_offsets.astype(np.int64)), G)
+    kp = k * max(refine, 1)
+    dev = torch.device("cuda", 0)
+    dq = torch.from_numpy(q).to(dev)
+    g_d = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
+    g_i = torch.empty((G, Q, kp), dtype=torch.int64, device=dev)
+    g_c = torch.empty((G, Q), dtype=torch.int32, device=dev)
+    g_e = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
+    shards = []
+    for g in range(G):
+        ix = IvfPqIndex(data.subset(np.nonzero(owner == g)[0]))
+        shards.append(ix)
+        ix.search_device(dq.data_ptr(), Q, nprobes, k, refine, g_d[g].data_ptr(), g_i[g].data_ptr(),
+                         g_c[g].data_ptr(), d_out_exact=g_e[g].data_ptr())
+    torch.cuda.synchronize()
+    fd = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    fi = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    fc = torch.empty((Q,), dtype=torch.int32, device=dev)
+    merge_topk_device(0, g_d.data_ptr(), g_i.data_ptr(), g_e.data_ptr() if refine else None, g_c.data_ptr(), G, Q, kp,
+                      kp, k, fd.data_ptr(), fi.data_ptr(), fc.data_ptr())
+    torch.cuda.synchronize()
+    _assert_same(fd.cpu().numpy(), fi.cpu().numpy().astype(np.uint64), fc.cpu().numpy(), rd[:, :k], ri[:, :k], rc,
+                 f"sharded {metric} G={G}")
+    for ix in shards:
+        ix.close()
