@@ -156,11 +156,23 @@ static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint3
     return set_err(LB200_EUNSUPPORTED, "nlist=%u > 8192 not supported by the coarse select kernel yet", ix->nlist);
   dim3 grid((ix->nlist + COARSE_THREADS - 1) / COARSE_THREADS, (Q + COARSE_TQ - 1) / COARSE_TQ);
   size_t smem = (size_t)COARSE_TQ * ix->dim * 4;
-  if (ix->metric == LB200_DOT)
+  const size_t tsm = ((size_t)ix->dim * CQ_PITCH + (size_t)CQ_QB * ix->dim) * 4;
+  if (ix->metric != LB200_DOT && ix->dim % 16 == 0 && ix->dim >= 32 && tsm <= ix->smem_optin && Q >= 8 &&
+      !getenv("LB200_COARSE_SIMPLE")) {
+    CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
+    dim3 g2((ix->nlist + 127) / 128, (Q + CQ_QB - 1) / CQ_QB);
+    coarse_dist_l2_tiled_kernel<<<g2, 128, tsm, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
+  } else if (ix->metric == LB200_DOT)
     coarse_dist_kernel<false><<<grid, COARSE_THREADS, smem, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
   else
     coarse_dist_kernel<true><<<grid, COARSE_THREADS, smem, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
   CK(cudaGetLastError());
+  if (P <= 256 && !getenv("LB200_COARSE_FULLSORT")) {
+    coarse_select2_kernel<<<Q, 256, 0, st>>>(d_D, ix->nlist, P, d_probes, d_pdists);
+    CK(cudaGetLastError());
+    *launches += 2;
+    return 0;
+  }
   uint32_t np2 = next_pow2(ix->nlist);
   size_t ssm = (size_t)np2 * 8;
   if (ssm > 48 * 1024)

@@ -145,4 +145,150 @@ coarse_select_kernel(const float* __restrict__ dist /*[Q][nlist]*/, uint32_t nli
   }
 }
 
+// Fast path of the same selection for P <= 256 (every BASELINE config): instead of sorting all
+// nlist keys, bound the P-th smallest from above by the P-th smallest of 256 strided group
+// minima, collect the (few) keys under that bound and sort only those.  Keys are (ordered
+// distance << 32 | centroid id): unique, so the result is the same total order as the full sort.
+constexpr uint32_t CSEL_CAP = 1024;
+__global__ void __launch_bounds__(256)
+coarse_select2_kernel(const float* __restrict__ dist /*[Q][nlist]*/, uint32_t nlist, uint32_t P,
+                      uint32_t* __restrict__ out_ids, float* __restrict__ out_dists) {
+  __shared__ unsigned long long cand[CSEL_CAP];
+  __shared__ unsigned long long mins[256];
+  __shared__ unsigned long long sT;
+  __shared__ uint32_t scnt;
+  const uint32_t q = blockIdx.x, t = threadIdx.x;
+  const float* drow = dist + (size_t)q * nlist;
+  unsigned long long m = ~0ull;
+  for (uint32_t i = t; i < nlist; i += 256) {
+    unsigned long long kv = ((unsigned long long)ordered_key(drow[i]) << 32) | i;
+    m = kv < m ? kv : m;
+  }
+  mins[t] = m;
+  if (t == 0) scnt = 0;
+  __syncthreads();
+  {
+    uint32_t r = 0;
+    for (uint32_t j = 0; j < 256; j++) r += mins[j] < m ? 1u : 0u;
+    if (r == P - 1 && m != ~0ull) sT = m;  // unique keys -> exactly one thread has rank P-1
+  }
+  __syncthreads();
+  unsigned long long T = sT;
+  for (uint32_t i = t; i < nlist; i += 256) {
+    unsigned long long kv = ((unsigned long long)ordered_key(drow[i]) << 32) | i;
+    if (kv <= T) {
+      uint32_t pos = atomicAdd(&scnt, 1u);
+      if (pos < CSEL_CAP) cand[pos] = kv;
+    }
+  }
+  __syncthreads();
+  uint32_t cnt = scnt;
+  if (cnt > CSEL_CAP) {
+    // adversarial layout: find the exact P-th smallest key by bitwise binary search, re-collect
+    unsigned long long X = 0;
+    for (int bit = 63; bit >= 0; --bit) {
+      unsigned long long c2 = X | (1ull << bit);
+      uint32_t c = 0;
+      for (uint32_t i = t; i < nlist; i += 256) {
+        unsigned long long kv = ((unsigned long long)ordered_key(drow[i]) << 32) | i;
+        c += kv < c2 ? 1u : 0u;
+      }
+      __syncthreads();
+      if (t == 0) scnt = 0;
+      __syncthreads();
+      atomicAdd(&scnt, c);
+      __syncthreads();
+      if (scnt < P) X = c2;  // largest X with #(kv < X) < P  ==  the P-th smallest key
+    }
+    __syncthreads();
+    if (t == 0) scnt = 0;
+    __syncthreads();
+    for (uint32_t i = t; i < nlist; i += 256) {
+      unsigned long long kv = ((unsigned long long)ordered_key(drow[i]) << 32) | i;
+      if (kv <= X) cand[atomicAdd(&scnt, 1u)] = kv;  // exactly P <= 256 entries
+    }
+    __syncthreads();
+    cnt = scnt;
+  }
+  uint32_t n2 = 2;
+  while (n2 < cnt) n2 <<= 1;
+  for (uint32_t i = cnt + t; i < n2; i += 256) cand[i] = ~0ull;
+  __syncthreads();
+  block_bitonic_sort_u64(cand, n2);
+  for (uint32_t i = t; i < P; i += 256) {
+    unsigned long long kv = cand[i];
+    out_ids[(size_t)q * P + i] = (uint32_t)kv;
+    if (out_dists) out_dists[(size_t)q * P + i] = key_to_float((uint32_t)(kv >> 32));
+  }
+}
+
+// Fast L2 coarse distances for d % 16 == 0, 32 <= d (l2_scalar<16> path, l2.rs:65-99): the block's
+// 128 centroid rows are staged ONCE in shared memory (pitch 129 floats: conflict-free both for the
+// coalesced fill and for the lane=centroid reads) and reused for CQ_QB queries, 4 at a time, so the
+// centroid matrix crosses L2 Q/CQ_QB times instead of Q/4 times.  Same operation order as
+// coarse_dist_kernel: 16 lane accumulators per (query, centroid), chunks ascending, lanes summed
+// 0..15, then 0 + t.
+constexpr int CQ_QB = 32;
+constexpr int CQ_PITCH = 129;
+__global__ void __launch_bounds__(128)
+coarse_dist_l2_tiled_kernel(const float* __restrict__ queries, const float* __restrict__ centroids,
+                            uint32_t Q, uint32_t nlist, uint32_t d, float* __restrict__ out) {
+  extern __shared__ float sm[];
+  float* tile = sm;                         // [d][129]
+  float* sq = sm + (size_t)d * CQ_PITCH;    // [CQ_QB][d]
+  const uint32_t c0 = blockIdx.x * 128, q0 = blockIdx.y * CQ_QB, t = threadIdx.x;
+  const uint32_t lane = t & 31, w = t >> 5;
+  // fill: warp w takes centroid rows w, w+4, ...; lanes read consecutive elements (coalesced)
+  for (uint32_t r = w; r < 128; r += 4) {
+    const uint32_t c = c0 + r;
+    for (uint32_t e = lane; e < d; e += 32)
+      tile[(size_t)e * CQ_PITCH + r] = c < nlist ? __ldg(centroids + (size_t)c * d + e) : 0.0f;
+  }
+  for (uint32_t i = t; i < CQ_QB * d; i += 128) {
+    uint32_t qq = q0 + i / d;
+    sq[i] = qq < Q ? __ldg(queries + (size_t)qq * d + (i % d)) : 0.0f;
+  }
+  __syncthreads();
+  const uint32_t c = c0 + t;
+  const uint32_t nchunk = d >> 4;
+#pragma unroll 1
+  for (uint32_t g = 0; g < CQ_QB / 4; g++) {
+    if (q0 + g * 4 >= Q) break;
+    float sums[4][16];
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+#pragma unroll
+      for (int i = 0; i < 16; i++) sums[k][i] = 0.0f;
+    const float* xq = sq + (size_t)g * 4 * d;
+#pragma unroll 1
+    for (uint32_t ch = 0; ch < nchunk; ch++) {
+      float yv[16];
+#pragma unroll
+      for (int i = 0; i < 16; i++) yv[i] = tile[(size_t)(ch * 16 + i) * CQ_PITCH + t];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const float4* x4 = reinterpret_cast<const float4*>(xq + (size_t)k * d + ch * 16);
+#pragma unroll
+        for (int i4 = 0; i4 < 4; i4++) {
+          const float4 xv = x4[i4];  // warp-wide broadcast
+          const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            float df = __fsub_rn(xs[j], yv[i4 * 4 + j]);
+            sums[k][i4 * 4 + j] = __fadd_rn(sums[k][i4 * 4 + j], __fmul_rn(df, df));
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      float tt = 0.0f;
+#pragma unroll
+      for (int i = 0; i < 16; i++) tt = __fadd_rn(tt, sums[k][i]);
+      const uint32_t qq = q0 + g * 4 + k;
+      if (qq < Q && c < nlist) out[(size_t)qq * nlist + c] = __fadd_rn(0.0f, tt);
+    }
+  }
+}
+
 }  // namespace lb200

@@ -53,7 +53,8 @@ def _ragged_index(metric, d, nlist, M, sizes, seed, keep_raw=False):
 
 # ---- A1/A2: find_partitions -------------------------------------------------------------
 @pytest.mark.parametrize("metric,d,nlist", [("l2", 128, 256), ("l2", 8, 33), ("l2", 16, 64), ("l2", 100, 50),
-                                            ("dot", 768, 128), ("dot", 70, 20), ("cosine", 1536, 64)])
+                                            ("dot", 768, 128), ("dot", 70, 20), ("cosine", 1536, 64),
+                                            ("l2", 256, 300), ("l2", 32, 5000), ("cosine", 64, 700)])
 def test_find_partitions_parity(oracle, metric, d, nlist):
     from lance_b200 import IvfPqIndex
     rng = np.random.default_rng(d + nlist)
@@ -62,10 +63,39 @@ def test_find_partitions_parity(oracle, metric, d, nlist):
     if metric == "cosine":
         q = np.stack([oracle.normalize(x) for x in q])
     ix = IvfPqIndex(data)
-    for nprobes in (1, 7, nlist, nlist + 5):
+    for nprobes in (1, 7, min(nlist, 256), min(nlist, 300), nlist, nlist + 5):
         ids, dist = ix.find_partitions(q, nprobes, return_distances=True)
         for i in range(q.shape[0]):
             rid, rd = oracle.find_partitions(data.centroids, q[i], nprobes, metric)
+            assert ids[i].tolist() == rid.tolist()
+            assert _bits(dist[i]).tolist() == _bits(rd).tolist()
+    ix.close()
+
+
+def test_find_partitions_ties_and_clustered_layout(oracle):
+    """Select fast path: (a) all centroids identical -> all distances tie -> order by id;
+    (b) the smallest distances all sit in ONE strided group (ids = 0 mod 256), the layout that
+    overflows the candidate buffer and takes the exact-select fallback."""
+    from lance_b200 import IvfPqIndex
+    rng = np.random.default_rng(0)
+    d, nlist = 64, 4096
+    q = rng.normal(size=(9, d)).astype(np.float32)
+    data = _ragged_index("l2", d, nlist, 2, [1] * nlist, seed=1)
+    data.centroids[:] = data.centroids[0]
+    ix = IvfPqIndex(data)
+    ids, _ = ix.find_partitions(q, 32, return_distances=True)
+    assert ids.tolist() == [list(range(32))] * 9
+    ix.close()
+    data = _ragged_index("l2", d, nlist, 2, [1] * nlist, seed=2)
+    data.centroids[:] = rng.normal(size=(nlist, d)).astype(np.float32) * 0.01 + 5.0
+    far = np.arange(nlist) % 256 != 0
+    data.centroids[far] += 100.0 + np.arange(nlist)[far, None] % 7   # 16 near centroids, 4080 far ones
+    data.centroids[~far] = q[0] + rng.normal(size=(16, d)).astype(np.float32) * 0.1
+    ix = IvfPqIndex(data)
+    for nprobes in (5, 16, 40, 256):
+        ids, dist = ix.find_partitions(q, nprobes, return_distances=True)
+        for i in range(len(q)):
+            rid, rd = oracle.find_partitions(data.centroids, q[i], nprobes, "l2")
             assert ids[i].tolist() == rid.tolist()
             assert _bits(dist[i]).tolist() == _bits(rd).tolist()
     ix.close()
