@@ -242,31 +242,21 @@ def main():
     d_oc = torch.empty((Q,), dtype=torch.int32, device=dev)
     d_ex = torch.empty((Q, ks), dtype=torch.float32, device=dev) if shard_mode else None
     if shard_mode:
-        g_od = torch.empty((world, Q, ks), dtype=torch.float32, device=dev)
-        g_oi = torch.empty((world, Q, ks), dtype=torch.int64, device=dev)
-        g_oc = torch.empty((world, Q), dtype=torch.int32, device=dev)
-        g_ex = torch.empty((world, Q, ks), dtype=torch.float32, device=dev)
-        f_od = torch.empty((Q, k), dtype=torch.float32, device=dev)
-        f_oi = torch.empty((Q, k), dtype=torch.int64, device=dev)
-        f_oc = torch.empty((Q,), dtype=torch.int32, device=dev)
+        from lance_b200.shard import ShardedIvfPq
+        sh = ShardedIvfPq(ix, dist, dev, shard_coarse=not os.environ.get("LB200_REPLICATED_COARSE"))
+        sh.prepare(Q, nprobes, k, refine)
+        f_od, f_oi, f_oc = sh.fd, sh.fi, sh.fc
     h_q = torch.from_numpy(queries).pin_memory()
     h_od = torch.empty((Q, k if (refine or shard_mode) else kprime), dtype=torch.float32).pin_memory()
     h_oi = torch.empty(h_od.shape, dtype=torch.int64).pin_memory()
     h_oc = torch.empty((Q,), dtype=torch.int32).pin_memory()
 
     def device_step():
-        ix.search_device(d_q.data_ptr(), Q, nprobes, k, refine, d_od.data_ptr(), d_oi.data_ptr(), d_oc.data_ptr(),
-                         d_out_exact=d_ex.data_ptr() if shard_mode else None, stream=sp)
         if shard_mode:
-            dist.all_gather_into_tensor(g_od, d_od)
-            dist.all_gather_into_tensor(g_oi, d_oi)
-            dist.all_gather_into_tensor(g_oc, d_oc)
-            if refine:
-                dist.all_gather_into_tensor(g_ex, d_ex)
-            if rank == 0:
-                merge_topk_device(local, g_od.data_ptr(), g_oi.data_ptr(), g_ex.data_ptr() if refine else None,
-                                  g_oc.data_ptr(), world, Q, ks, kprime, k, f_od.data_ptr(), f_oi.data_ptr(),
-                                  f_oc.data_ptr(), stream=sp)
+            sh.search_device(d_q, stream)
+        else:
+            ix.search_device(d_q.data_ptr(), Q, nprobes, k, refine, d_od.data_ptr(), d_oi.data_ptr(), d_oc.data_ptr(),
+                             stream=sp)
 
     from lance_b200 import Query
     hq_np = h_q.numpy()
@@ -322,7 +312,7 @@ def main():
         st = ix.stats()
         scan_ms.append(st["scan_ms"])
         scan_bytes.append(st["scan_code_bytes"])
-        launches += st["kernel_launches"] + (1 if (shard_mode and rank == 0) else 0)
+        launches += st["kernel_launches"] + ((3 if sh.shard_coarse else 0) + (1 if rank == 0 else 0) if shard_mode else 0)
 
     ms_total = timed(profiled_step, args.steps)
     clocks = sampler.stop() if rank == 0 else None

@@ -103,6 +103,22 @@ int32_t lb200_search_device(lb200_index* ix, const float* d_queries, uint32_t Q,
                             const float* upper_or_null, float* d_out_dist, uint64_t* d_out_rowid,
                             uint32_t* d_out_count, float* d_out_exact_or_null, void* stream);
 
+/* Multi-GPU helpers: the coarse step can be sharded over the ranks by QUERIES
+ * (each rank selects probes for Q/G queries, the [Q][P] probe lists are all-gathered) and the
+ * partition-sharded scan then runs with the probe lists given.
+ * lb200_find_partitions_device == lb200_find_partitions on device pointers, asynchronous on
+ *   `stream`; normalize_if_cosine != 0 applies the VectorIndex::search normalisation
+ *   (ivf/v2.rs:370-373) first, so raw queries can be passed.
+ * lb200_search_probed_device == lb200_search_device with find_partitions replaced by the given
+ *   d_part_ids [Q][P] (valid partition ids, as produced by lb200_find_partitions_device). */
+int32_t lb200_find_partitions_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
+                                     int32_t normalize_if_cosine, uint32_t* d_out_part_ids, void* stream);
+int32_t lb200_search_probed_device(lb200_index* ix, const float* d_queries, uint32_t Q,
+                                   const uint32_t* d_part_ids, uint32_t P, uint32_t k,
+                                   uint32_t refine_factor, const float* lower_or_null,
+                                   const float* upper_or_null, float* d_out_dist, uint64_t* d_out_rowid,
+                                   uint32_t* d_out_count, float* d_out_exact_or_null, void* stream);
+
 /* compute_distance (flat.rs:28-86; KNNVectorDistanceExec, io/exec/knn.rs:156-183): one
  * distance per (query,row); validity = Arrow validity bitmap (bit set = valid) or NULL;
  * null rows yield NaN.  out [Q][n]. */

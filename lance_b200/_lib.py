@@ -11,7 +11,7 @@ SO_PATH = os.path.join(_HERE, "liblance_b200.so")
 
 EXPORTS = [
     "lb200_index_create", "lb200_index_destroy", "lb200_find_partitions", "lb200_search_partitions",
-    "lb200_search", "lb200_search_device", "lb200_flat_distance", "lb200_flat_topk",
+    "lb200_search", "lb200_search_device", "lb200_find_partitions_device", "lb200_search_probed_device", "lb200_flat_distance", "lb200_flat_topk",
     "lb200_flat_topk_device", "lb200_merge_topk_device", "lb200_set_profiling", "lb200_get_stats",
     "lb200_set_scan_variant", "lb200_last_error", "lb200_version",
 ]

@@ -545,6 +545,62 @@ extern "C" int32_t lb200_search_device(lb200_index* ix, const float* d_queries, 
   return 0;
 }
 
+extern "C" int32_t lb200_find_partitions_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
+                                                int32_t normalize_if_cosine, uint32_t* d_out_part_ids,
+                                                void* stream) {
+  int rc = check_queries(ix, d_queries, Q);
+  if (rc) return rc;
+  if (!d_out_part_ids) return set_err(LB200_EINVAL, "null output");
+  if (nprobes == 0) return set_err(LB200_EINVAL, "nprobes must be > 0");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+  const uint32_t P = std::min(nprobes, ix->nlist);
+  if (!Q) return 0;
+  size_t need = Arena::pad((size_t)Q * ix->dim * 4) + Arena::pad((size_t)Q * ix->nlist * 4) + 1024;
+  rc = ix->arena.reserve(need);
+  if (rc) return rc;
+  ix->arena.reset();
+  float* d_keys = ix->arena.take<float>((size_t)Q * ix->dim);
+  float* d_D = ix->arena.take<float>((size_t)Q * ix->nlist);
+  const float* keys = d_queries;
+  uint32_t launches = 0;
+  if (normalize_if_cosine && ix->metric == LB200_COSINE) {
+    normalize_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(d_queries, d_keys, Q, ix->dim);
+    CK(cudaGetLastError());
+    keys = d_keys;
+  }
+  rc = coarse_device(ix, keys, Q, P, d_D, d_out_part_ids, nullptr, st, &launches);
+  if (rc) return rc;
+  if (!stream) CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int32_t lb200_search_probed_device(lb200_index* ix, const float* d_queries, uint32_t Q,
+                                              const uint32_t* d_part_ids, uint32_t P, uint32_t k,
+                                              uint32_t refine_factor, const float* lower_or_null,
+                                              const float* upper_or_null, float* d_out_dist, uint64_t* d_out_rowid,
+                                              uint32_t* d_out_count, float* d_out_exact_or_null, void* stream) {
+  int rc = check_queries(ix, d_queries, Q);
+  if (rc) return rc;
+  if (Q && (!d_out_dist || !d_out_rowid || !d_out_count || !d_part_ids)) return set_err(LB200_EINVAL, "null argument");
+  if (P == 0 || P > ix->nlist) return set_err(LB200_EINVAL, "P must be in [1, nlist]");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+  SearchArgs a = {};
+  a.d_queries = d_queries; a.Q = Q; a.d_part_ids = d_part_ids; a.P = P; a.k = k; a.refine_factor = refine_factor;
+  a.normalize = true; a.shard_mode = d_out_exact_or_null != nullptr;
+  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
+  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
+  a.d_out_dist = d_out_dist; a.d_out_rowid = d_out_rowid; a.d_out_count = d_out_count;
+  a.d_out_exact = d_out_exact_or_null;
+  rc = search_pipeline(ix, a, st);
+  if (rc) return rc;
+  if (!stream) CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
 extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
                                 uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
                                 float* out_dist, uint64_t* out_rowid, uint32_t* out_count) {

@@ -241,6 +241,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   uint32_t* spair = sthr + QL;
   uint32_t* sqidx = spair + QL;
   uint32_t* sitem = sqidx + QL;
+  uint32_t* ssb = sitem + 1;  // next superblock (relative to the chunk's first) to hand out
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -307,6 +308,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       sthrf[tid] = tid < nq ? key_to_float(t0) : __int_as_float(0xff800000);
     }
     if (tid < NW * QL) ccnt[tid] = 0;
+    if (tid == 0) *ssb = NW;
     for (uint32_t i = tid; i < QL * dim; i += NT) {
       uint32_t qq = i / dim, e = i - qq * dim;
       float val = 0.0f;
@@ -335,31 +337,43 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
 #pragma unroll
             for (int i = 0; i < DSUB; i++) xr[q][i] = resid[q * dim + m * DSUB + i];
         }
+        // codes in batches of BT: all codebook rows of a batch are requested before the first is
+        // used, so the L2 latency of the (L1-cold) codebook is paid once per batch, not per entry
+        constexpr int BT = DSUB == 8 ? 4 : (DSUB == 16 ? 2 : 1);
+        constexpr uint32_t CSTEP = NT / 16;
 #pragma unroll 1
-        for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
-          const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
-          float yr[DSUB > 0 ? DSUB : 1];
+        for (uint32_t code0 = tid >> 4; code0 < 256; code0 += CSTEP * BT) {
+          float yr[BT][DSUB > 0 ? DSUB : 1];
           if (DSUB > 0) {
 #pragma unroll
-            for (int i = 0; i < DSUB / 4; i++) {
-              float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
-              yr[4 * i] = v4.x; yr[4 * i + 1] = v4.y; yr[4 * i + 2] = v4.z; yr[4 * i + 3] = v4.w;
+            for (int b = 0; b < BT; b++) {
+              const float* y = p.codebook + ((size_t)m * 256 + code0 + b * CSTEP) * dsub;
+#pragma unroll
+              for (int i = 0; i < DSUB / 4; i++) {
+                float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
+                yr[b][4 * i] = v4.x; yr[b][4 * i + 1] = v4.y; yr[b][4 * i + 2] = v4.z; yr[b][4 * i + 3] = v4.w;
+              }
             }
           }
-          float val[QL];
 #pragma unroll
-          for (int q = 0; q < QL; q++) {
-            if (DSUB > 0)
-              val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr, dsub);
+          for (int b = 0; b < BT; b++) {
+            const uint32_t code = code0 + b * CSTEP;
+            float val[QL];
+#pragma unroll
+            for (int q = 0; q < QL; q++) {
+              if (DSUB > 0)
+                val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr[b], dsub);
+              else
+                val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub,
+                                     p.codebook + ((size_t)m * 256 + code) * dsub, dsub);
+              maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
+            }
+            unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
+            if (QL == 4)
+              *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
             else
-              val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub, y, dsub);
-            maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
+              *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
           }
-          unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
-          if (QL == 4)
-            *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
-          else
-            *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
         }
       }
     }
@@ -374,14 +388,51 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     const bool has_lower = p.has_lower != 0, has_upper = p.has_upper != 0;
     const uint8_t* cbase = p.codes + (size_t)p.sb_off[part] * units * 512 + lane * 16;
 
+    // Row test: fast path = running threshold only (4 FSETP + vote); bounds, tail rows and the
+    // prefilter are applied on the (rare) slow path.
+    auto check_rows = [&](const float (&dv)[QL], const uint32_t r) {
+      float thr[QL];
+      lds_volatile<QL>(sthrf_saddr, thr);
+      bool anyp = dv[0] <= thr[0];
+#pragma unroll
+      for (int q = 1; q < QL; q++) anyp = anyp || (dv[q] <= thr[q]);
+      if (__any_sync(FULL, anyp)) {
+        uint32_t pm = 0;
+#pragma unroll
+        for (int q = 0; q < QL; q++) {
+          bool ok = dv[q] <= thr[q];
+          if (has_lower) ok = ok && (lower <= dv[q]);
+          if (has_upper) ok = ok && (dv[q] < upper);
+          pm |= ok ? (1u << q) : 0u;
+        }
+        if (r >= vend) pm = 0;
+        pm &= (1u << nq) - 1u;
+        if (bm && pm) {
+          if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
+        }
+        if (__any_sync(FULL, pm != 0)) {
+#pragma unroll
+          for (int q = 0; q < QL; q++) {
+            const uint32_t b = (uint32_t)q * NW + w;
+            append_rows((pm >> q) & 1u, dv[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
+                        cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
+                        (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
+          }
+        }
+      }
+    };
+
+    // superblocks are handed out dynamically (shared counter) so that a warp that drew short or
+    // cheap superblocks keeps working instead of waiting at the barrier
+    uint32_t sb = sb_lo + w;
 #pragma unroll 1
-    for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
+    while (sb < sb_hi) {
       const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
       uint4 cur = __ldg(up), n1 = __ldg(up + 32);
       const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
-      float acc[QL], done[QL];
+      float acc[QL], done[QL], prev[QL];
 #pragma unroll
-      for (int q = 0; q < QL; q++) acc[q] = done[q] = 0.0f;
+      for (int q = 0; q < QL; q++) acc[q] = done[q] = prev[q] = 0.0f;
       const uint32_t row0 = sb * 32 * L + lane;
       // pick up bounds found meanwhile by other work items of the same queries
       if (p.qthr) {
@@ -406,40 +457,11 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
         }
         cur = n1; n1 = n2;
-        if (i >= 1) {
-          // `done` = distance of row i-1 of this lane.  Fast test: running threshold only; bounds,
-          // tail rows and the prefilter are applied on the (rare) slow path.
-          float thr[QL];
-          lds_volatile<QL>(sthrf_saddr, thr);
-          bool anyp = done[0] <= thr[0];
+        // `done` = distance of row i-1 of this lane; it is tested one iteration LATER (as `prev`),
+        // when its last LDS has long landed, so the test never stalls the lookup stream
+        if (i >= 2) check_rows(prev, row0 + (i - 2) * 32);
 #pragma unroll
-          for (int q = 1; q < QL; q++) anyp = anyp || (done[q] <= thr[q]);
-          if (__any_sync(FULL, anyp)) {
-            const uint32_t r = row0 + (i - 1) * 32;
-            uint32_t pm = 0;
-#pragma unroll
-            for (int q = 0; q < QL; q++) {
-              bool ok = done[q] <= thr[q];
-              if (has_lower) ok = ok && (lower <= done[q]);
-              if (has_upper) ok = ok && (done[q] < upper);
-              pm |= ok ? (1u << q) : 0u;
-            }
-            if (r >= vend) pm = 0;
-            pm &= (1u << nq) - 1u;
-            if (bm && pm) {
-              if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
-            }
-            if (__any_sync(FULL, pm != 0)) {
-#pragma unroll
-              for (int q = 0; q < QL; q++) {
-                const uint32_t b = (uint32_t)q * NW + w;
-                append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
-                            cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
-                            (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
-              }
-            }
-          }
-        }
+        for (int q = 0; q < QL; q++) prev[q] = done[q];
         if (i == L) break;
 #pragma unroll 1
         for (uint32_t u = 1; u < C16; u++) {
@@ -449,6 +471,10 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           cur = n1; n1 = n3;
         }
       }
+      check_rows(prev, row0 + (L - 1) * 32);
+      uint32_t nx = 0;
+      if (lane == 0) nx = atomicAdd(ssb, 1u);
+      sb = sb_lo + __shfl_sync(FULL, nx, 0);
     }
     __syncthreads();
 

@@ -136,24 +136,25 @@ merge_lists_kernel(const float* __restrict__ in_dist, const uint64_t* __restrict
   const size_t base = (size_t)g * group_stride;
   if (threadIdx.x == 0) s_n = 0;
   __syncthreads();
-  // the low word of a sort key is the entry's offset from `base` (must fit 32 bits)
-  for (uint32_t i = threadIdx.x; i < npow2; i += blockDim.x) {
-    unsigned long long v = ~0ull;
-    if (i < L * stride) {
-      uint32_t l = i / stride, r = i - l * stride;
-      if (r < in_cnt[(size_t)g * cnt_gs + (size_t)l * cnt_ls]) {
-        size_t off = (size_t)l * list_stride + r;
-        v = ((unsigned long long)ordered_key(in_dist[base + off]) << 32) | (uint32_t)off;
-        atomicAdd(&s_n, 1u);
-      }
+  // the low word of a sort key is the entry's offset from `base` (must fit 32 bits).
+  // Only the valid entries are gathered (most per-partition lists are short once the running
+  // threshold has tightened), so the bitonic network runs on next_pow2(valid), not on L*stride.
+  for (uint32_t i = threadIdx.x; i < L * stride; i += blockDim.x) {
+    uint32_t l = i / stride, r = i - l * stride;
+    if (r < in_cnt[(size_t)g * cnt_gs + (size_t)l * cnt_ls]) {
+      size_t off = (size_t)l * list_stride + r;
+      sk[atomicAdd(&s_n, 1u)] = ((unsigned long long)ordered_key(in_dist[base + off]) << 32) | (uint32_t)off;
     }
-    sk[i] = v;
   }
   __syncthreads();
+  uint32_t n2 = 2;
+  while (n2 < s_n) n2 <<= 1;  // <= npow2
+  for (uint32_t i = s_n + threadIdx.x; i < n2; i += blockDim.x) sk[i] = ~0ull;
+  __syncthreads();
   const uint64_t* rid = in_rowid + base;
-  for (uint32_t k = 2; k <= npow2; k <<= 1) {
+  for (uint32_t k = 2; k <= n2; k <<= 1) {
     for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-      for (uint32_t i = threadIdx.x; i < npow2; i += blockDim.x) {
+      for (uint32_t i = threadIdx.x; i < n2; i += blockDim.x) {
         uint32_t ixj = i ^ j;
         if (ixj > i) {
           unsigned long long a = sk[i], b = sk[ixj];

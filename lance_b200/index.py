@@ -162,6 +162,19 @@ class IvfPqIndex:
             C.c_void_p(d_out_count), C.c_void_p(d_out_exact) if d_out_exact else None,
             C.c_void_p(stream) if stream else None))
 
+    def find_partitions_device(self, d_queries_ptr, Q, nprobes, d_out_part_ids, normalize=True, stream=None):
+        check(self._L.lb200_find_partitions_device(
+            self._h, C.c_void_p(d_queries_ptr), C.c_uint32(Q), C.c_uint32(nprobes), C.c_int32(1 if normalize else 0),
+            C.c_void_p(d_out_part_ids), C.c_void_p(stream) if stream else None))
+
+    def search_probed_device(self, d_queries_ptr, Q, d_part_ids, P, k, refine_factor, d_out_dist, d_out_rowid,
+                             d_out_count, d_out_exact=None, stream=None, lower=None, upper=None):
+        check(self._L.lb200_search_probed_device(
+            self._h, C.c_void_p(d_queries_ptr), C.c_uint32(Q), C.c_void_p(d_part_ids), C.c_uint32(P), C.c_uint32(k),
+            C.c_uint32(refine_factor), _fptr(lower), _fptr(upper), C.c_void_p(d_out_dist), C.c_void_p(d_out_rowid),
+            C.c_void_p(d_out_count), C.c_void_p(d_out_exact) if d_out_exact else None,
+            C.c_void_p(stream) if stream else None))
+
     def set_profiling(self, on=True):
         check(self._L.lb200_set_profiling(self._h, C.c_int32(1 if on else 0)))
 

@@ -56,33 +56,65 @@ def gather_candidates(dist, local_dist, local_rowid, local_count, local_exact=No
 
 
 class ShardedIvfPq:
-    """One rank's view of a partition-sharded index: `search` returns the global top-k on rank 0."""
+    """One rank's view of a partition-sharded index.  `prepare` fixes the batch shape (buffers are
+    allocated once), `search_device` runs one batch and leaves the global top-k on rank 0.
 
-    def __init__(self, index, dist, device):
+    Per batch: (1) coarse step sharded by QUERIES -- rank r selects the probes of its Q/G slice,
+    one all_gather makes the [Q][P] probe lists identical everywhere; (2) every rank scans the
+    probed partitions it owns; (3) all_gather of the local k' lists; (4) merge on rank 0."""
+
+    def __init__(self, index, dist, device, shard_coarse=True):
         import torch
         self.ix, self.dist, self.dev = index, dist, device
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.shard_coarse = shard_coarse and self.world > 1
         self._torch = torch
 
-    def search_device(self, d_queries, Q, nprobes, k, refine_factor, stream):
-        """d_queries: CUDA tensor [Q][dim].  Returns (dist [Q][k], rowid [Q][k], count [Q]) CUDA
-        tensors on rank 0, None elsewhere.  Everything is ordered on `stream`."""
+    def prepare(self, Q, nprobes, k, refine_factor):
+        torch, dev, G = self._torch, self.dev, self.world
+        self.Q, self.P, self.k, self.refine = Q, min(nprobes, self.ix.nlist), k, refine_factor
+        kp = self.kp = k * max(refine_factor, 1)
+        self.qs = (Q + G - 1) // G                      # queries per rank in the coarse step
+        self.l_probes = torch.zeros((self.qs, self.P), dtype=torch.int32, device=dev)
+        self.g_probes = torch.zeros((G * self.qs, self.P), dtype=torch.int32, device=dev)
+        self.od = torch.empty((Q, kp), dtype=torch.float32, device=dev)
+        self.oi = torch.empty((Q, kp), dtype=torch.int64, device=dev)
+        self.oc = torch.empty((Q,), dtype=torch.int32, device=dev)
+        self.ex = torch.empty((Q, kp), dtype=torch.float32, device=dev)
+        self.g_od = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
+        self.g_oi = torch.empty((G, Q, kp), dtype=torch.int64, device=dev)
+        self.g_oc = torch.empty((G, Q), dtype=torch.int32, device=dev)
+        self.g_ex = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
+        self.fd = torch.empty((Q, k), dtype=torch.float32, device=dev)
+        self.fi = torch.empty((Q, k), dtype=torch.int64, device=dev)
+        self.fc = torch.empty((Q,), dtype=torch.int32, device=dev)
+
+    def search_device(self, d_queries, stream):
+        """d_queries: CUDA f32 tensor [Q][dim].  Everything is ordered on `stream` (which must be
+        torch's current stream so that NCCL orders after our kernels).  Returns (fd, fi, fc) --
+        valid on rank 0 only."""
         from .index import merge_topk_device
-        torch = self._torch
-        kp = k * max(refine_factor, 1)
-        od = torch.empty((Q, kp), dtype=torch.float32, device=self.dev)
-        oi = torch.empty((Q, kp), dtype=torch.int64, device=self.dev)
-        oc = torch.empty((Q,), dtype=torch.int32, device=self.dev)
-        ex = torch.empty((Q, kp), dtype=torch.float32, device=self.dev)
-        self.ix.search_device(d_queries.data_ptr(), Q, nprobes, k, refine_factor, od.data_ptr(), oi.data_ptr(),
-                              oc.data_ptr(), d_out_exact=ex.data_ptr(), stream=stream.cuda_stream)
-        g_od, g_oi, g_oc, g_ex = gather_candidates(self.dist, od, oi, oc, ex if refine_factor else None)
-        if self.rank != 0:
-            return None
-        fd = torch.empty((Q, k), dtype=torch.float32, device=self.dev)
-        fi = torch.empty((Q, k), dtype=torch.int64, device=self.dev)
-        fc = torch.empty((Q,), dtype=torch.int32, device=self.dev)
-        merge_topk_device(self.dev.index, g_od.data_ptr(), g_oi.data_ptr(), g_ex.data_ptr() if refine_factor else None,
-                          g_oc.data_ptr(), self.world, Q, kp, kp, k, fd.data_ptr(), fi.data_ptr(), fc.data_ptr(),
-                          stream=stream.cuda_stream)
-        return fd, fi, fc
+        dist, ix, sp = self.dist, self.ix, stream.cuda_stream
+        Q, P, k, rf = self.Q, self.P, self.k, self.refine
+        if self.shard_coarse:
+            lo = min(self.rank * self.qs, Q)
+            n = min(self.qs, Q - lo)
+            if n > 0:
+                ix.find_partitions_device(d_queries[lo:].data_ptr(), n, P, self.l_probes.data_ptr(), normalize=True,
+                                          stream=sp)
+            dist.all_gather_into_tensor(self.g_probes, self.l_probes)
+            ix.search_probed_device(d_queries.data_ptr(), Q, self.g_probes.data_ptr(), P, k, rf, self.od.data_ptr(),
+                                    self.oi.data_ptr(), self.oc.data_ptr(), d_out_exact=self.ex.data_ptr(), stream=sp)
+        else:
+            ix.search_device(d_queries.data_ptr(), Q, P, k, rf, self.od.data_ptr(), self.oi.data_ptr(),
+                             self.oc.data_ptr(), d_out_exact=self.ex.data_ptr(), stream=sp)
+        dist.all_gather_into_tensor(self.g_od, self.od)
+        dist.all_gather_into_tensor(self.g_oi, self.oi)
+        dist.all_gather_into_tensor(self.g_oc, self.oc)
+        if rf:
+            dist.all_gather_into_tensor(self.g_ex, self.ex)
+        if self.rank == 0:
+            merge_topk_device(self.dev.index, self.g_od.data_ptr(), self.g_oi.data_ptr(),
+                              self.g_ex.data_ptr() if rf else None, self.g_oc.data_ptr(), self.world, Q, self.kp,
+                              self.kp, k, self.fd.data_ptr(), self.fi.data_ptr(), self.fc.data_ptr(), stream=sp)
+        return self.fd, self.fi, self.fc

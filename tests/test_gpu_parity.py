@@ -408,8 +408,9 @@ def test_full_size_properties(oracle):
 
 
 # ---- multi-GPU protocol on one device: G shard handles + lb200_merge_topk_device --------------
+@pytest.mark.parametrize("probed", [False, True])
 @pytest.mark.parametrize("metric,refine,G", [("l2", 0, 2), ("l2", 4, 3), ("cosine", 3, 2), ("dot", 0, 4)])
-def test_sharded_search_merge_equals_single_index(oracle, metric, refine, G):
+def test_sharded_search_merge_equals_single_index(oracle, metric, refine, G, probed):
     """every shard returns its k' candidates (+ exact distances), the gathered lists
     are merged on the device; the result must be bit-identical to the unsharded oracle search."""
     from lance_b200 import IvfPqIndex
@@ -429,12 +430,21 @@ def test_sharded_search_merge_equals_single_index(oracle, metric, refine, G):
     g_i = torch.empty((G, Q, kp), dtype=torch.int64, device=dev)
     g_c = torch.empty((G, Q), dtype=torch.int32, device=dev)
     g_e = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
-    shards = []
-    for g in range(G):
-        ix = IvfPqIndex(data.subset(np.nonzero(owner == g)[0]))
-        shards.append(ix)
-        ix.search_device(dq.data_ptr(), Q, nprobes, k, refine, g_d[g].data_ptr(), g_i[g].data_ptr(),
-                         g_c[g].data_ptr(), d_out_exact=g_e[g].data_ptr())
+    shards = [IvfPqIndex(data.subset(np.nonzero(owner == g)[0])) for g in range(G)]
+    probes = torch.zeros((Q, nprobes), dtype=torch.int32, device=dev)
+    if probed:
+        # coarse step sharded by queries: "rank" g selects the probes of its slice of the batch
+        qs = (Q + G - 1) // G
+        for g in range(G):
+            lo, n = g * qs, min(qs, Q - g * qs)
+            shards[g].find_partitions_device(dq[lo:].data_ptr(), n, nprobes, probes[lo:].data_ptr(), normalize=True)
+    for g, ix in enumerate(shards):
+        if probed:
+            ix.search_probed_device(dq.data_ptr(), Q, probes.data_ptr(), nprobes, k, refine, g_d[g].data_ptr(),
+                                    g_i[g].data_ptr(), g_c[g].data_ptr(), d_out_exact=g_e[g].data_ptr())
+        else:
+            ix.search_device(dq.data_ptr(), Q, nprobes, k, refine, g_d[g].data_ptr(), g_i[g].data_ptr(),
+                             g_c[g].data_ptr(), d_out_exact=g_e[g].data_ptr())
     torch.cuda.synchronize()
     fd = torch.empty((Q, k), dtype=torch.float32, device=dev)
     fi = torch.empty((Q, k), dtype=torch.int64, device=dev)
