@@ -200,6 +200,8 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("LB200_WORKLOAD", "cfg4"), choices=sorted(WORKLOADS))
     ap.add_argument("--scan-variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard-of", type=int, default=0,
+                    help="diagnostic: single process holding rank 0's shard of an N-way partition split")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     wl = WORKLOADS[args.workload]
@@ -224,7 +226,7 @@ def main():
     N, d, nlist, M, metric, nprobes, k, refine, Q, desc = wl
     kprime = k * max(refine, 1)
     t_build = time.perf_counter()
-    data, sizes, owner = make_shard(wl, seed, rank, world, keep_raw=refine > 0)
+    data, sizes, owner = make_shard(wl, seed, rank, args.shard_of or world, keep_raw=refine > 0)
     queries = make_queries(wl, data.centroids, seed)
     ix = IvfPqIndex(data, device_id=local)
     if args.scan_variant:

@@ -318,7 +318,8 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     sp.chunk_vecs = chunk_vecs; sp.max_chunks = max_chunks; sp.capw = sc.capw;
     // merged searches share one running k'-th-best bound per query across all its partitions;
     // search_in_partition semantics (one full list per pair) must not.
-    sp.qthr = a.per_pair_output ? nullptr : d_qthr;
+    sp.qthr = (a.per_pair_output || getenv("LB200_NO_QTHR")) ? nullptr : d_qthr;
+    sp.no_boot = getenv("LB200_NO_BOOT") != nullptr;
     sp.lower = a.lower; sp.upper = a.upper; sp.has_lower = a.has_lower; sp.has_upper = a.has_upper;
     sp.bitmask = a.d_bitmask;
     sp.out_dist = d_sdist; sp.out_pos = d_spos; sp.out_rowid = d_srow; sp.out_count = d_scnt;

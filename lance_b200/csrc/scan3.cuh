@@ -55,6 +55,7 @@ struct Scan3Params {
   uint32_t max_chunks;
   uint32_t capw;                  // candidate buffer entries per (warp, query slot)
   uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
+  int32_t no_boot;                // diagnostic: disable the pooled bootstrap
   // bounds / prefilter
   float lower, upper;
   int32_t has_lower, has_upper;
@@ -223,6 +224,29 @@ __host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, u
   return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32;
 }
 
+// Pull the NW per-warp candidate segments of one query (segment w at w*capw, cnt[w] entries) together
+// at the start of the region.  dst index <= src index always, so the forward copy is safe.
+// Returns the total.  One warp.
+__device__ __forceinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, const uint32_t* cnt, uint32_t nw,
+                                                    uint32_t capw, uint32_t lane) {
+  uint32_t n = cnt[0];
+#pragma unroll 1
+  for (uint32_t w2 = 1; w2 < nw; w2++) {
+    const uint32_t n2 = cnt[w2];
+    const uint32_t* sk = dk + (size_t)w2 * capw;
+    const uint32_t* sp = dp + (size_t)w2 * capw;
+    for (uint32_t i0 = 0; i0 < n2; i0 += 32) {
+      uint32_t i = i0 + lane, kk = 0, pp = 0;
+      if (i < n2) { kk = sk[i]; pp = sp[i]; }
+      __syncwarp();
+      if (i < n2) { dk[n + i] = kk; dp[n + i] = pp; }
+      __syncwarp();
+    }
+    n += n2;
+  }
+  return n;
+}
+
 template <int QL, int D, int NW, int MINB, int DSUB>
 __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params p,
                                                               const uint32_t* __restrict__ total_items_p) {
@@ -242,6 +266,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   uint32_t* sqidx = spair + QL;
   uint32_t* sitem = sqidx + QL;
   uint32_t* ssb = sitem + 1;  // next superblock (relative to the chunk's first) to hand out
+  uint32_t* scold = sitem + 2;  // 1: some query of this item has no bound yet -> pooled bootstrap
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -308,7 +333,16 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       sthrf[tid] = tid < nq ? key_to_float(t0) : __int_as_float(0xff800000);
     }
     if (tid < NW * QL) ccnt[tid] = 0;
-    if (tid == 0) *ssb = NW;
+    if (tid == 0) {
+      *ssb = NW;
+      uint32_t cold = 0;
+      for (uint32_t qq = 0; qq < nq; qq++) {
+        uint32_t t0 = KEY_PINF;
+        if (p.qthr) t0 = __ldcg(p.qthr + p.pair_list[pbase + qq] / p.P);
+        cold |= t0 == KEY_PINF ? 1u : 0u;
+      }
+      *scold = p.no_boot ? 0u : cold;
+    }
     for (uint32_t i = tid; i < QL * dim; i += NT) {
       uint32_t qq = i / dim, e = i - qq * dim;
       float val = 0.0f;
@@ -422,6 +456,36 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       }
     };
 
+    // Pooled bootstrap of a cold item (no bound known for one of its queries): once every warp has
+    // buffered its first ~64 rows, the NW x 64 candidates of each query are pooled and pruned ONCE;
+    // the k'-th best of ~512 rows is a far tighter start than each warp pruning its own 64 over and
+    // over (the r01 N=8 run spent ~40% of the scan there: every item of a shard is cold).
+    const bool cold = *scold != 0;
+    bool booted = !cold;
+    auto bootstrap = [&]() {
+      __syncthreads();
+#pragma unroll 1
+      for (uint32_t qq = w; qq < nq; qq += NW) {
+        uint32_t* dk = ckey + (size_t)qq * NW * capw;
+        uint32_t* dp = cpos + (size_t)qq * NW * capw;
+        uint32_t n = gather_segments(dk, dp, ccnt + qq * NW, NW, capw, lane);
+        if (n > kprime) {
+          uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
+          n = kprime;
+          if (lane == 0) {
+            uint32_t old = atomicMin(sthr + qq, T);
+            sthrf[qq] = key_to_float(min(old, T));
+            if (p.qthr) atomicMin(p.qthr + sqidx[qq], T);
+          }
+        }
+        __syncwarp();
+        if (lane < NW) ccnt[qq * NW + lane] = lane == 0 ? n : 0u;
+      }
+      __syncthreads();
+      booted = true;
+    };
+    const uint32_t boot_i = min(L, 3u);
+
     // superblocks are handed out dynamically (shared counter) so that a warp that drew short or
     // cheap superblocks keeps working instead of waiting at the barrier
     uint32_t sb = sb_lo + w;
@@ -462,6 +526,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         if (i >= 2) check_rows(prev, row0 + (i - 2) * 32);
 #pragma unroll
         for (int q = 0; q < QL; q++) prev[q] = done[q];
+        if (!booted && i == boot_i) bootstrap();
         if (i == L) break;
 #pragma unroll 1
         for (uint32_t u = 1; u < C16; u++) {
@@ -476,6 +541,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       if (lane == 0) nx = atomicAdd(ssb, 1u);
       sb = sb_lo + __shfl_sync(FULL, nx, 0);
     }
+    if (!booted) bootstrap();  // warps that drew no superblock still owe the two barriers
     __syncthreads();
 
     // ---- finalize: one warp per query: gather the warps' buffers, select k', sorted emit ----
@@ -483,21 +549,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     for (uint32_t qq = w; qq < nq; qq += NW) {
       uint32_t* dk = ckey + (size_t)qq * NW * capw;
       uint32_t* dp = cpos + (size_t)qq * NW * capw;
-      uint32_t n = ccnt[qq * NW];
-#pragma unroll 1
-      for (uint32_t w2 = 1; w2 < NW; w2++) {
-        const uint32_t n2 = ccnt[qq * NW + w2];
-        const uint32_t* sk = dk + (size_t)w2 * capw;
-        const uint32_t* sp = dp + (size_t)w2 * capw;
-        for (uint32_t i0 = 0; i0 < n2; i0 += 32) {
-          uint32_t i = i0 + lane, kk = 0, pp = 0;
-          if (i < n2) { kk = sk[i]; pp = sp[i]; }
-          __syncwarp();
-          if (i < n2) { dk[n + i] = kk; dp[n + i] = pp; }
-          __syncwarp();
-        }
-        n += n2;
-      }
+      uint32_t n = gather_segments(dk, dp, ccnt + qq * NW, NW, capw, lane);
       if (n > kprime) {
         uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
         n = kprime;
