@@ -243,7 +243,8 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   add((size_t)Q * dim * 4);         // normalised keys
   add((size_t)Q * nlist * 4);       // coarse distances
   add(npairs * 4);                  // probes
-  add((size_t)nlist * 4);           // cnt
+  add((size_t)nlist * 4 * 2);       // cnt (cold, other)
+  add((size_t)Q * 4);               // first partition per query
   add(npairs * 4);                  // rank
   add((size_t)(nlist + 1) * 4 * 2); // pair_off, item_off
   add(npairs * 4);                  // pair_list
@@ -258,7 +259,9 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   float* d_keys = ix->arena.take<float>((size_t)Q * dim);
   float* d_D = ix->arena.take<float>((size_t)Q * nlist);
   uint32_t* d_probes = ix->arena.take<uint32_t>(npairs);
-  uint32_t* d_cnt = ix->arena.take<uint32_t>(nlist);
+  uint32_t* d_cnt = ix->arena.take<uint32_t>((size_t)nlist * 2);
+  uint32_t* d_cnt2 = d_cnt + nlist;
+  uint32_t* d_minp = ix->arena.take<uint32_t>(Q);
   uint32_t* d_rank = ix->arena.take<uint32_t>(npairs);
   uint32_t* d_pair_off = ix->arena.take<uint32_t>(nlist + 1);
   uint32_t* d_item_off = ix->arena.take<uint32_t>(nlist + 1);
@@ -296,16 +299,21 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   }
   if (prof) CK(cudaEventRecord(ix->ev[1], st));
   // ---- work list ------------------------------------------------------------------------
-  CK(cudaMemsetAsync(d_cnt, 0, (size_t)nlist * 4, st));
+  CK(cudaMemsetAsync(d_cnt, 0, (size_t)nlist * 4 * 2, st));
   CK(cudaMemsetAsync(d_stats, 0, 32, st));
   CK(cudaMemsetAsync(d_scnt, 0, nslots * 4, st));
-  count_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, (uint32_t)npairs, d_cnt, d_rank);
-  offsets_kernel<<<1, 1024, 0, st>>>(d_cnt, ix->d_part_off, nlist, (uint32_t)sc.ql, chunk_vecs, ix->M, d_pair_off,
-                                     d_item_off, d_stats);
-  scatter_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, d_rank, d_pair_off, (uint32_t)npairs,
-                                                                        d_pair_list);
+  if (getenv("LB200_NO_COLDPACK"))
+    CK(cudaMemsetAsync(d_minp, 0xff, (size_t)Q * 4, st));
+  else
+    first_part_kernel<<<(Q + 255) / 256, 256, 0, st>>>(probes, Q, P, ix->d_part_off, d_minp);
+  count_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, (uint32_t)npairs, P, d_minp, d_cnt,
+                                                                      d_cnt2, d_rank);
+  offsets_kernel<<<1, 1024, 0, st>>>(d_cnt, d_cnt2, ix->d_part_off, nlist, (uint32_t)sc.ql, chunk_vecs, ix->M,
+                                     d_pair_off, d_item_off, d_stats);
+  scatter_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, d_rank, d_pair_off, d_cnt,
+                                                                        (uint32_t)npairs, d_pair_list);
   CK(cudaGetLastError());
-  launches += 3;
+  launches += 4;
   // ---- A3-A6 scan -----------------------------------------------------------------------
   if (sc.variant == 3) {
     Scan3Params sp = {};
@@ -320,6 +328,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     // search_in_partition semantics (one full list per pair) must not.
     sp.qthr = (a.per_pair_output || getenv("LB200_NO_QTHR")) ? nullptr : d_qthr;
     sp.no_boot = getenv("LB200_NO_BOOT") != nullptr;
+    sp.boot2 = getenv("LB200_NO_BOOT2") == nullptr;
     sp.lower = a.lower; sp.upper = a.upper; sp.has_lower = a.has_lower; sp.has_upper = a.has_upper;
     sp.bitmask = a.d_bitmask;
     sp.out_dist = d_sdist; sp.out_pos = d_spos; sp.out_rowid = d_srow; sp.out_count = d_scnt;

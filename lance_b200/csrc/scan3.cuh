@@ -56,6 +56,7 @@ struct Scan3Params {
   uint32_t capw;                  // candidate buffer entries per (warp, query slot)
   uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
   int32_t no_boot;                // diagnostic: disable the pooled bootstrap
+  int32_t boot2;                  // second pooled prune at the end of each warp's first superblock
   // bounds / prefilter
   float lower, upper;
   int32_t has_lower, has_upper;
@@ -461,7 +462,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     // the k'-th best of ~512 rows is a far tighter start than each warp pruning its own 64 over and
     // over (the r01 N=8 run spent ~40% of the scan there: every item of a shard is cold).
     const bool cold = *scold != 0;
-    bool booted = !cold;
+    // pooled prunes still owed: #1 after ~64 rows per warp, #2 at the end of the warp's first superblock
+    bool need1 = cold, need2 = cold && L > 3 && p.boot2 != 0;
     auto bootstrap = [&]() {
       __syncthreads();
 #pragma unroll 1
@@ -482,7 +484,6 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         if (lane < NW) ccnt[qq * NW + lane] = lane == 0 ? n : 0u;
       }
       __syncthreads();
-      booted = true;
     };
     const uint32_t boot_i = min(L, 3u);
 
@@ -526,7 +527,13 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         if (i >= 2) check_rows(prev, row0 + (i - 2) * 32);
 #pragma unroll
         for (int q = 0; q < QL; q++) prev[q] = done[q];
-        if (!booted && i == boot_i) bootstrap();
+        if (need1 && i == boot_i) {
+          bootstrap();
+          need1 = false;
+        } else if (need2 && i == L) {
+          bootstrap();
+          need2 = false;
+        }
         if (i == L) break;
 #pragma unroll 1
         for (uint32_t u = 1; u < C16; u++) {
@@ -541,7 +548,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       if (lane == 0) nx = atomicAdd(ssb, 1u);
       sb = sb_lo + __shfl_sync(FULL, nx, 0);
     }
-    if (!booted) bootstrap();  // warps that drew no superblock still owe the two barriers
+    if (need1) bootstrap();  // warps that drew no superblock still owe the barriers
+    if (need2) bootstrap();
     __syncthreads();
 
     // ---- finalize: one warp per query: gather the warps' buffers, select k', sorted emit ----

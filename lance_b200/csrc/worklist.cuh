@@ -26,18 +26,43 @@ __global__ void repack_codes_kernel(const uint8_t* __restrict__ src, const uint6
   }
 }
 
-// Step 1: histogram of probed partitions; rank[e] = arrival order of pair e in its partition.
-__global__ void count_pairs_kernel(const uint32_t* __restrict__ probes, uint32_t npairs,
-                                   uint32_t* __restrict__ cnt, uint32_t* __restrict__ rank) {
+// Step 0: the partition each query meets FIRST in scheduling order (work items run in ascending
+// partition id): the smallest probed, non-empty partition.  Its pair is the query's "cold" pair
+// (no running bound yet); step 1/3 pack the cold pairs of a partition into the same work items so
+// that few items pay the cold start (with G shards a query has only P/G pairs per shard: without
+// the packing 1-(1-G/P)^QL of all items would hold a cold query).
+__global__ void first_part_kernel(const uint32_t* __restrict__ probes, uint32_t Q, uint32_t P,
+                                  const uint64_t* __restrict__ part_off, uint32_t* __restrict__ minp) {
+  uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= Q) return;
+  uint32_t m = 0xffffffffu;
+  for (uint32_t r = 0; r < P; r++) {
+    uint32_t p = probes[(size_t)q * P + r];
+    if (part_off[p + 1] > part_off[p]) m = min(m, p);
+  }
+  minp[q] = m;
+}
+
+// Step 1: histogram of probed partitions (cold pairs and the others counted apart);
+// rank[e] = arrival order of pair e in its class, bit 31 = cold.
+__global__ void count_pairs_kernel(const uint32_t* __restrict__ probes, uint32_t npairs, uint32_t P,
+                                   const uint32_t* __restrict__ minp, uint32_t* __restrict__ cnt_cold,
+                                   uint32_t* __restrict__ cnt_other, uint32_t* __restrict__ rank) {
   uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < npairs) rank[e] = atomicAdd(&cnt[probes[e]], 1u);
+  if (e >= npairs) return;
+  const uint32_t p = probes[e];
+  if (p == minp[e / P])
+    rank[e] = atomicAdd(&cnt_cold[p], 1u) | 0x80000000u;
+  else
+    rank[e] = atomicAdd(&cnt_other[p], 1u);
 }
 
 // Step 2 (single block): exclusive scans over partitions -> pair offsets and item offsets.
 // items(p) = ceil(cnt[p]/QL) * ceil(n_p/chunk_vecs).  Also accumulates the algorithmic scan
 // bytes sum_pairs n_p * M and the pair count into stats[0..1].
 __global__ void __launch_bounds__(1024)
-offsets_kernel(const uint32_t* __restrict__ cnt, const uint64_t* __restrict__ part_off, uint32_t nlist,
+offsets_kernel(const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cnt2,
+               const uint64_t* __restrict__ part_off, uint32_t nlist,
                uint32_t QL, uint32_t chunk_vecs, uint32_t M, uint32_t* __restrict__ pair_off,
                uint32_t* __restrict__ item_off, unsigned long long* __restrict__ stats) {
   __shared__ uint32_t s_pairs[1024], s_items[1024];
@@ -54,7 +79,7 @@ offsets_kernel(const uint32_t* __restrict__ cnt, const uint64_t* __restrict__ pa
     uint32_t p = base + threadIdx.x;
     uint32_t c = 0, it = 0;
     if (p < nlist) {
-      c = cnt[p];
+      c = cnt[p] + cnt2[p];
       uint64_t n = part_off[p + 1] - part_off[p];
       uint32_t nch = (uint32_t)((n + chunk_vecs - 1) / chunk_vecs);
       it = ((c + QL - 1) / QL) * nch;
@@ -96,12 +121,15 @@ offsets_kernel(const uint32_t* __restrict__ cnt, const uint64_t* __restrict__ pa
   }
 }
 
-// Step 3: scatter pair ids into partition-grouped order.
+// Step 3: scatter pair ids into partition-grouped order, cold pairs first.
 __global__ void scatter_pairs_kernel(const uint32_t* __restrict__ probes, const uint32_t* __restrict__ rank,
-                                     const uint32_t* __restrict__ pair_off, uint32_t npairs,
-                                     uint32_t* __restrict__ pair_list) {
+                                     const uint32_t* __restrict__ pair_off, const uint32_t* __restrict__ cnt_cold,
+                                     uint32_t npairs, uint32_t* __restrict__ pair_list) {
   uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < npairs) pair_list[pair_off[probes[e]] + rank[e]] = e;
+  if (e >= npairs) return;
+  const uint32_t p = probes[e], r = rank[e];
+  const uint32_t pos = (r & 0x80000000u) ? (r & 0x7fffffffu) : cnt_cold[p] + r;
+  pair_list[pair_off[p] + pos] = e;
 }
 
 // ---------------------------------------------------------------------------------------
