@@ -177,6 +177,43 @@ __device__ __forceinline__ void scan_unit(const uint4 W, const unsigned char* lu
   }
 }
 
+// Cheap bound for pruning: the k-th smallest of the 32 lanes' values `m` (0xffffffff = none) is the
+// k-th smallest of a SUBSET of the candidates, hence >= the true k-th best: a valid threshold
+// (tightness ~ k-th of all when each lane passes the minimum of its share).  Needs k <= 32.
+// Returns 0xffffffff when fewer than k lanes hold a value.  ~100 instructions, no memory traffic.
+__device__ __forceinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_t lane) {
+  uint32_t r = 0;
+#pragma unroll
+  for (int j = 0; j < 32; j++) {
+    const uint32_t o = __shfl_sync(FULL, m, j);
+    r += (o < m || (o == m && (uint32_t)j < lane)) ? 1u : 0u;
+  }
+  const uint32_t sel = __ballot_sync(FULL, r == k - 1);
+  return __shfl_sync(FULL, m, __ffs(sel) - 1);  // exactly one lane has rank k-1
+}
+
+// Keep the entries with key <= T of a warp's buffer (stable, in place).  Returns the new count.
+__device__ __forceinline__ uint32_t warp_compact_le(uint32_t* kb, uint32_t* pb, uint32_t cnt, uint32_t T,
+                                                    uint32_t lane) {
+  uint32_t outn = 0;
+  for (uint32_t base = 0; base < cnt; base += 32) {
+    const uint32_t i = base + lane;
+    uint32_t kk = 0xffffffffu, pp = 0;
+    if (i < cnt) { kk = kb[i]; pp = pb[i]; }
+    const bool keep = i < cnt && kk <= T;
+    const uint32_t mk = __ballot_sync(FULL, keep);
+    __syncwarp();
+    if (keep) {
+      const uint32_t dst = outn + __popc(mk & ((1u << lane) - 1u));
+      kb[dst] = kk;
+      pb[dst] = pp;
+    }
+    outn += __popc(mk);
+    __syncwarp();
+  }
+  return outn;
+}
+
 // Append the warp's passing rows for query slot q to its (query, warp) buffer; prune first when
 // it would overflow.  Warp-uniform call.
 __device__ __forceinline__ void append_rows(bool pass, float dist, uint32_t pos, uint32_t lane, uint32_t capw,
@@ -188,8 +225,22 @@ __device__ __forceinline__ void append_rows(bool pass, float dist, uint32_t pos,
   uint32_t np = __popc(mask);
   uint32_t cnt = *cnt_p;
   if (cnt + np > capw) {  // capw >= k'+32, so cnt > k' here
-    uint32_t T = warp_select_k(kb, pb, cnt, kprime, prow);
-    cnt = kprime;
+    uint32_t T = 0xffffffffu;
+    if (kprime <= 32) {
+      // cheap prune: bound from the lanes' minima, keep everything under it
+      uint32_t m = 0xffffffffu;
+      for (uint32_t i = lane; i < cnt; i += 32) m = min(m, kb[i]);
+      T = warp_bound_k(m, kprime, lane);
+      if (T != 0xffffffffu) {
+        const uint32_t c2 = warp_compact_le(kb, pb, cnt, T, lane);
+        if (c2 + np > capw) T = 0xffffffffu;  // mass of ties: exact select below
+        else cnt = c2;
+      }
+    }
+    if (T == 0xffffffffu) {
+      T = warp_select_k(kb, pb, cnt, kprime, prow);
+      cnt = kprime;
+    }
     if (lane == 0) {
       uint32_t old = atomicMin(sthr_q, T);
       *sthrf_q = key_to_float(min(old, T));
@@ -466,6 +517,37 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     bool need1 = cold, need2 = cold && L > 3 && p.boot2 != 0;
     auto bootstrap = [&]() {
       __syncthreads();
+      if (kprime <= 32) {
+        // bound = k'-th smallest of the lanes' minima over the pooled NW segments of the query
+#pragma unroll 1
+        for (uint32_t qq = w; qq < nq; qq += NW) {
+          uint32_t m = 0xffffffffu;
+          for (uint32_t w2 = 0; w2 < NW; w2++) {
+            const uint32_t n2 = ccnt[qq * NW + w2];
+            const uint32_t* sk = ckey + (size_t)(qq * NW + w2) * capw;
+            for (uint32_t i = lane; i < n2; i += 32) m = min(m, sk[i]);
+          }
+          const uint32_t T = warp_bound_k(m, kprime, lane);
+          if (T != 0xffffffffu && lane == 0) {
+            uint32_t old = atomicMin(sthr + qq, T);
+            sthrf[qq] = key_to_float(min(old, T));
+            if (p.qthr) atomicMin(p.qthr + sqidx[qq], T);
+          }
+        }
+        __syncthreads();
+        // every warp drops what the new bounds exclude from its own buffers
+#pragma unroll 1
+        for (uint32_t qq = 0; qq < nq; qq++) {
+          const uint32_t b = qq * NW + w;
+          const uint32_t n0 = ccnt[b];
+          if (n0) {
+            const uint32_t n1 = warp_compact_le(ckey + (size_t)b * capw, cpos + (size_t)b * capw, n0, sthr[qq], lane);
+            if (lane == 0) ccnt[b] = n1;
+          }
+        }
+        __syncwarp();
+        return;
+      }
 #pragma unroll 1
       for (uint32_t qq = w; qq < nq; qq += NW) {
         uint32_t* dk = ckey + (size_t)qq * NW * capw;
