@@ -191,19 +191,99 @@ def run_reference(args, wl):
     print(json.dumps(line), flush=True)
 
 
+def run_flat(args):
+    """--workload cfg2: flat brute-force L2 kNN 1M x 128, k=10 (KNNVectorDistanceExec path, no index;
+    BASELINE configs[1]).  A step = one batch of 256 queries against the device-resident vectors."""
+    import ctypes as C
+    import torch
+    from lance_b200 import _lib, flat_knn
+    from lance_b200._lib import check
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    dev = torch.device("cuda", 0)
+    N, d, k, Q = 1_000_000, 128, 10, 256
+    rng = np.random.default_rng(1234)
+    vecs = np.clip(np.rint(rng.normal(64, 32, size=(N, d))), 0, 218).astype(np.float32)  # SIFT-like integers
+    queries = np.clip(np.rint(rng.normal(64, 32, size=(Q, d))), 0, 218).astype(np.float32)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    d_v, d_q = torch.from_numpy(vecs).to(dev), torch.from_numpy(queries).to(dev)
+    od = torch.empty((Q, k), dtype=torch.float32, device=dev)
+    oi = torch.empty((Q, k), dtype=torch.int64, device=dev)
+    oc = torch.empty((Q,), dtype=torch.int32, device=dev)
+    L = _lib.lib()
+
+    def step():
+        check(L.lb200_flat_topk_device(C.c_int32(0), C.c_int32(0), C.c_uint32(d), C.c_void_p(d_q.data_ptr()),
+                                       C.c_uint32(Q), C.c_void_p(d_v.data_ptr()), None, C.c_uint64(N), C.c_uint32(k),
+                                       C.c_void_p(od.data_ptr()), C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()),
+                                       C.c_void_p(stream.cuda_stream)))
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    t0 = time.perf_counter()
+    e2e_steps = 3
+    for _ in range(e2e_steps):
+        flat_knn(queries, "l2", vecs, k)   # host-pointer ABI: uploads the 512 MB of vectors every call, as
+    ms_e2e = (time.perf_counter() - t0) * 1e3  # compute_distance gets a fresh RecordBatch every call
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+    qps = Q * args.steps / (ms * 1e-3)
+    tile_bytes = N * d * 4 * ((Q + 31) // 32)  # the vectors are streamed once per 32-query tile
+    line = {"metric": "flat kNN queries/sec (batched)", "value": qps, "unit": "queries/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "flat brute-force L2 kNN 1Mx128 f32, k=10, 256 queries per step (BASELINE configs[1])",
+                       "l2_policy": "inputs larger than L2 (512 MB of vectors)"},
+            "roofline": {"bound": "hbm", "achieved": tile_bytes / (ms / args.steps * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": tile_bytes / (ms / args.steps * 1e-3) / 1e9 / peak, "traffic": None,
+                         "kernel": "flat_dist_kernel + flat_select_kernel (whole step)",
+                         "note": "bytes = N*d*4 per 32-query tile of the distance kernel; the path is fp32-issue bound (Q*N*d*3 flop), not HBM bound"},
+            "e2e": {"value": Q * e2e_steps / (ms_e2e * 1e-3), "unit": "queries/s",
+                    "h2d_bytes_per_step": int(vecs.nbytes + queries.nbytes), "d2h_bytes_per_step": Q * k * 12 + Q * 4,
+                    "path": "lb200_flat_topk (host-pointer C ABI; uploads the vector batch every call)"},
+            "gpu_launches": 2 * args.steps, "clocks": clocks}
+    if not args.no_cpu_baseline:
+        import oracle
+        cores = oracle.max_threads()
+        nq = 32
+        t0 = time.perf_counter()
+        oracle.flat_knn("l2", queries[:nq], vecs, k, threads=cores)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": nq / dt, "unit": "queries/s", "cores": cores, "kind": "port",
+                                "sample": f"first {nq} queries, {dt:.1f} s, oracle port on {cores} threads"}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("LB200_WORKLOAD", "cfg4"), choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("LB200_WORKLOAD", "cfg4"), choices=sorted(WORKLOADS) + ["cfg2"])
     ap.add_argument("--scan-variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard-of", type=int, default=0,
                     help="diagnostic: single process holding rank 0's shard of an N-way partition split")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.workload == "cfg2":
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": "cfg2 reference arm: use --workload cfg4 (headline)"}))
+            return
+        run_flat(args)
+        return
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, wl)

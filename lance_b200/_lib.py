@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "liblance_b200.so")
+SO_PATH = os.environ.get("LB200_SO") or os.path.join(_HERE, "liblance_b200.so")  # LB200_SO: A/B of builds
 
 EXPORTS = [
     "lb200_index_create", "lb200_index_destroy", "lb200_find_partitions", "lb200_search_partitions",
@@ -46,6 +46,8 @@ def lib():
         _lib.lb200_version.restype = C.c_char_p
         _lib.lb200_index_destroy.restype = None
         for name in EXPORTS:
+            if os.environ.get("LB200_SO") and not hasattr(_lib, name):
+                continue  # an older build under A/B test may predate a symbol
             getattr(_lib, name)  # raises AttributeError if a declared symbol is missing
     return _lib
 

@@ -13,6 +13,19 @@ static int flat_check(int32_t metric, uint32_t dim, const void* q, uint32_t Q, c
 static int flat_dist_launch(int metric, const float* d_q, uint32_t Q, const float* d_v, const uint8_t* d_valid,
                             uint64_t n, uint32_t dim, float* d_out, size_t out_stride, cudaStream_t st) {
   if (!Q || !n) return 0;
+  // L2, d % 16 == 0: the tiled kernel of the coarse step (same l2_scalar<16> order) reads the rows once
+  // per 32 queries instead of once per 4
+  const size_t tsm = ((size_t)dim * CQ_PITCH + (size_t)CQ_QB * dim) * 4;
+  int dev = 0, optin = 0;
+  CK(cudaGetDevice(&dev));
+  CK(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  if (metric == LB200_L2 && dim % 16 == 0 && dim >= 32 && tsm <= (size_t)optin && Q >= 8 && !getenv("LB200_COARSE_SIMPLE")) {
+    CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
+    dim3 g2((uint32_t)((n + 127) / 128), (Q + CQ_QB - 1) / CQ_QB);
+    coarse_dist_l2_tiled_kernel<<<g2, 128, tsm, st>>>(d_q, d_v, Q, (uint32_t)n, dim, d_out, out_stride, d_valid);
+    CK(cudaGetLastError());
+    return 0;
+  }
   dim3 grid((uint32_t)((n + FLAT_THREADS - 1) / FLAT_THREADS), (Q + FLAT_TQ - 1) / FLAT_TQ);
   if (grid.y > 65535) return set_err(LB200_EINVAL, "query tile too large");
   size_t smem = (size_t)FLAT_TQ * dim * 4 + FLAT_TQ * 4;
@@ -30,7 +43,7 @@ static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uin
   if (k == 0) return set_err(LB200_EINVAL, "k must be > 0");
   if (k > 1024) return set_err(LB200_EUNSUPPORTED, "k=%u > 1024", k);
   if (!Q) return 0;
-  uint32_t tile = (uint32_t)std::max<uint64_t>(FLAT_TQ, std::min<uint64_t>(Q, (64ull << 20) / std::max<uint64_t>(1, n * 4)));
+  uint32_t tile = (uint32_t)std::max<uint64_t>(FLAT_TQ, std::min<uint64_t>(Q, (128ull << 20) / std::max<uint64_t>(1, n * 4)));
   tile = (tile + FLAT_TQ - 1) / FLAT_TQ * FLAT_TQ;
   float* d_D = nullptr;
   size_t stride = (size_t)std::max<uint64_t>(n, 1);
@@ -38,13 +51,40 @@ static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uin
   struct F { float* p; ~F() { cudaFree(p); } } guard{d_D};
   uint32_t kp2 = std::max(2u, next_pow2(k));
   size_t smem = (size_t)kp2 * 8;
+  // segments per row: ~32k rows each, bounded by what the merge kernel sorts per query
+  uint32_t nseg = (uint32_t)std::min<uint64_t>({(n + 32767) / 32768, 128ull, 16384ull / k});
+  nseg = std::max(nseg, 1u);
+  const uint64_t seg_len = (n + nseg - 1) / nseg;
+  nseg = (uint32_t)((n + seg_len - 1) / std::max<uint64_t>(seg_len, 1));
+  nseg = std::max(nseg, 1u);
+  float* t_d = nullptr;
+  uint64_t* t_i = nullptr;
+  uint32_t* t_c = nullptr;
+  struct G { void* p; ~G() { if (p) cudaFree(p); } } g2{nullptr};
+  if (nseg > 1) {
+    size_t cells = (size_t)tile * nseg * k;
+    CK(cudaMalloc(&g2.p, Arena::pad(cells * 4) + Arena::pad(cells * 8) + Arena::pad((size_t)tile * nseg * 4)));
+    t_d = (float*)g2.p;
+    t_i = (uint64_t*)((char*)g2.p + Arena::pad(cells * 4));
+    t_c = (uint32_t*)((char*)t_i + Arena::pad(cells * 8));
+  }
   for (uint32_t q0 = 0; q0 < Q; q0 += tile) {
     uint32_t qn = std::min(tile, Q - q0);
     int rc = flat_dist_launch(metric, d_q + (size_t)q0 * dim, qn, d_v, d_valid, n, dim, d_D, stride, st);
     if (rc) return rc;
-    flat_select_kernel<<<qn, 256, smem, st>>>(d_D, stride, n, k, kp2, has_lower, lower, has_upper, upper,
-                                              d_od + (size_t)q0 * k, d_oi + (size_t)q0 * k, d_oc + q0);
-    CK(cudaGetLastError());
+    if (nseg == 1) {
+      flat_select_kernel<<<qn, 256, smem, st>>>(d_D, stride, n, 1, std::max<uint64_t>(n, 1), k, kp2, has_lower, lower,
+                                                has_upper, upper, d_od + (size_t)q0 * k, d_oi + (size_t)q0 * k,
+                                                d_oc + q0);
+      CK(cudaGetLastError());
+    } else {
+      flat_select_kernel<<<qn * nseg, 256, smem, st>>>(d_D, stride, n, nseg, seg_len, k, kp2, has_lower, lower,
+                                                       has_upper, upper, t_d, t_i, t_c);
+      CK(cudaGetLastError());
+      rc = launch_merge(t_d, t_i, nullptr, nullptr, t_c, qn, nseg, k, (size_t)nseg * k, k, nseg, 1, k, k,
+                        d_od + (size_t)q0 * k, d_oi + (size_t)q0 * k, nullptr, nullptr, d_oc + q0, st);
+      if (rc) return rc;
+    }
   }
   CK(cudaStreamSynchronize(st));  // d_D is freed on return
   return 0;

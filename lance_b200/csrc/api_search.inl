@@ -99,12 +99,12 @@ static cudaError_t launch_scan(const ScanConfig& c, int grid, cudaStream_t st, c
   }
 }
 
-template <int QL, int D, int MINB>
+template <int QL, int D, int MINB, bool BOOT>
 static cudaError_t launch_scan3_d(int dsub_t, int sm_count, size_t smem, cudaStream_t st, const Scan3Params& sp,
                                   const uint32_t* total_items) {
 #define LB200_LAUNCH3(DS)                                                                         \
   do {                                                                                            \
-    auto kern = scan3_kernel<QL, D, SCAN_NW, MINB, DS>;                                           \
+    auto kern = BOOT ? scan3_kernel<QL, D, SCAN_NW, MINB, DS, true> : scan3_nb_kernel<QL, D, SCAN_NW, MINB, DS>;                                        \
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                               \
     int nb = 0;                                                                                   \
@@ -120,14 +120,20 @@ static cudaError_t launch_scan3_d(int dsub_t, int sm_count, size_t smem, cudaStr
 #undef LB200_LAUNCH3
 }
 
-static cudaError_t launch_scan3(const ScanConfig& c, int sm_count, cudaStream_t st, const Scan3Params& sp,
-                                const uint32_t* total_items) {
+template <bool BOOT>
+static cudaError_t launch_scan3_b(const ScanConfig& c, int sm_count, cudaStream_t st, const Scan3Params& sp,
+                                  const uint32_t* total_items) {
   if (c.ql == 4) {
-    if (c.minb == 2) return launch_scan3_d<4, 8, 2>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-    return launch_scan3_d<4, 8, 1>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+    if (c.minb == 2) return launch_scan3_d<4, 8, 2, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+    return launch_scan3_d<4, 8, 1, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
   }
-  if (c.minb == 2) return launch_scan3_d<2, 16, 2>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-  return launch_scan3_d<2, 16, 1>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+  if (c.minb == 2) return launch_scan3_d<2, 16, 2, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+  return launch_scan3_d<2, 16, 1, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+}
+static cudaError_t launch_scan3(const ScanConfig& c, bool boot, int sm_count, cudaStream_t st, const Scan3Params& sp,
+                                const uint32_t* total_items) {
+  return boot ? launch_scan3_b<true>(c, sm_count, st, sp, total_items)
+              : launch_scan3_b<false>(c, sm_count, st, sp, total_items);
 }
 
 struct SearchArgs {
@@ -161,7 +167,8 @@ static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint3
       !getenv("LB200_COARSE_SIMPLE")) {
     CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
     dim3 g2((ix->nlist + 127) / 128, (Q + CQ_QB - 1) / CQ_QB);
-    coarse_dist_l2_tiled_kernel<<<g2, 128, tsm, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
+    coarse_dist_l2_tiled_kernel<<<g2, 128, tsm, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D, ix->nlist,
+                                                      nullptr);
   } else if (ix->metric == LB200_DOT)
     coarse_dist_kernel<false><<<grid, COARSE_THREADS, smem, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
   else
@@ -338,7 +345,11 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
       launches++;
     }
     if (prof) CK(cudaEventRecord(ix->ev[2], st));
-    CK(launch_scan3(sc, ix->sm_count, st, sp, d_item_off + nlist));
+    // pooled bootstrap when most work items are cold: a shard (few of a query's probes are local), few
+    // probes per query, or per-pair outputs (no cross-item bound at all)
+    bool boot = a.shard_mode || a.per_pair_output || P < 16;
+    if (const char* eb = getenv("LB200_BOOT")) boot = atoi(eb) != 0;
+    CK(launch_scan3(sc, boot, ix->sm_count, st, sp, d_item_off + nlist));
     launches++;
   } else {
   ScanParams sp = {};

@@ -232,7 +232,8 @@ constexpr int CQ_QB = 32;
 constexpr int CQ_PITCH = 129;
 __global__ void __launch_bounds__(128)
 coarse_dist_l2_tiled_kernel(const float* __restrict__ queries, const float* __restrict__ centroids,
-                            uint32_t Q, uint32_t nlist, uint32_t d, float* __restrict__ out) {
+                            uint32_t Q, uint32_t nlist, uint32_t d, float* __restrict__ out, size_t out_stride,
+                            const uint8_t* __restrict__ validity /*Arrow bitmap or null (flat path)*/) {
   extern __shared__ float sm[];
   float* tile = sm;                         // [d][129]
   float* sq = sm + (size_t)d * CQ_PITCH;    // [CQ_QB][d]
@@ -286,7 +287,10 @@ coarse_dist_l2_tiled_kernel(const float* __restrict__ queries, const float* __re
 #pragma unroll
       for (int i = 0; i < 16; i++) tt = __fadd_rn(tt, sums[k][i]);
       const uint32_t qq = q0 + g * 4 + k;
-      if (qq < Q && c < nlist) out[(size_t)qq * nlist + c] = __fadd_rn(0.0f, tt);
+      if (qq < Q && c < nlist) {
+        const bool valid = !validity || ((validity[c >> 3] >> (c & 7)) & 1);
+        out[(size_t)qq * out_stride + c] = valid ? __fadd_rn(0.0f, tt) : __int_as_float(0x7fc00000);
+      }
     }
   }
 }

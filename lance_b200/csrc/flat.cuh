@@ -44,14 +44,19 @@ flat_dist_kernel(int metric, const float* __restrict__ queries, uint32_t Q, cons
 // the 32-bit ordered key, then an unordered gather of keys < T plus an index-ordered gather of
 // the ties, then a small bitonic sort.  One block (256 threads) per query.  k <= 1024.
 __global__ void __launch_bounds__(256)
-flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t n, uint32_t k, uint32_t kpow2,
+flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t n_total, uint32_t nseg,
+                   uint64_t seg_len, uint32_t k, uint32_t kpow2,
                    int has_lower, float lower, int has_upper, float upper, float* __restrict__ out_dist,
                    uint64_t* __restrict__ out_idx, uint32_t* __restrict__ out_cnt) {
   extern __shared__ unsigned long long sl[];  // [kpow2] result list
   __shared__ uint32_t hist[4096];
   __shared__ uint32_t s_prefix, s_mask, s_kk, s_less, s_fill, s_tiebase, s_wsum[8];
-  const uint32_t q = blockIdx.x;
-  const float* drow = dist + (size_t)q * dist_stride;
+  // block = (query, segment of the row): a row is cut into nseg segments so that a small query tile
+  // still fills the GPU; the per-segment lists are merged afterwards (merge_lists_kernel)
+  const uint32_t q = blockIdx.x;                       // output slot [query][segment]
+  const uint64_t off = (uint64_t)(blockIdx.x % nseg) * seg_len;
+  const uint64_t n = min(seg_len, n_total - off);
+  const float* drow = dist + (size_t)(blockIdx.x / nseg) * dist_stride + off;
   auto admissible = [&](float v) {
     bool ok = v == v;
     if (has_lower) ok = ok && v >= lower;
@@ -113,7 +118,7 @@ flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t 
       float v = drow[i];
       if (!admissible(v)) continue;
       uint32_t o = atomicAdd(&s_fill, 1u);
-      sl[o] = ((unsigned long long)ordered_key(v) << 32) | (uint32_t)i;
+      sl[o] = ((unsigned long long)ordered_key(v) << 32) | (uint32_t)(i + off);
     }
   } else {
     // keys < T: unordered; keys == T: first need_ties in index order (block-ordered compaction)
@@ -127,7 +132,7 @@ flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t 
           uint32_t key = ordered_key(v);
           if (key < T) {
             uint32_t o = atomicAdd(&s_fill, 1u);
-            sl[o] = ((unsigned long long)key << 32) | (uint32_t)i;
+            sl[o] = ((unsigned long long)key << 32) | (uint32_t)(i + off);
           }
           tie = key == T;
         }
@@ -138,7 +143,7 @@ flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t 
       uint32_t before = s_tiebase;
       for (uint32_t ww = 0; ww < w; ww++) before += s_wsum[ww];
       uint32_t r = before + __popc(bal & ((1u << lane) - 1u));
-      if (tie && r < need_ties) sl[nless + r] = ((unsigned long long)T << 32) | (uint32_t)i;
+      if (tie && r < need_ties) sl[nless + r] = ((unsigned long long)T << 32) | (uint32_t)(i + off);
       __syncthreads();
       if (threadIdx.x == 0) {
         uint32_t tot = 0;
@@ -154,7 +159,7 @@ flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t 
           uint32_t key = ordered_key(v);
           if (key < T) {
             uint32_t o = atomicAdd(&s_fill, 1u);
-            sl[o] = ((unsigned long long)key << 32) | (uint32_t)j;
+            sl[o] = ((unsigned long long)key << 32) | (uint32_t)(j + off);
           }
         }
         break;

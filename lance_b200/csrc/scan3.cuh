@@ -181,7 +181,7 @@ __device__ __forceinline__ void scan_unit(const uint4 W, const unsigned char* lu
 // k-th smallest of a SUBSET of the candidates, hence >= the true k-th best: a valid threshold
 // (tightness ~ k-th of all when each lane passes the minimum of its share).  Needs k <= 32.
 // Returns 0xffffffff when fewer than k lanes hold a value.  ~100 instructions, no memory traffic.
-__device__ __forceinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_t lane) {
+__device__ __noinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_t lane) {
   uint32_t r = 0;
 #pragma unroll
   for (int j = 0; j < 32; j++) {
@@ -193,7 +193,7 @@ __device__ __forceinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_
 }
 
 // Keep the entries with key <= T of a warp's buffer (stable, in place).  Returns the new count.
-__device__ __forceinline__ uint32_t warp_compact_le(uint32_t* kb, uint32_t* pb, uint32_t cnt, uint32_t T,
+__device__ __noinline__ uint32_t warp_compact_le(uint32_t* kb, uint32_t* pb, uint32_t cnt, uint32_t T,
                                                     uint32_t lane) {
   uint32_t outn = 0;
   for (uint32_t base = 0; base < cnt; base += 32) {
@@ -225,22 +225,8 @@ __device__ __forceinline__ void append_rows(bool pass, float dist, uint32_t pos,
   uint32_t np = __popc(mask);
   uint32_t cnt = *cnt_p;
   if (cnt + np > capw) {  // capw >= k'+32, so cnt > k' here
-    uint32_t T = 0xffffffffu;
-    if (kprime <= 32) {
-      // cheap prune: bound from the lanes' minima, keep everything under it
-      uint32_t m = 0xffffffffu;
-      for (uint32_t i = lane; i < cnt; i += 32) m = min(m, kb[i]);
-      T = warp_bound_k(m, kprime, lane);
-      if (T != 0xffffffffu) {
-        const uint32_t c2 = warp_compact_le(kb, pb, cnt, T, lane);
-        if (c2 + np > capw) T = 0xffffffffu;  // mass of ties: exact select below
-        else cnt = c2;
-      }
-    }
-    if (T == 0xffffffffu) {
-      T = warp_select_k(kb, pb, cnt, kprime, prow);
-      cnt = kprime;
-    }
+    uint32_t T = warp_select_k(kb, pb, cnt, kprime, prow);
+    cnt = kprime;
     if (lane == 0) {
       uint32_t old = atomicMin(sthr_q, T);
       *sthrf_q = key_to_float(min(old, T));
@@ -270,16 +256,33 @@ __device__ __forceinline__ void lds_volatile(uint32_t saddr, float (&v)[QL]) {
     asm volatile("ld.volatile.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v[0]), "=f"(v[1]) : "r"(saddr));
 }
 
+// Per-item state the COLD paths need, kept in shared memory so that those paths can live in
+// out-of-line functions: the hot loop must stay small (r01: with the cold code inlined the kernel
+// grew from 4.9k to 21k instructions and the scan lost 10% to instruction-cache misses and spills).
+struct ItemCtx {
+  uint32_t *ckey, *cpos, *ccnt, *sthr, *sqidx, *spair, *qthr;
+  float* sthrf;
+  const uint64_t* prow;
+  const uint64_t* bm;
+  float *out_dist;
+  uint64_t *out_pos, *out_rowid;
+  uint32_t* out_count;
+  uint64_t row_base;
+  uint32_t capw, kprime, nq, vend, nw, max_chunks, chunk;
+  float lower, upper;
+  int32_t has_lower, has_upper;
+};
+
 // Shared-memory footprint of scan3_kernel (host + device agree through this one function).
 __host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, uint32_t dim, uint32_t capw) {
   size_t lut = (size_t)(M / 16) * 256 * 64 * QL;
-  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32;
+  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32 + sizeof(ItemCtx) + 16;
 }
 
 // Pull the NW per-warp candidate segments of one query (segment w at w*capw, cnt[w] entries) together
 // at the start of the region.  dst index <= src index always, so the forward copy is safe.
 // Returns the total.  One warp.
-__device__ __forceinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, const uint32_t* cnt, uint32_t nw,
+__device__ __noinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, const uint32_t* cnt, uint32_t nw,
                                                     uint32_t capw, uint32_t lane) {
   uint32_t n = cnt[0];
 #pragma unroll 1
@@ -299,7 +302,87 @@ __device__ __forceinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, 
   return n;
 }
 
-template <int QL, int D, int NW, int MINB, int DSUB>
+// Pooled prune of a cold item (see the kernel).  Called by ALL threads of the CTA.
+__device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
+  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime, nq = c->nq;
+  __syncthreads();
+  if (kprime <= 32) {
+    // bound = k'-th smallest of the lanes' minima over the pooled NW segments of the query
+    for (uint32_t qq = w; qq < nq; qq += NW) {
+      uint32_t m = 0xffffffffu;
+      for (uint32_t w2 = 0; w2 < NW; w2++) {
+        const uint32_t n2 = c->ccnt[qq * NW + w2];
+        const uint32_t* sk = c->ckey + (size_t)(qq * NW + w2) * capw;
+        for (uint32_t i = lane; i < n2; i += 32) m = min(m, sk[i]);
+      }
+      const uint32_t T = warp_bound_k(m, kprime, lane);
+      if (T != 0xffffffffu && lane == 0) {
+        uint32_t old = atomicMin(c->sthr + qq, T);
+        c->sthrf[qq] = key_to_float(min(old, T));
+        if (c->qthr) atomicMin(c->qthr + c->sqidx[qq], T);
+      }
+    }
+    __syncthreads();
+    // every warp drops what the new bounds exclude from its own buffers
+    for (uint32_t qq = 0; qq < nq; qq++) {
+      const uint32_t b = qq * NW + w;
+      const uint32_t n0 = c->ccnt[b];
+      if (n0) {
+        const uint32_t n1 = warp_compact_le(c->ckey + (size_t)b * capw, c->cpos + (size_t)b * capw, n0, c->sthr[qq], lane);
+        if (lane == 0) c->ccnt[b] = n1;
+      }
+    }
+    __syncwarp();
+    return;
+  }
+  for (uint32_t qq = w; qq < nq; qq += NW) {
+    uint32_t* dk = c->ckey + (size_t)qq * NW * capw;
+    uint32_t* dp = c->cpos + (size_t)qq * NW * capw;
+    uint32_t n = gather_segments(dk, dp, c->ccnt + qq * NW, NW, capw, lane);
+    if (n > kprime) {
+      uint32_t T = warp_select_k(dk, dp, n, kprime, c->prow);
+      n = kprime;
+      if (lane == 0) {
+        uint32_t old = atomicMin(c->sthr + qq, T);
+        c->sthrf[qq] = key_to_float(min(old, T));
+        if (c->qthr) atomicMin(c->qthr + c->sqidx[qq], T);
+      }
+    }
+    __syncwarp();
+    if (lane < NW) c->ccnt[qq * NW + lane] = lane == 0 ? n : 0u;
+  }
+  __syncthreads();
+}
+
+// End of an item: one warp per query gathers the warps' buffers, selects k', emits sorted.
+__device__ __noinline__ void finalize_fn(const ItemCtx* c) {
+  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime;
+  for (uint32_t qq = w; qq < c->nq; qq += NW) {
+    uint32_t* dk = c->ckey + (size_t)qq * NW * capw;
+    uint32_t* dp = c->cpos + (size_t)qq * NW * capw;
+    uint32_t n = gather_segments(dk, dp, c->ccnt + qq * NW, NW, capw, lane);
+    if (n > kprime) {
+      uint32_t T = warp_select_k(dk, dp, n, kprime, c->prow);
+      n = kprime;
+      if (c->qthr && lane == 0) atomicMin(c->qthr + c->sqidx[qq], T);
+    } else if (n == kprime && c->qthr) {
+      uint32_t mx = 0;
+      for (uint32_t i = lane; i < n; i += 32) mx = max(mx, dk[i]);
+      mx = __reduce_max_sync(FULL, mx);
+      if (lane == 0) atomicMin(c->qthr + c->sqidx[qq], mx);
+    }
+    const size_t slot = (size_t)c->spair[qq] * c->max_chunks + c->chunk;
+    warp_sort_emit(dk, dp, n, c->prow, c->row_base, c->out_dist + slot * kprime, c->out_pos + slot * kprime,
+                   c->out_rowid + slot * kprime);
+    if (lane == 0) c->out_count[slot] = n;
+  }
+}
+
+// BOOT: compile the pooled-bootstrap calls in (shards / few probes per query: most items are cold) or
+// leave the row loop exactly as the call-free single-GPU version (r01 bisect: the calls cost ~4% there).
+template <int QL, int D, int NW, int MINB, int DSUB, bool BOOT>
 __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params p,
                                                               const uint32_t* __restrict__ total_items_p) {
   constexpr int NT = NW * 32;
@@ -317,8 +400,282 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   uint32_t* spair = sthr + QL;
   uint32_t* sqidx = spair + QL;
   uint32_t* sitem = sqidx + QL;
-  uint32_t* ssb = sitem + 1;  // next superblock (relative to the chunk's first) to hand out
-  uint32_t* scold = sitem + 2;  // 1: some query of this item has no bound yet -> pooled bootstrap
+  ItemCtx* ictx = reinterpret_cast<ItemCtx*>(sitem + 4);  // 16-byte aligned
+  const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
+
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t d = lane % D;
+  const uint32_t M = p.M, dsub = p.dsub, dim = p.dim, kprime = p.kprime, capw = p.capw, L = p.L;
+  const uint32_t units = L * C16 + 1;
+  const uint32_t total_items = *total_items_p;
+
+  // per-lane table offsets for static step j (see header): slot = (j-d) mod 16;
+  //   Bp[j]: relative to chunk (u-1): + CB when the lane is already on chunk u (j >= d)
+  //   B0[j]: unit 0 of a row, relative to the table start: lanes with j < d are on the LAST chunk
+  uint32_t Bp[16], B0[D];
+  float keepf[D], swf[D];
+#pragma unroll
+  for (int j = 0; j < 16; j++) Bp[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? CB : 0u);
+#pragma unroll
+  for (int j = 0; j < D; j++) {
+    B0[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? 0u : (C16 - 1) * CB);
+    keepf[j] = d == (uint32_t)j ? 0.0f : 1.0f;
+    swf[j] = d == (uint32_t)j ? 1.0f : 0.0f;
+  }
+  // Keep these per-lane constants in registers: left alone, ptxas rematerialises them inside the
+  // hot loop (ISETP+FSEL per switch step; r01 profile) which costs more issue slots than the FMAs.
+#pragma unroll
+  for (int j = 0; j < 16; j++) asm volatile("" : "+r"(Bp[j]));
+#pragma unroll
+  for (int j = 0; j < D; j++) {
+    asm volatile("" : "+r"(B0[j]));
+    asm volatile("" : "+f"(keepf[j]));
+    asm volatile("" : "+f"(swf[j]));
+  }
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) *sitem = atomicAdd(p.item_counter, 1u);
+    __syncthreads();
+    const uint32_t item = *sitem;
+    if (item >= total_items) break;
+    uint32_t lo = 0, hi = p.nlist;
+    while (hi - lo > 1) {
+      uint32_t mid = (lo + hi) >> 1;
+      if (p.item_off[mid] <= item) lo = mid; else hi = mid;
+    }
+    const uint32_t part = lo;
+    const uint64_t row_base = p.part_off[part];
+    const uint32_t n_p = (uint32_t)(p.part_off[part + 1] - row_base);
+    const uint32_t nch = (n_p + p.chunk_vecs - 1) / p.chunk_vecs;
+    const uint32_t local = item - p.item_off[part];
+    const uint32_t g = local / nch, c = local % nch;
+    const uint32_t pbase = p.part_pair_off[part] + g * QL;
+    const uint32_t nq = min((uint32_t)QL, p.part_pair_off[part + 1] - pbase);
+    const uint64_t* prow = p.row_ids + row_base;
+    const uint64_t* bm = p.bitmask ? p.bitmask[part] : nullptr;
+
+    bool mycold = false;
+    if (tid < QL) {
+      uint32_t pr = tid < nq ? p.pair_list[pbase + tid] : 0xffffffffu;
+      spair[tid] = pr;
+      const uint32_t qi = tid < nq ? pr / p.P : 0u;
+      sqidx[tid] = qi;
+      uint32_t t0 = KEY_PINF;
+      if (p.qthr && tid < nq) t0 = __ldcg(p.qthr + qi);
+      sthr[tid] = t0;
+      // unused query slots never pass the fast test
+      sthrf[tid] = tid < nq ? key_to_float(t0) : __int_as_float(0xff800000);
+      mycold = tid < nq && t0 == KEY_PINF;
+    }
+    if (tid < NW * QL) ccnt[tid] = 0;
+    if (tid == 0) {
+      ItemCtx ic;
+      ic.ckey = ckey; ic.cpos = cpos; ic.ccnt = ccnt; ic.sthr = sthr; ic.sqidx = sqidx; ic.spair = spair;
+      ic.qthr = p.qthr; ic.sthrf = sthrf; ic.prow = prow; ic.bm = bm;
+      ic.out_dist = p.out_dist; ic.out_pos = p.out_pos; ic.out_rowid = p.out_rowid; ic.out_count = p.out_count;
+      ic.row_base = row_base; ic.capw = capw; ic.kprime = kprime; ic.nq = nq;
+      ic.vend = min(n_p, c * p.chunk_vecs + p.chunk_vecs); ic.nw = NW; ic.max_chunks = p.max_chunks; ic.chunk = c;
+      ic.lower = p.lower; ic.upper = p.upper; ic.has_lower = p.has_lower; ic.has_upper = p.has_upper;
+      *ictx = ic;
+    }
+    for (uint32_t i = tid; i < QL * dim; i += NT) {
+      uint32_t qq = i / dim, e = i - qq * dim;
+      float val = 0.0f;
+      if (qq < nq) {
+        uint32_t qidx = p.pair_list[pbase + qq] / p.P;
+        float x = p.queries[(size_t)qidx * dim + e];
+        val = p.residual ? __fsub_rn(x, p.centroids[(size_t)part * dim + e]) : x;
+      }
+      resid[i] = val;
+    }
+    const bool cold_item = __syncthreads_or(mycold) != 0;  // some query of the item has no bound yet
+
+    // ---- A4: ADC tables, interleaved over the QL queries --------------------------------
+    // thread -> (slot = tid%16, code = tid/16 + k*NT/16): a quarter/half warp writes consecutive
+    // slots of one code row -> conflict-free wide stores.
+    uint32_t maxbits = 0;
+    {
+      const uint32_t slot = tid & 15;
+#pragma unroll 1
+      for (uint32_t ch = 0; ch < C16; ch++) {
+        const uint32_t m = ch * 16 + slot;
+        float xr[QL][DSUB > 0 ? DSUB : 1];
+        if (DSUB > 0) {
+#pragma unroll
+          for (int q = 0; q < QL; q++)
+#pragma unroll
+            for (int i = 0; i < DSUB; i++) xr[q][i] = resid[q * dim + m * DSUB + i];
+        }
+#pragma unroll 1
+        for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
+          const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
+          float yr[DSUB > 0 ? DSUB : 1];
+          if (DSUB > 0) {
+#pragma unroll
+            for (int i = 0; i < DSUB / 4; i++) {
+              float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
+              yr[4 * i] = v4.x; yr[4 * i + 1] = v4.y; yr[4 * i + 2] = v4.z; yr[4 * i + 3] = v4.w;
+            }
+          }
+          float val[QL];
+#pragma unroll
+          for (int q = 0; q < QL; q++) {
+            if (DSUB > 0)
+              val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr, dsub);
+            else
+              val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub, y, dsub);
+            maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
+          }
+          unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
+          if (QL == 4)
+            *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
+          else
+            *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
+        }
+      }
+    }
+    // exact-FMA switch only if no partial sum of <=256 entries can overflow: |T| < 2^118
+    const bool unsafe = __syncthreads_or(maxbits >= 0x7a800000u) != 0;
+
+    // ---- A5 + A6: scan the chunk's superblocks ---------------------------------------------
+    const uint32_t v0 = c * p.chunk_vecs;
+    const uint32_t vend = min(n_p, v0 + p.chunk_vecs);
+    const uint32_t sb_lo = v0 / (32 * L), sb_hi = (vend + 32 * L - 1) / (32 * L);
+    const float lower = p.lower, upper = p.upper;
+    const bool has_lower = p.has_lower != 0, has_upper = p.has_upper != 0;
+    const uint8_t* cbase = p.codes + (size_t)p.sb_off[part] * units * 512 + lane * 16;
+
+    // Pooled bootstrap of a cold item (some query has no bound yet): the candidates the NW warps
+    // buffered in their first rows are pooled and pruned once (#1 after ~96 rows per warp, #2 at the
+    // end of each warp's first superblock).  The calls sit BETWEEN segments of the row loop, never
+    // inside it: the loop body must stay free of calls and of inlined cold code (r01 bisect: either
+    // costs the scan ~10% through register pressure / instruction-cache misses).
+    const bool cold = BOOT && cold_item && !p.no_boot;
+    bool need1 = cold, need2 = cold && L > 3 && p.boot2 != 0;
+    const uint32_t boot_i = min(L, 3u);
+#pragma unroll 1
+    for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
+      const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
+      uint4 cur = __ldg(up), n1 = __ldg(up + 32);
+      const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
+      float acc[QL], done[QL];
+#pragma unroll
+      for (int q = 0; q < QL; q++) acc[q] = done[q] = 0.0f;
+      const uint32_t row0 = sb * 32 * L + lane;
+      // pick up bounds found meanwhile by other work items of the same queries
+      if (p.qthr) {
+        if (lane < nq) {
+          uint32_t t = __ldcg(p.qthr + sqidx[lane]);
+          if (t < sthr[lane]) {
+            uint32_t old = atomicMin(sthr + lane, t);
+            sthrf[lane] = key_to_float(min(old, t));
+          }
+        }
+        __syncwarp();
+      }
+      uint32_t i = 0;
+      uint32_t stop = (BOOT && need1) ? boot_i + 1 : L + 1;
+#pragma unroll 1
+      for (;;) {
+#pragma unroll 1
+      for (; i < stop; i++) {
+        const uint4 n2 = __ldg(pf);
+        pf += 32;
+        if (i < L) {
+          if (unsafe) scan_unit<QL, D, true, true, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+          else scan_unit<QL, D, true, false, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+        } else {
+          if (unsafe) scan_unit<QL, D, true, true, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+          else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
+        }
+        cur = n1; n1 = n2;
+        if (i >= 1) {
+          // `done` = distance of row i-1 of this lane.  Fast test: running threshold only; bounds,
+          // tail rows and the prefilter are applied on the (rare) slow path.
+          float thr[QL];
+          lds_volatile<QL>(sthrf_saddr, thr);
+          bool anyp = done[0] <= thr[0];
+#pragma unroll
+          for (int q = 1; q < QL; q++) anyp = anyp || (done[q] <= thr[q]);
+          if (__any_sync(FULL, anyp)) {
+            const uint32_t r = row0 + (i - 1) * 32;
+            uint32_t pm = 0;
+#pragma unroll
+            for (int q = 0; q < QL; q++) {
+              bool ok = done[q] <= thr[q];
+              if (has_lower) ok = ok && (lower <= done[q]);
+              if (has_upper) ok = ok && (done[q] < upper);
+              pm |= ok ? (1u << q) : 0u;
+            }
+            if (r >= vend) pm = 0;
+            pm &= (1u << nq) - 1u;
+            if (bm && pm) {
+              if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
+            }
+            if (__any_sync(FULL, pm != 0)) {
+#pragma unroll
+              for (int q = 0; q < QL; q++) {
+                const uint32_t b = (uint32_t)q * NW + w;
+                append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
+                            cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
+                            (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
+              }
+            }
+          }
+        }
+        if (i == L) continue;  // drain iteration: no further units (and the last of the loop)
+#pragma unroll 1
+        for (uint32_t u = 1; u < C16; u++) {
+          const uint4 n3 = __ldg(pf);
+          pf += 32;
+          scan_unit<QL, D, false, true, 16>(cur, lut + (size_t)(u - 1) * CB, Bp, B0, keepf, swf, d, acc, done);
+          cur = n1; n1 = n3;
+        }
+      }
+        if (BOOT && need1) {
+          bootstrap_fn(ictx);
+          need1 = false;
+          stop = L + 1;
+        }
+        if (!BOOT || i > L) break;
+      }
+      if (BOOT && need2) {
+        bootstrap_fn(ictx);
+        need2 = false;
+      }
+    }
+    if (BOOT && need1) bootstrap_fn(ictx);  // warps that drew no superblock still owe the barriers
+    if (BOOT && need2) bootstrap_fn(ictx);
+    __syncthreads();
+
+    finalize_fn(ictx);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The same kernel WITHOUT the pooled bootstrap and with the end-of-item code inlined: the text the
+// single-GPU headline configuration was tuned on.  Kept verbatim because the scan is sensitive to
+// what else lives in the function (r01 same-box bisect: 25.1 ms here vs 26.0 ms for the BOOT=false
+// instantiation of the kernel above, cfg 4); the host picks it whenever most work items are warm.
+template <int QL, int D, int NW, int MINB, int DSUB>
+__global__ void __launch_bounds__(NW * 32, MINB) scan3_nb_kernel(const Scan3Params p,
+                                                              const uint32_t* __restrict__ total_items_p) {
+  constexpr int NT = NW * 32;
+  constexpr uint32_t CB = 256u * 64u * QL;  // bytes per table chunk (16 sub-vectors)
+  constexpr uint32_t SLOTB = 4u * QL;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned char* lut = smem_raw;
+  const uint32_t C16 = p.M >> 4;
+  float* resid = reinterpret_cast<float*>(smem_raw + (size_t)C16 * CB);
+  uint32_t* ckey = reinterpret_cast<uint32_t*>(resid + QL * p.dim);
+  uint32_t* cpos = ckey + (size_t)QL * NW * p.capw;
+  uint32_t* ccnt = cpos + (size_t)QL * NW * p.capw;
+  float* sthrf = reinterpret_cast<float*>(ccnt + QL * NW);  // 16-byte aligned (all sizes are multiples of 16)
+  uint32_t* sthr = reinterpret_cast<uint32_t*>(sthrf + QL);
+  uint32_t* spair = sthr + QL;
+  uint32_t* sqidx = spair + QL;
+  uint32_t* sitem = sqidx + QL;
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -385,16 +742,6 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       sthrf[tid] = tid < nq ? key_to_float(t0) : __int_as_float(0xff800000);
     }
     if (tid < NW * QL) ccnt[tid] = 0;
-    if (tid == 0) {
-      *ssb = NW;
-      uint32_t cold = 0;
-      for (uint32_t qq = 0; qq < nq; qq++) {
-        uint32_t t0 = KEY_PINF;
-        if (p.qthr) t0 = __ldcg(p.qthr + p.pair_list[pbase + qq] / p.P);
-        cold |= t0 == KEY_PINF ? 1u : 0u;
-      }
-      *scold = p.no_boot ? 0u : cold;
-    }
     for (uint32_t i = tid; i < QL * dim; i += NT) {
       uint32_t qq = i / dim, e = i - qq * dim;
       float val = 0.0f;
@@ -423,43 +770,31 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
 #pragma unroll
             for (int i = 0; i < DSUB; i++) xr[q][i] = resid[q * dim + m * DSUB + i];
         }
-        // codes in batches of BT: all codebook rows of a batch are requested before the first is
-        // used, so the L2 latency of the (L1-cold) codebook is paid once per batch, not per entry
-        constexpr int BT = DSUB == 8 ? 4 : (DSUB == 16 ? 2 : 1);
-        constexpr uint32_t CSTEP = NT / 16;
 #pragma unroll 1
-        for (uint32_t code0 = tid >> 4; code0 < 256; code0 += CSTEP * BT) {
-          float yr[BT][DSUB > 0 ? DSUB : 1];
+        for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
+          const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
+          float yr[DSUB > 0 ? DSUB : 1];
           if (DSUB > 0) {
 #pragma unroll
-            for (int b = 0; b < BT; b++) {
-              const float* y = p.codebook + ((size_t)m * 256 + code0 + b * CSTEP) * dsub;
-#pragma unroll
-              for (int i = 0; i < DSUB / 4; i++) {
-                float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
-                yr[b][4 * i] = v4.x; yr[b][4 * i + 1] = v4.y; yr[b][4 * i + 2] = v4.z; yr[b][4 * i + 3] = v4.w;
-              }
+            for (int i = 0; i < DSUB / 4; i++) {
+              float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
+              yr[4 * i] = v4.x; yr[4 * i + 1] = v4.y; yr[4 * i + 2] = v4.z; yr[4 * i + 3] = v4.w;
             }
           }
+          float val[QL];
 #pragma unroll
-          for (int b = 0; b < BT; b++) {
-            const uint32_t code = code0 + b * CSTEP;
-            float val[QL];
-#pragma unroll
-            for (int q = 0; q < QL; q++) {
-              if (DSUB > 0)
-                val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr[b], dsub);
-              else
-                val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub,
-                                     p.codebook + ((size_t)m * 256 + code) * dsub, dsub);
-              maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
-            }
-            unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
-            if (QL == 4)
-              *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
+          for (int q = 0; q < QL; q++) {
+            if (DSUB > 0)
+              val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr, dsub);
             else
-              *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
+              val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub, y, dsub);
+            maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
           }
+          unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
+          if (QL == 4)
+            *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
+          else
+            *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
         }
       }
     }
@@ -474,112 +809,14 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     const bool has_lower = p.has_lower != 0, has_upper = p.has_upper != 0;
     const uint8_t* cbase = p.codes + (size_t)p.sb_off[part] * units * 512 + lane * 16;
 
-    // Row test: fast path = running threshold only (4 FSETP + vote); bounds, tail rows and the
-    // prefilter are applied on the (rare) slow path.
-    auto check_rows = [&](const float (&dv)[QL], const uint32_t r) {
-      float thr[QL];
-      lds_volatile<QL>(sthrf_saddr, thr);
-      bool anyp = dv[0] <= thr[0];
-#pragma unroll
-      for (int q = 1; q < QL; q++) anyp = anyp || (dv[q] <= thr[q]);
-      if (__any_sync(FULL, anyp)) {
-        uint32_t pm = 0;
-#pragma unroll
-        for (int q = 0; q < QL; q++) {
-          bool ok = dv[q] <= thr[q];
-          if (has_lower) ok = ok && (lower <= dv[q]);
-          if (has_upper) ok = ok && (dv[q] < upper);
-          pm |= ok ? (1u << q) : 0u;
-        }
-        if (r >= vend) pm = 0;
-        pm &= (1u << nq) - 1u;
-        if (bm && pm) {
-          if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
-        }
-        if (__any_sync(FULL, pm != 0)) {
-#pragma unroll
-          for (int q = 0; q < QL; q++) {
-            const uint32_t b = (uint32_t)q * NW + w;
-            append_rows((pm >> q) & 1u, dv[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
-                        cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
-                        (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
-          }
-        }
-      }
-    };
-
-    // Pooled bootstrap of a cold item (no bound known for one of its queries): once every warp has
-    // buffered its first ~64 rows, the NW x 64 candidates of each query are pooled and pruned ONCE;
-    // the k'-th best of ~512 rows is a far tighter start than each warp pruning its own 64 over and
-    // over (the r01 N=8 run spent ~40% of the scan there: every item of a shard is cold).
-    const bool cold = *scold != 0;
-    // pooled prunes still owed: #1 after ~64 rows per warp, #2 at the end of the warp's first superblock
-    bool need1 = cold, need2 = cold && L > 3 && p.boot2 != 0;
-    auto bootstrap = [&]() {
-      __syncthreads();
-      if (kprime <= 32) {
-        // bound = k'-th smallest of the lanes' minima over the pooled NW segments of the query
 #pragma unroll 1
-        for (uint32_t qq = w; qq < nq; qq += NW) {
-          uint32_t m = 0xffffffffu;
-          for (uint32_t w2 = 0; w2 < NW; w2++) {
-            const uint32_t n2 = ccnt[qq * NW + w2];
-            const uint32_t* sk = ckey + (size_t)(qq * NW + w2) * capw;
-            for (uint32_t i = lane; i < n2; i += 32) m = min(m, sk[i]);
-          }
-          const uint32_t T = warp_bound_k(m, kprime, lane);
-          if (T != 0xffffffffu && lane == 0) {
-            uint32_t old = atomicMin(sthr + qq, T);
-            sthrf[qq] = key_to_float(min(old, T));
-            if (p.qthr) atomicMin(p.qthr + sqidx[qq], T);
-          }
-        }
-        __syncthreads();
-        // every warp drops what the new bounds exclude from its own buffers
-#pragma unroll 1
-        for (uint32_t qq = 0; qq < nq; qq++) {
-          const uint32_t b = qq * NW + w;
-          const uint32_t n0 = ccnt[b];
-          if (n0) {
-            const uint32_t n1 = warp_compact_le(ckey + (size_t)b * capw, cpos + (size_t)b * capw, n0, sthr[qq], lane);
-            if (lane == 0) ccnt[b] = n1;
-          }
-        }
-        __syncwarp();
-        return;
-      }
-#pragma unroll 1
-      for (uint32_t qq = w; qq < nq; qq += NW) {
-        uint32_t* dk = ckey + (size_t)qq * NW * capw;
-        uint32_t* dp = cpos + (size_t)qq * NW * capw;
-        uint32_t n = gather_segments(dk, dp, ccnt + qq * NW, NW, capw, lane);
-        if (n > kprime) {
-          uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
-          n = kprime;
-          if (lane == 0) {
-            uint32_t old = atomicMin(sthr + qq, T);
-            sthrf[qq] = key_to_float(min(old, T));
-            if (p.qthr) atomicMin(p.qthr + sqidx[qq], T);
-          }
-        }
-        __syncwarp();
-        if (lane < NW) ccnt[qq * NW + lane] = lane == 0 ? n : 0u;
-      }
-      __syncthreads();
-    };
-    const uint32_t boot_i = min(L, 3u);
-
-    // superblocks are handed out dynamically (shared counter) so that a warp that drew short or
-    // cheap superblocks keeps working instead of waiting at the barrier
-    uint32_t sb = sb_lo + w;
-#pragma unroll 1
-    while (sb < sb_hi) {
+    for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
       const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
       uint4 cur = __ldg(up), n1 = __ldg(up + 32);
       const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
-      float acc[QL], done[QL], prev[QL];
+      float acc[QL], done[QL];
 #pragma unroll
-      for (int q = 0; q < QL; q++) acc[q] = done[q] = prev[q] = 0.0f;
+      for (int q = 0; q < QL; q++) acc[q] = done[q] = 0.0f;
       const uint32_t row0 = sb * 32 * L + lane;
       // pick up bounds found meanwhile by other work items of the same queries
       if (p.qthr) {
@@ -604,17 +841,39 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
         }
         cur = n1; n1 = n2;
-        // `done` = distance of row i-1 of this lane; it is tested one iteration LATER (as `prev`),
-        // when its last LDS has long landed, so the test never stalls the lookup stream
-        if (i >= 2) check_rows(prev, row0 + (i - 2) * 32);
+        if (i >= 1) {
+          // `done` = distance of row i-1 of this lane.  Fast test: running threshold only; bounds,
+          // tail rows and the prefilter are applied on the (rare) slow path.
+          float thr[QL];
+          lds_volatile<QL>(sthrf_saddr, thr);
+          bool anyp = done[0] <= thr[0];
 #pragma unroll
-        for (int q = 0; q < QL; q++) prev[q] = done[q];
-        if (need1 && i == boot_i) {
-          bootstrap();
-          need1 = false;
-        } else if (need2 && i == L) {
-          bootstrap();
-          need2 = false;
+          for (int q = 1; q < QL; q++) anyp = anyp || (done[q] <= thr[q]);
+          if (__any_sync(FULL, anyp)) {
+            const uint32_t r = row0 + (i - 1) * 32;
+            uint32_t pm = 0;
+#pragma unroll
+            for (int q = 0; q < QL; q++) {
+              bool ok = done[q] <= thr[q];
+              if (has_lower) ok = ok && (lower <= done[q]);
+              if (has_upper) ok = ok && (done[q] < upper);
+              pm |= ok ? (1u << q) : 0u;
+            }
+            if (r >= vend) pm = 0;
+            pm &= (1u << nq) - 1u;
+            if (bm && pm) {
+              if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
+            }
+            if (__any_sync(FULL, pm != 0)) {
+#pragma unroll
+              for (int q = 0; q < QL; q++) {
+                const uint32_t b = (uint32_t)q * NW + w;
+                append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
+                            cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
+                            (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
+              }
+            }
+          }
         }
         if (i == L) break;
 #pragma unroll 1
@@ -625,13 +884,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           cur = n1; n1 = n3;
         }
       }
-      check_rows(prev, row0 + (L - 1) * 32);
-      uint32_t nx = 0;
-      if (lane == 0) nx = atomicAdd(ssb, 1u);
-      sb = sb_lo + __shfl_sync(FULL, nx, 0);
     }
-    if (need1) bootstrap();  // warps that drew no superblock still owe the barriers
-    if (need2) bootstrap();
     __syncthreads();
 
     // ---- finalize: one warp per query: gather the warps' buffers, select k', sorted emit ----
@@ -639,7 +892,21 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     for (uint32_t qq = w; qq < nq; qq += NW) {
       uint32_t* dk = ckey + (size_t)qq * NW * capw;
       uint32_t* dp = cpos + (size_t)qq * NW * capw;
-      uint32_t n = gather_segments(dk, dp, ccnt + qq * NW, NW, capw, lane);
+      uint32_t n = ccnt[qq * NW];
+#pragma unroll 1
+      for (uint32_t w2 = 1; w2 < NW; w2++) {
+        const uint32_t n2 = ccnt[qq * NW + w2];
+        const uint32_t* sk = dk + (size_t)w2 * capw;
+        const uint32_t* sp = dp + (size_t)w2 * capw;
+        for (uint32_t i0 = 0; i0 < n2; i0 += 32) {
+          uint32_t i = i0 + lane, kk = 0, pp = 0;
+          if (i < n2) { kk = sk[i]; pp = sp[i]; }
+          __syncwarp();
+          if (i < n2) { dk[n + i] = kk; dp[n + i] = pp; }
+          __syncwarp();
+        }
+        n += n2;
+      }
       if (n > kprime) {
         uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
         n = kprime;

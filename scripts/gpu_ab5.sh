@@ -13,9 +13,9 @@ except Exception as e:
     print("$name parse fail", e); print(open("gpurun_out/ab_$name.err").read()[-800:])
 PY
 }
-run s8 "--workload cfg4 --shard-of 8" X=1
+run cfg2 "--workload cfg2" X=1
 run s1 "--workload cfg4" X=1
-run s1_noqthr "--workload cfg4" LB200_NO_QTHR=1
+
 run cfg1 "--workload cfg1" X=1
-run cfg5 "--workload cfg5" X=1
-run cfg3 "--workload cfg3" X=1
+
+

@@ -348,6 +348,23 @@ def test_flat_parity(oracle, metric, d):
         _assert_same(gd, gi, gc, rd, ri, rc, f"flat {metric} k={k}")
 
 
+def test_flat_segmented_select(oracle):
+    """n large enough that each distance row is cut into several select segments + merge; many
+    duplicated rows so that ties straddle segment borders."""
+    from lance_b200 import flat_knn
+    rng = np.random.default_rng(11)
+    n, d = 150_001, 32
+    base = rng.normal(size=(500, d)).astype(np.float32)
+    vecs = base[rng.integers(0, 500, n)]          # every row has ~300 exact duplicates
+    q = base[:12] + 0.01 * rng.normal(size=(12, d)).astype(np.float32)
+    valid = rng.random(n) < 0.95
+    vbits = np.packbits(valid, bitorder="little")
+    for k in (1, 10, 400):
+        gd, gi, gc = flat_knn(q, "l2", vecs, k, validity=vbits)
+        rd, ri, rc = oracle.flat_knn("l2", q, vecs, k, validity=vbits)
+        _assert_same(gd, gi, gc, rd, ri, rc, f"segmented flat k={k}")
+
+
 def test_flat_edge_cases(oracle):
     from lance_b200 import flat_knn
     rng = np.random.default_rng(0)
