@@ -191,6 +191,16 @@ def run_reference(args, wl):
     print(json.dumps(line), flush=True)
 
 
+def _result_crc(od, oi, oc):
+    """CRC of the last batch's results (counts, row ids, distance bits of the valid entries): the same
+    value at every N says the sharded result is bit-identical to the single-GPU one."""
+    import zlib
+    valid = np.arange(od.shape[1])[None, :] < oc.astype(np.int64)[:, None]
+    c = zlib.crc32(np.ascontiguousarray(oc).tobytes())
+    c = zlib.crc32(np.ascontiguousarray(oi[valid]).tobytes(), c)
+    return zlib.crc32(np.ascontiguousarray(od[valid]).tobytes(), c)
+
+
 def run_flat(args):
     """--workload cfg2: flat brute-force L2 kNN 1M x 128, k=10 (KNNVectorDistanceExec path, no index;
     BASELINE configs[1]).  A step = one batch of 256 queries against the device-resident vectors."""
@@ -466,6 +476,7 @@ def main():
                         "lb200_search (host-pointer C ABI, pinned host buffers, blocking; host wall clock)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
+        "result_crc32": _result_crc(h_od.numpy(), h_oi.numpy(), h_oc.numpy()),
     }
     if world > 1:
         line["roofline"]["all_ranks_achieved"] = float(bsum.item()) / (float(tmax.item()) * 1e-3) / 1e9

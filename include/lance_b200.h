@@ -119,6 +119,28 @@ int32_t lb200_search_probed_device(lb200_index* ix, const float* d_queries, uint
                                    const float* upper_or_null, float* d_out_dist, uint64_t* d_out_rowid,
                                    uint32_t* d_out_count, float* d_out_exact_or_null, void* stream);
 
+/* Shared pruning bounds between the shards of one index (multi-GPU).
+ * Inside one index the scan keeps, per query, the running k'-th best distance over everything
+ * scanned so far and skips rows above it.  On a partition-sharded index every shard would have
+ * to find that bound again on its own (G times the cold starts); instead each shard publishes the
+ * bounds it finds into every peer's table with remote atomic-min over NVLink peer memory, from
+ * inside the scan kernel.  A bound found on ANY shard is a valid bound for the merged result, so
+ * the merged top-k' stays exactly the single-index one (the shard-local lists may be shorter).
+ *   export: allocates this shard's table for up to max_queries queries per batch and returns a
+ *           64-byte CUDA IPC handle (for peers in other processes) and the device address (for
+ *           peers in the same process).
+ *   attach: world shards, this one is `self`.  handles = [world][64] bytes as exported (entry
+ *           `self` ignored), or NULL with same_process_ptrs = [world] device addresses.
+ *   Contract: all shards run the same sequence of shard-mode searches, and a cross-rank
+ *   synchronisation (the candidate exchange) separates consecutive batches; tables are
+ *   double-buffered by batch parity so a late peer never writes into the next batch's bounds.
+ *   Only shard-mode searches (d_out_exact != NULL) with Q <= max_queries use the tables. */
+int32_t lb200_peer_thresholds_export(lb200_index* ix, uint32_t max_queries, void* handle_out_64,
+                                     uint64_t* dev_ptr_out);
+int32_t lb200_peer_thresholds_attach(lb200_index* ix, uint32_t world, uint32_t self, const void* handles_or_null,
+                                     const uint64_t* same_process_ptrs_or_null);
+int32_t lb200_peer_thresholds_detach(lb200_index* ix);
+
 /* compute_distance (flat.rs:28-86; KNNVectorDistanceExec, io/exec/knn.rs:156-183): one
  * distance per (query,row); validity = Arrow validity bitmap (bit set = valid) or NULL;
  * null rows yield NaN.  out [Q][n]. */

@@ -14,6 +14,7 @@ EXPORTS = [
     "lb200_search", "lb200_search_device", "lb200_find_partitions_device", "lb200_search_probed_device", "lb200_flat_distance", "lb200_flat_topk",
     "lb200_flat_topk_device", "lb200_merge_topk_device", "lb200_set_profiling", "lb200_get_stats",
     "lb200_set_scan_variant", "lb200_last_error", "lb200_version",
+    "lb200_peer_thresholds_export", "lb200_peer_thresholds_attach", "lb200_peer_thresholds_detach",
 ]
 
 

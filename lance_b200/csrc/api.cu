@@ -81,6 +81,7 @@ struct Arena {
   static size_t pad(size_t b) { return (b + 255) & ~(size_t)255; }
 };
 
+constexpr uint32_t LB200_MAX_PEERS = 15;
 struct lb200_index {
   int device = 0, metric = 0;
   uint32_t dim = 0, nlist = 0, M = 0, dsub = 0;
@@ -103,6 +104,13 @@ struct lb200_index {
   Arena arena;
   Arena stage;  // host<->device staging of lb200_search (queries in, results out)
   const uint64_t** d_bitmask_ptrs = nullptr;  // scratch for prefilter pointers
+  // shared pruning bounds between shards (lb200_peer_thresholds_*): two tables of pthr_cap keys
+  // (batch parity), the peers' addresses of both, and which of them were opened through CUDA IPC
+  uint32_t* pthr_local = nullptr;
+  uint32_t pthr_cap = 0, pthr_peers = 0;
+  uint64_t pthr_epoch = 0;
+  uint32_t** d_pthr_tbl = nullptr;  // device [2][LB200_MAX_PEERS]
+  void* pthr_ipc[LB200_MAX_PEERS] = {};
 };
 
 static int select_device(int device_id) {
@@ -274,10 +282,102 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->arena.base);
   cudaFree(ix->stage.base);
   cudaFree((void*)ix->d_bitmask_ptrs);
+  lb200_peer_thresholds_detach(ix);
+  cudaFree(ix->pthr_local);
+  cudaFree(ix->d_pthr_tbl);
   for (auto& e : ix->ev)
     if (e) cudaEventDestroy(e);
   if (ix->stream) cudaStreamDestroy(ix->stream);
   delete ix;
+}
+
+// ---- shared pruning bounds between shards (include/lance_b200.h) ---------------------------------
+extern "C" int32_t lb200_peer_thresholds_export(lb200_index* ix, uint32_t max_queries, void* handle_out_64,
+                                                uint64_t* dev_ptr_out) {
+  if (!ix || !max_queries) return set_err(LB200_EINVAL, "null index or max_queries == 0");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (ix->pthr_peers) return set_err(LB200_EINVAL, "peer tables are attached; detach first");
+  if (ix->pthr_local && ix->pthr_cap < max_queries) {
+    CK(cudaFree(ix->pthr_local));
+    ix->pthr_local = nullptr;
+  }
+  if (!ix->pthr_local) {
+    // plain cudaMalloc: pooled / stream-ordered allocations cannot be exported over IPC
+    CK(cudaMalloc(&ix->pthr_local, (size_t)2 * max_queries * 4));
+    ix->pthr_cap = max_queries;
+  }
+  fill_u32_kernel<<<(2 * ix->pthr_cap + 255) / 256, 256, 0, ix->stream>>>(ix->pthr_local, KEY_PINF,
+                                                                          (size_t)2 * ix->pthr_cap);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(ix->stream));
+  if (handle_out_64) {
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, ix->pthr_local));
+    memcpy(handle_out_64, &h, 64);
+  }
+  if (dev_ptr_out) *dev_ptr_out = (uint64_t)(uintptr_t)ix->pthr_local;
+  return 0;
+}
+
+extern "C" int32_t lb200_peer_thresholds_detach(lb200_index* ix) {
+  if (!ix) return set_err(LB200_EINVAL, "null index");
+  cudaSetDevice(ix->device);
+  for (auto& p : ix->pthr_ipc)
+    if (p) {
+      cudaIpcCloseMemHandle(p);
+      p = nullptr;
+    }
+  ix->pthr_peers = 0;
+  ix->pthr_epoch = 0;
+  return 0;
+}
+
+extern "C" int32_t lb200_peer_thresholds_attach(lb200_index* ix, uint32_t world, uint32_t self,
+                                                const void* handles_or_null,
+                                                const uint64_t* same_process_ptrs_or_null) {
+  if (!ix) return set_err(LB200_EINVAL, "null index");
+  if (!ix->pthr_local) return set_err(LB200_EINVAL, "call lb200_peer_thresholds_export first");
+  if (world < 1 || world > LB200_MAX_PEERS + 1 || self >= world)
+    return set_err(LB200_EINVAL, "world=%u self=%u out of range (at most %u shards)", world, self, LB200_MAX_PEERS + 1);
+  if (!handles_or_null && !same_process_ptrs_or_null) return set_err(LB200_EINVAL, "no peer handles given");
+  lb200_peer_thresholds_detach(ix);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CK(cudaSetDevice(ix->device));
+  uint32_t* tbl[2 * LB200_MAX_PEERS] = {};
+  uint32_t n = 0;
+  for (uint32_t r = 0; r < world; r++) {
+    if (r == self) continue;
+    uint32_t* base = nullptr;
+    if (same_process_ptrs_or_null) {
+      base = reinterpret_cast<uint32_t*>((uintptr_t)same_process_ptrs_or_null[r]);
+      if (!base) return set_err(LB200_EINVAL, "peer %u: null table address", r);
+    } else {
+      cudaIpcMemHandle_t h;
+      memcpy(&h, (const char*)handles_or_null + (size_t)r * 64, 64);
+      void* p = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        for (uint32_t j = 0; j < n; j++) {
+          cudaIpcCloseMemHandle(ix->pthr_ipc[j]);
+          ix->pthr_ipc[j] = nullptr;
+        }
+        return set_err(LB200_ECUDA, "cudaIpcOpenMemHandle(peer %u) failed: %s", r, cudaGetErrorString(e));
+      }
+      ix->pthr_ipc[n] = p;
+      base = (uint32_t*)p;
+    }
+    // every shard exported the same max_queries: parity b of peer r lives at base + b*cap
+    tbl[n] = base;
+    tbl[LB200_MAX_PEERS + n] = base + ix->pthr_cap;
+    n++;
+  }
+  if (!ix->d_pthr_tbl) CK(cudaMalloc(&ix->d_pthr_tbl, sizeof(tbl)));
+  CK(cudaMemcpy(ix->d_pthr_tbl, tbl, sizeof(tbl), cudaMemcpyHostToDevice));
+  ix->pthr_peers = n;
+  ix->pthr_epoch = 0;
+  return 0;
 }
 
 extern "C" int32_t lb200_set_profiling(lb200_index* ix, int32_t enabled) {

@@ -339,8 +339,21 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     sp.lower = a.lower; sp.upper = a.upper; sp.has_lower = a.has_lower; sp.has_upper = a.has_upper;
     sp.bitmask = a.d_bitmask;
     sp.out_dist = d_sdist; sp.out_pos = d_spos; sp.out_rowid = d_srow; sp.out_count = d_scnt;
+    uint32_t* reset = d_qthr;
+    uint32_t nreset = Q;
+    if (sp.qthr && a.shard_mode && ix->pthr_peers && Q <= ix->pthr_cap && !getenv("LB200_NO_PEER_THR")) {
+      // bounds shared with the peer shards: this batch uses table (epoch & 1) -- reset one batch ago, peers
+      // may already have published into it -- and clears the other one for the next batch
+      const uint32_t par = (uint32_t)(ix->pthr_epoch & 1);
+      sp.qthr = ix->pthr_local + (size_t)par * ix->pthr_cap;
+      sp.peers = ix->d_pthr_tbl + (size_t)par * LB200_MAX_PEERS;
+      sp.n_peers = ix->pthr_peers;
+      reset = ix->pthr_local + (size_t)(par ^ 1) * ix->pthr_cap;
+      nreset = ix->pthr_cap;
+      ix->pthr_epoch++;
+    }
     if (sp.qthr) {
-      fill_u32_kernel<<<(Q + 255) / 256, 256, 0, st>>>(d_qthr, KEY_PINF, Q);
+      fill_u32_kernel<<<(nreset + 255) / 256, 256, 0, st>>>(reset, KEY_PINF, nreset);
       CK(cudaGetLastError());
       launches++;
     }

@@ -55,6 +55,8 @@ struct Scan3Params {
   uint32_t max_chunks;
   uint32_t capw;                  // candidate buffer entries per (warp, query slot)
   uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
+  uint32_t* const* peers;         // [n_peers] the same table on the peer GPUs (NVLink peer memory), or null
+  uint32_t n_peers;
   int32_t no_boot;                // diagnostic: disable the pooled bootstrap
   int32_t boot2;                  // second pooled prune at the end of each warp's first superblock
   // bounds / prefilter
@@ -261,6 +263,8 @@ __device__ __forceinline__ void lds_volatile(uint32_t saddr, float (&v)[QL]) {
 // grew from 4.9k to 21k instructions and the scan lost 10% to instruction-cache misses and spills).
 struct ItemCtx {
   uint32_t *ckey, *cpos, *ccnt, *sthr, *sqidx, *spair, *qthr;
+  uint32_t* const* peers;
+  uint32_t n_peers;
   float* sthrf;
   const uint64_t* prow;
   const uint64_t* bm;
@@ -277,6 +281,15 @@ struct ItemCtx {
 __host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, uint32_t dim, uint32_t capw) {
   size_t lut = (size_t)(M / 16) * 256 * 64 * QL;
   return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32 + sizeof(ItemCtx) + 16;
+}
+
+// Publish a query's bound (one thread): into this GPU's table and -- partition shards on several
+// GPUs -- into every peer's table with a fire-and-forget atomic-min over NVLink peer memory.  The
+// peers get the best value known here, so bounds found by the in-loop prunes travel too.
+__device__ __noinline__ void publish_bound(const ItemCtx* c, uint32_t qidx, uint32_t T) {
+  const uint32_t old = atomicMin(c->qthr + qidx, T);
+  const uint32_t best = min(old, T);
+  for (uint32_t j = 0; j < c->n_peers; j++) atomicMin(c->peers[j] + qidx, best);
 }
 
 // Pull the NW per-warp candidate segments of one query (segment w at w*capw, cnt[w] entries) together
@@ -320,7 +333,7 @@ __device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
       if (T != 0xffffffffu && lane == 0) {
         uint32_t old = atomicMin(c->sthr + qq, T);
         c->sthrf[qq] = key_to_float(min(old, T));
-        if (c->qthr) atomicMin(c->qthr + c->sqidx[qq], T);
+        if (c->qthr) publish_bound(c, c->sqidx[qq], T);
       }
     }
     __syncthreads();
@@ -346,7 +359,7 @@ __device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
       if (lane == 0) {
         uint32_t old = atomicMin(c->sthr + qq, T);
         c->sthrf[qq] = key_to_float(min(old, T));
-        if (c->qthr) atomicMin(c->qthr + c->sqidx[qq], T);
+        if (c->qthr) publish_bound(c, c->sqidx[qq], T);
       }
     }
     __syncwarp();
@@ -366,12 +379,12 @@ __device__ __noinline__ void finalize_fn(const ItemCtx* c) {
     if (n > kprime) {
       uint32_t T = warp_select_k(dk, dp, n, kprime, c->prow);
       n = kprime;
-      if (c->qthr && lane == 0) atomicMin(c->qthr + c->sqidx[qq], T);
+      if (c->qthr && lane == 0) publish_bound(c, c->sqidx[qq], T);
     } else if (n == kprime && c->qthr) {
       uint32_t mx = 0;
       for (uint32_t i = lane; i < n; i += 32) mx = max(mx, dk[i]);
       mx = __reduce_max_sync(FULL, mx);
-      if (lane == 0) atomicMin(c->qthr + c->sqidx[qq], mx);
+      if (lane == 0) publish_bound(c, c->sqidx[qq], mx);
     }
     const size_t slot = (size_t)c->spair[qq] * c->max_chunks + c->chunk;
     warp_sort_emit(dk, dp, n, c->prow, c->row_base, c->out_dist + slot * kprime, c->out_pos + slot * kprime,
@@ -472,7 +485,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     if (tid == 0) {
       ItemCtx ic;
       ic.ckey = ckey; ic.cpos = cpos; ic.ccnt = ccnt; ic.sthr = sthr; ic.sqidx = sqidx; ic.spair = spair;
-      ic.qthr = p.qthr; ic.sthrf = sthrf; ic.prow = prow; ic.bm = bm;
+      ic.qthr = p.qthr; ic.peers = p.peers; ic.n_peers = p.n_peers; ic.sthrf = sthrf; ic.prow = prow; ic.bm = bm;
       ic.out_dist = p.out_dist; ic.out_pos = p.out_pos; ic.out_rowid = p.out_rowid; ic.out_count = p.out_count;
       ic.row_base = row_base; ic.capw = capw; ic.kprime = kprime; ic.nq = nq;
       ic.vend = min(n_p, c * p.chunk_vecs + p.chunk_vecs); ic.nw = NW; ic.max_chunks = p.max_chunks; ic.chunk = c;

@@ -175,6 +175,28 @@ class IvfPqIndex:
             C.c_void_p(d_out_count), C.c_void_p(d_out_exact) if d_out_exact else None,
             C.c_void_p(stream) if stream else None))
 
+    def peer_thresholds_export(self, max_queries):
+        """Allocate this shard's table of shared pruning bounds; returns (64-byte IPC handle, device address)."""
+        h = (C.c_ubyte * 64)()
+        ptr = C.c_uint64(0)
+        check(self._L.lb200_peer_thresholds_export(self._h, C.c_uint32(max_queries), h, C.byref(ptr)))
+        return bytes(h), int(ptr.value)
+
+    def peer_thresholds_attach(self, world, rank, handles=None, ptrs=None):
+        """handles: list of `world` 64-byte IPC handles (peers in other processes), or ptrs: list of
+        `world` device addresses (peers in this process).  See include/lance_b200.h for the contract."""
+        hb = pb = None
+        if ptrs is not None:
+            pb = (C.c_uint64 * world)(*[int(p) for p in ptrs])
+        else:
+            raw = b"".join(handles)
+            assert len(raw) == 64 * world
+            hb = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+        check(self._L.lb200_peer_thresholds_attach(self._h, C.c_uint32(world), C.c_uint32(rank), hb, pb))
+
+    def peer_thresholds_detach(self):
+        check(self._L.lb200_peer_thresholds_detach(self._h))
+
     def set_profiling(self, on=True):
         check(self._L.lb200_set_profiling(self._h, C.c_int32(1 if on else 0)))
 

@@ -3,15 +3,19 @@
 IVF partitions are independent units (rust/lance/src/io/exec/knn.rs:519-635 searches them one by
 one and merges), so they shard with no data-path collective except ONE exchange step:
 
-  rank r:  coarse step on the full batch (replicated) -> scan of the probed partitions it owns
-           -> local k' candidates per query            (lb200_search_device, shard mode)
+  rank r:  coarse step (sharded by queries, probe lists all-gathered) -> scan of the probed
+           partitions it owns -> local k' candidates per query   (lb200_search_probed_device)
+           While scanning, the ranks publish each query's running k'-th-best bound into their
+           peers' tables over NVLink peer memory (lb200_peer_thresholds_*), so a row that cannot
+           reach the merged top-k' is skipped on every GPU, not only on the one that knows.
   all:     all_gather of [Q][k'] (dist f32, row id i64, count i32[, exact f32])
   rank 0:  merge of the G lists == concat + sort_to_indices(limit k') of ivf/v2.rs:383-400,
            then the refine cut of scanner.rs:1706-1721     (lb200_merge_topk_device)
 
-The result is bit-identical to the single-index search because every shard list is the exact
-(distance, row id)-ordered top-k' of its rows and top-k'(union) is contained in the union of the
-shards' top-k'.  This module is host-side plumbing only (torch.distributed); all compute is in
+The result is bit-identical to the single-index search because every shard list holds, in
+(distance, row id) order, every one of its rows that can be in the merged top-k': its exact local
+top-k', minus only rows above a bound some shard has PROVED (k' rows at or below it exist), and
+top-k'(union) is contained in the union of the shards' top-k'.  This module is host-side plumbing only (torch.distributed); all compute is in
 liblance_b200.so.
 """
 import numpy as np
@@ -88,6 +92,25 @@ class ShardedIvfPq:
         self.fd = torch.empty((Q, k), dtype=torch.float32, device=dev)
         self.fi = torch.empty((Q, k), dtype=torch.int64, device=dev)
         self.fc = torch.empty((Q,), dtype=torch.int32, device=dev)
+        self._share_bounds(Q)
+
+    def _share_bounds(self, Q):
+        """Give every shard a table of per-query pruning bounds that its peers update from inside
+        their scan kernels (remote atomic-min over NVLink peer memory; include/lance_b200.h,
+        lb200_peer_thresholds_*).  One all_gather of the 64-byte CUDA IPC handles at set-up."""
+        import os
+        torch, G = self._torch, self.world
+        self.shared_bounds = False
+        if G == 1 or os.environ.get("LB200_NO_PEER_THR"):
+            return
+        handle, _ = self.ix.peer_thresholds_export(Q)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=self.dev)
+        allh = torch.empty((G, 64), dtype=torch.uint8, device=self.dev)
+        self.dist.all_gather_into_tensor(allh, mine)
+        handles = [bytes(allh[g].cpu().tolist()) for g in range(G)]
+        self.ix.peer_thresholds_attach(G, self.rank, handles=handles)
+        self.dist.barrier()  # every table exists and is cleared before anyone's first batch publishes
+        self.shared_bounds = True
 
     def search_device(self, d_queries, stream):
         """d_queries: CUDA f32 tensor [Q][dim].  Everything is ordered on `stream` (which must be

@@ -473,3 +473,56 @@ def test_sharded_search_merge_equals_single_index(oracle, metric, refine, G, pro
                  f"sharded {metric} G={G}")
     for ix in shards:
         ix.close()
+
+
+@pytest.mark.parametrize("metric,refine,G", [("l2", 0, 2), ("l2", 3, 4), ("cosine", 2, 3), ("dot", 0, 2)])
+def test_sharded_search_with_shared_bounds(oracle, metric, refine, G):
+    """lb200_peer_thresholds_*: the shards publish their per-query pruning bounds into each other's
+    tables (here: G shard handles of one process on one device, attached by address; across
+    processes the same tables are opened through CUDA IPC and written over NVLink).  The merged
+    result must stay bit-identical to the unsharded oracle search for consecutive batches with
+    different queries (tables are double-buffered by batch parity), and shards searched later must
+    have been pruned by the bounds of the earlier ones."""
+    from lance_b200 import IvfPqIndex
+    from lance_b200.index import merge_topk_device
+    from lance_b200.shard import assign_partitions
+    rng = np.random.default_rng(10 + G)
+    d, nlist, M, k, nprobes, Q = 64, 24, 16, 10, 12, 48
+    vecs = rng.normal(size=(16000, d)).astype(np.float32)
+    data = build_ivf_pq(vecs, metric, nlist, M, seed=2, keep_raw=True, ivf_iters=3, pq_iters=2, sample=4096)
+    owner = assign_partitions(np.diff(data.part_offsets.astype(np.int64)), G)
+    kp = k * max(refine, 1)
+    dev = torch.device("cuda", 0)
+    shards = [IvfPqIndex(data.subset(np.nonzero(owner == g)[0])) for g in range(G)]
+    ptrs = [ix.peer_thresholds_export(Q)[1] for ix in shards]
+    for g, ix in enumerate(shards):
+        ix.peer_thresholds_attach(G, g, ptrs=ptrs)
+    pruned = 0
+    for batch in range(3):
+        nq = Q if batch != 1 else Q - 7  # a smaller batch in the middle
+        g_d = torch.empty((G, nq, kp), dtype=torch.float32, device=dev)
+        g_i = torch.empty((G, nq, kp), dtype=torch.int64, device=dev)
+        g_c = torch.empty((G, nq), dtype=torch.int32, device=dev)
+        g_e = torch.empty((G, nq, kp), dtype=torch.float32, device=dev)
+        fd = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        fi = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        fc = torch.empty((nq,), dtype=torch.int32, device=dev)
+        q = vecs[rng.integers(0, len(vecs), nq)] + 0.05 * rng.normal(size=(nq, d)).astype(np.float32)
+        rd, ri, rc, _ = oracle.OracleIndex(data).search(q, k=k, nprobes=nprobes, refine_factor=refine)
+        dq = torch.from_numpy(q).to(dev)
+        order = list(range(G)) if batch % 2 == 0 else list(range(G - 1, -1, -1))
+        for g in order:
+            shards[g].search_device(dq.data_ptr(), nq, nprobes, k, refine, g_d[g].data_ptr(), g_i[g].data_ptr(),
+                                    g_c[g].data_ptr(), d_out_exact=g_e[g].data_ptr())
+            torch.cuda.synchronize()
+        cnt = g_c.cpu().numpy()
+        pruned += int((cnt[order[-1]] < kp).sum())
+        merge_topk_device(0, g_d.data_ptr(), g_i.data_ptr(), g_e.data_ptr() if refine else None, g_c.data_ptr(), G, nq,
+                          kp, kp, k, fd.data_ptr(), fi.data_ptr(), fc.data_ptr())
+        torch.cuda.synchronize()
+        _assert_same(fd.cpu().numpy(), fi.cpu().numpy().astype(np.uint64), fc.cpu().numpy(), rd[:, :k],
+                     ri[:, :k], rc, f"shared bounds {metric} G={G} batch {batch}")
+    assert pruned > 0, "the last shard of a batch never returned a shortened list: bounds were not shared"
+    for ix in shards:
+        ix.peer_thresholds_detach()
+        ix.close()
