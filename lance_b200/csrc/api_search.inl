@@ -169,6 +169,12 @@ static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint3
     dim3 g2((ix->nlist + 127) / 128, (Q + CQ_QB - 1) / CQ_QB);
     coarse_dist_l2_tiled_kernel<<<g2, 128, tsm, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D, ix->nlist,
                                                       nullptr);
+  } else if (ix->metric == LB200_DOT && ix->dim % 64 == 0 && Q >= 8 &&
+             (2 * (size_t)CD_SLAB + (size_t)CD_QB * ix->dim) * 4 <= ix->smem_optin && !getenv("LB200_COARSE_SIMPLE")) {
+    const size_t dsm = (2 * (size_t)CD_SLAB + (size_t)CD_QB * ix->dim) * 4;
+    CK(cudaFuncSetAttribute(coarse_dist_dot_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsm));
+    dim3 g2((ix->nlist + 127) / 128, (Q + CD_QB - 1) / CD_QB);
+    coarse_dist_dot_slab_kernel<<<g2, 512, dsm, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D, ix->nlist);
   } else if (ix->metric == LB200_DOT)
     coarse_dist_kernel<false><<<grid, COARSE_THREADS, smem, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D);
   else

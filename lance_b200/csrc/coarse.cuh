@@ -295,4 +295,95 @@ coarse_dist_l2_tiled_kernel(const float* __restrict__ queries, const float* __re
   }
 }
 
+// Fast dot-metric coarse distances for d % 64 == 0 (Dot for f32, dot.rs:141-195: 16 lane accumulators,
+// per 64-chunk sum16[i] += (p1 + p2) + (p3 + p4), p_j = x[16j+i]*y[16j+i]; no 8-lane or scalar tail).
+// Block = 512 threads = 128 centroids x 4 query groups of 4 queries.  The centroid tile is streamed
+// through shared memory in 64-dimension slabs (pitch 129, double-buffered: the next slab is fetched
+// into registers while the current one is consumed), so the centroid matrix crosses L2 once per 16
+// queries and each thread keeps only its 4 x 16 accumulators across slabs -- any d fits.
+constexpr int CD_QB = 16;
+constexpr int CD_SLAB = 64 * CQ_PITCH;  // floats per slab buffer
+__global__ void __launch_bounds__(512, 1)
+coarse_dist_dot_slab_kernel(const float* __restrict__ queries, const float* __restrict__ centroids, uint32_t Q,
+                            uint32_t nlist, uint32_t d, float* __restrict__ out, size_t out_stride) {
+  extern __shared__ float sm[];
+  float* tile = sm;                 // [2][64][129]
+  float* sq = sm + 2 * CD_SLAB;     // [CD_QB][d]
+  const uint32_t c0 = blockIdx.x * 128, q0 = blockIdx.y * CD_QB, t = threadIdx.x;
+  const uint32_t lane = t & 31, w = t >> 5, ct = t & 127, qg = t >> 7;
+  const uint32_t nslab = d >> 6;
+  for (uint32_t i = t; i < CD_QB * d; i += 512) {
+    uint32_t qq = q0 + i / d;
+    sq[i] = qq < Q ? __ldg(queries + (size_t)qq * d + (i % d)) : 0.0f;
+  }
+  // slab fetch: warp w takes rows w, w+16, ... (8 rows); lanes read elements lane, lane+32 (coalesced)
+  float pre[16];
+  auto fetch = [&](uint32_t slab) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const uint32_t c = c0 + w + 16 * i;
+      const float* src = centroids + (size_t)c * d + slab * 64 + lane;
+      pre[2 * i] = c < nlist ? __ldg(src) : 0.0f;
+      pre[2 * i + 1] = c < nlist ? __ldg(src + 32) : 0.0f;
+    }
+  };
+  auto stash = [&](float* buf) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      buf[(size_t)lane * CQ_PITCH + w + 16 * i] = pre[2 * i];
+      buf[(size_t)(lane + 32) * CQ_PITCH + w + 16 * i] = pre[2 * i + 1];
+    }
+  };
+  fetch(0);
+  stash(tile);
+  __syncthreads();
+  float acc[4][16];
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[k][i] = 0.0f;
+  const float* xq = sq + (size_t)qg * 4 * d;
+#pragma unroll 1
+  for (uint32_t s = 0; s < nslab; s++) {
+    const float* buf = tile + (s & 1) * CD_SLAB;
+    if (s + 1 < nslab) fetch(s + 1);
+#pragma unroll
+    for (int i4 = 0; i4 < 4; i4++) {
+      float y[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+#pragma unroll
+        for (int r = 0; r < 4; r++) y[j][r] = buf[(size_t)(16 * j + 4 * i4 + r) * CQ_PITCH + ct];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        float pj[4][4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const float4 xv = *reinterpret_cast<const float4*>(xq + (size_t)k * d + s * 64 + 16 * j + 4 * i4);
+          pj[j][0] = __fmul_rn(xv.x, y[j][0]);
+          pj[j][1] = __fmul_rn(xv.y, y[j][1]);
+          pj[j][2] = __fmul_rn(xv.z, y[j][2]);
+          pj[j][3] = __fmul_rn(xv.w, y[j][3]);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+          acc[k][4 * i4 + r] = __fadd_rn(acc[k][4 * i4 + r],
+                                         __fadd_rn(__fadd_rn(pj[0][r], pj[1][r]), __fadd_rn(pj[2][r], pj[3][r])));
+      }
+    }
+    if (s + 1 < nslab) stash(tile + ((s + 1) & 1) * CD_SLAB);
+    __syncthreads();
+  }
+  const uint32_t c = c0 + ct;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t qq = q0 + qg * 4 + k;
+    float z8[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) z8[i] = 0.0f;
+    const float dot = __fadd_rn(__fadd_rn(reduce_sum16(acc[k]), reduce_sum8(z8)), 0.0f);
+    if (qq < Q && c < nlist) out[(size_t)qq * out_stride + c] = __fsub_rn(1.0f, dot);
+  }
+}
+
 }  // namespace lb200

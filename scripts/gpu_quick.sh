@@ -8,7 +8,7 @@ python - <<PY
 import json
 try:
     j=json.loads(open("gpurun_out/q_$w.json").read().strip().splitlines()[-1])
-    print("$w", round(j["value"]), "q/s  scan ms", round(j["roofline"]["scan_ms_per_launch"],2), "GB/s", round(j["roofline"]["achieved"]), "frac", round(j["roofline"]["frac"],3))
+    print("$w", round(j["value"]), "q/s  scan ms", round(j["roofline"]["scan_ms_per_launch"],2), "GB/s", round(j["roofline"]["achieved"]), "frac", round(j["roofline"]["frac"],3), "ms/step", round(j["ms_per_step"],2))
 except Exception as e:
     print("$w parse fail", e); print(open("gpurun_out/q_$w.err").read()[-800:])
 PY

@@ -54,7 +54,8 @@ def _ragged_index(metric, d, nlist, M, sizes, seed, keep_raw=False):
 # ---- A1/A2: find_partitions -------------------------------------------------------------
 @pytest.mark.parametrize("metric,d,nlist", [("l2", 128, 256), ("l2", 8, 33), ("l2", 16, 64), ("l2", 100, 50),
                                             ("dot", 768, 128), ("dot", 70, 20), ("cosine", 1536, 64),
-                                            ("l2", 256, 300), ("l2", 32, 5000), ("cosine", 64, 700)])
+                                            ("l2", 256, 300), ("l2", 32, 5000), ("cosine", 64, 700),
+                                            ("dot", 64, 300), ("dot", 128, 129), ("dot", 1536, 40)])
 def test_find_partitions_parity(oracle, metric, d, nlist):
     from lance_b200 import IvfPqIndex
     rng = np.random.default_rng(d + nlist)
