@@ -86,6 +86,7 @@ struct lb200_index {
   int device = 0, metric = 0;
   uint32_t dim = 0, nlist = 0, M = 0, dsub = 0;
   uint64_t N = 0, ntiles = 0, max_part = 0;
+  double avg_np = 0;  // mean rows per NON-EMPTY partition
   float *d_centroids = nullptr, *d_codebook = nullptr, *d_raw = nullptr;
   uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
   uint8_t* d_codes = nullptr;          // tile16 layout (variants 1/2), or null
@@ -156,6 +157,11 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   ix->dsub = dim / M;
   ix->N = N;
   ix->h_part_off.assign(part_offsets, part_offsets + nlist + 1);
+  {
+    uint32_t ne = 0;
+    for (uint32_t p = 0; p < nlist; p++) ne += part_offsets[p + 1] > part_offsets[p];
+    ix->avg_np = (double)N / std::max(1u, ne);
+  }
   std::vector<uint64_t> tile_off(nlist + 1);
   uint64_t t = 0;
   for (uint32_t p = 0; p < nlist; p++) {

@@ -266,6 +266,21 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
   add((size_t)Q * kprime * 4);      // exact
   add((size_t)Q * 4);               // per-query thresholds
+  // ADC tables as a pre-pass (scan3.cuh, lut_prepass_kernel): always for dot (one table per query serves all
+  // its probes), for residual metrics when a pair's table costs more than its rows (256*dsub flops per
+  // sub-vector against n_p lookups)
+  bool use_pre = false, pre_by_query = false;
+  size_t pre_units = 0;
+  if (sc.variant == 3 && (ix->dsub == 8 || ix->dsub == 16)) {
+    pre_by_query = ix->metric == LB200_DOT;
+    pre_units = pre_by_query ? (size_t)Q : npairs;
+    bool want = pre_by_query || 256.0 * ix->dsub > ix->avg_np;
+    if (const char* e = getenv("LB200_LUT_PREPASS")) want = atoi(e) != 0;
+    double cap_gb = 24.0;
+    if (const char* e = getenv("LB200_LUT_SCRATCH_GB")) cap_gb = atof(e);
+    use_pre = want && (double)pre_units * ix->M * 1024.0 <= cap_gb * 1e9 && pre_units <= 65535ull * LUTPRE_UNITS;
+  }
+  if (use_pre) { add(pre_units * ix->M * 1024); add(pre_units * 4); }
   rc = ix->arena.reserve(need);
   if (rc) return rc;
   ix->arena.reset();
@@ -291,6 +306,8 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   uint32_t* d_mcnt = ix->arena.take<uint32_t>(Q);
   float* d_exact = ix->arena.take<float>((size_t)Q * kprime);
   uint32_t* d_qthr = ix->arena.take<uint32_t>(Q);
+  float* d_lut = use_pre ? ix->arena.take<float>(pre_units * ix->M * 256) : nullptr;
+  uint32_t* d_lut_max = use_pre ? ix->arena.take<uint32_t>(pre_units) : nullptr;
 
   const bool prof = ix->profiling;
   if (prof) CK(cudaEventRecord(ix->ev[0], st));
@@ -364,11 +381,30 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
       launches++;
     }
     if (prof) CK(cudaEventRecord(ix->ev[2], st));
+    if (use_pre) {  // inside the scan's timed span: the tables are part of the scan's cost
+      CK(cudaMemsetAsync(d_lut_max, 0, pre_units * 4, st));
+      dim3 g((ix->M / 16) * 4, (uint32_t)((pre_units + LUTPRE_UNITS - 1) / LUTPRE_UNITS));
+      const uint32_t* pr = pre_by_query ? nullptr : probes;
+      if (ix->dsub == 8)
+        lut_prepass_kernel<8><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
+                                                 (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max);
+      else
+        lut_prepass_kernel<16><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
+                                                  (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max);
+      CK(cudaGetLastError());
+      launches++;
+      sp.lut_src = d_lut;
+      sp.lut_max = d_lut_max;
+      sp.lut_by_query = pre_by_query;
+    }
     // pooled bootstrap when most work items are cold: a shard (few of a query's probes are local), few
     // probes per query, or per-pair outputs (no cross-item bound at all)
     bool boot = a.shard_mode || a.per_pair_output || P < 16;
     if (const char* eb = getenv("LB200_BOOT")) boot = atoi(eb) != 0;
-    CK(launch_scan3(sc, boot, ix->sm_count, st, sp, d_item_off + nlist));
+    // pre-built tables are fetched by scan3_kernel only (scan3_nb_kernel stays the untouched text the
+    // headline was tuned on); without `boot` its bootstrap calls are switched off at run time
+    if (!boot) sp.no_boot = 1;
+    CK(launch_scan3(sc, boot || use_pre, ix->sm_count, st, sp, d_item_off + nlist));
     launches++;
   } else {
   ScanParams sp = {};

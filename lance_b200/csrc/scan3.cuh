@@ -54,6 +54,9 @@ struct Scan3Params {
   uint32_t chunk_vecs;            // rows per chunk (multiple of 32*L)
   uint32_t max_chunks;
   uint32_t capw;                  // candidate buffer entries per (warp, query slot)
+  const float* lut_src;           // ADC tables built by lut_prepass_kernel: [unit][M/16][256][16] f32, or null
+  const uint32_t* lut_max;        // [unit] largest |entry| bit pattern of the unit's table
+  int32_t lut_by_query;           // unit = query index (dot: no residual) instead of pair id
   uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
   uint32_t* const* peers;         // [n_peers] the same table on the peer GPUs (NVLink peer memory), or null
   uint32_t n_peers;
@@ -107,6 +110,114 @@ __global__ void repack_skew_kernel(const uint8_t* __restrict__ src, const uint64
 __global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// ADC tables as a pre-pass (A3 + A4 out of the scan kernel).  The scan kernel builds its tables per
+// work item, re-reading the whole codebook (M*256*dsub*4 bytes) for QL queries; when tables are
+// expensive relative to the rows they serve (small partitions, many sub-vectors) or do not depend
+// on the partition at all (dot: no residual -> one table per QUERY, not per pair), they are built
+// here instead, with each thread's codebook rows held in registers across 64 units, and the scan
+// kernel only copies them into shared memory (lut_fetch).  Same arithmetic as the in-kernel build:
+// residual = q - centroid (v2.rs:285-301), entries by lut_elem (pq/distance.rs:17-85).
+// grid.x = (M/16) * 4: 16 sub-vectors x a quarter of the 256 codes; grid.y = unit tiles.
+// Output layout per unit: [M/16][256][16] f32 == the scan kernel's table order for one query.
+constexpr uint32_t LUTPRE_UNITS = 64;
+template <int DSUB>
+__global__ void __launch_bounds__(256)
+lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ centroids,
+                   const float* __restrict__ codebook, const uint32_t* __restrict__ probes /*[Q][P]; null: by query*/,
+                   const uint64_t* __restrict__ part_off, uint32_t n_units, uint32_t P, uint32_t dim, uint32_t M,
+                   float* __restrict__ out, uint32_t* __restrict__ out_max /*[n_units], zeroed*/) {
+  constexpr int PITCH = DSUB + 4;  // floats; 8 lanes of an LDS.128 phase land on 8 distinct bank groups
+  constexpr int UB = 8;
+  __shared__ __align__(16) float xs[UB][16 * PITCH];
+  __shared__ int sval[UB];
+  const uint32_t ch = blockIdx.x >> 2, quarter = blockIdx.x & 3;
+  const uint32_t t = threadIdx.x, slot = t & 15, cq = t >> 4;
+  const uint32_t m = ch * 16 + slot;
+  const bool residual = probes != nullptr;
+  float y[4][DSUB];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t code = quarter * 64 + cq + 16 * i;
+    const float4* src = reinterpret_cast<const float4*>(codebook + ((size_t)m * 256 + code) * DSUB);
+#pragma unroll
+    for (int j = 0; j < DSUB / 4; j++) {
+      const float4 v = __ldg(src + j);
+      y[i][4 * j] = v.x; y[i][4 * j + 1] = v.y; y[i][4 * j + 2] = v.z; y[i][4 * j + 3] = v.w;
+    }
+  }
+  const uint32_t u0 = blockIdx.y * LUTPRE_UNITS, u1 = min(n_units, u0 + LUTPRE_UNITS);
+#pragma unroll 1
+  for (uint32_t ub = u0; ub < u1; ub += UB) {
+    __syncthreads();
+    for (uint32_t idx = t; idx < UB * 16 * DSUB; idx += 256) {
+      const uint32_t ui = idx / (16 * DSUB), rem = idx % (16 * DSUB), u = ub + ui;
+      float v = 0.0f;
+      if (u < u1) {
+        const uint32_t e = ch * 16 * DSUB + rem;
+        v = __ldg(queries + (size_t)(residual ? u / P : u) * dim + e);
+        if (residual) v = __fsub_rn(v, __ldg(centroids + (size_t)probes[u] * dim + e));
+      }
+      xs[ui][(rem / DSUB) * PITCH + rem % DSUB] = v;
+    }
+    if (t < UB) {
+      const uint32_t u = ub + t;
+      bool valid = u < u1;
+      if (valid && residual) {  // a shard holds all nlist partitions, most of them empty: no items, no table
+        const uint32_t part = probes[u];
+        valid = part_off[part + 1] > part_off[part];
+      }
+      sval[t] = valid;
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (uint32_t ui = 0; ui < UB; ui++) {
+      if (!sval[ui]) continue;
+      float x[DSUB];
+#pragma unroll
+      for (int j = 0; j < DSUB / 4; j++) {
+        const float4 v = *reinterpret_cast<const float4*>(&xs[ui][slot * PITCH + 4 * j]);
+        x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+      }
+      float* o = out + (size_t)(ub + ui) * M * 256 + (size_t)ch * 4096 + slot;
+      uint32_t mb = 0;
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const float v = lut_elem<DSUB>(residual, x, y[i], DSUB);
+        o[(quarter * 64 + cq + 16 * i) * 16] = v;
+        mb = max(mb, __float_as_uint(v) & 0x7fffffffu);
+      }
+      mb = __reduce_max_sync(0xffffffffu, mb);
+      if ((t & 31) == 0) atomicMax(out_max + ub + ui, mb);
+    }
+  }
+}
+
+// Copy the pre-built tables of the item's queries into the interleaved shared-memory table
+// (entry e of query q at byte (e*QL + q)*4) with 4-byte cp.async: lane -> (q = lane % QL,
+// e = base + lane / QL), so one warp instruction reads QL runs of 32/QL consecutive floats (whole
+// 32-byte sectors) and writes 128 consecutive shared bytes (conflict-free); nothing is staged in
+// registers, so every thread keeps its whole share of the table in flight at once -- the copy is
+// bandwidth- not latency-bound.  Returns the largest |entry| bit pattern of the item's tables (from
+// the pre-pass) for the exact-FMA row switch test.  Out of line: runs once per item.
+template <int QL>
+__device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const float* __restrict__ src,
+                                           const uint32_t* __restrict__ lut_max, size_t unit_stride,
+                                           const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent) {
+  constexpr uint32_t EPW = 32 / QL;
+  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const uint32_t unit = units[min(lane % QL, nq - 1)];  // unused slots replicate a valid table (never read back)
+  const float* s = src + (size_t)unit * unit_stride + lane / QL;
+  const uint32_t dst = (uint32_t)__cvta_generic_to_shared(lut) + lane * 4;
+#pragma unroll 8
+  for (uint32_t e = w * EPW; e < nent; e += nwarp * EPW)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + e * (4 * QL)), "l"(s + e) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  const uint32_t mb = lut_max[unit];
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  return mb;
 }
 
 template <int QL>
@@ -492,6 +603,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       ic.lower = p.lower; ic.upper = p.upper; ic.has_lower = p.has_lower; ic.has_upper = p.has_upper;
       *ictx = ic;
     }
+    if (!p.lut_src)
     for (uint32_t i = tid; i < QL * dim; i += NT) {
       uint32_t qq = i / dim, e = i - qq * dim;
       float val = 0.0f;
@@ -508,7 +620,9 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     // thread -> (slot = tid%16, code = tid/16 + k*NT/16): a quarter/half warp writes consecutive
     // slots of one code row -> conflict-free wide stores.
     uint32_t maxbits = 0;
-    {
+    if (p.lut_src) {
+      maxbits = lut_fetch<QL>(lut, p.lut_src, p.lut_max, (size_t)M * 256, p.lut_by_query ? sqidx : spair, nq, C16 * 4096u);
+    } else {
       const uint32_t slot = tid & 15;
 #pragma unroll 1
       for (uint32_t ch = 0; ch < C16; ch++) {

@@ -527,3 +527,36 @@ def test_sharded_search_with_shared_bounds(oracle, metric, refine, G):
     for ix in shards:
         ix.peer_thresholds_detach()
         ix.close()
+
+
+@pytest.mark.parametrize("prepass", ["0", "1"])
+@pytest.mark.parametrize("metric,d,M", [("l2", 128, 16), ("cosine", 768, 48), ("dot", 768, 48), ("cosine", 1536, 96),
+                                        ("dot", 128, 16), ("l2", 64, 4)])
+def test_table_prepass_equals_in_kernel_tables(oracle, metric, d, M, prepass, monkeypatch):
+    """ADC tables built by lut_prepass_kernel (forced on) or by the scanning CTA (forced off) give the
+    same bit-identical results as the oracle -- merged search, per-pair search and a shard with
+    empty partitions (tables of pairs without local rows are skipped)."""
+    from lance_b200 import IvfPqIndex, Query
+    monkeypatch.setenv("LB200_LUT_PREPASS", prepass)
+    sizes = [0, 300, 5, 0, 1000, 33, 2049, 0, 64, 7, 700, 4100, 9, 0, 0, 130]
+    nlist = len(sizes)
+    data = _ragged_index(metric, d, nlist, M, sizes, seed=d + M, keep_raw=True)
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    rng = np.random.default_rng(8)
+    Q = 77
+    q = rng.normal(size=(Q, d)).astype(np.float32)
+    for nprobes, refine in ((1, 0), (5, 0), (nlist, 3)):
+        rd, ri, rc, _ = o.search(q, k=7, nprobes=nprobes, refine_factor=refine)
+        gd, gi, gc = ix.search(Query(key=q, k=7, nprobes=nprobes, refine_factor=refine or None))
+        _assert_same(gd, gi, gc, rd[:, :gd.shape[1]], ri[:, :gd.shape[1]], rc, f"prepass={prepass} {metric} P={nprobes}")
+    parts = np.tile(np.arange(nlist, dtype=np.uint32), (5, 1))
+    key = q[:5] if metric != "cosine" else np.stack([oracle.normalize(x) for x in q[:5]])
+    gd, gi, gc = ix.search_in_partition(parts, key, 6)
+    for i in range(5):
+        for p in range(nlist):
+            rd1, ri1 = o.search_in_partition(p, key[i], 6)
+            n = len(rd1)
+            assert gc[i, p] == n
+            assert gi[i, p, :n].tolist() == ri1.tolist() and _bits(gd[i, p, :n]).tolist() == _bits(rd1).tolist()
+    ix.close()
