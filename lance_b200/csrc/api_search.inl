@@ -7,6 +7,7 @@ struct ScanConfig {
   uint32_t capw;
   size_t smem;
   int minb;  // variant 3: CTAs per SM the kernel is compiled for
+  int nw = 8;  // variant 3: warps per CTA
 };
 constexpr int SCAN_NW = 8;
 
@@ -99,24 +100,31 @@ static cudaError_t launch_scan(const ScanConfig& c, int grid, cudaStream_t st, c
   }
 }
 
-template <int QL, int D, int MINB, bool BOOT>
+template <int QL, int D, int NW, int MINB, int DS, bool BOOT>
+static auto scan3_entry() {
+  if constexpr (BOOT) return scan3_kernel<QL, D, NW, MINB, DS, true>;
+  else return scan3_nb_kernel<QL, D, NW, MINB, DS>;
+}
+
+template <int QL, int D, int MINB, bool BOOT, int NW = SCAN_NW>
 static cudaError_t launch_scan3_d(int dsub_t, int sm_count, size_t smem, cudaStream_t st, const Scan3Params& sp,
                                   const uint32_t* total_items) {
 #define LB200_LAUNCH3(DS)                                                                         \
   do {                                                                                            \
-    auto kern = BOOT ? scan3_kernel<QL, D, SCAN_NW, MINB, DS, true> : scan3_nb_kernel<QL, D, SCAN_NW, MINB, DS>;                                        \
+    auto kern = scan3_entry<QL, D, NW, MINB, DS, BOOT>();                                         \
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                               \
     int nb = 0;                                                                                   \
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, SCAN_NW * 32, smem);             \
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, NW * 32, smem);                  \
     if (e != cudaSuccess) return e;                                                               \
     if (nb < 1) return cudaErrorLaunchOutOfResources;                                             \
-    kern<<<sm_count * nb, SCAN_NW * 32, smem, st>>>(sp, total_items);                             \
+    kern<<<sm_count * nb, NW * 32, smem, st>>>(sp, total_items);                                  \
     return cudaGetLastError();                                                                    \
   } while (0)
   if (dsub_t == 8) LB200_LAUNCH3(8);
   if (dsub_t == 16) LB200_LAUNCH3(16);
-  LB200_LAUNCH3(0);
+  if constexpr (NW == SCAN_NW) LB200_LAUNCH3(0);
+  return cudaErrorInvalidValue;
 #undef LB200_LAUNCH3
 }
 
@@ -132,6 +140,11 @@ static cudaError_t launch_scan3_b(const ScanConfig& c, int sm_count, cudaStream_
 }
 static cudaError_t launch_scan3(const ScanConfig& c, bool boot, int sm_count, cudaStream_t st, const Scan3Params& sp,
                                 const uint32_t* total_items) {
+  if (c.nw == 16) {  // wide CTA: one CTA per SM, tables pre-built (see search_device)
+    if (c.dsub_t == 0) return cudaErrorInvalidValue;
+    if (c.ql == 4) return launch_scan3_d<4, 8, 1, true, 16>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+    return launch_scan3_d<2, 16, 1, true, 16>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
+  }
   return boot ? launch_scan3_b<true>(c, sm_count, st, sp, total_items)
               : launch_scan3_b<false>(c, sm_count, st, sp, total_items);
 }
@@ -281,6 +294,15 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     use_pre = want && (double)pre_units * ix->M * 1024.0 <= cap_gb * 1e9 && pre_units <= 65535ull * LUTPRE_UNITS;
   }
   if (use_pre) { add(pre_units * ix->M * 1024); add(pre_units * 4); }
+  // Tables that leave room for one CTA per SM only (M >= 48): with the tables pre-built the residual
+  // staging area is not needed, which makes room for the candidate buffers of 16 warps instead of 8.
+  if (use_pre && sc.minb == 1 && !getenv("LB200_NO_WIDE")) {
+    const size_t smem16 = scan3_smem_bytes(sc.ql, 16, ix->M, 0, sc.capw);
+    if (smem16 <= ix->smem_optin) {
+      sc.nw = 16;
+      sc.smem = smem16;
+    }
+  }
   rc = ix->arena.reserve(need);
   if (rc) return rc;
   ix->arena.reset();

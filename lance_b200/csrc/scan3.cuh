@@ -516,7 +516,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   unsigned char* lut = smem_raw;
   const uint32_t C16 = p.M >> 4;
   float* resid = reinterpret_cast<float*>(smem_raw + (size_t)C16 * CB);
-  uint32_t* ckey = reinterpret_cast<uint32_t*>(resid + QL * p.dim);
+  uint32_t* ckey = reinterpret_cast<uint32_t*>(resid + (p.lut_src ? 0u : QL * p.dim));  // no residuals with pre-built tables
   uint32_t* cpos = ckey + (size_t)QL * NW * p.capw;
   uint32_t* ccnt = cpos + (size_t)QL * NW * p.capw;
   float* sthrf = reinterpret_cast<float*>(ccnt + QL * NW);  // 16-byte aligned (all sizes are multiples of 16)
