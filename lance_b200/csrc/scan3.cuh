@@ -112,6 +112,63 @@ __global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
   if (i < n) p[i] = v;
 }
 
+// Packed FP32 (Blackwell FADD2/FMUL2, PTX .f32x2): two IEEE round-to-nearest operations per
+// instruction, bit-identical per half to the scalar ops.  ptxas 12.9 CONTRACTS a mul.rn.f32x2 that
+// feeds an add.rn.f32x2 into one FFMA2 (single rounding) although both carry .rn, so products are
+// always unpacked and summed first with scalar __fadd_rn; only sub, mul and add-of-sums are packed.
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t pk2(float a, float b) {
+  f32x2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ f32x2_t add2(f32x2_t a, f32x2_t b) {
+  f32x2_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2_t sub2(f32x2_t a, f32x2_t b) {
+  f32x2_t r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2_t mul2(f32x2_t a, f32x2_t b) {
+  f32x2_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// l2_once<f32x8,8> / l2_once<f32x16,16> (l2.rs:207-216) with the reduce_sum trees of simd/f32.rs,
+// on packed pairs X[i] = (x[2i], x[2i+1]).  Same operations, same order per value as dist.cuh.
+template <int DSUB>
+__device__ __forceinline__ float l2_once_packed(const f32x2_t* X, const f32x2_t* Y) {
+  float sq[DSUB];
+#pragma unroll
+  for (int i = 0; i < DSUB / 2; i++) {
+    const f32x2_t d = sub2(X[i], Y[i]);
+    upk2(mul2(d, d), sq[2 * i], sq[2 * i + 1]);
+  }
+  if (DSUB == 16) {
+    float y8[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) y8[i] = __fadd_rn(sq[i], sq[i + 8]);       // reduce_sum16: halves first
+    const f32x2_t a01 = add2(pk2(y8[0], y8[1]), pk2(y8[4], y8[5]));        // reduce_sum8: (a0, a1)
+    const f32x2_t a23 = add2(pk2(y8[2], y8[3]), pk2(y8[6], y8[7]));        //              (a2, a3)
+    float lo, hi;
+    upk2(add2(a01, a23), lo, hi);                                           // (a0+a2, a1+a3)
+    return __fadd_rn(lo, hi);
+  } else {
+    float a[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) a[i] = __fadd_rn(sq[i], sq[i + 4]);
+    float lo, hi;
+    upk2(add2(pk2(a[0], a[1]), pk2(a[2], a[3])), lo, hi);
+    return __fadd_rn(lo, hi);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // ADC tables as a pre-pass (A3 + A4 out of the scan kernel).  The scan kernel builds its tables per
 // work item, re-reading the whole codebook (M*256*dsub*4 bytes) for QL queries; when tables are
@@ -183,9 +240,20 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
       }
       float* o = out + (size_t)(ub + ui) * M * 256 + (size_t)ch * 4096 + slot;
       uint32_t mb = 0;
+      f32x2_t X[DSUB / 2];
+#pragma unroll
+      for (int j = 0; j < DSUB / 2; j++) X[j] = pk2(x[2 * j], x[2 * j + 1]);
 #pragma unroll
       for (int i = 0; i < 4; i++) {
-        const float v = lut_elem<DSUB>(residual, x, y[i], DSUB);
+        float v;
+        if (residual) {
+          f32x2_t Y[DSUB / 2];
+#pragma unroll
+          for (int j = 0; j < DSUB / 2; j++) Y[j] = pk2(y[i][2 * j], y[i][2 * j + 1]);
+          v = l2_once_packed<DSUB>(X, Y);
+        } else {
+          v = lut_elem<DSUB>(false, x, y[i], DSUB);
+        }
         o[(quarter * 64 + cq + 16 * i) * 16] = v;
         mb = max(mb, __float_as_uint(v) & 0x7fffffffu);
       }
