@@ -283,6 +283,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=os.environ.get("LB200_WORKLOAD", "cfg4"), choices=sorted(WORKLOADS) + ["cfg2"])
     ap.add_argument("--scan-variant", type=int, default=0)
+    ap.add_argument("--queries", type=int, default=0,
+                    help="override the workload's queries per step (batch-size sweep of BASELINE configs[4])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard-of", type=int, default=0,
                     help="diagnostic: single process holding rank 0's shard of an N-way partition split")
@@ -295,6 +297,9 @@ def main():
         run_flat(args)
         return
     wl = WORKLOADS[args.workload]
+    if args.queries:
+        wl = wl[:8] + (args.queries, wl[9].replace("%d queries" % wl[8], "%d queries" % args.queries)
+                       .replace("10k queries", "%d queries" % args.queries))
     if args.impl == "reference":
         run_reference(args, wl)
         return

@@ -176,13 +176,13 @@ static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint3
   dim3 grid((ix->nlist + COARSE_THREADS - 1) / COARSE_THREADS, (Q + COARSE_TQ - 1) / COARSE_TQ);
   size_t smem = (size_t)COARSE_TQ * ix->dim * 4;
   const size_t tsm = ((size_t)ix->dim * CQ_PITCH + (size_t)CQ_QB * ix->dim) * 4;
-  if (ix->metric != LB200_DOT && ix->dim % 16 == 0 && ix->dim >= 32 && tsm <= ix->smem_optin && Q >= 8 &&
+  if (ix->metric != LB200_DOT && ix->dim % 16 == 0 && ix->dim >= 32 && tsm <= ix->smem_optin &&
       !getenv("LB200_COARSE_SIMPLE")) {
     CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
     dim3 g2((ix->nlist + 127) / 128, (Q + CQ_QB - 1) / CQ_QB);
     coarse_dist_l2_tiled_kernel<<<g2, 128, tsm, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D, ix->nlist,
                                                       nullptr);
-  } else if (ix->metric == LB200_DOT && ix->dim % 64 == 0 && Q >= 8 &&
+  } else if (ix->metric == LB200_DOT && ix->dim % 64 == 0 &&
              (2 * (size_t)CD_SLAB + (size_t)CD_QB * ix->dim) * 4 <= ix->smem_optin && !getenv("LB200_COARSE_SIMPLE")) {
     const size_t dsm = (2 * (size_t)CD_SLAB + (size_t)CD_QB * ix->dim) * 4;
     CK(cudaFuncSetAttribute(coarse_dist_dot_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsm));
@@ -405,7 +405,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     if (prof) CK(cudaEventRecord(ix->ev[2], st));
     if (use_pre) {  // inside the scan's timed span: the tables are part of the scan's cost
       CK(cudaMemsetAsync(d_lut_max, 0, pre_units * 4, st));
-      dim3 g((ix->M / 16) * 4, (uint32_t)((pre_units + LUTPRE_UNITS - 1) / LUTPRE_UNITS));
+      dim3 g((ix->M / 16) * LUTPRE_SPLIT, (uint32_t)((pre_units + LUTPRE_UNITS - 1) / LUTPRE_UNITS));
       const uint32_t* pr = pre_by_query ? nullptr : probes;
       if (ix->dsub == 8)
         lut_prepass_kernel<8><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,

@@ -55,7 +55,7 @@ struct Scan3Params {
   uint32_t max_chunks;
   uint32_t capw;                  // candidate buffer entries per (warp, query slot)
   const float* lut_src;           // ADC tables built by lut_prepass_kernel: [unit][M/16][256][16] f32, or null
-  const uint32_t* lut_max;        // [unit] largest |entry| bit pattern of the unit's table
+  const uint32_t* lut_max;        // [unit] 0, or the largest |entry| bit pattern if some entry is >= 2^118
   int32_t lut_by_query;           // unit = query index (dot: no residual) instead of pair id
   uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
   uint32_t* const* peers;         // [n_peers] the same table on the peer GPUs (NVLink peer memory), or null
@@ -177,9 +177,11 @@ __device__ __forceinline__ float l2_once_packed(const f32x2_t* X, const f32x2_t*
 // here instead, with each thread's codebook rows held in registers across 64 units, and the scan
 // kernel only copies them into shared memory (lut_fetch).  Same arithmetic as the in-kernel build:
 // residual = q - centroid (v2.rs:285-301), entries by lut_elem (pq/distance.rs:17-85).
-// grid.x = (M/16) * 4: 16 sub-vectors x a quarter of the 256 codes; grid.y = unit tiles.
+// grid.x = (M/16) * LUTPRE_SPLIT: 16 sub-vectors x a slice of the 256 codes; grid.y = unit tiles.
 // Output layout per unit: [M/16][256][16] f32 == the scan kernel's table order for one query.
 constexpr uint32_t LUTPRE_UNITS = 64;
+constexpr int LUTPRE_CPT = 2;                              // codes per thread
+constexpr uint32_t LUTPRE_SPLIT = 256 / (16 * LUTPRE_CPT);  // blocks per 16-sub-vector chunk
 template <int DSUB>
 __global__ void __launch_bounds__(256)
 lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ centroids,
@@ -187,17 +189,29 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
                    const uint64_t* __restrict__ part_off, uint32_t n_units, uint32_t P, uint32_t dim, uint32_t M,
                    float* __restrict__ out, uint32_t* __restrict__ out_max /*[n_units], zeroed*/) {
   constexpr int PITCH = DSUB + 4;  // floats; 8 lanes of an LDS.128 phase land on 8 distinct bank groups
-  constexpr int UB = 8;
+  constexpr int UB = 16;           // units staged at a time
   __shared__ __align__(16) float xs[UB][16 * PITCH];
-  __shared__ int sval[UB];
-  const uint32_t ch = blockIdx.x >> 2, quarter = blockIdx.x & 3;
+  __shared__ uint32_t spart[LUTPRE_UNITS];  // partition of each unit of the tile; 0xffffffff: no table needed
+  const uint32_t ch = blockIdx.x / LUTPRE_SPLIT, quarter = blockIdx.x % LUTPRE_SPLIT;
   const uint32_t t = threadIdx.x, slot = t & 15, cq = t >> 4;
   const uint32_t m = ch * 16 + slot;
   const bool residual = probes != nullptr;
-  float y[4][DSUB];
+  const uint32_t u0 = blockIdx.y * LUTPRE_UNITS, u1 = min(n_units, u0 + LUTPRE_UNITS);
+  if (t < LUTPRE_UNITS) {
+    uint32_t part = 0xffffffffu;
+    if (u0 + t < u1) {
+      part = 0;
+      if (residual) {  // a shard holds all nlist partitions, most of them empty: no items, no table
+        part = probes[u0 + t];
+        if (part_off[part + 1] == part_off[part]) part = 0xffffffffu;
+      }
+    }
+    spart[t] = part;
+  }
+  float y[LUTPRE_CPT][DSUB];
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const uint32_t code = quarter * 64 + cq + 16 * i;
+  for (int i = 0; i < LUTPRE_CPT; i++) {
+    const uint32_t code = quarter * (16 * LUTPRE_CPT) + cq + 16 * i;
     const float4* src = reinterpret_cast<const float4*>(codebook + ((size_t)m * 256 + code) * DSUB);
 #pragma unroll
     for (int j = 0; j < DSUB / 4; j++) {
@@ -205,33 +219,26 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
       y[i][4 * j] = v.x; y[i][4 * j + 1] = v.y; y[i][4 * j + 2] = v.z; y[i][4 * j + 3] = v.w;
     }
   }
-  const uint32_t u0 = blockIdx.y * LUTPRE_UNITS, u1 = min(n_units, u0 + LUTPRE_UNITS);
 #pragma unroll 1
   for (uint32_t ub = u0; ub < u1; ub += UB) {
     __syncthreads();
+    // stage the residual (or query) chunk of UB units: all loads of a thread are independent
+#pragma unroll
     for (uint32_t idx = t; idx < UB * 16 * DSUB; idx += 256) {
       const uint32_t ui = idx / (16 * DSUB), rem = idx % (16 * DSUB), u = ub + ui;
+      const uint32_t part = u < u1 ? spart[u - u0] : 0xffffffffu;
       float v = 0.0f;
-      if (u < u1) {
+      if (part != 0xffffffffu) {
         const uint32_t e = ch * 16 * DSUB + rem;
         v = __ldg(queries + (size_t)(residual ? u / P : u) * dim + e);
-        if (residual) v = __fsub_rn(v, __ldg(centroids + (size_t)probes[u] * dim + e));
+        if (residual) v = __fsub_rn(v, __ldg(centroids + (size_t)part * dim + e));
       }
       xs[ui][(rem / DSUB) * PITCH + rem % DSUB] = v;
     }
-    if (t < UB) {
-      const uint32_t u = ub + t;
-      bool valid = u < u1;
-      if (valid && residual) {  // a shard holds all nlist partitions, most of them empty: no items, no table
-        const uint32_t part = probes[u];
-        valid = part_off[part + 1] > part_off[part];
-      }
-      sval[t] = valid;
-    }
     __syncthreads();
-#pragma unroll 1
+#pragma unroll 2
     for (uint32_t ui = 0; ui < UB; ui++) {
-      if (!sval[ui]) continue;
+      if (ub + ui >= u1 || spart[ub + ui - u0] == 0xffffffffu) continue;
       float x[DSUB];
 #pragma unroll
       for (int j = 0; j < DSUB / 4; j++) {
@@ -244,7 +251,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
 #pragma unroll
       for (int j = 0; j < DSUB / 2; j++) X[j] = pk2(x[2 * j], x[2 * j + 1]);
 #pragma unroll
-      for (int i = 0; i < 4; i++) {
+      for (int i = 0; i < LUTPRE_CPT; i++) {
         float v;
         if (residual) {
           f32x2_t Y[DSUB / 2];
@@ -254,11 +261,11 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
         } else {
           v = lut_elem<DSUB>(false, x, y[i], DSUB);
         }
-        o[(quarter * 64 + cq + 16 * i) * 16] = v;
+        o[(quarter * (16 * LUTPRE_CPT) + cq + 16 * i) * 16] = v;
         mb = max(mb, __float_as_uint(v) & 0x7fffffffu);
       }
-      mb = __reduce_max_sync(0xffffffffu, mb);
-      if ((t & 31) == 0) atomicMax(out_max + ub + ui, mb);
+      // only magnitudes that rule out the exact-FMA row switch (>= 2^118) are recorded: (almost) never
+      if (mb >= 0x7a800000u) atomicMax(out_max + ub + ui, mb);
     }
   }
 }
