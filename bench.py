@@ -449,7 +449,18 @@ def main():
     my_scan_ms = float(np.mean(scan_ms))
     my_bytes = float(np.mean(scan_bytes))
     achieved = my_bytes / (my_scan_ms * 1e-3) / 1e9 if my_scan_ms > 0 else 0.0
-    kname = "scan3_kernel" if st["scan_variant"] == 3 else "scan_kernel"
+    # which instantiation ran (the library's rule, api_search.inl): pre-built tables or mostly-cold items
+    # (shards, few probes) -> scan3_kernel; otherwise the call-free scan3_nb_kernel
+    avg_np = float(np.mean(sizes[sizes > 0])) if len(sizes) else 0.0
+    pre = metric == "dot" or 256.0 * (d // M) > avg_np
+    if os.environ.get("LB200_LUT_PREPASS"):
+        pre = os.environ["LB200_LUT_PREPASS"] != "0"
+    pre = pre and (d // M) in (8, 16)
+    kname = "scan_kernel"
+    if st["scan_variant"] == 3:
+        kname = "scan3_kernel" if (shard_mode or nprobes < 16 or pre) else "scan3_nb_kernel"
+        if pre:
+            kname += " + lut_prepass_kernel"
     traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_scan_traffic.json")
     if os.path.exists(tpath):

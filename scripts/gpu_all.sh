@@ -16,4 +16,5 @@ except Exception as e:
     print("$w parse fail", e); print(open("gpurun_out/bench_$w.err").read()[-1500:])
 PY
 done
+timeout 600 python bench.py --workload cfg2 --steps 5 --warmup 3 > gpurun_out/bench_cfg2.json 2> gpurun_out/bench_cfg2.err; echo "cfg2 exit $?"; cut -c1-300 gpurun_out/bench_cfg2.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref exit $?"; cut -c1-400 gpurun_out/bench_ref.json
