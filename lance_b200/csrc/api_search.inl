@@ -222,9 +222,34 @@ static int launch_merge(const float* in_dist, const uint64_t* in_rowid, const ui
     CK(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   merge_lists_kernel<<<groups, 256, smem, st>>>(in_dist, in_rowid, in_pos, in_aux, in_cnt, L, stride, group_stride,
                                                 list_stride, cnt_gs, cnt_ls, np2, kout, out_stride, out_dist,
-                                                out_rowid, out_pos, out_aux, out_cnt);
+                                                out_rowid, out_pos, out_aux, out_cnt, 1, L);
   CK(cudaGetLastError());
   return 0;
+}
+
+// Lists per slice of the first level of a two-level merge, or 0 when one level is enough.
+static uint32_t merge_slice_lists(uint64_t L, uint32_t stride) {
+  return L * stride > 16384 ? std::max(1u, 16384u / stride) : 0u;
+}
+// Two-level merge for L*stride > 16384 candidates per group (many probes x large k'): slices of F lists
+// are merged to `stride` survivors each into t_* ([groups][slices][stride]), then the slices are merged.
+// The survivors of a slice are its exact top-`stride` by (distance, row id), so the result is the same.
+static int launch_merge2(const float* in_dist, const uint64_t* in_rowid, const uint64_t* in_pos,
+                         const uint32_t* in_cnt, uint32_t groups, uint32_t L, uint32_t stride, float* t_dist,
+                         uint64_t* t_rowid, uint64_t* t_pos, uint32_t* t_cnt, float* out_dist, uint64_t* out_rowid,
+                         uint64_t* out_pos, uint32_t* out_cnt, cudaStream_t st) {
+  const uint32_t F = merge_slice_lists(L, stride), S = (L + F - 1) / F;
+  if ((uint64_t)S * stride > 16384)
+    return set_err(LB200_EUNSUPPORTED, "merge of %u lists of %u per query exceeds two merge levels", L, stride);
+  uint32_t np2 = std::max(2u, next_pow2(F * stride));
+  size_t smem = (size_t)np2 * 8;
+  CK(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)));
+  merge_lists_kernel<<<groups * S, 256, smem, st>>>(in_dist, in_rowid, in_pos, nullptr, in_cnt, F, stride,
+                                                    (size_t)L * stride, stride, L, 1, np2, stride, stride, t_dist,
+                                                    t_rowid, t_pos, nullptr, t_cnt, S, L);
+  CK(cudaGetLastError());
+  return launch_merge(t_dist, t_rowid, t_pos, nullptr, t_cnt, groups, S, stride, (size_t)S * stride, stride, S, 1,
+                      stride, stride, out_dist, out_rowid, out_pos, nullptr, out_cnt, st);
 }
 
 // The whole device pipeline for one batch of queries; asynchronous on `st`.
@@ -255,6 +280,12 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     cv = std::max<uint64_t>(2048, (cv + 511) / 512 * 512);
     chunk_vecs = (uint32_t)std::min<uint64_t>(chunk_vecs, cv);
   }
+  {
+    // the per-query merge sorts at most 16384 candidates: P * chunks * k' must stay below that
+    const uint64_t allowed = std::max<uint64_t>(1, 16384ull / ((uint64_t)P * kprime));
+    const uint64_t cv_min = (ix->max_part + allowed - 1) / allowed;
+    if (chunk_vecs < cv_min) chunk_vecs = (uint32_t)((cv_min + 15) / 16 * 16);
+  }
   if (sc.variant == 3) {  // chunks are whole superblocks
     const uint32_t sbr = 32 * ix->skew_L;
     chunk_vecs = (chunk_vecs + sbr - 1) / sbr * sbr;
@@ -279,6 +310,9 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
   add((size_t)Q * kprime * 4);      // exact
   add((size_t)Q * 4);               // per-query thresholds
+  const uint32_t mslice = a.per_pair_output ? 0 : merge_slice_lists((uint64_t)P * max_chunks, kprime);
+  const uint32_t mslices = mslice ? (P * max_chunks + mslice - 1) / mslice : 0;
+  if (mslice) { add((size_t)Q * mslices * kprime * 4); add((size_t)Q * mslices * kprime * 8); add((size_t)Q * mslices * kprime * 8); add((size_t)Q * mslices * 4); }
   // ADC tables as a pre-pass (scan3.cuh, lut_prepass_kernel): always for dot (one table per query serves all
   // its probes), for residual metrics when a pair's table costs more than its rows (256*dsub flops per
   // sub-vector against n_p lookups)
@@ -328,6 +362,10 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   uint32_t* d_mcnt = ix->arena.take<uint32_t>(Q);
   float* d_exact = ix->arena.take<float>((size_t)Q * kprime);
   uint32_t* d_qthr = ix->arena.take<uint32_t>(Q);
+  float* t_mdist = mslice ? ix->arena.take<float>((size_t)Q * mslices * kprime) : nullptr;
+  uint64_t* t_mrow = mslice ? ix->arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
+  uint64_t* t_mpos = mslice ? ix->arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
+  uint32_t* t_mcnt = mslice ? ix->arena.take<uint32_t>((size_t)Q * mslices) : nullptr;
   float* d_lut = use_pre ? ix->arena.take<float>(pre_units * ix->M * 256) : nullptr;
   uint32_t* d_lut_max = use_pre ? ix->arena.take<uint32_t>(pre_units) : nullptr;
 
@@ -456,6 +494,12 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   } else {
     const uint32_t L = P * max_chunks;
     const bool direct = !refine && !a.shard_mode;  // merged list is the final answer
+    if (mslice) {
+      rc = launch_merge2(d_sdist, d_srow, d_spos, d_scnt, Q, L, kprime, t_mdist, t_mrow, t_mpos, t_mcnt,
+                         direct ? a.d_out_dist : d_mdist, direct ? a.d_out_rowid : d_mrow, d_mpos,
+                         direct ? a.d_out_count : d_mcnt, st);
+      launches++;
+    } else
     rc = launch_merge(d_sdist, d_srow, d_spos, nullptr, d_scnt, Q, L, kprime, (size_t)L * kprime, kprime, L, 1,
                       kprime, kprime, direct ? a.d_out_dist : d_mdist, direct ? a.d_out_rowid : d_mrow, d_mpos,
                       nullptr, direct ? a.d_out_count : d_mcnt, st);

@@ -157,11 +157,20 @@ merge_lists_kernel(const float* __restrict__ in_dist, const uint64_t* __restrict
                    size_t group_stride, size_t list_stride, size_t cnt_gs, size_t cnt_ls,
                    uint32_t npow2, uint32_t kout, uint32_t out_stride, float* __restrict__ out_dist,
                    uint64_t* __restrict__ out_rowid, uint64_t* __restrict__ out_pos /*or null*/,
-                   float* __restrict__ out_aux /*or null*/, uint32_t* __restrict__ out_cnt) {
+                   float* __restrict__ out_aux /*or null*/, uint32_t* __restrict__ out_cnt,
+                   uint32_t sub_groups, uint32_t lists_total) {
   extern __shared__ unsigned long long sk[];
   __shared__ uint32_t s_n;
   const uint32_t g = blockIdx.x;
-  const size_t base = (size_t)g * group_stride;
+  // sub_groups > 1 (first level of a two-level merge): block g = (group g / sub_groups, slice g % sub_groups)
+  // merges lists [slice*L, min(lists_total, slice*L + L)) of its group
+  size_t base = (size_t)g * group_stride, cbase = (size_t)g * cnt_gs;
+  if (sub_groups > 1) {
+    const uint32_t gg = g / sub_groups, sl = g - gg * sub_groups;
+    base = (size_t)gg * group_stride + (size_t)sl * L * list_stride;
+    cbase = (size_t)gg * cnt_gs + (size_t)sl * L * cnt_ls;
+    L = min(L, lists_total - sl * L);
+  }
   if (threadIdx.x == 0) s_n = 0;
   __syncthreads();
   // the low word of a sort key is the entry's offset from `base` (must fit 32 bits).
@@ -169,7 +178,7 @@ merge_lists_kernel(const float* __restrict__ in_dist, const uint64_t* __restrict
   // threshold has tightened), so the bitonic network runs on next_pow2(valid), not on L*stride.
   for (uint32_t i = threadIdx.x; i < L * stride; i += blockDim.x) {
     uint32_t l = i / stride, r = i - l * stride;
-    if (r < in_cnt[(size_t)g * cnt_gs + (size_t)l * cnt_ls]) {
+    if (r < in_cnt[cbase + (size_t)l * cnt_ls]) {
       size_t off = (size_t)l * list_stride + r;
       sk[atomicAdd(&s_n, 1u)] = ((unsigned long long)ordered_key(in_dist[base + off]) << 32) | (uint32_t)off;
     }

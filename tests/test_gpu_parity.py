@@ -560,3 +560,35 @@ def test_table_prepass_equals_in_kernel_tables(oracle, metric, d, M, prepass, mo
             assert gc[i, p] == n
             assert gi[i, p, :n].tolist() == ri1.tolist() and _bits(gd[i, p, :n]).tolist() == _bits(rd1).tolist()
     ix.close()
+
+
+@pytest.mark.parametrize("Q", [1, 3])
+def test_single_query_on_large_partitions(oracle, Q):
+    """Tiny batches cut large partitions into chunks to fill the GPU; the number of chunks must
+    respect the merge capacity (P * chunks * k' <= 16384) -- a one-query search with k = 100 over
+    50k-row partitions used to fail with LB200_EUNSUPPORTED."""
+    from lance_b200 import IvfPqIndex, Query
+    data = random_index(400_000, 128, 8, 16, "l2", seed=11)
+    q = queries_near_centroids(data, Q, seed=12)
+    rd, ri, rc, _ = oracle.OracleIndex(data).search(q, k=100, nprobes=8)
+    ix = IvfPqIndex(data)
+    gd, gi, gc = ix.search(Query(key=q, k=100, nprobes=8))
+    _assert_same(gd, gi, gc, rd[:, :100], ri[:, :100], rc, f"single query Q={Q}")
+    ix.close()
+
+
+def test_many_probes_large_k_two_level_merge(oracle):
+    """nprobes * k' > 16384 candidates per query (64 probes x k' = 300): the per-query merge runs in
+    two levels; result identical to the oracle's single sort."""
+    from lance_b200 import IvfPqIndex, Query
+    rng = np.random.default_rng(21)
+    vecs = rng.normal(size=(30000, 64)).astype(np.float32)
+    data = build_ivf_pq(vecs, "l2", 64, 16, seed=3, keep_raw=True, ivf_iters=3, pq_iters=2, sample=4096)
+    q = vecs[rng.integers(0, len(vecs), 9)] + 0.05 * rng.normal(size=(9, 64)).astype(np.float32)
+    o = oracle.OracleIndex(data)
+    ix = IvfPqIndex(data)
+    for k, refine in ((100, 3), (300, 0)):
+        rd, ri, rc, _ = o.search(q, k=k, nprobes=64, refine_factor=refine)
+        gd, gi, gc = ix.search(Query(key=q, k=k, nprobes=64, refine_factor=refine or None))
+        _assert_same(gd, gi, gc, rd[:, :gd.shape[1]], ri[:, :gd.shape[1]], rc, f"two-level merge k={k} refine={refine}")
+    ix.close()
