@@ -220,7 +220,9 @@ static int launch_merge(const float* in_dist, const uint64_t* in_rowid, const ui
   size_t smem = (size_t)np2 * 8;
   if (smem > 48 * 1024)
     CK(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  merge_lists_kernel<<<groups, 256, smem, st>>>(in_dist, in_rowid, in_pos, in_aux, in_cnt, L, stride, group_stride,
+  // few groups with many candidates (tiny batches of chunked partitions): a wide block per group
+  const uint32_t mthreads = tot > 2048 ? 1024 : 256;
+  merge_lists_kernel<<<groups, mthreads, smem, st>>>(in_dist, in_rowid, in_pos, in_aux, in_cnt, L, stride, group_stride,
                                                 list_stride, cnt_gs, cnt_ls, np2, kout, out_stride, out_dist,
                                                 out_rowid, out_pos, out_aux, out_cnt, 1, L);
   CK(cudaGetLastError());
@@ -244,7 +246,7 @@ static int launch_merge2(const float* in_dist, const uint64_t* in_rowid, const u
   uint32_t np2 = std::max(2u, next_pow2(F * stride));
   size_t smem = (size_t)np2 * 8;
   CK(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)));
-  merge_lists_kernel<<<groups * S, 256, smem, st>>>(in_dist, in_rowid, in_pos, nullptr, in_cnt, F, stride,
+  merge_lists_kernel<<<groups * S, 1024, smem, st>>>(in_dist, in_rowid, in_pos, nullptr, in_cnt, F, stride,
                                                     (size_t)L * stride, stride, L, 1, np2, stride, stride, t_dist,
                                                     t_rowid, t_pos, nullptr, t_cnt, S, L);
   CK(cudaGetLastError());

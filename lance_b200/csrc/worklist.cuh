@@ -150,7 +150,7 @@ __device__ __forceinline__ bool merge_less(unsigned long long a, unsigned long l
 
 // Addressing: entry r of list l of group g lives at g*group_stride + l*list_stride + r;
 // its count at g*cnt_gs + l*cnt_ls (covers both [group][list][r] and [list][group][r] inputs).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 merge_lists_kernel(const float* __restrict__ in_dist, const uint64_t* __restrict__ in_rowid,
                    const uint64_t* __restrict__ in_pos /*or null*/, const float* __restrict__ in_aux /*or null*/,
                    const uint32_t* __restrict__ in_cnt, uint32_t L, uint32_t stride,
