@@ -282,6 +282,10 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     cv = std::max<uint64_t>(2048, (cv + 511) / 512 * 512);
     chunk_vecs = (uint32_t)std::min<uint64_t>(chunk_vecs, cv);
   }
+  if (const char* e = getenv("LB200_CHUNK_ROWS")) {  // experiment: bound the rows of one work item
+    const uint32_t cr = (uint32_t)atoi(e);
+    if (cr >= 512) chunk_vecs = std::min(chunk_vecs, cr);
+  }
   {
     // the per-query merge sorts at most 16384 candidates: P * chunks * k' must stay below that
     const uint64_t allowed = std::max<uint64_t>(1, 16384ull / ((uint64_t)P * kprime));
