@@ -367,8 +367,7 @@ def main():
     def e2e_step():
         if not shard_mode:
             return e2e_host_abi_step()
-        d_q.copy_(h_q, non_blocking=True)
-        device_step()
+        sh.search_host(h_q, stream)
         if rank == 0:
             src = (f_od, f_oi, f_oc) if shard_mode else (d_od, d_oi, d_oc)
             h_od.copy_(src[0], non_blocking=True)
@@ -485,10 +484,10 @@ def main():
                      "algorithmic_bytes_per_launch": my_bytes,
                      "note": "algorithmic bytes = sum over (query,partition) pairs of n_p*M code bytes; QL queries "
                              "share each code load, so the figure can exceed DRAM traffic (SURVEY 8d)"},
-        "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": int(h_q.numel() * 4) * world,
+        "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": int(h_q.numel() * 4),
                 "d2h_bytes_per_step": int(h_od.numel() * 4 + h_oi.numel() * 8 + h_oc.numel() * 4),
                 "ms_per_step": ms_e2e / e2e_steps,
-                "path": "torch pinned copies + lb200_search_device + NCCL all_gather + merge" if shard_mode else
+                "path": "per-rank pinned H2D of Q/N queries + NCCL all_gather of queries + sharded search + NCCL all_gather + merge, D2H on rank 0" if shard_mode else
                         "lb200_search (host-pointer C ABI, pinned host buffers, blocking; host wall clock)"},
         "gpu_launches": int(launches),
         "clocks": clocks,

@@ -92,6 +92,8 @@ class ShardedIvfPq:
         self.fd = torch.empty((Q, k), dtype=torch.float32, device=dev)
         self.fi = torch.empty((Q, k), dtype=torch.int64, device=dev)
         self.fc = torch.empty((Q,), dtype=torch.int32, device=dev)
+        self.l_q = torch.zeros((self.qs, self.ix.dim), dtype=torch.float32, device=dev)
+        self.g_q = torch.zeros((G * self.qs, self.ix.dim), dtype=torch.float32, device=dev)
         self._share_bounds(Q)
 
     def _share_bounds(self, Q):
@@ -111,6 +113,17 @@ class ShardedIvfPq:
         self.ix.peer_thresholds_attach(G, self.rank, handles=handles)
         self.dist.barrier()  # every table exists and is cleared before anyone's first batch publishes
         self.shared_bounds = True
+
+    def search_host(self, h_queries, stream):
+        """End-to-end entry: h_queries = pinned host f32 tensor [Q][dim], the same on every rank.  Each rank
+        copies only ITS Q/G slice over PCIe and the slices are all-gathered over NVLink (every rank needs
+        every query for the tables of its pairs), then search_device."""
+        lo = min(self.rank * self.qs, self.Q)
+        n = min(self.qs, self.Q - lo)
+        if n > 0:
+            self.l_q[:n].copy_(h_queries[lo:lo + n], non_blocking=True)
+        self.dist.all_gather_into_tensor(self.g_q, self.l_q)
+        return self.search_device(self.g_q[:self.Q], stream)
 
     def search_device(self, d_queries, stream):
         """d_queries: CUDA f32 tensor [Q][dim].  Everything is ordered on `stream` (which must be
