@@ -19,6 +19,15 @@ static int flat_dist_launch(int metric, const float* d_q, uint32_t Q, const floa
   int dev = 0, optin = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const size_t ssm2 = (2 * (size_t)CD_SLAB + (size_t)CD_QB * dim) * 4;
+  if (metric == LB200_L2 && dim % 64 == 0 && ssm2 <= (size_t)optin && Q >= 4 && !getenv("LB200_COARSE_SIMPLE") &&
+      !getenv("LB200_COARSE_TILED")) {
+    CK(cudaFuncSetAttribute(coarse_dist_l2_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm2));
+    dim3 g2((uint32_t)((n + 127) / 128), (Q + CD_QB - 1) / CD_QB);
+    coarse_dist_l2_slab_kernel<<<g2, 512, ssm2, st>>>(d_q, d_v, Q, (uint32_t)n, dim, d_out, out_stride, d_valid);
+    CK(cudaGetLastError());
+    return 0;
+  }
   if (metric == LB200_L2 && dim % 16 == 0 && dim >= 32 && tsm <= (size_t)optin && Q >= 8 && !getenv("LB200_COARSE_SIMPLE")) {
     CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
     dim3 g2((uint32_t)((n + 127) / 128), (Q + CQ_QB - 1) / CQ_QB);

@@ -176,7 +176,14 @@ static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint3
   dim3 grid((ix->nlist + COARSE_THREADS - 1) / COARSE_THREADS, (Q + COARSE_TQ - 1) / COARSE_TQ);
   size_t smem = (size_t)COARSE_TQ * ix->dim * 4;
   const size_t tsm = ((size_t)ix->dim * CQ_PITCH + (size_t)CQ_QB * ix->dim) * 4;
-  if (ix->metric != LB200_DOT && ix->dim % 16 == 0 && ix->dim >= 32 && tsm <= ix->smem_optin &&
+  const size_t ssm2 = (2 * (size_t)CD_SLAB + (size_t)CD_QB * ix->dim) * 4;
+  if (ix->metric != LB200_DOT && ix->dim % 64 == 0 && ssm2 <= ix->smem_optin && !getenv("LB200_COARSE_SIMPLE") &&
+      !getenv("LB200_COARSE_TILED")) {
+    CK(cudaFuncSetAttribute(coarse_dist_l2_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm2));
+    dim3 g2((ix->nlist + 127) / 128, (Q + CD_QB - 1) / CD_QB);
+    coarse_dist_l2_slab_kernel<<<g2, 512, ssm2, st>>>(d_keys, ix->d_centroids, Q, ix->nlist, ix->dim, d_D, ix->nlist,
+                                                      nullptr);
+  } else if (ix->metric != LB200_DOT && ix->dim % 16 == 0 && ix->dim >= 32 && tsm <= ix->smem_optin &&
       !getenv("LB200_COARSE_SIMPLE")) {
     CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
     dim3 g2((ix->nlist + 127) / 128, (Q + CQ_QB - 1) / CQ_QB);

@@ -386,4 +386,89 @@ coarse_dist_dot_slab_kernel(const float* __restrict__ queries, const float* __re
   }
 }
 
+// The same slab pipeline for L2 (l2_scalar<16>, l2.rs:65-99; d % 64 == 0): 16 lane accumulators per
+// (query, row), 16-element chunks in ascending order, lanes summed 0..15, then 0 + t -- the operation
+// order of coarse_dist_l2_tiled_kernel, with 16 warps per CTA sharing each staged slab instead of 4
+// (the whole-row tile of that kernel leaves room for only 8 warps per SM).  Serves the coarse step and
+// the flat kNN distances (validity = Arrow bitmap or null; null rows yield NaN).
+__global__ void __launch_bounds__(512, 1)
+coarse_dist_l2_slab_kernel(const float* __restrict__ queries, const float* __restrict__ rows, uint32_t Q,
+                           uint32_t n, uint32_t d, float* __restrict__ out, size_t out_stride,
+                           const uint8_t* __restrict__ validity) {
+  extern __shared__ float sm[];
+  float* tile = sm;                 // [2][64][129]
+  float* sq = sm + 2 * CD_SLAB;     // [CD_QB][d]
+  const uint32_t c0 = blockIdx.x * 128, q0 = blockIdx.y * CD_QB, t = threadIdx.x;
+  const uint32_t lane = t & 31, w = t >> 5, ct = t & 127, qg = t >> 7;
+  const uint32_t nslab = d >> 6;
+  for (uint32_t i = t; i < CD_QB * d; i += 512) {
+    uint32_t qq = q0 + i / d;
+    sq[i] = qq < Q ? __ldg(queries + (size_t)qq * d + (i % d)) : 0.0f;
+  }
+  float pre[16];
+  auto fetch = [&](uint32_t slab) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const uint32_t c = c0 + w + 16 * i;
+      const float* src = rows + (size_t)c * d + slab * 64 + lane;
+      pre[2 * i] = c < n ? __ldg(src) : 0.0f;
+      pre[2 * i + 1] = c < n ? __ldg(src + 32) : 0.0f;
+    }
+  };
+  auto stash = [&](float* buf) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      buf[(size_t)lane * CQ_PITCH + w + 16 * i] = pre[2 * i];
+      buf[(size_t)(lane + 32) * CQ_PITCH + w + 16 * i] = pre[2 * i + 1];
+    }
+  };
+  fetch(0);
+  stash(tile);
+  __syncthreads();
+  float acc[4][16];
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[k][i] = 0.0f;
+  const float* xq = sq + (size_t)qg * 4 * d;
+#pragma unroll 1
+  for (uint32_t s = 0; s < nslab; s++) {
+    const float* buf = tile + (s & 1) * CD_SLAB;
+    if (s + 1 < nslab) fetch(s + 1);
+#pragma unroll
+    for (int ch = 0; ch < 4; ch++) {
+#pragma unroll
+      for (int i4 = 0; i4 < 4; i4++) {
+        float y[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) y[r] = buf[(size_t)(16 * ch + 4 * i4 + r) * CQ_PITCH + ct];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const float4 xv = *reinterpret_cast<const float4*>(xq + (size_t)k * d + s * 64 + 16 * ch + 4 * i4);
+          const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+          for (int r = 0; r < 4; r++) {
+            const float df = __fsub_rn(xs[r], y[r]);
+            acc[k][4 * i4 + r] = __fadd_rn(acc[k][4 * i4 + r], __fmul_rn(df, df));
+          }
+        }
+      }
+    }
+    if (s + 1 < nslab) stash(tile + ((s + 1) & 1) * CD_SLAB);
+    __syncthreads();
+  }
+  const uint32_t c = c0 + ct;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t qq = q0 + qg * 4 + k;
+    float tt = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 16; i++) tt = __fadd_rn(tt, acc[k][i]);
+    if (qq < Q && c < n) {
+      const bool valid = !validity || ((validity[c >> 3] >> (c & 7)) & 1);
+      out[(size_t)qq * out_stride + c] = valid ? __fadd_rn(0.0f, tt) : __int_as_float(0x7fc00000);
+    }
+  }
+}
+
 }  // namespace lb200
