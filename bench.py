@@ -257,12 +257,13 @@ def run_flat(args):
                        "l2_policy": "inputs larger than L2 (512 MB of vectors)"},
             "roofline": {"bound": "hbm", "achieved": tile_bytes / (ms / args.steps * 1e-3) / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": tile_bytes / (ms / args.steps * 1e-3) / 1e9 / peak, "traffic": None,
-                         "kernel": "flat_dist_kernel + flat_select_kernel (whole step)",
+                         "kernel": "coarse_dist_l2_slab_kernel + flat_select_kernel + merge_lists_kernel (whole step)",
                          "note": "bytes = N*d*4 per 32-query tile of the distance kernel; the path is fp32-issue bound (Q*N*d*3 flop), not HBM bound"},
             "e2e": {"value": Q * e2e_steps / (ms_e2e * 1e-3), "unit": "queries/s",
                     "h2d_bytes_per_step": int(vecs.nbytes + queries.nbytes), "d2h_bytes_per_step": Q * k * 12 + Q * 4,
                     "path": "lb200_flat_topk (host-pointer C ABI; uploads the vector batch every call)"},
-            "gpu_launches": 2 * args.steps, "clocks": clocks}
+            "gpu_launches": 3 * ((Q + 31) // 32) * args.steps,  # per 32-query tile: distance, segmented select, merge
+            "clocks": clocks}
     if not args.no_cpu_baseline:
         import oracle
         cores = oracle.max_threads()

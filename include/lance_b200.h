@@ -14,6 +14,11 @@
  *  - there is NO CPU fallback: without a usable CUDA device every call fails with
  *    LB200_ECUDA.
  *
+ * Limits of this build (LB200_EUNSUPPORTED beyond them): 8-bit PQ only; nlist <= 8192;
+ * num_sub_vectors <= 192 (the bank-conflict-free scan for multiples of 16 up to 96);
+ * k * max(refine_factor,1) <= 512; N < 2^32 rows; Q * nprobes < 2^31 per call;
+ * nprobes * k' up to (16384/k')^2 lists (two-level merge above 16384 candidates per query).
+ *
  * Numerics: all distances are IEEE f32 computed in the reference's own operation order
  * (see DESIGN.md "Numerics"), so results are bit-identical to the CPU reference wherever the
  * reference itself is deterministic; equal distances are ordered by row id.

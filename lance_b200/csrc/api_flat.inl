@@ -44,6 +44,16 @@ static int flat_dist_launch(int metric, const float* d_q, uint32_t Q, const floa
   return 0;
 }
 
+struct FlatScratch {
+  std::mutex mu;
+  void* p = nullptr;
+  size_t cap = 0;
+};
+static FlatScratch& flat_scratch(int dev) {
+  static FlatScratch tab[64];
+  return tab[(dev < 0 ? 0 : dev) & 63];
+}
+
 // queries are processed in tiles so that the [tile][n] distance block stays L2-resident
 static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uint32_t Q, const float* d_v,
                                  const uint8_t* d_valid, uint64_t n, uint32_t k, bool has_lower, float lower,
@@ -54,10 +64,7 @@ static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uin
   if (!Q) return 0;
   uint32_t tile = (uint32_t)std::max<uint64_t>(FLAT_TQ, std::min<uint64_t>(Q, (128ull << 20) / std::max<uint64_t>(1, n * 4)));
   tile = (tile + FLAT_TQ - 1) / FLAT_TQ * FLAT_TQ;
-  float* d_D = nullptr;
   size_t stride = (size_t)std::max<uint64_t>(n, 1);
-  CK(cudaMalloc(&d_D, (size_t)tile * stride * 4));
-  struct F { float* p; ~F() { cudaFree(p); } } guard{d_D};
   uint32_t kp2 = std::max(2u, next_pow2(k));
   size_t smem = (size_t)kp2 * 8;
   // segments per row: ~32k rows each, bounded by what the merge kernel sorts per query
@@ -66,15 +73,31 @@ static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uin
   const uint64_t seg_len = (n + nseg - 1) / nseg;
   nseg = (uint32_t)((n + seg_len - 1) / std::max<uint64_t>(seg_len, 1));
   nseg = std::max(nseg, 1u);
+  // Scratch (distance block + per-segment candidates) comes from a grow-only per-device cache: a
+  // cudaMalloc/cudaFree pair per call costs up to tens of milliseconds (r01: 15 -> 195 ms per 256-query
+  // batch on one box).  Calls on one device serialise on the cache's mutex.
+  const size_t cells = nseg > 1 ? (size_t)tile * nseg * k : 0;
+  const size_t b_D = Arena::pad((size_t)tile * stride * 4);
+  const size_t need = b_D + Arena::pad(cells * 4) + Arena::pad(cells * 8) + Arena::pad((size_t)tile * nseg * 4) + 1024;
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  FlatScratch& fs = flat_scratch(dev);
+  std::lock_guard<std::mutex> lk(fs.mu);
+  if (fs.cap < need) {
+    if (fs.p) CK(cudaFree(fs.p));
+    fs.p = nullptr;
+    fs.cap = 0;
+    cudaError_t e = cudaMalloc(&fs.p, need);
+    if (e != cudaSuccess) return set_err(LB200_ENOMEM, "flat kNN scratch of %zu bytes: %s", need, cudaGetErrorString(e));
+    fs.cap = need;
+  }
+  float* d_D = (float*)fs.p;
   float* t_d = nullptr;
   uint64_t* t_i = nullptr;
   uint32_t* t_c = nullptr;
-  struct G { void* p; ~G() { if (p) cudaFree(p); } } g2{nullptr};
   if (nseg > 1) {
-    size_t cells = (size_t)tile * nseg * k;
-    CK(cudaMalloc(&g2.p, Arena::pad(cells * 4) + Arena::pad(cells * 8) + Arena::pad((size_t)tile * nseg * 4)));
-    t_d = (float*)g2.p;
-    t_i = (uint64_t*)((char*)g2.p + Arena::pad(cells * 4));
+    t_d = (float*)((char*)fs.p + b_D);
+    t_i = (uint64_t*)((char*)t_d + Arena::pad(cells * 4));
     t_c = (uint32_t*)((char*)t_i + Arena::pad(cells * 8));
   }
   for (uint32_t q0 = 0; q0 < Q; q0 += tile) {
@@ -95,7 +118,7 @@ static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uin
       if (rc) return rc;
     }
   }
-  CK(cudaStreamSynchronize(st));  // d_D is freed on return
+  CK(cudaStreamSynchronize(st));  // the scratch is shared: finish before the next call may take it
   return 0;
 }
 
