@@ -180,6 +180,32 @@ int32_t lb200_merge_topk_device(int32_t device_id, const float* d_dist, const ui
                                 float* d_out_dist, uint64_t* d_out_rowid, uint32_t* d_out_count,
                                 void* stream);
 
+/* Host-pointer form of lb200_merge_topk_device: the union of G result lists of one query batch.
+ * == UnionExec over the delta indices of one column + SortExec(_distance).with_fetch(k') of
+ * Scanner::ann (rust/lance/src/dataset/scanner.rs:2139-2157; fan-out over deltas in
+ * new_knn_exec / ANNIvfSubIndexExec, rust/lance/src/io/exec/knn.rs:405-635).
+ * dist/rowid/exact [G][Q][stride], count [G][Q], outputs [Q][k] / [Q]; all host pointers. */
+int32_t lb200_merge_topk(int32_t device_id, const float* dist, const uint64_t* rowid,
+                         const float* exact_or_null, const uint32_t* count, uint32_t G, uint32_t Q,
+                         uint32_t stride, uint32_t kprime, uint32_t k, const float* lower_or_null,
+                         const float* upper_or_null, float* out_dist, uint64_t* out_rowid,
+                         uint32_t* out_count);
+
+/* flat_knn over a per-query candidate set whose vectors the CALLER fetched (TakeExec,
+ * rust/lance/src/io/exec/take.rs:178): compute_distance with the original key and the index's
+ * metric (flat.rs:28-86), [lower,upper) filter, SortExec(fetch=k), NOT NULL
+ * (scanner.rs:2066-2136).  This is the refine step on the drop-in path (scanner.rs:1706-1721,
+ * raw vectors not resident on the device) and the final step of knn_combined
+ * (scanner.rs:1755-1835: ANN results of the indexed rows UNION flat kNN of the unindexed
+ * fragments, all re-scored exactly).
+ * cand_vectors [Q][C][dim], cand_rowids [Q][C], cand_count [Q] (<= C, C <= 4096); outputs
+ * [Q][k] ascending by (distance,row id), out_count [Q].  All host pointers. */
+int32_t lb200_rerank(int32_t device_id, int32_t metric, uint32_t dim, const float* queries,
+                     uint32_t Q, const float* cand_vectors, const uint64_t* cand_rowids,
+                     const uint32_t* cand_count, uint32_t C, uint32_t k,
+                     const float* lower_or_null, const float* upper_or_null, float* out_dist,
+                     uint64_t* out_rowid, uint32_t* out_count);
+
 /* Instrumentation (not part of the reference surface): per-handle counters of the last
  * search / search_partitions call, used by bench.py for the roofline line. */
 typedef struct {

@@ -15,6 +15,7 @@ EXPORTS = [
     "lb200_flat_topk_device", "lb200_merge_topk_device", "lb200_set_profiling", "lb200_get_stats",
     "lb200_set_scan_variant", "lb200_last_error", "lb200_version",
     "lb200_peer_thresholds_export", "lb200_peer_thresholds_attach", "lb200_peer_thresholds_detach",
+    "lb200_merge_topk", "lb200_rerank",
 ]
 
 

@@ -258,3 +258,47 @@ def flat_knn(key, metric, vectors, k, validity=None, lower_bound=None, upper_bou
                                      C.c_uint64(n), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound), _p(od),
                                      _p(oi), _p(oc)))
     return od, oi, oc
+
+
+def merge_topk(dist, rowid, count, k, exact=None, kprime=None, lower_bound=None, upper_bound=None, device_id=0):
+    """Union of G result lists per query -> the k smallest by (distance,row id): the SortExec(fetch) above the
+    fan-out over delta indices (scanner.rs:2139-2157).  dist/rowid [G][Q][stride], count [G][Q]."""
+    dist = np.ascontiguousarray(dist, dtype=np.float32)
+    rowid = np.ascontiguousarray(rowid, dtype=np.uint64)
+    count = np.ascontiguousarray(count, dtype=np.uint32)
+    if dist.ndim != 3 or rowid.shape != dist.shape or count.shape != dist.shape[:2]:
+        raise ValueError("merge_topk: expected dist/rowid [G][Q][stride] and count [G][Q]")
+    if k <= 0:
+        raise ValueError("k must be positive")
+    G, Q, stride = dist.shape
+    ex = None if exact is None else np.ascontiguousarray(exact, dtype=np.float32)
+    od = np.full((Q, k), np.inf, dtype=np.float32)
+    oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+    oc = np.zeros(Q, dtype=np.uint32)
+    check(_lib.lib().lb200_merge_topk(
+        C.c_int32(device_id), _p(dist), _p(rowid), _p(ex), _p(count), C.c_uint32(G), C.c_uint32(Q), C.c_uint32(stride),
+        C.c_uint32(kprime or k), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound), _p(od), _p(oi), _p(oc)))
+    return od, oi, oc
+
+
+def rerank(key, metric, cand_vectors, cand_rowids, cand_count, k, lower_bound=None, upper_bound=None, device_id=0):
+    """flat_knn (scanner.rs:2066-2136) over per-query candidates fetched by the caller (TakeExec): exact distances
+    with the original key, [lower,upper), top k by (distance,row id).  key [Q][d], cand_vectors [Q][C][d],
+    cand_rowids [Q][C], cand_count [Q]."""
+    key2 = np.atleast_2d(_f32(key))
+    cv = _f32(cand_vectors)
+    cr = np.ascontiguousarray(cand_rowids, dtype=np.uint64)
+    cc = np.ascontiguousarray(cand_count, dtype=np.uint32)
+    Q = key2.shape[0]
+    if cv.ndim != 3 or cv.shape[0] != Q or cv.shape[2] != key2.shape[1] or cr.shape != cv.shape[:2] or cc.shape != (Q,):
+        raise ValueError("rerank: expected cand_vectors [Q][C][d], cand_rowids [Q][C], cand_count [Q]")
+    if k <= 0:
+        raise ValueError("k must be positive")
+    od = np.full((Q, k), np.inf, dtype=np.float32)
+    oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+    oc = np.zeros(Q, dtype=np.uint32)
+    check(_lib.lib().lb200_rerank(
+        C.c_int32(device_id), C.c_int32(DistanceType.code(metric)), C.c_uint32(key2.shape[1]), _p(key2), C.c_uint32(Q),
+        _p(cv), _p(cr), _p(cc), C.c_uint32(cv.shape[1]), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound),
+        _p(od), _p(oi), _p(oc)))
+    return od, oi, oc

@@ -1,0 +1,304 @@
+"""Reader for Lance's legacy (v1, file version 0.1) IVF_PQ `index.idx` → the exchange format
+`lb200_index_create` takes.
+
+Follows, without any Lance code in the process:
+  * the file tail `[metadata position u64][major u16][minor u16]"LANC"` and the protobuf framing
+    "u32 length, then the message" — rust/lance-io/src/utils.rs:83-101,124-137 and
+    `open_index_proto` (rust/lance/src/index.rs:169-181);
+  * `pb::Index` → `VectorIndex{spec_version, dimension, stages[], metric_type}` with stages
+    `IVF{centroids | centroids_tensor, offsets, lengths}` and `PQ{num_bits, num_sub_vectors, dimension,
+    codebook | codebook_tensor}` — protos/index.proto, consumed by `open_vector_index`
+    (rust/lance/src/index/vector.rs:446-513), `IvfModel::try_from(pb::Ivf)`
+    (rust/lance-index/src/vector/ivf/storage.rs:174-215) and `ProductQuantizer::from_proto`
+    (rust/lance-index/src/vector/pq.rs:77-96);
+  * a partition page = `length × M` row-major code bytes at the IVF stage's byte offset, followed by
+    `length` u64 row ids — `PQIndex::load` (rust/lance/src/index/vector/pq.rs:292-330), which also
+    transposes the codes to `[M][n_p]` exactly as done here.
+
+The protobuf wire decoder below handles what those messages use (varint, 64-bit, length-delimited,
+32-bit; packed and unpacked repeated scalars).  Errors follow the reference: a malformed file raises
+`ValueError` with the reference's wording where it has one (`Error::Index`, `Error::io`).
+"""
+import struct
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+
+from .synth import IvfPqData
+
+MAGIC = b"LANC"
+_METRICS = {0: "l2", 1: "cosine", 2: "dot"}          # pb::VectorMetricType (index.proto)
+_TENSOR_DTYPES = {2: np.float32, 3: np.float64}        # pb::Tensor::DataType FLOAT32 / FLOAT64
+
+
+# ---------------------------------------------------------------------------------------------
+# protobuf wire format
+# ---------------------------------------------------------------------------------------------
+def _varint(buf, pos):
+    out, shift = 0, 0
+    while True:
+        if pos >= len(buf):
+            raise ValueError("truncated varint in index metadata")
+        b = buf[pos]
+        pos += 1
+        out |= (b & 0x7F) << shift
+        if not b & 0x80:
+            return out, pos
+        shift += 7
+        if shift > 63:
+            raise ValueError("varint too long in index metadata")
+
+
+def _fields(buf):
+    """Yield (field number, wire type, value) — value is an int (wire 0/1/5) or a memoryview (wire 2)."""
+    buf = memoryview(buf)
+    pos, end = 0, len(buf)
+    while pos < end:
+        key, pos = _varint(buf, pos)
+        fno, wt = key >> 3, key & 7
+        if wt == 0:
+            v, pos = _varint(buf, pos)
+        elif wt == 1:
+            if pos + 8 > end:
+                raise ValueError("truncated fixed64 in index metadata")
+            v = struct.unpack_from("<Q", buf, pos)[0]
+            pos += 8
+        elif wt == 2:
+            n, pos = _varint(buf, pos)
+            if pos + n > end:
+                raise ValueError("truncated length-delimited field in index metadata")
+            v = buf[pos:pos + n]
+            pos += n
+        elif wt == 5:
+            if pos + 4 > end:
+                raise ValueError("truncated fixed32 in index metadata")
+            v = struct.unpack_from("<I", buf, pos)[0]
+            pos += 4
+        else:
+            raise ValueError(f"unsupported protobuf wire type {wt}")
+        yield fno, wt, v
+
+
+def _packed_varints(v, wt, out):
+    if wt == 2:
+        pos = 0
+        while pos < len(v):
+            x, pos = _varint(v, pos)
+            out.append(x)
+    else:
+        out.append(v)
+
+
+def _packed_f32(v, wt, out):
+    if wt == 2:
+        out.append(np.frombuffer(v, dtype="<f4"))
+    else:
+        out.append(np.array([v], dtype="<u4").view("<f4"))
+
+
+def _tensor(buf):
+    """pb::Tensor → 2-D array (rust/lance-index/src/vector/utils.rs:125-165)."""
+    dt, shape, data = 0, [], b""
+    for fno, wt, v in _fields(buf):
+        if fno == 1:
+            dt = v
+        elif fno == 2:
+            _packed_varints(v, wt, shape)
+        elif fno == 3:
+            data = v
+    if len(shape) != 2:
+        raise ValueError(f"only accept 2-D tensor shape, got: {shape}")
+    if dt not in _TENSOR_DTYPES:
+        raise ValueError(f"tensor data type {dt} is not supported on the B200 path (f32 only)")
+    arr = np.frombuffer(data, dtype=np.dtype(_TENSOR_DTYPES[dt]).newbyteorder("<"))
+    if arr.size != shape[0] * shape[1]:
+        raise ValueError(f"Tensor shape {shape} does not match to data len: {arr.size}")
+    return arr.astype(np.float32).reshape(shape[0], shape[1])
+
+
+# ---------------------------------------------------------------------------------------------
+# pb::Index and its stages
+# ---------------------------------------------------------------------------------------------
+@dataclass
+class IvfStage:
+    centroids: Optional[np.ndarray]   # [nlist][dim] f32
+    offsets: List[int]                # byte offsets of the partition pages in this file (v1)
+    lengths: List[int]                # rows per partition
+
+
+@dataclass
+class PqStage:
+    num_bits: int
+    num_sub_vectors: int
+    dimension: int
+    codebook: np.ndarray              # [M][2^bits][dim/M] f32
+
+
+@dataclass
+class LegacyIndexMeta:
+    name: str
+    columns: List[str]
+    dataset_version: int
+    spec_version: int
+    dimension: int
+    metric: str
+    ivf: IvfStage
+    pq: PqStage
+
+
+def _ivf(buf):
+    cents_rep, offsets, lengths, tensor = [], [], [], None
+    for fno, wt, v in _fields(buf):
+        if fno == 1:
+            _packed_f32(v, wt, cents_rep)
+        elif fno == 2:
+            _packed_varints(v, wt, offsets)
+        elif fno == 3:
+            _packed_varints(v, wt, lengths)
+        elif fno == 4:
+            tensor = _tensor(v)
+    if tensor is not None:
+        cents = tensor
+    elif cents_rep:
+        flat = np.concatenate(cents_rep).astype(np.float32)
+        cents = flat.reshape(len(lengths), flat.size // max(len(lengths), 1))
+    else:
+        cents = None
+    if not offsets:   # storage.rs:198-207: row offsets from the prefix sum when the file has none
+        offsets = list(np.concatenate([[0], np.cumsum(lengths)[:-1]]).astype(np.int64)) if lengths else []
+    if len(offsets) != len(lengths):
+        raise ValueError("IVF stage: offsets and lengths differ in length")
+    return IvfStage(cents, [int(o) for o in offsets], [int(n) for n in lengths])
+
+
+def _pq(buf):
+    bits = M = dim = 0
+    rep, tensor = [], None
+    for fno, wt, v in _fields(buf):
+        if fno == 1:
+            bits = v
+        elif fno == 2:
+            M = v
+        elif fno == 3:
+            dim = v
+        elif fno == 4:
+            _packed_f32(v, wt, rep)
+        elif fno == 5:
+            tensor = _tensor(v)
+    flat = tensor.reshape(-1) if tensor is not None else (
+        np.concatenate(rep).astype(np.float32) if rep else np.zeros(0, np.float32))
+    if M == 0 or dim == 0 or dim % M:
+        raise ValueError(f"PQ stage: dimension {dim} is not divisible by num_sub_vectors {M}")
+    ncent = 1 << bits
+    if flat.size != ncent * dim:
+        raise ValueError(f"PQ codebook has {flat.size} values, expected {ncent}x{dim}")
+    # The stored FixedSizeList of 2^bits·M rows × dsub is sub-space major (pq/utils.rs:54-71).
+    return PqStage(int(bits), int(M), int(dim), np.ascontiguousarray(flat.reshape(M, ncent, dim // M)))
+
+
+def parse_index_proto(buf) -> LegacyIndexMeta:
+    name, columns, version, vec = "", [], 0, None
+    for fno, wt, v in _fields(buf):
+        if fno == 1:
+            name = bytes(v).decode()
+        elif fno == 2:
+            columns.append(bytes(v).decode())
+        elif fno == 3:
+            version = v
+        elif fno == 5:
+            vec = v
+    if vec is None:
+        raise ValueError("Index proto was missing implementation field")   # index.rs:787-790
+    spec = dim = metric = 0
+    stages = []
+    for fno, wt, v in _fields(vec):
+        if fno == 1:
+            spec = v
+        elif fno == 2:
+            dim = v
+        elif fno == 3:
+            stages.append(v)
+        elif fno == 4:
+            metric = v
+    if metric not in _METRICS:
+        raise ValueError(f"Metric type '{metric}' is not supported")
+    ivf = pq = None
+    for st in stages:
+        for fno, wt, v in _fields(st):
+            if fno == 2:
+                ivf = _ivf(v)
+            elif fno == 3:
+                pq = _pq(v)
+            elif fno == 1:
+                raise ValueError("IVF_FLAT sub-index is out of scope of the B200 path")
+            elif fno == 4:
+                raise ValueError("OPQ transform stage is not supported")   # vector.rs:460-466 removed it too
+            elif fno == 5:
+                raise ValueError("DiskANN is not supported")               # vector.rs:495-500
+    if ivf is None or pq is None:
+        raise ValueError("index is not IVF_PQ: expected an IVF stage followed by a PQ stage")
+    if ivf.centroids is None:
+        raise ValueError("IVF stage has no centroids")
+    if ivf.centroids.shape[1] != dim or pq.dimension != dim:
+        raise ValueError(f"stage dimensions ({ivf.centroids.shape[1]}, {pq.dimension}) do not match index dimension {dim}")
+    return LegacyIndexMeta(name, columns, int(version), int(spec), int(dim), _METRICS[metric], ivf, pq)
+
+
+def read_footer(blob):
+    """(metadata position, major, minor) of a Lance v1 file — utils.rs:124-156."""
+    if len(blob) < 16:
+        raise ValueError(f"does not have sufficient data, len: {len(blob)}")
+    if blob[-4:] != MAGIC:
+        raise ValueError("not a Lance file: magic number mismatch")
+    pos, major, minor = struct.unpack("<QHH", blob[-16:-4])
+    return pos, major, minor
+
+
+def open_legacy_ivf_pq(path_or_bytes, raw_lookup=None) -> "LoadedIndex":
+    """`open_vector_index` + eager `PQIndex::load` of every partition.
+
+    raw_lookup: optional callable(row_ids u64[n]) → f32 [n][dim] (the TakeExec of the refine step); when
+    given, raw vectors are attached in index order so the device can refine."""
+    blob = path_or_bytes if isinstance(path_or_bytes, (bytes, bytearray, memoryview)) else open(path_or_bytes, "rb").read()
+    blob = bytes(blob)
+    pos, major, minor = read_footer(blob)
+    if (major, minor) not in ((0, 1), (0, 0)):
+        raise ValueError(f"index file version {major}.{minor} is not the legacy IVF_PQ layout "
+                         "(0.2 / 0.3 are Lance-v2 containers; SURVEY 8(f)-2)")
+    if pos + 4 > len(blob) - 16:
+        raise ValueError("file size is too small")                         # utils.rs:85-87
+    (mlen,) = struct.unpack_from("<I", blob, pos)
+    if pos + 4 + mlen > len(blob) - 16:
+        raise ValueError("index metadata runs past the end of the file")
+    meta = parse_index_proto(blob[pos + 4:pos + 4 + mlen])
+    if meta.pq.num_bits != 8:
+        raise ValueError(f"num_bits {meta.pq.num_bits}: only 8-bit PQ is on the B200 path")
+    M, nlist = meta.pq.num_sub_vectors, len(meta.ivf.lengths)
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(meta.ivf.lengths)
+    N = int(offs[-1])
+    codes = np.empty(N * M, dtype=np.uint8)
+    rids = np.empty(N, dtype=np.uint64)
+    for p, (o, n) in enumerate(zip(meta.ivf.offsets, meta.ivf.lengths)):
+        end = o + n * M + n * 8
+        if end > pos:
+            raise ValueError(f"partition {p} page [{o}, {end}) overlaps the metadata at {pos}")
+        page = np.frombuffer(blob, dtype=np.uint8, count=n * M, offset=o).reshape(n, M)
+        r0 = int(offs[p])
+        codes[r0 * M:(r0 + n) * M] = page.T.reshape(-1)                    # transpose(), pq/storage.rs:357-377
+        rids[r0:r0 + n] = np.frombuffer(blob, dtype="<u8", count=n, offset=o + n * M)
+    raw = None if raw_lookup is None else np.ascontiguousarray(raw_lookup(rids), dtype=np.float32)
+    data = IvfPqData(meta.metric, meta.dimension, nlist, M, np.ascontiguousarray(meta.ivf.centroids),
+                     meta.pq.codebook, offs, codes, rids, raw)
+    return LoadedIndex(meta, data)
+
+
+@dataclass
+class LoadedIndex:
+    meta: LegacyIndexMeta
+    data: IvfPqData
+
+    def to_device(self, device_id=0):
+        from .index import IvfPqIndex
+        return IvfPqIndex(self.data, device_id)

@@ -215,3 +215,53 @@ def flat_knn(metric, queries, vectors, k, validity=None, row_ids=None, threads=0
 
 def max_threads():
     return int(lib().lo_max_threads())
+
+
+# ---------------------------------------------------------------------------------------------
+# The plan around the index: Scanner::knn / ann / flat_knn / knn_combined
+# (rust/lance/src/dataset/scanner.rs:1670-1835,2066-2157), restated per query with the C oracle's
+# arithmetic.  Test infrastructure like the rest of this package.
+# ---------------------------------------------------------------------------------------------
+def _topk_by_distance(dist, rowid, k):
+    """SortExec(_distance ASC).with_fetch(k); equal distances ordered by row id (the oracle's own rule:
+    the reference leaves tie order unpinned)."""
+    order = np.lexsort((rowid, dist))[:k]
+    return dist[order], rowid[order]
+
+
+def flat_knn_rows(metric, key, vectors, row_ids, k, lower=None, upper=None):
+    """Scanner::flat_knn (scanner.rs:2066-2136) for one key over rows that carry row ids."""
+    vectors = _f32(vectors).reshape(-1, len(key))
+    row_ids = np.asarray(row_ids, dtype=np.uint64)
+    if vectors.shape[0] == 0:
+        return np.zeros(0, np.float32), np.zeros(0, np.uint64)
+    d = distance_batch(metric, key, vectors)
+    keep = ~np.isnan(d)
+    if lower is not None:
+        keep &= d >= np.float32(lower)
+    if upper is not None:
+        keep &= d < np.float32(upper)
+    return _topk_by_distance(d[keep], row_ids[keep], k)
+
+
+def nearest_plan(deltas, take, key, k, nprobes, refine_factor=None, lower=None, upper=None,
+                 unindexed_ids=None, unindexed_vectors=None, fast_search=False):
+    """Scanner::knn for ONE key.  deltas: OracleIndex list (same metric); take(row_ids) -> vectors."""
+    key = _f32(key)
+    metric = deltas[0].data.metric
+    kp = k * (refine_factor or 1)
+    ds, rs = [], []
+    for ix in deltas:          # ANNIvfSubIndexExec fan-out over the delta indices
+        od, oi, oc, _ = ix.search(key[None, :], kp, nprobes, 0, lower, upper)
+        ds.append(od[0, :oc[0]])
+        rs.append(oi[0, :oc[0]])
+    ad, ar = _topk_by_distance(np.concatenate(ds), np.concatenate(rs), kp)   # ann(): fetch k * refine
+    if refine_factor is not None:
+        ad, ar = flat_knn_rows(metric, key, take(ar), ar, k, lower, upper)
+    if fast_search or unindexed_ids is None or len(unindexed_ids) == 0:
+        return ad, ar
+    fd, fr = flat_knn_rows(metric, key, unindexed_vectors, unindexed_ids, k, lower, upper)
+    lut = {int(r): i for i, r in enumerate(np.asarray(unindexed_ids, dtype=np.uint64).tolist())}
+    fv = _f32(unindexed_vectors)[[lut[int(r)] for r in fr.tolist()]] if len(fr) else np.zeros((0, len(key)), np.float32)
+    av = _f32(take(ar)).reshape(-1, len(key)) if len(ar) else np.zeros((0, len(key)), np.float32)
+    return flat_knn_rows(metric, key, np.concatenate([fv, av]), np.concatenate([fr, ar]), k, lower, upper)
