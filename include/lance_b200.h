@@ -63,6 +63,34 @@ int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint
                            const float* raw_vectors_or_null, lb200_index** out);
 void lb200_index_destroy(lb200_index* ix);
 
+/* Native reader of the reference's legacy IVF_PQ index file (`_indices/<uuid>/index.idx`, Lance file
+ * version 0.1).  Replaces open_index_proto + open_vector_index + PQIndex::load
+ * (rust/lance/src/index.rs:169-181,774-786, rust/lance/src/index/vector.rs:446-513,
+ * rust/lance/src/index/vector/pq.rs:292-330): parses the file on the host into the arrays
+ * lb200_index_create takes (codes already transposed per partition).  Pure host code: usable
+ * without a GPU.  The v0.2 / v0.3 containers (index.idx + auxiliary.idx) are LB200_EUNSUPPORTED. */
+typedef struct lb200_index_file lb200_index_file; /* opaque, host memory */
+typedef struct {
+  int32_t metric;              /* LB200_L2 / COSINE / DOT (pb::VectorMetricType)                 */
+  uint32_t dim, nlist, num_sub_vectors, num_bits, spec_version;
+  uint64_t num_rows, dataset_version;
+  const float* centroids;      /* [nlist][dim]                                                   */
+  const float* codebook;       /* [M][256][dim/M]                                                */
+  const uint64_t* part_offsets;/* [nlist+1]                                                      */
+  const uint8_t* codes;        /* concat over p of [M][n_p]                                      */
+  const uint64_t* row_ids;     /* [num_rows]                                                     */
+  const char* name;            /* pb::Index.name                                                 */
+  const char* column;          /* pb::Index.columns[0]                                           */
+} lb200_index_file_info;       /* pointers live until lb200_index_file_close                     */
+int32_t lb200_index_file_open(const char* path, lb200_index_file** out);
+int32_t lb200_index_file_open_bytes(const void* bytes, uint64_t size, lb200_index_file** out);
+int32_t lb200_index_file_get_info(const lb200_index_file* f, lb200_index_file_info* info);
+void lb200_index_file_close(lb200_index_file* f);
+/* lb200_index_file_open + lb200_index_create in one call (== Dataset::open_vector_index for a
+ * legacy IVF_PQ index).  raw_vectors [num_rows][dim] in the FILE's row order, or NULL. */
+int32_t lb200_index_open(int32_t device_id, const char* path, const float* raw_vectors_or_null,
+                         lb200_index** out);
+
 /* VectorIndex::find_partitions (vector.rs:146; ivf/v2.rs:403-411 ->
  * kmeans_find_partitions, rust/lance-linalg/src/kmeans.rs:624-644), batched.
  * As in the reference, the key is used AS GIVEN: for a cosine index the caller passes the

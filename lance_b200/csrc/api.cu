@@ -408,3 +408,4 @@ extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
 #include "api_search.inl"
 #include "api_flat.inl"
 #include "api_combined.inl"
+#include "api_file.inl"

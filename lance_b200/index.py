@@ -79,6 +79,16 @@ class IvfPqIndex:
             _p(self.part_offsets), _p(codes), _p(rids), _p(raw), C.byref(h)))
         self._h = h
 
+    @classmethod
+    def _adopt(cls, handle, meta, device_id, has_raw):
+        """Wrap a handle the library created itself (lb200_index_open)."""
+        self = cls.__new__(cls)
+        self._L = _lib.lib()
+        self.metric, self.dim, self.nlist, self.M = meta.metric, int(meta.dim), int(meta.nlist), int(meta.M)
+        self.part_offsets = np.ascontiguousarray(meta.part_offsets, dtype=np.uint64)
+        self.has_raw, self.device_id, self._h = has_raw, device_id, handle
+        return self
+
     def close(self):
         if getattr(self, "_h", None):
             self._L.lb200_index_destroy(self._h)

@@ -302,3 +302,64 @@ class LoadedIndex:
     def to_device(self, device_id=0):
         from .index import IvfPqIndex
         return IvfPqIndex(self.data, device_id)
+
+
+# ---------------------------------------------------------------------------------------------
+# The same reader, native: lb200_index_file_* / lb200_index_open of the C ABI (csrc/api_file.inl).
+# ---------------------------------------------------------------------------------------------
+def open_legacy_ivf_pq_native(path_or_bytes) -> IvfPqData:
+    """Parse with the library's C++ reader (host only, no GPU needed) and copy out the arrays."""
+    import ctypes as C
+
+    from . import _lib
+
+    class Info(C.Structure):
+        _fields_ = [("metric", C.c_int32), ("dim", C.c_uint32), ("nlist", C.c_uint32), ("M", C.c_uint32),
+                    ("num_bits", C.c_uint32), ("spec_version", C.c_uint32), ("num_rows", C.c_uint64),
+                    ("dataset_version", C.c_uint64), ("centroids", C.c_void_p), ("codebook", C.c_void_p),
+                    ("part_offsets", C.c_void_p), ("codes", C.c_void_p), ("row_ids", C.c_void_p),
+                    ("name", C.c_char_p), ("column", C.c_char_p)]
+
+    L = _lib.lib()
+    L.lb200_index_file_close.restype = None
+    h = C.c_void_p()
+    if isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
+        b = bytes(path_or_bytes)
+        _lib.check(L.lb200_index_file_open_bytes(b, C.c_uint64(len(b)), C.byref(h)))
+    else:
+        _lib.check(L.lb200_index_file_open(str(path_or_bytes).encode(), C.byref(h)))
+    try:
+        info = Info()
+        _lib.check(L.lb200_index_file_get_info(h, C.byref(info)))
+
+        def arr(ptr, n, dt):
+            if n == 0:
+                return np.zeros(0, dtype=dt)
+            return np.frombuffer((C.c_char * (n * np.dtype(dt).itemsize)).from_address(ptr), dtype=dt).copy()
+
+        N, M, d, nl = int(info.num_rows), int(info.M), int(info.dim), int(info.nlist)
+        data = IvfPqData(_METRICS[info.metric], d, nl, M, arr(info.centroids, nl * d, np.float32).reshape(nl, d),
+                         arr(info.codebook, 256 * d, np.float32).reshape(M, 256, d // M),
+                         arr(info.part_offsets, nl + 1, np.uint64), arr(info.codes, N * M, np.uint8),
+                         arr(info.row_ids, N, np.uint64))
+        data.name, data.column, data.dataset_version = info.name.decode(errors="replace"), info.column.decode(errors="replace"), int(info.dataset_version)
+        return data
+    finally:
+        L.lb200_index_file_close(h)
+
+
+def open_index(path, device_id=0, raw_vectors=None):
+    """Dataset::open_vector_index for a legacy IVF_PQ index: lb200_index_open (native parse + upload)."""
+    import ctypes as C
+
+    from . import _lib
+    from .index import IvfPqIndex
+
+    meta = open_legacy_ivf_pq_native(path)      # host-side shape information for the Python mirror
+    raw = None if raw_vectors is None else np.ascontiguousarray(raw_vectors, dtype=np.float32)
+    if raw is not None and raw.shape != (meta.N, meta.dim):
+        raise ValueError(f"raw_vectors must be [{meta.N}][{meta.dim}] in the file's row order")
+    h = C.c_void_p()
+    _lib.check(_lib.lib().lb200_index_open(C.c_int32(device_id), str(path).encode(),
+                                           None if raw is None else raw.ctypes.data_as(C.c_void_p), C.byref(h)))
+    return IvfPqIndex._adopt(h, meta, device_id, raw is not None)

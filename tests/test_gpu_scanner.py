@@ -204,3 +204,25 @@ def test_nearest_plan_synthetic_three_deltas_and_unindexed(oracle, metric):
         ds.nearest(Query(q, k=5, refine_factor=0))
     for ix in ixs:
         ix.close()
+
+
+@pytest.mark.parametrize("tag,u", [("v0.8.14", "f358a219"), ("v0.21.0", "ca9b1111")])
+def test_native_index_open_equals_python_reader_path(oracle, tag, u):
+    """lb200_index_open (C++ parse + upload inside the library) against the oracle on the Python reader's arrays."""
+    from lance_b200 import Query
+    from lance_b200.reader import open_index
+    take, _, vec = _raw(tag)
+    path = os.path.join(G, f"{tag}_{u}_index.idx")
+    data = open_legacy_ivf_pq(path, raw_lookup=take).data
+    ox = oracle.OracleIndex(data)
+    q = np.concatenate([np.zeros((1, data.dim), np.float32), vec[3::41][:20]])
+    for raw in (None, data.raw_vectors):
+        ix = open_index(path, raw_vectors=raw)
+        assert (ix.metric_type(), ix.dim, ix.nlist, ix.M) == (data.metric, data.dim, data.nlist, data.M)
+        for k, nprobes, rf in ((10, 2, 0), (5, data.nlist, 4 if raw is not None else 0)):
+            gd, gi, gc = ix.search(Query(q, k=k, nprobes=nprobes, refine_factor=rf or None))
+            rd, ri, rc, _ = ox.search(q, k, nprobes, rf)
+            assert gc.tolist() == rc.tolist()
+            for j in range(len(q)):
+                _same_row(gd[j], gi[j], int(gc[j]), rd[j, :rc[j]], ri[j, :rc[j]], f"open {tag} k={k} rf={rf} q{j}")
+        ix.close()

@@ -201,3 +201,55 @@ def _four_bit(data):
     d = IvfPqData(**{**data.__dict__})
     d.codebook = data.codebook[:, :16, :].copy()
     return d
+
+
+# ---- the library's native reader (csrc/api_file.inl) must agree with the Python one byte for byte -------------------
+@pytest.mark.parametrize("key", sorted(FILES))
+def test_native_reader_on_reference_written_files(key):
+    from lance_b200.reader import open_legacy_ivf_pq_native
+    want = open_legacy_ivf_pq(_path(*key))
+    got = open_legacy_ivf_pq_native(_path(*key))
+    assert (got.metric, got.dim, got.nlist, got.M) == (want.data.metric, want.data.dim, want.data.nlist, want.data.M)
+    assert (got.name, got.column, got.dataset_version) == (want.meta.name, "vector", want.meta.dataset_version)
+    for f in ("centroids", "codebook", "part_offsets", "codes", "row_ids"):
+        assert np.array_equal(getattr(got, f), getattr(want.data, f)), f
+
+
+@pytest.mark.parametrize("tensors", [True, False])
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+def test_native_reader_round_trip(metric, tensors):
+    from lance_b200.reader import open_legacy_ivf_pq_native
+    data = _synthetic(metric)
+    got = open_legacy_ivf_pq_native(write_legacy(data, tensors=tensors))
+    assert (got.metric, got.dim, got.nlist, got.M) == (metric, data.dim, data.nlist, data.M)
+    for f in ("centroids", "codebook", "part_offsets", "codes", "row_ids"):
+        assert np.array_equal(getattr(got, f), getattr(data, f)), f
+
+
+def test_native_reader_errors(tmp_path):
+    from lance_b200 import LanceB200Error
+    from lance_b200.reader import open_legacy_ivf_pq_native
+    data = _synthetic("l2")
+    good = write_legacy(data)
+    cases = [(good[-8:], "sufficient data"), (good[:-4] + b"XXXX", "magic"),
+             (write_legacy(data, version=(0, 3)), "legacy IVF_PQ layout"),
+             (write_legacy(_four_bit(data), num_bits=4), "8-bit"),
+             (write_legacy(data, metric_code=3), "not supported"),
+             (good[:-16] + struct.pack("<QHH", len(good), 0, 1) + b"LANC", "too small"),
+             (good[:100] + good[-16:], None)]
+    for blob, msg in cases:
+        with pytest.raises(LanceB200Error, match=msg):
+            open_legacy_ivf_pq_native(blob)
+    with pytest.raises(LanceB200Error, match="cannot open"):
+        open_legacy_ivf_pq_native(str(tmp_path / "missing.idx"))
+    # a corrupted varint / truncated message inside the metadata must fail cleanly, never crash
+    pos = struct.unpack("<Q", good[-16:-8])[0]
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        b = bytearray(good)
+        i = int(rng.integers(pos + 4, pos + 4 + 60))
+        b[i] = int(rng.integers(0, 256))
+        try:
+            open_legacy_ivf_pq_native(bytes(b))
+        except LanceB200Error:
+            pass
