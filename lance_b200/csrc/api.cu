@@ -20,6 +20,7 @@
 #include "flat.cuh"
 #include "scan.cuh"
 #include "scan3.cuh"
+#include "scan4.cuh"
 #include "worklist.cuh"
 
 using namespace lb200;
@@ -91,6 +92,8 @@ struct lb200_index {
   uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
   uint8_t* d_codes = nullptr;          // tile16 layout (variants 1/2), or null
   uint8_t* d_codes3 = nullptr;         // skew-stream layout (variant 3), or null
+  uint8_t* d_codes4 = nullptr;         // 4-bit PQ: concat over p of [M/2][n_p], rows sorted by row id
+  uint32_t bits = 8;                   // PQ code width
   uint64_t* d_sb_off = nullptr;        // [nlist+1] first superblock per partition
   uint32_t skew_L = 0, skew_D = 0;     // superblock = 32*skew_L rows; lane delay period
   std::vector<uint64_t> h_part_off;
@@ -125,6 +128,11 @@ static int select_device(int device_id) {
   return 0;
 }
 
+namespace {
+int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist, const float* centroids, uint32_t M,
+                  const float* codebook, const uint64_t* part_offsets, const uint8_t* codes, const uint64_t* row_ids,
+                  const float* raw, lb200_index** out);
+}
 extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist,
                                       const float* centroids, uint32_t M, uint32_t num_bits,
                                       const float* codebook, const uint64_t* part_offsets,
@@ -132,8 +140,11 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
                                       const float* raw_vectors_or_null, lb200_index** out) {
   if (!out) return set_err(LB200_EINVAL, "out is null");
   *out = nullptr;
+  if (num_bits == 4)
+    return create_index4(device_id, metric, dim, nlist, centroids, M, codebook, part_offsets, codes, row_ids,
+                         raw_vectors_or_null, out);
   if (num_bits != 8)
-    return set_err(LB200_EUNSUPPORTED, "num_bits=%u: only 8-bit PQ is supported (4-bit: SURVEY 8f-4)", num_bits);
+    return set_err(LB200_EUNSUPPORTED, "num_bits=%u: only 8-bit and 4-bit PQ are supported", num_bits);
   if (metric != LB200_L2 && metric != LB200_COSINE && metric != LB200_DOT)
     return set_err(LB200_EINVAL, "unknown metric %d", metric);
   if (!dim || !nlist || !M || dim % M) return set_err(LB200_EINVAL, "bad shape dim=%u nlist=%u M=%u", dim, nlist, M);
@@ -284,6 +295,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_row_ids);
   cudaFree(ix->d_codes);
   cudaFree(ix->d_codes3);
+  cudaFree(ix->d_codes4);
   cudaFree(ix->d_sb_off);
   cudaFree(ix->arena.base);
   cudaFree(ix->stage.base);
@@ -407,5 +419,6 @@ extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
 
 #include "api_search.inl"
 #include "api_flat.inl"
+#include "api_pq4.inl"
 #include "api_combined.inl"
 #include "api_file.inl"

@@ -75,7 +75,7 @@ class IvfPqIndex:
         raw = None if data.raw_vectors is None else _f32(data.raw_vectors)
         check(L.lb200_index_create(
             C.c_int32(device_id), C.c_int32(DistanceType.code(data.metric)), C.c_uint32(self.dim),
-            C.c_uint32(self.nlist), _p(cents), C.c_uint32(self.M), C.c_uint32(8), _p(cb),
+            C.c_uint32(self.nlist), _p(cents), C.c_uint32(self.M), C.c_uint32(int(getattr(data, "num_bits", 8))), _p(cb),
             _p(self.part_offsets), _p(codes), _p(rids), _p(raw), C.byref(h)))
         self._h = h
 

@@ -28,14 +28,21 @@ class IvfPqData:
     codes: np.ndarray         # u8, concat over p of [M][n_p] (transposed)
     row_ids: np.ndarray       # [N] u64, index order
     raw_vectors: Optional[np.ndarray] = None  # [N][dim] f32, index order (for refine)
+    num_bits: int = 8         # 4: codebook [M][16][dim/M], codes concat over p of [M/2][n_p] (two codes per byte)
 
     @property
     def N(self):
         return int(self.part_offsets[-1])
 
+    @property
+    def code_bytes(self):
+        """bytes of PQ code per row (pq/storage.rs:172-176)."""
+        return self.M // 2 if self.num_bits == 4 else self.M
+
     def part_codes(self, p):
         o, e = int(self.part_offsets[p]), int(self.part_offsets[p + 1])
-        return self.codes[o * self.M:e * self.M].reshape(self.M, e - o)
+        cb = self.code_bytes
+        return self.codes[o * cb:e * cb].reshape(cb, e - o)
 
     def subset(self, parts):
         """Index restricted to the given partitions (others become empty): the per-GPU
@@ -48,14 +55,14 @@ class IvfPqData:
         codes, rids, raws = [], [], []
         for p in np.nonzero(keep)[0]:
             o, e = int(self.part_offsets[p]), int(self.part_offsets[p + 1])
-            codes.append(self.codes[o * self.M:e * self.M])
+            codes.append(self.codes[o * self.code_bytes:e * self.code_bytes])
             rids.append(self.row_ids[o:e])
             if self.raw_vectors is not None:
                 raws.append(self.raw_vectors[o:e])
         cat = lambda xs, dt, shp: (np.concatenate(xs) if xs else np.zeros(shp, dtype=dt))
         return IvfPqData(self.metric, self.dim, self.nlist, self.M, self.centroids, self.codebook,
                          offs, cat(codes, np.uint8, (0,)), cat(rids, np.uint64, (0,)),
-                         None if self.raw_vectors is None else cat(raws, np.float32, (0, self.dim)))
+                         None if self.raw_vectors is None else cat(raws, np.float32, (0, self.dim)), self.num_bits)
 
 
 def _assign(x, cents, chunk=65536):

@@ -28,6 +28,7 @@ class _Index(C.Structure):
         ("metric", C.c_int32), ("dim", C.c_uint32), ("nlist", C.c_uint32), ("M", C.c_uint32),
         ("centroids", C.c_void_p), ("codebook", C.c_void_p), ("part_offsets", C.c_void_p),
         ("codes", C.c_void_p), ("row_ids", C.c_void_p), ("raw_vectors", C.c_void_p),
+        ("num_bits", C.c_uint32),
     ]
 
 
@@ -46,6 +47,7 @@ def lib():
         f.lo_norm_l2.restype = C.c_float
         f.lo_cosine_fast.restype = C.c_float
         f.lo_pq_distance_one.restype = C.c_float
+        f.lo_pq_distance_one_4bit.restype = C.c_float
         f.lo_find_partitions.restype = C.c_uint32
         f.lo_search_in_partition.restype = C.c_uint32
         f.lo_search_one.restype = C.c_uint32
@@ -147,6 +149,58 @@ def pq_quantize(metric, codebook, vecs):
     return out
 
 
+# ---- 4-bit PQ (pq/distance.rs:138-229) -----------------------------------------------------
+def build_distance_table4(metric, codebook, query):
+    """codebook [M][16][dsub]; returns [M][16]."""
+    codebook, query = _f32(codebook), _f32(query)
+    M = codebook.shape[0]
+    out = np.empty((M, 16), dtype=np.float32)
+    m = METRICS[metric]
+    lib().lo_build_distance_table4(C.c_int(DOT if m == DOT else L2), _p(codebook), C.c_uint32(M),
+                                   C.c_uint32(query.size), _p(query), _p(out))
+    return out
+
+
+def quantize_distance_table(table):
+    """quantize_distance_table: (qmin, qmax, u8 table [M][16])."""
+    table = _f32(table)
+    M = table.shape[0]
+    qt = np.empty((M, 16), dtype=np.uint8)
+    qmin, qmax = C.c_float(), C.c_float()
+    lib().lo_quantize_distance_table(_p(table), C.c_uint32(M), C.byref(qmin), C.byref(qmax), _p(qt))
+    return np.float32(qmin.value), np.float32(qmax.value), qt
+
+
+def compute_pq_distance_4bit(table, codes_t):
+    """table [M][16] f32, codes_t transposed packed [M/2][n] u8 -> [n] f32."""
+    table = _f32(table)
+    codes_t = np.ascontiguousarray(codes_t, dtype=np.uint8)
+    M = table.shape[0]
+    n = codes_t.shape[1]
+    out = np.empty(n, dtype=np.float32)
+    lib().lo_compute_pq_distance_4bit(_p(table), C.c_uint32(M), _p(codes_t), C.c_size_t(n), _p(out))
+    return out
+
+
+def pq_distance_one_4bit(table, codes_t, i):
+    table = _f32(table)
+    codes_t = np.ascontiguousarray(codes_t, dtype=np.uint8)
+    return float(lib().lo_pq_distance_one_4bit(_p(table), C.c_uint32(table.shape[0]), _p(codes_t),
+                                               C.c_size_t(codes_t.shape[1]), C.c_size_t(i)))
+
+
+def pq_quantize4(metric, codebook, vecs):
+    """transform_impl::<4>: codebook [M][16][dsub] -> packed row-major codes [n][M/2]."""
+    codebook, vecs = _f32(codebook), _f32(vecs)
+    M = codebook.shape[0]
+    n, d = vecs.shape
+    out = np.zeros((n, M // 2), dtype=np.uint8)
+    m = METRICS[metric]
+    lib().lo_pq_quantize4(C.c_int(DOT if m == DOT else L2), _p(codebook), C.c_uint32(M), C.c_uint32(d),
+                          _p(vecs), C.c_size_t(n), _p(out))
+    return out
+
+
 class OracleIndex:
     """Mirror of IVFIndex<FlatIndex, ProductQuantizer> (lance/src/index/vector/ivf/v2.rs:76)
     over the exchange format of lance_b200.synth.IvfPqData."""
@@ -163,7 +217,7 @@ class OracleIndex:
         k = self._keep
         self.ix = _Index(METRICS[data.metric], data.dim, data.nlist, data.M, k[0].ctypes.data,
                          k[1].ctypes.data, k[2].ctypes.data, k[3].ctypes.data, k[4].ctypes.data,
-                         None if k[5] is None else k[5].ctypes.data)
+                         None if k[5] is None else k[5].ctypes.data, int(getattr(data, "num_bits", 8)))
 
     def preprocess_query(self, part, key):
         key = _f32(key)

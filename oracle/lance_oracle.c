@@ -348,6 +348,79 @@ void lo_build_distance_table(int metric, const float *codebook, uint32_t M, uint
   }
 }
 
+/* The same tables for 4-bit PQ: build_distance_table_{l2,dot}_impl::<4> (pq/distance.rs:24,60): 16 centroids per
+ * sub-space, codebook [M][16][dsub], table [M][16]. */
+void lo_build_distance_table4(int metric, const float *codebook, uint32_t M, uint32_t d,
+                              const float *query, float *table) {
+  uint32_t dsub = d / M;
+  for (uint32_t m = 0; m < M; m++) {
+    const float *sub = query + (size_t)m * dsub;
+    const float *cents = codebook + (size_t)m * 16 * dsub;
+    if (metric == LO_DOT)
+      lo_dot_distance_batch(sub, cents, 16, dsub, table + (size_t)m * 16);
+    else
+      lo_l2_distance_batch(sub, cents, 16, dsub, table + (size_t)m * 16);
+  }
+}
+
+/* pq/distance.rs:206-229 quantize_distance_table: qmin = min of all entries (f32::min fold), qmax = max over
+ * ADJACENT sub-space pairs (tuple_windows) of (max_a + max_b), entry -> ceil((d-qmin)*255/(qmax-qmin)) as u8
+ * (Rust `as u8`: saturating, NaN -> 0). */
+void lo_quantize_distance_table(const float *table, uint32_t M, float *qmin_out, float *qmax_out,
+                                uint8_t *qt) {
+  float qmin = INFINITY, qmax = -INFINITY;
+  for (size_t i = 0; i < (size_t)M * 16; i++) qmin = fminf(qmin, table[i]);
+  for (uint32_t m = 0; m + 1 < M; m++) {
+    float a = -INFINITY, b = -INFINITY;
+    for (int j = 0; j < 16; j++) a = fmaxf(a, table[(size_t)m * 16 + j]);
+    for (int j = 0; j < 16; j++) b = fmaxf(b, table[(size_t)(m + 1) * 16 + j]);
+    qmax = fmaxf(qmax, a + b);
+  }
+  for (size_t i = 0; i < (size_t)M * 16; i++) {
+    float v = ceilf((table[i] - qmin) * 255.0f / (qmax - qmin));
+    qt[i] = v != v ? 0 : (v <= 0.0f ? 0 : (v >= 255.0f ? 255 : (uint8_t)v));
+  }
+  *qmin_out = qmin;
+  *qmax_out = qmax;
+}
+
+/* pq/distance.rs:138-204 compute_pq_distance_4bit, codes transposed [M/2][n], byte = (code[2j+1] << 4) | code[2j]
+ * (pq.rs:166-170).  Rows in whole blocks of 16 go through u8x16: the two looked-up bytes are added with
+ * _mm_add_epi8, i.e. WRAPPING u8 (simd/u8.rs:279-287; x86_64 is the reference CPU of this repo, .cargo/config.toml
+ * target-cpu=haswell) before widening to f32; the n % 16 tail rows add the two bytes as f32 separately.
+ * Then d = d * (qmax - qmin) / 255 + qmin.  n < 16 makes the reference's block loop bound underflow
+ * (`num_vectors - 16 + 1` on usize); here such partitions are all tail rows. */
+void lo_compute_pq_distance_4bit(const float *table, uint32_t M, const uint8_t *codes, size_t n,
+                                 float *out) {
+  uint8_t *qt = (uint8_t *)malloc((size_t)M * 16);
+  float qmin, qmax;
+  lo_quantize_distance_table(table, M, &qmin, &qmax, qt);
+  size_t blocks = n >= 16 ? n - n % 16 : 0;
+  for (size_t i = 0; i < n; i++) out[i] = 0.0f;
+  for (uint32_t j = 0; j < M / 2; j++) {
+    const uint8_t *t0 = qt + (size_t)(2 * j) * 16, *t1 = qt + (size_t)(2 * j + 1) * 16;
+    const uint8_t *c = codes + (size_t)j * n;
+    for (size_t i = 0; i < blocks; i++) out[i] += (float)(uint8_t)(t0[c[i] & 15] + t1[c[i] >> 4]);
+    for (size_t i = blocks; i < n; i++) {
+      out[i] += (float)t0[c[i] & 15];
+      out[i] += (float)t1[c[i] >> 4];
+    }
+  }
+  for (size_t i = 0; i < n; i++) out[i] = out[i] * (qmax - qmin) / 255.0f + qmin;
+  free(qt);
+}
+
+/* pq/storage.rs:602-617 PQDistCalculator::distance(id) for 4 bit: the UNQUANTISED f32 table, pair sums added in
+ * ascending j (prefilter path only). */
+float lo_pq_distance_one_4bit(const float *table, uint32_t M, const uint8_t *codes, size_t n, size_t id) {
+  float s = 0.0f;
+  for (uint32_t j = 0; j < M / 2; j++) {
+    uint8_t c = codes[(size_t)j * n + id];
+    s += table[(size_t)(2 * j) * 16 + (c & 15)] + table[(size_t)(2 * j + 1) * 16 + (c >> 4)];
+  }
+  return s;
+}
+
 /* pq/distance.rs:102-135 compute_pq_distance (8 bit), codes transposed [M][n]. */
 void lo_compute_pq_distance(const float *table, uint32_t M, const uint8_t *codes, size_t n,
                             float *out) {
@@ -376,6 +449,7 @@ typedef struct {
   const uint8_t *codes;        /* concat over p of [M][n_p] */
   const uint64_t *row_ids;     /* [N] */
   const float *raw_vectors;    /* [N][dim] in row_ids (index) order, or NULL */
+  uint32_t num_bits;           /* 0 or 8: 8-bit PQ; 4: codebook [M][16][dim/M], codes [M/2][n_p] packed nibbles */
 } lo_index;
 
 /* lance/src/index/vector/ivf/v2.rs:285-301 preprocess_query: the key that reaches the
@@ -410,14 +484,25 @@ uint32_t lo_search_in_partition(const lo_index *ix, uint32_t part, const float *
     memcpy(q, key, sizeof(float) * d);
   }
   float *table = (float *)malloc(sizeof(float) * M * 256);
-  lo_build_distance_table(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
-  const uint8_t *codes = ix->codes + off * M;
   float *dist = (float *)malloc(sizeof(float) * (n ? n : 1));
-  if (!bitmask_or_null) {
-    lo_compute_pq_distance(table, M, codes, n, dist);
+  if (ix->num_bits == 4) {
+    const uint8_t *codes = ix->codes + off * (M / 2);
+    lo_build_distance_table4(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+    if (!bitmask_or_null) {
+      lo_compute_pq_distance_4bit(table, M, codes, n, dist);
+    } else {
+      for (size_t i = 0; i < n; i++)
+        if ((bitmask_or_null[i >> 6] >> (i & 63)) & 1) dist[i] = lo_pq_distance_one_4bit(table, M, codes, n, i);
+    }
   } else {
-    for (size_t i = 0; i < n; i++)
-      if ((bitmask_or_null[i >> 6] >> (i & 63)) & 1) dist[i] = lo_pq_distance_one(table, M, codes, n, i);
+    const uint8_t *codes = ix->codes + off * M;
+    lo_build_distance_table(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+    if (!bitmask_or_null) {
+      lo_compute_pq_distance(table, M, codes, n, dist);
+    } else {
+      for (size_t i = 0; i < n; i++)
+        if ((bitmask_or_null[i >> 6] >> (i & 63)) & 1) dist[i] = lo_pq_distance_one(table, M, codes, n, i);
+    }
   }
   float lb = has_lower ? lower : -3.402823466e+38f, ub = has_upper ? upper : 3.402823466e+38f;
   int bounded = has_lower || has_upper;
@@ -665,4 +750,30 @@ void lo_pq_quantize(int metric, const float *codebook, uint32_t M, uint32_t d, c
                     size_t n, uint8_t *out_codes) {
   lo_pq_ctx c = {metric, codebook, vecs, M, d, out_codes};
   lo_parallel_for((int64_t)n, 256, 0, lo_pq_body, &c);
+}
+
+/* ProductQuantizer::transform_impl::<4> (lance-index/src/vector/pq.rs:112-190): per sub-space argmin over the 16
+ * centroids, two codes per byte as (code[2j+1] << 4) | code[2j].  out_codes row-major [n][M/2]. */
+void lo_pq_quantize4(int metric, const float *codebook, uint32_t M, uint32_t d, const float *vecs,
+                     size_t n, uint8_t *out_codes) {
+  uint32_t dsub = d / M;
+  float dist[16];
+  for (size_t i = 0; i < n; i++)
+    for (uint32_t m = 0; m < M; m++) {
+      const float *sub = vecs + i * d + (size_t)m * dsub;
+      const float *cents = codebook + (size_t)m * 16 * dsub;
+      if (metric == LO_DOT)
+        lo_dot_distance_batch(sub, cents, 16, dsub, dist);
+      else
+        lo_l2_distance_batch(sub, cents, 16, dsub, dist);
+      float best = INFINITY;
+      int bi = 0;
+      for (int j = 0; j < 16; j++)
+        if (dist[j] < best) {
+          best = dist[j];
+          bi = j;
+        }
+      uint8_t *o = out_codes + i * (M / 2) + m / 2;
+      *o = (m & 1) ? (uint8_t)(*o | (bi << 4)) : (uint8_t)bi;
+    }
 }

@@ -50,8 +50,10 @@ def test_argument_validation_without_gpu():
                                         cent.ctypes.data_as(C.c_void_p), C.c_uint32(M), C.c_uint32(bits),
                                         cb.ctypes.data_as(C.c_void_p), offs.ctypes.data_as(C.c_void_p), None, None,
                                         None, C.byref(h))
-    assert L.lb200_index_create(*args(4)) == -4  # 4-bit PQ unsupported
-    assert b"8-bit" in L.lb200_last_error()
+    assert L.lb200_index_create(*args(5)) == -4  # only 8-bit and 4-bit PQ exist (pq.rs:103-111)
+    assert b"8-bit and 4-bit" in L.lb200_last_error()
+    assert L.lb200_index_create(*args(4, M=1)) == -1  # 4-bit: num_sub_vectors must be even (pq.rs:131-138)
+    assert b"divisible by 2" in L.lb200_last_error()
     assert L.lb200_index_create(*args(8, M=3)) == -1  # dim % M != 0
     assert L.lb200_index_create(*args(8, metric=7)) == -1
     assert L.lb200_set_scan_variant(None, 0) == -1

@@ -1,0 +1,124 @@
+"""GPU parity of the 4-bit PQ path (SURVEY 8(a) row A5'': compute_pq_distance_4bit / quantize_distance_table,
+rust/lance-index/src/vector/pq/distance.rs:138-229) against the oracle: bit-identical distances, identical row ids.
+The scan between the f32 table and the dequantisation is integer arithmetic (u8 table, wrapping u8 pair sums on whole
+16-row blocks, separate adds on the n % 16 tail), so exactness is the natural bar."""
+import numpy as np
+import pytest
+import torch
+
+from lance_b200.synth import IvfPqData
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_gpu():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from lance_b200 import _lib
+    assert _lib.lib() is not None
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def _index4(metric, d, nlist, M, sizes, seed, keep_raw=False, scale=1.0):
+    rng = np.random.default_rng(seed)
+    sizes = np.asarray(sizes, dtype=np.int64)
+    N = int(sizes.sum())
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    return IvfPqData(metric, d, nlist, M, rng.normal(size=(nlist, d)).astype(np.float32),
+                     (scale * rng.normal(size=(M, 16, d // M))).astype(np.float32), offs,
+                     rng.integers(0, 256, size=N * M // 2, dtype=np.uint8),
+                     rng.permutation(N * 3)[:N].astype(np.uint64),
+                     rng.normal(size=(N, d)).astype(np.float32) if keep_raw else None, 4)
+
+
+def _check_search(oracle, data, q, cases):
+    from lance_b200 import IvfPqIndex, Query
+    ix, ox = IvfPqIndex(data), oracle.OracleIndex(data)
+    for k, nprobes, rf, lo, hi in cases:
+        gd, gi, gc = ix.search(Query(q, k=k, nprobes=nprobes, refine_factor=rf or None, lower_bound=lo, upper_bound=hi))
+        rd, ri, rc, _ = ox.search(q, k, nprobes, rf, lo, hi)
+        assert gc.tolist() == rc.tolist(), f"counts k={k} P={nprobes} rf={rf}"
+        for j in range(len(q)):
+            n = int(rc[j])
+            assert gi[j, :n].tolist() == ri[j, :n].tolist(), f"row ids k={k} P={nprobes} rf={rf} [{lo},{hi}) q{j}"
+            assert _bits(gd[j, :n]).tolist() == _bits(rd[j, :n]).tolist(), f"distances k={k} P={nprobes} rf={rf} q{j}"
+    assert ix.stats()["scan_variant"] == 4
+    ix.close()
+
+
+@pytest.mark.parametrize("metric,d,M", [("l2", 128, 16), ("l2", 32, 2), ("l2", 30, 6), ("cosine", 96, 12),
+                                        ("dot", 64, 8), ("dot", 768, 48), ("l2", 1536, 96)])
+def test_search_4bit_parity_ragged(oracle, metric, d, M):
+    sizes = [0, 1, 15, 16, 17, 100, 333, 0, 1000, 47, 256, 31]
+    data = _index4(metric, d, len(sizes), M, sizes, seed=d + M, keep_raw=True)
+    rng = np.random.default_rng(1)
+    q = rng.normal(size=(13, d)).astype(np.float32)
+    dall = oracle.OracleIndex(data).search(q, 50, len(sizes))[0]
+    lo, hi = float(np.quantile(dall[np.isfinite(dall)], 0.1)), float(np.quantile(dall[np.isfinite(dall)], 0.7))
+    _check_search(oracle, data, q, [(1, 1, 0, None, None), (10, 4, 0, None, None), (10, len(sizes), 0, None, None),
+                                    (100, 6, 0, None, None), (10, 5, 0, lo, hi), (7, 5, 4, None, None),
+                                    (10, len(sizes) + 3, 2, None, None)])
+
+
+def test_search_4bit_many_ties_order_by_row_id(oracle):
+    """A tiny codebook scale makes most quantised distances collide: the order inside a tie is by row id."""
+    sizes = [500, 700, 300]
+    data = _index4("l2", 16, 3, 2, sizes, seed=5)
+    data.codes = (data.codes & 0x11).astype(np.uint8)          # 4 distinct codes per byte -> massive ties
+    rng = np.random.default_rng(2)
+    q = rng.normal(size=(6, 16)).astype(np.float32)
+    _check_search(oracle, data, q, [(20, 3, 0, None, None), (128, 2, 0, None, None)])
+
+
+def test_search_in_partition_4bit(oracle):
+    from lance_b200 import IvfPqIndex
+    sizes = [40, 0, 23, 160]
+    data = _index4("l2", 32, 4, 8, sizes, seed=3)
+    ix, ox = IvfPqIndex(data), oracle.OracleIndex(data)
+    rng = np.random.default_rng(4)
+    q = rng.normal(size=(5, 32)).astype(np.float32)
+    parts = np.array([[0, 3], [1, 2], [3, 0], [2, 2], [3, 1]], dtype=np.uint32)
+    od, oi, oc = ix.search_in_partition(parts, q, 25)
+    for i in range(5):
+        for j in range(2):
+            rd, rr = ox.search_in_partition(int(parts[i, j]), q[i], 25)
+            n = int(oc[i, j])
+            assert n == len(rr) and oi[i, j, :n].tolist() == rr.tolist()
+            assert _bits(od[i, j, :n]).tolist() == _bits(rd).tolist()
+    with pytest.raises(Exception, match="prefilter"):
+        ix.search_in_partition(parts, q, 5, prefilter={0: np.ones(40, bool)})
+    ix.close()
+
+
+def test_4bit_real_built_index(oracle):
+    """Codes produced by the oracle's transform_impl::<4> on residuals of clustered data; refine on raw vectors."""
+    rng = np.random.default_rng(8)
+    d, nlist, M, n = 64, 6, 16, 3000
+    cents = rng.normal(scale=4.0, size=(nlist, d)).astype(np.float32)
+    part = rng.integers(0, nlist, size=n)
+    x = (cents[part] + rng.normal(size=(n, d))).astype(np.float32)
+    order = np.argsort(part, kind="stable")
+    x, part = x[order], part[order]
+    cb = rng.normal(size=(M, 16, d // M)).astype(np.float32)
+    packed = oracle.pq_quantize4("l2", cb, x - cents[part])     # [n][M/2]
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(np.bincount(part, minlength=nlist))
+    codes = np.concatenate([packed[int(offs[p]):int(offs[p + 1])].T.reshape(-1) for p in range(nlist)])
+    data = IvfPqData("l2", d, nlist, M, cents, cb, offs, codes, rng.permutation(n).astype(np.uint64), x, 4)
+    q = (x[::250] + rng.normal(scale=0.1, size=x[::250].shape)).astype(np.float32)
+    _check_search(oracle, data, q, [(10, 2, 0, None, None), (10, 3, 10, None, None), (1, nlist, 50, None, None)])
+
+
+def test_4bit_create_errors():
+    import ctypes as C
+    from lance_b200 import IvfPqIndex, LanceB200Error
+    data = _index4("l2", 30, 2, 6, [5, 5], seed=1)
+    bad = IvfPqData(**{**data.__dict__})
+    bad.M = 3
+    bad.codebook = np.zeros((3, 16, 10), np.float32)
+    with pytest.raises(LanceB200Error, match="divisible by 2"):
+        IvfPqIndex(bad)

@@ -1,0 +1,115 @@
+"""CPU tests of the oracle's 4-bit PQ restatement (rust/lance-index/src/vector/pq/distance.rs:138-229).
+
+PARITY UNPINNED for this sub-path: the reference holds no known-answer vector for compute_pq_distance_4bit (only
+whole-index recall floors), so the C restatement is checked here against an independent numpy restatement written
+from the same source lines, against the definitional relation to the unquantised table, and against the packing rule
+of transform_impl::<4> (pq.rs:166-170).
+"""
+import numpy as np
+import pytest
+
+
+def _np_quantize(table):
+    """quantize_distance_table, numpy float32 ops in the reference's order."""
+    t = table.astype(np.float32)
+    qmin = np.float32(t.min())
+    mx = t.max(axis=1)
+    qmax = np.float32((mx[:-1] + mx[1:]).max())
+    with np.errstate(all="ignore"):
+        v = np.ceil((t - qmin) * np.float32(255.0) / np.float32(qmax - qmin))
+    v = np.where(np.isnan(v), 0, np.clip(v, 0, 255))
+    return qmin, qmax, v.astype(np.uint8)
+
+
+def _np_distance_4bit(table, codes_t):
+    qmin, qmax, qt = _np_quantize(table)
+    M = table.shape[0]
+    n = codes_t.shape[1]
+    blocks = n - n % 16 if n >= 16 else 0
+    acc = np.zeros(n, dtype=np.float32)
+    for j in range(M // 2):
+        lo = qt[2 * j][codes_t[j] & 15].astype(np.uint16)
+        hi = qt[2 * j + 1][codes_t[j] >> 4].astype(np.uint16)
+        s = lo + hi
+        s[:blocks] &= 255                      # _mm_add_epi8 on whole 16-row blocks
+        acc += s.astype(np.float32)
+    return (acc * np.float32(qmax - qmin) / np.float32(255.0) + qmin).astype(np.float32), qmin, qmax, qt
+
+
+@pytest.mark.parametrize("metric", ["l2", "dot"])
+@pytest.mark.parametrize("M,dsub,n", [(2, 8, 100), (16, 8, 1000), (16, 8, 15), (16, 8, 16), (6, 5, 77), (96, 16, 333),
+                                      (4, 16, 0)])
+def test_4bit_distance_equals_numpy_restatement(oracle, metric, M, dsub, n):
+    rng = np.random.default_rng(M * 1000 + n)
+    cb = rng.normal(size=(M, 16, dsub)).astype(np.float32)
+    q = rng.normal(size=M * dsub).astype(np.float32)
+    codes = rng.integers(0, 256, size=(M // 2, n), dtype=np.uint8)
+    table = oracle.build_distance_table4(metric, cb, q)
+    # the table itself: per sub-space the same batch distance as the 8-bit table uses
+    for m in range(M):
+        want = oracle.distance_batch("dot" if metric == "dot" else "l2", q[m * dsub:(m + 1) * dsub], cb[m])
+        assert np.array_equal(table[m].view(np.uint32), want.view(np.uint32))
+    qmin, qmax, qt = oracle.quantize_distance_table(table)
+    want_d, wmin, wmax, wqt = _np_distance_4bit(table, codes)
+    assert (qmin, qmax) == (wmin, wmax) and np.array_equal(qt, wqt)
+    got = oracle.compute_pq_distance_4bit(table, codes)
+    assert np.array_equal(got.view(np.uint32), want_d.view(np.uint32))
+
+
+def test_4bit_relation_to_unquantised_table(oracle):
+    """Dequantised 4-bit distance = sum of per-pair quantised entries: with qmin >= 0 (L2) no u8 sum wraps except
+    by the +1 of the two ceilings, and d4 + (M/2 - 1) * qmin' tracks the exact table sum within M quantisation steps
+    (each entry rounds up by < 1 step); pins the direction of the rounding and the pair structure."""
+    rng = np.random.default_rng(4)
+    M, dsub, n = 16, 8, 512
+    cb = rng.normal(size=(M, 16, dsub)).astype(np.float32)
+    q = rng.normal(size=M * dsub).astype(np.float32)
+    codes = rng.integers(0, 256, size=(M // 2, n), dtype=np.uint8)
+    table = oracle.build_distance_table4("l2", cb, q)
+    qmin, qmax, qt = oracle.quantize_distance_table(table)
+    step = (qmax - qmin) / 255.0
+    d4 = oracle.compute_pq_distance_4bit(table, codes).astype(np.float64)
+    exact = np.array([oracle.pq_distance_one_4bit(table, codes, i) for i in range(n)], dtype=np.float64)
+    # sum_m ceil((T_m - qmin)/step) * step + qmin  vs  sum_m T_m :  d4 - qmin = sum (T_m - qmin) + [0, M) steps
+    lhs = d4 - qmin
+    rhs = exact - M * float(qmin)
+    assert (lhs >= rhs - 1e-3).all() and (lhs <= rhs + M * step + 1e-3).all()
+    assert qt.max() <= 255 and (qt[table == table.min()] == 0).all()
+
+
+def test_4bit_quantize_packs_low_then_high_nibble(oracle):
+    rng = np.random.default_rng(9)
+    M, dsub, n = 8, 4, 50
+    cb = rng.normal(size=(M, 16, dsub)).astype(np.float32)
+    x = rng.normal(size=(n, M * dsub)).astype(np.float32)
+    packed = oracle.pq_quantize4("l2", cb, x)
+    assert packed.shape == (n, M // 2)
+    for i in range(n):
+        for m in range(M):
+            d = ((x[i, m * dsub:(m + 1) * dsub][None, :] - cb[m]) ** 2).sum(1)
+            code = (packed[i, m // 2] >> 4) if m & 1 else (packed[i, m // 2] & 15)
+            assert code == d.argmin()
+
+
+def test_4bit_search_in_partition_uses_the_quantised_scan(oracle):
+    from lance_b200.synth import IvfPqData
+    rng = np.random.default_rng(12)
+    d, nlist, M = 32, 3, 8
+    sizes = np.array([40, 0, 23])
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    N = int(sizes.sum())
+    data = IvfPqData("l2", d, nlist, M, rng.normal(size=(nlist, d)).astype(np.float32),
+                     rng.normal(size=(M, 16, d // M)).astype(np.float32), offs,
+                     rng.integers(0, 256, size=N * M // 2, dtype=np.uint8),
+                     rng.permutation(1000)[:N].astype(np.uint64), None, 4)
+    ox = oracle.OracleIndex(data)
+    key = rng.normal(size=d).astype(np.float32)
+    for p in (0, 1, 2):
+        dist, ids = ox.search_in_partition(p, key, 5)
+        table = oracle.build_distance_table4("l2", data.codebook, ox.preprocess_query(p, key))
+        want = oracle.compute_pq_distance_4bit(table, data.part_codes(p))
+        o, e = int(offs[p]), int(offs[p + 1])
+        order = np.lexsort((data.row_ids[o:e], want))[:5]
+        assert ids.tolist() == data.row_ids[o:e][order].tolist()
+        assert np.array_equal(dist.view(np.uint32), want[order].view(np.uint32))
