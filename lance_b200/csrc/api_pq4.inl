@@ -78,7 +78,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     const size_t p0 = (size_t)q0 * P, pn = (size_t)qn * P;
     scan4_kernel<<<(uint32_t)pn, 256, smem, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim, M,
                                                    ix->d_centroids, ix->d_codebook, ix->d_part_off, ix->d_codes4,
-                                                   d_dist, stride, d_stats);
+                                                   ix->d_tail4, d_dist, stride, d_stats);
     CK(cudaGetLastError());
     flat_select_kernel<<<(uint32_t)pn, 256, (size_t)kp2 * 8, st>>>(d_dist, stride, stride, 1, stride, kprime, kp2,
                                                                    a.has_lower, a.lower, a.has_upper, a.upper,
@@ -164,6 +164,7 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   const uint32_t cb = M / 2;
   std::vector<uint8_t> h_codes((size_t)N * cb);
   std::vector<uint64_t> h_rid((size_t)N);
+  std::vector<uint8_t> h_tail((size_t)N);
   std::vector<float> h_raw(raw ? (size_t)N * dim : 0);
   std::vector<uint32_t> perm;
   uint32_t nonempty = 0;
@@ -176,8 +177,10 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
     std::stable_sort(perm.begin(), perm.end(), [&](uint32_t x, uint32_t y) { return row_ids[o + x] < row_ids[o + y]; });
     const uint8_t* src = codes + o * cb;
     uint8_t* dst = h_codes.data() + o * cb;
+    const uint64_t blocks = n >= 16 ? n - (n & 15) : 0;  // rows the reference runs through u8x16 (distance.rs:158)
     for (uint64_t i = 0; i < n; i++) {
       h_rid[o + i] = row_ids[o + perm[i]];
+      h_tail[o + i] = perm[i] >= blocks;
       for (uint32_t j = 0; j < cb; j++) dst[(size_t)j * n + i] = src[(size_t)j * n + perm[i]];
       if (raw) memcpy(h_raw.data() + (o + i) * dim, raw + (o + perm[i]) * dim, (size_t)dim * 4);
     }
@@ -196,12 +199,14 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   CK4(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
   CK4(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));
   CK4(cudaMalloc(&ix->d_codes4, std::max<size_t>((size_t)N * cb, 1)));
+  CK4(cudaMalloc(&ix->d_tail4, std::max<uint64_t>(N, 1)));
   CK4(cudaMemcpyAsync(ix->d_centroids, centroids, cent_b, cudaMemcpyHostToDevice, ix->stream));
   CK4(cudaMemcpyAsync(ix->d_codebook, codebook, cb_b, cudaMemcpyHostToDevice, ix->stream));
   CK4(cudaMemcpyAsync(ix->d_part_off, part_offsets, (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
   if (N) {
     CK4(cudaMemcpyAsync(ix->d_row_ids, h_rid.data(), N * 8, cudaMemcpyHostToDevice, ix->stream));
     CK4(cudaMemcpyAsync(ix->d_codes4, h_codes.data(), (size_t)N * cb, cudaMemcpyHostToDevice, ix->stream));
+    CK4(cudaMemcpyAsync(ix->d_tail4, h_tail.data(), (size_t)N, cudaMemcpyHostToDevice, ix->stream));
     if (raw) {
       CK4(cudaMalloc(&ix->d_raw, (size_t)N * dim * 4));
       CK4(cudaMemcpyAsync(ix->d_raw, h_raw.data(), (size_t)N * dim * 4, cudaMemcpyHostToDevice, ix->stream));

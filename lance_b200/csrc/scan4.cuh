@@ -14,6 +14,7 @@
 //
 // Layout: codes4 = concat over partitions of [M/2][n_p] bytes (the reference's transposed 4-bit storage), rows of a
 // partition sorted by row id at create time so that (distance, local index) order == (distance, row id) order.
+// Step 3 depends on a row's POSITION in the reference's order (block or tail), so tail4[row] keeps that bit.
 // This is the first correct path for 4-bit PQ (SURVEY 8(a) row A5''): distances of a pair are written to an HBM
 // scratch row and selected by flat_select_kernel, as the reference's distance_all + sort does; it is not tuned.
 #pragma once
@@ -33,8 +34,9 @@ __device__ __forceinline__ uint8_t sat_u8(float v) {  // Rust `f32 as u8`
 __global__ void __launch_bounds__(256)
 scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
              uint32_t M, const float* __restrict__ centroids, const float* __restrict__ codebook /*[M][16][dsub]*/,
-             const uint64_t* __restrict__ part_off, const uint8_t* __restrict__ codes4, float* __restrict__ out,
-             size_t out_stride, unsigned long long* __restrict__ stats) {
+             const uint64_t* __restrict__ part_off, const uint8_t* __restrict__ codes4,
+             const uint8_t* __restrict__ tail4, float* __restrict__ out, size_t out_stride,
+             unsigned long long* __restrict__ stats) {
   extern __shared__ float sm4[];
   float* r = sm4;                 // [dim] residual (or the key for dot)
   float* T = sm4 + dim;           // [M][16]
@@ -79,14 +81,13 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
     qt[e] = sat_u8(ceilf(__fdiv_rn(__fmul_rn(__fsub_rn(T[e], qmin), 255.0f), range)));
   __syncthreads();
   const uint64_t off = part_off[p], n = part_off[p + 1] - off;
-  const uint64_t blocks = n >= 16 ? n - (n & 15) : 0;
   const uint8_t* cp = codes4 + off * (M / 2);
   float* orow = out + (size_t)pair * out_stride;
   for (uint64_t i = tid; i < out_stride; i += 256) {
     float v = __int_as_float(0x7fc00000);
     if (i < n) {
       uint32_t acc = 0;
-      const bool blk = i < blocks;
+      const bool blk = !tail4[off + i];  // was this row in a whole 16-row block of the reference's order?
       for (uint32_t j = 0; j < M / 2; j++) {
         const uint8_t b = cp[(size_t)j * n + i];
         const uint32_t lo = qt[(2 * j) * 16 + (b & 15)], hi = qt[(2 * j + 1) * 16 + (b >> 4)];
