@@ -37,7 +37,12 @@ WORKLOADS = {
     "cfg3": (1_000_000, 1536, 1024, 96, "cosine", 102, 10, 5, 1000,
              "dbpedia-openai-shaped 1Mx1536 cosine IVF1024,PQ96, k=10, refine_factor=5, nprobes=102 (BASELINE configs[2])"),
     "tiny": (200_000, 128, 64, 16, "l2", 8, 10, 0, 512, "tiny CI workload"),
+    # SURVEY 8(a) row A5'': the same shape as cfg1 with 4-bit PQ codes (not a BASELINE config)
+    "cfg1_pq4": (1_000_000, 128, 256, 16, "l2", 20, 10, 0, 10_000,
+                 "SIFT-shaped 1Mx128 f32, IVF256,PQ16 4-bit, L2, k=10, nprobes=20, 10k queries (cfg1 shape, num_bits=4)"),
 }
+PQ_BITS = {"cfg1_pq4": 4}
+_BITS = 8  # set by main() from the workload
 
 
 def partition_sizes(N, nlist, seed, sigma=0.5):
@@ -56,19 +61,20 @@ def make_shard(wl, seed, rank, world, keep_raw=False):
     (scan cost is value independent), seeded per partition so every rank builds only its shard."""
     from lance_b200.synth import IvfPqData
     N, d, nlist, M, metric = wl[0], wl[1], wl[2], wl[3], wl[4]
+    ncent, cbytes = (16, M // 2) if _BITS == 4 else (256, M)
     sizes = partition_sizes(N, nlist, seed)
     owner = assign_partitions(sizes, world)
     rng = np.random.default_rng(seed + 1)
     if metric == "dot":
         cents = rng.normal(size=(nlist, d)).astype(np.float32)
-        codebook = rng.normal(size=(M, 256, d // M)).astype(np.float32)
+        codebook = rng.normal(size=(M, ncent, d // M)).astype(np.float32)
     elif metric == "cosine":
         cents = rng.normal(size=(nlist, d)).astype(np.float32)
         cents /= np.linalg.norm(cents, axis=1, keepdims=True)
-        codebook = (rng.normal(size=(M, 256, d // M)) * 0.02).astype(np.float32)
+        codebook = (rng.normal(size=(M, ncent, d // M)) * 0.02).astype(np.float32)
     else:
         cents = rng.uniform(0, 128, size=(nlist, d)).astype(np.float32)
-        codebook = rng.normal(0, 16, size=(M, 256, d // M)).astype(np.float32)
+        codebook = rng.normal(0, 16, size=(M, ncent, d // M)).astype(np.float32)
     goffs = np.zeros(nlist + 1, dtype=np.int64)
     goffs[1:] = np.cumsum(sizes)
     mine = owner == rank
@@ -76,18 +82,18 @@ def make_shard(wl, seed, rank, world, keep_raw=False):
     offs = np.zeros(nlist + 1, dtype=np.uint64)
     offs[1:] = np.cumsum(lsizes)
     n_local = int(offs[-1])
-    codes = np.empty(n_local * M, dtype=np.uint8)
+    codes = np.empty(n_local * cbytes, dtype=np.uint8)
     rids = np.empty(n_local, dtype=np.uint64)
     raw = np.empty((n_local, d), dtype=np.float32) if keep_raw else None
     for p in np.nonzero(mine)[0]:
         prng = np.random.default_rng([seed, int(p)])
         o, n = int(offs[p]), int(sizes[p])
-        codes[o * M:(o + n) * M] = prng.integers(0, 256, size=n * M, dtype=np.uint8)
+        codes[o * cbytes:(o + n) * cbytes] = prng.integers(0, 256, size=n * cbytes, dtype=np.uint8)
         gpos = np.arange(goffs[p], goffs[p] + n, dtype=np.uint64)
         rids[o:o + n] = (gpos * np.uint64(2654435761)) % np.uint64(1 << 32)  # bijection on u32
         if keep_raw:
             raw[o:o + n] = cents[p] + prng.normal(0, 0.05 if metric == "cosine" else 8.0, size=(n, d)).astype(np.float32)
-    data = IvfPqData(metric, d, nlist, M, cents, codebook, offs, codes, rids, raw)
+    data = IvfPqData(metric, d, nlist, M, cents, codebook, offs, codes, rids, raw, _BITS)
     return data, sizes, owner
 
 
@@ -298,6 +304,8 @@ def main():
         run_flat(args)
         return
     wl = WORKLOADS[args.workload]
+    global _BITS
+    _BITS = PQ_BITS.get(args.workload, 8)
     if args.queries:
         wl = wl[:8] + (args.queries, wl[9].replace("%d queries" % wl[8], "%d queries" % args.queries)
                        .replace("10k queries", "%d queries" % args.queries))
@@ -457,6 +465,8 @@ def main():
         pre = os.environ["LB200_LUT_PREPASS"] != "0"
     pre = pre and (d // M) in (8, 16)
     kname = "scan_kernel"
+    if st["scan_variant"] == 4:
+        kname = "scan4_kernel + flat_select_kernel (4-bit PQ)"
     if st["scan_variant"] == 3:
         kname = "scan3_kernel" if (shard_mode or nprobes < 16 or pre) else "scan3_nb_kernel"
         if pre:

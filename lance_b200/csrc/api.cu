@@ -93,6 +93,7 @@ struct lb200_index {
   uint8_t* d_codes = nullptr;          // tile16 layout (variants 1/2), or null
   uint8_t* d_codes3 = nullptr;         // skew-stream layout (variant 3), or null
   uint8_t* d_codes4 = nullptr;         // 4-bit PQ: concat over p of [M/2][n_p], rows sorted by row id
+  uint64_t* d_pad_off = nullptr;       // 4-bit PQ: [nlist+1] prefix sum of partition rows padded to 16
   uint8_t* d_tail4 = nullptr;          // 4-bit PQ: [N] 1 = row sat in the n % 16 tail of the reference's order
   uint32_t bits = 8;                   // PQ code width
   uint64_t* d_sb_off = nullptr;        // [nlist+1] first superblock per partition
@@ -298,6 +299,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_codes3);
   cudaFree(ix->d_codes4);
   cudaFree(ix->d_tail4);
+  cudaFree(ix->d_pad_off);
   cudaFree(ix->d_sb_off);
   cudaFree(ix->arena.base);
   cudaFree(ix->stage.base);

@@ -21,10 +21,16 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   // queries per tile: the [pairs][stride] distance scratch stays below 512 MB
   const uint32_t tileQ = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(Q, (512ull << 20) / (stride * 4 * P)));
   const size_t tpairs = (size_t)tileQ * P, npairs = (size_t)Q * P;
+  // fused histogram-select kernel (scan4.cuh) unless its shared memory does not fit or LB200_PQ4_SIMPLE=1 asks for
+  // the distance-scratch path (kept as the A/B check of the fused select)
+  const uint32_t kp2 = std::max(2u, next_pow2(kprime));
+  const uint32_t nbins = (M / 2) * 510 + 1;
+  const size_t fsmem = ((size_t)dim + (size_t)M * 16 + ((M + 1) & ~1u)) * 4 + (size_t)kp2 * 8 + (size_t)nbins * 4 + (size_t)M * 16;
+  const bool fused = fsmem <= ix->smem_optin && !getenv("LB200_PQ4_SIMPLE");
   size_t need = 0;
   auto add = [&](size_t b) { need += Arena::pad(b) + 256; };
   add((size_t)Q * dim * 4); add((size_t)Q * nlist * 4); add(npairs * 4); add(64);
-  add(tpairs * stride * 4);
+  add(fused ? 256 : tpairs * stride * 4);
   add(npairs * kprime * 4); add(npairs * kprime * 8); add(npairs * kprime * 8); add(npairs * kprime * 8); add(npairs * 4);
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
   add((size_t)Q * kprime * 4);
@@ -35,7 +41,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   float* d_D = ix->arena.take<float>((size_t)Q * nlist);
   uint32_t* d_probes = ix->arena.take<uint32_t>(npairs);
   unsigned long long* d_stats = ix->arena.take<unsigned long long>(8);
-  float* d_dist = ix->arena.take<float>(tpairs * stride);
+  float* d_dist = ix->arena.take<float>(fused ? 64 : tpairs * stride);
   float* d_sdist = ix->arena.take<float>(npairs * kprime);
   uint64_t* d_sidx = ix->arena.take<uint64_t>(npairs * kprime);
   uint64_t* d_srow = ix->arena.take<uint64_t>(npairs * kprime);
@@ -68,17 +74,27 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   CK(cudaMemsetAsync(d_stats, 0, 32, st));
   const size_t smem = ((size_t)dim + (size_t)M * 16 + M) * 4 + (size_t)M * 16;
   if (smem > 48 * 1024) CK(cudaFuncSetAttribute(scan4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const uint32_t kp2 = std::max(2u, next_pow2(kprime));
   // the per-pair cut: FlatIndex::search keeps [lower, upper) and the first k' (flat/index.rs:97-126)
   float* pd = a.per_pair_output ? a.d_out_dist : d_sdist;
   uint32_t* pc = a.per_pair_output ? a.d_out_count : d_scnt;
+  uint64_t* prow = a.per_pair_output ? a.d_out_rowid : d_srow;
   if (prof) CK(cudaEventRecord(ix->ev[2], st));
-  for (uint32_t q0 = 0; q0 < Q; q0 += tileQ) {
+  if (fused) {
+    if (fsmem > 48 * 1024) CK(cudaFuncSetAttribute(scan4f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+    scan4f_kernel<<<(uint32_t)npairs, 256, fsmem, st>>>(ix->metric, keys, probes, P, dim, M, ix->d_centroids,
+                                                        ix->d_codebook, ix->d_part_off, ix->d_pad_off, ix->d_codes4,
+                                                        ix->d_tail4, ix->d_row_ids, kprime, kp2, a.has_lower, a.lower,
+                                                        a.has_upper, a.upper, pd, prow,
+                                                        a.per_pair_output ? nullptr : d_spos, pc, d_stats);
+    CK(cudaGetLastError());
+    launches++;
+  }
+  for (uint32_t q0 = 0; q0 < Q && !fused; q0 += tileQ) {
     const uint32_t qn = std::min(tileQ, Q - q0);
     const size_t p0 = (size_t)q0 * P, pn = (size_t)qn * P;
     scan4_kernel<<<(uint32_t)pn, 256, smem, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim, M,
-                                                   ix->d_centroids, ix->d_codebook, ix->d_part_off, ix->d_codes4,
-                                                   ix->d_tail4, d_dist, stride, d_stats);
+                                                   ix->d_centroids, ix->d_codebook, ix->d_part_off, ix->d_pad_off,
+                                                   ix->d_codes4, ix->d_tail4, d_dist, stride, d_stats);
     CK(cudaGetLastError());
     flat_select_kernel<<<(uint32_t)pn, 256, (size_t)kp2 * 8, st>>>(d_dist, stride, stride, 1, stride, kprime, kp2,
                                                                    a.has_lower, a.lower, a.has_upper, a.upper,
@@ -87,11 +103,12 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     launches += 2;
   }
   if (prof) CK(cudaEventRecord(ix->ev[3], st));
-  gather4_kernel<<<(uint32_t)((npairs * kprime + 255) / 256), 256, 0, st>>>(
-      probes, ix->d_part_off, ix->d_row_ids, d_sidx, pc, npairs, kprime, a.per_pair_output ? a.d_out_rowid : d_srow,
-      a.per_pair_output ? nullptr : d_spos);
-  CK(cudaGetLastError());
-  launches++;
+  if (!fused) {
+    gather4_kernel<<<(uint32_t)((npairs * kprime + 255) / 256), 256, 0, st>>>(
+        probes, ix->d_part_off, ix->d_row_ids, d_sidx, pc, npairs, kprime, prow, a.per_pair_output ? nullptr : d_spos);
+    CK(cudaGetLastError());
+    launches++;
+  }
   if (!a.per_pair_output) {
     const bool direct = !refine;
     rc = launch_merge(d_sdist, d_srow, d_spos, nullptr, d_scnt, Q, P, kprime, (size_t)P * kprime, kprime, P, 1, kprime,
@@ -125,6 +142,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   }
   stats.kernel_launches = launches;
   stats.scan_variant = 4;
+  stats.scan_items = (uint32_t)npairs;
   stats.scan_ql = 1;
   ix->stats = stats;
   return 0;
@@ -162,7 +180,10 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   } while (0)
   // rows of a partition sorted by row id: (distance, local index) order == (distance, row id) order (scan4.cuh)
   const uint32_t cb = M / 2;
-  std::vector<uint8_t> h_codes((size_t)N * cb);
+  std::vector<uint64_t> pad_off(nlist + 1, 0);
+  for (uint32_t p = 0; p < nlist; p++) pad_off[p + 1] = pad_off[p] + ((part_offsets[p + 1] - part_offsets[p] + 15) & ~15ull);
+  const uint64_t NP = pad_off[nlist];
+  std::vector<uint8_t> h_codes((size_t)NP * cb, 0);
   std::vector<uint64_t> h_rid((size_t)N);
   std::vector<uint8_t> h_tail((size_t)N);
   std::vector<float> h_raw(raw ? (size_t)N * dim : 0);
@@ -176,12 +197,13 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
     for (uint64_t i = 0; i < n; i++) perm[i] = (uint32_t)i;
     std::stable_sort(perm.begin(), perm.end(), [&](uint32_t x, uint32_t y) { return row_ids[o + x] < row_ids[o + y]; });
     const uint8_t* src = codes + o * cb;
-    uint8_t* dst = h_codes.data() + o * cb;
+    const uint64_t npad = pad_off[p + 1] - pad_off[p];
+    uint8_t* dst = h_codes.data() + pad_off[p] * cb;
     const uint64_t blocks = n >= 16 ? n - (n & 15) : 0;  // rows the reference runs through u8x16 (distance.rs:158)
     for (uint64_t i = 0; i < n; i++) {
       h_rid[o + i] = row_ids[o + perm[i]];
       h_tail[o + i] = perm[i] >= blocks;
-      for (uint32_t j = 0; j < cb; j++) dst[(size_t)j * n + i] = src[(size_t)j * n + perm[i]];
+      for (uint32_t j = 0; j < cb; j++) dst[(size_t)j * npad + i] = src[(size_t)j * n + perm[i]];
       if (raw) memcpy(h_raw.data() + (o + i) * dim, raw + (o + perm[i]) * dim, (size_t)dim * 4);
     }
   }
@@ -198,14 +220,16 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   CK4(cudaMalloc(&ix->d_codebook, cb_b));
   CK4(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
   CK4(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));
-  CK4(cudaMalloc(&ix->d_codes4, std::max<size_t>((size_t)N * cb, 1)));
+  CK4(cudaMalloc(&ix->d_codes4, std::max<size_t>((size_t)NP * cb, 16)));
+  CK4(cudaMalloc(&ix->d_pad_off, (nlist + 1) * 8));
+  CK4(cudaMemcpyAsync(ix->d_pad_off, pad_off.data(), (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
   CK4(cudaMalloc(&ix->d_tail4, std::max<uint64_t>(N, 1)));
   CK4(cudaMemcpyAsync(ix->d_centroids, centroids, cent_b, cudaMemcpyHostToDevice, ix->stream));
   CK4(cudaMemcpyAsync(ix->d_codebook, codebook, cb_b, cudaMemcpyHostToDevice, ix->stream));
   CK4(cudaMemcpyAsync(ix->d_part_off, part_offsets, (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
   if (N) {
     CK4(cudaMemcpyAsync(ix->d_row_ids, h_rid.data(), N * 8, cudaMemcpyHostToDevice, ix->stream));
-    CK4(cudaMemcpyAsync(ix->d_codes4, h_codes.data(), (size_t)N * cb, cudaMemcpyHostToDevice, ix->stream));
+    CK4(cudaMemcpyAsync(ix->d_codes4, h_codes.data(), (size_t)NP * cb, cudaMemcpyHostToDevice, ix->stream));
     CK4(cudaMemcpyAsync(ix->d_tail4, h_tail.data(), (size_t)N, cudaMemcpyHostToDevice, ix->stream));
     if (raw) {
       CK4(cudaMalloc(&ix->d_raw, (size_t)N * dim * 4));

@@ -12,14 +12,16 @@
 // Everything between the table and step 4 is integer arithmetic, so the result is bit-identical by construction;
 // the f32 steps use explicit round-to-nearest intrinsics in the reference's order (no FMA contraction).
 //
-// Layout: codes4 = concat over partitions of [M/2][n_p] bytes (the reference's transposed 4-bit storage), rows of a
-// partition sorted by row id at create time so that (distance, local index) order == (distance, row id) order.
+// Layout: codes4p = concat over partitions of [M/2][npad] bytes (the reference's transposed 4-bit storage with the row
+// count padded to a multiple of 16), rows of a partition sorted by row id at create time so that (distance, local
+// index) order == (distance, row id) order.
 // Step 3 depends on a row's POSITION in the reference's order (block or tail), so tail4[row] keeps that bit.
 // This is the first correct path for 4-bit PQ (SURVEY 8(a) row A5''): distances of a pair are written to an HBM
 // scratch row and selected by flat_select_kernel, as the reference's distance_all + sort does; it is not tuned.
 #pragma once
 #include <cstdint>
 
+#include "coarse.cuh"
 #include "dist.cuh"
 
 namespace lb200 {
@@ -34,9 +36,9 @@ __device__ __forceinline__ uint8_t sat_u8(float v) {  // Rust `f32 as u8`
 __global__ void __launch_bounds__(256)
 scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
              uint32_t M, const float* __restrict__ centroids, const float* __restrict__ codebook /*[M][16][dsub]*/,
-             const uint64_t* __restrict__ part_off, const uint8_t* __restrict__ codes4,
-             const uint8_t* __restrict__ tail4, float* __restrict__ out, size_t out_stride,
-             unsigned long long* __restrict__ stats) {
+             const uint64_t* __restrict__ part_off, const uint64_t* __restrict__ pad_off,
+             const uint8_t* __restrict__ codes4p, const uint8_t* __restrict__ tail4, float* __restrict__ out,
+             size_t out_stride, unsigned long long* __restrict__ stats) {
   extern __shared__ float sm4[];
   float* r = sm4;                 // [dim] residual (or the key for dot)
   float* T = sm4 + dim;           // [M][16]
@@ -81,7 +83,8 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
     qt[e] = sat_u8(ceilf(__fdiv_rn(__fmul_rn(__fsub_rn(T[e], qmin), 255.0f), range)));
   __syncthreads();
   const uint64_t off = part_off[p], n = part_off[p + 1] - off;
-  const uint8_t* cp = codes4 + off * (M / 2);
+  const uint64_t npad = pad_off[p + 1] - pad_off[p];
+  const uint8_t* cp = codes4p + pad_off[p] * (M / 2);
   float* orow = out + (size_t)pair * out_stride;
   for (uint64_t i = tid; i < out_stride; i += 256) {
     float v = __int_as_float(0x7fc00000);
@@ -89,7 +92,7 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
       uint32_t acc = 0;
       const bool blk = !tail4[off + i];  // was this row in a whole 16-row block of the reference's order?
       for (uint32_t j = 0; j < M / 2; j++) {
-        const uint8_t b = cp[(size_t)j * n + i];
+        const uint8_t b = cp[(size_t)j * npad + i];
         const uint32_t lo = qt[(2 * j) * 16 + (b & 15)], hi = qt[(2 * j + 1) * 16 + (b >> 4)];
         acc += blk ? ((lo + hi) & 255u) : (lo + hi);
       }
@@ -100,6 +103,284 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
   if (stats && tid == 0) {
     atomicAdd(&stats[0], (unsigned long long)n * (M / 2));
     atomicAdd(&stats[1], 1ull);
+  }
+}
+
+// ---- fused variant -------------------------------------------------------------------------------------------
+// Same arithmetic, no HBM distance scratch: the pre-dequantisation sum S of a row is a small integer
+// (<= (M/2) * 510), so the CTA selects on a shared-memory HISTOGRAM of S instead of on floats.
+//   pass 1  S of every admissible row -> hist[S]; after the first 1024 rows the k'-th smallest so far bounds which
+//           rows still need counting (rows above it can never be selected), so the atomics stop early;
+//   select  k'-th smallest: bin S*; T = f(S*) with f = the reference's dequantisation; because f may map adjacent S
+//           to one float, "ties" are all bins with f(S) == T and are taken in row order (= row id order);
+//   pass 2  re-reads the codes (L2-resident: one partition), gathers rows below T and the first ties, sorts the
+//           <= k' keys and writes (distance, row id, index position).
+// Codes: layout `codes4p` = per partition [M/2][npad], npad = n rounded up to 16, base 16-byte aligned, so a thread
+// takes 4 consecutive rows of a plane with one 32-bit load and a warp reads 128 contiguous bytes.
+// [lower, upper) is applied on f(S) (exactly the float the reference filters on).
+struct Scan4Sel {
+  uint32_t s_lt, s_hi, nless, need_ties, have_kth;
+};
+
+__device__ __forceinline__ float dequant4(uint32_t S, float range, float qmin) {
+  return __fadd_rn(__fdiv_rn(__fmul_rn((float)S, range), 255.0f), qmin);
+}
+
+// k-th smallest over hist[0..nbins): fills sel (thread 0), all threads must call. scratch: part[256].
+__device__ __forceinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nbins, uint32_t k, float range, float qmin,
+                                               uint32_t* part, Scan4Sel* sel) {
+  const uint32_t tid = threadIdx.x, chunk = (nbins + 255) / 256;
+  const uint32_t b0 = tid * chunk, b1 = min(nbins, b0 + chunk);
+  uint32_t c = 0;
+  for (uint32_t b = b0; b < b1; b++) c += hist[b];
+  part[tid] = c;
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t cum = 0, t = 0;
+    for (; t < 256; t++) {
+      if (cum + part[t] >= k) break;
+      cum += part[t];
+    }
+    if (t == 256) {
+      sel->have_kth = 0;
+      sel->s_lt = nbins;   // everything counted is "less"
+      sel->s_hi = nbins - 1;
+      sel->nless = cum;
+      sel->need_ties = 0;
+    } else {
+      uint32_t b = t * chunk;
+      for (;; b++) {
+        if (cum + hist[b] >= k) break;
+        cum += hist[b];
+      }
+      // bins whose dequantised float equals the threshold's: ties are taken in row order across all of them
+      const float T = dequant4(b, range, qmin);
+      uint32_t lo = b, hi = b;
+      while (lo > 0 && dequant4(lo - 1, range, qmin) == T) {
+        lo--;
+        cum -= hist[lo];
+      }
+      while (hi + 1 < nbins && dequant4(hi + 1, range, qmin) == T) hi++;
+      sel->have_kth = 1;
+      sel->s_lt = lo;
+      sel->s_hi = hi;
+      sel->nless = cum;
+      sel->need_ties = k - cum;
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
+              uint32_t M, const float* __restrict__ centroids, const float* __restrict__ codebook,
+              const uint64_t* __restrict__ part_off, const uint64_t* __restrict__ pad_off /*[nlist+1] padded rows*/,
+              const uint8_t* __restrict__ codes4p, const uint8_t* __restrict__ tail4,
+              const uint64_t* __restrict__ row_ids, uint32_t kprime, uint32_t kpow2, int has_lower, float lower,
+              int has_upper, float upper, float* __restrict__ out_dist, uint64_t* __restrict__ out_rowid,
+              uint64_t* __restrict__ out_pos, uint32_t* __restrict__ out_cnt, unsigned long long* __restrict__ stats) {
+  extern __shared__ float sm4[];
+  const uint32_t nbins = (M / 2) * 510 + 1;
+  float* r = sm4;
+  float* T = sm4 + dim;
+  float* smax = T + (size_t)M * 16;
+  unsigned long long* sl = (unsigned long long*)(smax + ((M + 1) & ~1u));  // [kpow2], 8-byte aligned
+  uint32_t* hist = (uint32_t*)(sl + kpow2);                                  // [nbins]
+  uint8_t* qt = (uint8_t*)(hist + nbins);                                    // [M][16]
+  __shared__ float s_red[8];
+  __shared__ float s_qmin, s_qmax;
+  __shared__ uint32_t s_part[256], s_wsum[8], s_fill, s_tiebase, s_adm[3];
+  __shared__ Scan4Sel s_sel;
+  const uint32_t pair = blockIdx.x, q = pair / P, p = probes[pair], tid = threadIdx.x;
+  const uint32_t dsub = dim / M;
+  const float* key = keys + (size_t)q * dim;
+  const float* c = centroids + (size_t)p * dim;
+  for (uint32_t i = tid; i < dim; i += 256) r[i] = metric == 2 ? key[i] : __fsub_rn(key[i], c[i]);
+  for (uint32_t b = tid; b < nbins; b += 256) hist[b] = 0;
+  for (uint32_t i = tid; i < kpow2; i += 256) sl[i] = ~0ull;
+  if (tid == 0) {
+    s_fill = 0;
+    s_tiebase = 0;
+  }
+  __syncthreads();
+  float lmin = __int_as_float(0x7f800000);
+  for (uint32_t e = tid; e < M * 16; e += 256) {
+    const uint32_t m = e >> 4;
+    const float* cb = codebook + (size_t)e * dsub;
+    float v = metric == 2 ? dot_distance(r + (size_t)m * dsub, cb, (int)dsub) : l2_batch_elem(r + (size_t)m * dsub, cb, (int)dsub);
+    T[e] = v;
+    lmin = fminf(lmin, v);
+  }
+  for (int o = 16; o; o >>= 1) lmin = fminf(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+  if ((tid & 31) == 0) s_red[tid >> 5] = lmin;
+  __syncthreads();
+  for (uint32_t m = tid; m < M; m += 256) {
+    float mx = __int_as_float(0xff800000);
+    for (int j = 0; j < 16; j++) mx = fmaxf(mx, T[m * 16 + j]);
+    smax[m] = mx;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float mn = s_red[0];
+    for (int w = 1; w < 8; w++) mn = fminf(mn, s_red[w]);
+    float mx = __int_as_float(0xff800000);
+    for (uint32_t m = 0; m + 1 < M; m++) mx = fmaxf(mx, __fadd_rn(smax[m], smax[m + 1]));
+    s_qmin = mn;
+    s_qmax = mx;
+  }
+  __syncthreads();
+  const float qmin = s_qmin, range = __fsub_rn(s_qmax, s_qmin);
+  for (uint32_t e = tid; e < M * 16; e += 256)
+    qt[e] = sat_u8(ceilf(__fdiv_rn(__fmul_rn(__fsub_rn(T[e], qmin), 255.0f), range)));
+  __syncthreads();
+
+  const uint64_t off = part_off[p], n = part_off[p + 1] - off;
+  const uint64_t poff = pad_off[p], npad = pad_off[p + 1] - poff;
+  const uint8_t* cp = codes4p + poff * (M / 2);
+  const uint8_t* tl = tail4 + off;
+  auto admissible_f = [&](uint32_t S) {
+    const float v = dequant4(S, range, qmin);
+    bool ok = v == v;
+    if (has_lower) ok = ok && v >= lower;
+    if (has_upper) ok = ok && v < upper;
+    return ok;
+  };
+  // f is monotone non-decreasing in S when range >= 0 and finite: [lower, upper) on floats becomes a range of S,
+  // found once per CTA; no bounds -> every S is admissible (f finite or +inf, never NaN); anything else per row.
+  if (tid == 0) {
+    const bool fin = (range - range == 0.0f) && (qmin - qmin == 0.0f);
+    uint32_t mode = 2, alo = 0, ahi = nbins;
+    if (fin && !has_lower && !has_upper) mode = 0;
+    else if (fin && range >= 0.0f) {
+      mode = 1;
+      auto first_ge = [&](float x) {  // first S in [0, nbins] with f(S) >= x
+        uint32_t lo = 0, hi = nbins;
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (dequant4(mid, range, qmin) >= x) hi = mid; else lo = mid + 1;
+        }
+        return lo;
+      };
+      if (has_lower) alo = (lower == lower) ? first_ge(lower) : nbins;
+      if (has_upper) ahi = (upper == upper) ? first_ge(upper) : 0;
+    }
+    s_adm[0] = mode; s_adm[1] = alo; s_adm[2] = ahi;
+  }
+  __syncthreads();
+  const uint32_t amode = s_adm[0], alo = s_adm[1], ahi = s_adm[2];
+  auto admissible = [&](uint32_t S) {
+    if (amode == 0) return true;
+    if (amode == 1) return S >= alo && S < ahi;
+    return admissible_f(S);
+  };
+  // S of the 4 rows i0..i0+3 (i0 % 4 == 0, i0 < npad)
+  auto sums4 = [&](uint64_t i0, uint32_t S[4]) {
+    uint32_t blkmask = 0;  // bit r set: row is a block row (wrapping pair sums)
+#pragma unroll
+    for (int rr = 0; rr < 4; rr++) {
+      S[rr] = 0;
+      if (i0 + rr < n && !tl[i0 + rr]) blkmask |= 1u << rr;
+    }
+    for (uint32_t j = 0; j < M / 2; j++) {
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(cp + (size_t)j * npad + i0);
+      const uint8_t* t0 = qt + (2 * j) * 16;
+      const uint8_t* t1 = t0 + 16;
+#pragma unroll
+      for (int rr = 0; rr < 4; rr++) {
+        const uint32_t b = (w >> (8 * rr)) & 255u;
+        const uint32_t sum = (uint32_t)t0[b & 15] + (uint32_t)t1[b >> 4];
+        S[rr] += ((blkmask >> rr) & 1u) ? (sum & 255u) : sum;
+      }
+    }
+  };
+
+  // ---- pass 1: histogram of S -------------------------------------------------------------------------------
+  uint32_t bound = nbins - 1;
+  for (uint64_t base = 0; base < n; base += 1024) {
+    const uint64_t i0 = base + (uint64_t)tid * 4;
+    if (i0 < n) {
+      uint32_t S[4];
+      sums4(i0, S);
+#pragma unroll
+      for (int rr = 0; rr < 4; rr++)
+        if (i0 + rr < n && S[rr] <= bound && admissible(S[rr])) atomicAdd(&hist[S[rr]], 1u);
+    }
+    if (base == 0 && n > 1024) {
+      __syncthreads();
+      scan4_find_kth(hist, nbins, kprime, range, qmin, s_part, &s_sel);
+      if (s_sel.have_kth) bound = s_sel.s_hi;
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+  scan4_find_kth(hist, nbins, kprime, range, qmin, s_part, &s_sel);
+  const uint32_t s_lt = s_sel.s_lt, s_hi = s_sel.s_hi, nless = s_sel.nless, need_ties = s_sel.need_ties;
+  const bool have_kth = s_sel.have_kth != 0;
+
+  // ---- pass 2: gather -----------------------------------------------------------------------------------------
+  const uint32_t lane = tid & 31, wrp = tid >> 5;
+  for (uint64_t base = 0; base < n; base += 1024) {
+    const uint64_t i0 = base + (uint64_t)tid * 4;
+    uint32_t S[4] = {0, 0, 0, 0};
+    uint32_t tmask = 0;  // rows of this thread that tie with the threshold
+    if (i0 < n) {
+      sums4(i0, S);
+#pragma unroll
+      for (int rr = 0; rr < 4; rr++) {
+        if (i0 + rr >= n || S[rr] > bound || !admissible(S[rr])) continue;
+        if (S[rr] < s_lt) {
+          const uint32_t o = atomicAdd(&s_fill, 1u);
+          sl[o] = ((unsigned long long)ordered_key(dequant4(S[rr], range, qmin)) << 32) | (uint32_t)(i0 + rr);
+        } else if (have_kth && S[rr] <= s_hi) {
+          tmask |= 1u << rr;
+        }
+      }
+    }
+    if (have_kth && s_tiebase < need_ties) {  // uniform across the CTA: s_tiebase changes only between barriers
+      // rank of this thread's ties in row order: threads hold consecutive rows, warps consecutive threads
+      const uint32_t cnt = __popc(tmask);
+      uint32_t incl = cnt;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (uint32_t)o) incl += v;
+      }
+      if (lane == 31) s_wsum[wrp] = incl;
+      __syncthreads();
+      uint32_t before = s_tiebase + incl - cnt;
+      for (uint32_t ww = 0; ww < wrp; ww++) before += s_wsum[ww];
+#pragma unroll
+      for (int rr = 0; rr < 4; rr++) {
+        if (!((tmask >> rr) & 1u)) continue;
+        if (before < need_ties)
+          sl[nless + before] = ((unsigned long long)ordered_key(dequant4(S[rr], range, qmin)) << 32) | (uint32_t)(i0 + rr);
+        before++;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        uint32_t tot = 0;
+        for (int ww = 0; ww < 8; ww++) tot += s_wsum[ww];
+        s_tiebase += tot;
+      }
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+  const uint32_t cnt = have_kth ? kprime : s_fill;
+  block_bitonic_sort_u64(sl, kpow2);
+  for (uint32_t i = tid; i < kprime; i += 256) {
+    const unsigned long long v = sl[i];
+    const bool ok = i < cnt;
+    const uint64_t pos = off + (uint32_t)v;
+    out_dist[(size_t)pair * kprime + i] = ok ? key_to_float((uint32_t)(v >> 32)) : __int_as_float(0x7f800000);
+    out_rowid[(size_t)pair * kprime + i] = ok ? row_ids[pos] : ~0ull;
+    if (out_pos) out_pos[(size_t)pair * kprime + i] = ok ? pos : 0;
+  }
+  if (tid == 0) {
+    out_cnt[pair] = cnt;
+    if (stats) {
+      atomicAdd(&stats[0], (unsigned long long)n * (M / 2));
+      atomicAdd(&stats[1], 1ull);
+    }
   }
 }
 

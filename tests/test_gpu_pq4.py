@@ -36,18 +36,30 @@ def _index4(metric, d, nlist, M, sizes, seed, keep_raw=False, scale=1.0):
 
 
 def _check_search(oracle, data, q, cases):
+    """Every case through both device paths: the fused histogram-select kernel (default) and the distance-scratch +
+    flat_select path (LB200_PQ4_SIMPLE=1, read per call)."""
+    import os
     from lance_b200 import IvfPqIndex, Query
     ix, ox = IvfPqIndex(data), oracle.OracleIndex(data)
-    for k, nprobes, rf, lo, hi in cases:
-        gd, gi, gc = ix.search(Query(q, k=k, nprobes=nprobes, refine_factor=rf or None, lower_bound=lo, upper_bound=hi))
-        rd, ri, rc, _ = ox.search(q, k, nprobes, rf, lo, hi)
-        assert gc.tolist() == rc.tolist(), f"counts k={k} P={nprobes} rf={rf}"
-        for j in range(len(q)):
-            n = int(rc[j])
-            assert gi[j, :n].tolist() == ri[j, :n].tolist(), f"row ids k={k} P={nprobes} rf={rf} [{lo},{hi}) q{j}"
-            assert _bits(gd[j, :n]).tolist() == _bits(rd[j, :n]).tolist(), f"distances k={k} P={nprobes} rf={rf} q{j}"
-    assert ix.stats()["scan_variant"] == 4
-    ix.close()
+    try:
+        for k, nprobes, rf, lo, hi in cases:
+            rd, ri, rc, _ = ox.search(q, k, nprobes, rf, lo, hi)
+            for simple in (False, True):
+                os.environ.pop("LB200_PQ4_SIMPLE", None)
+                if simple:
+                    os.environ["LB200_PQ4_SIMPLE"] = "1"
+                what = f"{'simple' if simple else 'fused'} k={k} P={nprobes} rf={rf} [{lo},{hi})"
+                gd, gi, gc = ix.search(Query(q, k=k, nprobes=nprobes, refine_factor=rf or None, lower_bound=lo,
+                                             upper_bound=hi))
+                assert gc.tolist() == rc.tolist(), f"counts {what}"
+                for j in range(len(q)):
+                    n = int(rc[j])
+                    assert gi[j, :n].tolist() == ri[j, :n].tolist(), f"row ids {what} q{j}"
+                    assert _bits(gd[j, :n]).tolist() == _bits(rd[j, :n]).tolist(), f"distances {what} q{j}"
+        assert ix.stats()["scan_variant"] == 4
+    finally:
+        os.environ.pop("LB200_PQ4_SIMPLE", None)
+        ix.close()
 
 
 @pytest.mark.parametrize("metric,d,M", [("l2", 128, 16), ("l2", 32, 2), ("l2", 30, 6), ("cosine", 96, 12),
@@ -64,9 +76,22 @@ def test_search_4bit_parity_ragged(oracle, metric, d, M):
                                     (10, len(sizes) + 3, 2, None, None)])
 
 
+@pytest.mark.parametrize("metric", ["l2", "dot"])
+def test_search_4bit_large_partitions_and_large_k(oracle, metric):
+    """Partitions above 1024 rows take the early bound of the fused kernel's first pass; k' up to 512."""
+    sizes = [5000, 1025, 1024, 2500, 3, 0, 7777]
+    data = _index4(metric, 64, len(sizes), 16, sizes, seed=21, keep_raw=True)
+    rng = np.random.default_rng(3)
+    q = rng.normal(size=(9, 64)).astype(np.float32)
+    dall = oracle.OracleIndex(data).search(q, 100, len(sizes))[0]
+    lo, hi = float(np.quantile(dall, 0.3)), float(np.quantile(dall, 0.9))
+    _check_search(oracle, data, q, [(10, 7, 0, None, None), (512, 3, 0, None, None), (64, 7, 8, None, None),
+                                    (100, 7, 0, lo, hi), (1, 7, 0, hi, None), (5, 7, 0, None, lo)])
+
+
 def test_search_4bit_many_ties_order_by_row_id(oracle):
     """A tiny codebook scale makes most quantised distances collide: the order inside a tie is by row id."""
-    sizes = [500, 700, 300]
+    sizes = [500, 1700, 3000]
     data = _index4("l2", 16, 3, 2, sizes, seed=5)
     data.codes = (data.codes & 0x11).astype(np.uint8)          # 4 distinct codes per byte -> massive ties
     rng = np.random.default_rng(2)
