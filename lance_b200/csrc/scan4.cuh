@@ -109,25 +109,27 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
 // ---- fused variant -------------------------------------------------------------------------------------------
 // Same arithmetic, no HBM distance scratch: the pre-dequantisation sum S of a row is a small integer
 // (<= (M/2) * 510), so the CTA selects on a shared-memory HISTOGRAM of S instead of on floats.
-//   pass 1  S of every admissible row -> hist[S]; after the first 1024 rows the k'-th smallest so far bounds which
+//   pass 1  S of every admissible row -> hist[S]; after the first 4096 rows the k'-th smallest so far bounds which
 //           rows still need counting (rows above it can never be selected), so the atomics stop early;
 //   select  k'-th smallest: bin S*; T = f(S*) with f = the reference's dequantisation; because f may map adjacent S
 //           to one float, "ties" are all bins with f(S) == T and are taken in row order (= row id order);
 //   pass 2  re-reads the codes (L2-resident: one partition), gathers rows below T and the first ties, sorts the
 //           <= k' keys and writes (distance, row id, index position).
 // Codes: layout `codes4p` = per partition [M/2][npad], npad = n rounded up to 16, base 16-byte aligned, so a thread
-// takes 4 consecutive rows of a plane with one 32-bit load and a warp reads 128 contiguous bytes.
+// takes 4 consecutive rows of a plane with one 32-bit load and a warp reads 128 contiguous bytes.  The sums of the
+// first 4096 rows are kept in shared memory (u16), so partitions up to 4096 rows are scanned ONCE.  Lookups go through a per-pair 16-bit table pt[j][byte] = qt[2j][lo] + qt[2j+1][hi]
+// built once per CTA (one LDS per code byte instead of two plus the nibble split).
 // [lower, upper) is applied on f(S) (exactly the float the reference filters on).
 struct Scan4Sel {
   uint32_t s_lt, s_hi, nless, need_ties, have_kth;
 };
 
-__device__ __forceinline__ float dequant4(uint32_t S, float range, float qmin) {
+__device__ __noinline__ float dequant4(uint32_t S, float range, float qmin) {
   return __fadd_rn(__fdiv_rn(__fmul_rn((float)S, range), 255.0f), qmin);
 }
 
 // k-th smallest over hist[0..nbins): fills sel (thread 0), all threads must call. scratch: part[256].
-__device__ __forceinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nbins, uint32_t k, float range, float qmin,
+__device__ __noinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nbins, uint32_t k, float range, float qmin,
                                                uint32_t* part, Scan4Sel* sel) {
   const uint32_t tid = threadIdx.x, chunk = (nbins + 255) / 256;
   const uint32_t b0 = tid * chunk, b1 = min(nbins, b0 + chunk);
@@ -135,20 +137,36 @@ __device__ __forceinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nb
   for (uint32_t b = b0; b < b1; b++) c += hist[b];
   part[tid] = c;
   __syncthreads();
-  if (tid == 0) {
-    uint32_t cum = 0, t = 0;
-    for (; t < 256; t++) {
-      if (cum + part[t] >= k) break;
-      cum += part[t];
+  if (tid < 32) {  // warp 0: scan of the 256 chunk sums, 8 per lane; the lane that crosses k finishes the search
+    uint32_t loc[8], sum = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      loc[i] = part[tid * 8 + i];
+      sum += loc[i];
     }
-    if (t == 256) {
-      sel->have_kth = 0;
-      sel->s_lt = nbins;   // everything counted is "less"
-      sel->s_hi = nbins - 1;
-      sel->nless = cum;
-      sel->need_ties = 0;
-    } else {
-      uint32_t b = t * chunk;
+    uint32_t incl = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (tid >= (uint32_t)o) incl += v;
+    }
+    uint32_t cum = incl - sum;
+    const bool hit = cum < k && incl >= k;
+    const uint32_t any = __ballot_sync(0xffffffffu, hit);
+    if (!any) {
+      if (tid == 31) {
+        sel->have_kth = 0;
+        sel->s_lt = nbins;   // everything counted is "less"
+        sel->s_hi = nbins - 1;
+        sel->nless = incl;
+        sel->need_ties = 0;
+      }
+    } else if (hit) {
+      uint32_t t = 0;
+      for (; t < 8; t++) {
+        if (cum + loc[t] >= k) break;
+        cum += loc[t];
+      }
+      uint32_t b = (tid * 8 + t) * chunk;
       for (;; b++) {
         if (cum + hist[b] >= k) break;
         cum += hist[b];
@@ -186,7 +204,9 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
   float* smax = T + (size_t)M * 16;
   unsigned long long* sl = (unsigned long long*)(smax + ((M + 1) & ~1u));  // [kpow2], 8-byte aligned
   uint32_t* hist = (uint32_t*)(sl + kpow2);                                  // [nbins]
-  uint8_t* qt = (uint8_t*)(hist + nbins);                                    // [M][16]
+  uint8_t* qt = (uint8_t*)(hist + ((nbins + 1) & ~1u));                      // [M][16], 8-byte aligned
+  uint16_t* pt = (uint16_t*)(qt + (size_t)M * 16);                           // [M/2][256] pair sums
+  uint16_t* scache = pt + (size_t)(M / 2) * 256;                             // [4096] sums of the first rows
   __shared__ float s_red[8];
   __shared__ float s_qmin, s_qmax;
   __shared__ uint32_t s_part[256], s_wsum[8], s_fill, s_tiebase, s_adm[3];
@@ -273,30 +293,52 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
     if (amode == 1) return S >= alo && S < ahi;
     return admissible_f(S);
   };
-  // S of the 4 rows i0..i0+3 (i0 % 4 == 0, i0 < npad)
+  // pair table: pt[j][byte] = qt[2j][byte & 15] + qt[2j+1][byte >> 4] (0..510); one 16-bit lookup per code byte
+  for (uint32_t e = tid; e < (M / 2) * 256; e += 256) {
+    const uint32_t j = e >> 8, b = e & 255u;
+    pt[e] = (uint16_t)((uint32_t)qt[(2 * j) * 16 + (b & 15)] + (uint32_t)qt[(2 * j + 1) * 16 + (b >> 4)]);
+  }
+  __syncthreads();
+  // S of the 4 rows i0..i0+3 (i0 % 4 == 0, i0 < npad): one 32-bit load per code plane.  Block rows (all rows but
+  // the reference's n % 16 tail) take the pair sum modulo 256 (_mm_add_epi8), tail rows the plain sum.
   auto sums4 = [&](uint64_t i0, uint32_t S[4]) {
-    uint32_t blkmask = 0;  // bit r set: row is a block row (wrapping pair sums)
+    uint32_t tailmask = 0;
 #pragma unroll
     for (int rr = 0; rr < 4; rr++) {
       S[rr] = 0;
-      if (i0 + rr < n && !tl[i0 + rr]) blkmask |= 1u << rr;
+      if (i0 + rr < n && tl[i0 + rr]) tailmask |= 1u << rr;
     }
-    for (uint32_t j = 0; j < M / 2; j++) {
-      const uint32_t w = *reinterpret_cast<const uint32_t*>(cp + (size_t)j * npad + i0);
-      const uint8_t* t0 = qt + (2 * j) * 16;
-      const uint8_t* t1 = t0 + 16;
+    const uint8_t* c0 = cp + i0;
+    if (tailmask == 0) {
+#pragma unroll 2
+      for (uint32_t j = 0; j < M / 2; j++) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(c0 + (size_t)j * npad);
+        const uint16_t* t = pt + j * 256;
 #pragma unroll
-      for (int rr = 0; rr < 4; rr++) {
-        const uint32_t b = (w >> (8 * rr)) & 255u;
-        const uint32_t sum = (uint32_t)t0[b & 15] + (uint32_t)t1[b >> 4];
-        S[rr] += ((blkmask >> rr) & 1u) ? (sum & 255u) : sum;
+        for (int rr = 0; rr < 4; rr++) S[rr] += (uint32_t)t[(w >> (8 * rr)) & 255u] & 255u;
+      }
+    } else {
+#pragma unroll 1
+      for (uint32_t j = 0; j < M / 2; j++) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(c0 + (size_t)j * npad);
+        const uint16_t* t = pt + j * 256;
+#pragma unroll
+        for (int rr = 0; rr < 4; rr++) {
+          const uint32_t v = t[(w >> (8 * rr)) & 255u];
+          S[rr] += ((tailmask >> rr) & 1u) ? v : (v & 255u);
+        }
       }
     }
   };
+  constexpr uint64_t GROUP = 1024, CACHED = 4096;  // rows per CTA step; rows whose sums are kept in shared memory
+  const uint32_t lane = tid & 31, wrp = tid >> 5;
 
-  // ---- pass 1: histogram of S -------------------------------------------------------------------------------
+  // ---- pass 1: histogram of S; the sums of the first 4096 rows are kept (u16) for pass 2 ---------------------------
+  // (loops deliberately NOT unrolled: the first version of this kernel spent most of its issue slots waiting for
+  // instruction fetch, ncu "no_instruction" 16.5 per issue)
   uint32_t bound = nbins - 1;
-  for (uint64_t base = 0; base < n; base += 1024) {
+#pragma unroll 1
+  for (uint64_t base = 0; base < n; base += GROUP) {
     const uint64_t i0 = base + (uint64_t)tid * 4;
     if (i0 < n) {
       uint32_t S[4];
@@ -304,8 +346,10 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
 #pragma unroll
       for (int rr = 0; rr < 4; rr++)
         if (i0 + rr < n && S[rr] <= bound && admissible(S[rr])) atomicAdd(&hist[S[rr]], 1u);
+      if (i0 < CACHED)
+        *reinterpret_cast<uint2*>(scache + i0) = make_uint2(S[0] | (S[1] << 16), S[2] | (S[3] << 16));
     }
-    if (base == 0 && n > 1024) {
+    if (base + GROUP == CACHED && n > CACHED) {  // uniform
       __syncthreads();
       scan4_find_kth(hist, nbins, kprime, range, qmin, s_part, &s_sel);
       if (s_sel.have_kth) bound = s_sel.s_hi;
@@ -317,14 +361,19 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
   const uint32_t s_lt = s_sel.s_lt, s_hi = s_sel.s_hi, nless = s_sel.nless, need_ties = s_sel.need_ties;
   const bool have_kth = s_sel.have_kth != 0;
 
-  // ---- pass 2: gather -----------------------------------------------------------------------------------------
-  const uint32_t lane = tid & 31, wrp = tid >> 5;
-  for (uint64_t base = 0; base < n; base += 1024) {
+  // ---- pass 2: gather (rows below the threshold in any order, ties in row order) ----------------------------------
+#pragma unroll 1
+  for (uint64_t base = 0; base < n; base += GROUP) {
     const uint64_t i0 = base + (uint64_t)tid * 4;
     uint32_t S[4] = {0, 0, 0, 0};
     uint32_t tmask = 0;  // rows of this thread that tie with the threshold
     if (i0 < n) {
-      sums4(i0, S);
+      if (i0 < CACHED) {
+        const uint2 c2 = *reinterpret_cast<const uint2*>(scache + i0);
+        S[0] = c2.x & 0xffffu; S[1] = c2.x >> 16; S[2] = c2.y & 0xffffu; S[3] = c2.y >> 16;
+      } else {
+        sums4(i0, S);
+      }
 #pragma unroll
       for (int rr = 0; rr < 4; rr++) {
         if (i0 + rr >= n || S[rr] > bound || !admissible(S[rr])) continue;
@@ -336,7 +385,8 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
         }
       }
     }
-    if (have_kth && s_tiebase < need_ties) {  // uniform across the CTA: s_tiebase changes only between barriers
+    if (have_kth && s_tiebase < need_ties) {  // uniform: s_tiebase changes only between barriers
+      if (!__syncthreads_or(tmask != 0)) continue;
       // rank of this thread's ties in row order: threads hold consecutive rows, warps consecutive threads
       const uint32_t cnt = __popc(tmask);
       uint32_t incl = cnt;

@@ -78,7 +78,7 @@ def test_search_4bit_parity_ragged(oracle, metric, d, M):
 
 @pytest.mark.parametrize("metric", ["l2", "dot"])
 def test_search_4bit_large_partitions_and_large_k(oracle, metric):
-    """Partitions above 1024 rows take the early bound of the fused kernel's first pass; k' up to 512."""
+    """Partitions above 4096 rows take the early bound of the fused kernel's first pass; k' up to 512."""
     sizes = [5000, 1025, 1024, 2500, 3, 0, 7777]
     data = _index4(metric, 64, len(sizes), 16, sizes, seed=21, keep_raw=True)
     rng = np.random.default_rng(3)
