@@ -26,7 +26,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   const uint32_t kp2 = std::max(2u, next_pow2(kprime));
   const uint32_t nbins = (M / 2) * 510 + 1;
   const size_t fsmem = ((size_t)dim + (size_t)M * 16 + ((M + 1) & ~1u)) * 4 + (size_t)kp2 * 8 + (size_t)((nbins + 1) & ~1u) * 4 + (size_t)M * 16 +
-                       (size_t)(M / 2) * 512 + 4096 * 2;
+                       (size_t)(M / 2) * 256 + 4096 * 2;
   const bool fused = fsmem <= ix->smem_optin && !getenv("LB200_PQ4_SIMPLE");
   size_t need = 0;
   auto add = [&](size_t b) { need += Arena::pad(b) + 256; };

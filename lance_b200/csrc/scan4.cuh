@@ -117,8 +117,9 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
 //           <= k' keys and writes (distance, row id, index position).
 // Codes: layout `codes4p` = per partition [M/2][npad], npad = n rounded up to 16, base 16-byte aligned, so a thread
 // takes 4 consecutive rows of a plane with one 32-bit load and a warp reads 128 contiguous bytes.  The sums of the
-// first 4096 rows are kept in shared memory (u16), so partitions up to 4096 rows are scanned ONCE.  Lookups go through a per-pair 16-bit table pt[j][byte] = qt[2j][lo] + qt[2j+1][hi]
-// built once per CTA (one LDS per code byte instead of two plus the nibble split).
+// first 4096 rows are kept in shared memory (u16), so partitions up to 4096 rows are scanned ONCE.  Lookups of block rows go through a per-pair 8-bit table
+// pt[j][byte] = (qt[2j][lo] + qt[2j+1][hi]) mod 256 built once per CTA (one LDS per code byte instead of two plus the
+// nibble split; 256 B per plane keeps bank conflicts at most two-way).
 // [lower, upper) is applied on f(S) (exactly the float the reference filters on).
 struct Scan4Sel {
   uint32_t s_lt, s_hi, nless, need_ties, have_kth;
@@ -205,8 +206,8 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
   unsigned long long* sl = (unsigned long long*)(smax + ((M + 1) & ~1u));  // [kpow2], 8-byte aligned
   uint32_t* hist = (uint32_t*)(sl + kpow2);                                  // [nbins]
   uint8_t* qt = (uint8_t*)(hist + ((nbins + 1) & ~1u));                      // [M][16], 8-byte aligned
-  uint16_t* pt = (uint16_t*)(qt + (size_t)M * 16);                           // [M/2][256] pair sums
-  uint16_t* scache = pt + (size_t)(M / 2) * 256;                             // [4096] sums of the first rows
+  uint8_t* pt = qt + (size_t)M * 16;                                         // [M/2][256] wrapped pair sums
+  uint16_t* scache = (uint16_t*)(pt + (size_t)(M / 2) * 256);                // [4096] sums of the first rows
   __shared__ float s_red[8];
   __shared__ float s_qmin, s_qmax;
   __shared__ uint32_t s_part[256], s_wsum[8], s_fill, s_tiebase, s_adm[3];
@@ -293,14 +294,15 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
     if (amode == 1) return S >= alo && S < ahi;
     return admissible_f(S);
   };
-  // pair table: pt[j][byte] = qt[2j][byte & 15] + qt[2j+1][byte >> 4] (0..510); one 16-bit lookup per code byte
+  // pair table for block rows: pt[j][byte] = (qt[2j][byte & 15] + qt[2j+1][byte >> 4]) mod 256 -- exactly the wrapping
+  // u8 lane sum of _mm_add_epi8; one 8-bit lookup per code byte (256 B per plane: at most two words per bank)
   for (uint32_t e = tid; e < (M / 2) * 256; e += 256) {
     const uint32_t j = e >> 8, b = e & 255u;
-    pt[e] = (uint16_t)((uint32_t)qt[(2 * j) * 16 + (b & 15)] + (uint32_t)qt[(2 * j + 1) * 16 + (b >> 4)]);
+    pt[e] = (uint8_t)((uint32_t)qt[(2 * j) * 16 + (b & 15)] + (uint32_t)qt[(2 * j + 1) * 16 + (b >> 4)]);
   }
   __syncthreads();
-  // S of the 4 rows i0..i0+3 (i0 % 4 == 0, i0 < npad): one 32-bit load per code plane.  Block rows (all rows but
-  // the reference's n % 16 tail) take the pair sum modulo 256 (_mm_add_epi8), tail rows the plain sum.
+  // S of the 4 rows i0..i0+3 (i0 % 4 == 0, i0 < npad): one 32-bit load per code plane.  Rows of the reference's
+  // n % 16 tail add the two looked-up bytes without the wrap (rare: the slow branch).
   auto sums4 = [&](uint64_t i0, uint32_t S[4]) {
     uint32_t tailmask = 0;
 #pragma unroll
@@ -313,18 +315,19 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
 #pragma unroll 2
       for (uint32_t j = 0; j < M / 2; j++) {
         const uint32_t w = *reinterpret_cast<const uint32_t*>(c0 + (size_t)j * npad);
-        const uint16_t* t = pt + j * 256;
+        const uint8_t* t = pt + j * 256;
 #pragma unroll
-        for (int rr = 0; rr < 4; rr++) S[rr] += (uint32_t)t[(w >> (8 * rr)) & 255u] & 255u;
+        for (int rr = 0; rr < 4; rr++) S[rr] += t[(w >> (8 * rr)) & 255u];
       }
     } else {
 #pragma unroll 1
       for (uint32_t j = 0; j < M / 2; j++) {
         const uint32_t w = *reinterpret_cast<const uint32_t*>(c0 + (size_t)j * npad);
-        const uint16_t* t = pt + j * 256;
+        const uint8_t* t0 = qt + (2 * j) * 16;
 #pragma unroll
         for (int rr = 0; rr < 4; rr++) {
-          const uint32_t v = t[(w >> (8 * rr)) & 255u];
+          const uint32_t b = (w >> (8 * rr)) & 255u;
+          const uint32_t v = (uint32_t)t0[b & 15] + (uint32_t)t0[16 + (b >> 4)];
           S[rr] += ((tailmask >> rr) & 1u) ? v : (v & 255u);
         }
       }
@@ -416,14 +419,33 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
   }
   __syncthreads();
   const uint32_t cnt = have_kth ? kprime : s_fill;
-  block_bitonic_sort_u64(sl, kpow2);
-  for (uint32_t i = tid; i < kprime; i += 256) {
-    const unsigned long long v = sl[i];
-    const bool ok = i < cnt;
-    const uint64_t pos = off + (uint32_t)v;
-    out_dist[(size_t)pair * kprime + i] = ok ? key_to_float((uint32_t)(v >> 32)) : __int_as_float(0x7f800000);
-    out_rowid[(size_t)pair * kprime + i] = ok ? row_ids[pos] : ~0ull;
-    if (out_pos) out_pos[(size_t)pair * kprime + i] = ok ? pos : 0;
+  if (kpow2 <= 32) {  // one warp sorts in registers: no barriers
+    if (tid < 32) {
+      unsigned long long v = tid < kpow2 ? sl[tid] : ~0ull;
+      for (uint32_t k = 2; k <= 32; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+          const unsigned long long o = __shfl_xor_sync(0xffffffffu, v, j);
+          const bool up = (tid & k) == 0, lower_lane = (tid & j) == 0;
+          v = (lower_lane == up) ? (v < o ? v : o) : (v < o ? o : v);
+        }
+      if (tid < kprime) {
+        const bool ok = tid < cnt;
+        const uint64_t pos = off + (uint32_t)v;
+        out_dist[(size_t)pair * kprime + tid] = ok ? key_to_float((uint32_t)(v >> 32)) : __int_as_float(0x7f800000);
+        out_rowid[(size_t)pair * kprime + tid] = ok ? row_ids[pos] : ~0ull;
+        if (out_pos) out_pos[(size_t)pair * kprime + tid] = ok ? pos : 0;
+      }
+    }
+  } else {
+    block_bitonic_sort_u64(sl, kpow2);
+    for (uint32_t i = tid; i < kprime; i += 256) {
+      const unsigned long long v = sl[i];
+      const bool ok = i < cnt;
+      const uint64_t pos = off + (uint32_t)v;
+      out_dist[(size_t)pair * kprime + i] = ok ? key_to_float((uint32_t)(v >> 32)) : __int_as_float(0x7f800000);
+      out_rowid[(size_t)pair * kprime + i] = ok ? row_ids[pos] : ~0ull;
+      if (out_pos) out_pos[(size_t)pair * kprime + i] = ok ? pos : 0;
+    }
   }
   if (tid == 0) {
     out_cnt[pair] = cnt;
