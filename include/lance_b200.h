@@ -195,6 +195,20 @@ int32_t lb200_flat_topk_device(int32_t device_id, int32_t metric, uint32_t dim,
                                float* d_out_dist, uint64_t* d_out_idx, uint32_t* d_out_count,
                                void* stream);
 
+/* The same two entry points for Float16 columns (the reference's f16 path:
+ * `impl L2/Dot/Cosine/Normalize for f16`, rust/lance-linalg/src/distance/{l2.rs:136-166, dot.rs:100-137,
+ * cosine.rs:88-121, norm_l2.rs:46-76}, C kernels rust/lance-linalg/src/simd/f16.c).  queries / vectors are
+ * IEEE binary16 bit patterns (the key is cast to the column type by the scanner); distances are f32, computed in the
+ * order of the reference's deterministic scalar fallbacks (see csrc/api_f16.inl). */
+int32_t lb200_flat_distance_f16(int32_t device_id, int32_t metric, uint32_t dim, const uint16_t* queries,
+                                uint32_t Q, const uint16_t* vectors, const uint8_t* validity_or_null,
+                                uint64_t n, float* out);
+int32_t lb200_flat_topk_f16(int32_t device_id, int32_t metric, uint32_t dim, const uint16_t* queries,
+                            uint32_t Q, const uint16_t* vectors, const uint8_t* validity_or_null,
+                            uint64_t n, uint32_t k, const float* lower_or_null,
+                            const float* upper_or_null, float* out_dist, uint64_t* out_idx,
+                            uint32_t* out_count);
+
 /* Multi-GPU merge step of SURVEY 8(e): G gathered per-shard candidate lists -> global result.
  * d_dist/d_rowid/d_exact [G][Q][stride], d_count [G][Q]; device pointers.
  * Selects the kprime smallest by (dist,row id) (== the merge of ivf/v2.rs:395-400); if

@@ -426,3 +426,4 @@ extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
 #include "api_pq4.inl"
 #include "api_combined.inl"
 #include "api_file.inl"
+#include "api_f16.inl"

@@ -312,3 +312,43 @@ def rerank(key, metric, cand_vectors, cand_rowids, cand_count, k, lower_bound=No
         _p(cv), _p(cr), _p(cc), C.c_uint32(cv.shape[1]), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound),
         _p(od), _p(oi), _p(oc)))
     return od, oi, oc
+
+
+def _f16(a):
+    return np.ascontiguousarray(a, dtype=np.float16)
+
+
+def compute_distance_f16(key, metric, vectors, validity=None, device_id=0):
+    """compute_distance (flat.rs:28-86) on a Float16 column: key [d] or [Q][d] and vectors [n][d] as float16;
+    returns f32 distances, NaN where null."""
+    key2 = np.atleast_2d(_f16(key))
+    vectors = _f16(vectors)
+    if vectors.ndim != 2 or key2.shape[1] != vectors.shape[1]:
+        raise ValueError("dimension mismatch between key and vectors")
+    Q, n = key2.shape[0], vectors.shape[0]
+    out = np.zeros((Q, n), dtype=np.float32)
+    v = None if validity is None else np.ascontiguousarray(validity, dtype=np.uint8)
+    check(_lib.lib().lb200_flat_distance_f16(C.c_int32(device_id), C.c_int32(DistanceType.code(metric)),
+                                             C.c_uint32(vectors.shape[1]), _p(key2), C.c_uint32(Q), _p(vectors), _p(v),
+                                             C.c_uint64(n), _p(out)))
+    return out[0] if np.ndim(key) == 1 else out
+
+
+def flat_knn_f16(key, metric, vectors, k, validity=None, lower_bound=None, upper_bound=None, device_id=0):
+    """Scanner::flat_knn (scanner.rs:2066-2136) on a Float16 column."""
+    key2 = np.atleast_2d(_f16(key))
+    vectors = _f16(vectors)
+    if vectors.ndim != 2 or key2.shape[1] != vectors.shape[1]:
+        raise ValueError("dimension mismatch between key and vectors")
+    if k <= 0:
+        raise ValueError("k must be positive")
+    Q, n = key2.shape[0], vectors.shape[0]
+    od = np.full((Q, k), np.inf, dtype=np.float32)
+    oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+    oc = np.zeros(Q, dtype=np.uint32)
+    v = None if validity is None else np.ascontiguousarray(validity, dtype=np.uint8)
+    check(_lib.lib().lb200_flat_topk_f16(C.c_int32(device_id), C.c_int32(DistanceType.code(metric)),
+                                         C.c_uint32(vectors.shape[1]), _p(key2), C.c_uint32(Q), _p(vectors), _p(v),
+                                         C.c_uint64(n), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound), _p(od),
+                                         _p(oi), _p(oc)))
+    return od, oi, oc

@@ -53,6 +53,8 @@ def lib():
         f.lo_search_one.restype = C.c_uint32
         f.lo_flat_knn_one.restype = C.c_uint32
         f.lo_max_threads.restype = C.c_int
+        for name in ("lo_l2_f16", "lo_dot_f16", "lo_norm_l2_f16", "lo_cosine_f16"):
+            getattr(f, name).restype = C.c_float
     return _lib
 
 
@@ -319,3 +321,51 @@ def nearest_plan(deltas, take, key, k, nprobes, refine_factor=None, lower=None, 
     fv = _f32(unindexed_vectors)[[lut[int(r)] for r in fr.tolist()]] if len(fr) else np.zeros((0, len(key)), np.float32)
     av = _f32(take(ar)).reshape(-1, len(key)) if len(ar) else np.zeros((0, len(key)), np.float32)
     return flat_knn_rows(metric, key, np.concatenate([fv, av]), np.concatenate([fr, ar]), k, lower, upper)
+
+
+# ---- f16 vectors ---------------------------------------------------------------------------------
+def distance_batch_f16(metric, q, vectors):
+    """{l2,cosine,dot}_distance_arrow_batch on Float16 data, the reference's deterministic scalar fallback
+    (lo_distance_batch_f16).  q [d] f16, vectors [n][d] f16 -> [n] f32."""
+    q = np.ascontiguousarray(q, dtype=np.float16)
+    vectors = np.ascontiguousarray(vectors, dtype=np.float16)
+    n, d = vectors.shape
+    out = np.empty(n, dtype=np.float32)
+    lib().lo_distance_batch_f16(C.c_int(METRICS[metric]), _p(q), _p(vectors), C.c_size_t(n), C.c_size_t(d), _p(out))
+    return out
+
+
+_REF_SO = os.path.join(_HERE, "_ref", "libf16_ref.so")
+_ref = None
+
+
+def ref_f16():
+    """oracle/_ref/libf16_ref.so: the REFERENCE's own f16 kernels (rust/lance-linalg/src/simd/f16.c compiled by
+    `make -C oracle ref` with build.rs's flags), or None when it has not been built."""
+    global _ref
+    if _ref is None and os.path.exists(_REF_SO):
+        _ref = C.CDLL(_REF_SO)
+        for name in ("norm_l2_f16_avx2", "dot_f16_avx2", "l2_f16_avx2", "cosine_f16_avx2"):
+            getattr(_ref, name).restype = C.c_float
+    return _ref
+
+
+def ref_distance_batch_f16(metric, q, vectors):
+    """The same batch through the reference's C kernels, called the way l2.rs:150-155 / dot.rs:120-125 /
+    cosine.rs:104-108 call them."""
+    r = ref_f16()
+    q = np.ascontiguousarray(q, dtype=np.float16)
+    vectors = np.ascontiguousarray(vectors, dtype=np.float16)
+    n, d = vectors.shape
+    out = np.empty(n, dtype=np.float32)
+    m = METRICS[metric]
+    xn = r.norm_l2_f16_avx2(_p(q), C.c_uint32(d)) if m == COSINE else 0.0
+    for i in range(n):
+        y = vectors[i].ctypes.data_as(C.c_void_p)
+        if m == L2:
+            out[i] = r.l2_f16_avx2(_p(q), y, C.c_uint32(d))
+        elif m == DOT:
+            out[i] = 1.0 - r.dot_f16_avx2(_p(q), y, C.c_uint32(d))
+        else:
+            out[i] = r.cosine_f16_avx2(_p(q), C.c_float(xn), y, C.c_uint32(d))
+    return out

@@ -777,3 +777,78 @@ void lo_pq_quantize4(int metric, const float *codebook, uint32_t M, uint32_t d, 
       *o = (m & 1) ? (uint8_t)(*o | (bi << 4)) : (uint8_t)bi;
     }
 }
+
+/* ------------------------------------------------------------------------- */
+/* f16 vectors.  The reference has two CPU behaviours for f16 (l2.rs:136-166, dot.rs:100-137,
+ * cosine.rs:88-121, norm_l2.rs:46-76): with the `fp16kernels` feature the C kernels of simd/f16.c (built
+ * -ffast-math, so their summation order is the compiler's), otherwise the generic scalar fallbacks restated here,
+ * which ARE deterministic: every element is widened to f32 first (`x.as_()`), then
+ *   L2      l2_scalar::<f16,f32,16>   (l2.rs:65-99)      == lo_l2 on the widened values
+ *   dot     dot_scalar::<f16,f32,32>  (dot.rs:33-61)     remainder first, 32 lane sums, lanes added in order
+ *   norm    norm_l2_impl::<f16,f32,32> (norm_l2.rs:102-126)
+ *   cosine  cosine_scalar (cosine.rs:233-238): 1 - xy / (x_norm * sqrt(dot(y,y)))
+ * oracle/_ref/libf16_ref.so (the reference's own f16.c, compiled by `make ref`) is the cross-check within tolerance. */
+typedef _Float16 lo_f16;
+
+float lo_l2_f16(const lo_f16 *x, const lo_f16 *y, size_t d) {
+  size_t nchunk = d / 16, rem0 = nchunk * 16;
+  float s = 0.0f;
+  for (size_t i = rem0; i < d; i++) {
+    float diff = (float)x[i] - (float)y[i];
+    s += diff * diff;
+  }
+  float sums[16];
+  for (int i = 0; i < 16; i++) sums[i] = 0.0f;
+  for (size_t c = 0; c < nchunk; c++)
+    for (int i = 0; i < 16; i++) {
+      float diff = (float)x[c * 16 + i] - (float)y[c * 16 + i];
+      sums[i] += diff * diff;
+    }
+  float t = 0.0f;
+  for (int i = 0; i < 16; i++) t += sums[i];
+  return s + t;
+}
+
+float lo_dot_f16(const lo_f16 *x, const lo_f16 *y, size_t d) {
+  size_t nchunk = d / 32, rem0 = nchunk * 32;
+  float s = 0.0f;
+  for (size_t i = rem0; i < d; i++) s += (float)x[i] * (float)y[i];
+  float sums[32];
+  for (int i = 0; i < 32; i++) sums[i] = 0.0f;
+  for (size_t c = 0; c < nchunk; c++)
+    for (int i = 0; i < 32; i++) sums[i] += (float)x[c * 32 + i] * (float)y[c * 32 + i];
+  float t = 0.0f;
+  for (int i = 0; i < 32; i++) t += sums[i];
+  return s + t;
+}
+
+float lo_norm_l2_f16(const lo_f16 *v, size_t d) {
+  size_t nchunk = d / 32, rem0 = nchunk * 32;
+  float s = 0.0f;
+  for (size_t i = rem0; i < d; i++) s += (float)v[i] * (float)v[i];
+  float sums[32];
+  for (int i = 0; i < 32; i++) sums[i] = 0.0f;
+  for (size_t c = 0; c < nchunk; c++)
+    for (int i = 0; i < 32; i++) sums[i] += (float)v[c * 32 + i] * (float)v[c * 32 + i];
+  float t = 0.0f;
+  for (int i = 0; i < 32; i++) t += sums[i];
+  return sqrtf(s + t);
+}
+
+float lo_cosine_f16(const lo_f16 *x, float x_norm, const lo_f16 *y, size_t d) {
+  float y_sq = lo_dot_f16(y, y, d);
+  float xy = lo_dot_f16(x, y, d);
+  return 1.0f - xy / (x_norm * sqrtf(y_sq));
+}
+
+/* {l2,cosine,dot}_distance_arrow_batch on a Float16 FixedSizeList (l2.rs:288-310, cosine.rs:315-340,
+ * dot.rs:270-295): one key against n rows. */
+void lo_distance_batch_f16(int metric, const lo_f16 *from, const lo_f16 *to, size_t n, size_t d, float *out) {
+  float xn = metric == LO_COSINE ? lo_norm_l2_f16(from, d) : 0.0f;
+  for (size_t i = 0; i < n; i++) {
+    const lo_f16 *y = to + i * d;
+    out[i] = metric == LO_L2 ? lo_l2_f16(from, y, d)
+           : metric == LO_DOT ? 1.0f - lo_dot_f16(from, y, d)
+                              : lo_cosine_f16(from, xn, y, d);
+  }
+}
