@@ -14,7 +14,7 @@
  *  - there is NO CPU fallback: without a usable CUDA device every call fails with
  *    LB200_ECUDA.
  *
- * Limits of this build (LB200_EUNSUPPORTED beyond them): 8-bit PQ only; nlist <= 8192;
+ * Limits of this build (LB200_EUNSUPPORTED beyond them): PQ code width 8 or 4 bits; nlist <= 8192;
  * num_sub_vectors <= 192 (the bank-conflict-free scan for multiples of 16 up to 96);
  * k * max(refine_factor,1) <= 512; N < 2^32 rows; Q * nprobes < 2^31 per call;
  * nprobes * k' up to (16384/k')^2 lists (two-level merge above 16384 candidates per query).
@@ -55,7 +55,14 @@ enum {
  *   codes        concat over p of [M][n_p] u8, transposed  (pq/storage.rs:357-377,455-470)
  *   row_ids      [N] u64 in index order                    (`_rowid` column of auxiliary.idx)
  *   raw_vectors  [N][dim] f32 in index order, or NULL      (only for device-side refine)
- * num_bits must be 8 (4-bit PQ: LB200_EUNSUPPORTED). */
+ * num_bits = 8: as above.
+ * num_bits = 4 (pq/distance.rs:138-229): codebook [M][16][dim/M]; codes concat over p of
+ *   [M/2][n_p] bytes, low nibble = sub-space 2j, high nibble = 2j+1 (pq.rs:166-170); M even.
+ * num_bits = 32: IVF_FLAT (IVFIndex<FlatIndex, FlatQuantizer>, flat/storage.rs:315-375): no
+ *   quantizer -- codebook, codes and num_sub_vectors are ignored and raw_vectors is REQUIRED;
+ *   search returns exact distances on the raw rows of the probed partitions.
+ * 4-bit and IVF_FLAT handles take every search entry point except prefilter bitmasks and the
+ * multi-GPU shard mode (LB200_EUNSUPPORTED). */
 int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist,
                            const float* centroids, uint32_t num_sub_vectors, uint32_t num_bits,
                            const float* codebook, const uint64_t* part_offsets,

@@ -134,6 +134,8 @@ namespace {
 int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist, const float* centroids, uint32_t M,
                   const float* codebook, const uint64_t* part_offsets, const uint8_t* codes, const uint64_t* row_ids,
                   const float* raw, lb200_index** out);
+int create_index_flat(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist, const float* centroids,
+                      const uint64_t* part_offsets, const uint64_t* row_ids, const float* raw, lb200_index** out);
 }
 extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist,
                                       const float* centroids, uint32_t M, uint32_t num_bits,
@@ -145,6 +147,8 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   if (num_bits == 4)
     return create_index4(device_id, metric, dim, nlist, centroids, M, codebook, part_offsets, codes, row_ids,
                          raw_vectors_or_null, out);
+  if (num_bits == 32)  // IVF_FLAT: raw f32 rows, no quantizer
+    return create_index_flat(device_id, metric, dim, nlist, centroids, part_offsets, row_ids, raw_vectors_or_null, out);
   if (num_bits != 8)
     return set_err(LB200_EUNSUPPORTED, "num_bits=%u: only 8-bit and 4-bit PQ are supported", num_bits);
   if (metric != LB200_L2 && metric != LB200_COSINE && metric != LB200_DOT)

@@ -1,5 +1,6 @@
-// api_pq4.inl -- 4-bit PQ indexes behind the same entry points (included by api.cu): create, and the search
-// pipeline search_pipeline() hands over to when ix->bits == 4.
+// api_pq4.inl -- 4-bit PQ indexes and IVF_FLAT indexes (bits == 32: raw f32 rows instead of codes) behind the same
+// entry points (included by api.cu): create, and the search pipeline search_pipeline() hands over to when
+// ix->bits != 8.
 
 namespace {
 
@@ -9,8 +10,9 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);
   if (a.k == 0) return set_err(LB200_EINVAL, "k must be > 0");
   if (kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", kprime);
-  if (a.shard_mode) return set_err(LB200_EUNSUPPORTED, "4-bit PQ: sharded search is not supported yet");
-  if (a.d_bitmask) return set_err(LB200_EUNSUPPORTED, "4-bit PQ: prefilter bitmasks are not supported yet");
+  const bool flat = ix->bits == 32;
+  if (a.shard_mode) return set_err(LB200_EUNSUPPORTED, "4-bit PQ / IVF_FLAT: sharded search is not supported yet");
+  if (a.d_bitmask) return set_err(LB200_EUNSUPPORTED, "4-bit PQ / IVF_FLAT: prefilter bitmasks are not supported yet");
   if (P == 0 || Q == 0) return 0;
   const bool refine = a.refine_factor > 0 && ix->d_raw != nullptr && !a.per_pair_output;
   if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output)
@@ -27,7 +29,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   const uint32_t nbins = (M / 2) * 510 + 1;
   const size_t fsmem = ((size_t)dim + (size_t)M * 16 + ((M + 1) & ~1u)) * 4 + (size_t)kp2 * 8 + (size_t)((nbins + 1) & ~1u) * 4 + (size_t)M * 16 +
                        (size_t)(M / 2) * 256 + 4096 * 2;
-  const bool fused = fsmem <= ix->smem_optin && !getenv("LB200_PQ4_SIMPLE");
+  const bool fused = !flat && fsmem <= ix->smem_optin && !getenv("LB200_PQ4_SIMPLE");
   size_t need = 0;
   auto add = [&](size_t b) { need += Arena::pad(b) + 256; };
   add((size_t)Q * dim * 4); add((size_t)Q * nlist * 4); add(npairs * 4); add(64);
@@ -93,9 +95,16 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   for (uint32_t q0 = 0; q0 < Q && !fused; q0 += tileQ) {
     const uint32_t qn = std::min(tileQ, Q - q0);
     const size_t p0 = (size_t)q0 * P, pn = (size_t)qn * P;
-    scan4_kernel<<<(uint32_t)pn, 256, smem, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim, M,
-                                                   ix->d_centroids, ix->d_codebook, ix->d_part_off, ix->d_pad_off,
-                                                   ix->d_codes4, ix->d_tail4, d_dist, stride, d_stats);
+    if (flat) {
+      const size_t fs = (size_t)dim * 4;
+      if (fs > 48 * 1024) CK(cudaFuncSetAttribute(scanflat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs));
+      scanflat_kernel<<<(uint32_t)pn, 256, fs, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim,
+                                                      ix->d_part_off, ix->d_raw, d_dist, stride, d_stats);
+    } else {
+      scan4_kernel<<<(uint32_t)pn, 256, smem, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim, M,
+                                                     ix->d_centroids, ix->d_codebook, ix->d_part_off, ix->d_pad_off,
+                                                     ix->d_codes4, ix->d_tail4, d_dist, stride, d_stats);
+    }
     CK(cudaGetLastError());
     flat_select_kernel<<<(uint32_t)pn, 256, (size_t)kp2 * 8, st>>>(d_dist, stride, stride, 1, stride, kprime, kp2,
                                                                    a.has_lower, a.lower, a.has_upper, a.upper,
@@ -142,7 +151,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     stats.scan_items = (uint32_t)npairs;
   }
   stats.kernel_launches = launches;
-  stats.scan_variant = 4;
+  stats.scan_variant = flat ? 32 : 4;
   stats.scan_items = (uint32_t)npairs;
   stats.scan_ql = 1;
   ix->stats = stats;
@@ -239,6 +248,74 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   }
   CK4(cudaStreamSynchronize(ix->stream));
 #undef CK4
+  *out = ix;
+  return 0;
+}
+
+
+// lb200_index_create for num_bits == 32: IVF_FLAT -- no codebook, no codes; raw f32 rows per partition.
+int create_index_flat(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist, const float* centroids,
+                      const uint64_t* part_offsets, const uint64_t* row_ids, const float* raw, lb200_index** out) {
+  if (metric != LB200_L2 && metric != LB200_COSINE && metric != LB200_DOT) return set_err(LB200_EINVAL, "unknown metric %d", metric);
+  if (!dim || !nlist) return set_err(LB200_EINVAL, "bad shape dim=%u nlist=%u", dim, nlist);
+  if (!centroids || !part_offsets) return set_err(LB200_EINVAL, "null index buffers");
+  if (part_offsets[0] != 0) return set_err(LB200_EINVAL, "part_offsets[0] must be 0");
+  for (uint32_t p = 0; p < nlist; p++)
+    if (part_offsets[p + 1] < part_offsets[p]) return set_err(LB200_EINVAL, "part_offsets not monotone at %u", p);
+  const uint64_t N = part_offsets[nlist];
+  if (N >= (1ull << 32)) return set_err(LB200_EUNSUPPORTED, "N=%llu rows >= 2^32", (unsigned long long)N);
+  if (N && (!raw || !row_ids)) return set_err(LB200_EINVAL, "IVF_FLAT needs the raw vectors and row ids");
+  int rc = select_device(device_id);
+  if (rc) return rc;
+  lb200_index* ix = new lb200_index();
+  ix->device = device_id; ix->metric = metric; ix->dim = dim; ix->nlist = nlist; ix->M = 1; ix->dsub = dim;
+  ix->N = N; ix->bits = 32;
+  ix->h_part_off.assign(part_offsets, part_offsets + nlist + 1);
+  auto fail = [&](int code) { lb200_index_destroy(ix); return code; };
+#define CKX(call)                                                                                          \
+  do {                                                                                                     \
+    cudaError_t e_ = (call);                                                                               \
+    if (e_ != cudaSuccess)                                                                                 \
+      return fail(set_err(e_ == cudaErrorMemoryAllocation ? LB200_ENOMEM : LB200_ECUDA, "%s failed: %s (%s:%d)", \
+                          #call, cudaGetErrorString(e_), __FILE__, __LINE__));                             \
+  } while (0)
+  // rows of a partition sorted by row id: (distance, local index) order == (distance, row id) order
+  std::vector<uint64_t> h_rid((size_t)N);
+  std::vector<float> h_raw((size_t)N * dim);
+  std::vector<uint32_t> perm;
+  uint32_t nonempty = 0;
+  for (uint32_t p = 0; p < nlist; p++) {
+    const uint64_t o = part_offsets[p], n = part_offsets[p + 1] - o;
+    ix->max_part = std::max(ix->max_part, n);
+    nonempty += n > 0;
+    perm.resize(n);
+    for (uint64_t i = 0; i < n; i++) perm[i] = (uint32_t)i;
+    std::stable_sort(perm.begin(), perm.end(), [&](uint32_t x, uint32_t y) { return row_ids[o + x] < row_ids[o + y]; });
+    for (uint64_t i = 0; i < n; i++) {
+      h_rid[o + i] = row_ids[o + perm[i]];
+      memcpy(h_raw.data() + (o + i) * dim, raw + (o + perm[i]) * dim, (size_t)dim * 4);
+    }
+  }
+  ix->avg_np = (double)N / std::max(1u, nonempty);
+  cudaDeviceProp prop;
+  CKX(cudaGetDeviceProperties(&prop, device_id));
+  ix->sm_count = prop.multiProcessorCount;
+  ix->smem_optin = prop.sharedMemPerBlockOptin;
+  ix->smem_per_sm = prop.sharedMemPerMultiprocessor;
+  CKX(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+  for (auto& e : ix->ev) CKX(cudaEventCreate(&e));
+  CKX(cudaMalloc(&ix->d_centroids, (size_t)nlist * dim * 4));
+  CKX(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
+  CKX(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));
+  CKX(cudaMalloc(&ix->d_raw, std::max<size_t>((size_t)N * dim * 4, 16)));
+  CKX(cudaMemcpyAsync(ix->d_centroids, centroids, (size_t)nlist * dim * 4, cudaMemcpyHostToDevice, ix->stream));
+  CKX(cudaMemcpyAsync(ix->d_part_off, part_offsets, (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
+  if (N) {
+    CKX(cudaMemcpyAsync(ix->d_row_ids, h_rid.data(), N * 8, cudaMemcpyHostToDevice, ix->stream));
+    CKX(cudaMemcpyAsync(ix->d_raw, h_raw.data(), (size_t)N * dim * 4, cudaMemcpyHostToDevice, ix->stream));
+  }
+  CKX(cudaStreamSynchronize(ix->stream));
+#undef CKX
   *out = ix;
   return 0;
 }

@@ -264,7 +264,7 @@ static int launch_merge2(const float* in_dist, const uint64_t* in_rowid, const u
 // The whole device pipeline for one batch of queries; asynchronous on `st`.
 static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st);  // api_pq4.inl
 static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st) {
-  if (ix->bits == 4) return search4_pipeline(ix, a, st);
+  if (ix->bits != 8) return search4_pipeline(ix, a, st);  // 4-bit PQ, IVF_FLAT
   const uint32_t Q = a.Q, dim = ix->dim, nlist = ix->nlist;
   const uint32_t P = a.d_part_ids ? a.P : std::min(a.nprobes, nlist);
   const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);

@@ -456,6 +456,34 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
   }
 }
 
+// ---- IVF_FLAT sub-index ------------------------------------------------------------------------------------------
+// FlatDistanceCal::distance_all (rust/lance-index/src/vector/flat/storage.rs:315-375) of one probed partition:
+// distance_type.func()(key, row) per row -- l2 / cosine (norm_l2(key), cosine_fast) / dot_distance on the raw f32 rows,
+// no residual (FlatQuantizer::use_residual = false, quantizer.rs:46), key already normalised for cosine
+// (ivf/v2.rs:370-373).  One CTA per (query, partition) pair; distances go to an HBM scratch row for
+// flat_select_kernel.  exact_distance() is the device restatement the refine step already uses.
+__global__ void __launch_bounds__(256)
+scanflat_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
+                const uint64_t* __restrict__ part_off, const float* __restrict__ raw, float* __restrict__ out,
+                size_t out_stride, unsigned long long* __restrict__ stats) {
+  extern __shared__ float smf[];  // [dim] key
+  __shared__ float s_xn;
+  const uint32_t pair = blockIdx.x, q = pair / P, p = probes[pair], tid = threadIdx.x;
+  for (uint32_t i = tid; i < dim; i += 256) smf[i] = keys[(size_t)q * dim + i];
+  __syncthreads();
+  if (tid == 0) s_xn = metric == 1 ? norm_l2(smf, (int)dim) : 0.0f;
+  __syncthreads();
+  const float xn = s_xn;
+  const uint64_t off = part_off[p], n = part_off[p + 1] - off;
+  float* orow = out + (size_t)pair * out_stride;
+  for (uint64_t i = tid; i < out_stride; i += 256)
+    orow[i] = i < n ? exact_distance(metric, smf, xn, raw + (off + i) * dim, (int)dim) : __int_as_float(0x7fc00000);
+  if (stats && tid == 0) {
+    atomicAdd(&stats[0], (unsigned long long)n * dim * 4);
+    atomicAdd(&stats[1], 1ull);
+  }
+}
+
 // local index of a selected row -> row id and position in the index (for the merge and the refine)
 __global__ void gather4_kernel(const uint32_t* __restrict__ probes, const uint64_t* __restrict__ part_off,
                                const uint64_t* __restrict__ row_ids, const uint64_t* __restrict__ sel_idx,

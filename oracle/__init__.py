@@ -369,3 +369,28 @@ def ref_distance_batch_f16(metric, q, vectors):
         else:
             out[i] = r.cosine_f16_avx2(_p(q), C.c_float(xn), y, C.c_uint32(d))
     return out
+
+
+# ---- IVF_FLAT (IVFIndex<FlatIndex, FlatQuantizer>) -------------------------------------------------
+def ivf_flat_search(data, query, k, nprobes, refine_factor=None, lower=None, upper=None):
+    """VectorIndex::search on an IVF_FLAT index for ONE query (ivf/v2.rs:368-401), then the scanner's refine when
+    refine_factor is given.  data: IvfPqData with raw_vectors [N][dim] in partition order (codes unused).
+    Per probed partition FlatIndex::search (flat/index.rs:76-137) with FlatDistanceCal (flat/storage.rs:315-375):
+    distance_type.func()(key, row) on the raw rows, key normalised for cosine, no residual."""
+    query = _f32(query)
+    metric = data.metric
+    key = normalize(query) if metric == "cosine" else query
+    kp = k * (refine_factor or 1)
+    probes, _ = find_partitions(data.centroids, key, nprobes, metric)
+    ds, rs = [], []
+    for p in probes.tolist():
+        o, e = int(data.part_offsets[p]), int(data.part_offsets[p + 1])
+        d, r = flat_knn_rows(metric, key, data.raw_vectors[o:e], data.row_ids[o:e], kp, lower, upper)
+        ds.append(d)
+        rs.append(r)
+    ad, ar = _topk_by_distance(np.concatenate(ds), np.concatenate(rs), kp) if ds else (np.zeros(0, np.float32), np.zeros(0, np.uint64))
+    if refine_factor is not None:
+        lut = {int(r): i for i, r in enumerate(np.asarray(data.row_ids, dtype=np.uint64).tolist())}
+        vec = _f32(data.raw_vectors)[[lut[int(r)] for r in ar.tolist()]] if len(ar) else np.zeros((0, len(query)), np.float32)
+        ad, ar = flat_knn_rows(metric, query, vec, ar, k, lower, upper)
+    return ad, ar
