@@ -41,7 +41,9 @@ WORKLOADS = {
     "cfg1_pq4": (1_000_000, 128, 256, 16, "l2", 20, 10, 0, 10_000,
                  "SIFT-shaped 1Mx128 f32, IVF256,PQ16 4-bit, L2, k=10, nprobes=20, 10k queries (cfg1 shape, num_bits=4)"),
 }
-PQ_BITS = {"cfg1_pq4": 4}
+WORKLOADS["cfg1_flat"] = (1_000_000, 128, 256, 16, "l2", 20, 10, 0, 2_000,
+                          "SIFT-shaped 1Mx128 f32, IVF256 IVF_FLAT (raw rows, no quantizer), L2, k=10, nprobes=20, 2000 queries (cfg1 shape)")
+PQ_BITS = {"cfg1_pq4": 4, "cfg1_flat": 32}
 _BITS = 8  # set by main() from the workload
 
 
@@ -310,6 +312,9 @@ def main():
         wl = wl[:8] + (args.queries, wl[9].replace("%d queries" % wl[8], "%d queries" % args.queries)
                        .replace("10k queries", "%d queries" % args.queries))
     if args.impl == "reference":
+        if _BITS == 32:
+            print(json.dumps({"impl": "reference", "unavailable": "cfg1_flat has no oracle arm: use --workload cfg4 (headline)"}))
+            return
         run_reference(args, wl)
         return
 
@@ -330,7 +335,7 @@ def main():
     N, d, nlist, M, metric, nprobes, k, refine, Q, desc = wl
     kprime = k * max(refine, 1)
     t_build = time.perf_counter()
-    data, sizes, owner = make_shard(wl, seed, rank, args.shard_of or world, keep_raw=refine > 0)
+    data, sizes, owner = make_shard(wl, seed, rank, args.shard_of or world, keep_raw=refine > 0 or _BITS == 32)
     queries = make_queries(wl, data.centroids, seed)
     ix = IvfPqIndex(data, device_id=local)
     if args.scan_variant:
@@ -466,7 +471,9 @@ def main():
     pre = pre and (d // M) in (8, 16)
     kname = "scan_kernel"
     if st["scan_variant"] == 4:
-        kname = "scan4_kernel + flat_select_kernel (4-bit PQ)"
+        kname = ("scan4_kernel + flat_select_kernel" if os.environ.get("LB200_PQ4_SIMPLE") else "scan4f_kernel") + " (4-bit PQ)"
+    if st["scan_variant"] == 32:
+        kname = "scanflat_kernel + flat_select_kernel (IVF_FLAT; bytes = n_p*dim*4 per pair)"
     if st["scan_variant"] == 3:
         kname = "scan3_kernel" if (shard_mode or nprobes < 16 or pre) else "scan3_nb_kernel"
         if pre:
@@ -506,7 +513,7 @@ def main():
     }
     if world > 1:
         line["roofline"]["all_ranks_achieved"] = float(bsum.item()) / (float(tmax.item()) * 1e-3) / 1e9
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and _BITS != 32:  # the C oracle index has no IVF_FLAT mode (tests use oracle.ivf_flat_search)
         import oracle
         cores = oracle.max_threads()
         qps0, _ = cpu_reference_run(wl, data, queries, min(32, Q), cores)

@@ -98,6 +98,11 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     if (flat) {
       const size_t fs = (size_t)dim * 4;
       if (fs > 48 * 1024) CK(cudaFuncSetAttribute(scanflat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs));
+      if (ix->metric == LB200_L2 && !getenv("LB200_FLAT_SIMPLE")) {
+        if (fs > 48 * 1024) CK(cudaFuncSetAttribute(scanflat_l2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs));
+        scanflat_l2_kernel<<<(uint32_t)pn, 256, fs, st>>>(keys + (size_t)q0 * dim, probes + p0, P, dim, ix->d_part_off,
+                                                           ix->d_raw, d_dist, stride, d_stats);
+      } else
       scanflat_kernel<<<(uint32_t)pn, 256, fs, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim,
                                                       ix->d_part_off, ix->d_raw, d_dist, stride, d_stats);
     } else {

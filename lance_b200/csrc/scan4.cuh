@@ -484,6 +484,65 @@ scanflat_kernel(int metric, const float* __restrict__ keys, const uint32_t* __re
   }
 }
 
+// L2 variant with coalesced row reads: a HALF-WARP per row, lane l = accumulator lane l of l2_scalar::<f32,f32,16>
+// (l2.rs:65-99: sums[l] += (x[c*16+l] - y[c*16+l])^2 over the chunks in order), so a chunk is one 64-byte read of
+// the half-warp; the 16 lane sums are then added in lane order (shuffles) exactly as `sums.iter().sum()` does, after
+// the d % 16 remainder that the reference sums first.  Four rows per half-warp step for load-level parallelism.
+__global__ void __launch_bounds__(256)
+scanflat_l2_kernel(const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
+                   const uint64_t* __restrict__ part_off, const float* __restrict__ raw, float* __restrict__ out,
+                   size_t out_stride, unsigned long long* __restrict__ stats) {
+  extern __shared__ float smf[];  // [dim] key
+  const uint32_t pair = blockIdx.x, q = pair / P, p = probes[pair], tid = threadIdx.x;
+  for (uint32_t i = tid; i < dim; i += 256) smf[i] = keys[(size_t)q * dim + i];
+  __syncthreads();
+  const uint64_t off = part_off[p], n = part_off[p + 1] - off;
+  float* orow = out + (size_t)pair * out_stride;
+  const uint32_t hw = tid >> 4, l = tid & 15;
+  const uint32_t nchunk = dim >> 4, rem0 = nchunk << 4;
+  for (uint64_t i = n + tid; i < out_stride; i += 256) orow[i] = __int_as_float(0x7fc00000);  // padding of the scratch row
+  constexpr int RW = 4;  // rows per half-warp step: RW independent load streams
+  for (uint64_t base = 0; base < n; base += 16 * RW) {   // uniform trip count
+    uint64_t r[RW];
+    const float* y[RW];
+    float a[RW], sr[RW];
+#pragma unroll
+    for (int k = 0; k < RW; k++) {
+      r[k] = base + 16 * k + hw;
+      y[k] = raw + (off + (r[k] < n ? r[k] : 0)) * dim;
+      a[k] = 0.0f;
+      sr[k] = 0.0f;
+    }
+    for (uint32_t i = rem0; i < dim; i++) {   // remainder first (every lane the same value)
+#pragma unroll
+      for (int k = 0; k < RW; k++) {
+        const float d = __fsub_rn(smf[i], y[k][i]);
+        sr[k] = __fadd_rn(sr[k], __fmul_rn(d, d));
+      }
+    }
+#pragma unroll 4
+    for (uint32_t c = 0; c < nchunk; c++) {
+      const float x = smf[c * 16 + l];
+#pragma unroll
+      for (int k = 0; k < RW; k++) {
+        const float d = __fsub_rn(x, y[k][c * 16 + l]);
+        a[k] = __fadd_rn(a[k], __fmul_rn(d, d));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < RW; k++) {
+      float t = 0.0f;
+#pragma unroll
+      for (int i = 0; i < 16; i++) t = __fadd_rn(t, __shfl_sync(0xffffffffu, a[k], i, 16));
+      if (l == 0 && r[k] < n) orow[r[k]] = __fadd_rn(sr[k], t);
+    }
+  }
+  if (stats && tid == 0) {
+    atomicAdd(&stats[0], (unsigned long long)n * dim * 4);
+    atomicAdd(&stats[1], 1ull);
+  }
+}
+
 // local index of a selected row -> row id and position in the index (for the merge and the refine)
 __global__ void gather4_kernel(const uint32_t* __restrict__ probes, const uint64_t* __restrict__ part_off,
                                const uint64_t* __restrict__ row_ids, const uint64_t* __restrict__ sel_idx,
