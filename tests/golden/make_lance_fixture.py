@@ -1,7 +1,8 @@
 """Extracts the reference-written IVF_PQ fixtures used by tests/test_reader.py.
 
-Runs only where /root/reference exists (this container).  It copies, byte for byte, the legacy
-`index.idx` files the reference keeps as test data —
+Runs only where /root/reference exists (this container).  It packs, byte for byte, the legacy
+`index.idx` files the reference keeps as test data (Apache-2.0, like the rest of the reference) into
+`lance_files/reference_index_files.npz` —
   test_data/v0.8.14/corrupt_index/_indices/*/index.idx          (Lance 0.8.14; dim 128, IVF4, PQ16; 1000 / 2000 rows)
   test_data/v0.21.0/bad_index_fragment_bitmap/_indices/*/index.idx (Lance 0.21.0; dim 16, IVF1, PQ1; 256 + 32-row delta)
 (used by rust/lance/src/dataset.rs:4262,4392) — and pulls the indexed column's raw vectors out of the
@@ -17,7 +18,6 @@ Data-file parsing (test tooling only):
   * manifest: `pb::Manifest.fragments[] {id, files[] {path}, physical_rows}` (protos/table.proto).
 """
 import os
-import shutil
 import struct
 import sys
 
@@ -108,8 +108,9 @@ def main():
         rid.append((np.uint64(fid) << np.uint64(32)) | np.arange(len(x), dtype=np.uint64))
         vec.append(x)
     np.savez_compressed(f"{OUT}/v0.8.14_raw_vectors.npz", row_ids=np.concatenate(rid), vectors=np.concatenate(vec))
+    packed = {}
     for u in os.listdir(f"{src}/_indices"):
-        shutil.copyfile(f"{src}/_indices/{u}/index.idx", f"{OUT}/v0.8.14_{u[:8]}_index.idx")
+        packed[f"v0.8.14_{u[:8]}"] = np.frombuffer(open(f"{src}/_indices/{u}/index.idx", "rb").read(), dtype=np.uint8)
     # ---- v0.21.0 -------------------------------------------------------------------------------------
     src = f"{REF}/v0.21.0/bad_index_fragment_bitmap"
     frags = {}
@@ -122,7 +123,9 @@ def main():
         vec.append(x)
     np.savez_compressed(f"{OUT}/v0.21.0_raw_vectors.npz", row_ids=np.concatenate(rid), vectors=np.concatenate(vec))
     for u in os.listdir(f"{src}/_indices"):
-        shutil.copyfile(f"{src}/_indices/{u}/index.idx", f"{OUT}/v0.21.0_{u[:8]}_index.idx")
+        packed[f"v0.21.0_{u[:8]}"] = np.frombuffer(open(f"{src}/_indices/{u}/index.idx", "rb").read(), dtype=np.uint8)
+    # the index files' bytes, unchanged, in one archive (tests/conftest.py::lance_files_dir writes them back out)
+    np.savez_compressed(f"{OUT}/reference_index_files.npz", **packed)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(f"{OUT}/{f}"))
 

@@ -13,7 +13,9 @@ from lance_b200.reader import open_legacy_ivf_pq
 from lance_b200.synth import build_ivf_pq
 
 pytestmark = pytest.mark.gpu
-G = os.path.join(os.path.dirname(__file__), "golden", "lance_files")
+from conftest import lance_files_dir  # noqa: E402
+
+G = lance_files_dir()
 
 
 @pytest.fixture(scope="module", autouse=True)

@@ -17,7 +17,9 @@ import pytest
 from lance_b200.reader import open_legacy_ivf_pq, parse_index_proto, read_footer
 from lance_b200.synth import IvfPqData
 
-G = os.path.join(os.path.dirname(__file__), "golden", "lance_files")
+from conftest import lance_files_dir  # noqa: E402
+
+G = lance_files_dir()
 FILES = {
     # tag, uuid prefix: (name, dataset_version, dim, nlist, M, lengths)
     ("v0.8.14", "d32dac97"): ("vector_idx", 1, 128, 4, 16, [251, 236, 249, 264]),
