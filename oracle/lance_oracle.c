@@ -9,8 +9,16 @@
  * tests/test_oracle_golden.py: l2.rs:316-335, fixture_test.rs:165-231,
  * pq/distance.rs:281-308, pq/storage.rs:741-751, pq.rs:546-592, kmeans.rs:785-810,
  * scanner.rs:2410-2510/2773-2814, knn.rs:667-747, ivf/v2.rs:1192-1302).  The reference
- * itself (Rust, lance v0.23.1) cannot be built in this image (no cargo/rustc), so
- * there is no oracle/_ref binary; tie order of equal distances is unpinned in the
+ * and on reference-WRITTEN bytes: all 48 288 PQ codes and partition assignments of the four
+ * legacy index files the reference keeps as test data equal lo_pq_quantize /
+ * lo_find_partitions on the datasets' raw vectors (tests/test_reader.py).
+ * 4-bit PQ (lo_compute_pq_distance_4bit, lo_quantize_distance_table): PARITY UNPINNED -- the
+ * reference holds no known-answer vector for it; checked against an independent numpy
+ * restatement of the same source lines (tests/test_oracle_pq4.py).
+ * The reference itself (Rust, lance v0.23.1) cannot be built in this image (no cargo/rustc);
+ * the one piece that compiles from its own source, rust/lance-linalg/src/simd/f16.c, is built
+ * by `make ref` into oracle/_ref/libf16_ref.so and pins the f16 restatement at the end of this
+ * file within tolerance (tests/test_f16.py).  Tie order of equal distances is unpinned in the
  * reference (arrow-ord 53.3.0 sort_to_indices / slice::sort_unstable / datafusion
  * 44.0.0 TopK are all unstable) and is fixed here as (distance total-order, id) ascending.
  *
