@@ -190,7 +190,7 @@ __device__ __noinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nbins
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 6)
 scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
               uint32_t M, const float* __restrict__ centroids, const float* __restrict__ codebook,
               const uint64_t* __restrict__ part_off, const uint64_t* __restrict__ pad_off /*[nlist+1] padded rows*/,
