@@ -255,6 +255,12 @@ int32_t lb200_rerank(int32_t device_id, int32_t metric, uint32_t dim, const floa
                      const float* lower_or_null, const float* upper_or_null, float* out_dist,
                      uint64_t* out_rowid, uint32_t* out_count);
 
+/* normalize_arrow (rust/lance-linalg/src/kernels.rs:119-142) of a batch of keys: the step the ANN exec
+ * nodes apply to the key of a cosine index before find_partitions / search_in_partition
+ * (rust/lance/src/io/exec/knn.rs:366-369,616-619), for callers that drive those two entry points
+ * themselves (e.g. the prefilter path).  lb200_search does it internally. */
+int32_t lb200_normalize(int32_t device_id, uint32_t dim, const float* queries, uint32_t Q, float* out);
+
 /* Instrumentation (not part of the reference surface): per-handle counters of the last
  * search / search_partitions call, used by bench.py for the roofline line. */
 typedef struct {

@@ -17,7 +17,7 @@ EXPORTS = [
     "lb200_peer_thresholds_export", "lb200_peer_thresholds_attach", "lb200_peer_thresholds_detach",
     "lb200_merge_topk", "lb200_rerank",
     "lb200_index_file_open", "lb200_index_file_open_bytes", "lb200_index_file_get_info", "lb200_index_file_close",
-    "lb200_index_open", "lb200_flat_distance_f16", "lb200_flat_topk_f16",
+    "lb200_index_open", "lb200_flat_distance_f16", "lb200_flat_topk_f16", "lb200_normalize",
 ]
 
 

@@ -102,3 +102,25 @@ extern "C" int32_t lb200_rerank(int32_t device_id, int32_t metric, uint32_t dim,
   CK(cudaStreamSynchronize(st));
   return 0;
 }
+
+// normalize_arrow (rust/lance-linalg/src/kernels.rs:119-142) for a batch of keys: what the ANN exec nodes apply to the
+// key of a cosine index before find_partitions / search_in_partition (rust/lance/src/io/exec/knn.rs:366-369,616-619).
+extern "C" int32_t lb200_normalize(int32_t device_id, uint32_t dim, const float* queries, uint32_t Q, float* out) {
+  if (!dim) return set_err(LB200_EINVAL, "dim must be > 0");
+  int rc = select_device(device_id);
+  if (rc) return rc;
+  if (!Q) return 0;
+  if (!queries || !out) return set_err(LB200_EINVAL, "null argument");
+  HostStage hs;
+  const size_t b = Arena::pad((size_t)Q * dim * 4);
+  CK(cudaMalloc(&hs.p, 2 * b));
+  float* d_in = (float*)hs.p;
+  float* d_out = (float*)((char*)hs.p + b);
+  cudaStream_t st = nullptr;
+  CK(cudaMemcpyAsync(d_in, queries, (size_t)Q * dim * 4, cudaMemcpyHostToDevice, st));
+  normalize_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(d_in, d_out, Q, dim);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, d_out, (size_t)Q * dim * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}

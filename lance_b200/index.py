@@ -68,6 +68,7 @@ class IvfPqIndex:
         self.part_offsets = np.ascontiguousarray(data.part_offsets, dtype=np.uint64)
         self.has_raw = data.raw_vectors is not None
         self.device_id = device_id
+        self.row_ids = np.ascontiguousarray(data.row_ids, dtype=np.uint64)   # host copy, index order (prefilter masks)
         h = C.c_void_p()
         cents, cb = _f32(data.centroids), _f32(data.codebook)
         codes = np.ascontiguousarray(data.codes, dtype=np.uint8)
@@ -87,6 +88,7 @@ class IvfPqIndex:
         self.metric, self.dim, self.nlist, self.M = meta.metric, int(meta.dim), int(meta.nlist), int(meta.M)
         self.part_offsets = np.ascontiguousarray(meta.part_offsets, dtype=np.uint64)
         self.has_raw, self.device_id, self._h = has_raw, device_id, handle
+        self.row_ids = np.ascontiguousarray(meta.row_ids, dtype=np.uint64)
         return self
 
     def close(self):
@@ -352,3 +354,12 @@ def flat_knn_f16(key, metric, vectors, k, validity=None, lower_bound=None, upper
                                          C.c_uint64(n), C.c_uint32(k), _fptr(lower_bound), _fptr(upper_bound), _p(od),
                                          _p(oi), _p(oc)))
     return od, oi, oc
+
+
+def normalize(key, device_id=0):
+    """normalize_arrow (kernels.rs:119-142) of a batch of keys on the device (lb200_normalize)."""
+    key2 = np.atleast_2d(_f32(key))
+    out = np.empty_like(key2)
+    check(_lib.lib().lb200_normalize(C.c_int32(device_id), C.c_uint32(key2.shape[1]), _p(key2), C.c_uint32(key2.shape[0]),
+                                     _p(out)))
+    return out

@@ -301,13 +301,33 @@ def flat_knn_rows(metric, key, vectors, row_ids, k, lower=None, upper=None):
 
 
 def nearest_plan(deltas, take, key, k, nprobes, refine_factor=None, lower=None, upper=None,
-                 unindexed_ids=None, unindexed_vectors=None, fast_search=False):
-    """Scanner::knn for ONE key.  deltas: OracleIndex list (same metric); take(row_ids) -> vectors."""
+                 unindexed_ids=None, unindexed_vectors=None, fast_search=False, allowed=None):
+    """Scanner::knn for ONE key.  deltas: OracleIndex list (same metric); take(row_ids) -> vectors.
+    allowed: optional row-id allow-list (the prefilter's RowIdMask): per probed partition the reference then runs the
+    per-row path (flat/index.rs:106-122 -> DistCalculator::distance), and the flat scan is filtered."""
     key = _f32(key)
     metric = deltas[0].data.metric
     kp = k * (refine_factor or 1)
     ds, rs = [], []
+    if allowed is not None:
+        allowed = np.unique(np.asarray(allowed, dtype=np.uint64))
+        if unindexed_ids is not None:
+            keep = np.isin(np.asarray(unindexed_ids, dtype=np.uint64), allowed)
+            unindexed_ids, unindexed_vectors = np.asarray(unindexed_ids)[keep], _f32(unindexed_vectors)[keep]
     for ix in deltas:          # ANNIvfSubIndexExec fan-out over the delta indices
+        if allowed is not None:
+            d = ix.data
+            k2 = normalize(key) if metric == "cosine" else key
+            probes, _ = find_partitions(d.centroids, k2, nprobes, metric)
+            for p in probes.tolist():
+                o, e = int(d.part_offsets[p]), int(d.part_offsets[p + 1])
+                bits = np.zeros(((e - o + 63) // 64) + 1, dtype=np.uint64)
+                on = np.nonzero(np.isin(d.row_ids[o:e], allowed))[0]
+                np.bitwise_or.at(bits, on >> 6, np.uint64(1) << (on & 63).astype(np.uint64))
+                pd, pr = ix.search_in_partition(p, k2, kp, lower, upper, bitmask=bits)
+                ds.append(pd)
+                rs.append(pr)
+            continue
         od, oi, oc, _ = ix.search(key[None, :], kp, nprobes, 0, lower, upper)
         ds.append(od[0, :oc[0]])
         rs.append(oi[0, :oc[0]])

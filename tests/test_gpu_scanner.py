@@ -228,3 +228,34 @@ def test_native_index_open_equals_python_reader_path(oracle, tag, u):
             for j in range(len(q)):
                 _same_row(gd[j], gi[j], int(gc[j]), rd[j, :rc[j]], ri[j, :rc[j]], f"open {tag} k={k} rf={rf} q{j}")
         ix.close()
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+def test_nearest_with_prefilter(oracle, metric):
+    """A row-id allow-list (deletions / scalar filter -> RowIdMask, prefilter.rs:26-51) through the whole plan: masked
+    index scan per probed partition, filtered flat scan of the unindexed rows, refine, knn_combined."""
+    from lance_b200 import IvfPqIndex
+    from lance_b200.scanner import VectorDataset
+    rng = np.random.default_rng(23)
+    d, n = 32, 3000
+    x = rng.normal(size=(n, d)).astype(np.float32)
+    rid = (rng.permutation(1 << 20)[:n]).astype(np.uint64)
+    lut = {int(r): i for i, r in enumerate(rid.tolist())}
+    take = lambda ids: x[[lut[int(r)] for r in np.asarray(ids).reshape(-1).tolist()]]
+    datas = [build_ivf_pq(x[a:b], metric, 6, 4, seed=a, row_ids=rid[a:b]) for a, b in ((0, 1500), (1500, 2500))]
+    ixs = [IvfPqIndex(dd) for dd in datas]
+    oxs = [oracle.OracleIndex(dd) for dd in datas]
+    q = np.concatenate([x[::400], rng.normal(size=(4, d)).astype(np.float32)])
+    ds = VectorDataset(take, d, ixs, rid[2500:], x[2500:])
+    from lance_b200 import Query
+    for frac in (0.5, 0.02):
+        allowed = rid[rng.random(n) < frac]
+        for k, nprobes, rf, fast in ((10, 3, None, False), (5, 6, 3, False), (10, 2, None, True)):
+            gd, gi, gc = ds.nearest(Query(q, k=k, nprobes=nprobes, refine_factor=rf), fast_search=fast, allowed_row_ids=allowed)
+            for j in range(len(q)):
+                rd, rr = oracle.nearest_plan(oxs, take, q[j], k, nprobes, rf, None, None, rid[2500:], x[2500:], fast,
+                                             allowed=allowed)
+                _same_row(gd[j], gi[j], int(gc[j]), rd, rr, f"prefilter {metric} frac={frac} k={k} P={nprobes} rf={rf} q{j}")
+                assert np.isin(gi[j, :int(gc[j])], allowed).all()
+    for ix in ixs:
+        ix.close()
