@@ -84,3 +84,21 @@ def test_host_mirror_validation():
     with pytest.raises(ValueError):
         DistanceType.code("manhattan")
     assert DistanceType.code("L2") == 0 and DistanceType.code("cosine") == 1 and DistanceType.code("dot") == 2
+
+
+def test_header_is_plain_c_and_a_c_host_links(tmp_path):
+    """include/lance_b200.h must be consumable from C (the reference-side binding is an `extern "C"` block in a
+    Rust -sys crate): compile examples/open_legacy_index.c with gcc -std=c11, link it against the built library and
+    run its host-only part on a reference-written index file."""
+    import subprocess
+    from conftest import lance_files_dir
+    exe = str(tmp_path / "open_legacy_index")
+    libdir = os.path.join(ROOT, "lance_b200")
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "open_legacy_index.c"), "-L", libdir, "-llance_b200",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    out = subprocess.run([exe, os.path.join(lance_files_dir(), "v0.8.14_f358a219_index.idx")], capture_output=True,
+                         text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    assert "sm_100a" in out.stdout
+    assert "name=vector_idx column=vector metric=0 dim=128 nlist=4 M=16 bits=8 rows=2000" in out.stdout
