@@ -255,3 +255,26 @@ def test_native_reader_errors(tmp_path):
             open_legacy_ivf_pq_native(bytes(b))
         except LanceB200Error:
             pass
+
+
+def test_native_reader_survives_truncations_and_tail_edits():
+    """Random truncations of a reference-written file (with and without a re-attached tail) and random edits of the
+    16-byte tail: the native parser must either succeed or fail with an error code, never read out of bounds."""
+    from lance_b200 import LanceB200Error
+    from lance_b200.reader import open_legacy_ivf_pq_native
+    good = open(_path("v0.21.0", "dc833a6e"), "rb").read()
+    rng = np.random.default_rng(7)
+    ok = 0
+    for i in range(300):
+        cut = int(rng.integers(0, len(good)))
+        blob = good[:cut] + (good[-16:] if i % 2 else b"")
+        if i % 3 == 0:
+            t = bytearray(good[-16:])
+            t[int(rng.integers(0, 12))] = int(rng.integers(0, 256))
+            blob = good[:-16] + bytes(t)
+        try:
+            open_legacy_ivf_pq_native(blob)
+            ok += 1
+        except LanceB200Error:
+            pass
+    assert ok < 300
