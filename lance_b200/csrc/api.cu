@@ -18,8 +18,7 @@
 #include "../../include/lance_b200.h"
 #include "coarse.cuh"
 #include "flat.cuh"
-#include "scan.cuh"
-#include "scan3.cuh"
+#include "launch.h"
 #include "scan4.cuh"
 #include "worklist.cuh"
 

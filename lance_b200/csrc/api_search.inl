@@ -2,15 +2,6 @@
 
 namespace {
 
-struct ScanConfig {
-  int variant, ql, dsub_t;
-  uint32_t capw;
-  size_t smem;
-  int minb;  // variant 3: CTAs per SM the kernel is compiled for
-  int nw = 8;  // variant 3: warps per CTA
-};
-constexpr int SCAN_NW = 8;
-
 static size_t scan_smem_bytes(int variant, int ql, uint32_t M, uint32_t dim, uint32_t capw) {
   int vg = 32 / ql;
   size_t lut = variant == 1 ? (size_t)M * 256 * 4 : (size_t)(M / vg) * 256 * 32 * 4;
@@ -70,83 +61,6 @@ static int choose_scan(const lb200_index* ix, uint32_t kprime, double avg_q_per_
   if (fit(1, 1, out)) return 0;
   return set_err(LB200_EUNSUPPORTED, "k'=%u does not fit the shared-memory candidate buffers (M=%u, dim=%u)",
                  kprime, ix->M, ix->dim);
-}
-
-template <int VARIANT, int QL>
-static cudaError_t launch_scan_d(int dsub_t, int grid, size_t smem, cudaStream_t st, const ScanParams& sp,
-                                 const uint32_t* total_items) {
-#define LB200_LAUNCH(D)                                                                           \
-  do {                                                                                            \
-    auto kern = scan_kernel<VARIANT, QL, SCAN_NW, D>;                                             \
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    if (e != cudaSuccess) return e;                                                               \
-    kern<<<grid, SCAN_NW * 32, smem, st>>>(sp, total_items);                                      \
-    return cudaGetLastError();                                                                    \
-  } while (0)
-  if (dsub_t == 8) LB200_LAUNCH(8);
-  if (dsub_t == 16) LB200_LAUNCH(16);
-  LB200_LAUNCH(0);
-#undef LB200_LAUNCH
-}
-
-static cudaError_t launch_scan(const ScanConfig& c, int grid, cudaStream_t st, const ScanParams& sp,
-                               const uint32_t* total_items) {
-  if (c.variant == 1) return launch_scan_d<1, 1>(c.dsub_t, grid, c.smem, st, sp, total_items);
-  switch (c.ql) {
-    case 8: return launch_scan_d<2, 8>(c.dsub_t, grid, c.smem, st, sp, total_items);
-    case 4: return launch_scan_d<2, 4>(c.dsub_t, grid, c.smem, st, sp, total_items);
-    case 2: return launch_scan_d<2, 2>(c.dsub_t, grid, c.smem, st, sp, total_items);
-    default: return launch_scan_d<2, 1>(c.dsub_t, grid, c.smem, st, sp, total_items);
-  }
-}
-
-template <int QL, int D, int NW, int MINB, int DS, bool BOOT>
-static auto scan3_entry() {
-  if constexpr (BOOT) return scan3_kernel<QL, D, NW, MINB, DS, true>;
-  else return scan3_nb_kernel<QL, D, NW, MINB, DS>;
-}
-
-template <int QL, int D, int MINB, bool BOOT, int NW = SCAN_NW>
-static cudaError_t launch_scan3_d(int dsub_t, int sm_count, size_t smem, cudaStream_t st, const Scan3Params& sp,
-                                  const uint32_t* total_items) {
-#define LB200_LAUNCH3(DS)                                                                         \
-  do {                                                                                            \
-    auto kern = scan3_entry<QL, D, NW, MINB, DS, BOOT>();                                         \
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    if (e != cudaSuccess) return e;                                                               \
-    int nb = 0;                                                                                   \
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, NW * 32, smem);                  \
-    if (e != cudaSuccess) return e;                                                               \
-    if (nb < 1) return cudaErrorLaunchOutOfResources;                                             \
-    kern<<<sm_count * nb, NW * 32, smem, st>>>(sp, total_items);                                  \
-    return cudaGetLastError();                                                                    \
-  } while (0)
-  if (dsub_t == 8) LB200_LAUNCH3(8);
-  if (dsub_t == 16) LB200_LAUNCH3(16);
-  if constexpr (NW == SCAN_NW) LB200_LAUNCH3(0);
-  return cudaErrorInvalidValue;
-#undef LB200_LAUNCH3
-}
-
-template <bool BOOT>
-static cudaError_t launch_scan3_b(const ScanConfig& c, int sm_count, cudaStream_t st, const Scan3Params& sp,
-                                  const uint32_t* total_items) {
-  if (c.ql == 4) {
-    if (c.minb == 2) return launch_scan3_d<4, 8, 2, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-    return launch_scan3_d<4, 8, 1, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-  }
-  if (c.minb == 2) return launch_scan3_d<2, 16, 2, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-  return launch_scan3_d<2, 16, 1, BOOT>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-}
-static cudaError_t launch_scan3(const ScanConfig& c, bool boot, int sm_count, cudaStream_t st, const Scan3Params& sp,
-                                const uint32_t* total_items) {
-  if (c.nw == 16) {  // wide CTA: one CTA per SM, tables pre-built (see search_device)
-    if (c.dsub_t == 0) return cudaErrorInvalidValue;
-    if (c.ql == 4) return launch_scan3_d<4, 8, 1, true, 16>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-    return launch_scan3_d<2, 16, 1, true, 16>(c.dsub_t, sm_count, c.smem, st, sp, total_items);
-  }
-  return boot ? launch_scan3_b<true>(c, sm_count, st, sp, total_items)
-              : launch_scan3_b<false>(c, sm_count, st, sp, total_items);
 }
 
 struct SearchArgs {

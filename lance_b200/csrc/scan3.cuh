@@ -75,43 +75,6 @@ struct Scan3Params {
 
 constexpr uint32_t KEY_PINF = 0xff800000u;  // ordered_key(+inf)
 
-// Reference layout (concat over p of transposed [M][n_p]) -> skew streams.
-// grid = (nlist, Y); one thread per 16-byte unit-lane.
-__global__ void repack_skew_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ part_off,
-                                   const uint64_t* __restrict__ sb_off, uint32_t M, uint32_t L, uint32_t D,
-                                   uint8_t* __restrict__ dst) {
-  const uint32_t p = blockIdx.x;
-  const uint64_t o = part_off[p], n = part_off[p + 1] - o;
-  const uint64_t sb0 = sb_off[p], nsb = sb_off[p + 1] - sb0;
-  const uint32_t units = L * (M / 16) + 1;
-  const uint8_t* s = src + o * M;
-  const uint64_t total = nsb * units * 32;  // 16-byte records
-  for (uint64_t rec = (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; rec < total;
-       rec += (uint64_t)gridDim.y * blockDim.x) {
-    const uint32_t lane = (uint32_t)(rec & 31);
-    const uint64_t ug = rec >> 5;
-    const uint64_t sb = ug / units;
-    const uint32_t g = (uint32_t)(ug - sb * units);
-    const uint32_t d = lane % D;
-    uint32_t w[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int b = 0; b < 16; b++) {
-      int64_t t = (int64_t)g * 16 + b - (int64_t)d;
-      if (t >= 0 && t < (int64_t)L * M) {
-        uint32_t ri = (uint32_t)(t / M), m = (uint32_t)(t % M);
-        uint64_t row = sb * 32 * L + (uint64_t)ri * 32 + lane;
-        if (row < n) w[b >> 2] |= (uint32_t)s[(uint64_t)m * n + row] << (8 * (b & 3));
-      }
-    }
-    reinterpret_cast<uint4*>(dst)[(sb0 * units) * 32 + rec] = make_uint4(w[0], w[1], w[2], w[3]);
-  }
-}
-
-__global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) p[i] = v;
-}
-
 // Packed FP32 (Blackwell FADD2/FMUL2, PTX .f32x2): two IEEE round-to-nearest operations per
 // instruction, bit-identical per half to the scalar ops.  ptxas 12.9 CONTRACTS a mul.rn.f32x2 that
 // feeds an add.rn.f32x2 into one FFMA2 (single rounding) although both carry .rn, so products are
@@ -278,7 +241,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
 // bandwidth- not latency-bound.  Returns the largest |entry| bit pattern of the item's tables (from
 // the pre-pass) for the exact-FMA row switch test.  Out of line: runs once per item.
 template <int QL>
-__device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const float* __restrict__ src,
+static __device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const float* __restrict__ src,
                                            const uint32_t* __restrict__ lut_max, size_t unit_stride,
                                            const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent) {
   constexpr uint32_t EPW = 32 / QL;
@@ -369,7 +332,7 @@ __device__ __forceinline__ void scan_unit(const uint4 W, const unsigned char* lu
 // k-th smallest of a SUBSET of the candidates, hence >= the true k-th best: a valid threshold
 // (tightness ~ k-th of all when each lane passes the minimum of its share).  Needs k <= 32.
 // Returns 0xffffffff when fewer than k lanes hold a value.  ~100 instructions, no memory traffic.
-__device__ __noinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_t lane) {
+static __device__ __noinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_t lane) {
   uint32_t r = 0;
 #pragma unroll
   for (int j = 0; j < 32; j++) {
@@ -381,7 +344,7 @@ __device__ __noinline__ uint32_t warp_bound_k(uint32_t m, uint32_t k, uint32_t l
 }
 
 // Keep the entries with key <= T of a warp's buffer (stable, in place).  Returns the new count.
-__device__ __noinline__ uint32_t warp_compact_le(uint32_t* kb, uint32_t* pb, uint32_t cnt, uint32_t T,
+static __device__ __noinline__ uint32_t warp_compact_le(uint32_t* kb, uint32_t* pb, uint32_t cnt, uint32_t T,
                                                     uint32_t lane) {
   uint32_t outn = 0;
   for (uint32_t base = 0; base < cnt; base += 32) {
@@ -472,7 +435,7 @@ __host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, u
 // Publish a query's bound (one thread): into this GPU's table and -- partition shards on several
 // GPUs -- into every peer's table with a fire-and-forget atomic-min over NVLink peer memory.  The
 // peers get the best value known here, so bounds found by the in-loop prunes travel too.
-__device__ __noinline__ void publish_bound(const ItemCtx* c, uint32_t qidx, uint32_t T) {
+static __device__ __noinline__ void publish_bound(const ItemCtx* c, uint32_t qidx, uint32_t T) {
   const uint32_t old = atomicMin(c->qthr + qidx, T);
   const uint32_t best = min(old, T);
   for (uint32_t j = 0; j < c->n_peers; j++) atomicMin(c->peers[j] + qidx, best);
@@ -481,7 +444,7 @@ __device__ __noinline__ void publish_bound(const ItemCtx* c, uint32_t qidx, uint
 // Pull the NW per-warp candidate segments of one query (segment w at w*capw, cnt[w] entries) together
 // at the start of the region.  dst index <= src index always, so the forward copy is safe.
 // Returns the total.  One warp.
-__device__ __noinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, const uint32_t* cnt, uint32_t nw,
+static __device__ __noinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, const uint32_t* cnt, uint32_t nw,
                                                     uint32_t capw, uint32_t lane) {
   uint32_t n = cnt[0];
 #pragma unroll 1
@@ -502,7 +465,7 @@ __device__ __noinline__ uint32_t gather_segments(uint32_t* dk, uint32_t* dp, con
 }
 
 // Pooled prune of a cold item (see the kernel).  Called by ALL threads of the CTA.
-__device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
+static __device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime, nq = c->nq;
   __syncthreads();
@@ -555,7 +518,7 @@ __device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
 }
 
 // End of an item: one warp per query gathers the warps' buffers, selects k', emits sorted.
-__device__ __noinline__ void finalize_fn(const ItemCtx* c) {
+static __device__ __noinline__ void finalize_fn(const ItemCtx* c) {
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime;
   for (uint32_t qq = w; qq < c->nq; qq += NW) {

@@ -125,12 +125,12 @@ struct Scan4Sel {
   uint32_t s_lt, s_hi, nless, need_ties, have_kth;
 };
 
-__device__ __noinline__ float dequant4(uint32_t S, float range, float qmin) {
+static __device__ __noinline__ float dequant4(uint32_t S, float range, float qmin) {
   return __fadd_rn(__fdiv_rn(__fmul_rn((float)S, range), 255.0f), qmin);
 }
 
 // k-th smallest over hist[0..nbins): fills sel (thread 0), all threads must call. scratch: part[256].
-__device__ __noinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nbins, uint32_t k, float range, float qmin,
+static __device__ __noinline__ void scan4_find_kth(const uint32_t* hist, uint32_t nbins, uint32_t k, float range, float qmin,
                                                uint32_t* part, Scan4Sel* sel) {
   const uint32_t tid = threadIdx.x, chunk = (nbins + 255) / 256;
   const uint32_t b0 = tid * chunk, b1 = min(nbins, b0 + chunk);

@@ -22,7 +22,7 @@ __device__ __forceinline__ bool cand_less(uint32_t ka, uint32_t pa, uint32_t kb,
 
 // Keep the k smallest of (key[i],pos[i]), i<n, n>=k>=1, by (key,rowid); they end up in
 // [0,k) in unspecified order.  Returns the k-th smallest key.  All 32 lanes must call.
-__device__ __noinline__ uint32_t warp_select_k(uint32_t* key, uint32_t* pos, uint32_t n,
+static __device__ __noinline__ uint32_t warp_select_k(uint32_t* key, uint32_t* pos, uint32_t n,
                                                uint32_t k, const uint64_t* __restrict__ rowids) {
   const uint32_t lane = threadIdx.x & 31;
   // bitwise binary search for T = k-th smallest key: largest T with #(key < T) < k
@@ -89,7 +89,7 @@ __device__ __noinline__ uint32_t warp_select_k(uint32_t* key, uint32_t* pos, uin
 
 // Sort (key,pos)[0..n) ascending by (key,rowid) via rank counting and write the result to
 // global memory.  n is small (<= 2k').  All 32 lanes must call.
-__device__ __noinline__ void warp_sort_emit(const uint32_t* key, const uint32_t* pos, uint32_t n,
+static __device__ __noinline__ void warp_sort_emit(const uint32_t* key, const uint32_t* pos, uint32_t n,
                                             const uint64_t* __restrict__ rowids /*partition base*/,
                                             uint64_t part_row_base, float* __restrict__ out_dist,
                                             uint64_t* __restrict__ out_pos,

@@ -26,6 +26,43 @@ __global__ void repack_codes_kernel(const uint8_t* __restrict__ src, const uint6
   }
 }
 
+// Reference layout (concat over p of transposed [M][n_p]) -> skew streams.
+// grid = (nlist, Y); one thread per 16-byte unit-lane.
+__global__ void repack_skew_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ part_off,
+                                   const uint64_t* __restrict__ sb_off, uint32_t M, uint32_t L, uint32_t D,
+                                   uint8_t* __restrict__ dst) {
+  const uint32_t p = blockIdx.x;
+  const uint64_t o = part_off[p], n = part_off[p + 1] - o;
+  const uint64_t sb0 = sb_off[p], nsb = sb_off[p + 1] - sb0;
+  const uint32_t units = L * (M / 16) + 1;
+  const uint8_t* s = src + o * M;
+  const uint64_t total = nsb * units * 32;  // 16-byte records
+  for (uint64_t rec = (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; rec < total;
+       rec += (uint64_t)gridDim.y * blockDim.x) {
+    const uint32_t lane = (uint32_t)(rec & 31);
+    const uint64_t ug = rec >> 5;
+    const uint64_t sb = ug / units;
+    const uint32_t g = (uint32_t)(ug - sb * units);
+    const uint32_t d = lane % D;
+    uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int b = 0; b < 16; b++) {
+      int64_t t = (int64_t)g * 16 + b - (int64_t)d;
+      if (t >= 0 && t < (int64_t)L * M) {
+        uint32_t ri = (uint32_t)(t / M), m = (uint32_t)(t % M);
+        uint64_t row = sb * 32 * L + (uint64_t)ri * 32 + lane;
+        if (row < n) w[b >> 2] |= (uint32_t)s[(uint64_t)m * n + row] << (8 * (b & 3));
+      }
+    }
+    reinterpret_cast<uint4*>(dst)[(sb0 * units) * 32 + rec] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+__global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
 // Step 0: the partition each query meets FIRST in scheduling order (work items run in ascending
 // partition id): the smallest probed, non-empty partition.  Its pair is the query's "cold" pair
 // (no running bound yet); step 1/3 pack the cold pairs of a partition into the same work items so
