@@ -155,15 +155,49 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_run(wl, data, queries, nq, threads):
-    """The reference's CPU algorithm (oracle port) on a bounded sample of the workload."""
+def cpu_reference_run(wl, data, queries, nq, threads, keep=False):
+    """The reference's CPU algorithm (oracle port) on a bounded sample of the workload.  keep=True also returns
+    the oracle's outputs (dist [nq][k'], row ids, counts, probed partitions) for the parity block."""
     import oracle
     o = oracle.OracleIndex(data)
     k, nprobes, refine = wl[6], wl[5], wl[7]
     t0 = time.perf_counter()
-    o.search(queries[:nq], k=k, nprobes=nprobes, refine_factor=refine, threads=threads)
+    res = o.search(queries[:nq], k=k, nprobes=nprobes, refine_factor=refine, threads=threads)
     dt = time.perf_counter() - t0
-    return nq / dt, dt
+    return (nq / dt, dt, res) if keep else (nq / dt, dt)
+
+
+def parity_block(ref, gpu, k, gpu_probes=None, tol=1e-5):
+    """Compare the GPU results of the benchmarked batch with the oracle's on the same queries of the same index
+    (north star: identical probed partitions; row ids identical except distance ties within 1e-5 relative;
+    distances within 1e-5 relative).  ref = (dist, rowid, count, probes) from the oracle, gpu = (dist, rowid, count)."""
+    rd, ri, rc, rp = ref
+    gd, gi, gc = gpu
+    nq = rd.shape[0]
+    rd, ri = rd[:, :k], ri[:, :k]
+    gd, gi, gc = gd[:nq, :k], gi[:nq, :k].astype(np.uint64), gc[:nq].astype(np.int64)
+    rc = np.minimum(rc.astype(np.int64), k)
+    valid = np.arange(k)[None, :] < rc[:, None]
+    out = {"queries_checked": int(nq), "tolerance_rel": tol,
+           "count_mismatches": int(np.count_nonzero(gc != rc))}
+    if gpu_probes is not None:
+        gp = np.asarray(gpu_probes)[:nq]
+        out["probe_set_mismatches"] = int(sum(set(a.tolist()) != set(b.tolist()) for a, b in zip(gp, rp)))
+        out["probe_order_mismatches"] = int(np.count_nonzero((gp != rp).any(axis=1)))
+    idm = (gi != ri) & valid
+    scale = np.maximum(np.abs(rd), np.float32(1e-30))
+    with np.errstate(invalid="ignore", over="ignore"):
+        rel = np.where(valid, np.abs(gd.astype(np.float64) - rd.astype(np.float64)) / scale, 0.0)
+    rel = np.nan_to_num(rel, nan=0.0, posinf=np.inf)
+    # an id mismatch is an explained tie when the two rows' distances agree within the tolerance
+    explained = idm & (rel <= tol)
+    out["id_mismatches"] = int(np.count_nonzero(idm))
+    out["explained_ties"] = int(np.count_nonzero(explained))
+    out["unexplained_mismatches"] = int(np.count_nonzero(idm & ~explained)) + out["count_mismatches"]
+    out["max_rel_err"] = float(rel.max()) if rel.size else 0.0
+    out["distance_bits_identical"] = bool(np.array_equal(gd.view(np.uint32)[valid], rd.view(np.uint32)[valid]))
+    out["checker"] = "oracle port (oracle/lance_oracle.c) on the same index and the first queries of the same batch"
+    return out
 
 
 def run_reference(args, wl):
@@ -277,10 +311,13 @@ def run_flat(args):
         cores = oracle.max_threads()
         nq = 32
         t0 = time.perf_counter()
-        oracle.flat_knn("l2", queries[:nq], vecs, k, threads=cores)
+        fres = oracle.flat_knn("l2", queries[:nq], vecs, k, threads=cores)
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": nq / dt, "unit": "queries/s", "cores": cores, "kind": "port",
                                 "sample": f"first {nq} queries, {dt:.1f} s, oracle port on {cores} threads"}
+        torch.cuda.synchronize()
+        line["parity"] = parity_block((fres[0], fres[1], fres[2], None),
+                                      (od.cpu().numpy(), oi.cpu().numpy().view(np.uint64), oc.cpu().numpy()), k)
     print(json.dumps(line), flush=True)
 
 
@@ -518,10 +555,18 @@ def main():
         cores = oracle.max_threads()
         qps0, _ = cpu_reference_run(wl, data, queries, min(32, Q), cores)
         nq = int(max(32, min(Q, qps0 * 15.0)))
-        cqps, cdt = cpu_reference_run(wl, data, queries, nq, cores)
+        cqps, cdt, ref = cpu_reference_run(wl, data, queries, nq, cores, keep=True)
         line["cpu_baseline"] = {"value": cqps, "unit": "queries/s", "cores": cores, "kind": "port",
                                 "sample": f"first {nq} queries of the same batch, {cdt:.1f} s, queries spread over "
-                                          f"{cores} threads (oracle port of the Rust reference)"}
+                                          f"{cores} threads (oracle port of the Rust reference)",
+                                "note": "kinder to the CPU than the reference: heap top-k per partition where "
+                                        "flat/index.rs:124 sorts all n_p candidates; queries spread over all threads"}
+        # parity at the benchmarked size: the oracle's outputs for those queries against the GPU results of the
+        # same batch (the last lb200_search call above), plus the probed partitions through lb200_find_partitions
+        from lance_b200 import normalize as _normalize
+        keys = _normalize(queries[:nq], device_id=local) if metric == "cosine" else queries[:nq]
+        gp = ix.find_partitions(keys, nprobes)
+        line["parity"] = parity_block(ref, (h_od.numpy(), h_oi.numpy().view(np.uint64), h_oc.numpy()), k, gpu_probes=gp)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

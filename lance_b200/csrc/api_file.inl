@@ -104,6 +104,10 @@ static int pb_tensor(const uint8_t* b, size_t n, std::vector<float>& out, uint64
   }
   if (!r.ok || !ok) return set_err(LB200_EINVAL, "malformed tensor in index metadata");
   if (shp.size() != 2) return set_err(LB200_EINVAL, "only accept 2-D tensor shape, got %zu dims", shp.size());
+  // shape comes from the file: checked multiplication, and the element count must fit the payload
+  if (shp[1] != 0 && shp[0] > (uint64_t)plen / shp[1])
+    return set_err(LB200_EINVAL, "Tensor shape [%llu, %llu] does not match to data len: %zu",
+                   (unsigned long long)shp[0], (unsigned long long)shp[1], plen);
   const uint64_t cnt = shp[0] * shp[1];
   if (dt == 2) {  // FLOAT32
     if (plen != cnt * 4) return set_err(LB200_EINVAL, "Tensor shape [%llu, %llu] does not match to data len: %zu",
@@ -132,10 +136,11 @@ static int parse_legacy_index(const uint8_t* blob, size_t size, lb200_index_file
   memcpy(&minor, blob + size - 6, 2);
   if (!(major == 0 && (minor == 1 || minor == 0)))
     return set_err(LB200_EUNSUPPORTED, "index file version %u.%u is not the legacy IVF_PQ layout", major, minor);
-  if (pos + 4 > size - 16) return set_err(LB200_EINVAL, "file size is too small");
+  // `pos` comes from the file: compare without additions that can wrap (pos near 2^64)
+  if (size < 20 || pos > size - 20) return set_err(LB200_EINVAL, "file size is too small");
   uint32_t mlen;
   memcpy(&mlen, blob + pos, 4);
-  if (pos + 4 + (uint64_t)mlen > size - 16) return set_err(LB200_EINVAL, "index metadata runs past the end of the file");
+  if ((uint64_t)mlen > size - 20 - pos) return set_err(LB200_EINVAL, "index metadata runs past the end of the file");
 
   // ---- pb::Index ----
   PbReader r(blob + pos + 4, mlen);
@@ -239,7 +244,18 @@ static int parse_legacy_index(const uint8_t* blob, size_t size, lb200_index_file
   // ---- partition pages: PQIndex::load of every partition, codes transposed to [M][n_p] ----
   const uint32_t M = f->M;
   f->part_offsets.assign(f->nlist + 1, 0);
-  for (uint32_t p = 0; p < f->nlist; p++) f->part_offsets[p + 1] = f->part_offsets[p] + lengths[p];
+  // every size below comes from the file: validate each page against the (validated) metadata position and
+  // the running total against the file size BEFORE anything is allocated from them
+  const uint64_t max_rows = pos / (M + 8ull);
+  for (uint32_t p = 0; p < f->nlist; p++) {
+    const uint64_t o = offsets[p], n = lengths[p];
+    if (o > pos || n > (pos - o) / (M + 8ull))
+      return set_err(LB200_EINVAL, "partition %u page at %llu (%llu rows) overlaps the metadata at %llu", p,
+                     (unsigned long long)o, (unsigned long long)n, (unsigned long long)pos);
+    if (n > max_rows - f->part_offsets[p])
+      return set_err(LB200_EINVAL, "IVF stage: partition lengths add up to more rows than the file can hold");
+    f->part_offsets[p + 1] = f->part_offsets[p] + n;
+  }
   const uint64_t N = f->part_offsets[f->nlist];
   f->codes.resize((size_t)N * M);
   f->row_ids.resize((size_t)N);
@@ -248,9 +264,6 @@ static int parse_legacy_index(const uint8_t* blob, size_t size, lb200_index_file
   for (uint32_t p = 0; p < f->nlist; p++) {
     const uint64_t o = offsets[p], n = lengths[p];
     f->lengths[p] = (uint32_t)n;
-    if (o > pos || n > (pos - o) / (M + 8ull))
-      return set_err(LB200_EINVAL, "partition %u page at %llu (%llu rows) overlaps the metadata at %llu", p,
-                     (unsigned long long)o, (unsigned long long)n, (unsigned long long)pos);
     const uint8_t* page = blob + o;
     uint8_t* dst = f->codes.data() + (size_t)f->part_offsets[p] * M;
     for (uint64_t i = 0; i < n; i++)
@@ -266,9 +279,19 @@ extern "C" int32_t lb200_index_file_open_bytes(const void* bytes, uint64_t size,
   if (!out) return set_err(LB200_EINVAL, "null output");
   *out = nullptr;
   if (!bytes && size) return set_err(LB200_EINVAL, "null argument");
-  lb200_index_file* f = new lb200_index_file();
-  int rc = parse_legacy_index((const uint8_t*)bytes, (size_t)size, f);
-  if (rc) { delete f; return rc; }
+  // no C++ exception may cross the C ABI (the host is Rust): allocation failures become error codes
+  lb200_index_file* f = nullptr;
+  try {
+    f = new lb200_index_file();
+    int rc = parse_legacy_index((const uint8_t*)bytes, (size_t)size, f);
+    if (rc) { delete f; return rc; }
+  } catch (const std::bad_alloc&) {
+    delete f;
+    return set_err(LB200_ENOMEM, "out of host memory while parsing the index file");
+  } catch (...) {
+    delete f;
+    return set_err(LB200_EINVAL, "malformed index file");
+  }
   *out = f;
   return 0;
 }
@@ -277,13 +300,19 @@ extern "C" int32_t lb200_index_file_open(const char* path, lb200_index_file** ou
   if (!out) return set_err(LB200_EINVAL, "null output");
   *out = nullptr;
   if (!path) return set_err(LB200_EINVAL, "null path");
-  std::ifstream in(path, std::ios::binary | std::ios::ate);
-  if (!in) return set_err(LB200_EINVAL, "cannot open index file %s", path);
-  const std::streamsize n = in.tellg();
-  std::vector<uint8_t> buf((size_t)std::max<std::streamsize>(n, 0));
-  in.seekg(0);
-  if (n > 0 && !in.read((char*)buf.data(), n)) return set_err(LB200_EINVAL, "cannot read index file %s", path);
-  return lb200_index_file_open_bytes(buf.data(), buf.size(), out);
+  try {
+    std::ifstream in(path, std::ios::binary | std::ios::ate);
+    if (!in) return set_err(LB200_EINVAL, "cannot open index file %s", path);
+    const std::streamsize n = in.tellg();
+    std::vector<uint8_t> buf((size_t)std::max<std::streamsize>(n, 0));
+    in.seekg(0);
+    if (n > 0 && !in.read((char*)buf.data(), n)) return set_err(LB200_EINVAL, "cannot read index file %s", path);
+    return lb200_index_file_open_bytes(buf.data(), buf.size(), out);
+  } catch (const std::bad_alloc&) {
+    return set_err(LB200_ENOMEM, "out of host memory while reading %s", path);
+  } catch (...) {
+    return set_err(LB200_EINVAL, "cannot read index file %s", path);
+  }
 }
 
 extern "C" int32_t lb200_index_file_get_info(const lb200_index_file* f, lb200_index_file_info* info) {

@@ -19,12 +19,19 @@ int main(int argc, char** argv) {
   std::mt19937_64 rng(11); int ok = 0, bad = 0;
   for (int it = 0; it < 20000; it++) {
     std::vector<uint8_t> b = good;
-    int mode = it % 4;
+    int mode = it % 6;
     uint64_t pos; memcpy(&pos, good.data() + good.size() - 16, 8);
     if (mode == 0) { size_t cut = rng() % good.size(); b.resize(cut); b.insert(b.end(), good.end() - 16, good.end()); }
     else if (mode == 1) { for (int k = 0; k < 1 + (int)(rng() % 4); k++) b[pos + rng() % (good.size() - pos)] = (uint8_t)rng(); }
     else if (mode == 2) { b[good.size() - 16 + rng() % 12] = (uint8_t)rng(); }
-    else { size_t cut = rng() % good.size(); b.resize(cut); }
+    else if (mode == 3) { size_t cut = rng() % good.size(); b.resize(cut); }
+    else if (mode == 4) {  // crafted footer positions (pos + 4 wrapped for pos >= 2^64-4)
+      const uint64_t sz = good.size();
+      const uint64_t cand[] = {~0ull, ~0ull - 3, ~0ull - 19, sz - 16, sz - 19, sz - 20, sz, 1ull << 63, rng()};
+      uint64_t p2 = cand[rng() % 9]; memcpy(b.data() + sz - 16, &p2, 8); }
+    else {  // saturate a run of metadata bytes: varints (lengths, offsets, tensor shapes) become huge
+      size_t at = pos + rng() % (good.size() - 16 - pos), n = 1 + rng() % 9;
+      for (size_t k = 0; k < n && at + k < good.size() - 16; k++) b[at + k] = k + 1 == n ? 0x3f : 0xff; }
     // exact-size heap copy so ASan sees any overread
     uint8_t* heap = (uint8_t*)malloc(b.size() ? b.size() : 1); memcpy(heap, b.data(), b.size());
     lb200_index_file* f = nullptr;

@@ -592,3 +592,37 @@ def test_many_probes_large_k_two_level_merge(oracle):
         gd, gi, gc = ix.search(Query(key=q, k=k, nprobes=64, refine_factor=refine or None))
         _assert_same(gd, gi, gc, rd[:, :gd.shape[1]], ri[:, :gd.shape[1]], rc, f"two-level merge k={k} refine={refine}")
     ix.close()
+
+
+# ---- cfg 3 / cfg 5 SHAPES above toy size: M = 96 / 48, the real partition counts, >= 100k rows,
+# so the QL = 2 / 16-warp / table pre-pass instantiations are checked on the shapes they are benchmarked on ------------
+@pytest.mark.parametrize("name,N,d,nlist,M,metric,nprobes,refine,Q", [
+    ("cfg3-shape", 120_000, 1536, 1024, 96, "cosine", 102, 5, 96),
+    ("cfg5-shape", 400_000, 768, 2048, 48, "dot", 32, 0, 160),
+    ("cfg4-shape-many-probes", 600_000, 128, 4096, 16, "l2", 32, 0, 300),
+])
+def test_baseline_config_shapes_bit_identical(oracle, name, N, d, nlist, M, metric, nprobes, refine, Q):
+    from lance_b200 import IvfPqIndex, Query
+    data = random_index(N, d, nlist, M, metric, seed=31, keep_raw=refine > 0)
+    if metric == "cosine":                     # a cosine index holds L2 structures over normalised data
+        data.centroids /= np.linalg.norm(data.centroids, axis=1, keepdims=True)
+        data.codebook *= np.float32(0.02 / 16.0)
+    q = queries_near_centroids(data, Q, seed=32, scale=0.05 if metric == "cosine" else None)
+    ix = IvfPqIndex(data)
+    gd, gi, gc = ix.search(Query(key=q, k=10, nprobes=nprobes, refine_factor=refine or None))
+    st = ix.stats()
+    assert st["scan_variant"] == 3 and st["scan_ql"] == (4 if M <= 48 else 2)
+    o = oracle.OracleIndex(data)
+    rd, ri, rc, rp = o.search(q, k=10, nprobes=nprobes, refine_factor=refine)
+    _assert_same(gd, gi, gc, rd[:, :10], ri[:, :10], np.minimum(rc, 10), name)
+    keys = np.stack([oracle.normalize(x) for x in q]) if metric == "cosine" else q
+    assert ix.find_partitions(keys, nprobes).tolist() == rp.tolist(), f"{name}: probed partitions differ"
+    # the same pairs through search_in_partition (per-pair lists, no shared bound): first 8 queries
+    od, oi, oc = ix.search_in_partition(rp[:8], keys[:8], 10)
+    for qi in range(8):
+        for j in range(rp.shape[1]):
+            pd, pr = o.search_in_partition(int(rp[qi, j]), keys[qi], 10)
+            n = len(pd)
+            assert oc[qi, j] == n and oi[qi, j, :n].tolist() == pr.tolist()
+            assert _bits(od[qi, j, :n]).tolist() == _bits(pd).tolist()
+    ix.close()

@@ -278,3 +278,38 @@ def test_native_reader_survives_truncations_and_tail_edits():
         except LanceB200Error:
             pass
     assert ok < 300
+
+
+def test_native_reader_crafted_footer_and_sizes():
+    """sizes taken from the file must be validated without wrapping additions and BEFORE they size an
+    allocation.  Footer positions near 2^64 / at the tail, partition lengths and tensor shapes of 2^62: every one must
+    come back as an error code (no out-of-bounds read, no std::bad_alloc crossing the C ABI)."""
+    from lance_b200 import LanceB200Error
+    from lance_b200.reader import open_legacy_ivf_pq_native
+    data = _synthetic("l2")
+    good = write_legacy(data)
+    size = len(good)
+    for pos in (2**64 - 1, 2**64 - 4, 2**64 - 20, size - 16, size - 19, size - 20, size, 2**63):
+        blob = good[:-16] + struct.pack("<QHH", pos, 0, 1) + b"LANC"
+        with pytest.raises(LanceB200Error):
+            open_legacy_ivf_pq_native(blob)
+
+    def with_ivf(lengths, offsets=None, cshape=None):
+        offs = offsets if offsets is not None else [0] * len(lengths)
+        ivf = _ld(2, b"".join(_vi(o) for o in offs)) + _ld(3, b"".join(_vi(n) for n in lengths))
+        ct = _tensor(data.centroids)
+        if cshape is not None:
+            ct = _vf(1, 2) + _ld(2, b"".join(_vi(x) for x in cshape)) + _ld(3, b"")
+        ivf += _ld(4, ct)
+        pq = _vf(1, 8) + _vf(2, data.M) + _vf(3, data.dim) + _ld(5, _tensor(data.codebook.reshape(-1, data.dim // data.M)))
+        vec = _vf(1, 1) + _vf(2, data.dim) + _ld(3, _ld(2, ivf)) + _ld(3, _ld(3, pq)) + _vf(4, 0)
+        msg = _ld(1, b"i") + _ld(2, b"vector") + _vf(3, 7) + _vf(4, 0) + _ld(5, vec)
+        body = b"\0" * 4096
+        return body + struct.pack("<I", len(msg)) + msg + struct.pack("<QHH", len(body), 0, 1) + b"LANC"
+
+    bad = [with_ivf([2**62] * 5), with_ivf([2**63, 2**63, 1, 1, 1]), with_ivf([100] * 5),   # sum exceeds the pages
+           with_ivf([1] * 5, offsets=[2**64 - 8] * 5),
+           with_ivf([1] * 5, cshape=[2**62, 4]), with_ivf([1] * 5, cshape=[2**32, 2**32]), with_ivf([1] * 5, cshape=[2**63, 2])]
+    for blob in bad:
+        with pytest.raises(LanceB200Error):
+            open_legacy_ivf_pq_native(blob)
