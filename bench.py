@@ -321,6 +321,120 @@ def run_flat(args):
     print(json.dumps(line), flush=True)
 
 
+class _DropinBackend(__import__("ctypes").Structure):
+    import ctypes as _C
+    _fields_ = [("kind", _C.c_int32), ("handle", _C.c_void_p), ("fn_find", _C.c_void_p), ("fn_search", _C.c_void_p),
+                ("metric", _C.c_int32), ("dim", _C.c_uint32), ("nlist", _C.c_uint32), ("centroids", _C.c_void_p)]
+
+
+def _dropin_lib():
+    import ctypes as C
+    path = os.path.join(ROOT, "examples", "libdropin_host.so")
+    if not os.path.exists(path):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "examples")])
+    lib = C.CDLL(path)
+    lib.dropin_run.restype = C.c_int
+    return lib
+
+
+def _dropin_call(lib, be, queries, nprobes, k, threads, clients):
+    import ctypes as C
+    Q = queries.shape[0]
+    od = np.full((Q, k), np.inf, dtype=np.float32)
+    oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+    oc = np.zeros(Q, dtype=np.uint32)
+    lat = np.zeros(Q, dtype=np.float64)
+    wall = C.c_double(0)
+    q = np.ascontiguousarray(queries, dtype=np.float32)
+    rc = lib.dropin_run(C.byref(be), q.ctypes.data_as(C.c_void_p), C.c_uint32(Q), C.c_uint32(nprobes), C.c_uint32(k),
+                        C.c_int(threads), C.c_int(clients), od.ctypes.data_as(C.c_void_p), oi.ctypes.data_as(C.c_void_p),
+                        oc.ctypes.data_as(C.c_void_p), lat.ctypes.data_as(C.c_void_p), C.byref(wall))
+    if rc:
+        from lance_b200 import _lib
+        raise RuntimeError(f"dropin_run failed: {rc}: {_lib.lib().lb200_last_error().decode()}")
+    return od, oi, oc, lat, wall.value
+
+
+def run_dropin(args, wl):
+    """--mode dropin: the call pattern of the reference's exec nodes (knn.rs:349-393,606-634) through the C ABI:
+    per query ONE lb200_find_partitions(Q=1), then nprobes x lb200_search_partitions(Q=1,P=1) with T host threads in
+    flight, then a host-side merge -- driven by examples/dropin_host.cpp -- and the CPU oracle port driven the SAME
+    way beside it (the "reference-shaped" baseline of SURVEY 8(d): partitions of one query fanned out over
+    T = nproc - 2 threads, lance-core/src/utils/tokio.rs:12-31)."""
+    import ctypes as C
+    import torch
+    import oracle
+    from lance_b200 import IvfPqIndex, Query, _lib
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    N, d, nlist, M, metric, nprobes, k, refine, Q, desc = wl
+    seed = 77
+    data, sizes, _ = make_shard(wl, seed, 0, 1, keep_raw=False)
+    queries = make_queries(wl, data.centroids, seed)
+    ix = IvfPqIndex(data, device_id=0)
+    L = _lib.lib()
+    lib = _dropin_lib()
+    nproc = os.cpu_count() or 1
+    T = max(1, nproc - 2)                                   # get_num_compute_intensive_cpus()
+    mcode = {"l2": 0, "cosine": 1, "dot": 2}[metric]
+    gbe = _DropinBackend(0, ix._h, C.cast(L.lb200_find_partitions, C.c_void_p), C.cast(L.lb200_search_partitions, C.c_void_p),
+                         mcode, d, nlist, None)
+    nq = min(Q, args.queries or 2000)
+    kq = k * max(refine, 1)
+    _dropin_call(lib, gbe, queries[:64], nprobes, kq, T, 1)                     # warm-up (contexts, buffers)
+    sampler = ClockSampler(0)
+    sampler.start()
+    gd, gi, gc, glat, gwall = _dropin_call(lib, gbe, queries[:nq], nprobes, kq, T, 1)
+    clocks = sampler.stop()
+    st = ix.stats()
+    per_call_launches = st["kernel_launches"]
+    # several queries in flight (concurrent users of one index handle)
+    clients = min(8, T)
+    _, _, _, _, gwall_c = _dropin_call(lib, gbe, queries[:nq], nprobes, kq, T, clients)
+    # the batched entry point with Q = 1 beside it (host buffers, blocking)
+    one = np.empty(min(nq, 500))
+    for i in range(-20, len(one)):
+        t0 = time.perf_counter()
+        ix.search(Query(key=queries[max(i, 0)], k=k, nprobes=nprobes, refine_factor=None))
+        if i >= 0:
+            one[i] = (time.perf_counter() - t0) * 1e3
+    # the CPU oracle port driven the same way, bounded sample
+    o = oracle.OracleIndex(data)
+    olib = oracle.lib()
+    obe = _DropinBackend(1, C.addressof(o.ix), C.cast(olib.lo_find_partitions, C.c_void_p),
+                         C.cast(olib.lo_search_in_partition, C.c_void_p), mcode, d, nlist,
+                         data.centroids.ctypes.data_as(C.c_void_p))
+    _, _, _, l0, w0 = _dropin_call(lib, obe, queries[:8], nprobes, kq, T, 1)
+    ncpu = int(max(16, min(nq, 12.0 / max(w0 / 8, 1e-6))))
+    cd, ci, cc, clat, cwall = _dropin_call(lib, obe, queries[:ncpu], nprobes, kq, T, 1)
+    par = parity_block((cd, ci, cc, None), (gd, gi, gc), kq)
+    par["checker"] = "oracle port driven through the same drop-in host (examples/dropin_host.cpp), same queries"
+    pct = lambda a, p: float(np.percentile(a, p))
+    line = {
+        "metric": "IVF_PQ queries/sec (drop-in call pattern: find_partitions + nprobes x search_in_partition)",
+        "mode": "dropin", "value": nq / gwall, "unit": "queries/s", "n_gpus": 1, "steps": 1, "warmup": 1,
+        "ms_per_step": gwall * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": desc, "queries": nq, "k": k, "nprobes": nprobes, "threads_in_flight": T,
+                   "host": "examples/dropin_host.cpp (std::thread pool; mirrors knn.rs:349-393,606-634)",
+                   "calls_per_query": 1 + nprobes},
+        "latency_ms": {"p50": pct(glat, 50), "p99": pct(glat, 99), "mean": float(glat.mean()),
+                       "lb200_search_Q1_p50": pct(one, 50), "lb200_search_Q1_p99": pct(one, 99),
+                       "ratio_p50_vs_lb200_search_Q1": pct(glat, 50) / pct(one, 50)},
+        "concurrent_clients": {"clients": clients, "value": nq / gwall_c, "unit": "queries/s"},
+        "e2e": {"value": nq / gwall, "unit": "queries/s", "h2d_bytes_per_step": int(nq * (1 + nprobes) * d * 4),
+                "d2h_bytes_per_step": int(nq * (nprobes * 4 + nprobes * (kq * 12 + 4))),
+                "path": "lb200_find_partitions(Q=1) + nprobes x lb200_search_partitions(Q=1,P=1), host buffers"},
+        "gpu_launches": int(nq * (2 + nprobes * per_call_launches)),
+        "cpu_baseline": {"value": ncpu / cwall, "unit": "queries/s", "cores": T, "kind": "port",
+                         "sample": f"first {ncpu} queries, {cwall:.1f} s; reference-shaped: one query at a time, its "
+                                   f"{nprobes} partitions fanned out over {T} threads (nproc {nproc} - 2)",
+                         "latency_ms": {"p50": pct(clat, 50), "p99": pct(clat, 99)}},
+        "parity": par, "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    ix.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -328,6 +442,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=os.environ.get("LB200_WORKLOAD", "cfg4"), choices=sorted(WORKLOADS) + ["cfg2"])
+    ap.add_argument("--mode", default="batch", choices=["batch", "dropin"],
+                    help="dropin: the exec nodes' call pattern (per query find_partitions + nprobes x search_in_partition)")
     ap.add_argument("--scan-variant", type=int, default=0)
     ap.add_argument("--queries", type=int, default=0,
                     help="override the workload's queries per step (batch-size sweep of BASELINE configs[4])")
@@ -348,6 +464,12 @@ def main():
     if args.queries:
         wl = wl[:8] + (args.queries, wl[9].replace("%d queries" % wl[8], "%d queries" % args.queries)
                        .replace("10k queries", "%d queries" % args.queries))
+    if args.mode == "dropin":
+        if args.impl == "reference" or _BITS != 8:
+            print(json.dumps({"impl": args.impl, "unavailable": "--mode dropin runs both arms itself (8-bit IVF_PQ only)"}))
+            return
+        run_dropin(args, wl)
+        return
     if args.impl == "reference":
         if _BITS == 32:
             print(json.dumps({"impl": "reference", "unavailable": "cfg1_flat has no oracle arm: use --workload cfg4 (headline)"}))

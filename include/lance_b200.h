@@ -10,7 +10,11 @@
  *  - return 0 = OK, negative = error (LB200_E*); message via lb200_last_error() (thread-local).
  *  - pointers are HOST memory unless the function name ends in `_device`.
  *  - nothing is retained after return except what lb200_index_create copies to the GPU.
- *  - a handle may be used from several host threads; calls serialise on the handle.
+ *  - a handle may be used from several host threads at once: every call leases one of the handle's call
+ *    contexts (stream + scratch; LB200_CTX_POOL of them, default 16), so concurrent calls overlap on the
+ *    GPU -- the exec nodes keep up to get_num_compute_intensive_cpus() search_in_partition calls in flight
+ *    per query (rust/lance/src/io/exec/knn.rs:606-634).  GPU work of consecutive users of a context is
+ *    ordered by an event, also for the asynchronous *_device entry points on caller streams.
  *  - there is NO CPU fallback: without a usable CUDA device every call fails with
  *    LB200_ECUDA.
  *
@@ -119,6 +123,19 @@ int32_t lb200_search_partitions(lb200_index* ix, const float* queries, uint32_t 
                                 const float* lower_or_null, const float* upper_or_null,
                                 const uint64_t* const* part_bitmask_or_null, float* out_dist,
                                 uint64_t* out_rowid, uint32_t* out_count);
+
+/* A PreFilter evaluated once (DatasetPreFilter::wait_for_ready, rust/lance/src/index/prefilter.rs:227-290)
+ * and shared by all search_in_partition calls of a query, as the Arc<dyn PreFilter> the exec node passes
+ * to every partition (knn.rs:621): the per-partition bitmasks are uploaded once and stay on the device.
+ * part_bitmask: [nlist] host pointers as for lb200_search_partitions (NULL entry = all rows allowed). */
+typedef struct lb200_prefilter lb200_prefilter;
+int32_t lb200_prefilter_create(lb200_index* ix, const uint64_t* const* part_bitmask, lb200_prefilter** out);
+void lb200_prefilter_destroy(lb200_prefilter* pf);
+int32_t lb200_search_partitions_filtered(lb200_index* ix, const float* queries, uint32_t Q,
+                                         const uint32_t* part_ids, uint32_t P, uint32_t k_prime,
+                                         const float* lower_or_null, const float* upper_or_null,
+                                         const lb200_prefilter* prefilter_or_null, float* out_dist,
+                                         uint64_t* out_rowid, uint32_t* out_count);
 
 /* VectorIndex::search (vector.rs:133; ivf/v2.rs:368-401): normalise (cosine) ->
  * find_partitions -> search_in_partition per probe -> merge to k' = k*max(refine_factor,1).

@@ -18,6 +18,7 @@ EXPORTS = [
     "lb200_merge_topk", "lb200_rerank",
     "lb200_index_file_open", "lb200_index_file_open_bytes", "lb200_index_file_get_info", "lb200_index_file_close",
     "lb200_index_open", "lb200_flat_distance_f16", "lb200_flat_topk_f16", "lb200_normalize",
+    "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
 ]
 
 
@@ -49,6 +50,7 @@ def lib():
         _lib.lb200_last_error.restype = C.c_char_p
         _lib.lb200_version.restype = C.c_char_p
         _lib.lb200_index_destroy.restype = None
+        _lib.lb200_prefilter_destroy.restype = None
         for name in EXPORTS:
             if os.environ.get("LB200_SO") and not hasattr(_lib, name):
                 continue  # an older build under A/B test may predate a symbol

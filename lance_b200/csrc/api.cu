@@ -11,6 +11,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <condition_variable>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -81,6 +82,42 @@ struct Arena {
   static size_t pad(size_t b) { return (b + 255) & ~(size_t)255; }
 };
 
+// Per-call context: stream, device scratch, host<->device staging (device side + pinned host side) and
+// events.  A handle owns a small pool of them so that concurrent calls -- the reference fires up to
+// get_num_compute_intensive_cpus() search_in_partition calls per query (rust/lance/src/io/exec/knn.rs:606-634)
+// -- run side by side on their own streams instead of serialising on one arena.  Grow-only: no allocation
+// in steady state.
+struct CallCtx {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;  // recorded after the last GPU work that touches arena / stage
+  cudaEvent_t ev[6] = {};      // profiling
+  Arena arena;                 // pipeline scratch
+  Arena stage;                 // device side of the host-pointer entry points
+  char* h_pin = nullptr;       // pinned host side
+  size_t h_pin_cap = 0;
+  bool busy = false;
+  std::vector<uint32_t> h_work;  // host-built work list of small calls
+  int pin_reserve(size_t bytes) {
+    if (bytes <= h_pin_cap) return 0;
+    if (h_pin) cudaFreeHost(h_pin);
+    h_pin = nullptr;
+    h_pin_cap = 0;
+    const size_t want = std::max<size_t>(bytes + (bytes >> 2), 64 * 1024);
+    cudaError_t e = cudaHostAlloc((void**)&h_pin, want, cudaHostAllocDefault);
+    if (e != cudaSuccess) return set_err(LB200_ENOMEM, "cudaHostAlloc(%zu) failed: %s", want, cudaGetErrorString(e));
+    h_pin_cap = want;
+    return 0;
+  }
+};
+
+// Device-resident prefilter (lb200_prefilter_create): the per-partition row bitmasks of one RowIdMask,
+// uploaded once and shared by every search_in_partition call of a query (Arc<dyn PreFilter>).
+struct lb200_prefilter {
+  lb200_index* ix = nullptr;
+  char* base = nullptr;            // [nlist] device pointers, then the mask words
+  const uint64_t** d_ptrs = nullptr;
+};
+
 constexpr uint32_t LB200_MAX_PEERS = 15;
 struct lb200_index {
   int device = 0, metric = 0;
@@ -98,17 +135,17 @@ struct lb200_index {
   uint64_t* d_sb_off = nullptr;        // [nlist+1] first superblock per partition
   uint32_t skew_L = 0, skew_D = 0;     // superblock = 32*skew_L rows; lane delay period
   std::vector<uint64_t> h_part_off;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev[6] = {};
-  std::mutex mu, stage_mu;
+  cudaStream_t stream = nullptr;  // create-time uploads and the peer-table set-up
+  std::mutex mu;                  // guards stats, pthr_* and the admin calls (never held across a search)
+  std::vector<CallCtx*> ctxs;     // pool of per-call contexts (LB200_CTX_POOL, default 16)
+  std::mutex pool_mu;
+  std::condition_variable pool_cv;
+  uint32_t max_ctx = 16;
   bool profiling = false;
   int force_variant = 0;
   lb200_stats stats = {};
   int sm_count = 148;
   size_t smem_optin = 0, smem_per_sm = 0;
-  Arena arena;
-  Arena stage;  // host<->device staging of lb200_search (queries in, results out)
-  const uint64_t** d_bitmask_ptrs = nullptr;  // scratch for prefilter pointers
   // shared pruning bounds between shards (lb200_peer_thresholds_*): two tables of pthr_cap keys
   // (batch parity), the peers' addresses of both, and which of them were opened through CUDA IPC
   uint32_t* pthr_local = nullptr;
@@ -116,6 +153,60 @@ struct lb200_index {
   uint64_t pthr_epoch = 0;
   uint32_t** d_pthr_tbl = nullptr;  // device [2][LB200_MAX_PEERS]
   void* pthr_ipc[LB200_MAX_PEERS] = {};
+};
+
+// Lease of one CallCtx for the duration of a call.  `user` = the caller's stream for the *_device entry
+// points (the work is only enqueued; `done` orders the next user of the context behind it), or null for
+// the context's own stream.
+struct CtxLease {
+  lb200_index* ix = nullptr;
+  CallCtx* cx = nullptr;
+  cudaStream_t st = nullptr;
+  int acquire(lb200_index* ix_, cudaStream_t user) {
+    ix = ix_;
+    cudaError_t e = cudaSetDevice(ix->device);
+    if (e != cudaSuccess) return set_err(LB200_ECUDA, "cudaSetDevice(%d) failed: %s", ix->device, cudaGetErrorString(e));
+    {
+      std::unique_lock<std::mutex> lk(ix->pool_mu);
+      for (;;) {
+        for (CallCtx* c : ix->ctxs)
+          if (!c->busy) { cx = c; break; }
+        if (cx) break;
+        if (ix->ctxs.size() < ix->max_ctx) {
+          CallCtx* c = new CallCtx();
+          cudaError_t e1 = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+          if (e1 == cudaSuccess) e1 = cudaEventCreateWithFlags(&c->done, cudaEventDisableTiming);
+          for (auto& ev : c->ev)
+            if (e1 == cudaSuccess) e1 = cudaEventCreate(&ev);
+          if (e1 != cudaSuccess) {
+            if (c->stream) cudaStreamDestroy(c->stream);
+            if (c->done) cudaEventDestroy(c->done);
+            for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+            delete c;
+            return set_err(LB200_ECUDA, "cannot create a call context: %s", cudaGetErrorString(e1));
+          }
+          ix->ctxs.push_back(c);
+          cx = c;
+          break;
+        }
+        ix->pool_cv.wait(lk);
+      }
+      cx->busy = true;
+    }
+    st = user ? user : cx->stream;
+    e = cudaStreamWaitEvent(st, cx->done, 0);  // earlier work on this context's scratch (maybe on another stream)
+    if (e != cudaSuccess) return set_err(LB200_ECUDA, "cudaStreamWaitEvent failed: %s", cudaGetErrorString(e));
+    return 0;
+  }
+  ~CtxLease() {
+    if (!cx) return;
+    cudaEventRecord(cx->done, st);
+    {
+      std::lock_guard<std::mutex> lk(ix->pool_mu);
+      cx->busy = false;
+    }
+    ix->pool_cv.notify_one();
+  }
 };
 
 static int select_device(int device_id) {
@@ -206,7 +297,7 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   ix->smem_optin = prop.sharedMemPerBlockOptin;
   ix->smem_per_sm = prop.sharedMemPerMultiprocessor;
   CKF(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
-  for (auto& e : ix->ev) CKF(cudaEventCreate(&e));
+  if (const char* e = getenv("LB200_CTX_POOL")) ix->max_ctx = (uint32_t)std::min(64, std::max(1, atoi(e)));
   size_t cent_b = (size_t)nlist * dim * 4, cb_b = (size_t)M * 256 * ix->dsub * 4;
   CKF(cudaMalloc(&ix->d_centroids, cent_b));
   CKF(cudaMalloc(&ix->d_codebook, cb_b));
@@ -304,14 +395,21 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_tail4);
   cudaFree(ix->d_pad_off);
   cudaFree(ix->d_sb_off);
-  cudaFree(ix->arena.base);
-  cudaFree(ix->stage.base);
-  cudaFree((void*)ix->d_bitmask_ptrs);
+  for (CallCtx* c : ix->ctxs) {
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    cudaFree(c->arena.base);
+    cudaFree(c->stage.base);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
+    if (c->done) cudaEventDestroy(c->done);
+    for (auto& e : c->ev)
+      if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+  }
+  ix->ctxs.clear();
   lb200_peer_thresholds_detach(ix);
   cudaFree(ix->pthr_local);
   cudaFree(ix->d_pthr_tbl);
-  for (auto& e : ix->ev)
-    if (e) cudaEventDestroy(e);
   if (ix->stream) cudaStreamDestroy(ix->stream);
   delete ix;
 }
@@ -412,6 +510,7 @@ extern "C" int32_t lb200_set_profiling(lb200_index* ix, int32_t enabled) {
 }
 extern "C" int32_t lb200_get_stats(const lb200_index* ix, lb200_stats* out) {
   if (!ix || !out) return set_err(LB200_EINVAL, "null argument");
+  std::lock_guard<std::mutex> lk(const_cast<lb200_index*>(ix)->mu);
   *out = ix->stats;
   return 0;
 }

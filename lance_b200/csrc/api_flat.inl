@@ -62,6 +62,13 @@ static int flat_topk_device_impl(int metric, uint32_t dim, const float* d_q, uin
   if (k == 0) return set_err(LB200_EINVAL, "k must be > 0");
   if (k > 1024) return set_err(LB200_EUNSUPPORTED, "k=%u > 1024", k);
   if (!Q) return 0;
+  if (n == 0) {  // an empty batch: empty result (the reference returns an empty RecordBatch), not a scratch request
+    fill_u32_kernel<<<(uint32_t)(((size_t)Q * k + 255) / 256), 256, 0, st>>>(reinterpret_cast<uint32_t*>(d_od), 0x7f800000u, (size_t)Q * k);
+    CK(cudaMemsetAsync(d_oi, 0xff, (size_t)Q * k * 8, st));
+    CK(cudaMemsetAsync(d_oc, 0, (size_t)Q * 4, st));
+    CK(cudaGetLastError());
+    return 0;
+  }
   uint32_t tile = (uint32_t)std::max<uint64_t>(FLAT_TQ, std::min<uint64_t>(Q, (128ull << 20) / std::max<uint64_t>(1, n * 4)));
   tile = (tile + FLAT_TQ - 1) / FLAT_TQ * FLAT_TQ;
   size_t stride = (size_t)std::max<uint64_t>(n, 1);

@@ -4,7 +4,7 @@
 
 namespace {
 
-static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st) {
+static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cudaStream_t st) {
   const uint32_t Q = a.Q, dim = ix->dim, nlist = ix->nlist, M = ix->M;
   const uint32_t P = a.d_part_ids ? a.P : std::min(a.nprobes, nlist);
   const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);
@@ -37,29 +37,29 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   add(npairs * kprime * 4); add(npairs * kprime * 8); add(npairs * kprime * 8); add(npairs * kprime * 8); add(npairs * 4);
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
   add((size_t)Q * kprime * 4);
-  int rc = ix->arena.reserve(need);
+  int rc = cx.arena.reserve(need);
   if (rc) return rc;
-  ix->arena.reset();
-  float* d_keys = ix->arena.take<float>((size_t)Q * dim);
-  float* d_D = ix->arena.take<float>((size_t)Q * nlist);
-  uint32_t* d_probes = ix->arena.take<uint32_t>(npairs);
-  unsigned long long* d_stats = ix->arena.take<unsigned long long>(8);
-  float* d_dist = ix->arena.take<float>(fused ? 64 : tpairs * stride);
-  float* d_sdist = ix->arena.take<float>(npairs * kprime);
-  uint64_t* d_sidx = ix->arena.take<uint64_t>(npairs * kprime);
-  uint64_t* d_srow = ix->arena.take<uint64_t>(npairs * kprime);
-  uint64_t* d_spos = ix->arena.take<uint64_t>(npairs * kprime);
-  uint32_t* d_scnt = ix->arena.take<uint32_t>(npairs);
-  float* d_mdist = ix->arena.take<float>((size_t)Q * kprime);
-  uint64_t* d_mrow = ix->arena.take<uint64_t>((size_t)Q * kprime);
-  uint64_t* d_mpos = ix->arena.take<uint64_t>((size_t)Q * kprime);
-  uint32_t* d_mcnt = ix->arena.take<uint32_t>(Q);
-  float* d_exact = ix->arena.take<float>((size_t)Q * kprime);
+  cx.arena.reset();
+  float* d_keys = cx.arena.take<float>((size_t)Q * dim);
+  float* d_D = cx.arena.take<float>((size_t)Q * nlist);
+  uint32_t* d_probes = cx.arena.take<uint32_t>(npairs);
+  unsigned long long* d_stats = cx.arena.take<unsigned long long>(8);
+  float* d_dist = cx.arena.take<float>(fused ? 64 : tpairs * stride);
+  float* d_sdist = cx.arena.take<float>(npairs * kprime);
+  uint64_t* d_sidx = cx.arena.take<uint64_t>(npairs * kprime);
+  uint64_t* d_srow = cx.arena.take<uint64_t>(npairs * kprime);
+  uint64_t* d_spos = cx.arena.take<uint64_t>(npairs * kprime);
+  uint32_t* d_scnt = cx.arena.take<uint32_t>(npairs);
+  float* d_mdist = cx.arena.take<float>((size_t)Q * kprime);
+  uint64_t* d_mrow = cx.arena.take<uint64_t>((size_t)Q * kprime);
+  uint64_t* d_mpos = cx.arena.take<uint64_t>((size_t)Q * kprime);
+  uint32_t* d_mcnt = cx.arena.take<uint32_t>(Q);
+  float* d_exact = cx.arena.take<float>((size_t)Q * kprime);
 
   uint32_t launches = 0;
   lb200_stats stats = {};
   const bool prof = ix->profiling;
-  if (prof) CK(cudaEventRecord(ix->ev[0], st));
+  if (prof) CK(cudaEventRecord(cx.ev[0], st));
   const float* keys = a.d_queries;
   if (a.normalize && ix->metric == LB200_COSINE) {
     normalize_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(a.d_queries, d_keys, Q, dim);
@@ -73,7 +73,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     if (rc) return rc;
     probes = d_probes;
   }
-  if (prof) CK(cudaEventRecord(ix->ev[1], st));
+  if (prof) CK(cudaEventRecord(cx.ev[1], st));
   CK(cudaMemsetAsync(d_stats, 0, 32, st));
   const size_t smem = ((size_t)dim + (size_t)M * 16 + M) * 4 + (size_t)M * 16;
   if (smem > 48 * 1024) CK(cudaFuncSetAttribute(scan4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -81,7 +81,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   float* pd = a.per_pair_output ? a.d_out_dist : d_sdist;
   uint32_t* pc = a.per_pair_output ? a.d_out_count : d_scnt;
   uint64_t* prow = a.per_pair_output ? a.d_out_rowid : d_srow;
-  if (prof) CK(cudaEventRecord(ix->ev[2], st));
+  if (prof) CK(cudaEventRecord(cx.ev[2], st));
   if (fused) {
     if (fsmem > 48 * 1024) CK(cudaFuncSetAttribute(scan4f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     scan4f_kernel<<<(uint32_t)npairs, 256, fsmem, st>>>(ix->metric, keys, probes, P, dim, M, ix->d_centroids,
@@ -117,7 +117,7 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     CK(cudaGetLastError());
     launches += 2;
   }
-  if (prof) CK(cudaEventRecord(ix->ev[3], st));
+  if (prof) CK(cudaEventRecord(cx.ev[3], st));
   if (!fused) {
     gather4_kernel<<<(uint32_t)((npairs * kprime + 255) / 256), 256, 0, st>>>(
         probes, ix->d_part_off, ix->d_row_ids, d_sidx, pc, npairs, kprime, prow, a.per_pair_output ? nullptr : d_spos);
@@ -143,12 +143,12 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
     }
   }
   if (prof) {
-    CK(cudaEventRecord(ix->ev[4], st));
+    CK(cudaEventRecord(cx.ev[4], st));
     CK(cudaStreamSynchronize(st));
     float ms = 0;
-    CK(cudaEventElapsedTime(&ms, ix->ev[0], ix->ev[1])); stats.coarse_ms = ms;
-    CK(cudaEventElapsedTime(&ms, ix->ev[2], ix->ev[3])); stats.scan_ms = ms;
-    CK(cudaEventElapsedTime(&ms, ix->ev[0], ix->ev[4])); stats.total_ms = ms;
+    CK(cudaEventElapsedTime(&ms, cx.ev[0], cx.ev[1])); stats.coarse_ms = ms;
+    CK(cudaEventElapsedTime(&ms, cx.ev[2], cx.ev[3])); stats.scan_ms = ms;
+    CK(cudaEventElapsedTime(&ms, cx.ev[0], cx.ev[4])); stats.total_ms = ms;
     unsigned long long hs[2];
     CK(cudaMemcpy(hs, d_stats, 16, cudaMemcpyDeviceToHost));
     stats.scan_code_bytes = hs[0];
@@ -159,7 +159,10 @@ static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t s
   stats.scan_variant = flat ? 32 : 4;
   stats.scan_items = (uint32_t)npairs;
   stats.scan_ql = 1;
-  ix->stats = stats;
+  {
+    std::lock_guard<std::mutex> lk(ix->mu);
+    ix->stats = stats;
+  }
   return 0;
 }
 
@@ -229,7 +232,6 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   ix->smem_optin = prop.sharedMemPerBlockOptin;
   ix->smem_per_sm = prop.sharedMemPerMultiprocessor;
   CK4(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
-  for (auto& e : ix->ev) CK4(cudaEventCreate(&e));
   const size_t cent_b = (size_t)nlist * dim * 4, cb_b = (size_t)M * 16 * ix->dsub * 4;
   CK4(cudaMalloc(&ix->d_centroids, cent_b));
   CK4(cudaMalloc(&ix->d_codebook, cb_b));
@@ -308,7 +310,6 @@ int create_index_flat(int32_t device_id, int32_t metric, uint32_t dim, uint32_t 
   ix->smem_optin = prop.sharedMemPerBlockOptin;
   ix->smem_per_sm = prop.sharedMemPerMultiprocessor;
   CKX(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
-  for (auto& e : ix->ev) CKX(cudaEventCreate(&e));
   CKX(cudaMalloc(&ix->d_centroids, (size_t)nlist * dim * 4));
   CKX(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
   CKX(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));

@@ -80,6 +80,24 @@ struct SearchArgs {
   uint64_t* d_out_rowid;
   uint32_t* d_out_count;
   float* d_out_exact;          // shard mode only
+  const struct PrebuiltWork* pw = nullptr;  // work list built on the host (small search_partitions calls)
+};
+
+// Scan plan of one call: kernel configuration and how partitions are cut into chunks.
+struct ScanPlan {
+  ScanConfig sc;
+  uint32_t chunk_vecs, max_chunks;
+};
+
+// Work list of a small call, built on the host and already uploaded: search_in_partition calls of the
+// drop-in path carry one (query, partition) pair each, and the four work-list kernels + three memsets of
+// the batched path would be most of their latency.
+struct PrebuiltWork {
+  ScanPlan plan;
+  const uint32_t *d_pair_list, *d_pair_off, *d_item_off;
+  uint32_t* d_counter;  // zeroed
+  uint64_t code_bytes, pairs;
+  uint32_t items;
 };
 
 // find_partitions on device: distances [Q][nlist] + per-query sort.  Output [Q][P].
@@ -175,25 +193,13 @@ static int launch_merge2(const float* in_dist, const uint64_t* in_rowid, const u
                       stride, stride, out_dist, out_rowid, out_pos, nullptr, out_cnt, st);
 }
 
-// The whole device pipeline for one batch of queries; asynchronous on `st`.
-static int search4_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st);  // api_pq4.inl
-static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st) {
-  if (ix->bits != 8) return search4_pipeline(ix, a, st);  // 4-bit PQ, IVF_FLAT
-  const uint32_t Q = a.Q, dim = ix->dim, nlist = ix->nlist;
-  const uint32_t P = a.d_part_ids ? a.P : std::min(a.nprobes, nlist);
-  const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);
-  if (a.k == 0) return set_err(LB200_EINVAL, "k must be > 0");       // scanner.rs:642 validation
-  if (kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", kprime);
-  if (P == 0 || Q == 0) return 0;
-  const bool refine = a.refine_factor > 0 && ix->d_raw != nullptr && !a.per_pair_output;
-  if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output && !a.shard_mode)
-    return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
-  uint32_t launches = 0;
-  lb200_stats stats = {};
-
+// Kernel choice and chunking for a batch of Q queries x P partitions.
+static int plan_scan(const lb200_index* ix, uint32_t Q, uint32_t P, uint32_t kprime, ScanPlan* out) {
+  const uint32_t nlist = ix->nlist;
+  int rc;
   ScanConfig sc;
   double avg_q = (double)Q * P / std::max(1u, nlist);
-  int rc = choose_scan(ix, kprime, avg_q, &sc);
+  rc = choose_scan(ix, kprime, avg_q, &sc);
   if (rc) return rc;
   // chunking: enough work items to fill the SMs even for tiny batches
   uint64_t est_items = std::max<uint64_t>(1, (uint64_t)Q * P / sc.ql);
@@ -220,6 +226,36 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     chunk_vecs = (chunk_vecs + sbr - 1) / sbr * sbr;
   }
   const uint32_t max_chunks = (uint32_t)std::max<uint64_t>(1, (ix->max_part + chunk_vecs - 1) / chunk_vecs);
+
+  out->sc = sc;
+  out->chunk_vecs = chunk_vecs;
+  out->max_chunks = max_chunks;
+  return 0;
+}
+
+// The whole device pipeline for one batch of queries; asynchronous on `st`.
+static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cudaStream_t st);  // api_pq4.inl
+static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cudaStream_t st) {
+  if (ix->bits != 8) return search4_pipeline(ix, cx, a, st);  // 4-bit PQ, IVF_FLAT
+  const uint32_t Q = a.Q, dim = ix->dim, nlist = ix->nlist;
+  const uint32_t P = a.d_part_ids ? a.P : std::min(a.nprobes, nlist);
+  const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);
+  if (a.k == 0) return set_err(LB200_EINVAL, "k must be > 0");       // scanner.rs:642 validation
+  if (kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", kprime);
+  if (P == 0 || Q == 0) return 0;
+  const bool refine = a.refine_factor > 0 && ix->d_raw != nullptr && !a.per_pair_output;
+  // (a shard that owns no rows has no raw vectors and nothing to refine; any other handle must hold them)
+  if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output && !(a.shard_mode && ix->N == 0))
+    return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
+  uint32_t launches = 0;
+  lb200_stats stats = {};
+  int rc;
+
+  ScanPlan plan;
+  if (a.pw) plan = a.pw->plan;
+  else if ((rc = plan_scan(ix, Q, P, kprime, &plan))) return rc;
+  ScanConfig sc = plan.sc;
+  const uint32_t chunk_vecs = plan.chunk_vecs, max_chunks = plan.max_chunks;
 
   // ---- workspace -----------------------------------------------------------------------
   const size_t npairs = (size_t)Q * P, nslots = npairs * max_chunks;
@@ -266,40 +302,40 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
       sc.smem = smem16;
     }
   }
-  rc = ix->arena.reserve(need);
+  rc = cx.arena.reserve(need);
   if (rc) return rc;
-  ix->arena.reset();
-  float* d_keys = ix->arena.take<float>((size_t)Q * dim);
-  float* d_D = ix->arena.take<float>((size_t)Q * nlist);
-  uint32_t* d_probes = ix->arena.take<uint32_t>(npairs);
-  uint32_t* d_cnt = ix->arena.take<uint32_t>((size_t)nlist * 2);
+  cx.arena.reset();
+  float* d_keys = cx.arena.take<float>((size_t)Q * dim);
+  float* d_D = cx.arena.take<float>((size_t)Q * nlist);
+  uint32_t* d_probes = cx.arena.take<uint32_t>(npairs);
+  uint32_t* d_cnt = cx.arena.take<uint32_t>((size_t)nlist * 2);
   uint32_t* d_cnt2 = d_cnt + nlist;
-  uint32_t* d_minp = ix->arena.take<uint32_t>(Q);
-  uint32_t* d_rank = ix->arena.take<uint32_t>(npairs);
-  uint32_t* d_pair_off = ix->arena.take<uint32_t>(nlist + 1);
-  uint32_t* d_item_off = ix->arena.take<uint32_t>(nlist + 1);
-  uint32_t* d_pair_list = ix->arena.take<uint32_t>(npairs);
-  unsigned long long* d_stats = ix->arena.take<unsigned long long>(4);
+  uint32_t* d_minp = cx.arena.take<uint32_t>(Q);
+  uint32_t* d_rank = cx.arena.take<uint32_t>(npairs);
+  uint32_t* d_pair_off = cx.arena.take<uint32_t>(nlist + 1);
+  uint32_t* d_item_off = cx.arena.take<uint32_t>(nlist + 1);
+  uint32_t* d_pair_list = cx.arena.take<uint32_t>(npairs);
+  unsigned long long* d_stats = cx.arena.take<unsigned long long>(4);
   uint32_t* d_counter = reinterpret_cast<uint32_t*>(d_stats + 2);
-  float* d_sdist = ix->arena.take<float>(nslots * kprime);
-  uint64_t* d_spos = ix->arena.take<uint64_t>(nslots * kprime);
-  uint64_t* d_srow = ix->arena.take<uint64_t>(nslots * kprime);
-  uint32_t* d_scnt = ix->arena.take<uint32_t>(nslots);
-  float* d_mdist = ix->arena.take<float>((size_t)Q * kprime);
-  uint64_t* d_mrow = ix->arena.take<uint64_t>((size_t)Q * kprime);
-  uint64_t* d_mpos = ix->arena.take<uint64_t>((size_t)Q * kprime);
-  uint32_t* d_mcnt = ix->arena.take<uint32_t>(Q);
-  float* d_exact = ix->arena.take<float>((size_t)Q * kprime);
-  uint32_t* d_qthr = ix->arena.take<uint32_t>(Q);
-  float* t_mdist = mslice ? ix->arena.take<float>((size_t)Q * mslices * kprime) : nullptr;
-  uint64_t* t_mrow = mslice ? ix->arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
-  uint64_t* t_mpos = mslice ? ix->arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
-  uint32_t* t_mcnt = mslice ? ix->arena.take<uint32_t>((size_t)Q * mslices) : nullptr;
-  float* d_lut = use_pre ? ix->arena.take<float>(pre_units * ix->M * 256) : nullptr;
-  uint32_t* d_lut_max = use_pre ? ix->arena.take<uint32_t>(pre_units) : nullptr;
+  float* d_sdist = cx.arena.take<float>(nslots * kprime);
+  uint64_t* d_spos = cx.arena.take<uint64_t>(nslots * kprime);
+  uint64_t* d_srow = cx.arena.take<uint64_t>(nslots * kprime);
+  uint32_t* d_scnt = cx.arena.take<uint32_t>(nslots);
+  float* d_mdist = cx.arena.take<float>((size_t)Q * kprime);
+  uint64_t* d_mrow = cx.arena.take<uint64_t>((size_t)Q * kprime);
+  uint64_t* d_mpos = cx.arena.take<uint64_t>((size_t)Q * kprime);
+  uint32_t* d_mcnt = cx.arena.take<uint32_t>(Q);
+  float* d_exact = cx.arena.take<float>((size_t)Q * kprime);
+  uint32_t* d_qthr = cx.arena.take<uint32_t>(Q);
+  float* t_mdist = mslice ? cx.arena.take<float>((size_t)Q * mslices * kprime) : nullptr;
+  uint64_t* t_mrow = mslice ? cx.arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
+  uint64_t* t_mpos = mslice ? cx.arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
+  uint32_t* t_mcnt = mslice ? cx.arena.take<uint32_t>((size_t)Q * mslices) : nullptr;
+  float* d_lut = use_pre ? cx.arena.take<float>(pre_units * ix->M * 256) : nullptr;
+  uint32_t* d_lut_max = use_pre ? cx.arena.take<uint32_t>(pre_units) : nullptr;
 
   const bool prof = ix->profiling;
-  if (prof) CK(cudaEventRecord(ix->ev[0], st));
+  if (prof) CK(cudaEventRecord(cx.ev[0], st));
 
   // ---- A1 normalise (VectorIndex::search on a cosine index, ivf/v2.rs:370-373) ----------
   const float* keys = a.d_queries;
@@ -316,11 +352,19 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     if (rc) return rc;
     probes = d_probes;
   }
-  if (prof) CK(cudaEventRecord(ix->ev[1], st));
+  if (prof) CK(cudaEventRecord(cx.ev[1], st));
   // ---- work list ------------------------------------------------------------------------
+  CK(cudaMemsetAsync(d_scnt, 0, nslots * 4, st));
+  const uint32_t* total_items_p = d_item_off + nlist;
+  if (a.pw) {  // built on the host and uploaded with the queries (small search_partitions calls)
+    d_pair_list = const_cast<uint32_t*>(a.pw->d_pair_list);
+    d_pair_off = const_cast<uint32_t*>(a.pw->d_pair_off);
+    d_item_off = const_cast<uint32_t*>(a.pw->d_item_off);
+    d_counter = a.pw->d_counter;
+    total_items_p = d_item_off + nlist;
+  } else {
   CK(cudaMemsetAsync(d_cnt, 0, (size_t)nlist * 4 * 2, st));
   CK(cudaMemsetAsync(d_stats, 0, 32, st));
-  CK(cudaMemsetAsync(d_scnt, 0, nslots * 4, st));
   if (getenv("LB200_NO_COLDPACK"))
     CK(cudaMemsetAsync(d_minp, 0xff, (size_t)Q * 4, st));
   else
@@ -333,6 +377,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
                                                                         (uint32_t)npairs, d_pair_list);
   CK(cudaGetLastError());
   launches += 4;
+  }
   // ---- A3-A6 scan -----------------------------------------------------------------------
   if (sc.variant == 3) {
     Scan3Params sp = {};
@@ -356,6 +401,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     if (sp.qthr && a.shard_mode && ix->pthr_peers && Q <= ix->pthr_cap && !getenv("LB200_NO_PEER_THR")) {
       // bounds shared with the peer shards: this batch uses table (epoch & 1) -- reset one batch ago, peers
       // may already have published into it -- and clears the other one for the next batch
+      std::lock_guard<std::mutex> lk(ix->mu);
       const uint32_t par = (uint32_t)(ix->pthr_epoch & 1);
       sp.qthr = ix->pthr_local + (size_t)par * ix->pthr_cap;
       sp.peers = ix->d_pthr_tbl + (size_t)par * LB200_MAX_PEERS;
@@ -369,7 +415,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
       CK(cudaGetLastError());
       launches++;
     }
-    if (prof) CK(cudaEventRecord(ix->ev[2], st));
+    if (prof) CK(cudaEventRecord(cx.ev[2], st));
     if (use_pre) {  // inside the scan's timed span: the tables are part of the scan's cost
       CK(cudaMemsetAsync(d_lut_max, 0, pre_units * 4, st));
       dim3 g((ix->M / 16) * LUTPRE_SPLIT, (uint32_t)((pre_units + LUTPRE_UNITS - 1) / LUTPRE_UNITS));
@@ -393,7 +439,7 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     // pre-built tables are fetched by scan3_kernel only (scan3_nb_kernel stays the untouched text the
     // headline was tuned on); without `boot` its bootstrap calls are switched off at run time
     if (!boot) sp.no_boot = 1;
-    CK(launch_scan3(sc, boot || use_pre, ix->sm_count, st, sp, d_item_off + nlist));
+    CK(launch_scan3(sc, boot || use_pre, ix->sm_count, st, sp, total_items_p));
     launches++;
   } else {
   ScanParams sp = {};
@@ -407,11 +453,11 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   sp.lower = a.lower; sp.upper = a.upper; sp.has_lower = a.has_lower; sp.has_upper = a.has_upper;
   sp.bitmask = a.d_bitmask;
   sp.out_dist = d_sdist; sp.out_pos = d_spos; sp.out_rowid = d_srow; sp.out_count = d_scnt;
-  if (prof) CK(cudaEventRecord(ix->ev[2], st));
-  CK(launch_scan(sc, ix->sm_count, st, sp, d_item_off + nlist));
+  if (prof) CK(cudaEventRecord(cx.ev[2], st));
+  CK(launch_scan(sc, ix->sm_count, st, sp, total_items_p));
   launches++;
   }
-  if (prof) CK(cudaEventRecord(ix->ev[3], st));
+  if (prof) CK(cudaEventRecord(cx.ev[3], st));
   // ---- A7 merge ---------------------------------------------------------------------------
   if (a.per_pair_output) {
     // search_in_partition semantics: one list per (query, partition); merge only the chunks
@@ -459,16 +505,20 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
     }
   }
   if (prof) {
-    CK(cudaEventRecord(ix->ev[4], st));
+    CK(cudaEventRecord(cx.ev[4], st));
     CK(cudaStreamSynchronize(st));
     float ms = 0;
-    CK(cudaEventElapsedTime(&ms, ix->ev[0], ix->ev[1])); stats.coarse_ms = ms;
-    CK(cudaEventElapsedTime(&ms, ix->ev[2], ix->ev[3])); stats.scan_ms = ms;
-    CK(cudaEventElapsedTime(&ms, ix->ev[0], ix->ev[4])); stats.total_ms = ms;
+    CK(cudaEventElapsedTime(&ms, cx.ev[0], cx.ev[1])); stats.coarse_ms = ms;
+    CK(cudaEventElapsedTime(&ms, cx.ev[2], cx.ev[3])); stats.scan_ms = ms;
+    CK(cudaEventElapsedTime(&ms, cx.ev[0], cx.ev[4])); stats.total_ms = ms;
     unsigned long long hs[2];
     uint32_t items = 0;
-    CK(cudaMemcpy(hs, d_stats, 16, cudaMemcpyDeviceToHost));
-    CK(cudaMemcpy(&items, d_item_off + nlist, 4, cudaMemcpyDeviceToHost));
+    if (a.pw) {
+      hs[0] = a.pw->code_bytes; hs[1] = a.pw->pairs; items = a.pw->items;
+    } else {
+      CK(cudaMemcpy(hs, d_stats, 16, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(&items, d_item_off + nlist, 4, cudaMemcpyDeviceToHost));
+    }
     stats.scan_code_bytes = hs[0];
     stats.pairs = hs[1];
     stats.scan_items = items;
@@ -476,7 +526,10 @@ static int search_pipeline(lb200_index* ix, const SearchArgs& a, cudaStream_t st
   stats.kernel_launches = launches;
   stats.scan_variant = sc.variant;
   stats.scan_ql = sc.ql;
-  ix->stats = stats;
+  {
+    std::lock_guard<std::mutex> lk(ix->mu);
+    ix->stats = stats;
+  }
   return 0;
 }
 
@@ -488,43 +541,264 @@ static int check_queries(const lb200_index* ix, const void* q, uint32_t Q) {
 
 }  // namespace
 
+namespace {
+// One-shot device scratch of the handle-less host-pointer entry points (merge_topk, rerank, flat, f16).
+struct HostStage {
+  void* p = nullptr;
+  ~HostStage() { if (p) cudaFree(p); }
+};
+}  // namespace
+
+// Host<->device staging of the host-pointer entry points.  Small payloads go through the context's pinned
+// buffer (one async copy, no driver-side staging of pageable memory); large ones are copied straight from /
+// to the caller's memory (pinned by the caller in the benchmarks).
+constexpr size_t LB200_PIN_BYTES = 256 * 1024;
+
 extern "C" int32_t lb200_find_partitions(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes,
                                          uint32_t* out_part_ids, float* out_part_dists_or_null) {
   int rc = check_queries(ix, queries, Q);
   if (rc) return rc;
   if (!out_part_ids) return set_err(LB200_EINVAL, "null output");
-  std::lock_guard<std::mutex> lk(ix->mu);
-  CK(cudaSetDevice(ix->device));
   const uint32_t P = std::min(nprobes, ix->nlist);
   if (!Q || !P) return 0;
-  size_t need = Arena::pad((size_t)Q * ix->dim * 4) + Arena::pad((size_t)Q * ix->nlist * 4) +
-                Arena::pad((size_t)Q * P * 4) * 2 + 2048;
-  rc = ix->arena.reserve(need);
-  if (rc) return rc;
-  ix->arena.reset();
-  float* d_q = ix->arena.take<float>((size_t)Q * ix->dim);
-  float* d_D = ix->arena.take<float>((size_t)Q * ix->nlist);
-  uint32_t* d_p = ix->arena.take<uint32_t>((size_t)Q * P);
-  float* d_pd = ix->arena.take<float>((size_t)Q * P);
-  cudaStream_t st = ix->stream;
-  CK(cudaMemcpyAsync(d_q, queries, (size_t)Q * ix->dim * 4, cudaMemcpyHostToDevice, st));
+  CtxLease ls;
+  if ((rc = ls.acquire(ix, nullptr))) return rc;
+  CallCtx& cx = *ls.cx;
+  cudaStream_t st = ls.st;
+  const size_t nq = (size_t)Q * ix->dim * 4, np = (size_t)Q * P * 4;
+  size_t need = Arena::pad(nq) + Arena::pad((size_t)Q * ix->nlist * 4) + Arena::pad(np) * 2 + 2048;
+  if ((rc = cx.arena.reserve(need))) return rc;
+  cx.arena.reset();
+  float* d_q = cx.arena.take<float>((size_t)Q * ix->dim);
+  float* d_D = cx.arena.take<float>((size_t)Q * ix->nlist);
+  uint32_t* d_p = cx.arena.take<uint32_t>((size_t)Q * P);   // d_p and d_pd are adjacent (pad(np) apart)
+  float* d_pd = cx.arena.take<float>((size_t)Q * P);
+  const bool pin = nq + 2 * Arena::pad(np) <= LB200_PIN_BYTES;
+  if (pin) {
+    if ((rc = cx.pin_reserve(nq + 2 * Arena::pad(np)))) return rc;
+    memcpy(cx.h_pin, queries, nq);
+    CK(cudaMemcpyAsync(d_q, cx.h_pin, nq, cudaMemcpyHostToDevice, st));
+  } else {
+    CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
+  }
   uint32_t launches = 0;
   rc = coarse_device(ix, d_q, Q, P, d_D, d_p, d_pd, st, &launches);
   if (rc) return rc;
-  CK(cudaMemcpyAsync(out_part_ids, d_p, (size_t)Q * P * 4, cudaMemcpyDeviceToHost, st));
-  if (out_part_dists_or_null)
-    CK(cudaMemcpyAsync(out_part_dists_or_null, d_pd, (size_t)Q * P * 4, cudaMemcpyDeviceToHost, st));
+  if (pin) {
+    const size_t span = out_part_dists_or_null ? Arena::pad(np) + np : np;
+    CK(cudaMemcpyAsync(cx.h_pin, d_p, span, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    memcpy(out_part_ids, cx.h_pin, np);
+    if (out_part_dists_or_null) memcpy(out_part_dists_or_null, cx.h_pin + Arena::pad(np), np);
+    return 0;
+  }
+  CK(cudaMemcpyAsync(out_part_ids, d_p, np, cudaMemcpyDeviceToHost, st));
+  if (out_part_dists_or_null) CK(cudaMemcpyAsync(out_part_dists_or_null, d_pd, np, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return 0;
 }
 
+// ---- prefilter objects ----------------------------------------------------------------------------
+extern "C" int32_t lb200_prefilter_create(lb200_index* ix, const uint64_t* const* part_bitmask, lb200_prefilter** out) {
+  if (!out) return set_err(LB200_EINVAL, "null output");
+  *out = nullptr;
+  if (!ix || !part_bitmask) return set_err(LB200_EINVAL, "null argument");
+  if (ix->bits != 8) return set_err(LB200_EUNSUPPORTED, "prefilter bitmasks are supported on 8-bit PQ handles only");
+  CK(cudaSetDevice(ix->device));
+  const uint32_t nlist = ix->nlist;
+  size_t words = 0;
+  for (uint32_t p = 0; p < nlist; p++)
+    if (part_bitmask[p]) words += (size_t)((ix->h_part_off[p + 1] - ix->h_part_off[p] + 63) / 64) + 1;
+  const size_t tbl = Arena::pad((size_t)nlist * 8), total = tbl + words * 8;
+  std::vector<uint64_t> h;
+  try {
+    h.assign(total / 8, 0);
+  } catch (...) {
+    return set_err(LB200_ENOMEM, "out of host memory for %zu prefilter words", words);
+  }
+  lb200_prefilter* pf = new lb200_prefilter();
+  pf->ix = ix;
+  cudaError_t e = cudaMalloc((void**)&pf->base, std::max<size_t>(total, 8));
+  if (e != cudaSuccess) {
+    delete pf;
+    return set_err(LB200_ENOMEM, "cudaMalloc(%zu) failed: %s", total, cudaGetErrorString(e));
+  }
+  size_t w = tbl / 8;
+  for (uint32_t p = 0; p < nlist; p++) {
+    if (!part_bitmask[p]) continue;
+    const size_t nw = (size_t)((ix->h_part_off[p + 1] - ix->h_part_off[p] + 63) / 64);
+    h[p] = (uint64_t)(uintptr_t)(pf->base + w * 8);
+    memcpy(h.data() + w, part_bitmask[p], nw * 8);  // + one zero word: the scan may test one row past a ragged end
+    w += nw + 1;
+  }
+  e = cudaMemcpy(pf->base, h.data(), total, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    cudaFree(pf->base);
+    delete pf;
+    return set_err(LB200_ECUDA, "prefilter upload failed: %s", cudaGetErrorString(e));
+  }
+  pf->d_ptrs = reinterpret_cast<const uint64_t**>(pf->base);
+  *out = pf;
+  return 0;
+}
+
+extern "C" void lb200_prefilter_destroy(lb200_prefilter* pf) {
+  if (!pf) return;
+  if (pf->ix) cudaSetDevice(pf->ix->device);
+  cudaFree(pf->base);
+  delete pf;
+}
+
 namespace {
-// Host-pointer front end shared by lb200_search and lb200_search_partitions: stages inputs in
-// device scratch (separate from the pipeline arena), runs the pipeline, copies results back.
-struct HostStage {
-  void* p = nullptr;
-  ~HostStage() { if (p) cudaFree(p); }
-};
+
+// search_in_partition for explicit pairs; masks either as host pointers (uploaded with this call, only the
+// partitions the call probes) or as a device-resident lb200_prefilter.
+static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_t Q, const uint32_t* part_ids, uint32_t P,
+                                  uint32_t k_prime, const float* lower_or_null, const float* upper_or_null,
+                                  const uint64_t* const* host_masks, const lb200_prefilter* pf, float* out_dist,
+                                  uint64_t* out_rowid, uint32_t* out_count) {
+  int rc = check_queries(ix, queries, Q);
+  if (rc) return rc;
+  if (Q && P && (!part_ids || !out_dist || !out_rowid || !out_count)) return set_err(LB200_EINVAL, "null argument");
+  if (k_prime == 0) return set_err(LB200_EINVAL, "k must be > 0");
+  if (k_prime > 512) return set_err(LB200_EUNSUPPORTED, "k=%u > 512", k_prime);
+  if (!Q || !P) return 0;
+  if (pf && pf->ix != ix) return set_err(LB200_EINVAL, "prefilter belongs to another index handle");
+  const uint32_t nlist = ix->nlist;
+  const size_t npairs = (size_t)Q * P;
+  if (npairs >= (1ull << 31)) return set_err(LB200_EUNSUPPORTED, "Q*P too large");
+  for (size_t i = 0; i < npairs; i++)
+    if (part_ids[i] >= nlist)  // ivf/v2.rs:288-293 "partition centroid {} does not exist"
+      return set_err(LB200_EINVAL, "partition centroid %u does not exist", part_ids[i]);
+  if ((host_masks || pf) && ix->bits != 8)
+    return set_err(LB200_EUNSUPPORTED, "prefilter bitmasks are supported on 8-bit PQ handles only");
+  CtxLease ls;
+  if ((rc = ls.acquire(ix, nullptr))) return rc;
+  CallCtx& cx = *ls.cx;
+  cudaStream_t st = ls.st;
+
+  // ---- plan; small calls get their work list from the host ----
+  ScanPlan plan = {};
+  bool small = ix->bits == 8 && npairs <= 2048 && !getenv("LB200_NO_HOST_WORKLIST");
+  if (ix->bits == 8) {
+    if ((rc = plan_scan(ix, Q, P, k_prime, &plan))) return rc;
+    small = small && plan.sc.variant == 3;
+  }
+  // ---- staging layout (device `stage` mirrors the pinned host buffer byte for byte on the way in) ----
+  const size_t nq = (size_t)Q * ix->dim * 4, np = npairs * 4, no = npairs * k_prime;
+  size_t in_bytes = 0;
+  auto put = [&](size_t b) { size_t o = in_bytes; in_bytes += Arena::pad(b); return o; };
+  const size_t o_q = put(nq), o_p = put(np);
+  size_t o_pl = 0, o_po = 0, o_io = 0, o_ctr = 0, o_tbl = 0, o_masks = 0, mask_words = 0;
+  if (small) { o_pl = put(np); o_po = put((size_t)(nlist + 1) * 4); o_io = put((size_t)(nlist + 1) * 4); o_ctr = put(16); }
+  std::vector<uint32_t> mparts;  // probed partitions that carry a host mask
+  if (host_masks) {
+    for (size_t i = 0; i < npairs; i++)
+      if (host_masks[part_ids[i]]) mparts.push_back(part_ids[i]);
+    std::sort(mparts.begin(), mparts.end());
+    mparts.erase(std::unique(mparts.begin(), mparts.end()), mparts.end());
+    for (uint32_t p : mparts) mask_words += (size_t)((ix->h_part_off[p + 1] - ix->h_part_off[p] + 63) / 64) + 1;
+    o_tbl = put((size_t)nlist * 8);
+    o_masks = put(mask_words * 8);
+  }
+  const size_t o_od = in_bytes, o_or = o_od + Arena::pad(no * 4), o_oc = o_or + Arena::pad(no * 8);
+  const size_t out_bytes = o_oc + Arena::pad(np) - o_od;
+  if ((rc = cx.stage.reserve(in_bytes + out_bytes))) return rc;
+  char* dbase = cx.stage.base;
+  const bool pin_in = in_bytes <= 4 * LB200_PIN_BYTES, pin_out = out_bytes <= LB200_PIN_BYTES;
+  if ((rc = cx.pin_reserve((pin_in ? in_bytes : 0) + (pin_out ? out_bytes : 0)))) return rc;
+  char* hin = cx.h_pin;
+  char* hout = cx.h_pin + (pin_in ? in_bytes : 0);
+  std::vector<char> pageable;
+  if (!pin_in) {  // large call: build the small tables in a pageable buffer, copy queries straight from the caller
+    pageable.resize(in_bytes - Arena::pad(nq));
+    hin = pageable.data() - Arena::pad(nq);
+  }
+  if (pin_in) memcpy(hin + o_q, queries, nq);
+  memcpy(hin + o_p, part_ids, np);
+
+  PrebuiltWork pw = {};
+  if (small) {
+    uint32_t* pl = reinterpret_cast<uint32_t*>(hin + o_pl);
+    uint32_t* po = reinterpret_cast<uint32_t*>(hin + o_po);
+    uint32_t* io = reinterpret_cast<uint32_t*>(hin + o_io);
+    memset(po, 0, (size_t)(nlist + 1) * 4);
+    for (size_t i = 0; i < npairs; i++) po[part_ids[i]]++;
+    uint32_t pacc = 0, iacc = 0;
+    uint64_t bytes = 0;
+    const uint32_t ql = (uint32_t)plan.sc.ql;
+    for (uint32_t p = 0; p < nlist; p++) {  // == offsets_kernel
+      const uint32_t c = po[p];
+      const uint64_t n = ix->h_part_off[p + 1] - ix->h_part_off[p];
+      po[p] = pacc;
+      io[p] = iacc;
+      if (c) {
+        pacc += c;
+        iacc += ((c + ql - 1) / ql) * (uint32_t)((n + plan.chunk_vecs - 1) / plan.chunk_vecs);
+        bytes += (uint64_t)c * n * ix->M;
+      }
+    }
+    po[nlist] = pacc;
+    io[nlist] = iacc;
+    cx.h_work.assign(nlist, 0);  // fill position per partition
+    for (size_t i = 0; i < npairs; i++) pl[po[part_ids[i]] + cx.h_work[part_ids[i]]++] = (uint32_t)i;  // == scatter_pairs_kernel
+    memset(hin + o_ctr, 0, 16);
+    pw.plan = plan;
+    pw.d_pair_list = reinterpret_cast<uint32_t*>(dbase + o_pl);
+    pw.d_pair_off = reinterpret_cast<uint32_t*>(dbase + o_po);
+    pw.d_item_off = reinterpret_cast<uint32_t*>(dbase + o_io);
+    pw.d_counter = reinterpret_cast<uint32_t*>(dbase + o_ctr);
+    pw.code_bytes = bytes;
+    pw.pairs = pacc;
+    pw.items = iacc;
+  }
+  if (host_masks) {
+    uint64_t* tbl = reinterpret_cast<uint64_t*>(hin + o_tbl);
+    uint64_t* mw = reinterpret_cast<uint64_t*>(hin + o_masks);
+    memset(tbl, 0, (size_t)nlist * 8);
+    size_t w = 0;
+    for (uint32_t p : mparts) {
+      const size_t nw = (size_t)((ix->h_part_off[p + 1] - ix->h_part_off[p] + 63) / 64);
+      tbl[p] = (uint64_t)(uintptr_t)(dbase + o_masks + w * 8);
+      memcpy(mw + w, host_masks[p], nw * 8);
+      mw[w + nw] = 0;
+      w += nw + 1;
+    }
+  }
+  if (pin_in) {
+    CK(cudaMemcpyAsync(dbase, hin, in_bytes, cudaMemcpyHostToDevice, st));
+  } else {
+    CK(cudaMemcpyAsync(dbase + o_q, queries, nq, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(dbase + o_p, hin + o_p, in_bytes - Arena::pad(nq), cudaMemcpyHostToDevice, st));
+  }
+  SearchArgs a = {};
+  a.d_queries = reinterpret_cast<const float*>(dbase + o_q); a.Q = Q;
+  a.d_part_ids = reinterpret_cast<const uint32_t*>(dbase + o_p); a.P = P; a.k = k_prime; a.refine_factor = 0;
+  a.normalize = false; a.per_pair_output = true;
+  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
+  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
+  a.d_bitmask = host_masks ? reinterpret_cast<const uint64_t* const*>(dbase + o_tbl) : pf ? pf->d_ptrs : nullptr;
+  a.d_out_dist = reinterpret_cast<float*>(dbase + o_od);
+  a.d_out_rowid = reinterpret_cast<uint64_t*>(dbase + o_or);
+  a.d_out_count = reinterpret_cast<uint32_t*>(dbase + o_oc);
+  a.pw = small ? &pw : nullptr;
+  rc = search_pipeline(ix, cx, a, st);
+  if (rc) return rc;
+  if (pin_out) {
+    CK(cudaMemcpyAsync(hout, dbase + o_od, out_bytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    memcpy(out_dist, hout, no * 4);
+    memcpy(out_rowid, hout + (o_or - o_od), no * 8);
+    memcpy(out_count, hout + (o_oc - o_od), np);
+    return 0;
+  }
+  CK(cudaMemcpyAsync(out_dist, dbase + o_od, no * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_rowid, dbase + o_or, no * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_count, dbase + o_oc, np, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
 }  // namespace
 
 extern "C" int32_t lb200_search_partitions(lb200_index* ix, const float* queries, uint32_t Q,
@@ -532,65 +806,41 @@ extern "C" int32_t lb200_search_partitions(lb200_index* ix, const float* queries
                                            const float* lower_or_null, const float* upper_or_null,
                                            const uint64_t* const* part_bitmask_or_null, float* out_dist,
                                            uint64_t* out_rowid, uint32_t* out_count) {
-  int rc = check_queries(ix, queries, Q);
+  return search_partitions_impl(ix, queries, Q, part_ids, P, k_prime, lower_or_null, upper_or_null,
+                                part_bitmask_or_null, nullptr, out_dist, out_rowid, out_count);
+}
+
+extern "C" int32_t lb200_search_partitions_filtered(lb200_index* ix, const float* queries, uint32_t Q,
+                                                    const uint32_t* part_ids, uint32_t P, uint32_t k_prime,
+                                                    const float* lower_or_null, const float* upper_or_null,
+                                                    const lb200_prefilter* prefilter_or_null, float* out_dist,
+                                                    uint64_t* out_rowid, uint32_t* out_count) {
+  return search_partitions_impl(ix, queries, Q, part_ids, P, k_prime, lower_or_null, upper_or_null, nullptr,
+                                prefilter_or_null, out_dist, out_rowid, out_count);
+}
+
+namespace {
+static int search_device_impl(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
+                              const uint32_t* d_part_ids, uint32_t P, uint32_t k, uint32_t refine_factor,
+                              const float* lower_or_null, const float* upper_or_null, float* d_out_dist,
+                              uint64_t* d_out_rowid, uint32_t* d_out_count, float* d_out_exact_or_null, void* stream) {
+  CtxLease ls;
+  int rc = ls.acquire(ix, (cudaStream_t)stream);
   if (rc) return rc;
-  if (Q && P && (!part_ids || !out_dist || !out_rowid || !out_count)) return set_err(LB200_EINVAL, "null argument");
-  if (k_prime == 0) return set_err(LB200_EINVAL, "k must be > 0");
-  if (!Q || !P) return 0;
-  for (size_t i = 0; i < (size_t)Q * P; i++)
-    if (part_ids[i] >= ix->nlist)  // ivf/v2.rs:288-293 "partition centroid {} does not exist"
-      return set_err(LB200_EINVAL, "partition centroid %u does not exist", part_ids[i]);
-  std::lock_guard<std::mutex> lk(ix->mu);
-  CK(cudaSetDevice(ix->device));
-  cudaStream_t st = ix->stream;
-  const size_t nq = (size_t)Q * ix->dim * 4, np = (size_t)Q * P * 4, no = (size_t)Q * P * k_prime;
-  HostStage hs;
-  size_t total = Arena::pad(nq) + Arena::pad(np) + Arena::pad(no * 4) + Arena::pad(no * 8) + Arena::pad(np) +
-                 Arena::pad((size_t)ix->nlist * 8);
-  CK(cudaMalloc(&hs.p, total));
-  char* b = (char*)hs.p;
-  float* d_q = (float*)b; b += Arena::pad(nq);
-  uint32_t* d_p = (uint32_t*)b; b += Arena::pad(np);
-  float* d_od = (float*)b; b += Arena::pad(no * 4);
-  uint64_t* d_or = (uint64_t*)b; b += Arena::pad(no * 8);
-  uint32_t* d_oc = (uint32_t*)b; b += Arena::pad(np);
-  const uint64_t** d_bmp = (const uint64_t**)b;
-  CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(d_p, part_ids, np, cudaMemcpyHostToDevice, st));
-  // prefilter bitmasks: upload each partition's mask, then the pointer table
-  std::vector<void*> mask_bufs;
-  std::vector<const uint64_t*> h_ptrs;
-  struct Cleanup { std::vector<void*>& v; ~Cleanup() { for (void* p : v) cudaFree(p); } } cleanup{mask_bufs};
-  if (part_bitmask_or_null) {
-    h_ptrs.assign(ix->nlist, nullptr);
-    for (uint32_t p = 0; p < ix->nlist; p++) {
-      if (!part_bitmask_or_null[p]) continue;
-      uint64_t n = ix->h_part_off[p + 1] - ix->h_part_off[p];
-      size_t words = (size_t)((n + 63) / 64) + 1;
-      void* dm = nullptr;
-      CK(cudaMalloc(&dm, words * 8));
-      mask_bufs.push_back(dm);
-      CK(cudaMemsetAsync(dm, 0, words * 8, st));
-      CK(cudaMemcpyAsync(dm, part_bitmask_or_null[p], (words - 1) * 8, cudaMemcpyHostToDevice, st));
-      h_ptrs[p] = (const uint64_t*)dm;
-    }
-    CK(cudaMemcpyAsync((void*)d_bmp, h_ptrs.data(), (size_t)ix->nlist * 8, cudaMemcpyHostToDevice, st));
-  }
   SearchArgs a = {};
-  a.d_queries = d_q; a.Q = Q; a.d_part_ids = d_p; a.P = P; a.k = k_prime; a.refine_factor = 0;
-  a.normalize = false; a.per_pair_output = true;
+  a.d_queries = d_queries; a.Q = Q; a.nprobes = nprobes; a.d_part_ids = d_part_ids; a.P = P; a.k = k;
+  a.refine_factor = refine_factor;
+  a.normalize = true; a.shard_mode = d_out_exact_or_null != nullptr;
   a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
   a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
-  a.d_bitmask = part_bitmask_or_null ? d_bmp : nullptr;
-  a.d_out_dist = d_od; a.d_out_rowid = d_or; a.d_out_count = d_oc;
-  rc = search_pipeline(ix, a, st);
+  a.d_out_dist = d_out_dist; a.d_out_rowid = d_out_rowid; a.d_out_count = d_out_count;
+  a.d_out_exact = d_out_exact_or_null;
+  rc = search_pipeline(ix, *ls.cx, a, ls.st);
   if (rc) return rc;
-  CK(cudaMemcpyAsync(out_dist, d_od, no * 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(out_rowid, d_or, no * 8, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(out_count, d_oc, np, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  if (!stream) CK(cudaStreamSynchronize(ls.st));
   return 0;
 }
+}  // namespace
 
 extern "C" int32_t lb200_search_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
                                        uint32_t k, uint32_t refine_factor, const float* lower_or_null,
@@ -600,20 +850,8 @@ extern "C" int32_t lb200_search_device(lb200_index* ix, const float* d_queries, 
   if (rc) return rc;
   if (Q && (!d_out_dist || !d_out_rowid || !d_out_count)) return set_err(LB200_EINVAL, "null output");
   if (nprobes == 0) return set_err(LB200_EINVAL, "nprobes must be > 0");
-  std::lock_guard<std::mutex> lk(ix->mu);
-  CK(cudaSetDevice(ix->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
-  SearchArgs a = {};
-  a.d_queries = d_queries; a.Q = Q; a.nprobes = nprobes; a.k = k; a.refine_factor = refine_factor;
-  a.normalize = true; a.shard_mode = d_out_exact_or_null != nullptr;
-  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
-  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
-  a.d_out_dist = d_out_dist; a.d_out_rowid = d_out_rowid; a.d_out_count = d_out_count;
-  a.d_out_exact = d_out_exact_or_null;
-  rc = search_pipeline(ix, a, st);
-  if (rc) return rc;
-  if (!stream) CK(cudaStreamSynchronize(st));
-  return 0;
+  return search_device_impl(ix, d_queries, Q, nprobes, nullptr, 0, k, refine_factor, lower_or_null, upper_or_null,
+                            d_out_dist, d_out_rowid, d_out_count, d_out_exact_or_null, stream);
 }
 
 extern "C" int32_t lb200_find_partitions_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes,
@@ -623,17 +861,18 @@ extern "C" int32_t lb200_find_partitions_device(lb200_index* ix, const float* d_
   if (rc) return rc;
   if (!d_out_part_ids) return set_err(LB200_EINVAL, "null output");
   if (nprobes == 0) return set_err(LB200_EINVAL, "nprobes must be > 0");
-  std::lock_guard<std::mutex> lk(ix->mu);
-  CK(cudaSetDevice(ix->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
   const uint32_t P = std::min(nprobes, ix->nlist);
   if (!Q) return 0;
+  CtxLease ls;
+  if ((rc = ls.acquire(ix, (cudaStream_t)stream))) return rc;
+  CallCtx& cx = *ls.cx;
+  cudaStream_t st = ls.st;
   size_t need = Arena::pad((size_t)Q * ix->dim * 4) + Arena::pad((size_t)Q * ix->nlist * 4) + 1024;
-  rc = ix->arena.reserve(need);
+  rc = cx.arena.reserve(need);
   if (rc) return rc;
-  ix->arena.reset();
-  float* d_keys = ix->arena.take<float>((size_t)Q * ix->dim);
-  float* d_D = ix->arena.take<float>((size_t)Q * ix->nlist);
+  cx.arena.reset();
+  float* d_keys = cx.arena.take<float>((size_t)Q * ix->dim);
+  float* d_D = cx.arena.take<float>((size_t)Q * ix->nlist);
   const float* keys = d_queries;
   uint32_t launches = 0;
   if (normalize_if_cosine && ix->metric == LB200_COSINE) {
@@ -656,20 +895,8 @@ extern "C" int32_t lb200_search_probed_device(lb200_index* ix, const float* d_qu
   if (rc) return rc;
   if (Q && (!d_out_dist || !d_out_rowid || !d_out_count || !d_part_ids)) return set_err(LB200_EINVAL, "null argument");
   if (P == 0 || P > ix->nlist) return set_err(LB200_EINVAL, "P must be in [1, nlist]");
-  std::lock_guard<std::mutex> lk(ix->mu);
-  CK(cudaSetDevice(ix->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
-  SearchArgs a = {};
-  a.d_queries = d_queries; a.Q = Q; a.d_part_ids = d_part_ids; a.P = P; a.k = k; a.refine_factor = refine_factor;
-  a.normalize = true; a.shard_mode = d_out_exact_or_null != nullptr;
-  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
-  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
-  a.d_out_dist = d_out_dist; a.d_out_rowid = d_out_rowid; a.d_out_count = d_out_count;
-  a.d_out_exact = d_out_exact_or_null;
-  rc = search_pipeline(ix, a, st);
-  if (rc) return rc;
-  if (!stream) CK(cudaStreamSynchronize(st));
-  return 0;
+  return search_device_impl(ix, d_queries, Q, 0, d_part_ids, P, k, refine_factor, lower_or_null, upper_or_null,
+                            d_out_dist, d_out_rowid, d_out_count, d_out_exact_or_null, stream);
 }
 
 extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
@@ -684,29 +911,45 @@ extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t 
   const bool refined = refine_factor > 0 && ix->d_raw;
   if (refine_factor > 0 && !ix->d_raw) return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
   const uint32_t ostride = refined ? k : k * std::max(refine_factor, 1u);
-  // staging for queries/results: a grow-only buffer owned by the handle (no cudaMalloc per call)
+  CtxLease ls;
+  if ((rc = ls.acquire(ix, nullptr))) return rc;
+  CallCtx& cx = *ls.cx;
+  cudaStream_t st = ls.st;
+  // staging for queries/results: grow-only buffers owned by the call context (no allocation per call)
   const size_t nq = (size_t)Q * ix->dim * 4, no = (size_t)Q * ostride;
-  char* b = nullptr;
-  std::lock_guard<std::mutex> slk(ix->stage_mu);  // whole call: the staging buffer is per handle
-  {
-    std::lock_guard<std::mutex> lk(ix->mu);
-    CK(cudaSetDevice(ix->device));
-    int rs = ix->stage.reserve(Arena::pad(nq) + Arena::pad(no * 4) + Arena::pad(no * 8) + Arena::pad((size_t)Q * 4));
-    if (rs) return rs;
-    b = ix->stage.base;
+  const size_t o_od = Arena::pad(nq), o_or = o_od + Arena::pad(no * 4), o_oc = o_or + Arena::pad(no * 8);
+  const size_t total = o_oc + Arena::pad((size_t)Q * 4);
+  if ((rc = cx.stage.reserve(total))) return rc;
+  char* b = cx.stage.base;
+  const bool pin = total <= LB200_PIN_BYTES;
+  if (pin) {
+    if ((rc = cx.pin_reserve(total))) return rc;
+    memcpy(cx.h_pin, queries, nq);
+    CK(cudaMemcpyAsync(b, cx.h_pin, nq, cudaMemcpyHostToDevice, st));
+  } else {
+    CK(cudaMemcpyAsync(b, queries, nq, cudaMemcpyHostToDevice, st));
   }
-  float* d_q = (float*)b; b += Arena::pad(nq);
-  float* d_od = (float*)b; b += Arena::pad(no * 4);
-  uint64_t* d_or = (uint64_t*)b; b += Arena::pad(no * 8);
-  uint32_t* d_oc = (uint32_t*)b;
-  cudaStream_t st = ix->stream;
-  CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
-  rc = lb200_search_device(ix, d_q, Q, nprobes, k, refine_factor, lower_or_null, upper_or_null, d_od, d_or, d_oc,
-                           nullptr, (void*)st);
+  SearchArgs a = {};
+  a.d_queries = reinterpret_cast<const float*>(b); a.Q = Q; a.nprobes = nprobes; a.k = k; a.refine_factor = refine_factor;
+  a.normalize = true;
+  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
+  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
+  a.d_out_dist = reinterpret_cast<float*>(b + o_od);
+  a.d_out_rowid = reinterpret_cast<uint64_t*>(b + o_or);
+  a.d_out_count = reinterpret_cast<uint32_t*>(b + o_oc);
+  rc = search_pipeline(ix, cx, a, st);
   if (rc) return rc;
-  CK(cudaMemcpyAsync(out_dist, d_od, no * 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(out_rowid, d_or, no * 8, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(out_count, d_oc, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  if (pin) {
+    CK(cudaMemcpyAsync(cx.h_pin + o_od, b + o_od, total - o_od, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    memcpy(out_dist, cx.h_pin + o_od, no * 4);
+    memcpy(out_rowid, cx.h_pin + o_or, no * 8);
+    memcpy(out_count, cx.h_pin + o_oc, (size_t)Q * 4);
+    return 0;
+  }
+  CK(cudaMemcpyAsync(out_dist, b + o_od, no * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_rowid, b + o_or, no * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_count, b + o_oc, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return 0;
 }

@@ -113,9 +113,27 @@ class IvfPqIndex:
         check(self._L.lb200_find_partitions(self._h, _p(key), C.c_uint32(Q), C.c_uint32(nprobes), _p(ids), _p(d)))
         return (ids, d) if return_distances else ids
 
+    def _mask_table(self, prefilter, keep):
+        """{partition id: bool array over the partition's rows} -> the [nlist] pointer table of the C ABI."""
+        ptrs = (C.c_void_p * self.nlist)()
+        for p, mask in prefilter.items():
+            n = int(self.part_offsets[p + 1] - self.part_offsets[p])
+            bits = np.zeros(((n + 63) // 64) * 8 + 8, dtype=np.uint8)
+            packed = np.packbits(np.asarray(mask, dtype=bool)[:n], bitorder="little")
+            bits[:packed.size] = packed
+            keep.append(bits)
+            ptrs[p] = bits.ctypes.data
+        return ptrs
+
+    def prefilter(self, masks):
+        """Upload a prefilter once (lb200_prefilter_create): the Arc<dyn PreFilter> every search_in_partition
+        call of a query shares (knn.rs:621).  masks: {partition id: bool array over that partition's rows}."""
+        return Prefilter(self, masks)
+
     def search_in_partition(self, part_ids, key, k, lower_bound=None, upper_bound=None, prefilter=None):
         """VectorIndex::search_in_partition (vector.rs:165) for [Q][P] explicit partitions.
-        prefilter: optional dict {partition id: bool/0-1 array over that partition's rows}."""
+        prefilter: optional dict {partition id: bool/0-1 array over that partition's rows}, or a
+        device-resident Prefilter made by self.prefilter(...)."""
         key = np.atleast_2d(_f32(key))
         self._check_dim(key)
         Q = key.shape[0]
@@ -125,16 +143,13 @@ class IvfPqIndex:
         oi = np.full((Q, P, max(k, 1)), np.iinfo(np.uint64).max, dtype=np.uint64)
         oc = np.zeros((Q, P), dtype=np.uint32)
         bm_arr, keep = None, []
+        if isinstance(prefilter, Prefilter):
+            check(self._L.lb200_search_partitions_filtered(
+                self._h, _p(key), C.c_uint32(Q), _p(part_ids), C.c_uint32(P), C.c_uint32(k), _fptr(lower_bound),
+                _fptr(upper_bound), prefilter._h, _p(od), _p(oi), _p(oc)))
+            return od, oi, oc
         if prefilter is not None:
-            ptrs = (C.c_void_p * self.nlist)()
-            for p, mask in prefilter.items():
-                n = int(self.part_offsets[p + 1] - self.part_offsets[p])
-                bits = np.zeros(((n + 63) // 64) * 8 + 8, dtype=np.uint8)
-                packed = np.packbits(np.asarray(mask, dtype=bool)[:n], bitorder="little")
-                bits[:packed.size] = packed
-                keep.append(bits)
-                ptrs[p] = bits.ctypes.data
-            bm_arr = ptrs
+            bm_arr = self._mask_table(prefilter, keep)
         check(self._L.lb200_search_partitions(
             self._h, _p(key), C.c_uint32(Q), _p(part_ids), C.c_uint32(P), C.c_uint32(k), _fptr(lower_bound),
             _fptr(upper_bound), bm_arr, _p(od), _p(oi), _p(oc)))
@@ -224,6 +239,23 @@ class IvfPqIndex:
         if key.shape[1] != self.dim:
             # scanner.rs:642-700: "query dim({}) doesn't match the column {} vector dim({})"
             raise ValueError(f"query dim({key.shape[1]}) doesn't match the index vector dim({self.dim})")
+
+
+class Prefilter:
+    """Device-resident per-partition row bitmasks of one index handle (lb200_prefilter_*)."""
+
+    def __init__(self, index, masks):
+        self._L, self._index, keep = index._L, index, []
+        h = C.c_void_p()
+        check(self._L.lb200_prefilter_create(index._h, index._mask_table(masks, keep), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lb200_prefilter_destroy(self._h)
+            self._h = None
+
+    __del__ = close
 
 
 def merge_topk_device(device_id, d_dist, d_rowid, d_exact, d_count, G, Q, stride, kprime, k, d_out_dist,

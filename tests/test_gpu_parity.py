@@ -349,6 +349,14 @@ def test_flat_parity(oracle, metric, d):
         _assert_same(gd, gi, gc, rd, ri, rc, f"flat {metric} k={k}")
 
 
+def test_flat_empty_batch():
+    """n = 0 (e.g. the allow-list removed every unindexed row): empty results, not an error."""
+    from lance_b200 import flat_knn
+    q = np.ones((3, 16), dtype=np.float32)
+    gd, gi, gc = flat_knn(q, "l2", np.zeros((0, 16), dtype=np.float32), 5)
+    assert gc.tolist() == [0, 0, 0] and np.all(np.isinf(gd))
+
+
 def test_flat_segmented_select(oracle):
     """n large enough that each distance row is cut into several select segments + merge; many
     duplicated rows so that ties straddle segment borders."""
