@@ -97,6 +97,45 @@ struct CallCtx {
   size_t h_pin_cap = 0;
   bool busy = false;
   std::vector<uint32_t> h_work;  // host-built work list of small calls
+  // CUDA graphs of small calls: the whole device side of a call (H2D from the pinned buffer, kernels, D2H into
+  // it) is fixed by the call's shape and this context's buffer addresses, so it is captured the second time a
+  // shape is seen and replayed afterwards -- ONE driver call per search_in_partition instead of ~6, which is
+  // what bounds the drop-in pattern (nprobes calls per query from a pool of host threads all contend on the
+  // driver's per-context lock).
+  struct GraphEntry {
+    std::vector<uint64_t> key;
+    cudaGraphExec_t exec = nullptr;
+    uint64_t last_use = 0;
+  };
+  std::vector<GraphEntry> graphs;
+  std::vector<std::vector<uint64_t>> seen;  // shapes seen once (first call runs eagerly and sizes the buffers)
+  uint64_t tick = 0;
+  cudaGraphExec_t find_graph(const std::vector<uint64_t>& key) {
+    for (auto& g : graphs)
+      if (g.key == key) { g.last_use = ++tick; return g.exec; }
+    return nullptr;
+  }
+  bool seen_before(const std::vector<uint64_t>& key) {
+    for (auto& k : seen)
+      if (k == key) return true;
+    if (seen.size() >= 16) seen.erase(seen.begin());
+    seen.push_back(key);
+    return false;
+  }
+  void store_graph(const std::vector<uint64_t>& key, cudaGraphExec_t exec) {
+    if (graphs.size() >= 8) {  // evict the least recently used
+      size_t lru = 0;
+      for (size_t i = 1; i < graphs.size(); i++)
+        if (graphs[i].last_use < graphs[lru].last_use) lru = i;
+      cudaGraphExecDestroy(graphs[lru].exec);
+      graphs.erase(graphs.begin() + lru);
+    }
+    GraphEntry e;
+    e.key = key;
+    e.exec = exec;
+    e.last_use = ++tick;
+    graphs.push_back(e);
+  }
   int pin_reserve(size_t bytes) {
     if (bytes <= h_pin_cap) return 0;
     if (h_pin) cudaFreeHost(h_pin);
@@ -397,6 +436,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_sb_off);
   for (CallCtx* c : ix->ctxs) {
     if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
     cudaFree(c->arena.base);
     cudaFree(c->stage.base);
     if (c->h_pin) cudaFreeHost(c->h_pin);

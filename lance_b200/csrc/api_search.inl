@@ -549,6 +549,49 @@ struct HostStage {
 };
 }  // namespace
 
+namespace {
+// Capture-once / replay of the device side of a small host-pointer call (see CallCtx::graphs).
+struct GraphRun {
+  CallCtx& cx;
+  cudaStream_t st;
+  std::vector<uint64_t> key;
+  bool capturing = false;
+  static uint64_t fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+  // 1: replayed (the device work is enqueued); 0: the caller enqueues it (eagerly, or into a capture); < 0: error
+  int begin(bool eligible) {
+    if (!eligible) return 0;
+    if (cudaGraphExec_t exec = cx.find_graph(key)) {
+      CK(cudaGraphLaunch(exec, st));
+      return 1;
+    }
+    if (!cx.seen_before(key)) return 0;  // first call of a shape runs eagerly: it sizes the context's buffers
+    CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    capturing = true;
+    return 0;
+  }
+  int end(int rc) {
+    if (!capturing) return rc;
+    capturing = false;
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture(st, &g);
+    if (rc) {
+      if (g) cudaGraphDestroy(g);
+      cudaGetLastError();
+      return rc;
+    }
+    if (e != cudaSuccess || !g) return set_err(LB200_ECUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    cudaGraphExec_t exec = nullptr;
+    e = cudaGraphInstantiate(&exec, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) return set_err(LB200_ECUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    cx.store_graph(key, exec);
+    CK(cudaGraphLaunch(exec, st));
+    return 0;
+  }
+};
+static bool graphs_enabled(const lb200_index* ix) { return !ix->profiling && !getenv("LB200_NO_GRAPHS"); }
+}  // namespace
+
 // Host<->device staging of the host-pointer entry points.  Small payloads go through the context's pinned
 // buffer (one async copy, no driver-side staging of pageable memory); large ones are copied straight from /
 // to the caller's memory (pinned by the caller in the benchmarks).
@@ -574,24 +617,32 @@ extern "C" int32_t lb200_find_partitions(lb200_index* ix, const float* queries, 
   uint32_t* d_p = cx.arena.take<uint32_t>((size_t)Q * P);   // d_p and d_pd are adjacent (pad(np) apart)
   float* d_pd = cx.arena.take<float>((size_t)Q * P);
   const bool pin = nq + 2 * Arena::pad(np) <= LB200_PIN_BYTES;
+  uint32_t launches = 0;
   if (pin) {
     if ((rc = cx.pin_reserve(nq + 2 * Arena::pad(np)))) return rc;
     memcpy(cx.h_pin, queries, nq);
-    CK(cudaMemcpyAsync(d_q, cx.h_pin, nq, cudaMemcpyHostToDevice, st));
-  } else {
-    CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
-  }
-  uint32_t launches = 0;
-  rc = coarse_device(ix, d_q, Q, P, d_D, d_p, d_pd, st, &launches);
-  if (rc) return rc;
-  if (pin) {
     const size_t span = out_part_dists_or_null ? Arena::pad(np) + np : np;
-    CK(cudaMemcpyAsync(cx.h_pin, d_p, span, cudaMemcpyDeviceToHost, st));
+    GraphRun gr{cx, st, {1, Q, P, span, (uint64_t)(uintptr_t)cx.arena.base, (uint64_t)(uintptr_t)cx.h_pin}};
+    int r = gr.begin(graphs_enabled(ix));
+    if (r < 0) return r;
+    if (r == 0) {
+      auto enqueue = [&]() -> int {
+        CK(cudaMemcpyAsync(d_q, cx.h_pin, nq, cudaMemcpyHostToDevice, st));
+        int rc2 = coarse_device(ix, d_q, Q, P, d_D, d_p, d_pd, st, &launches);
+        if (rc2) return rc2;
+        CK(cudaMemcpyAsync(cx.h_pin, d_p, span, cudaMemcpyDeviceToHost, st));
+        return 0;
+      };
+      if ((rc = gr.end(enqueue()))) return rc;
+    }
     CK(cudaStreamSynchronize(st));
     memcpy(out_part_ids, cx.h_pin, np);
     if (out_part_dists_or_null) memcpy(out_part_dists_or_null, cx.h_pin + Arena::pad(np), np);
     return 0;
   }
+  CK(cudaMemcpyAsync(d_q, queries, nq, cudaMemcpyHostToDevice, st));
+  rc = coarse_device(ix, d_q, Q, P, d_D, d_p, d_pd, st, &launches);
+  if (rc) return rc;
   CK(cudaMemcpyAsync(out_part_ids, d_p, np, cudaMemcpyDeviceToHost, st));
   if (out_part_dists_or_null) CK(cudaMemcpyAsync(out_part_dists_or_null, d_pd, np, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -765,12 +816,6 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
       w += nw + 1;
     }
   }
-  if (pin_in) {
-    CK(cudaMemcpyAsync(dbase, hin, in_bytes, cudaMemcpyHostToDevice, st));
-  } else {
-    CK(cudaMemcpyAsync(dbase + o_q, queries, nq, cudaMemcpyHostToDevice, st));
-    CK(cudaMemcpyAsync(dbase + o_p, hin + o_p, in_bytes - Arena::pad(nq), cudaMemcpyHostToDevice, st));
-  }
   SearchArgs a = {};
   a.d_queries = reinterpret_cast<const float*>(dbase + o_q); a.Q = Q;
   a.d_part_ids = reinterpret_cast<const uint32_t*>(dbase + o_p); a.P = P; a.k = k_prime; a.refine_factor = 0;
@@ -782,6 +827,39 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
   a.d_out_rowid = reinterpret_cast<uint64_t*>(dbase + o_or);
   a.d_out_count = reinterpret_cast<uint32_t*>(dbase + o_oc);
   a.pw = small ? &pw : nullptr;
+  if (pin_in && pin_out) {
+    // fixed device-side sequence for this shape and these buffers: captured once, replayed afterwards
+    GraphRun gr{cx, st, {2, Q, P, k_prime, (uint64_t)a.has_lower, GraphRun::fbits(a.lower), (uint64_t)a.has_upper,
+                         GraphRun::fbits(a.upper), (uint64_t)(uintptr_t)(pf ? pf->d_ptrs : nullptr), (uint64_t)small,
+                         in_bytes, (uint64_t)(uintptr_t)cx.arena.base, (uint64_t)(uintptr_t)dbase,
+                         (uint64_t)(uintptr_t)cx.h_pin}};
+    // which partitions are probed reaches the kernels only through device memory (the uploaded work list); the
+    // chunk plan and every launch dimension depend on (Q, P, k') alone.  Host masks change the upload size per
+    // call: not captured (lb200_prefilter objects are).
+    int r = gr.begin(graphs_enabled(ix) && small && !host_masks);
+    if (r < 0) return r;
+    if (r == 0) {
+      auto enqueue = [&]() -> int {
+        CK(cudaMemcpyAsync(dbase, hin, in_bytes, cudaMemcpyHostToDevice, st));
+        int rc2 = search_pipeline(ix, cx, a, st);
+        if (rc2) return rc2;
+        CK(cudaMemcpyAsync(hout, dbase + o_od, out_bytes, cudaMemcpyDeviceToHost, st));
+        return 0;
+      };
+      if ((rc = gr.end(enqueue()))) return rc;
+    }
+    CK(cudaStreamSynchronize(st));
+    memcpy(out_dist, hout, no * 4);
+    memcpy(out_rowid, hout + (o_or - o_od), no * 8);
+    memcpy(out_count, hout + (o_oc - o_od), np);
+    return 0;
+  }
+  if (pin_in) {
+    CK(cudaMemcpyAsync(dbase, hin, in_bytes, cudaMemcpyHostToDevice, st));
+  } else {
+    CK(cudaMemcpyAsync(dbase + o_q, queries, nq, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(dbase + o_p, hin + o_p, in_bytes - Arena::pad(nq), cudaMemcpyHostToDevice, st));
+  }
   rc = search_pipeline(ix, cx, a, st);
   if (rc) return rc;
   if (pin_out) {
@@ -922,13 +1000,6 @@ extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t 
   if ((rc = cx.stage.reserve(total))) return rc;
   char* b = cx.stage.base;
   const bool pin = total <= LB200_PIN_BYTES;
-  if (pin) {
-    if ((rc = cx.pin_reserve(total))) return rc;
-    memcpy(cx.h_pin, queries, nq);
-    CK(cudaMemcpyAsync(b, cx.h_pin, nq, cudaMemcpyHostToDevice, st));
-  } else {
-    CK(cudaMemcpyAsync(b, queries, nq, cudaMemcpyHostToDevice, st));
-  }
   SearchArgs a = {};
   a.d_queries = reinterpret_cast<const float*>(b); a.Q = Q; a.nprobes = nprobes; a.k = k; a.refine_factor = refine_factor;
   a.normalize = true;
@@ -937,16 +1008,33 @@ extern "C" int32_t lb200_search(lb200_index* ix, const float* queries, uint32_t 
   a.d_out_dist = reinterpret_cast<float*>(b + o_od);
   a.d_out_rowid = reinterpret_cast<uint64_t*>(b + o_or);
   a.d_out_count = reinterpret_cast<uint32_t*>(b + o_oc);
-  rc = search_pipeline(ix, cx, a, st);
-  if (rc) return rc;
   if (pin) {
-    CK(cudaMemcpyAsync(cx.h_pin + o_od, b + o_od, total - o_od, cudaMemcpyDeviceToHost, st));
+    if ((rc = cx.pin_reserve(total))) return rc;
+    memcpy(cx.h_pin, queries, nq);
+    GraphRun gr{cx, st, {3, Q, nprobes, k, refine_factor, (uint64_t)a.has_lower, GraphRun::fbits(a.lower),
+                         (uint64_t)a.has_upper, GraphRun::fbits(a.upper), (uint64_t)(uintptr_t)cx.arena.base,
+                         (uint64_t)(uintptr_t)b, (uint64_t)(uintptr_t)cx.h_pin}};
+    int r = gr.begin(graphs_enabled(ix) && ix->bits == 8);
+    if (r < 0) return r;
+    if (r == 0) {
+      auto enqueue = [&]() -> int {
+        CK(cudaMemcpyAsync(b, cx.h_pin, nq, cudaMemcpyHostToDevice, st));
+        int rc2 = search_pipeline(ix, cx, a, st);
+        if (rc2) return rc2;
+        CK(cudaMemcpyAsync(cx.h_pin + o_od, b + o_od, total - o_od, cudaMemcpyDeviceToHost, st));
+        return 0;
+      };
+      if ((rc = gr.end(enqueue()))) return rc;
+    }
     CK(cudaStreamSynchronize(st));
     memcpy(out_dist, cx.h_pin + o_od, no * 4);
     memcpy(out_rowid, cx.h_pin + o_or, no * 8);
     memcpy(out_count, cx.h_pin + o_oc, (size_t)Q * 4);
     return 0;
   }
+  CK(cudaMemcpyAsync(b, queries, nq, cudaMemcpyHostToDevice, st));
+  rc = search_pipeline(ix, cx, a, st);
+  if (rc) return rc;
   CK(cudaMemcpyAsync(out_dist, b + o_od, no * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(out_rowid, b + o_or, no * 8, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(out_count, b + o_oc, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
