@@ -511,7 +511,14 @@ def main():
     d_oi = torch.empty((Q, ks), dtype=torch.int64, device=dev)
     d_oc = torch.empty((Q,), dtype=torch.int32, device=dev)
     d_ex = torch.empty((Q, ks), dtype=torch.float32, device=dev) if shard_mode else None
-    if shard_mode:
+    peer_exchange = shard_mode and os.environ.get("LB200_EXCHANGE", "peer") == "peer"
+    if shard_mode and peer_exchange:
+        # the whole exchange inside the library (lb200_shard_*): NVLink peer stores + epoch flags, no collective
+        from lance_b200.shard import PeerShardedIvfPq
+        sh = PeerShardedIvfPq(ix, dist, dev)
+        sh.prepare(Q, nprobes, k, refine)
+        f_od, f_oi, f_oc = sh.fd, sh.fi, sh.fc
+    elif shard_mode:
         from lance_b200.shard import ShardedIvfPq
         sh = ShardedIvfPq(ix, dist, dev, shard_coarse=not os.environ.get("LB200_REPLICATED_COARSE"))
         sh.prepare(Q, nprobes, k, refine)
@@ -540,6 +547,9 @@ def main():
     def e2e_step():
         if not shard_mode:
             return e2e_host_abi_step()
+        if peer_exchange:   # lb200_shard_search: host buffers in, host results out (rank 0), blocking
+            sh.search_host(hq_np, e2e_out)
+            return
         sh.search_host(h_q, stream)
         if rank == 0:
             src = (f_od, f_oi, f_oc) if shard_mode else (d_od, d_oi, d_oc)
@@ -581,7 +591,10 @@ def main():
         st = ix.stats()
         scan_ms.append(st["scan_ms"])
         scan_bytes.append(st["scan_code_bytes"])
-        launches += st["kernel_launches"] + ((3 if sh.shard_coarse else 0) + (1 if rank == 0 else 0) if shard_mode else 0)
+        if shard_mode and peer_exchange:   # + coarse (2) + publish + signal/wait x2 (+ root: wait + merge)
+            launches += st["kernel_launches"] + 6 + (2 if rank == 0 else 0)
+        else:
+            launches += st["kernel_launches"] + ((3 if sh.shard_coarse else 0) + (1 if rank == 0 else 0) if shard_mode else 0)
 
     ms_total = timed(profiled_step, args.steps)
     clocks = sampler.stop() if rank == 0 else None
@@ -651,6 +664,8 @@ def main():
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "queries_per_step": Q, "k": k, "nprobes": nprobes, "refine_factor": refine,
                    "parallelism": f"ivf-partitions sharded over {world} GPU(s)",
+                   "exchange": ("peer memory inside liblance_b200.so (lb200_shard_*), 0 collectives per batch" if peer_exchange
+                                else "NCCL all_gather from the host") if shard_mode else None,
                    "l2_policy": "inputs larger than L2 (PQ codes %.2f GB per GPU)" % (data.codes.nbytes / 1e9),
                    "scan_variant": st["scan_variant"], "scan_queries_per_cta": st["scan_ql"],
                    "index_build_s": round(t_build, 1)},
@@ -664,7 +679,8 @@ def main():
         "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": int(h_q.numel() * 4),
                 "d2h_bytes_per_step": int(h_od.numel() * 4 + h_oi.numel() * 8 + h_oc.numel() * 4),
                 "ms_per_step": ms_e2e / e2e_steps,
-                "path": "per-rank pinned H2D of Q/N queries + NCCL all_gather of queries + sharded search + NCCL all_gather + merge, D2H on rank 0" if shard_mode else
+                "path": ("lb200_shard_search on every rank (host buffers; own Q/N slice over PCIe, peers' slices and probe lists over NVLink peer memory, lists into rank 0's gather buffer, merge, D2H on rank 0; no collective)" if peer_exchange else
+                         "per-rank pinned H2D of Q/N queries + NCCL all_gather of queries + sharded search + NCCL all_gather + merge, D2H on rank 0") if shard_mode else
                         "lb200_search (host-pointer C ABI, pinned host buffers, blocking; host wall clock)"},
         "gpu_launches": int(launches),
         "clocks": clocks,

@@ -198,6 +198,52 @@ int32_t lb200_peer_thresholds_attach(lb200_index* ix, uint32_t world, uint32_t s
                                      const uint64_t* same_process_ptrs_or_null);
 int32_t lb200_peer_thresholds_detach(lb200_index* ix);
 
+/* The multi-GPU form of lb200_search: IVF partitions sharded over the GPUs of one box, the
+ * whole exchange inside the library -- no collective library, no host round trip per batch.  Per batch a shard
+ * selects the probes of its slice of the queries, stores them into every peer's exchange block over NVLink peer
+ * memory, scans the probed partitions it owns (sharing pruning bounds with the peers from inside the scan kernel,
+ * see lb200_peer_thresholds_*), writes its k' candidates straight into the ROOT shard's gather buffer, and the
+ * root merges the G lists (== concat_batches + sort_to_indices(limit), ivf/v2.rs:383-400, then the scanner's
+ * refine cut).  Ranks meet through epoch flags in each other's memory; a peer that never arrives makes the call
+ * fail after a time-out (LB200_ECUDA) instead of hanging the GPU.  Results are bit-identical to lb200_search on
+ * the unsharded index.
+ *
+ * (a) one process per GPU: every rank builds an lb200_index from ITS partitions (all nlist partitions, the ones
+ *     it does not own empty; centroids and codebook replicated), then
+ *       lb200_shard_export  -> a 128-byte opaque blob (CUDA IPC handles); capacities are per batch;
+ *       the host exchanges the blobs of all ranks any way it likes (MPI, torch.distributed, a socket);
+ *       lb200_shard_attach(world, rank, root, blobs [world][128])  (or same_process_ptrs [world][2] as returned
+ *       in dev_ptrs_out_2, for shards living in one process);
+ *       lb200_shard_search / lb200_shard_search_device on EVERY rank, same arguments, same order.  The result
+ *       is written on the root rank only.  lb200_shard_search takes the full batch on every rank but moves only
+ *       the rank's own slice over PCIe (the rest arrives from the peers over NVLink).
+ * (b) one process driving all GPUs (a host that embeds the library): lb200_group_create shards a whole index by
+ *     part_owner [nlist] (NULL = greedy bin-packing on row count, largest first) onto device_ids[G], root =
+ *     shard 0; lb200_group_search == lb200_search. */
+int32_t lb200_shard_export(lb200_index* ix, uint32_t max_queries, uint32_t max_nprobes, uint32_t max_kprime,
+                           void* blob_out_128_or_null, uint64_t* dev_ptrs_out_2_or_null);
+int32_t lb200_shard_attach(lb200_index* ix, uint32_t world, uint32_t rank, uint32_t root, const void* blobs_or_null,
+                           const uint64_t* same_process_ptrs_or_null);
+int32_t lb200_shard_detach(lb200_index* ix);
+int32_t lb200_shard_search(lb200_index* ix, const float* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
+                           uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
+                           float* out_dist, uint64_t* out_rowid, uint32_t* out_count);
+int32_t lb200_shard_search_device(lb200_index* ix, const float* d_queries, uint32_t Q, uint32_t nprobes, uint32_t k,
+                                  uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
+                                  float* d_out_dist, uint64_t* d_out_rowid, uint32_t* d_out_count, void* stream);
+int32_t lb200_shard_check(lb200_index* ix); /* error state of the exchange after asynchronous calls */
+
+typedef struct lb200_group lb200_group;
+int32_t lb200_group_create(const int32_t* device_ids, uint32_t G, int32_t metric, uint32_t dim, uint32_t nlist,
+                           const float* centroids, uint32_t num_sub_vectors, uint32_t num_bits, const float* codebook,
+                           const uint64_t* part_offsets, const uint8_t* codes, const uint64_t* row_ids,
+                           const float* raw_vectors_or_null, const uint32_t* part_owner_or_null,
+                           uint32_t max_queries, uint32_t max_nprobes, uint32_t max_kprime, lb200_group** out);
+int32_t lb200_group_search(lb200_group* g, const float* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
+                           uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
+                           float* out_dist, uint64_t* out_rowid, uint32_t* out_count);
+void lb200_group_destroy(lb200_group* g);
+
 /* compute_distance (flat.rs:28-86; KNNVectorDistanceExec, io/exec/knn.rs:156-183): one
  * distance per (query,row); validity = Arrow validity bitmap (bit set = valid) or NULL;
  * null rows yield NaN.  out [Q][n]. */

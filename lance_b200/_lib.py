@@ -18,6 +18,8 @@ EXPORTS = [
     "lb200_merge_topk", "lb200_rerank",
     "lb200_index_file_open", "lb200_index_file_open_bytes", "lb200_index_file_get_info", "lb200_index_file_close",
     "lb200_index_open", "lb200_flat_distance_f16", "lb200_flat_topk_f16", "lb200_normalize",
+    "lb200_shard_export", "lb200_shard_attach", "lb200_shard_detach", "lb200_shard_search", "lb200_shard_search_device",
+    "lb200_shard_check", "lb200_group_create", "lb200_group_search", "lb200_group_destroy",
     "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
 ]
 
@@ -51,6 +53,7 @@ def lib():
         _lib.lb200_version.restype = C.c_char_p
         _lib.lb200_index_destroy.restype = None
         _lib.lb200_prefilter_destroy.restype = None
+        _lib.lb200_group_destroy.restype = None
         for name in EXPORTS:
             if os.environ.get("LB200_SO") and not hasattr(_lib, name):
                 continue  # an older build under A/B test may predate a symbol

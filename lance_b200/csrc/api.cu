@@ -56,12 +56,23 @@ static inline uint32_t next_pow2(uint32_t v) {
 struct Arena {
   char* base = nullptr;
   size_t cap = 0, used = 0;
-  int reserve(size_t bytes) {
-    if (bytes <= cap) return 0;
-    if (base) cudaFree(base);
+  // Outgrown buffers are retired, not freed: cudaFree synchronises the whole device, and on a shard whose stream
+  // holds a kernel waiting for a peer that this very host thread has yet to launch (one process driving several
+  // GPUs, api_group.inl) that would dead-lock.  Growth is geometric, so the retired buffers stay below the live one.
+  std::vector<char*> retired;
+  void release() {
+    for (char* p : retired) cudaFree(p);
+    retired.clear();
+    cudaFree(base);
     base = nullptr;
     cap = 0;
-    size_t want = bytes + (bytes >> 3);
+  }
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (base) retired.push_back(base);
+    base = nullptr;
+    cap = 0;
+    size_t want = bytes + (bytes >> 1);
     cudaError_t e = cudaMalloc((void**)&base, want);
     if (e != cudaSuccess) {
       cudaGetLastError();
@@ -158,7 +169,9 @@ struct lb200_prefilter {
 };
 
 constexpr uint32_t LB200_MAX_PEERS = 15;
+struct ShardComm;  // api_group.inl: the exchange block of a partition shard (multi-GPU)
 struct lb200_index {
+  ShardComm* comm = nullptr;
   int device = 0, metric = 0;
   uint32_t dim = 0, nlist = 0, M = 0, dsub = 0;
   uint64_t N = 0, ntiles = 0, max_part = 0;
@@ -419,9 +432,11 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   return 0;
 }
 
+static void shard_comm_free(lb200_index* ix);  // api_group.inl
 extern "C" void lb200_index_destroy(lb200_index* ix) {
   if (!ix) return;
   cudaSetDevice(ix->device);
+  shard_comm_free(ix);
   cudaFree(ix->d_centroids);
   cudaFree(ix->d_codebook);
   cudaFree(ix->d_raw);
@@ -437,8 +452,8 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   for (CallCtx* c : ix->ctxs) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
-    cudaFree(c->arena.base);
-    cudaFree(c->stage.base);
+    c->arena.release();
+    c->stage.release();
     if (c->h_pin) cudaFreeHost(c->h_pin);
     if (c->done) cudaEventDestroy(c->done);
     for (auto& e : c->ev)
@@ -567,5 +582,6 @@ extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
 #include "api_flat.inl"
 #include "api_pq4.inl"
 #include "api_combined.inl"
+#include "api_group.inl"
 #include "api_file.inl"
 #include "api_f16.inl"

@@ -492,9 +492,10 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
         CK(cudaMemsetAsync(exact, 0xff, (size_t)Q * kprime * 4, st));  // NaN
       }
       if (a.shard_mode) {
-        CK(cudaMemcpyAsync(a.d_out_dist, d_mdist, (size_t)Q * kprime * 4, cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(a.d_out_rowid, d_mrow, (size_t)Q * kprime * 8, cudaMemcpyDeviceToDevice, st));
-        CK(cudaMemcpyAsync(a.d_out_count, d_mcnt, (size_t)Q * 4, cudaMemcpyDeviceToDevice, st));
+        // (the outputs may live in the ROOT shard's gather buffer on another GPU: peer memory, api_group.inl)
+        CK(cudaMemcpyAsync(a.d_out_dist, d_mdist, (size_t)Q * kprime * 4, cudaMemcpyDefault, st));
+        CK(cudaMemcpyAsync(a.d_out_rowid, d_mrow, (size_t)Q * kprime * 8, cudaMemcpyDefault, st));
+        CK(cudaMemcpyAsync(a.d_out_count, d_mcnt, (size_t)Q * 4, cudaMemcpyDefault, st));
       } else {
         rerank_kernel<<<(Q * 32 + 127) / 128, 128, 0, st>>>(exact, d_mrow, d_mcnt, Q, kprime, a.k, a.has_lower, a.lower,
                                                           a.has_upper, a.upper, a.d_out_dist, a.d_out_rowid,

@@ -25,4 +25,6 @@ cudaError_t launch_scan(const ScanConfig& c, int grid, cudaStream_t st, const Sc
 cudaError_t launch_scan3(const ScanConfig& c, bool boot, int sm_count, cudaStream_t st, const Scan3Params& sp,
                          const uint32_t* total_items);
 
+void preload_scan3(int ql, int dsub_t);  // module-load every variant-3 instantiation of this (QL, dsub)
+
 }  // namespace lb200

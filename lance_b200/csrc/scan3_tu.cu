@@ -52,4 +52,31 @@ cudaError_t launch_scan3(const ScanConfig& c, bool boot, int sm_count, cudaStrea
               : launch_scan3_b<false>(c, sm_count, st, sp, total_items);
 }
 
+
+// Force the module load of every instantiation a handle with this (QL, dsub) may launch.  Under CUDA's lazy
+// module loading the FIRST launch of a kernel may have to synchronise with running kernels; a shard whose
+// stream holds a kernel waiting for a peer (api_group.inl) must never meet that on its way to the kernels
+// the peer is waiting for.
+template <int QL, int D, int DS>
+static void preload_qd() {
+  cudaFuncAttributes a;
+  cudaFuncGetAttributes(&a, scan3_entry<QL, D, 8, 1, DS, true>());
+  cudaFuncGetAttributes(&a, scan3_entry<QL, D, 8, 2, DS, true>());
+  cudaFuncGetAttributes(&a, scan3_entry<QL, D, 8, 1, DS, false>());
+  cudaFuncGetAttributes(&a, scan3_entry<QL, D, 8, 2, DS, false>());
+  if constexpr (DS != 0) cudaFuncGetAttributes(&a, scan3_entry<QL, D, 16, 1, DS, true>());
+}
+void preload_scan3(int ql, int dsub_t) {
+  if (ql == 4) {
+    if (dsub_t == 8) preload_qd<4, 8, 8>();
+    else if (dsub_t == 16) preload_qd<4, 8, 16>();
+    else preload_qd<4, 8, 0>();
+  } else {
+    if (dsub_t == 8) preload_qd<2, 16, 8>();
+    else if (dsub_t == 16) preload_qd<2, 16, 16>();
+    else preload_qd<2, 16, 0>();
+  }
+  cudaGetLastError();
+}
+
 }  // namespace lb200

@@ -224,6 +224,59 @@ class IvfPqIndex:
     def peer_thresholds_detach(self):
         check(self._L.lb200_peer_thresholds_detach(self._h))
 
+    # -- multi-GPU: partition shards that exchange through peer memory (lb200_shard_*) ------------
+    def shard_export(self, max_queries, max_nprobes, max_kprime):
+        """Allocate this shard's exchange block; returns (128-byte blob for peers in other processes,
+        (block address, bound-table address) for peers in this process)."""
+        blob = (C.c_ubyte * 128)()
+        ptrs = (C.c_uint64 * 2)()
+        check(self._L.lb200_shard_export(self._h, C.c_uint32(max_queries), C.c_uint32(max_nprobes), C.c_uint32(max_kprime),
+                                         blob, ptrs))
+        return bytes(blob), (int(ptrs[0]), int(ptrs[1]))
+
+    def shard_attach(self, world, rank, blobs=None, ptrs=None, root=0):
+        """blobs: `world` 128-byte blobs (one process per GPU), or ptrs: `world` (block, table) address pairs."""
+        bb = pb = None
+        if ptrs is not None:
+            flat = [int(x) for pair in ptrs for x in pair]
+            pb = (C.c_uint64 * (2 * world))(*flat)
+        else:
+            raw = b"".join(blobs)
+            assert len(raw) == 128 * world
+            bb = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+        check(self._L.lb200_shard_attach(self._h, C.c_uint32(world), C.c_uint32(rank), C.c_uint32(root), bb, pb))
+
+    def shard_detach(self):
+        check(self._L.lb200_shard_detach(self._h))
+
+    def shard_check(self):
+        check(self._L.lb200_shard_check(self._h))
+
+    def shard_search_device(self, d_queries_ptr, Q, nprobes, k, refine_factor, d_out_dist, d_out_rowid, d_out_count,
+                            stream=None, lower=None, upper=None):
+        """One batch on this shard, asynchronous on `stream`; every rank calls it, the root gets the result."""
+        check(self._L.lb200_shard_search_device(
+            self._h, C.c_void_p(d_queries_ptr), C.c_uint32(Q), C.c_uint32(nprobes), C.c_uint32(k),
+            C.c_uint32(refine_factor), _fptr(lower), _fptr(upper), C.c_void_p(d_out_dist), C.c_void_p(d_out_rowid),
+            C.c_void_p(d_out_count), C.c_void_p(stream) if stream else None))
+
+    def shard_search(self, query: Query, out=None):
+        """Host-pointer form (blocking): every rank passes the full batch; returns (dist, ids, counts) -- meaningful
+        on the root rank only."""
+        key = np.atleast_2d(_f32(query.key))
+        self._check_dim(key)
+        Q, rf = key.shape[0], int(query.refine_factor or 0)
+        if out is not None:
+            od, oi, oc = out
+        else:
+            od = np.full((Q, query.k), np.inf, dtype=np.float32)
+            oi = np.full((Q, query.k), np.iinfo(np.uint64).max, dtype=np.uint64)
+            oc = np.zeros(Q, dtype=np.uint32)
+        check(self._L.lb200_shard_search(
+            self._h, _p(key), C.c_uint32(Q), C.c_uint32(query.nprobes), C.c_uint32(query.k), C.c_uint32(rf),
+            _fptr(query.lower_bound), _fptr(query.upper_bound), _p(od), _p(oi), _p(oc)))
+        return od, oi, oc
+
     def set_profiling(self, on=True):
         check(self._L.lb200_set_profiling(self._h, C.c_int32(1 if on else 0)))
 
@@ -239,6 +292,48 @@ class IvfPqIndex:
         if key.shape[1] != self.dim:
             # scanner.rs:642-700: "query dim({}) doesn't match the column {} vector dim({})"
             raise ValueError(f"query dim({key.shape[1]}) doesn't match the index vector dim({self.dim})")
+
+
+class IvfPqGroup:
+    """A whole index sharded over several GPUs of ONE process (lb200_group_*): search() == IvfPqIndex.search()."""
+
+    def __init__(self, data, device_ids, max_queries, max_nprobes, max_kprime, part_owner=None):
+        L = _lib.lib()
+        self._L, self.dim, self.has_raw = L, int(data.dim), data.raw_vectors is not None
+        G = len(device_ids)
+        devs = (C.c_int32 * G)(*[int(d) for d in device_ids])
+        po = None if part_owner is None else np.ascontiguousarray(part_owner, dtype=np.uint32)
+        cents, cb = _f32(data.centroids), _f32(data.codebook)
+        codes = np.ascontiguousarray(data.codes, dtype=np.uint8)
+        rids = np.ascontiguousarray(data.row_ids, dtype=np.uint64)
+        offs = np.ascontiguousarray(data.part_offsets, dtype=np.uint64)
+        raw = None if data.raw_vectors is None else _f32(data.raw_vectors)
+        h = C.c_void_p()
+        check(L.lb200_group_create(devs, C.c_uint32(G), C.c_int32(DistanceType.code(data.metric)), C.c_uint32(self.dim),
+                                   C.c_uint32(int(data.nlist)), _p(cents), C.c_uint32(int(data.M)), C.c_uint32(8), _p(cb),
+                                   _p(offs), _p(codes), _p(rids), _p(raw), _p(po), C.c_uint32(max_queries),
+                                   C.c_uint32(max_nprobes), C.c_uint32(max_kprime), C.byref(h)))
+        self._h = h
+
+    def search(self, query: Query):
+        key = np.atleast_2d(_f32(query.key))
+        if key.shape[1] != self.dim:
+            raise ValueError(f"query dim({key.shape[1]}) doesn't match the index vector dim({self.dim})")
+        Q, rf = key.shape[0], int(query.refine_factor or 0)
+        od = np.full((Q, query.k), np.inf, dtype=np.float32)
+        oi = np.full((Q, query.k), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros(Q, dtype=np.uint32)
+        check(self._L.lb200_group_search(self._h, _p(key), C.c_uint32(Q), C.c_uint32(query.nprobes), C.c_uint32(query.k),
+                                         C.c_uint32(rf), _fptr(query.lower_bound), _fptr(query.upper_bound), _p(od), _p(oi),
+                                         _p(oc)))
+        return od, oi, oc
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lb200_group_destroy(self._h)
+            self._h = None
+
+    __del__ = close
 
 
 class Prefilter:

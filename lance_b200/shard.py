@@ -154,3 +154,39 @@ class ShardedIvfPq:
                               self.g_ex.data_ptr() if rf else None, self.g_oc.data_ptr(), self.world, Q, self.kp,
                               self.kp, k, self.fd.data_ptr(), self.fi.data_ptr(), self.fc.data_ptr(), stream=sp)
         return self.fd, self.fi, self.fc
+
+
+class PeerShardedIvfPq:
+    """One rank's view of a partition-sharded index whose whole exchange lives in liblance_b200.so (lb200_shard_*):
+    probe lists and candidate lists move between the GPUs through NVLink peer memory, ranks meet through epoch flags
+    -- no collective per batch.  torch.distributed is used ONCE, at set-up, to hand the 128-byte blobs around (any
+    channel would do)."""
+
+    def __init__(self, index, dist, device):
+        import torch
+        self.ix, self.dist, self.dev, self._torch = index, dist, device, torch
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+
+    def prepare(self, Q, nprobes, k, refine_factor):
+        torch, G = self._torch, self.world
+        self.Q, self.P, self.k, self.refine = Q, min(nprobes, self.ix.nlist), k, refine_factor
+        blob, _ = self.ix.shard_export(Q, self.P, k * max(refine_factor, 1))
+        mine = torch.tensor(list(blob), dtype=torch.uint8, device=self.dev)
+        allb = torch.empty((G, 128), dtype=torch.uint8, device=self.dev)
+        self.dist.all_gather_into_tensor(allb, mine)
+        self.ix.shard_attach(G, self.rank, blobs=[bytes(allb[g].cpu().tolist()) for g in range(G)])
+        self.dist.barrier()   # every block exists and is mapped before anyone's first batch stores into it
+        self.fd = torch.empty((Q, k), dtype=torch.float32, device=self.dev)
+        self.fi = torch.empty((Q, k), dtype=torch.int64, device=self.dev)
+        self.fc = torch.empty((Q,), dtype=torch.int32, device=self.dev)
+
+    def search_device(self, d_queries, stream):
+        """d_queries: CUDA f32 [Q][dim], the same on every rank.  Asynchronous on `stream`; (fd, fi, fc) on rank 0."""
+        self.ix.shard_search_device(d_queries.data_ptr(), self.Q, self.P, self.k, self.refine, self.fd.data_ptr(),
+                                    self.fi.data_ptr(), self.fc.data_ptr(), stream=stream.cuda_stream)
+        return self.fd, self.fi, self.fc
+
+    def search_host(self, h_queries_np, out):
+        """Blocking host-pointer entry (lb200_shard_search): only this rank's slice of the batch crosses PCIe."""
+        from .index import Query
+        return self.ix.shard_search(Query(key=h_queries_np, k=self.k, nprobes=self.P, refine_factor=self.refine or None), out=out)
