@@ -55,7 +55,7 @@ def partition_sizes(N, nlist, seed, sigma=0.5):
     return sizes
 
 
-from lance_b200.shard import assign_partitions  # noqa: E402  (greedy bin-packing)
+from lance_b200.shard import assign_partitions, probe_load_weights  # noqa: E402  (greedy bin-packing)
 
 
 def make_shard(wl, seed, rank, world, keep_raw=False):
@@ -65,7 +65,6 @@ def make_shard(wl, seed, rank, world, keep_raw=False):
     N, d, nlist, M, metric = wl[0], wl[1], wl[2], wl[3], wl[4]
     ncent, cbytes = (16, M // 2) if _BITS == 4 else (256, M)
     sizes = partition_sizes(N, nlist, seed)
-    owner = assign_partitions(sizes, world)
     rng = np.random.default_rng(seed + 1)
     if metric == "dot":
         cents = rng.normal(size=(nlist, d)).astype(np.float32)
@@ -77,6 +76,9 @@ def make_shard(wl, seed, rank, world, keep_raw=False):
     else:
         cents = rng.uniform(0, 128, size=(nlist, d)).astype(np.float32)
         codebook = rng.normal(0, 16, size=(M, ncent, d // M)).astype(np.float32)
+    # partitions -> ranks: balanced on rows x expected probes (estimated from the centroids alone, shard.py)
+    weights = None if (world == 1 or os.environ.get("LB200_BALANCE") == "rows") else probe_load_weights(cents, metric, wl[5])
+    owner = assign_partitions(sizes, world, weights)
     goffs = np.zeros(nlist + 1, dtype=np.int64)
     goffs[1:] = np.cumsum(sizes)
     mine = owner == rank
@@ -635,7 +637,7 @@ def main():
     my_bytes = float(np.mean(scan_bytes))
     achieved = my_bytes / (my_scan_ms * 1e-3) / 1e9 if my_scan_ms > 0 else 0.0
     # which instantiation ran (the library's rule, api_search.inl): pre-built tables or mostly-cold items
-    # (shards, few probes) -> scan3_kernel; otherwise the call-free scan3_nb_kernel
+    # (shards, few probes) -> the BOOT=true instantiation of scan3_kernel; otherwise the call-free BOOT=false one
     avg_np = float(np.mean(sizes[sizes > 0])) if len(sizes) else 0.0
     pre = metric == "dot" or 256.0 * (d // M) > avg_np
     if os.environ.get("LB200_LUT_PREPASS"):
@@ -647,7 +649,7 @@ def main():
     if st["scan_variant"] == 32:
         kname = "scanflat_kernel + flat_select_kernel (IVF_FLAT; bytes = n_p*dim*4 per pair)"
     if st["scan_variant"] == 3:
-        kname = "scan3_kernel" if (shard_mode or nprobes < 16 or pre) else "scan3_nb_kernel"
+        kname = "scan3_kernel<BOOT=%s>" % ("true" if (shard_mode or nprobes < 16) else "false")
         if pre:
             kname += " + lut_prepass_kernel"
     traffic, traffic_src = None, None

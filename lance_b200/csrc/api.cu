@@ -366,13 +366,10 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   const bool want_tile = !want_skew || want_all;
   std::vector<uint64_t> sb_off(nlist + 1, 0);
   if (want_skew) {
-    // rows per lane per superblock: ~2 superblocks per warp of an 8-warp CTA on an average
-    // partition, clamped to [4, 32] (drain overhead is 0.5/L of the lookups).
-    uint32_t nonempty = 0;
-    for (uint32_t p = 0; p < nlist; p++) nonempty += part_offsets[p + 1] > part_offsets[p];
-    double avg = (double)N / std::max(1u, nonempty);  // a shard holds all nlist partitions, most of them empty
-    uint32_t L = 4;
-    while (L < 32 && avg >= 768.0 * L) L <<= 1;
+    // rows per lane per superblock.  The scan deals ROW GROUPS (32 rows) to its warps, not superblocks, so the
+    // depth no longer has to follow the partition size: the deepest one always wins (one drain unit per
+    // L * M / 16 units; a partition's last superblock may be mostly padding, which the scan never reads).
+    uint32_t L = 32;
     if (const char* el = getenv("LB200_SKEW_L")) {  // test hook: force the superblock depth
       int v = atoi(el);
       if (v >= 1 && v <= 256) L = (uint32_t)v;

@@ -502,17 +502,39 @@ extern "C" int32_t lb200_group_create(const int32_t* device_ids, uint32_t G, int
         if (part_owner_or_null[p] >= G) { delete g; return set_err(LB200_EINVAL, "partition %u assigned to shard %u >= G", p, part_owner_or_null[p]); }
         g->owner[p] = part_owner_or_null[p];
       }
-    } else {  // greedy bin-packing on row count, largest first; stable order -> deterministic
+    } else {
+      // greedy bin-packing, largest first, on rows x expected probes: in high dimension a few "hub"
+      // centroids are among the nprobes nearest of many more queries than the others, so equal rows are not
+      // equal scan work.  The probe frequency is estimated from the index alone -- how often a partition is among
+      // the max_nprobes nearest of the other centroids -- with the library's own find_partitions on an empty
+      // handle (same coarse metric as the searches).
+      std::vector<double> w(nlist, 1.0);
+      {
+        std::vector<uint64_t> zoffs(nlist + 1, 0);
+        lb200_index* tmp = nullptr;
+        const uint32_t Pw = std::min(std::max(max_nprobes, 1u), nlist);
+        int rc = lb200_index_create(device_ids[0], metric, dim, nlist, centroids, M, num_bits, codebook, zoffs.data(), nullptr,
+                                    nullptr, nullptr, &tmp);
+        if (!rc) {
+          std::vector<uint32_t> ids((size_t)nlist * Pw);
+          rc = lb200_find_partitions(tmp, centroids, nlist, Pw, ids.data(), nullptr);
+          if (!rc)
+            for (uint32_t id : ids) w[id] += 1.0;
+          lb200_index_destroy(tmp);
+        }
+        if (rc) { delete g; return rc; }
+      }
       std::vector<uint32_t> order(nlist);
-      for (uint32_t p = 0; p < nlist; p++) order[p] = p;
-      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
-        return part_offsets[a + 1] - part_offsets[a] > part_offsets[b + 1] - part_offsets[b];
-      });
-      std::vector<uint64_t> load(G, 0);
+      for (uint32_t p = 0; p < nlist; p++) {
+        order[p] = p;
+        w[p] *= (double)(part_offsets[p + 1] - part_offsets[p]);
+      }
+      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return w[a] > w[b]; });
+      std::vector<double> load(G, 0.0);
       for (uint32_t p : order) {
         uint32_t r = (uint32_t)(std::min_element(load.begin(), load.end()) - load.begin());
         g->owner[p] = r;
-        load[r] += part_offsets[p + 1] - part_offsets[p];
+        load[r] += w[p];
       }
     }
     std::vector<uint64_t> ptrs(2 * (size_t)G, 0);

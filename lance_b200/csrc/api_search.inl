@@ -95,6 +95,7 @@ struct ScanPlan {
 struct PrebuiltWork {
   ScanPlan plan;
   const uint32_t *d_pair_list, *d_pair_off, *d_item_off;
+  const uint4* d_item_desc;
   uint32_t* d_counter;  // zeroed
   uint64_t code_bytes, pairs;
   uint32_t items;
@@ -270,6 +271,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   add(npairs * 4);                  // rank
   add((size_t)(nlist + 1) * 4 * 2); // pair_off, item_off
   add(npairs * 4);                  // pair_list
+  add(nslots * 16);                 // item descriptors (items <= pairs * chunks)
   add(64);                          // counter + stats
   add(nslots * kprime * 4); add(nslots * kprime * 8); add(nslots * kprime * 8); add(nslots * 4);
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
@@ -315,6 +317,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   uint32_t* d_pair_off = cx.arena.take<uint32_t>(nlist + 1);
   uint32_t* d_item_off = cx.arena.take<uint32_t>(nlist + 1);
   uint32_t* d_pair_list = cx.arena.take<uint32_t>(npairs);
+  uint4* d_item_desc = cx.arena.take<uint4>(nslots);
   unsigned long long* d_stats = cx.arena.take<unsigned long long>(4);
   uint32_t* d_counter = reinterpret_cast<uint32_t*>(d_stats + 2);
   float* d_sdist = cx.arena.take<float>(nslots * kprime);
@@ -361,6 +364,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
     d_pair_off = const_cast<uint32_t*>(a.pw->d_pair_off);
     d_item_off = const_cast<uint32_t*>(a.pw->d_item_off);
     d_counter = a.pw->d_counter;
+    d_item_desc = const_cast<uint4*>(a.pw->d_item_desc);
     total_items_p = d_item_off + nlist;
   } else {
   CK(cudaMemsetAsync(d_cnt, 0, (size_t)nlist * 4 * 2, st));
@@ -375,6 +379,10 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
                                      d_pair_off, d_item_off, d_stats);
   scatter_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, d_rank, d_pair_off, d_cnt,
                                                                         (uint32_t)npairs, d_pair_list);
+  if (sc.variant == 3) {
+    expand_items_kernel<<<(nlist * 32 + 255) / 256, 256, 0, st>>>(d_item_off, ix->d_part_off, nlist, chunk_vecs, d_item_desc);
+    launches++;
+  }
   CK(cudaGetLastError());
   launches += 4;
   }
@@ -387,6 +395,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
     sp.residual = ix->metric != LB200_DOT;
     sp.queries = keys; sp.Q = Q; sp.P = P; sp.kprime = kprime;
     sp.pair_list = d_pair_list; sp.part_pair_off = d_pair_off; sp.item_off = d_item_off; sp.item_counter = d_counter;
+    sp.item_desc = d_item_desc;
     sp.chunk_vecs = chunk_vecs; sp.max_chunks = max_chunks; sp.capw = sc.capw;
     // merged searches share one running k'-th-best bound per query across all its partitions;
     // search_in_partition semantics (one full list per pair) must not.
@@ -436,10 +445,9 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
     // probes per query, or per-pair outputs (no cross-item bound at all)
     bool boot = a.shard_mode || a.per_pair_output || P < 16;
     if (const char* eb = getenv("LB200_BOOT")) boot = atoi(eb) != 0;
-    // pre-built tables are fetched by scan3_kernel only (scan3_nb_kernel stays the untouched text the
-    // headline was tuned on); without `boot` its bootstrap calls are switched off at run time
     if (!boot) sp.no_boot = 1;
-    CK(launch_scan3(sc, boot || use_pre, ix->sm_count, st, sp, total_items_p));
+    // wide CTAs (16 warps, pre-built tables) exist as the BOOT instantiation only; its calls are off via no_boot
+    CK(launch_scan3(sc, boot || sc.nw == 16, ix->sm_count, st, sp, total_items_p));
     launches++;
   } else {
   ScanParams sp = {};
@@ -742,7 +750,11 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
   auto put = [&](size_t b) { size_t o = in_bytes; in_bytes += Arena::pad(b); return o; };
   const size_t o_q = put(nq), o_p = put(np);
   size_t o_pl = 0, o_po = 0, o_io = 0, o_ctr = 0, o_tbl = 0, o_masks = 0, mask_words = 0;
-  if (small) { o_pl = put(np); o_po = put((size_t)(nlist + 1) * 4); o_io = put((size_t)(nlist + 1) * 4); o_ctr = put(16); }
+  size_t o_desc = 0;
+  if (small) {
+    o_pl = put(np); o_po = put((size_t)(nlist + 1) * 4); o_io = put((size_t)(nlist + 1) * 4); o_ctr = put(16);
+    o_desc = put(npairs * plan.max_chunks * 16);  // items <= pairs * chunks
+  }
   std::vector<uint32_t> mparts;  // probed partitions that carry a host mask
   if (host_masks) {
     for (size_t i = 0; i < npairs; i++)
@@ -779,14 +791,20 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
     uint32_t pacc = 0, iacc = 0;
     uint64_t bytes = 0;
     const uint32_t ql = (uint32_t)plan.sc.ql;
-    for (uint32_t p = 0; p < nlist; p++) {  // == offsets_kernel
+    uint32_t* desc = reinterpret_cast<uint32_t*>(hin + o_desc);
+    for (uint32_t p = 0; p < nlist; p++) {  // == offsets_kernel + expand_items_kernel
       const uint32_t c = po[p];
       const uint64_t n = ix->h_part_off[p + 1] - ix->h_part_off[p];
       po[p] = pacc;
       io[p] = iacc;
       if (c) {
+        const uint32_t nch = (uint32_t)((n + plan.chunk_vecs - 1) / plan.chunk_vecs), ni = ((c + ql - 1) / ql) * nch;
+        for (uint32_t local = 0; local < ni; local++) {
+          uint32_t* de = desc + (size_t)(iacc + local) * 4;
+          de[0] = p; de[1] = local / nch; de[2] = local % nch; de[3] = 0;
+        }
         pacc += c;
-        iacc += ((c + ql - 1) / ql) * (uint32_t)((n + plan.chunk_vecs - 1) / plan.chunk_vecs);
+        iacc += ni;
         bytes += (uint64_t)c * n * ix->M;
       }
     }
@@ -800,6 +818,7 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
     pw.d_pair_off = reinterpret_cast<uint32_t*>(dbase + o_po);
     pw.d_item_off = reinterpret_cast<uint32_t*>(dbase + o_io);
     pw.d_counter = reinterpret_cast<uint32_t*>(dbase + o_ctr);
+    pw.d_item_desc = reinterpret_cast<const uint4*>(dbase + o_desc);
     pw.code_bytes = bytes;
     pw.pairs = pacc;
     pw.items = iacc;

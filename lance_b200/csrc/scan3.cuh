@@ -51,6 +51,7 @@ struct Scan3Params {
   const uint32_t* part_pair_off;
   const uint32_t* item_off;
   uint32_t* item_counter;
+  const uint4* item_desc;         // [items] (partition, query group, chunk, 0), see expand_items_kernel
   uint32_t chunk_vecs;            // rows per chunk (multiple of 32*L)
   uint32_t max_chunks;
   uint32_t capw;                  // candidate buffer entries per (warp, query slot)
@@ -429,7 +430,7 @@ struct ItemCtx {
 // Shared-memory footprint of scan3_kernel (host + device agree through this one function).
 __host__ __device__ inline size_t scan3_smem_bytes(int QL, int NW, uint32_t M, uint32_t dim, uint32_t capw) {
   size_t lut = (size_t)(M / 16) * 256 * 64 * QL;
-  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32 + sizeof(ItemCtx) + 16;
+  return lut + (size_t)QL * dim * 4 + (size_t)QL * NW * capw * 8 + (size_t)QL * NW * 4 + (size_t)QL * 16 + 32 + sizeof(ItemCtx) + 16;  // 32: next item (16) + its descriptor (16)
 }
 
 // Publish a query's bound (one thread): into this GPU's table and -- partition shards on several
@@ -542,8 +543,11 @@ static __device__ __noinline__ void finalize_fn(const ItemCtx* c) {
   }
 }
 
-// BOOT: compile the pooled-bootstrap calls in (shards / few probes per query: most items are cold) or
-// leave the row loop exactly as the call-free single-GPU version (r01 bisect: the calls cost ~4% there).
+// One kernel, two instantiations per shape.  BOOT = true compiles the pooled-bootstrap calls in (shards, few
+// probes per query, per-pair outputs: most work items are cold) and keeps the end-of-item code out of line;
+// BOOT = false is the call-free text for batches whose items are mostly warm (merged search, nprobes >= 16):
+// no ItemCtx, end-of-item code inline.  (r01 kept two verbatim copies of this function because the row loop is
+// sensitive to what else lives in it; `if constexpr` gives the same two texts from one source.)
 template <int QL, int D, int NW, int MINB, int DSUB, bool BOOT>
 __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params p,
                                                               const uint32_t* __restrict__ total_items_p) {
@@ -561,8 +565,9 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   uint32_t* sthr = reinterpret_cast<uint32_t*>(sthrf + QL);
   uint32_t* spair = sthr + QL;
   uint32_t* sqidx = spair + QL;
-  uint32_t* sitem = sqidx + QL;
-  ItemCtx* ictx = reinterpret_cast<ItemCtx*>(sitem + 4);  // 16-byte aligned
+  uint32_t* sitem = sqidx + QL;                            // [0]: the item to run next
+  uint4* sdesc = reinterpret_cast<uint4*>(sitem + 4);      // its descriptor (partition, query group, chunk)
+  ItemCtx* ictx = reinterpret_cast<ItemCtx*>(sitem + 8);   // 16-byte aligned
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -595,23 +600,26 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     asm volatile("" : "+f"(swf[j]));
   }
 
+  // Work items come from a device queue.  Taking one costs an atomic and a descriptor load, ~2 us of latency
+  // that r02's ncu put at 9.5 % of the warp time when it sat between items (atomicAdd -> barrier -> binary
+  // search over item_off).  Now the NEXT item is taken while the current one runs: the atomic is issued at the
+  // top of an item and its result is first used after the table build; the descriptor then travels global ->
+  // shared with cp.async during the row scan.
+  if (tid == 0) {
+    const uint32_t it = atomicAdd(p.item_counter, 1u);
+    sitem[0] = it;
+    if (it < total_items) *sdesc = p.item_desc[it];
+  }
   for (;;) {
     __syncthreads();
-    if (tid == 0) *sitem = atomicAdd(p.item_counter, 1u);
-    __syncthreads();
-    const uint32_t item = *sitem;
+    const uint32_t item = sitem[0];
     if (item >= total_items) break;
-    uint32_t lo = 0, hi = p.nlist;
-    while (hi - lo > 1) {
-      uint32_t mid = (lo + hi) >> 1;
-      if (p.item_off[mid] <= item) lo = mid; else hi = mid;
-    }
-    const uint32_t part = lo;
+    const uint4 de = *sdesc;
+    uint32_t nxt = 0;
+    if (tid == 0) nxt = atomicAdd(p.item_counter, 1u);
+    const uint32_t part = de.x, g = de.y, c = de.z;
     const uint64_t row_base = p.part_off[part];
     const uint32_t n_p = (uint32_t)(p.part_off[part + 1] - row_base);
-    const uint32_t nch = (n_p + p.chunk_vecs - 1) / p.chunk_vecs;
-    const uint32_t local = item - p.item_off[part];
-    const uint32_t g = local / nch, c = local % nch;
     const uint32_t pbase = p.part_pair_off[part] + g * QL;
     const uint32_t nq = min((uint32_t)QL, p.part_pair_off[part + 1] - pbase);
     const uint64_t* prow = p.row_ids + row_base;
@@ -631,7 +639,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       mycold = tid < nq && t0 == KEY_PINF;
     }
     if (tid < NW * QL) ccnt[tid] = 0;
-    if (tid == 0) {
+    if (BOOT && tid == 0) {
       ItemCtx ic;
       ic.ckey = ckey; ic.cpos = cpos; ic.ccnt = ccnt; ic.sthr = sthr; ic.sqidx = sqidx; ic.spair = spair;
       ic.qthr = p.qthr; ic.peers = p.peers; ic.n_peers = p.n_peers; ic.sthrf = sthrf; ic.prow = prow; ic.bm = bm;
@@ -652,7 +660,9 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       }
       resid[i] = val;
     }
-    const bool cold_item = __syncthreads_or(mycold) != 0;  // some query of the item has no bound yet
+    bool cold_item = false;
+    if (BOOT) cold_item = __syncthreads_or(mycold) != 0;  // some query of the item has no bound yet
+    else __syncthreads();
 
     // ---- A4: ADC tables, interleaved over the QL queries --------------------------------
     // thread -> (slot = tid%16, code = tid/16 + k*NT/16): a quarter/half warp writes consecutive
@@ -702,26 +712,45 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     }
     // exact-FMA switch only if no partial sum of <=256 entries can overflow: |T| < 2^118
     const bool unsafe = __syncthreads_or(maxbits >= 0x7a800000u) != 0;
+    if (tid == 0) {  // everyone has read sitem / sdesc (two barriers ago): hand over the next item
+      sitem[0] = nxt;
+      if (nxt < total_items)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sdesc)),
+                     "l"(p.item_desc + nxt) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
 
-    // ---- A5 + A6: scan the chunk's superblocks ---------------------------------------------
+    // ---- A5 + A6: scan the chunk's rows -----------------------------------------------------
     const uint32_t v0 = c * p.chunk_vecs;
     const uint32_t vend = min(n_p, v0 + p.chunk_vecs);
-    const uint32_t sb_lo = v0 / (32 * L), sb_hi = (vend + 32 * L - 1) / (32 * L);
+    const uint32_t sb_lo = v0 / (32 * L);
     const float lower = p.lower, upper = p.upper;
     const bool has_lower = p.has_lower != 0, has_upper = p.has_upper != 0;
     const uint8_t* cbase = p.codes + (size_t)p.sb_off[part] * units * 512 + lane * 16;
 
     // Pooled bootstrap of a cold item (some query has no bound yet): the candidates the NW warps
     // buffered in their first rows are pooled and pruned once (#1 after ~96 rows per warp, #2 at the
-    // end of each warp's first superblock).  The calls sit BETWEEN segments of the row loop, never
+    // end of each warp's first slice).  The calls sit BETWEEN segments of the row loop, never
     // inside it: the loop body must stay free of calls and of inlined cold code (r01 bisect: either
     // costs the scan ~10% through register pressure / instruction-cache misses).
     const bool cold = BOOT && cold_item && !p.no_boot;
-    bool need1 = cold, need2 = cold && L > 3 && p.boot2 != 0;
-    const uint32_t boot_i = min(L, 3u);
+    bool need1 = cold, need2 = cold && p.boot2 != 0;
+    const uint32_t boot_i = 3u;
+    // The chunk's rows are dealt to the NW warps in row groups (32 rows = one row per lane) so that all warps
+    // finish an item together: whole superblocks per warp left 15 % of the warp time in the end-of-item barrier
+    // (r01 ncu: ceil(nsb / NW) rounds for nsb ~ 24 superblocks).  A warp's share [rg, rg_end) is cut into slices
+    // (sb, rows i0..i1 of each lane) at superblock borders.  A slice may start and end mid-stream: its first
+    // switch output (the tail of row i0-1) is dropped, and the tail of its last row is read from the first D
+    // bytes of the NEXT unit -- row i1's first unit, or the superblock's drain unit when i1 == L.
+    const uint32_t Tv = (vend - v0 + 31) / 32;
+    uint32_t rg = (uint32_t)(((uint64_t)Tv * w) / NW);
+    const uint32_t rg_end = (uint32_t)(((uint64_t)Tv * (w + 1)) / NW);
 #pragma unroll 1
-    for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
-      const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
+    while (rg < rg_end) {
+      const uint32_t sbr = rg / L, i0 = rg - sbr * L, i1 = min(L, i0 + (rg_end - rg));
+      const uint32_t sb = sb_lo + sbr;
+      rg += i1 - i0;
+      const uint4* up = reinterpret_cast<const uint4*>(cbase + ((size_t)sb * units + (size_t)i0 * C16) * 512);
       uint4 cur = __ldg(up), n1 = __ldg(up + 32);
       const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
       float acc[QL], done[QL];
@@ -739,15 +768,15 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         }
         __syncwarp();
       }
-      uint32_t i = 0;
-      uint32_t stop = (BOOT && need1) ? boot_i + 1 : L + 1;
+      uint32_t i = i0;
+      uint32_t stop = (BOOT && need1) ? min(i1, i0 + boot_i) + 1 : i1 + 1;
 #pragma unroll 1
       for (;;) {
 #pragma unroll 1
       for (; i < stop; i++) {
         const uint4 n2 = __ldg(pf);
         pf += 32;
-        if (i < L) {
+        if (i < i1) {
           if (unsafe) scan_unit<QL, D, true, true, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
           else scan_unit<QL, D, true, false, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
         } else {
@@ -755,7 +784,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
         }
         cur = n1; n1 = n2;
-        if (i >= 1) {
+        if (i > i0) {
           // `done` = distance of row i-1 of this lane.  Fast test: running threshold only; bounds,
           // tail rows and the prefilter are applied on the (rare) slow path.
           float thr[QL];
@@ -789,7 +818,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
             }
           }
         }
-        if (i == L) continue;  // drain iteration: no further units (and the last of the loop)
+        if (i == i1) continue;  // drain iteration: no further units (and the last of the loop)
 #pragma unroll 1
         for (uint32_t u = 1; u < C16; u++) {
           const uint4 n3 = __ldg(pf);
@@ -801,291 +830,58 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         if (BOOT && need1) {
           bootstrap_fn(ictx);
           need1 = false;
-          stop = L + 1;
+          stop = i1 + 1;
         }
-        if (!BOOT || i > L) break;
+        if (!BOOT || i > i1) break;
       }
       if (BOOT && need2) {
         bootstrap_fn(ictx);
         need2 = false;
       }
     }
-    if (BOOT && need1) bootstrap_fn(ictx);  // warps that drew no superblock still owe the barriers
+    if (BOOT && need1) bootstrap_fn(ictx);  // warps that drew no rows still owe the barriers
     if (BOOT && need2) bootstrap_fn(ictx);
+    if (tid == 0) asm volatile("cp.async.wait_group 0;" ::: "memory");  // the next item's descriptor has landed
     __syncthreads();
 
-    finalize_fn(ictx);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// The same kernel WITHOUT the pooled bootstrap and with the end-of-item code inlined: the text the
-// single-GPU headline configuration was tuned on.  Kept verbatim because the scan is sensitive to
-// what else lives in the function (r01 same-box bisect: 25.1 ms here vs 26.0 ms for the BOOT=false
-// instantiation of the kernel above, cfg 4); the host picks it whenever most work items are warm.
-template <int QL, int D, int NW, int MINB, int DSUB>
-__global__ void __launch_bounds__(NW * 32, MINB) scan3_nb_kernel(const Scan3Params p,
-                                                              const uint32_t* __restrict__ total_items_p) {
-  constexpr int NT = NW * 32;
-  constexpr uint32_t CB = 256u * 64u * QL;  // bytes per table chunk (16 sub-vectors)
-  constexpr uint32_t SLOTB = 4u * QL;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  unsigned char* lut = smem_raw;
-  const uint32_t C16 = p.M >> 4;
-  float* resid = reinterpret_cast<float*>(smem_raw + (size_t)C16 * CB);
-  uint32_t* ckey = reinterpret_cast<uint32_t*>(resid + QL * p.dim);
-  uint32_t* cpos = ckey + (size_t)QL * NW * p.capw;
-  uint32_t* ccnt = cpos + (size_t)QL * NW * p.capw;
-  float* sthrf = reinterpret_cast<float*>(ccnt + QL * NW);  // 16-byte aligned (all sizes are multiples of 16)
-  uint32_t* sthr = reinterpret_cast<uint32_t*>(sthrf + QL);
-  uint32_t* spair = sthr + QL;
-  uint32_t* sqidx = spair + QL;
-  uint32_t* sitem = sqidx + QL;
-  const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
-
-  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const uint32_t d = lane % D;
-  const uint32_t M = p.M, dsub = p.dsub, dim = p.dim, kprime = p.kprime, capw = p.capw, L = p.L;
-  const uint32_t units = L * C16 + 1;
-  const uint32_t total_items = *total_items_p;
-
-  // per-lane table offsets for static step j (see header): slot = (j-d) mod 16;
-  //   Bp[j]: relative to chunk (u-1): + CB when the lane is already on chunk u (j >= d)
-  //   B0[j]: unit 0 of a row, relative to the table start: lanes with j < d are on the LAST chunk
-  uint32_t Bp[16], B0[D];
-  float keepf[D], swf[D];
-#pragma unroll
-  for (int j = 0; j < 16; j++) Bp[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? CB : 0u);
-#pragma unroll
-  for (int j = 0; j < D; j++) {
-    B0[j] = (((uint32_t)j - d) & 15u) * SLOTB + ((uint32_t)j >= d ? 0u : (C16 - 1) * CB);
-    keepf[j] = d == (uint32_t)j ? 0.0f : 1.0f;
-    swf[j] = d == (uint32_t)j ? 1.0f : 0.0f;
-  }
-  // Keep these per-lane constants in registers: left alone, ptxas rematerialises them inside the
-  // hot loop (ISETP+FSEL per switch step; r01 profile) which costs more issue slots than the FMAs.
-#pragma unroll
-  for (int j = 0; j < 16; j++) asm volatile("" : "+r"(Bp[j]));
-#pragma unroll
-  for (int j = 0; j < D; j++) {
-    asm volatile("" : "+r"(B0[j]));
-    asm volatile("" : "+f"(keepf[j]));
-    asm volatile("" : "+f"(swf[j]));
-  }
-
-  for (;;) {
-    __syncthreads();
-    if (tid == 0) *sitem = atomicAdd(p.item_counter, 1u);
-    __syncthreads();
-    const uint32_t item = *sitem;
-    if (item >= total_items) break;
-    uint32_t lo = 0, hi = p.nlist;
-    while (hi - lo > 1) {
-      uint32_t mid = (lo + hi) >> 1;
-      if (p.item_off[mid] <= item) lo = mid; else hi = mid;
-    }
-    const uint32_t part = lo;
-    const uint64_t row_base = p.part_off[part];
-    const uint32_t n_p = (uint32_t)(p.part_off[part + 1] - row_base);
-    const uint32_t nch = (n_p + p.chunk_vecs - 1) / p.chunk_vecs;
-    const uint32_t local = item - p.item_off[part];
-    const uint32_t g = local / nch, c = local % nch;
-    const uint32_t pbase = p.part_pair_off[part] + g * QL;
-    const uint32_t nq = min((uint32_t)QL, p.part_pair_off[part + 1] - pbase);
-    const uint64_t* prow = p.row_ids + row_base;
-    const uint64_t* bm = p.bitmask ? p.bitmask[part] : nullptr;
-
-    if (tid < QL) {
-      uint32_t pr = tid < nq ? p.pair_list[pbase + tid] : 0xffffffffu;
-      spair[tid] = pr;
-      const uint32_t qi = tid < nq ? pr / p.P : 0u;
-      sqidx[tid] = qi;
-      uint32_t t0 = KEY_PINF;
-      if (p.qthr && tid < nq) t0 = __ldcg(p.qthr + qi);
-      sthr[tid] = t0;
-      // unused query slots never pass the fast test
-      sthrf[tid] = tid < nq ? key_to_float(t0) : __int_as_float(0xff800000);
-    }
-    if (tid < NW * QL) ccnt[tid] = 0;
-    for (uint32_t i = tid; i < QL * dim; i += NT) {
-      uint32_t qq = i / dim, e = i - qq * dim;
-      float val = 0.0f;
-      if (qq < nq) {
-        uint32_t qidx = p.pair_list[pbase + qq] / p.P;
-        float x = p.queries[(size_t)qidx * dim + e];
-        val = p.residual ? __fsub_rn(x, p.centroids[(size_t)part * dim + e]) : x;
-      }
-      resid[i] = val;
-    }
-    __syncthreads();
-
-    // ---- A4: ADC tables, interleaved over the QL queries --------------------------------
-    // thread -> (slot = tid%16, code = tid/16 + k*NT/16): a quarter/half warp writes consecutive
-    // slots of one code row -> conflict-free wide stores.
-    uint32_t maxbits = 0;
-    {
-      const uint32_t slot = tid & 15;
+    if constexpr (BOOT) {
+      finalize_fn(ictx);
+    } else {
+      // ---- end of item, inline: one warp per query gathers the warps' buffers, selects k', emits sorted ----
 #pragma unroll 1
-      for (uint32_t ch = 0; ch < C16; ch++) {
-        const uint32_t m = ch * 16 + slot;
-        float xr[QL][DSUB > 0 ? DSUB : 1];
-        if (DSUB > 0) {
-#pragma unroll
-          for (int q = 0; q < QL; q++)
-#pragma unroll
-            for (int i = 0; i < DSUB; i++) xr[q][i] = resid[q * dim + m * DSUB + i];
-        }
+      for (uint32_t qq = w; qq < nq; qq += NW) {
+        uint32_t* dk = ckey + (size_t)qq * NW * capw;
+        uint32_t* dp = cpos + (size_t)qq * NW * capw;
+        uint32_t n = ccnt[qq * NW];
 #pragma unroll 1
-        for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
-          const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
-          float yr[DSUB > 0 ? DSUB : 1];
-          if (DSUB > 0) {
-#pragma unroll
-            for (int i = 0; i < DSUB / 4; i++) {
-              float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
-              yr[4 * i] = v4.x; yr[4 * i + 1] = v4.y; yr[4 * i + 2] = v4.z; yr[4 * i + 3] = v4.w;
-            }
+        for (uint32_t w2 = 1; w2 < NW; w2++) {
+          const uint32_t n2 = ccnt[qq * NW + w2];
+          const uint32_t* sk = dk + (size_t)w2 * capw;
+          const uint32_t* sp = dp + (size_t)w2 * capw;
+          for (uint32_t j0 = 0; j0 < n2; j0 += 32) {
+            uint32_t j = j0 + lane, kk = 0, pp = 0;
+            if (j < n2) { kk = sk[j]; pp = sp[j]; }
+            __syncwarp();
+            if (j < n2) { dk[n + j] = kk; dp[n + j] = pp; }
+            __syncwarp();
           }
-          float val[QL];
-#pragma unroll
-          for (int q = 0; q < QL; q++) {
-            if (DSUB > 0)
-              val[q] = lut_elem<DSUB>(p.residual != 0, xr[q], yr, dsub);
-            else
-              val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub, y, dsub);
-            maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
-          }
-          unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
-          if (QL == 4)
-            *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
-          else
-            *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
+          n += n2;
         }
+        if (n > kprime) {
+          uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
+          n = kprime;
+          if (p.qthr && lane == 0) atomicMin(p.qthr + sqidx[qq], T);
+        } else if (n == kprime && p.qthr) {
+          uint32_t mx = 0;
+          for (uint32_t j = lane; j < n; j += 32) mx = max(mx, dk[j]);
+          mx = __reduce_max_sync(FULL, mx);
+          if (lane == 0) atomicMin(p.qthr + sqidx[qq], mx);
+        }
+        const size_t slot = (size_t)spair[qq] * p.max_chunks + c;
+        warp_sort_emit(dk, dp, n, prow, row_base, p.out_dist + slot * kprime, p.out_pos + slot * kprime,
+                       p.out_rowid + slot * kprime);
+        if (lane == 0) p.out_count[slot] = n;
       }
-    }
-    // exact-FMA switch only if no partial sum of <=256 entries can overflow: |T| < 2^118
-    const bool unsafe = __syncthreads_or(maxbits >= 0x7a800000u) != 0;
-
-    // ---- A5 + A6: scan the chunk's superblocks ---------------------------------------------
-    const uint32_t v0 = c * p.chunk_vecs;
-    const uint32_t vend = min(n_p, v0 + p.chunk_vecs);
-    const uint32_t sb_lo = v0 / (32 * L), sb_hi = (vend + 32 * L - 1) / (32 * L);
-    const float lower = p.lower, upper = p.upper;
-    const bool has_lower = p.has_lower != 0, has_upper = p.has_upper != 0;
-    const uint8_t* cbase = p.codes + (size_t)p.sb_off[part] * units * 512 + lane * 16;
-
-#pragma unroll 1
-    for (uint32_t sb = sb_lo + w; sb < sb_hi; sb += NW) {
-      const uint4* up = reinterpret_cast<const uint4*>(cbase + (size_t)sb * units * 512);
-      uint4 cur = __ldg(up), n1 = __ldg(up + 32);
-      const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
-      float acc[QL], done[QL];
-#pragma unroll
-      for (int q = 0; q < QL; q++) acc[q] = done[q] = 0.0f;
-      const uint32_t row0 = sb * 32 * L + lane;
-      // pick up bounds found meanwhile by other work items of the same queries
-      if (p.qthr) {
-        if (lane < nq) {
-          uint32_t t = __ldcg(p.qthr + sqidx[lane]);
-          if (t < sthr[lane]) {
-            uint32_t old = atomicMin(sthr + lane, t);
-            sthrf[lane] = key_to_float(min(old, t));
-          }
-        }
-        __syncwarp();
-      }
-#pragma unroll 1
-      for (uint32_t i = 0; i <= L; i++) {
-        const uint4 n2 = __ldg(pf);
-        pf += 32;
-        if (i < L) {
-          if (unsafe) scan_unit<QL, D, true, true, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
-          else scan_unit<QL, D, true, false, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
-        } else {
-          if (unsafe) scan_unit<QL, D, true, true, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
-          else scan_unit<QL, D, true, false, D>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
-        }
-        cur = n1; n1 = n2;
-        if (i >= 1) {
-          // `done` = distance of row i-1 of this lane.  Fast test: running threshold only; bounds,
-          // tail rows and the prefilter are applied on the (rare) slow path.
-          float thr[QL];
-          lds_volatile<QL>(sthrf_saddr, thr);
-          bool anyp = done[0] <= thr[0];
-#pragma unroll
-          for (int q = 1; q < QL; q++) anyp = anyp || (done[q] <= thr[q]);
-          if (__any_sync(FULL, anyp)) {
-            const uint32_t r = row0 + (i - 1) * 32;
-            uint32_t pm = 0;
-#pragma unroll
-            for (int q = 0; q < QL; q++) {
-              bool ok = done[q] <= thr[q];
-              if (has_lower) ok = ok && (lower <= done[q]);
-              if (has_upper) ok = ok && (done[q] < upper);
-              pm |= ok ? (1u << q) : 0u;
-            }
-            if (r >= vend) pm = 0;
-            pm &= (1u << nq) - 1u;
-            if (bm && pm) {
-              if (!((bm[r >> 6] >> (r & 63)) & 1ull)) pm = 0;
-            }
-            if (__any_sync(FULL, pm != 0)) {
-#pragma unroll
-              for (int q = 0; q < QL; q++) {
-                const uint32_t b = (uint32_t)q * NW + w;
-                append_rows((pm >> q) & 1u, done[q], r, lane, capw, kprime, ckey + (size_t)b * capw,
-                            cpos + (size_t)b * capw, ccnt + b, sthr + q, sthrf + q,
-                            (p.qthr && (uint32_t)q < nq) ? p.qthr + sqidx[q] : nullptr, prow);
-              }
-            }
-          }
-        }
-        if (i == L) break;
-#pragma unroll 1
-        for (uint32_t u = 1; u < C16; u++) {
-          const uint4 n3 = __ldg(pf);
-          pf += 32;
-          scan_unit<QL, D, false, true, 16>(cur, lut + (size_t)(u - 1) * CB, Bp, B0, keepf, swf, d, acc, done);
-          cur = n1; n1 = n3;
-        }
-      }
-    }
-    __syncthreads();
-
-    // ---- finalize: one warp per query: gather the warps' buffers, select k', sorted emit ----
-#pragma unroll 1
-    for (uint32_t qq = w; qq < nq; qq += NW) {
-      uint32_t* dk = ckey + (size_t)qq * NW * capw;
-      uint32_t* dp = cpos + (size_t)qq * NW * capw;
-      uint32_t n = ccnt[qq * NW];
-#pragma unroll 1
-      for (uint32_t w2 = 1; w2 < NW; w2++) {
-        const uint32_t n2 = ccnt[qq * NW + w2];
-        const uint32_t* sk = dk + (size_t)w2 * capw;
-        const uint32_t* sp = dp + (size_t)w2 * capw;
-        for (uint32_t i0 = 0; i0 < n2; i0 += 32) {
-          uint32_t i = i0 + lane, kk = 0, pp = 0;
-          if (i < n2) { kk = sk[i]; pp = sp[i]; }
-          __syncwarp();
-          if (i < n2) { dk[n + i] = kk; dp[n + i] = pp; }
-          __syncwarp();
-        }
-        n += n2;
-      }
-      if (n > kprime) {
-        uint32_t T = warp_select_k(dk, dp, n, kprime, prow);
-        n = kprime;
-        if (p.qthr && lane == 0) atomicMin(p.qthr + sqidx[qq], T);
-      } else if (n == kprime && p.qthr) {
-        uint32_t mx = 0;
-        for (uint32_t i = lane; i < n; i += 32) mx = max(mx, dk[i]);
-        mx = __reduce_max_sync(FULL, mx);
-        if (lane == 0) atomicMin(p.qthr + sqidx[qq], mx);
-      }
-      const size_t slot = (size_t)spair[qq] * p.max_chunks + c;
-      warp_sort_emit(dk, dp, n, prow, row_base, p.out_dist + slot * kprime, p.out_pos + slot * kprime,
-                     p.out_rowid + slot * kprime);
-      if (lane == 0) p.out_count[slot] = n;
     }
   }
 }

@@ -1,12 +1,11 @@
-// scan3_tu.cu -- instantiations + launchers of scan3_kernel / scan3_nb_kernel (variant 3).
+// scan3_tu.cu -- instantiations + launchers of scan3_kernel (variant 3).
 #include "launch.h"
 
 namespace lb200 {
 
 template <int QL, int D, int NW, int MINB, int DS, bool BOOT>
 static auto scan3_entry() {
-  if constexpr (BOOT) return scan3_kernel<QL, D, NW, MINB, DS, true>;
-  else return scan3_nb_kernel<QL, D, NW, MINB, DS>;
+  return scan3_kernel<QL, D, NW, MINB, DS, BOOT>;
 }
 
 template <int QL, int D, int MINB, bool BOOT, int NW = SCAN_NW>

@@ -158,6 +158,23 @@ offsets_kernel(const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cn
   }
 }
 
+// Step 2b: one descriptor per work item -- (partition, query group, chunk) -- so that the scan kernel takes an
+// item with ONE load (prefetched while the previous item runs) instead of a binary search over item_off.
+// One warp per partition.
+__global__ void expand_items_kernel(const uint32_t* __restrict__ item_off, const uint64_t* __restrict__ part_off,
+                                    uint32_t nlist, uint32_t chunk_vecs, uint4* __restrict__ desc) {
+  const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (p >= nlist) return;
+  const uint32_t i0 = item_off[p], i1 = item_off[p + 1];
+  if (i1 == i0) return;
+  const uint64_t n = part_off[p + 1] - part_off[p];
+  const uint32_t nch = (uint32_t)((n + chunk_vecs - 1) / chunk_vecs);
+  for (uint32_t it = i0 + lane; it < i1; it += 32) {
+    const uint32_t local = it - i0;
+    desc[it] = make_uint4(p, local / nch, local % nch, 0u);
+  }
+}
+
 // Step 3: scatter pair ids into partition-grouped order, cold pairs first.
 __global__ void scatter_pairs_kernel(const uint32_t* __restrict__ probes, const uint32_t* __restrict__ rank,
                                      const uint32_t* __restrict__ pair_off, const uint32_t* __restrict__ cnt_cold,

@@ -21,25 +21,48 @@ liblance_b200.so.
 import numpy as np
 
 
-def assign_partitions(sizes, world):
-    """Greedy bin-packing (largest first) of partitions onto ranks by row count, so the code
-    bytes per GPU are balanced.  Deterministic: every rank computes the same owner map."""
+def assign_partitions(sizes, world, weights=None):
+    """Greedy bin-packing (largest first) of partitions onto ranks.  Deterministic: every rank computes the same
+    owner map.  By default the balanced quantity is the row count (code bytes per GPU); with `weights` (e.g.
+    probe_load_weights) it is rows x expected probes, i.e. the SCAN work per GPU -- in high dimension a few
+    "hub" centroids are among the nprobes nearest of many more queries than the others (cfg 4: probes per
+    partition have std = mean), so equal bytes are not equal work (r02: 6.9 % extra on the busiest of 8 shards)."""
     sizes = np.asarray(sizes, dtype=np.int64)
-    order = np.argsort(-sizes, kind="stable")
-    load = np.zeros(world, dtype=np.int64)
+    w = sizes.astype(np.float64) if weights is None else sizes.astype(np.float64) * np.asarray(weights, dtype=np.float64)
+    order = np.argsort(-w, kind="stable")
+    load = np.zeros(world, dtype=np.float64)
     owner = np.zeros(len(sizes), dtype=np.int64)
     for p in order:
         r = int(np.argmin(load))
         owner[p] = r
-        load[r] += sizes[p]
+        load[r] += w[p]
     return owner
 
 
-def shard_of(data, rank, world):
+def probe_load_weights(centroids, metric, nprobes, chunk=1024):
+    """Expected probe frequency of every partition, estimated from the index alone: how often a partition is among
+    the `nprobes` nearest of the OTHER centroids (queries follow the data, the data follows the centroids).  Uses the
+    coarse metric of find_partitions (dot -> largest inner product, else L2; a cosine index holds normalised
+    centroids).  +1 so that no partition weighs nothing."""
+    c = np.ascontiguousarray(centroids, dtype=np.float32)
+    nlist = c.shape[0]
+    P = min(int(nprobes), nlist)
+    counts = np.zeros(nlist, dtype=np.int64)
+    c2 = (c * c).sum(1)
+    for s in range(0, nlist, chunk):
+        x = c[s:s + chunk]
+        score = -(x @ c.T) if metric == "dot" else c2[None, :] - 2.0 * (x @ c.T)
+        idx = np.argpartition(score, P - 1, axis=1)[:, :P] if P < nlist else np.tile(np.arange(nlist), (len(x), 1))
+        counts += np.bincount(idx.ravel(), minlength=nlist)
+    return counts.astype(np.float64) + 1.0
+
+
+def shard_of(data, rank, world, nprobes=None):
     """The IvfPqData shard of `rank`: all nlist partitions, the ones it does not own empty;
-    centroids and codebook replicated."""
+    centroids and codebook replicated.  nprobes: balance scan work (rows x expected probes) instead of rows."""
     sizes = np.diff(data.part_offsets.astype(np.int64))
-    owner = assign_partitions(sizes, world)
+    weights = None if nprobes is None else probe_load_weights(data.centroids, data.metric, nprobes)
+    owner = assign_partitions(sizes, world, weights)
     return data.subset(np.nonzero(owner == rank)[0]), owner
 
 
