@@ -30,6 +30,13 @@
 #pragma once
 #include "scan.cuh"
 
+#ifndef LB200_OPT_TABLE
+#define LB200_OPT_TABLE 1
+#endif
+#ifndef LB200_CODE_LOAD
+#define LB200_CODE_LOAD 0
+#endif
+
 namespace lb200 {
 
 struct Scan3Params {
@@ -257,6 +264,22 @@ static __device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const floa
   const uint32_t mb = lut_max[unit];
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   return mb;
+}
+
+// One 16-byte unit of a lane's code stream.  The stream is read exactly once per work item by this CTA
+// (other CTAs scanning the same partition find it in L2), so it need not be kept in L1.
+__device__ __forceinline__ uint4 load_codes(const uint4* p) {
+#if LB200_CODE_LOAD == 1
+  return __ldcg(p);
+#elif LB200_CODE_LOAD == 2
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+#elif LB200_CODE_LOAD == 3
+  return __ldcs(p);
+#else
+  return __ldg(p);
+#endif
 }
 
 template <int QL>
@@ -682,6 +705,14 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
 #pragma unroll
             for (int i = 0; i < DSUB; i++) xr[q][i] = resid[q * dim + m * DSUB + i];
         }
+        // the codebook rows come from L2 (128 KB+ per item, more than L1 keeps): the next row is loaded while the
+        // current one is worked on (r02 ncu: 5.6 % of the kernel's warp time sat on the first use of this load)
+        float4 nx[DSUB > 0 ? DSUB / 4 : 1];
+        if (DSUB > 0) {
+#pragma unroll
+          for (int i = 0; i < DSUB / 4; i++)
+            nx[i] = __ldg(reinterpret_cast<const float4*>(p.codebook + ((size_t)m * 256 + (tid >> 4)) * DSUB) + i);
+        }
 #pragma unroll 1
         for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
           const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
@@ -689,11 +720,28 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
           if (DSUB > 0) {
 #pragma unroll
             for (int i = 0; i < DSUB / 4; i++) {
-              float4 v4 = __ldg(reinterpret_cast<const float4*>(y) + i);
-              yr[4 * i] = v4.x; yr[4 * i + 1] = v4.y; yr[4 * i + 2] = v4.z; yr[4 * i + 3] = v4.w;
+              yr[4 * i] = nx[i].x; yr[4 * i + 1] = nx[i].y; yr[4 * i + 2] = nx[i].z; yr[4 * i + 3] = nx[i].w;
+            }
+            if (code + NT / 16 < 256) {
+#pragma unroll
+              for (int i = 0; i < DSUB / 4; i++)
+                nx[i] = __ldg(reinterpret_cast<const float4*>(y + (size_t)(NT / 16) * DSUB) + i);
             }
           }
           float val[QL];
+          if (LB200_OPT_TABLE && DSUB > 0 && p.residual) {  // l2_once on packed pairs: FADD2 / FMUL2, bit-identical per half
+            f32x2_t Y[DSUB > 0 ? DSUB / 2 : 1];
+#pragma unroll
+            for (int i = 0; i < DSUB / 2; i++) Y[i] = pk2(yr[2 * i], yr[2 * i + 1]);
+#pragma unroll
+            for (int q = 0; q < QL; q++) {
+              f32x2_t X[DSUB > 0 ? DSUB / 2 : 1];
+#pragma unroll
+              for (int i = 0; i < DSUB / 2; i++) X[i] = pk2(xr[q][2 * i], xr[q][2 * i + 1]);
+              val[q] = l2_once_packed<(DSUB > 0 ? DSUB : 8)>(X, Y);
+              maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
+            }
+          } else {
 #pragma unroll
           for (int q = 0; q < QL; q++) {
             if (DSUB > 0)
@@ -701,6 +749,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
             else
               val[q] = lut_elem<0>(p.residual != 0, resid + q * dim + m * dsub, y, dsub);
             maxbits = max(maxbits, __float_as_uint(val[q]) & 0x7fffffffu);
+          }
           }
           unsigned char* dst = lut + (size_t)ch * CB + code * (64 * QL) + slot * SLOTB;
           if (QL == 4)
@@ -751,7 +800,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       const uint32_t sb = sb_lo + sbr;
       rg += i1 - i0;
       const uint4* up = reinterpret_cast<const uint4*>(cbase + ((size_t)sb * units + (size_t)i0 * C16) * 512);
-      uint4 cur = __ldg(up), n1 = __ldg(up + 32);
+      uint4 cur = load_codes(up), n1 = load_codes(up + 32);
       const uint4* pf = up + 64;  // prefetch pointer, 2 units ahead (the buffer is padded by 2 units)
       float acc[QL], done[QL];
 #pragma unroll
@@ -774,7 +823,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       for (;;) {
 #pragma unroll 1
       for (; i < stop; i++) {
-        const uint4 n2 = __ldg(pf);
+        const uint4 n2 = load_codes(pf);
         pf += 32;
         if (i < i1) {
           if (unsafe) scan_unit<QL, D, true, true, 16>(cur, lut - CB, Bp, B0, keepf, swf, d, acc, done);
@@ -821,7 +870,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         if (i == i1) continue;  // drain iteration: no further units (and the last of the loop)
 #pragma unroll 1
         for (uint32_t u = 1; u < C16; u++) {
-          const uint4 n3 = __ldg(pf);
+          const uint4 n3 = load_codes(pf);
           pf += 32;
           scan_unit<QL, D, false, true, 16>(cur, lut + (size_t)(u - 1) * CB, Bp, B0, keepf, swf, d, acc, done);
           cur = n1; n1 = n3;

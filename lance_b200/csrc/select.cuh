@@ -7,6 +7,7 @@
 #pragma once
 #include "dist.cuh"
 
+
 namespace lb200 {
 
 constexpr uint32_t FULL = 0xffffffffu;
