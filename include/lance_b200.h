@@ -79,7 +79,7 @@ void lb200_index_destroy(lb200_index* ix);
  * (rust/lance/src/index.rs:169-181,774-786, rust/lance/src/index/vector.rs:446-513,
  * rust/lance/src/index/vector/pq.rs:292-330): parses the file on the host into the arrays
  * lb200_index_create takes (codes already transposed per partition).  Pure host code: usable
- * without a GPU.  The v0.2 / v0.3 containers (index.idx + auxiliary.idx) are LB200_EUNSUPPORTED. */
+ * without a GPU.  The current (v3) index -- index.idx + auxiliary.idx -- has its own entry points below. */
 typedef struct lb200_index_file lb200_index_file; /* opaque, host memory */
 typedef struct {
   int32_t metric;              /* LB200_L2 / COSINE / DOT (pb::VectorMetricType)                 */
@@ -101,6 +101,20 @@ void lb200_index_file_close(lb200_index_file* f);
  * legacy IVF_PQ index).  raw_vectors [num_rows][dim] in the FILE's row order, or NULL. */
 int32_t lb200_index_open(int32_t device_id, const char* path, const float* raw_vectors_or_null,
                          lb200_index** out);
+
+/* Native reader of the CURRENT IVF_PQ index (IndexFileVersion::V3): `_indices/<uuid>/index.idx` (IVF model with the
+ * centroids, `lance:index` / `lance:ivf` schema metadata) + `auxiliary.idx` (`_rowid` and `__pq_code` columns in
+ * partition order, the PQ codebook in `storage_metadata`), both Lance-v2 file containers of format 2.0.  Replaces
+ * IVFIndex::try_new + IvfQuantizationStorage::try_new / load_partition (rust/lance/src/index/vector/ivf/v2.rs:110-202,
+ * rust/lance-index/src/vector/storage.rs:210-298); the writer it mirrors is rust/lance/src/index/vector/builder.rs:
+ * 624-770.  Pure host code.  Only the page encodings that writer produces for these columns are accepted (flat,
+ * uncompressed, no nulls); anything else is LB200_EUNSUPPORTED.  PARITY UNPINNED: the reference tree holds no v3
+ * index file; see csrc/api_file_v3.inl.  lb200_index_file_get_info / _close serve both file kinds. */
+int32_t lb200_index_file_open_v3(const char* index_idx_path, const char* auxiliary_idx_path, lb200_index_file** out);
+int32_t lb200_index_file_open_v3_bytes(const void* index_idx, uint64_t index_size, const void* auxiliary_idx,
+                                       uint64_t auxiliary_size, lb200_index_file** out);
+int32_t lb200_index_open_v3(int32_t device_id, const char* index_idx_path, const char* auxiliary_idx_path,
+                            const float* raw_vectors_or_null, lb200_index** out);
 
 /* VectorIndex::find_partitions (vector.rs:146; ivf/v2.rs:403-411 ->
  * kmeans_find_partitions, rust/lance-linalg/src/kmeans.rs:624-644), batched.

@@ -20,6 +20,7 @@ EXPORTS = [
     "lb200_index_open", "lb200_flat_distance_f16", "lb200_flat_topk_f16", "lb200_normalize",
     "lb200_shard_export", "lb200_shard_attach", "lb200_shard_detach", "lb200_shard_search", "lb200_shard_search_device",
     "lb200_shard_check", "lb200_group_create", "lb200_group_search", "lb200_group_destroy",
+    "lb200_index_file_open_v3", "lb200_index_file_open_v3_bytes", "lb200_index_open_v3",
     "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
 ]
 

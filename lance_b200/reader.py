@@ -307,7 +307,7 @@ class LoadedIndex:
 # ---------------------------------------------------------------------------------------------
 # The same reader, native: lb200_index_file_* / lb200_index_open of the C ABI (csrc/api_file.inl).
 # ---------------------------------------------------------------------------------------------
-def open_legacy_ivf_pq_native(path_or_bytes) -> IvfPqData:
+def open_legacy_ivf_pq_native(path_or_bytes, _aux=None) -> IvfPqData:
     """Parse with the library's C++ reader (host only, no GPU needed) and copy out the arrays."""
     import ctypes as C
 
@@ -323,7 +323,13 @@ def open_legacy_ivf_pq_native(path_or_bytes) -> IvfPqData:
     L = _lib.lib()
     L.lb200_index_file_close.restype = None
     h = C.c_void_p()
-    if isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
+    if _aux is not None:      # v3: index.idx + auxiliary.idx (csrc/api_file_v3.inl)
+        if isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
+            a, b = bytes(path_or_bytes), bytes(_aux)
+            _lib.check(L.lb200_index_file_open_v3_bytes(a, C.c_uint64(len(a)), b, C.c_uint64(len(b)), C.byref(h)))
+        else:
+            _lib.check(L.lb200_index_file_open_v3(str(path_or_bytes).encode(), str(_aux).encode(), C.byref(h)))
+    elif isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
         b = bytes(path_or_bytes)
         _lib.check(L.lb200_index_file_open_bytes(b, C.c_uint64(len(b)), C.byref(h)))
     else:
@@ -346,6 +352,28 @@ def open_legacy_ivf_pq_native(path_or_bytes) -> IvfPqData:
         return data
     finally:
         L.lb200_index_file_close(h)
+
+
+def open_v3_ivf_pq_native(index_idx, auxiliary_idx) -> IvfPqData:
+    """The v3 index (index.idx + auxiliary.idx, paths or bytes) through the library's native parser."""
+    return open_legacy_ivf_pq_native(index_idx, _aux=auxiliary_idx)
+
+
+def open_index_v3(index_idx_path, auxiliary_idx_path, device_id=0, raw_vectors=None):
+    """Dataset::open_vector_index for a v3 IVF_PQ index: lb200_index_open_v3 (native parse + upload)."""
+    import ctypes as C
+
+    from . import _lib
+    from .index import IvfPqIndex
+
+    meta = open_v3_ivf_pq_native(index_idx_path, auxiliary_idx_path)
+    raw = None if raw_vectors is None else np.ascontiguousarray(raw_vectors, dtype=np.float32)
+    if raw is not None and raw.shape != (meta.N, meta.dim):
+        raise ValueError(f"raw_vectors must be [{meta.N}][{meta.dim}] in the file's row order")
+    h = C.c_void_p()
+    _lib.check(_lib.lib().lb200_index_open_v3(C.c_int32(device_id), str(index_idx_path).encode(), str(auxiliary_idx_path).encode(),
+                                              None if raw is None else raw.ctypes.data_as(C.c_void_p), C.byref(h)))
+    return IvfPqIndex._adopt(h, meta, device_id, raw is not None)
 
 
 def open_index(path, device_id=0, raw_vectors=None):
