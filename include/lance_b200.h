@@ -279,6 +279,24 @@ int32_t lb200_flat_topk_device(int32_t device_id, int32_t metric, uint32_t dim,
                                float* d_out_dist, uint64_t* d_out_idx, uint32_t* d_out_count,
                                void* stream);
 
+/* lb200_flat_topk_device WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, kernels and results (bit-identical) as lb200_flat_topk_device with
+ * no bounds; the device scratch -- the [Q][n] f32 distance block plus the per-segment candidate lists -- lives in
+ * a fixed `static __device__` array of lb200_noalloc_scratch_bytes() = 32 MiB that every GPU loading the library
+ * holds until exit.  Limit: about Q * n * 4 bytes <= 32 MiB (e.g. 8 queries x 1M rows, 64 x 128k); beyond it the
+ * call fails with LB200_EINVAL and a message stating need and capacity.  The call is asynchronous on `stream`,
+ * never synchronises and calls no cudaMalloc / cudaFree / allocating routine; the first call on a device resolves
+ * the array's device address (cudaGetSymbolAddress), so make one call outside a graph capture.  ALL calls share
+ * the one array, which keeps the previous call's contents (the call clears what must start at zero): calls that
+ * overlap on the GPU -- different streams or host threads -- RACE; the caller must order them. */
+int32_t lb200_flat_topk_device_noalloc(int32_t device_id, int32_t metric, uint32_t dim,
+                                       const float* d_queries, uint32_t Q, const float* d_vectors,
+                                       const uint8_t* d_validity_or_null, uint64_t n, uint32_t k,
+                                       float* d_out_dist, uint64_t* d_out_idx, uint32_t* d_out_count,
+                                       void* stream);
+uint64_t lb200_noalloc_scratch_bytes(void);
+
 /* The same two entry points for Float16 columns (the reference's f16 path:
  * `impl L2/Dot/Cosine/Normalize for f16`, rust/lance-linalg/src/distance/{l2.rs:136-166, dot.rs:100-137,
  * cosine.rs:88-121, norm_l2.rs:46-76}, C kernels rust/lance-linalg/src/simd/f16.c).  queries / vectors are

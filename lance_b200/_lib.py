@@ -21,6 +21,7 @@ EXPORTS = [
     "lb200_shard_export", "lb200_shard_attach", "lb200_shard_detach", "lb200_shard_search", "lb200_shard_search_device",
     "lb200_shard_check", "lb200_group_create", "lb200_group_search", "lb200_group_destroy",
     "lb200_index_file_open_v3", "lb200_index_file_open_v3_bytes", "lb200_index_open_v3",
+    "lb200_flat_topk_device_noalloc", "lb200_noalloc_scratch_bytes",
     "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
 ]
 
@@ -54,6 +55,7 @@ def lib():
         _lib.lb200_version.restype = C.c_char_p
         _lib.lb200_index_destroy.restype = None
         _lib.lb200_prefilter_destroy.restype = None
+        _lib.lb200_noalloc_scratch_bytes.restype = C.c_uint64
         _lib.lb200_group_destroy.restype = None
         for name in EXPORTS:
             if os.environ.get("LB200_SO") and not hasattr(_lib, name):
