@@ -652,12 +652,13 @@ def main():
         kname = "scan3_kernel<BOOT=%s>" % ("true" if (shard_mode or nprobes < 16) else "false")
         if pre:
             kname += " + lut_prepass_kernel"
-    traffic, traffic_src = None, None
+    traffic, traffic_src, lsu_pct = None, None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_scan_traffic.json")
     if os.path.exists(tpath):
         for rec in json.load(open(tpath)):
             if rec["workload"] == args.workload and rec["scan_variant"] == st["scan_variant"] and rec["n_gpus"] == world:
                 traffic, traffic_src = rec["dram_bytes_per_launch"] / 1e9, rec["source"]
+                lsu_pct = rec.get("lsu_pipe_pct")
     qps = Q * args.steps / (ms_total * 1e-3)
     e2e_qps = Q * e2e_steps / (ms_e2e * 1e-3)
     line = {
@@ -673,6 +674,11 @@ def main():
                    "index_build_s": round(t_build, 1)},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu dram read+write)",
+                     # the physical figures beside the algorithmic one.  dram_frac = ncu DRAM bytes of one
+                     # launch / the live kernel time / peak; lsu_frac = the SM load/store data pipe (shared-memory table
+                     # gather + code stream through L1), the unit that actually saturates first (ncu, same capture)
+                     "dram_frac": (traffic * 1e9 / (my_scan_ms * 1e-3) / 1e9 / peak) if (traffic and my_scan_ms > 0) else None,
+                     "lsu_frac": (lsu_pct / 100.0) if lsu_pct is not None else None,
                      "traffic_source": traffic_src, "kernel": kname + " (rank 0)",
                      "peak_source": peak_src, "scan_ms_per_launch": my_scan_ms,
                      "algorithmic_bytes_per_launch": my_bytes,
