@@ -279,6 +279,51 @@ int32_t lb200_flat_topk_device(int32_t device_id, int32_t metric, uint32_t dim,
                                float* d_out_dist, uint64_t* d_out_idx, uint32_t* d_out_count,
                                void* stream);
 
+/* GPU index BUILD: the steps the reference runs on the CPU (rust/lance-linalg/src/kmeans.rs,
+ * lance-index/src/vector/pq.rs) or through torch (python/python/lance/torch/kmeans.py, lance/vector.py:134-700).
+ * Given the initial centroids every step is deterministic and bit-identical to the reference's arithmetic
+ * (tests/test_gpu_build.py: against the CPU restatement lo_kmeans_fit / lo_pq_quantize and against PQ codes the reference wrote).
+ *  lb200_kmeans_train      KMeans::new_with_params / train_kmeans (kmeans.rs:440-561): membership = argmin over
+ *                          l2 / dot distances (None when no distance is < +inf), centroid = f32 sum of the members
+ *                          in data order / count, empty clusters re-seeded by split_clusters (:135-148), stop when
+ *                          |loss - last| / last < tolerance.  metric L2 or DOT (cosine: normalise the rows first, as
+ *                          ivf/builder.rs does, and pass L2).  init_centroids_or_null [k][dim]: the reference's
+ *                          initialisation is an UNSEEDED random choice of k rows; NULL = a choice seeded by `seed`.
+ *                          `redos` (default 1 in the reference) is not offered.
+ *  lb200_compute_partitions compute_partitions (kmeans.rs:721-770): out_ids [n], 0xffffffff = None.
+ *  lb200_residuals_device  x - centroid[part] (ivf/v2.rs:285-301 at build time).
+ *  lb200_pq_train_device   one k-means (k = 256) per sub-space on the sub-vector slices (pq/builder.rs).
+ *  lb200_pq_encode         ProductQuantizer::transform (pq.rs:120-190): out_codes [n][M] row-major, code =
+ *                          argmin over the sub-space's 256 centroids (first minimum).
+ * `_device` variants take device pointers for the large arrays (vectors, ids, codes); centroids / codebooks of the
+ * training calls stay host arrays (they are small and the loop reads the loss on the host every round). */
+int32_t lb200_kmeans_train(int32_t device_id, int32_t metric, uint32_t dim, const float* vectors, uint64_t n,
+                           uint32_t k, uint32_t max_iters, float tolerance, uint64_t seed,
+                           const float* init_centroids_or_null, float* out_centroids,
+                           uint32_t* out_iters_or_null, double* out_loss_or_null);
+int32_t lb200_kmeans_train_device(int32_t device_id, int32_t metric, uint32_t dim, const float* d_vectors,
+                                  uint64_t n, uint32_t k, uint32_t max_iters, float tolerance, uint64_t seed,
+                                  const float* init_centroids_or_null, float* out_centroids,
+                                  uint32_t* out_iters_or_null, double* out_loss_or_null);
+int32_t lb200_compute_partitions(int32_t device_id, int32_t metric, uint32_t dim, const float* centroids,
+                                 uint32_t k, const float* vectors, uint64_t n, uint32_t* out_ids,
+                                 float* out_dists_or_null);
+int32_t lb200_compute_partitions_device(int32_t device_id, int32_t metric, uint32_t dim,
+                                        const float* d_centroids, uint32_t k, const float* d_vectors,
+                                        uint64_t n, uint32_t* d_out_ids, float* d_out_dists_or_null,
+                                        void* stream);
+int32_t lb200_residuals_device(int32_t device_id, uint32_t dim, const float* d_vectors,
+                               const uint32_t* d_part_ids, const float* d_centroids, uint64_t n,
+                               float* d_out, void* stream);
+int32_t lb200_pq_train_device(int32_t device_id, int32_t metric, uint32_t dim, uint32_t num_sub_vectors,
+                              const float* d_vectors, uint64_t n, uint32_t max_iters, float tolerance,
+                              uint64_t seed, const float* init_codebook_or_null, float* out_codebook);
+int32_t lb200_pq_encode(int32_t device_id, int32_t metric, uint32_t dim, uint32_t num_sub_vectors,
+                        const float* codebook, const float* vectors, uint64_t n, uint8_t* out_codes);
+int32_t lb200_pq_encode_device(int32_t device_id, int32_t metric, uint32_t dim, uint32_t num_sub_vectors,
+                               const float* d_codebook, const float* d_vectors, uint64_t n,
+                               uint8_t* d_out_codes, void* stream);
+
 /* lb200_flat_topk_device WITHOUT any allocation.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same arguments, kernels and results (bit-identical) as lb200_flat_topk_device with

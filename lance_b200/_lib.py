@@ -21,6 +21,8 @@ EXPORTS = [
     "lb200_shard_export", "lb200_shard_attach", "lb200_shard_detach", "lb200_shard_search", "lb200_shard_search_device",
     "lb200_shard_check", "lb200_group_create", "lb200_group_search", "lb200_group_destroy",
     "lb200_index_file_open_v3", "lb200_index_file_open_v3_bytes", "lb200_index_open_v3",
+    "lb200_kmeans_train", "lb200_kmeans_train_device", "lb200_compute_partitions", "lb200_compute_partitions_device",
+    "lb200_residuals_device", "lb200_pq_train_device", "lb200_pq_encode", "lb200_pq_encode_device",
     "lb200_flat_topk_device_noalloc", "lb200_noalloc_scratch_bytes",
     "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
 ]

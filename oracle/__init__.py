@@ -269,6 +269,29 @@ def flat_knn(metric, queries, vectors, k, validity=None, row_ids=None, threads=0
     return od, oi, oc
 
 
+def compute_membership(metric, centroids, data, threads=0):
+    """KMeansAlgoFloat::compute_membership_and_loss (kmeans.rs:208-240): ids [n] u32 (0xffffffff = None), dists [n]."""
+    centroids, data = _f32(centroids), _f32(data)
+    n, d = data.shape
+    ids = np.empty(n, dtype=np.uint32)
+    dists = np.empty(n, dtype=np.float32)
+    lib().lo_compute_membership(C.c_int(METRICS[metric]), _p(centroids), C.c_uint32(centroids.shape[0]), C.c_uint32(d), _p(data),
+                                C.c_size_t(n), C.c_int(threads), _p(ids), _p(dists))
+    return ids, dists
+
+
+def kmeans_fit(metric, data, init_centroids, max_iters=50, tolerance=1e-4, threads=0):
+    """KMeans::train_kmeans (kmeans.rs:440-525) from given initial centroids.  Returns (centroids, rounds, loss)."""
+    data = _f32(data)
+    cents = _f32(init_centroids).copy()
+    loss = C.c_double(0)
+    lib().lo_kmeans_fit.restype = C.c_uint32
+    it = lib().lo_kmeans_fit(C.c_int(METRICS[metric]), _p(data), C.c_size_t(data.shape[0]), C.c_uint32(data.shape[1]),
+                             C.c_uint32(cents.shape[0]), C.c_uint32(max_iters), C.c_double(tolerance), C.c_int(threads), _p(cents),
+                             C.byref(loss))
+    return cents, int(it), float(loss.value)
+
+
 def max_threads():
     return int(lib().lo_max_threads())
 

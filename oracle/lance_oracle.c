@@ -860,3 +860,104 @@ void lo_distance_batch_f16(int metric, const lo_f16 *from, const lo_f16 *to, siz
                               : lo_cosine_f16(from, xn, y, d);
   }
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * KMeans training (index build).  Restates lance-linalg/src/kmeans.rs:
+ *   KMeansAlgoFloat::compute_membership_and_loss (:208-240): per vector argmin_value_float over
+ *     l2_distance_batch / dot_distance_batch against all centroids (None when no distance is < +inf); loss = the
+ *     sequential f64 sum of the f32 minima (None counts 0);
+ *   KMeansAlgoFloat::to_kmeans (:242-300): per cluster the f32 sum of its members IN DATA ORDER, divided by the count
+ *     as f32; empty clusters become NaN and are then re-seeded by split_clusters (:135-148): the FIRST largest cluster
+ *     is halved, new = largest * (1 + eps), largest /= (1 + eps), eps = f32::EPSILON;
+ *   KMeans::train_kmeans (:440-525): up to max_iters rounds of (membership, update), stop when
+ *     |loss - last_loss| / last_loss < tolerance (checked AFTER the update of that round).
+ * Unpinned by the reference: the random initialisation (SmallRng::from_entropy) -- the caller supplies the initial
+ * centroids; `redos` (default 1) is not restated.  metric: LO_L2 or LO_DOT (cosine callers normalise and use L2,
+ * as ivf/builder.rs does). */
+typedef struct {
+  int metric;
+  const float *data, *cents;
+  uint32_t dim, k;
+  uint32_t *ids;
+  float *dists;
+} lo_km_ctx;
+static void lo_km_body(int64_t i, void *vctx) {
+  lo_km_ctx *c = (lo_km_ctx *)vctx;
+  float *dist = (float *)malloc(sizeof(float) * c->k);
+  const float *v = c->data + (size_t)i * c->dim;
+  if (c->metric == LO_DOT)
+    lo_dot_distance_batch(v, c->cents, c->k, c->dim, dist);
+  else
+    lo_l2_distance_batch(v, c->cents, c->k, c->dim, dist);
+  float best = INFINITY;
+  uint32_t bi = 0xffffffffu;
+  for (uint32_t j = 0; j < c->k; j++)
+    if (dist[j] < best) {
+      best = dist[j];
+      bi = j;
+    }
+  c->ids[i] = bi;
+  c->dists[i] = bi == 0xffffffffu ? 0.0f : best;
+  free(dist);
+}
+/* membership (0xffffffff = None) and distance to the chosen centroid, for n vectors */
+void lo_compute_membership(int metric, const float *cents, uint32_t k, uint32_t dim, const float *data, size_t n,
+                           int threads, uint32_t *ids, float *dists) {
+  lo_km_ctx c = {metric, data, cents, dim, k, ids, dists};
+  lo_parallel_for((int64_t)n, 64, threads, lo_km_body, &c);
+}
+/* centroids [k][dim]: in = initial, out = trained.  Returns the number of rounds run; *loss_out = last loss. */
+uint32_t lo_kmeans_fit(int metric, const float *data, size_t n, uint32_t dim, uint32_t k, uint32_t max_iters,
+                       double tolerance, int threads, float *centroids, double *loss_out) {
+  uint32_t *ids = (uint32_t *)malloc(sizeof(uint32_t) * (n ? n : 1));
+  float *dists = (float *)malloc(sizeof(float) * (n ? n : 1));
+  uint64_t *cnts = (uint64_t *)malloc(sizeof(uint64_t) * k);
+  const float one_eps = 1.0f + 1.1920929e-7f;
+  double loss = 1.7976931348623157e308, last_loss = 0.0;
+  uint32_t it = 0;
+  for (it = 1; it <= max_iters; it++) {
+    lo_compute_membership(metric, centroids, k, dim, data, n, threads, ids, dists);
+    last_loss = 0.0;
+    for (size_t i = 0; i < n; i++) last_loss += (double)dists[i];
+    for (uint32_t c = 0; c < k; c++) cnts[c] = 0;
+    for (size_t j = 0; j < (size_t)k * dim; j++) centroids[j] = 0.0f;
+    for (size_t i = 0; i < n; i++) {
+      if (ids[i] == 0xffffffffu) continue;
+      cnts[ids[i]]++;
+      float *c = centroids + (size_t)ids[i] * dim;
+      const float *v = data + i * dim;
+      for (uint32_t j = 0; j < dim; j++) c[j] += v[j];
+    }
+    for (uint32_t c = 0; c < k; c++) {
+      float *cc = centroids + (size_t)c * dim;
+      if (cnts[c] == 0)
+        for (uint32_t j = 0; j < dim; j++) cc[j] = NAN;
+      else
+        for (uint32_t j = 0; j < dim; j++) cc[j] /= (float)cnts[c];
+    }
+    for (uint32_t i = 0; i < k; i++) { /* split_clusters */
+      if (cnts[i] != 0) continue;
+      uint32_t largest = 0;
+      uint64_t mx = 0; /* argmax: first strictly greater than u64::MIN = 0 ... (all zero -> index stays None; k >= 1 and n >= k make that impossible) */
+      for (uint32_t j = 0; j < k; j++)
+        if (cnts[j] > mx) {
+          mx = cnts[j];
+          largest = j;
+        }
+      cnts[i] = cnts[largest] / 2;
+      cnts[largest] /= 2;
+      for (uint32_t j = 0; j < dim; j++) {
+        centroids[(size_t)i * dim + j] = centroids[(size_t)largest * dim + j] * one_eps;
+        centroids[(size_t)largest * dim + j] /= one_eps;
+      }
+    }
+    if (fabs(loss - last_loss) / last_loss < tolerance) break;
+    loss = last_loss;
+  }
+  if (it > max_iters) it = max_iters;
+  if (loss_out) *loss_out = last_loss;
+  free(ids);
+  free(dists);
+  free(cnts);
+  return it;
+}
