@@ -323,6 +323,88 @@ def run_flat(args):
     print(json.dumps(line), flush=True)
 
 
+def clustered_lowrank(N, d, seed, dev, nblobs=4096, rank=16, chunk=2_000_000):
+    """Synthetic vectors WITH neighbourhood structure, generated on the device: blob centres U[0,128)^d, inside a blob a
+    `rank`-dimensional Gaussian cloud (one random basis shared by all blobs, sigma 12) plus a little isotropic noise
+    (sigma 1).  Isotropic blobs (SURVEY 8(d)'s first recipe) make all neighbours of a 128-d point nearly equidistant,
+    so recall on them says nothing (r01: 0.17); here a point's neighbours differ clearly in distance, as in real data."""
+    import torch
+    g = torch.Generator(device=dev).manual_seed(1234)              # the structure (centres, basis) is fixed
+    centres = torch.rand((nblobs, d), generator=g, device=dev) * 128.0
+    basis = torch.randn((rank, d), generator=g, device=dev) / (rank ** 0.5)
+    g2 = torch.Generator(device=dev).manual_seed(seed)             # the draws depend on the seed
+    out = torch.empty((N, d), dtype=torch.float32, device=dev)
+    for s in range(0, N, chunk):
+        n = min(chunk, N - s)
+        which = torch.randint(0, nblobs, (n,), generator=g2, device=dev)
+        z = torch.randn((n, rank), generator=g2, device=dev) * 12.0
+        out[s:s + n] = centres[which] + z @ basis + torch.randn((n, d), generator=g2, device=dev)
+    return out
+
+
+def recall_block(wl, local, max_rows=10_000_000, nq=1000):
+    """recall@10 of the path on a REAL-BUILT index (the metric is "queries/sec @ recall@10"; pattern of
+    python/python/lance/torch/bench_utils.py:50-133): vectors with neighbourhood structure -> GPU index build
+    (lance_b200/build.py) with the workload's nlist / M / metric -> search with the workload's nprobes / k / refine ->
+    exact ground truth from the flat kernel (lb200_flat_topk_device) on the same vectors."""
+    import ctypes as C
+    import torch
+    from lance_b200 import IvfPqIndex, Query, _lib
+    from lance_b200.build import build_ivf_pq_gpu
+    N, d, nlist, M, metric, nprobes, k, refine, Q, desc = wl
+    dev = torch.device("cuda", local)
+    n = min(N, max_rows)
+    t0 = time.perf_counter()
+    x = clustered_lowrank(n, d, 99, dev)
+    q = clustered_lowrank(nq, d, 4321, dev)
+    if metric == "dot":   # inner-product search is used on embedding-like rows: zero mean, unit length
+        for t_ in (x, q):
+            t_.sub_(64.0)
+            t_.div_(t_.norm(dim=1, keepdim=True).clamp_min(1e-30))
+    torch.cuda.synchronize(dev)
+    t_gen = time.perf_counter() - t0
+    data, tb = build_ivf_pq_gpu(x, metric, nlist, M, seed=7, max_iters=10, keep_raw=refine > 0, device_id=local)
+    ix = IvfPqIndex(data, device_id=local)
+    hq = q.cpu().numpy()
+    qy = Query(key=hq, k=k, nprobes=nprobes, refine_factor=refine or None)
+    gd, gi, gc = ix.search(qy)
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        ix.search(qy)
+    qps = nq * reps / (time.perf_counter() - t0)
+    # exact ground truth with the flat kernel, queries in tiles that keep the [tile][n] distance block small
+    L = _lib.lib()
+    od = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    oi = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    oc = torch.empty((nq,), dtype=torch.int32, device=dev)
+    mcode = {"l2": 0, "cosine": 1, "dot": 2}[metric]
+    t0 = time.perf_counter()
+    _lib.check(L.lb200_flat_topk_device(C.c_int32(local), C.c_int32(mcode), C.c_uint32(d), C.c_void_p(q.data_ptr()), C.c_uint32(nq),
+                                        C.c_void_p(x.data_ptr()), None, C.c_uint64(n), C.c_uint32(k), C.c_void_p(od.data_ptr()),
+                                        C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()), None))
+    torch.cuda.synchronize(dev)
+    t_truth = time.perf_counter() - t0
+    truth = oi.cpu().numpy()
+    hits = [len(set(gi[i, :int(gc[i])].tolist()) & set(truth[i].tolist())) for i in range(nq)]
+    # a parity spot check on this index too: the oracle on the first queries
+    import oracle
+    ns = 64
+    rd, ri, rc, _ = oracle.OracleIndex(data).search(hq[:ns], k=k, nprobes=nprobes, refine_factor=refine, threads=oracle.max_threads())
+    par = parity_block((rd, ri, rc, None), (gd, gi, gc), k)
+    sizes = np.diff(data.part_offsets.astype(np.int64))
+    ix.close()
+    return {"recall_at_10": float(np.mean(hits)) / k, "queries": nq, "rows": n, "k": k, "nprobes": nprobes, "refine_factor": refine,
+            "index": f"real-built on the GPU (lance_b200/build.py): IVF{nlist},PQ{M}, {metric}, k-means <= 10 rounds, "
+                     f"partition sizes {int(sizes.min())}..{int(sizes.max())}",
+            "data": "clustered low-rank synthetic (4096 blobs, 16-dim clouds + noise" + ("; centred and unit-normalised for dot" if metric == "dot" else "") + "), queries = held-out draws",
+            "ground_truth": "exact kNN over the same rows with lb200_flat_topk_device",
+            "qps_on_this_index": qps, "parity_vs_oracle": {"queries_checked": ns, "unexplained_mismatches": par["unexplained_mismatches"],
+                                                            "distance_bits_identical": par["distance_bits_identical"]},
+            "seconds": {"generate": round(t_gen, 2), "build": {kk: (round(v, 2) if isinstance(v, float) else v) for kk, v in tb.items()},
+                        "ground_truth": round(t_truth, 2)}}
+
+
 class _DropinBackend(__import__("ctypes").Structure):
     import ctypes as _C
     _fields_ = [("kind", _C.c_int32), ("handle", _C.c_void_p), ("fn_find", _C.c_void_p), ("fn_search", _C.c_void_p),
@@ -450,6 +532,7 @@ def main():
     ap.add_argument("--queries", type=int, default=0,
                     help="override the workload's queries per step (batch-size sweep of BASELINE configs[4])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-recall", action="store_true", help="skip the real-built-index recall@10 block")
     ap.add_argument("--shard-of", type=int, default=0,
                     help="diagnostic: single process holding rank 0's shard of an N-way partition split")
     args = ap.parse_args()
@@ -713,6 +796,11 @@ def main():
         keys = _normalize(queries[:nq], device_id=local) if metric == "cosine" else queries[:nq]
         gp = ix.find_partitions(keys, nprobes)
         line["parity"] = parity_block(ref, (h_od.numpy(), h_oi.numpy().view(np.uint64), h_oc.numpy()), k, gpu_probes=gp)
+    if world == 1 and _BITS == 8 and not args.no_recall and not args.no_cpu_baseline and args.workload != "tiny":
+        ix.close()   # free the benchmark index first
+        rb = recall_block(wl, local)
+        line["recall"] = rb
+        line["recall_at_10"] = rb["recall_at_10"]
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
