@@ -246,31 +246,41 @@ def _result_crc(od, oi, oc):
 
 
 def run_flat(args):
-    """--workload cfg2: flat brute-force L2 kNN 1M x 128, k=10 (KNNVectorDistanceExec path, no index;
-    BASELINE configs[1]).  A step = one batch of 256 queries against the device-resident vectors."""
+    """--workload cfg2: flat brute-force L2 kNN 1M x 128, k=10 (KNNVectorDistanceExec path, no index; BASELINE
+    configs[1]).  A step = one batch of 256 queries against the device-resident column (lb200_column_*): tensor-core
+    candidate filter (tcgen05 + TMA, csrc/flat_tc.cuh) + exact fp32 re-score, results bit-identical to the exact path."""
     import ctypes as C
     import torch
-    from lance_b200 import _lib, flat_knn
+    from lance_b200 import _lib
     from lance_b200._lib import check
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     dev = torch.device("cuda", 0)
-    N, d, k, Q = 1_000_000, 128, 10, 256
+    N, d, k, Q = 1_000_000, 128, 10, args.queries or 256
     rng = np.random.default_rng(1234)
     vecs = np.clip(np.rint(rng.normal(64, 32, size=(N, d))), 0, 218).astype(np.float32)  # SIFT-like integers
     queries = np.clip(np.rint(rng.normal(64, 32, size=(Q, d))), 0, 218).astype(np.float32)
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
-    d_v, d_q = torch.from_numpy(vecs).to(dev), torch.from_numpy(queries).to(dev)
+    L = _lib.lib()
+    col = C.c_void_p()
+    check(L.lb200_column_create(C.c_int32(0), C.c_uint32(d), vecs.ctypes.data_as(C.c_void_p), None, C.c_uint64(N), C.byref(col)))
+    d_q = torch.from_numpy(queries).to(dev)
     od = torch.empty((Q, k), dtype=torch.float32, device=dev)
     oi = torch.empty((Q, k), dtype=torch.int64, device=dev)
     oc = torch.empty((Q,), dtype=torch.int32, device=dev)
-    L = _lib.lib()
+    h_q = torch.from_numpy(queries).pin_memory()
+    h_od = torch.empty((Q, k), dtype=torch.float32).pin_memory()
+    h_oi = torch.empty((Q, k), dtype=torch.int64).pin_memory()
+    h_oc = torch.empty((Q,), dtype=torch.int32).pin_memory()
 
     def step():
-        check(L.lb200_flat_topk_device(C.c_int32(0), C.c_int32(0), C.c_uint32(d), C.c_void_p(d_q.data_ptr()),
-                                       C.c_uint32(Q), C.c_void_p(d_v.data_ptr()), None, C.c_uint64(N), C.c_uint32(k),
-                                       C.c_void_p(od.data_ptr()), C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()),
-                                       C.c_void_p(stream.cuda_stream)))
+        check(L.lb200_column_flat_topk_device(col, C.c_int32(0), C.c_void_p(d_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
+                                              C.c_void_p(od.data_ptr()), C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()),
+                                              C.c_void_p(stream.cuda_stream)))
+
+    def e2e_step():  # host queries in, host results out, through the C ABI (H2D + D2H inside)
+        check(L.lb200_column_flat_topk(col, C.c_int32(0), C.c_void_p(h_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
+                                       C.c_void_p(h_od.data_ptr()), C.c_void_p(h_oi.data_ptr()), C.c_void_p(h_oc.data_ptr())))
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -285,33 +295,58 @@ def run_flat(args):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
+    tc, cand, fb = C.c_uint32(0), C.c_uint64(0), C.c_uint32(0)
+    check(L.lb200_column_last_call(col, C.byref(tc), C.byref(cand), C.byref(fb)))
+    for _ in range(2):
+        e2e_step()
     t0 = time.perf_counter()
-    e2e_steps = 3
+    e2e_steps = max(3, min(args.steps, 10))
     for _ in range(e2e_steps):
-        flat_knn(queries, "l2", vecs, k)   # host-pointer ABI: uploads the 512 MB of vectors every call, as
-    ms_e2e = (time.perf_counter() - t0) * 1e3  # compute_distance gets a fresh RecordBatch every call
+        e2e_step()
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+    # the exact path alone on the same column, for the line's own A/B
+    os.environ["LB200_FLAT_NO_TC"] = "1"
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    ms_exact = (time.perf_counter() - t0) * 1e3 / 3
+    del os.environ["LB200_FLAT_NO_TC"]
+    step()
+    torch.cuda.synchronize()
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+    peaks = json.load(open(peaks_path)) if os.path.exists(peaks_path) else {}
+    peak_hbm = float(peaks.get("hbm_gbs", 6650.0))
     qps = Q * args.steps / (ms * 1e-3)
-    tile_bytes = N * d * 4 * ((Q + 31) // 32)  # the vectors are streamed once per 32-query tile
+    step_ms = ms / args.steps
+    # the filter kernel streams the bf16 rows once per 128-query block: its algorithmic bytes
+    qblocks = (Q + 127) // 128
+    bytes_step = N * d * 2 * qblocks
     line = {"metric": "flat kNN queries/sec (batched)", "value": qps, "unit": "queries/s", "n_gpus": 1,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "flat brute-force L2 kNN 1Mx128 f32, k=10, 256 queries per step (BASELINE configs[1])",
-                       "l2_policy": "inputs larger than L2 (512 MB of vectors)"},
-            "roofline": {"bound": "hbm", "achieved": tile_bytes / (ms / args.steps * 1e-3) / 1e9, "peak": peak,
-                         "unit": "GB/s", "frac": tile_bytes / (ms / args.steps * 1e-3) / 1e9 / peak, "traffic": None,
-                         "kernel": "coarse_dist_l2_slab_kernel + flat_select_kernel + merge_lists_kernel (whole step)",
-                         "note": "bytes = N*d*4 per 32-query tile of the distance kernel; the path is fp32-issue bound (Q*N*d*3 flop), not HBM bound"},
-            "e2e": {"value": Q * e2e_steps / (ms_e2e * 1e-3), "unit": "queries/s",
-                    "h2d_bytes_per_step": int(vecs.nbytes + queries.nbytes), "d2h_bytes_per_step": Q * k * 12 + Q * 4,
-                    "path": "lb200_flat_topk (host-pointer C ABI; uploads the vector batch every call)"},
-            "gpu_launches": 3 * ((Q + 31) // 32) * args.steps,  # per 32-query tile: distance, segmented select, merge
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (results); bf16 tensor-core candidate filter + exact f32 re-score",
+            "data": "synthetic",
+            "config": {"workload": f"flat brute-force L2 kNN 1Mx128 f32, k=10, {Q} queries per step (BASELINE configs[1])",
+                       "l2_policy": "inputs larger than L2 (256 MB of bf16 rows + 512 MB of f32 rows)",
+                       "path": "lb200_column_flat_topk_device (resident column)",
+                       "filter": {"used_tc": bool(tc.value), "fell_back": bool(fb.value), "candidates_per_query": cand.value / Q},
+                       "exact_path_ms_per_step": ms_exact},
+            "roofline": {"bound": "hbm", "achieved": bytes_step / (step_ms * 1e-3) / 1e9, "peak": peak_hbm, "unit": "GB/s",
+                         "frac": bytes_step / (step_ms * 1e-3) / 1e9 / peak_hbm, "traffic": None,
+                         "kernel": "whole step (exact top-k over the 16k-row sample, flat_tc_filter_kernel, refine_distance_kernel, merge_lists_kernel)",
+                         "note": "bytes = N*d*2 (bf16 rows) per 128-query block of the filter kernel; flops = Q*N*d*2 on tcgen05"},
+            "e2e": {"value": Q * e2e_steps / (ms_e2e * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": int(queries.nbytes),
+                    "d2h_bytes_per_step": Q * k * 12 + Q * 4, "ms_per_step": ms_e2e / e2e_steps,
+                    "path": "lb200_column_flat_topk (host-pointer C ABI on the resident column; queries H2D, results D2H inside)"},
+            "gpu_launches": 9 * args.steps,  # sample distance + select + merge, threshold, bf16, filter, finish, clamp, exact, merge
             "clocks": clocks}
     if not args.no_cpu_baseline:
         import oracle
         cores = oracle.max_threads()
-        nq = 32
+        nq = min(32, Q)
         t0 = time.perf_counter()
         fres = oracle.flat_knn("l2", queries[:nq], vecs, k, threads=cores)
         dt = time.perf_counter() - t0
@@ -321,6 +356,7 @@ def run_flat(args):
         line["parity"] = parity_block((fres[0], fres[1], fres[2], None),
                                       (od.cpu().numpy(), oi.cpu().numpy().view(np.uint64), oc.cpu().numpy()), k)
     print(json.dumps(line), flush=True)
+    L.lb200_column_destroy(col)
 
 
 def clustered_lowrank(N, d, seed, dev, nblobs=4096, rank=16, chunk=2_000_000):

@@ -23,6 +23,8 @@ EXPORTS = [
     "lb200_index_file_open_v3", "lb200_index_file_open_v3_bytes", "lb200_index_open_v3",
     "lb200_kmeans_train", "lb200_kmeans_train_device", "lb200_compute_partitions", "lb200_compute_partitions_device",
     "lb200_residuals_device", "lb200_pq_train_device", "lb200_pq_encode", "lb200_pq_encode_device",
+    "lb200_column_create", "lb200_column_destroy", "lb200_column_flat_topk", "lb200_column_flat_topk_device",
+    "lb200_column_last_call",
     "lb200_flat_topk_device_noalloc", "lb200_noalloc_scratch_bytes",
     "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
 ]
@@ -57,6 +59,7 @@ def lib():
         _lib.lb200_version.restype = C.c_char_p
         _lib.lb200_index_destroy.restype = None
         _lib.lb200_prefilter_destroy.restype = None
+        _lib.lb200_column_destroy.restype = None
         _lib.lb200_noalloc_scratch_bytes.restype = C.c_uint64
         _lib.lb200_group_destroy.restype = None
         for name in EXPORTS:

@@ -584,4 +584,5 @@ extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
 #include "api_file_v3.inl"
 #include "api_f16.inl"
 #include "api_noalloc.inl"
+#include "api_column.inl"
 #include "api_build.inl"

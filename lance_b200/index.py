@@ -399,6 +399,47 @@ def flat_knn(key, metric, vectors, k, validity=None, lower_bound=None, upper_bou
     return od, oi, oc
 
 
+class VectorColumn:
+    """A vector column resident on the device (lb200_column_*): flat_knn(...) without re-uploading the rows."""
+
+    def __init__(self, vectors, validity=None, device_id=0):
+        self._L = _lib.lib()
+        v = _f32(vectors)
+        if v.ndim != 2:
+            raise ValueError("vectors must be [n][dim]")
+        self.n, self.dim = v.shape
+        m = None if validity is None else np.ascontiguousarray(validity, dtype=np.uint8)
+        h = C.c_void_p()
+        check(self._L.lb200_column_create(C.c_int32(device_id), C.c_uint32(self.dim), _p(v), _p(m), C.c_uint64(self.n), C.byref(h)))
+        self._h = h
+
+    def flat_knn(self, key, metric, k, lower_bound=None, upper_bound=None):
+        key2 = np.atleast_2d(_f32(key))
+        if key2.shape[1] != self.dim:
+            raise ValueError("dimension mismatch between key and vectors")
+        if k <= 0:
+            raise ValueError("k must be positive")
+        Q = key2.shape[0]
+        od = np.full((Q, k), np.inf, dtype=np.float32)
+        oi = np.full((Q, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros(Q, dtype=np.uint32)
+        check(self._L.lb200_column_flat_topk(self._h, C.c_int32(DistanceType.code(metric)), _p(key2), C.c_uint32(Q), C.c_uint32(k),
+                                             _fptr(lower_bound), _fptr(upper_bound), _p(od), _p(oi), _p(oc)))
+        return od, oi, oc
+
+    def last_call(self):
+        tc, cand, fb = C.c_uint32(0), C.c_uint64(0), C.c_uint32(0)
+        check(self._L.lb200_column_last_call(self._h, C.byref(tc), C.byref(cand), C.byref(fb)))
+        return {"used_tc": bool(tc.value), "candidates": int(cand.value), "fell_back": bool(fb.value)}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lb200_column_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
 def merge_topk(dist, rowid, count, k, exact=None, kprime=None, lower_bound=None, upper_bound=None, device_id=0):
     """Union of G result lists per query -> the k smallest by (distance,row id): the SortExec(fetch) above the
     fan-out over delta indices (scanner.rs:2139-2157).  dist/rowid [G][Q][stride], count [G][Q]."""
