@@ -295,6 +295,16 @@ def run_flat(args):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
+    if not clocks.get("samples"):   # a 10 ms timed region is shorter than nvidia-smi's sampling period: sample a repeat of it
+        sampler = ClockSampler(0)
+        sampler.start()
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < 1.5:
+            for _ in range(20):
+                step()
+            torch.cuda.synchronize()
+        clocks = sampler.stop()
+        clocks["note"] = "sampled over a 1.5 s repeat of the same steps right after the timed region (which is too short to sample)"
     tc, cand, fb = C.c_uint32(0), C.c_uint64(0), C.c_uint32(0)
     check(L.lb200_column_last_call(col, C.byref(tc), C.byref(cand), C.byref(fb)))
     for _ in range(2):
@@ -336,12 +346,12 @@ def run_flat(args):
                        "exact_path_ms_per_step": ms_exact},
             "roofline": {"bound": "hbm", "achieved": bytes_step / (step_ms * 1e-3) / 1e9, "peak": peak_hbm, "unit": "GB/s",
                          "frac": bytes_step / (step_ms * 1e-3) / 1e9 / peak_hbm, "traffic": None,
-                         "kernel": "whole step (exact top-k over the 16k-row sample, flat_tc_filter_kernel, refine_distance_kernel, merge_lists_kernel)",
+                         "kernel": "whole step (coarse_dist_l2_slab_kernel over the 16k-row sample, ftc_kth_kernel, flat_tc_filter_kernel, ftc_rescore_l2_kernel, ftc_prune_kernel, merge_lists_kernel)",
                          "note": "bytes = N*d*2 (bf16 rows) per 128-query block of the filter kernel; flops = Q*N*d*2 on tcgen05"},
             "e2e": {"value": Q * e2e_steps / (ms_e2e * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": int(queries.nbytes),
                     "d2h_bytes_per_step": Q * k * 12 + Q * 4, "ms_per_step": ms_e2e / e2e_steps,
                     "path": "lb200_column_flat_topk (host-pointer C ABI on the resident column; queries H2D, results D2H inside)"},
-            "gpu_launches": 9 * args.steps,  # sample distance + select + merge, threshold, bf16, filter, finish, clamp, exact, merge
+            "gpu_launches": 8 * args.steps,  # sample distances, k-th select, query bf16, filter, clamp, exact re-score, prune, merge
             "clocks": clocks}
     if not args.no_cpu_baseline:
         import oracle

@@ -32,6 +32,8 @@ struct lb200_column {
   CUtensorMap map_v;
   std::mutex mu;          // calls on one column serialise (shared scratch)
   Arena scratch;
+  std::mutex io_mu;       // host-buffer calls: device copies of the queries / results
+  Arena io;
   cudaStream_t stream = nullptr;
   int sm_count = 148;
   // last call
@@ -71,6 +73,7 @@ static int make_tile_map(CUtensorMap* map, const void* base, uint64_t rows, uint
 }
 
 constexpr uint32_t COL_SAMPLE = 16384;
+constexpr uint32_t COL_QCHUNK = 2048;
 
 // coefficients of E (header comment), each enlarged by 2^-21: the kernel evaluates the test as
 // NY (1 - e2) - 2 P - e1 |q||y| <= T - NQ (1 - e2), four more f32 roundings than the proof's form
@@ -85,6 +88,19 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   c->last_tc = 0;
   c->last_fallback = 0;
   c->last_candidates = 0;
+  if (Q > COL_QCHUNK) {  // bounds the scratch (the sample distances are [Q][16384] f32)
+    uint32_t tc = 1, fb = 0;
+    uint64_t cand = 0;
+    for (uint32_t q0 = 0; q0 < Q; q0 += COL_QCHUNK) {
+      const uint32_t qn = std::min(COL_QCHUNK, Q - q0);
+      int rc = column_topk(c, metric, d_q + (size_t)q0 * c->dim, qn, k, has_lower, lower, has_upper, upper, d_od + (size_t)q0 * k,
+                           d_oi + (size_t)q0 * k, d_oc + q0, st);
+      if (rc) return rc;
+      tc &= c->last_tc; fb |= c->last_fallback; cand += c->last_candidates;
+    }
+    c->last_tc = tc; c->last_fallback = fb; c->last_candidates = cand;
+    return 0;
+  }
   const uint64_t n = c->n;
   const uint32_t dim = c->dim;
   // expected candidates per query ~ k n / ns (rows below the sample's k-th distance); 4x head-room
@@ -96,10 +112,11 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   if (!use_tc)
     return flat_topk_device_impl(metric, dim, d_q, Q, c->d_v, c->d_valid, n, k, has_lower, lower, has_upper, upper, d_od, d_oi, d_oc, st);
   const uint32_t Qpad = (Q + FTC_M - 1) / FTC_M * FTC_M;
+  const uint32_t ns = c->ns;
   size_t need = 0;
   auto add = [&](size_t b) { need += Arena::pad(b) + 256; };
   add((size_t)Qpad * dim * 2); add((size_t)Qpad * 8); add((size_t)Qpad * 4); add((size_t)Qpad * cap * 4); add((size_t)Qpad * 4);
-  add((size_t)Q * cap * 8); add((size_t)Q * cap * 4); add(64); add((size_t)Q * k * 4); add((size_t)Q * k * 8); add((size_t)Q * 4);
+  add((size_t)Q * cap * 8); add((size_t)Q * cap * 4); add(64); add((size_t)Q * ns * 4); add((size_t)Q * 4);
   int rc = c->scratch.reserve(need);
   if (rc) return rc;
   c->scratch.reset();
@@ -111,13 +128,12 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   uint64_t* d_pos = c->scratch.take<uint64_t>((size_t)Q * cap);
   float* d_exact = c->scratch.take<float>((size_t)Q * cap);
   uint32_t* d_flag = c->scratch.take<uint32_t>(16);
-  float* d_sd = c->scratch.take<float>((size_t)Q * k);
-  uint64_t* d_si = c->scratch.take<uint64_t>((size_t)Q * k);
-  uint32_t* d_sc = c->scratch.take<uint32_t>(Q);
-  // (1) thresholds: exact top-k of every query over the sample rows
-  rc = flat_topk_device_impl(metric, dim, d_q, Q, c->d_sample, nullptr, c->ns, k, false, 0.f, false, 0.f, d_sd, d_si, d_sc, st);
-  if (rc) return rc;
-  ftc_threshold_kernel<<<(Qpad + 255) / 256, 256, 0, st>>>(d_sd, d_sc, Q, Qpad, k, d_thr, d_cnt);
+  float* d_sd = c->scratch.take<float>((size_t)Q * ns);
+  uint32_t* d_raw = c->scratch.take<uint32_t>(Q);
+  // (1) thresholds: exact distances of every query to the sample rows, k-th smallest per query
+  if ((rc = flat_dist_launch(metric, d_q, Q, c->d_sample, nullptr, ns, dim, d_sd, ns, st))) return rc;
+  static_assert(COL_SAMPLE == 256 * 64, "ftc_kth_kernel<64> holds the sample in 64 registers per thread");
+  ftc_kth_kernel<64><<<Qpad, 256, 0, st>>>(d_sd, ns, Q, k, d_thr, d_cnt);
   // (2) queries -> bf16 + norms (padding rows zero)
   CK(cudaMemsetAsync(d_qb, 0, (size_t)Qpad * dim * 2, st));
   CK(cudaMemsetAsync(d_qn, 0, (size_t)Qpad * 8, st));
@@ -140,13 +156,14 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   flat_tc_filter_kernel<<<grid, FTC_THREADS, smem, st>>>(map_q, c->map_v, p);
   CK(cudaGetLastError());
   // (4) exact re-score of the kept rows, top k by (distance, row index)
-  ftc_finish_kernel<<<(uint32_t)(((uint64_t)Q * cap + 255) / 256), 256, 0, st>>>(d_cand, d_cnt, Q, cap, d_pos, d_flag);
+  ftc_clamp_kernel<<<(Q + 255) / 256, 256, 0, st>>>(d_cnt, Q, cap, d_raw, d_flag);
   std::vector<uint32_t> h_cnt(Q);
   uint32_t h_flag = 0;
-  CK(cudaMemcpyAsync(h_cnt.data(), d_cnt, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(h_cnt.data(), d_raw, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(&h_flag, d_flag, 4, cudaMemcpyDeviceToHost, st));
-  ftc_clamp_kernel<<<(Q + 255) / 256, 256, 0, st>>>(d_cnt, Q, cap);
-  refine_distance_kernel<<<(uint32_t)(((size_t)Q * cap + 127) / 128), 128, 0, st>>>(metric, d_q, c->d_v, dim, d_pos, d_cnt, Q, cap, d_exact);
+  dim3 rgrid(std::max(1u, std::min(cap / 16, (uint32_t)(8 * c->sm_count + Q - 1) / Q)), Q);
+  ftc_rescore_l2_kernel<<<rgrid, 256, 0, st>>>(d_q, c->d_v, dim, d_cand, d_cnt, cap, d_exact, d_pos);
+  ftc_prune_kernel<<<Q, 256, 0, st>>>(d_exact, d_pos, d_cnt, cap, k);
   CK(cudaGetLastError());
   rc = launch_merge(d_exact, d_pos, nullptr, nullptr, d_cnt, Q, 1, cap, cap, cap, 1, 1, k, k, d_od, d_oi, nullptr, nullptr, d_oc, st);
   if (rc) return rc;
@@ -172,6 +189,7 @@ extern "C" void lb200_column_destroy(lb200_column* c) {
   cudaFree(c->d_norm);
   cudaFree(c->d_sample);
   c->scratch.release();
+  c->io.release();
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -260,15 +278,15 @@ extern "C" int32_t lb200_column_flat_topk(lb200_column* c, int32_t metric, const
   if (k == 0) return set_err(LB200_EINVAL, "k must be > 0");
   if (!Q) return 0;
   if (!out_dist || !out_idx || !out_count) return set_err(LB200_EINVAL, "null output");
-  HostStage hs;
   CK(cudaSetDevice(c->device));
+  std::lock_guard<std::mutex> lk(c->io_mu);
   const size_t bq = Arena::pad((size_t)Q * c->dim * 4), bod = Arena::pad((size_t)Q * k * 4), boi = Arena::pad((size_t)Q * k * 8);
-  CK(cudaMalloc(&hs.p, bq + bod + boi + Arena::pad((size_t)Q * 4)));
-  char* b = (char*)hs.p;
-  float* d_q = (float*)b;
-  float* d_od = (float*)(b + bq);
-  uint64_t* d_oi = (uint64_t*)(b + bq + bod);
-  uint32_t* d_oc = (uint32_t*)(b + bq + bod + boi);
+  if ((rc = c->io.reserve(bq + bod + boi + Arena::pad((size_t)Q * 4) + 1024))) return rc;
+  c->io.reset();
+  float* d_q = c->io.take<float>((size_t)Q * c->dim);
+  float* d_od = c->io.take<float>((size_t)Q * k);
+  uint64_t* d_oi = c->io.take<uint64_t>((size_t)Q * k);
+  uint32_t* d_oc = c->io.take<uint32_t>(Q);
   CK(cudaMemcpy(d_q, queries, (size_t)Q * c->dim * 4, cudaMemcpyHostToDevice));
   rc = lb200_column_flat_topk_device(c, metric, d_q, Q, k, lower_or_null, upper_or_null, d_od, d_oi, d_oc, nullptr);
   if (rc) return rc;

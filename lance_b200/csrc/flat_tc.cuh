@@ -20,6 +20,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "dist.cuh"
+
 namespace lb200 {
 
 constexpr uint32_t FTC_M = 128;        // queries per CTA (TMEM lanes)
@@ -193,23 +195,24 @@ flat_tc_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
               "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
             : "r"(taddr) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        const float4* nb4 = reinterpret_cast<const float4*>(nb + c0);
-        float mn0 = __int_as_float(0x7f800000), mn1 = mn0;
+        // one bit per row that passes; a few rows of a thousand do, so nearly every WARP has some lane with a bit
+        // set in a group of 32 rows -- the test must not branch per row
+        const uint32_t nb_addr = ftc_smem(nb + c0);
+        uint32_t mask = 0;
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {   // one LDS.128 (a broadcast) brings the norms of two rows
-          const float4 y2 = nb4[j >> 1];
-          mn0 = fminf(mn0, fmaf(ne1q, y2.y, fmaf(-2.0f, __uint_as_float(v[j]), y2.x)));
-          mn1 = fminf(mn1, fmaf(ne1q, y2.w, fmaf(-2.0f, __uint_as_float(v[j + 1]), y2.z)));
+          float4 y2;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(y2.x), "=f"(y2.y), "=f"(y2.z), "=f"(y2.w) : "r"(nb_addr + j * 8));
+          const float g0 = fmaf(ne1q, y2.y, fmaf(-2.0f, __uint_as_float(v[j]), y2.x));
+          const float g1 = fmaf(ne1q, y2.w, fmaf(-2.0f, __uint_as_float(v[j + 1]), y2.z));
+          mask |= g0 <= cq ? 1u << j : 0u;
+          mask |= g1 <= cq ? 2u << j : 0u;
         }
-        if (fminf(mn0, mn1) <= cq) {        // rare (a few rows of a thousand pass): find which
-#pragma unroll
-          for (int j = 0; j < 32; j++) {
-            const float2 yn = nb[c0 + j];
-            if (fmaf(ne1q, yn.y, fmaf(-2.0f, __uint_as_float(v[j]), yn.x)) <= cq) {
-              const uint32_t pos = atomicAdd(p.cand_cnt + qi, 1u);
-              if (pos < p.cap) p.cand[(size_t)qi * p.cap + pos] = row_cur + c0 + j;
-            }
-          }
+        while (mask) {
+          const uint32_t j = __ffs(mask) - 1;
+          mask &= mask - 1;
+          const uint32_t pos = atomicAdd(p.cand_cnt + qi, 1u);
+          if (pos < p.cap) p.cand[(size_t)qi * p.cap + pos] = row_cur + c0 + j;
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -256,30 +259,209 @@ __global__ void gather_rows_kernel(const float* __restrict__ x, uint64_t stride_
   out[i] = x[r * stride_rows * dim + (i - r * dim)];
 }
 
-// per query: threshold = exact k-th distance over the sample (+inf when the sample holds fewer than k admissible rows);
-// padding queries get -inf.  Also clears the candidate counters.
-__global__ void ftc_threshold_kernel(const float* __restrict__ sample_dist /*[Q][k]*/, const uint32_t* __restrict__ sample_cnt,
-                                     uint32_t Q, uint32_t Qpad, uint32_t k, float* __restrict__ thr, uint32_t* __restrict__ cnt) {
-  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= Qpad) return;
-  cnt[q] = 0;
-  if (q >= Q) thr[q] = __int_as_float(0xff800000);
-  else thr[q] = sample_cnt[q] >= k ? sample_dist[(size_t)q * k + k - 1] : __int_as_float(0x7f800000);
+// per query: threshold T_q = the exact k-th smallest of its ns sample distances (radix select over the order-preserving
+// u32 keys of dist.cuh, 8 bits per pass, values held in registers); padding queries get -inf.  Also clears the
+// candidate counters.  One block of 256 threads per query, ns = 256 * PER.
+template <int PER>
+__global__ void __launch_bounds__(256)
+ftc_kth_kernel(const float* __restrict__ D /*[Q][stride]*/, size_t stride, uint32_t Q, uint32_t k, float* __restrict__ thr,
+               uint32_t* __restrict__ cnt) {
+  __shared__ uint32_t hist[8][256];
+  __shared__ uint32_t s_digit, s_k;
+  const uint32_t q = blockIdx.x, t = threadIdx.x, w = t >> 5, lane = t & 31;
+  if (t == 0) cnt[q] = 0;
+  if (q >= Q) {
+    if (t == 0) thr[q] = __int_as_float(0xff800000);
+    return;
+  }
+  uint32_t key[PER];
+#pragma unroll
+  for (int i = 0; i < PER; i++) key[i] = ordered_key(D[(size_t)q * stride + (size_t)i * 256 + t]);
+  uint32_t prefix = 0, pmask = 0, kk = k;
+#pragma unroll 1
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (uint32_t i = t; i < 8 * 256; i += 256) (&hist[0][0])[i] = 0;
+    __syncthreads();
+    // runs of equal digits are counted in registers first: the top bits of a query's distances are nearly all alike
+    uint32_t run_d = 0xffffffffu, run_c = 0;
+#pragma unroll
+    for (int i = 0; i < PER; i++) {
+      if ((key[i] & pmask) == prefix) {
+        const uint32_t dg = (key[i] >> shift) & 255u;
+        if (dg == run_d) run_c++;
+        else {
+          if (run_c) atomicAdd(&hist[w][run_d], run_c);
+          run_d = dg;
+          run_c = 1;
+        }
+      }
+    }
+    if (run_c) atomicAdd(&hist[w][run_d], run_c);
+    __syncthreads();
+    uint32_t tot = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) tot += hist[j][t];
+    __syncthreads();
+    hist[0][t] = tot;
+    __syncthreads();
+    if (w == 0) {  // lane owns bins 8 lane .. 8 lane + 7
+      uint32_t c8[8], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 8; j++) { c8[j] = hist[0][lane * 8 + j]; sum += c8[j]; }
+      uint32_t incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (uint32_t)o) incl += v;
+      }
+      uint32_t before = incl - sum;
+      if (before < kk && kk <= incl) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          if (before < kk && kk <= before + c8[j]) { s_digit = lane * 8 + j; s_k = kk - before; }
+          before += c8[j];
+        }
+      }
+    }
+    __syncthreads();
+    prefix |= s_digit << shift;
+    pmask |= 255u << shift;
+    kk = s_k;
+    __syncthreads();
+  }
+  if (t == 0) thr[q] = key_to_float(prefix);
 }
 
-// clamp the candidate counts to cap, flag overflow, and widen the indices to the u64 positions the exact kernels take
-__global__ void ftc_finish_kernel(const uint32_t* __restrict__ cand, uint32_t* __restrict__ cnt, uint32_t Q, uint32_t cap,
-                                  uint64_t* __restrict__ pos, uint32_t* __restrict__ overflow) {
-  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (uint64_t)Q * cap) return;
-  const uint32_t q = (uint32_t)(i / cap), j = (uint32_t)(i - (uint64_t)q * cap);
-  const uint32_t c = cnt[q];
-  if (j == 0 && c > cap) atomicExch(overflow, 1u);
-  pos[i] = j < min(c, cap) ? (uint64_t)cand[i] : ~0ull;
+// exact L2 of the kept rows: l2_scalar::<f32,f32,16> (distance/l2.rs:65-99) with its 16 lane sums on 16 THREADS -- thread
+// i of a half-warp owns sums[i] (sub, mul, add per 16-element chunk, in chunk order), then the lanes are added in lane
+// order.  The half-warp reads 64 contiguous bytes of the row per chunk.  dim % 16 == 0, dim <= 256.
+// grid (blocks per query, Q), 256 threads = 16 half-warps striding over the query's kept rows.
+__global__ void __launch_bounds__(256)
+ftc_rescore_l2_kernel(const float* __restrict__ queries, const float* __restrict__ rows, uint32_t dim, const uint32_t* __restrict__ cand,
+                      const uint32_t* __restrict__ cnt, uint32_t cap, float* __restrict__ exact /*[Q][cap]*/,
+                      uint64_t* __restrict__ pos /*[Q][cap]*/) {
+  const uint32_t q = blockIdx.y, hl = threadIdx.x & 15, hw = threadIdx.x >> 4;
+  const uint32_t n = min(cnt[q], cap), nchunk = dim >> 4;
+  float xq[16];
+#pragma unroll
+  for (int c = 0; c < 16; c++) xq[c] = (uint32_t)c < nchunk ? queries[(size_t)q * dim + c * 16 + hl] : 0.0f;
+  for (uint32_t i0 = blockIdx.x * 16; i0 < n; i0 += gridDim.x * 16) {   // n is uniform over the block
+    const uint32_t i = i0 + hw;
+    const bool live = i < n;
+    const uint32_t r = live ? cand[(size_t)q * cap + i] : 0;
+    const float* y = rows + (size_t)r * dim + hl;
+    float yv[16];
+#pragma unroll
+    for (int c = 0; c < 16; c++) yv[c] = live && (uint32_t)c < nchunk ? __ldg(y + c * 16) : 0.0f;
+    float sum = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 16; c++)
+      if ((uint32_t)c < nchunk) {
+        const float df = __fsub_rn(xq[c], yv[c]);
+        sum = __fadd_rn(sum, __fmul_rn(df, df));
+      }
+    float tt = 0.0f;
+#pragma unroll
+    for (int l = 0; l < 16; l++) tt = __fadd_rn(tt, __shfl_sync(0xffffffffu, sum, l, 16));
+    if (hl == 0 && live) {
+      exact[(size_t)q * cap + i] = __fadd_rn(0.0f, tt);   // l2_scalar's `s + t` with an empty remainder
+      pos[(size_t)q * cap + i] = (uint64_t)r;
+    }
+  }
 }
-__global__ void ftc_clamp_kernel(uint32_t* __restrict__ cnt, uint32_t Q, uint32_t cap) {
+
+// before the final (distance, row) sort: drop the re-scored rows that cannot be among the k smallest.  Radix select of
+// the k-th smallest exact distance of the query (keys re-read from L2 per pass), then the rows with distance <= that
+// (the k smallest and every tie of the k-th) are packed to the front of the query's list, in place through shared
+// memory.  A query with more than PRUNE_MAX survivors (a sea of equal distances) keeps its whole list.
+constexpr uint32_t PRUNE_MAX = 2048;
+__global__ void __launch_bounds__(256)
+ftc_prune_kernel(float* __restrict__ exact /*[Q][cap]*/, uint64_t* __restrict__ pos, uint32_t* __restrict__ cnt, uint32_t cap, uint32_t k) {
+  __shared__ uint32_t hist[8][256];
+  __shared__ uint32_t s_digit, s_k, s_m;
+  __shared__ float keep_d[PRUNE_MAX];
+  __shared__ uint64_t keep_p[PRUNE_MAX];
+  const uint32_t q = blockIdx.x, t = threadIdx.x, w = t >> 5, lane = t & 31;
+  const uint32_t n = cnt[q];
+  if (n <= k || n <= 32) return;
+  float* ex = exact + (size_t)q * cap;
+  uint64_t* ps = pos + (size_t)q * cap;
+  uint32_t prefix = 0, pmask = 0, kk = k;
+#pragma unroll 1
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (uint32_t i = t; i < 8 * 256; i += 256) (&hist[0][0])[i] = 0;
+    __syncthreads();
+    uint32_t run_d = 0xffffffffu, run_c = 0;
+    for (uint32_t i = t; i < n; i += 256) {
+      const uint32_t key = ordered_key(ex[i]);
+      if ((key & pmask) == prefix) {
+        const uint32_t dg = (key >> shift) & 255u;
+        if (dg == run_d) run_c++;
+        else {
+          if (run_c) atomicAdd(&hist[w][run_d], run_c);
+          run_d = dg;
+          run_c = 1;
+        }
+      }
+    }
+    if (run_c) atomicAdd(&hist[w][run_d], run_c);
+    __syncthreads();
+    uint32_t tot = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) tot += hist[j][t];
+    __syncthreads();
+    hist[0][t] = tot;
+    __syncthreads();
+    if (w == 0) {
+      uint32_t c8[8], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 8; j++) { c8[j] = hist[0][lane * 8 + j]; sum += c8[j]; }
+      uint32_t incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (uint32_t)o) incl += v;
+      }
+      uint32_t before = incl - sum;
+      if (before < kk && kk <= incl) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          if (before < kk && kk <= before + c8[j]) { s_digit = lane * 8 + j; s_k = kk - before; }
+          before += c8[j];
+        }
+      }
+    }
+    __syncthreads();
+    prefix |= s_digit << shift;
+    pmask |= 255u << shift;
+    kk = s_k;
+    __syncthreads();
+  }
+  if (t == 0) s_m = 0;
+  __syncthreads();
+  for (uint32_t i = t; i < n; i += 256) {
+    const float d = ex[i];
+    if (ordered_key(d) <= prefix) {
+      const uint32_t o = atomicAdd(&s_m, 1u);
+      if (o < PRUNE_MAX) { keep_d[o] = d; keep_p[o] = ps[i]; }
+    }
+  }
+  __syncthreads();
+  const uint32_t m = s_m;
+  if (m > PRUNE_MAX) return;
+  for (uint32_t i = t; i < m; i += 256) { ex[i] = keep_d[i]; ps[i] = keep_p[i]; }
+  if (t == 0) cnt[q] = m;
+}
+
+// clamp the candidate counts to cap and flag overflow
+__global__ void ftc_clamp_kernel(uint32_t* __restrict__ cnt, uint32_t Q, uint32_t cap, uint32_t* __restrict__ raw_cnt,
+                                 uint32_t* __restrict__ overflow) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q < Q) cnt[q] = min(cnt[q], cap);
+  if (q >= Q) return;
+  const uint32_t c = cnt[q];
+  raw_cnt[q] = c;
+  if (c > cap) atomicExch(overflow, 1u);
+  cnt[q] = min(c, cap);
 }
 
 }  // namespace lb200
