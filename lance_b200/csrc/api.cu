@@ -187,6 +187,7 @@ struct lb200_index {
   uint64_t* d_sb_off = nullptr;        // [nlist+1] first superblock per partition
   uint32_t skew_L = 0, skew_D = 0;     // superblock = 32*skew_L rows; lane delay period
   std::vector<uint64_t> h_part_off;
+  std::vector<uint32_t> h_perm;   // 4-bit / IVF_FLAT handles: sorted row position -> the caller's position in its partition
   cudaStream_t stream = nullptr;  // create-time uploads and the peer-table set-up
   std::mutex mu;                  // guards stats, pthr_* and the admin calls (never held across a search)
   std::vector<CallCtx*> ctxs;     // pool of per-call contexts (LB200_CTX_POOL, default 16)

@@ -11,11 +11,9 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
   if (a.k == 0) return set_err(LB200_EINVAL, "k must be > 0");
   if (kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", kprime);
   const bool flat = ix->bits == 32;
-  if (a.shard_mode) return set_err(LB200_EUNSUPPORTED, "4-bit PQ / IVF_FLAT: sharded search is not supported yet");
-  if (a.d_bitmask) return set_err(LB200_EUNSUPPORTED, "4-bit PQ / IVF_FLAT: prefilter bitmasks are not supported yet");
   if (P == 0 || Q == 0) return 0;
   const bool refine = a.refine_factor > 0 && ix->d_raw != nullptr && !a.per_pair_output;
-  if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output)
+  if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output && !(a.shard_mode && ix->N == 0))
     return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
   if (!a.per_pair_output && (uint64_t)P * kprime > 16384)
     return set_err(LB200_EUNSUPPORTED, "4-bit PQ: nprobes*k'=%llu > 16384", (unsigned long long)P * kprime);
@@ -29,7 +27,8 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
   const uint32_t nbins = (M / 2) * 510 + 1;
   const size_t fsmem = ((size_t)dim + (size_t)M * 16 + ((M + 1) & ~1u)) * 4 + (size_t)kp2 * 8 + (size_t)((nbins + 1) & ~1u) * 4 + (size_t)M * 16 +
                        (size_t)(M / 2) * 256 + 4096 * 2;
-  const bool fused = !flat && fsmem <= ix->smem_optin && !getenv("LB200_PQ4_SIMPLE");
+  // (a prefilter switches the reference to per-row distances on the unquantised table: scan4_kernel's masked path)
+  const bool fused = !flat && fsmem <= ix->smem_optin && !getenv("LB200_PQ4_SIMPLE") && !a.d_bitmask;
   size_t need = 0;
   auto add = [&](size_t b) { need += Arena::pad(b) + 256; };
   add((size_t)Q * dim * 4); add((size_t)Q * nlist * 4); add(npairs * 4); add(64);
@@ -101,14 +100,14 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
       if (ix->metric == LB200_L2 && !getenv("LB200_FLAT_SIMPLE")) {
         if (fs > 48 * 1024) CK(cudaFuncSetAttribute(scanflat_l2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs));
         scanflat_l2_kernel<<<(uint32_t)pn, 256, fs, st>>>(keys + (size_t)q0 * dim, probes + p0, P, dim, ix->d_part_off,
-                                                           ix->d_raw, d_dist, stride, d_stats);
+                                                           ix->d_raw, d_dist, stride, d_stats, a.d_bitmask);
       } else
       scanflat_kernel<<<(uint32_t)pn, 256, fs, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim,
-                                                      ix->d_part_off, ix->d_raw, d_dist, stride, d_stats);
+                                                      ix->d_part_off, ix->d_raw, d_dist, stride, d_stats, a.d_bitmask);
     } else {
       scan4_kernel<<<(uint32_t)pn, 256, smem, st>>>(ix->metric, keys + (size_t)q0 * dim, probes + p0, P, dim, M,
                                                      ix->d_centroids, ix->d_codebook, ix->d_part_off, ix->d_pad_off,
-                                                     ix->d_codes4, ix->d_tail4, d_dist, stride, d_stats);
+                                                     ix->d_codes4, ix->d_tail4, d_dist, stride, d_stats, a.d_bitmask);
     }
     CK(cudaGetLastError());
     flat_select_kernel<<<(uint32_t)pn, 256, (size_t)kp2 * 8, st>>>(d_dist, stride, stride, 1, stride, kprime, kp2,
@@ -125,13 +124,27 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
     launches++;
   }
   if (!a.per_pair_output) {
-    const bool direct = !refine;
+    const bool direct = !refine && !a.shard_mode;
     rc = launch_merge(d_sdist, d_srow, d_spos, nullptr, d_scnt, Q, P, kprime, (size_t)P * kprime, kprime, P, 1, kprime,
                       kprime, direct ? a.d_out_dist : d_mdist, direct ? a.d_out_rowid : d_mrow, d_mpos, nullptr,
                       direct ? a.d_out_count : d_mcnt, st);
     if (rc) return rc;
     launches++;
-    if (refine) {
+    if (a.shard_mode) {
+      // a shard's answer: its merged k' list before the final cut, plus the exact distances when it refines
+      // (same contract as the 8-bit pipeline; the outputs may be peer memory of the root shard)
+      if (refine) {
+        refine_distance_kernel<<<(uint32_t)(((size_t)Q * kprime + 127) / 128), 128, 0, st>>>(
+            ix->metric, a.d_queries, ix->d_raw, dim, d_mpos, d_mcnt, Q, kprime, a.d_out_exact);
+        CK(cudaGetLastError());
+        launches++;
+      } else {
+        CK(cudaMemsetAsync(a.d_out_exact, 0xff, (size_t)Q * kprime * 4, st));  // NaN
+      }
+      CK(cudaMemcpyAsync(a.d_out_dist, d_mdist, (size_t)Q * kprime * 4, cudaMemcpyDefault, st));
+      CK(cudaMemcpyAsync(a.d_out_rowid, d_mrow, (size_t)Q * kprime * 8, cudaMemcpyDefault, st));
+      CK(cudaMemcpyAsync(a.d_out_count, d_mcnt, (size_t)Q * 4, cudaMemcpyDefault, st));
+    } else if (refine) {
       refine_distance_kernel<<<(uint32_t)(((size_t)Q * kprime + 127) / 128), 128, 0, st>>>(
           ix->metric, a.d_queries, ix->d_raw, dim, d_mpos, d_mcnt, Q, kprime, d_exact);
       CK(cudaGetLastError());
@@ -206,6 +219,7 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
   std::vector<uint8_t> h_tail((size_t)N);
   std::vector<float> h_raw(raw ? (size_t)N * dim : 0);
   std::vector<uint32_t> perm;
+  ix->h_perm.resize((size_t)N);  // sorted position -> the caller's position in its partition (prefilter bit order)
   uint32_t nonempty = 0;
   for (uint32_t p = 0; p < nlist; p++) {
     const uint64_t o = part_offsets[p], n = part_offsets[p + 1] - o;
@@ -219,6 +233,7 @@ int create_index4(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlis
     uint8_t* dst = h_codes.data() + pad_off[p] * cb;
     const uint64_t blocks = n >= 16 ? n - (n & 15) : 0;  // rows the reference runs through u8x16 (distance.rs:158)
     for (uint64_t i = 0; i < n; i++) {
+      ix->h_perm[o + i] = perm[i];
       h_rid[o + i] = row_ids[o + perm[i]];
       h_tail[o + i] = perm[i] >= blocks;
       for (uint32_t j = 0; j < cb; j++) dst[(size_t)j * npad + i] = src[(size_t)j * n + perm[i]];
@@ -290,6 +305,7 @@ int create_index_flat(int32_t device_id, int32_t metric, uint32_t dim, uint32_t 
   std::vector<uint64_t> h_rid((size_t)N);
   std::vector<float> h_raw((size_t)N * dim);
   std::vector<uint32_t> perm;
+  ix->h_perm.resize((size_t)N);  // sorted position -> the caller's position in its partition (prefilter bit order)
   uint32_t nonempty = 0;
   for (uint32_t p = 0; p < nlist; p++) {
     const uint64_t o = part_offsets[p], n = part_offsets[p + 1] - o;
@@ -299,6 +315,7 @@ int create_index_flat(int32_t device_id, int32_t metric, uint32_t dim, uint32_t 
     for (uint64_t i = 0; i < n; i++) perm[i] = (uint32_t)i;
     std::stable_sort(perm.begin(), perm.end(), [&](uint32_t x, uint32_t y) { return row_ids[o + x] < row_ids[o + y]; });
     for (uint64_t i = 0; i < n; i++) {
+      ix->h_perm[o + i] = perm[i];
       h_rid[o + i] = row_ids[o + perm[i]];
       memcpy(h_raw.data() + (o + i) * dim, raw + (o + perm[i]) * dim, (size_t)dim * 4);
     }

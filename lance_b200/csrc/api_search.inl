@@ -659,11 +659,28 @@ extern "C" int32_t lb200_find_partitions(lb200_index* ix, const float* queries, 
 }
 
 // ---- prefilter objects ----------------------------------------------------------------------------
+namespace {
+// the allow bits of partition p in the handle's row order.  8-bit handles keep the caller's order; 4-bit and
+// IVF_FLAT handles sort a partition's rows by row id at create time (h_perm: sorted position -> caller's position)
+static void put_mask_words(const lb200_index* ix, uint32_t p, const uint64_t* src, uint64_t* dst) {
+  const uint64_t o = ix->h_part_off[p], n = ix->h_part_off[p + 1] - o;
+  const size_t nw = (size_t)((n + 63) / 64);
+  if (ix->h_perm.empty()) {
+    memcpy(dst, src, nw * 8);
+    return;
+  }
+  memset(dst, 0, nw * 8);
+  for (uint64_t i = 0; i < n; i++) {
+    const uint32_t s = ix->h_perm[o + i];
+    if ((src[s >> 6] >> (s & 63)) & 1) dst[i >> 6] |= 1ull << (i & 63);
+  }
+}
+}  // namespace
+
 extern "C" int32_t lb200_prefilter_create(lb200_index* ix, const uint64_t* const* part_bitmask, lb200_prefilter** out) {
   if (!out) return set_err(LB200_EINVAL, "null output");
   *out = nullptr;
   if (!ix || !part_bitmask) return set_err(LB200_EINVAL, "null argument");
-  if (ix->bits != 8) return set_err(LB200_EUNSUPPORTED, "prefilter bitmasks are supported on 8-bit PQ handles only");
   CK(cudaSetDevice(ix->device));
   const uint32_t nlist = ix->nlist;
   size_t words = 0;
@@ -688,7 +705,7 @@ extern "C" int32_t lb200_prefilter_create(lb200_index* ix, const uint64_t* const
     if (!part_bitmask[p]) continue;
     const size_t nw = (size_t)((ix->h_part_off[p + 1] - ix->h_part_off[p] + 63) / 64);
     h[p] = (uint64_t)(uintptr_t)(pf->base + w * 8);
-    memcpy(h.data() + w, part_bitmask[p], nw * 8);  // + one zero word: the scan may test one row past a ragged end
+    put_mask_words(ix, p, part_bitmask[p], h.data() + w);  // + one zero word: the scan may test one row past a ragged end
     w += nw + 1;
   }
   e = cudaMemcpy(pf->base, h.data(), total, cudaMemcpyHostToDevice);
@@ -730,8 +747,6 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
   for (size_t i = 0; i < npairs; i++)
     if (part_ids[i] >= nlist)  // ivf/v2.rs:288-293 "partition centroid {} does not exist"
       return set_err(LB200_EINVAL, "partition centroid %u does not exist", part_ids[i]);
-  if ((host_masks || pf) && ix->bits != 8)
-    return set_err(LB200_EUNSUPPORTED, "prefilter bitmasks are supported on 8-bit PQ handles only");
   CtxLease ls;
   if ((rc = ls.acquire(ix, nullptr))) return rc;
   CallCtx& cx = *ls.cx;
@@ -831,7 +846,7 @@ static int search_partitions_impl(lb200_index* ix, const float* queries, uint32_
     for (uint32_t p : mparts) {
       const size_t nw = (size_t)((ix->h_part_off[p + 1] - ix->h_part_off[p] + 63) / 64);
       tbl[p] = (uint64_t)(uintptr_t)(dbase + o_masks + w * 8);
-      memcpy(mw + w, host_masks[p], nw * 8);
+      put_mask_words(ix, p, host_masks[p], mw + w);
       mw[w + nw] = 0;
       w += nw + 1;
     }

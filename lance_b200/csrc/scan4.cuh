@@ -38,7 +38,7 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
              uint32_t M, const float* __restrict__ centroids, const float* __restrict__ codebook /*[M][16][dsub]*/,
              const uint64_t* __restrict__ part_off, const uint64_t* __restrict__ pad_off,
              const uint8_t* __restrict__ codes4p, const uint8_t* __restrict__ tail4, float* __restrict__ out,
-             size_t out_stride, unsigned long long* __restrict__ stats) {
+             size_t out_stride, unsigned long long* __restrict__ stats, const uint64_t* const* __restrict__ bitmask) {
   extern __shared__ float sm4[];
   float* r = sm4;                 // [dim] residual (or the key for dot)
   float* T = sm4 + dim;           // [M][16]
@@ -86,6 +86,28 @@ scan4_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restr
   const uint64_t npad = pad_off[p + 1] - pad_off[p];
   const uint8_t* cp = codes4p + pad_off[p] * (M / 2);
   float* orow = out + (size_t)pair * out_stride;
+  const uint64_t* bm = bitmask ? bitmask[p] : nullptr;
+  if (bm) {
+    // prefilter (flat/index.rs:106-122): only the allowed rows, each through PQDistCalculator::distance(id)
+    // (pq/storage.rs:602-617) -- the UNQUANTISED f32 table, pair sums added in ascending j
+    for (uint64_t i = tid; i < out_stride; i += 256) {
+      float v = __int_as_float(0x7fc00000);
+      if (i < n && ((bm[i >> 6] >> (i & 63)) & 1)) {
+        float sacc = 0.0f;
+        for (uint32_t j = 0; j < M / 2; j++) {
+          const uint8_t b = cp[(size_t)j * npad + i];
+          sacc = __fadd_rn(sacc, __fadd_rn(T[(2 * j) * 16 + (b & 15)], T[(2 * j + 1) * 16 + (b >> 4)]));
+        }
+        v = sacc;
+      }
+      orow[i] = v;
+    }
+    if (stats && tid == 0) {
+      atomicAdd(&stats[0], (unsigned long long)n * (M / 2));
+      atomicAdd(&stats[1], 1ull);
+    }
+    return;
+  }
   for (uint64_t i = tid; i < out_stride; i += 256) {
     float v = __int_as_float(0x7fc00000);
     if (i < n) {
@@ -465,7 +487,7 @@ scan4f_kernel(int metric, const float* __restrict__ keys, const uint32_t* __rest
 __global__ void __launch_bounds__(256)
 scanflat_kernel(int metric, const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
                 const uint64_t* __restrict__ part_off, const float* __restrict__ raw, float* __restrict__ out,
-                size_t out_stride, unsigned long long* __restrict__ stats) {
+                size_t out_stride, unsigned long long* __restrict__ stats, const uint64_t* const* __restrict__ bitmask) {
   extern __shared__ float smf[];  // [dim] key
   __shared__ float s_xn;
   const uint32_t pair = blockIdx.x, q = pair / P, p = probes[pair], tid = threadIdx.x;
@@ -476,8 +498,10 @@ scanflat_kernel(int metric, const float* __restrict__ keys, const uint32_t* __re
   const float xn = s_xn;
   const uint64_t off = part_off[p], n = part_off[p + 1] - off;
   float* orow = out + (size_t)pair * out_stride;
+  const uint64_t* bm = bitmask ? bitmask[p] : nullptr;  // prefilter: allowed rows only (flat/index.rs:106-122)
   for (uint64_t i = tid; i < out_stride; i += 256)
-    orow[i] = i < n ? exact_distance(metric, smf, xn, raw + (off + i) * dim, (int)dim) : __int_as_float(0x7fc00000);
+    orow[i] = i < n && (!bm || ((bm[i >> 6] >> (i & 63)) & 1)) ? exact_distance(metric, smf, xn, raw + (off + i) * dim, (int)dim)
+                                                                 : __int_as_float(0x7fc00000);
   if (stats && tid == 0) {
     atomicAdd(&stats[0], (unsigned long long)n * dim * 4);
     atomicAdd(&stats[1], 1ull);
@@ -491,7 +515,7 @@ scanflat_kernel(int metric, const float* __restrict__ keys, const uint32_t* __re
 __global__ void __launch_bounds__(256)
 scanflat_l2_kernel(const float* __restrict__ keys, const uint32_t* __restrict__ probes, uint32_t P, uint32_t dim,
                    const uint64_t* __restrict__ part_off, const float* __restrict__ raw, float* __restrict__ out,
-                   size_t out_stride, unsigned long long* __restrict__ stats) {
+                   size_t out_stride, unsigned long long* __restrict__ stats, const uint64_t* const* __restrict__ bitmask) {
   extern __shared__ float smf[];  // [dim] key
   const uint32_t pair = blockIdx.x, q = pair / P, p = probes[pair], tid = threadIdx.x;
   for (uint32_t i = tid; i < dim; i += 256) smf[i] = keys[(size_t)q * dim + i];
@@ -500,6 +524,7 @@ scanflat_l2_kernel(const float* __restrict__ keys, const uint32_t* __restrict__ 
   float* orow = out + (size_t)pair * out_stride;
   const uint32_t hw = tid >> 4, l = tid & 15;
   const uint32_t nchunk = dim >> 4, rem0 = nchunk << 4;
+  const uint64_t* bm = bitmask ? bitmask[p] : nullptr;  // prefilter: rows that are not allowed come out as NaN
   for (uint64_t i = n + tid; i < out_stride; i += 256) orow[i] = __int_as_float(0x7fc00000);  // padding of the scratch row
   constexpr int RW = 4;  // rows per half-warp step: RW independent load streams
   for (uint64_t base = 0; base < n; base += 16 * RW) {   // uniform trip count
@@ -534,7 +559,8 @@ scanflat_l2_kernel(const float* __restrict__ keys, const uint32_t* __restrict__ 
       float t = 0.0f;
 #pragma unroll
       for (int i = 0; i < 16; i++) t = __fadd_rn(t, __shfl_sync(0xffffffffu, a[k], i, 16));
-      if (l == 0 && r[k] < n) orow[r[k]] = __fadd_rn(sr[k], t);
+      if (l == 0 && r[k] < n)
+        orow[r[k]] = !bm || ((bm[r[k] >> 6] >> (r[k] & 63)) & 1) ? __fadd_rn(sr[k], t) : __int_as_float(0x7fc00000);
     }
   }
   if (stats && tid == 0) {

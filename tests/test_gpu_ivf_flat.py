@@ -72,6 +72,65 @@ def test_ivf_flat_search_parity(oracle, metric, d):
     ix.close()
 
 
+@pytest.mark.parametrize("metric,d", [("l2", 128), ("l2", 20), ("cosine", 96), ("dot", 70)])
+def test_ivf_flat_prefilter_and_shards(oracle, metric, d):
+    """FlatIndex::search with a prefilter (flat/index.rs:106-122) on IVF_FLAT handles, as host masks and as a
+    device-resident Prefilter; then the shard contract (merged k' list + exact distances) against the whole index."""
+    from lance_b200 import IvfPqIndex
+    from lance_b200.index import merge_topk_device
+    from lance_b200.shard import assign_partitions
+    sizes = [50, 0, 1, 300, 17, 1200, 64]
+    data = _flat_index(metric, d, sizes, seed=d + 1)
+    rng = np.random.default_rng(2)
+    q = np.concatenate([data.raw_vectors[::311], rng.normal(size=(3, d)).astype(np.float32)])
+    key = np.stack([oracle.normalize(x) for x in q]) if metric == "cosine" else q
+    ix = IvfPqIndex(data)
+    masks = {0: rng.random(50) < 0.5, 3: rng.random(300) < 0.05, 5: rng.random(1200) < 0.7, 6: np.zeros(64, bool)}
+    parts = np.tile(np.array([[5, 0, 3, 6, 4]], dtype=np.uint32), (len(q), 1))
+    pf = ix.prefilter(masks)
+    for how in (masks, pf):
+        od, oi, oc = ix.search_in_partition(parts, key, 9, prefilter=how)
+        for j in range(len(q)):
+            for c, p in enumerate(parts[j].tolist()):
+                o, e = int(data.part_offsets[p]), int(data.part_offsets[p + 1])
+                m = masks.get(p, np.ones(e - o, bool))
+                rd, rr = oracle.flat_knn_rows(metric, key[j], data.raw_vectors[o:e][m], data.row_ids[o:e][m], 9)
+                n = int(oc[j, c])
+                assert n == len(rr) and oi[j, c, :n].tolist() == rr.tolist(), (metric, j, p)
+                assert _bits(od[j, c, :n]).tolist() == _bits(rd).tolist()
+    pf.close()
+    ix.close()
+    G, k, nprobes, Q = 3, 10, 4, len(q)
+    owner = assign_partitions(np.asarray(sizes, dtype=np.int64), G)
+    dev = torch.device("cuda", 0)
+    dq = torch.from_numpy(q).to(dev)
+    for refine in (0, 2):
+        kp = k * max(refine, 1)
+        g_d = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
+        g_i = torch.empty((G, Q, kp), dtype=torch.int64, device=dev)
+        g_c = torch.empty((G, Q), dtype=torch.int32, device=dev)
+        g_e = torch.empty((G, Q, kp), dtype=torch.float32, device=dev)
+        shards = [IvfPqIndex(data.subset(np.nonzero(owner == g)[0])) for g in range(G)]
+        for g, sh in enumerate(shards):
+            sh.search_device(dq.data_ptr(), Q, nprobes, k, refine, g_d[g].data_ptr(), g_i[g].data_ptr(), g_c[g].data_ptr(),
+                             d_out_exact=g_e[g].data_ptr())
+        torch.cuda.synchronize()
+        fd = torch.empty((Q, k), dtype=torch.float32, device=dev)
+        fi = torch.empty((Q, k), dtype=torch.int64, device=dev)
+        fc = torch.empty((Q,), dtype=torch.int32, device=dev)
+        merge_topk_device(0, g_d.data_ptr(), g_i.data_ptr(), g_e.data_ptr() if refine else None, g_c.data_ptr(), G, Q, kp, kp,
+                          k, fd.data_ptr(), fi.data_ptr(), fc.data_ptr())
+        torch.cuda.synchronize()
+        fd, fi, fc = fd.cpu().numpy(), fi.cpu().numpy().astype(np.uint64), fc.cpu().numpy()
+        for j in range(Q):
+            rd, rr = oracle.ivf_flat_search(data, q[j], k, nprobes, refine or None)
+            n = int(fc[j])
+            assert n == len(rr) and fi[j, :n].tolist() == rr.tolist(), (metric, refine, j)
+            assert _bits(fd[j, :n]).tolist() == _bits(rd).tolist()
+        for sh in shards:
+            sh.close()
+
+
 def test_ivf_flat_needs_raw_vectors():
     from lance_b200 import IvfPqIndex, LanceB200Error
     data = _flat_index("l2", 8, [4, 4], seed=0)

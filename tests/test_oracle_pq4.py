@@ -154,3 +154,63 @@ def test_4bit_whole_path_recall_floor_of_the_reference(oracle, metric, floor):
     gt = set(np.lexsort((np.arange(n), exact))[:100].tolist())
     recall = len(gt & set(oi[0].tolist())) / 100.0
     assert recall >= floor, recall
+
+
+def _np_quantize_nonfinite(table):
+    """quantize_distance_table once more, this time with the NaN rules of the Rust calls spelled out: `fold(INF,
+    f32::min)` / `fold(-INF, f32::max)` skip NaN operands (f32::min/max return the other operand), `as u8` saturates and
+    sends NaN to 0 (distance.rs:209-229)."""
+    t = table.astype(np.float32)
+    qmin = np.float32(np.fmin.reduce(t.ravel(), initial=np.float32(np.inf)))
+    mx = np.fmax.reduce(t, axis=1, initial=np.float32(-np.inf)).astype(np.float32)
+    with np.errstate(all="ignore"):
+        qmax = np.float32(np.fmax.reduce((mx[:-1] + mx[1:]).astype(np.float32), initial=np.float32(-np.inf)))
+        v = np.ceil((t - qmin) * np.float32(255.0) / np.float32(qmax - qmin))
+    v = np.where(np.isnan(v), 0, np.clip(v, 0, 255))
+    return qmin, qmax, v.astype(np.uint8)
+
+
+@pytest.mark.parametrize("case", ["inf_entry", "nan_entry", "neg_inf_entry", "constant_table", "nan_row"])
+def test_4bit_non_finite_tables_keep_the_reference_arithmetic(oracle, case):
+    """What is kept for tables that are not finite: exactly what the reference's f32 expressions give, no guard.
+      +inf entry   -> qmax = +inf, every finite entry quantises to 0, the inf entry to NaN -> 0; all distances are
+                      0 * inf / 255 + qmin = NaN  (rows are then dropped by the NaN filter of the top-k)
+      NaN entry    -> skipped by min/max, quantised to 0: the other entries are unaffected
+      -inf entry   -> qmin = -inf: (d - qmin) = +inf for finite d -> 255; distances = S * inf / 255 + (-inf) = NaN
+      constant     -> qmax - qmin may be 0 only for M = 2 with ... (here: range > 0 because qmax adds two maxima);
+                      checked as an ordinary table
+    The C restatement and this numpy one must agree on every bit that is not a NaN payload."""
+    rng = np.random.default_rng(len(case))
+    M, n = 8, 100
+    table = rng.random(size=(M, 16)).astype(np.float32) * 10
+    if case == "inf_entry":
+        table[3, 5] = np.inf
+    elif case == "nan_entry":
+        table[2, 7] = np.nan
+    elif case == "neg_inf_entry":
+        table[1, 1] = -np.inf
+    elif case == "constant_table":
+        table[:] = 2.5
+    elif case == "nan_row":
+        table[4, :] = np.nan
+    codes = rng.integers(0, 256, size=(M // 2, n), dtype=np.uint8)
+    qmin, qmax, qt = oracle.quantize_distance_table(table)
+    wmin, wmax, wqt = _np_quantize_nonfinite(table)
+    assert np.array_equal(np.float32(qmin).view(np.uint32), wmin.view(np.uint32)) and np.array_equal(np.float32(qmax).view(np.uint32), wmax.view(np.uint32))
+    assert np.array_equal(qt, wqt)
+    blocks = n - n % 16
+    acc = np.zeros(n, dtype=np.float32)
+    for j in range(M // 2):
+        s = wqt[2 * j][codes[j] & 15].astype(np.uint16) + wqt[2 * j + 1][codes[j] >> 4].astype(np.uint16)
+        s[:blocks] &= 255
+        acc += s.astype(np.float32)
+    with np.errstate(all="ignore"):
+        want = (acc * np.float32(wmax - wmin) / np.float32(255.0) + wmin).astype(np.float32)
+    got = oracle.compute_pq_distance_4bit(table, codes)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    ok = ~np.isnan(want)
+    assert np.array_equal(got[ok].view(np.uint32), want[ok].view(np.uint32))
+    if case in ("inf_entry", "neg_inf_entry"):
+        assert np.isnan(got).all()
+    if case in ("nan_entry", "nan_row", "constant_table"):
+        assert np.isfinite(got).all()
