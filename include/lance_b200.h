@@ -365,6 +365,24 @@ int32_t lb200_flat_topk_device_noalloc(int32_t device_id, int32_t metric, uint32
                                        void* stream);
 uint64_t lb200_noalloc_scratch_bytes(void);
 
+/* IVF_PQ over a Float16 column.  The reference runs its generic code with T = f16:
+ * kmeans_find_partitions::<f16> (rust/lance-linalg/src/kmeans.rs:581-586), the residual as a Float16 array
+ * (rust/lance/src/index/vector/ivf/v2.rs:285-301), build_distance_table_{l2,dot}::<f16> behind
+ * PQDistCalculator::new (rust/lance-index/src/vector/pq/storage.rs:500-512, pq/distance.rs:17-85), normalize::<f16> for
+ * cosine keys (rust/lance-linalg/src/kernels.rs:118-121), refine on the Float16 rows.  centroids [nlist][dim],
+ * codebook [M][256][dim/M], raw vectors and keys are IEEE binary16 bit patterns; codes are 8-bit, layout as
+ * lb200_index_create.  Distances are f32 in the order of the reference's scalar f16 fallbacks (csrc/f16pq.cuh).
+ * Limits: num_sub_vectors % 16 == 0; the handle takes lb200_search_f16 only (the f32 entry points answer
+ * LB200_EINVAL); stats / destroy as for any handle.  No bf16 form: the reference's find_partitions and PQ storage
+ * dispatch on Float16 / Float32 / Float64 only. */
+int32_t lb200_index_create_f16(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist, const uint16_t* centroids,
+                               uint32_t num_sub_vectors, const uint16_t* codebook, const uint64_t* part_offsets,
+                               const uint8_t* codes, const uint64_t* row_ids, const uint16_t* raw_vectors_or_null,
+                               lb200_index** out);
+int32_t lb200_search_f16(lb200_index* ix, const uint16_t* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
+                         uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
+                         float* out_dist, uint64_t* out_rowid, uint32_t* out_count);
+
 /* The same two entry points for Float16 columns (the reference's f16 path:
  * `impl L2/Dot/Cosine/Normalize for f16`, rust/lance-linalg/src/distance/{l2.rs:136-166, dot.rs:100-137,
  * cosine.rs:88-121, norm_l2.rs:46-76}, C kernels rust/lance-linalg/src/simd/f16.c).  queries / vectors are

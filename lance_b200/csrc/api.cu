@@ -18,6 +18,7 @@
 
 #include "../../include/lance_b200.h"
 #include "coarse.cuh"
+#include "f16pq.cuh"
 #include "flat.cuh"
 #include "launch.h"
 #include "scan4.cuh"
@@ -177,6 +178,8 @@ struct lb200_index {
   uint64_t N = 0, ntiles = 0, max_part = 0;
   double avg_np = 0;  // mean rows per NON-EMPTY partition
   float *d_centroids = nullptr, *d_codebook = nullptr, *d_raw = nullptr;
+  bool f16 = false;                    // Float16 handle (api_f16pq.inl): centroids / codebook are exact widenings
+  __half* d_raw16 = nullptr;           // its raw vectors for the refine step
   uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
   uint8_t* d_codes = nullptr;          // tile16 layout (variants 1/2), or null
   uint8_t* d_codes3 = nullptr;         // skew-stream layout (variant 3), or null
@@ -438,6 +441,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_centroids);
   cudaFree(ix->d_codebook);
   cudaFree(ix->d_raw);
+  cudaFree(ix->d_raw16);
   cudaFree(ix->d_part_off);
   cudaFree(ix->d_tile_off);
   cudaFree(ix->d_row_ids);
@@ -587,3 +591,4 @@ extern "C" int32_t lb200_set_scan_variant(lb200_index* ix, int32_t variant) {
 #include "api_noalloc.inl"
 #include "api_column.inl"
 #include "api_build.inl"
+#include "api_f16pq.inl"

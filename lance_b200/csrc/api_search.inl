@@ -34,7 +34,8 @@ static int choose_scan(const lb200_index* ix, uint32_t kprime, double avg_q_per_
     // variant 3: QL is tied to the layout's lane-delay period (8 -> LDS.128/QL 4, 16 -> LDS.64/QL 2)
     const int ql = ix->skew_D == 8 ? 4 : 2;
     uint32_t capw = std::max(64u, (kprime + 32 + 3) & ~3u);
-    size_t smem = scan3_smem_bytes(ql, SCAN_NW, ix->M, ix->dim, capw);
+    // (f16 handles always fetch pre-built tables: no residual staging area, see search_pipeline)
+    size_t smem = scan3_smem_bytes(ql, SCAN_NW, ix->M, ix->f16 ? 0 : ix->dim, capw);
     if (smem <= limit) {
       out->variant = 3;
       out->ql = ql;
@@ -81,6 +82,7 @@ struct SearchArgs {
   uint32_t* d_out_count;
   float* d_out_exact;          // shard mode only
   const struct PrebuiltWork* pw = nullptr;  // work list built on the host (small search_partitions calls)
+  const float* d_keys_override = nullptr;   // f16 handles: keys already normalised in f16 arithmetic (f16pq.cuh)
 };
 
 // Scan plan of one call: kernel configuration and how partitions are cut into chunks.
@@ -110,7 +112,12 @@ static int coarse_device(lb200_index* ix, const float* d_keys, uint32_t Q, uint3
   size_t smem = (size_t)COARSE_TQ * ix->dim * 4;
   const size_t tsm = ((size_t)ix->dim * CQ_PITCH + (size_t)CQ_QB * ix->dim) * 4;
   const size_t ssm2 = (2 * (size_t)CD_SLAB + (size_t)CD_QB * ix->dim) * 4;
-  if (ix->metric != LB200_DOT && ix->dim % 64 == 0 && ssm2 <= ix->smem_optin && !getenv("LB200_COARSE_SIMPLE") &&
+  if (ix->f16 && (ix->metric == LB200_DOT || ix->dim <= 16)) {
+    // f16::dot is dot_scalar::<f16,f32,32>, f16::l2 has no dimension-8/16 special case: not the f32 kernels' order
+    const uint64_t tot = (uint64_t)Q * ix->nlist;
+    coarse_dist_f16order_kernel<<<(uint32_t)((tot + 255) / 256), 256, 0, st>>>(ix->metric == LB200_DOT, d_keys, ix->d_centroids, Q,
+                                                                             ix->nlist, ix->dim, d_D);
+  } else if (ix->metric != LB200_DOT && ix->dim % 64 == 0 && ssm2 <= ix->smem_optin && !getenv("LB200_COARSE_SIMPLE") &&
       !getenv("LB200_COARSE_TILED")) {
     CK(cudaFuncSetAttribute(coarse_dist_l2_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm2));
     dim3 g2((ix->nlist + 127) / 128, (Q + CD_QB - 1) / CD_QB);
@@ -238,15 +245,18 @@ static int plan_scan(const lb200_index* ix, uint32_t Q, uint32_t P, uint32_t kpr
 static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cudaStream_t st);  // api_pq4.inl
 static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cudaStream_t st) {
   if (ix->bits != 8) return search4_pipeline(ix, cx, a, st);  // 4-bit PQ, IVF_FLAT
+  if (ix->f16 && !a.d_keys_override)
+    return set_err(LB200_EINVAL, "a Float16 handle takes Float16 keys: use lb200_search_f16");
   const uint32_t Q = a.Q, dim = ix->dim, nlist = ix->nlist;
   const uint32_t P = a.d_part_ids ? a.P : std::min(a.nprobes, nlist);
   const uint32_t kprime = a.k * std::max(a.refine_factor, 1u);
   if (a.k == 0) return set_err(LB200_EINVAL, "k must be > 0");       // scanner.rs:642 validation
   if (kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", kprime);
   if (P == 0 || Q == 0) return 0;
-  const bool refine = a.refine_factor > 0 && ix->d_raw != nullptr && !a.per_pair_output;
+  const bool has_raw = ix->d_raw != nullptr || ix->d_raw16 != nullptr;
+  const bool refine = a.refine_factor > 0 && has_raw && !a.per_pair_output;
   // (a shard that owns no rows has no raw vectors and nothing to refine; any other handle must hold them)
-  if (a.refine_factor > 0 && !ix->d_raw && !a.per_pair_output && !(a.shard_mode && ix->N == 0))
+  if (a.refine_factor > 0 && !has_raw && !a.per_pair_output && !(a.shard_mode && ix->N == 0))
     return set_err(LB200_EINVAL, "refine_factor>0 needs raw vectors in the index handle");
   uint32_t launches = 0;
   lb200_stats stats = {};
@@ -293,6 +303,18 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
     double cap_gb = 24.0;
     if (const char* e = getenv("LB200_LUT_SCRATCH_GB")) cap_gb = atof(e);
     use_pre = want && (double)pre_units * ix->M * 1024.0 <= cap_gb * 1e9 && pre_units <= 65535ull * LUTPRE_UNITS;
+  }
+  if (ix->f16) {
+    // f16 handles: the table arithmetic differs from the f32 kernels' (f16pq.cuh), so tables always come from the
+    // f16 pre-pass and the scan only fetches them
+    if (sc.variant != 3)
+      return set_err(LB200_EUNSUPPORTED, "Float16 IVF_PQ: k*refine_factor=%u does not fit the skew-stream scan's shared memory (M=%u)",
+                     kprime, ix->M);
+    pre_by_query = ix->metric == LB200_DOT;
+    pre_units = pre_by_query ? (size_t)Q : npairs;
+    if ((double)pre_units * ix->M * 1024.0 > 24e9)
+      return set_err(LB200_EUNSUPPORTED, "Float16 IVF_PQ: %zu ADC tables in one batch exceed the table scratch", pre_units);
+    use_pre = true;
   }
   if (use_pre) { add(pre_units * ix->M * 1024); add(pre_units * 4); }
   // Tables that leave room for one CTA per SM only (M >= 48): with the tables pre-built the residual
@@ -342,7 +364,9 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
 
   // ---- A1 normalise (VectorIndex::search on a cosine index, ivf/v2.rs:370-373) ----------
   const float* keys = a.d_queries;
-  if (a.normalize && ix->metric == LB200_COSINE) {
+  if (a.d_keys_override) {
+    keys = a.d_keys_override;
+  } else if (a.normalize && ix->metric == LB200_COSINE) {
     normalize_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(a.d_queries, d_keys, Q, dim);
     CK(cudaGetLastError());
     launches++;
@@ -429,7 +453,11 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
       CK(cudaMemsetAsync(d_lut_max, 0, pre_units * 4, st));
       dim3 g((ix->M / 16) * LUTPRE_SPLIT, (uint32_t)((pre_units + LUTPRE_UNITS - 1) / LUTPRE_UNITS));
       const uint32_t* pr = pre_by_query ? nullptr : probes;
-      if (ix->dsub == 8)
+      if (ix->f16)
+        lut_prepass_f16_kernel<<<(uint32_t)pre_units, 256, (size_t)dim * 4, st>>>(keys, ix->d_centroids, ix->d_codebook, pr,
+                                                                                 ix->d_part_off, P, dim, ix->M, ix->dsub, d_lut,
+                                                                                 d_lut_max);
+      else if (ix->dsub == 8)
         lut_prepass_kernel<8><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
                                                  (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max);
       else
@@ -491,7 +519,12 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
     if (!direct) {
       // ---- A8 refine ------------------------------------------------------------------------
       float* exact = a.shard_mode ? a.d_out_exact : d_exact;
-      if (a.refine_factor > 0 && ix->d_raw) {
+      if (a.refine_factor > 0 && ix->d_raw16) {
+        refine_distance_f16_kernel<<<(uint32_t)(((size_t)Q * kprime + 127) / 128), 128, 0, st>>>(
+            ix->metric, a.d_queries, ix->d_raw16, dim, d_mpos, d_mcnt, Q, kprime, exact);
+        CK(cudaGetLastError());
+        launches++;
+      } else if (a.refine_factor > 0 && ix->d_raw) {
         refine_distance_kernel<<<(uint32_t)(((size_t)Q * kprime + 127) / 128), 128, 0, st>>>(
             ix->metric, a.d_queries, ix->d_raw, dim, d_mpos, d_mcnt, Q, kprime, exact);
         CK(cudaGetLastError());

@@ -336,6 +336,51 @@ class IvfPqGroup:
     __del__ = close
 
 
+class IvfPqIndexF16:
+    """IVF_PQ over a Float16 column (lb200_index_create_f16 / lb200_search_f16): centroids, codebook, raw vectors and keys
+    are float16 arrays, as the reference holds them when the indexed column is Float16."""
+
+    def __init__(self, data, device_id=0):
+        L = _lib.lib()
+        self._L = L
+        self.metric = data.metric
+        self.dim, self.nlist, self.M = int(data.dim), int(data.nlist), int(data.M)
+        self.has_raw = data.raw_vectors is not None
+        h = C.c_void_p()
+        f16 = lambda a: np.ascontiguousarray(a, dtype=np.float16)
+        cents, cb = f16(data.centroids), f16(data.codebook)
+        offs = np.ascontiguousarray(data.part_offsets, dtype=np.uint64)
+        codes = np.ascontiguousarray(data.codes, dtype=np.uint8)
+        rids = np.ascontiguousarray(data.row_ids, dtype=np.uint64)
+        raw = None if data.raw_vectors is None else f16(data.raw_vectors)
+        check(L.lb200_index_create_f16(
+            C.c_int32(device_id), C.c_int32(DistanceType.code(data.metric)), C.c_uint32(self.dim), C.c_uint32(self.nlist), _p(cents),
+            C.c_uint32(self.M), _p(cb), _p(offs), _p(codes), _p(rids), _p(raw), C.byref(h)))
+        self._h = h
+
+    def search(self, query: "Query"):
+        """VectorIndex::search for a batch of float16 keys; returns (dist [Q][k'], row ids [Q][k'], count [Q])."""
+        q = np.ascontiguousarray(query.key, dtype=np.float16)
+        if q.ndim == 1:
+            q = q[None, :]
+        Q = q.shape[0]
+        rf = int(query.refine_factor or 0)
+        stride = query.k if (rf and self.has_raw) else query.k * max(rf, 1)
+        od = np.empty((Q, stride), dtype=np.float32)
+        oi = np.empty((Q, stride), dtype=np.uint64)
+        oc = np.empty(Q, dtype=np.uint32)
+        check(self._L.lb200_search_f16(self._h, _p(q), C.c_uint32(Q), C.c_uint32(query.nprobes), C.c_uint32(query.k), C.c_uint32(rf),
+                                       _fptr(query.lower_bound), _fptr(query.upper_bound), _p(od), _p(oi), _p(oc)))
+        return od, oi, oc
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lb200_index_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
 class Prefilter:
     """Device-resident per-partition row bitmasks of one index handle (lb200_prefilter_*)."""
 

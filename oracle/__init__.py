@@ -414,6 +414,59 @@ def ref_distance_batch_f16(metric, q, vectors):
     return out
 
 
+# ---- IVF_PQ on Float16 vectors -------------------------------------------------------------------
+class _IndexF16(C.Structure):
+    _fields_ = [
+        ("metric", C.c_int32), ("dim", C.c_uint32), ("nlist", C.c_uint32), ("M", C.c_uint32),
+        ("centroids", C.c_void_p), ("codebook", C.c_void_p), ("part_offsets", C.c_void_p),
+        ("codes", C.c_void_p), ("row_ids", C.c_void_p), ("raw_vectors", C.c_void_p),
+    ]
+
+
+def _f16(a):
+    return np.ascontiguousarray(a, dtype=np.float16)
+
+
+def normalize_f16(v):
+    """kernels.rs:118-121 normalize::<f16> (lo_normalize_f16; parity unpinned, see the C header)."""
+    v = _f16(v)
+    out = np.empty_like(v)
+    lib().lo_normalize_f16(_p(v), C.c_size_t(v.shape[-1]), _p(out))
+    return out
+
+
+class OracleIndexF16:
+    """IVFIndex<FlatIndex, ProductQuantizer> over Float16 centroids / codebook / raw vectors (lo_search_batch_f16).
+    data: IvfPqData whose centroids, codebook and raw_vectors hold values that are exactly representable in f16
+    (they are converted with astype(float16))."""
+
+    def __init__(self, data):
+        self.data = data
+        self._keep = [
+            _f16(data.centroids), _f16(data.codebook), np.ascontiguousarray(data.part_offsets, dtype=np.uint64),
+            np.ascontiguousarray(data.codes, dtype=np.uint8), np.ascontiguousarray(data.row_ids, dtype=np.uint64),
+            None if data.raw_vectors is None else _f16(data.raw_vectors),
+        ]
+        k = self._keep
+        self.ix = _IndexF16(METRICS[data.metric], data.dim, data.nlist, data.M, k[0].ctypes.data, k[1].ctypes.data,
+                            k[2].ctypes.data, k[3].ctypes.data, k[4].ctypes.data, None if k[5] is None else k[5].ctypes.data)
+
+    def search(self, queries, k, nprobes, refine_factor=0, lower=None, upper=None, threads=0):
+        queries = _f16(queries)
+        Q = queries.shape[0]
+        kp = k * (refine_factor if refine_factor else 1)
+        P = min(nprobes, self.data.nlist)
+        od = np.full((Q, max(kp, 1)), np.inf, dtype=np.float32)
+        oi = np.full((Q, max(kp, 1)), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros(Q, dtype=np.uint32)
+        pr = np.zeros((Q, max(nprobes, 1)), dtype=np.uint32)
+        lib().lo_search_batch_f16(
+            C.byref(self.ix), _p(queries), C.c_uint32(Q), C.c_uint32(k), C.c_uint32(nprobes), C.c_uint32(refine_factor),
+            C.c_int(lower is not None), C.c_float(lower or 0.0), C.c_int(upper is not None), C.c_float(upper or 0.0),
+            C.c_int(threads), _p(od), _p(oi), _p(oc), _p(pr))
+        return od, oi, oc, pr[:, :P]
+
+
 # ---- IVF_FLAT (IVFIndex<FlatIndex, FlatQuantizer>) -------------------------------------------------
 def ivf_flat_search(data, query, k, nprobes, refine_factor=None, lower=None, upper=None):
     """VectorIndex::search on an IVF_FLAT index for ONE query (ivf/v2.rs:368-401), then the scanner's refine when

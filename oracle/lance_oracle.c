@@ -471,31 +471,17 @@ void lo_preprocess_query(const lo_index *ix, uint32_t part, const float *key, fl
   }
 }
 
-/* lance/src/index/vector/ivf/v2.rs:414-433 search_in_partition:
- *   preprocess_query (:285-301: residual iff L2|Cosine, pq/builder.rs:66-68)
- *   FlatIndex::search (lance-index/src/vector/flat/index.rs:76-137): dist table,
- *   distance_all, [lower,upper) filter, sort, take(k'), local id -> row id.
- * `key` is the (already normalised, for cosine) query.  bitmask_or_null: per-row allow
- * bits of this partition (prefilter path, flat/index.rs:106-122).
- * Returns count (<= kprime); out sorted ascending by (dist, row id). */
-uint32_t lo_search_in_partition(const lo_index *ix, uint32_t part, const float *key,
-                                uint32_t kprime, int has_lower, float lower, int has_upper,
-                                float upper, const uint64_t *bitmask_or_null, float *out_dist,
-                                uint64_t *out_rowid, uint64_t *out_pos) {
-  uint32_t d = ix->dim, M = ix->M;
-  size_t off = ix->part_offsets[part], n = ix->part_offsets[part + 1] - off;
-  float *q = (float *)malloc(sizeof(float) * d);
-  if (ix->metric == LO_L2 || ix->metric == LO_COSINE) {
-    const float *c = ix->centroids + (size_t)part * d;
-    for (uint32_t i = 0; i < d; i++) q[i] = key[i] - c[i];
-  } else {
-    memcpy(q, key, sizeof(float) * d);
-  }
-  float *table = (float *)malloc(sizeof(float) * M * 256);
+/* The part of FlatIndex::search (flat/index.rs:76-137) after the distance table exists: distance_all (or the per-row
+ * path under a prefilter), [lower, upper) filter, sort, take(k'), local id -> row id.  Shared by the f32 and f16 entry
+ * points: from the table on, the element type of the vectors plays no part. */
+static uint32_t lo_partition_select(const uint64_t *part_offsets, const uint8_t *all_codes, const uint64_t *row_ids, uint32_t M,
+                                    uint32_t num_bits, uint32_t part, const float *table, uint32_t kprime, int has_lower,
+                                    float lower, int has_upper, float upper, const uint64_t *bitmask_or_null,
+                                    float *out_dist, uint64_t *out_rowid, uint64_t *out_pos) {
+  size_t off = part_offsets[part], n = part_offsets[part + 1] - off;
   float *dist = (float *)malloc(sizeof(float) * (n ? n : 1));
-  if (ix->num_bits == 4) {
-    const uint8_t *codes = ix->codes + off * (M / 2);
-    lo_build_distance_table4(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+  if (num_bits == 4) {
+    const uint8_t *codes = all_codes + off * (M / 2);
     if (!bitmask_or_null) {
       lo_compute_pq_distance_4bit(table, M, codes, n, dist);
     } else {
@@ -503,8 +489,7 @@ uint32_t lo_search_in_partition(const lo_index *ix, uint32_t part, const float *
         if ((bitmask_or_null[i >> 6] >> (i & 63)) & 1) dist[i] = lo_pq_distance_one_4bit(table, M, codes, n, i);
     }
   } else {
-    const uint8_t *codes = ix->codes + off * M;
-    lo_build_distance_table(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+    const uint8_t *codes = all_codes + off * M;
     if (!bitmask_or_null) {
       lo_compute_pq_distance(table, M, codes, n, dist);
     } else {
@@ -524,7 +509,7 @@ uint32_t lo_search_in_partition(const lo_index *ix, uint32_t part, const float *
     /* tie order: reference sorts by distance only (unstable); we pin (dist, row id). */
     cand_t c;
     c.dist = dist[i];
-    c.id = ix->row_ids[off + i];
+    c.id = row_ids[off + i];
     c.pos = off + i;
     heap_push(&hp, c);
   }
@@ -537,6 +522,35 @@ uint32_t lo_search_in_partition(const lo_index *ix, uint32_t part, const float *
   uint32_t cnt = (uint32_t)hp.n;
   free(hp.h);
   free(dist);
+  return cnt;
+}
+
+/* lance/src/index/vector/ivf/v2.rs:414-433 search_in_partition:
+ *   preprocess_query (:285-301: residual iff L2|Cosine, pq/builder.rs:66-68)
+ *   FlatIndex::search (lance-index/src/vector/flat/index.rs:76-137): dist table,
+ *   distance_all, [lower,upper) filter, sort, take(k'), local id -> row id.
+ * `key` is the (already normalised, for cosine) query.  bitmask_or_null: per-row allow
+ * bits of this partition (prefilter path, flat/index.rs:106-122).
+ * Returns count (<= kprime); out sorted ascending by (dist, row id). */
+uint32_t lo_search_in_partition(const lo_index *ix, uint32_t part, const float *key,
+                                uint32_t kprime, int has_lower, float lower, int has_upper,
+                                float upper, const uint64_t *bitmask_or_null, float *out_dist,
+                                uint64_t *out_rowid, uint64_t *out_pos) {
+  uint32_t d = ix->dim, M = ix->M;
+  float *q = (float *)malloc(sizeof(float) * d);
+  if (ix->metric == LO_L2 || ix->metric == LO_COSINE) {
+    const float *c = ix->centroids + (size_t)part * d;
+    for (uint32_t i = 0; i < d; i++) q[i] = key[i] - c[i];
+  } else {
+    memcpy(q, key, sizeof(float) * d);
+  }
+  float *table = (float *)malloc(sizeof(float) * M * 256);
+  if (ix->num_bits == 4)
+    lo_build_distance_table4(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+  else
+    lo_build_distance_table(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+  uint32_t cnt = lo_partition_select(ix->part_offsets, ix->codes, ix->row_ids, M, ix->num_bits, part, table, kprime, has_lower,
+                                     lower, has_upper, upper, bitmask_or_null, out_dist, out_rowid, out_pos);
   free(table);
   free(q);
   return cnt;
@@ -859,6 +873,187 @@ void lo_distance_batch_f16(int metric, const lo_f16 *from, const lo_f16 *to, siz
            : metric == LO_DOT ? 1.0f - lo_dot_f16(from, y, d)
                               : lo_cosine_f16(from, xn, y, d);
   }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * IVF_PQ on Float16 vectors: IVFIndex<FlatIndex, ProductQuantizer> whose centroids, codebook, keys and
+ * raw vectors are f16 arrays.  The generic code paths are the f32 ones with T = f16:
+ *   find_partitions    kmeans_find_partitions::<f16> (kmeans.rs:581-586,624-644): f16::l2 / f16::dot per centroid
+ *   residual           arrow_arith sub on Float16 arrays (v2.rs:294): half's Sub = f16(f32(a) - f32(b))
+ *   distance table     build_distance_table_{l2,dot}::<f16> (pq/distance.rs:17-85, storage.rs:500-512): f16::l2_batch is the
+ *                      DEFAULT trait impl (per centroid f16::l2 = l2_scalar::<f16,f32,16>, no dimension-8/16 special
+ *                      case as f32 has); dot_distance = 1 - dot_scalar::<f16,f32,32>
+ *   scan, select       identical to f32 (the table is f32): lo_partition_select
+ *   normalize (cosine) kernels.rs:118-121 normalize::<f16>: x.powi(2) per element, sum::<f16>, sqrt, x / norm with the
+ *                      half crate's software operators: every operation is done in f32 and rounded to f16, and
+ *                      `impl Sum for f16` accumulates in f32 and rounds once (half 2.x binary16.rs).  PARITY UNPINNED for
+ *                      this function: the half crate is a dependency that is absent from /root/reference.
+ *   refine             flat_knn on the raw f16 rows with the ORIGINAL key: lo_distance_batch_f16
+ * f16::l2 / dot / norm_l2 are the deterministic scalar fallbacks above (the fp16kernels C kernels agree within
+ * rounding: tests/test_f16.py). */
+typedef struct {
+  int32_t metric;
+  uint32_t dim, nlist, M;
+  const lo_f16 *centroids;      /* [nlist][dim] */
+  const lo_f16 *codebook;       /* [M][256][dim/M] */
+  const uint64_t *part_offsets; /* [nlist+1] */
+  const uint8_t *codes;         /* concat over p of [M][n_p] */
+  const uint64_t *row_ids;      /* [N] */
+  const lo_f16 *raw_vectors;    /* [N][dim] in index order, or NULL */
+} lo_index_f16;
+
+void lo_normalize_f16(const lo_f16 *v, size_t d, lo_f16 *out) {
+  float ss = 0.0f;
+  for (size_t i = 0; i < d; i++) {
+    lo_f16 p = (lo_f16)((float)v[i] * (float)v[i]); /* f16::powi(2) */
+    ss += (float)p;                                 /* Sum for f16: f32 accumulator */
+  }
+  lo_f16 s16 = (lo_f16)ss;
+  lo_f16 n16 = (lo_f16)sqrtf((float)s16);
+  for (size_t i = 0; i < d; i++) out[i] = (lo_f16)((float)v[i] / (float)n16);
+}
+
+uint32_t lo_find_partitions_f16(const lo_f16 *centroids, uint32_t nlist, uint32_t d, const lo_f16 *query, uint32_t nprobes,
+                                int metric, uint32_t *out_ids, float *out_dists) {
+  cand_t *all = (cand_t *)malloc(sizeof(cand_t) * (nlist ? nlist : 1));
+  for (uint32_t i = 0; i < nlist; i++) {
+    const lo_f16 *c = centroids + (size_t)i * d;
+    all[i].dist = metric == LO_DOT ? 1.0f - lo_dot_f16(query, c, d) : lo_l2_f16(query, c, d);
+    all[i].id = i;
+  }
+  uint32_t lim = nprobes < nlist ? nprobes : nlist;
+  qsort(all, nlist, sizeof(cand_t), cand_cmp);
+  for (uint32_t i = 0; i < lim; i++) {
+    out_ids[i] = (uint32_t)all[i].id;
+    if (out_dists) out_dists[i] = all[i].dist;
+  }
+  free(all);
+  return lim;
+}
+
+void lo_build_distance_table_f16(int metric, const lo_f16 *codebook, uint32_t M, uint32_t d, const lo_f16 *query,
+                                 float *table) {
+  uint32_t dsub = d / M;
+  for (uint32_t m = 0; m < M; m++)
+    for (uint32_t c = 0; c < 256; c++) {
+      const lo_f16 *y = codebook + ((size_t)m * 256 + c) * dsub;
+      table[(size_t)m * 256 + c] = metric == LO_DOT ? 1.0f - lo_dot_f16(query + (size_t)m * dsub, y, dsub)
+                                                    : lo_l2_f16(query + (size_t)m * dsub, y, dsub);
+    }
+}
+
+uint32_t lo_search_in_partition_f16(const lo_index_f16 *ix, uint32_t part, const lo_f16 *key, uint32_t kprime, int has_lower,
+                                    float lower, int has_upper, float upper, const uint64_t *bitmask_or_null,
+                                    float *out_dist, uint64_t *out_rowid, uint64_t *out_pos) {
+  uint32_t d = ix->dim, M = ix->M;
+  lo_f16 *q = (lo_f16 *)malloc(sizeof(lo_f16) * d);
+  if (ix->metric == LO_L2 || ix->metric == LO_COSINE) {
+    const lo_f16 *c = ix->centroids + (size_t)part * d;
+    for (uint32_t i = 0; i < d; i++) q[i] = (lo_f16)((float)key[i] - (float)c[i]);
+  } else {
+    memcpy(q, key, sizeof(lo_f16) * d);
+  }
+  float *table = (float *)malloc(sizeof(float) * M * 256);
+  lo_build_distance_table_f16(ix->metric == LO_DOT ? LO_DOT : LO_L2, ix->codebook, M, d, q, table);
+  uint32_t cnt = lo_partition_select(ix->part_offsets, ix->codes, ix->row_ids, M, 8, part, table, kprime, has_lower, lower,
+                                     has_upper, upper, bitmask_or_null, out_dist, out_rowid, out_pos);
+  free(table);
+  free(q);
+  return cnt;
+}
+
+uint32_t lo_search_one_f16(const lo_index_f16 *ix, const lo_f16 *query, uint32_t k, uint32_t nprobes, uint32_t refine_factor,
+                           int has_lower, float lower, int has_upper, float upper, float *out_dist, uint64_t *out_rowid,
+                           uint32_t *probes_out) {
+  uint32_t d = ix->dim;
+  uint32_t kprime = k * (refine_factor ? refine_factor : 1);
+  lo_f16 *key = (lo_f16 *)malloc(sizeof(lo_f16) * d);
+  if (ix->metric == LO_COSINE)
+    lo_normalize_f16(query, d, key);
+  else
+    memcpy(key, query, sizeof(lo_f16) * d);
+  uint32_t P = nprobes < ix->nlist ? nprobes : ix->nlist;
+  uint32_t *probes = (uint32_t *)malloc(sizeof(uint32_t) * (P ? P : 1));
+  P = lo_find_partitions_f16(ix->centroids, ix->nlist, d, key, nprobes, ix->metric == LO_DOT ? LO_DOT : LO_L2, probes, NULL);
+  if (probes_out) memcpy(probes_out, probes, sizeof(uint32_t) * P);
+  size_t tot = (size_t)P * kprime;
+  float *pd = (float *)malloc(sizeof(float) * (tot ? tot : 1));
+  uint64_t *pr = (uint64_t *)malloc(sizeof(uint64_t) * (tot ? tot : 1));
+  uint64_t *pp = (uint64_t *)malloc(sizeof(uint64_t) * (tot ? tot : 1));
+  cand_t *cps = (cand_t *)malloc(sizeof(cand_t) * (tot ? tot : 1));
+  size_t na = 0;
+  for (uint32_t i = 0; i < P; i++) {
+    uint32_t c = lo_search_in_partition_f16(ix, probes[i], key, kprime, has_lower, lower, has_upper, upper, NULL,
+                                            pd + (size_t)i * kprime, pr + (size_t)i * kprime, pp + (size_t)i * kprime);
+    for (uint32_t j = 0; j < c; j++) {
+      cps[na].dist = pd[(size_t)i * kprime + j];
+      cps[na].id = pr[(size_t)i * kprime + j];
+      cps[na].pos = pp[(size_t)i * kprime + j];
+      na++;
+    }
+  }
+  qsort(cps, na, sizeof(cand_t), cand_cmp);
+  uint32_t cnt = (uint32_t)(na < kprime ? na : kprime);
+  if (!refine_factor) {
+    for (uint32_t i = 0; i < cnt; i++) {
+      out_dist[i] = cps[i].dist;
+      out_rowid[i] = cps[i].id;
+    }
+  } else {
+    cand_t *ref = (cand_t *)malloc(sizeof(cand_t) * (cnt ? cnt : 1));
+    uint32_t nr = 0;
+    for (uint32_t i = 0; i < cnt; i++) {
+      float dist;
+      lo_distance_batch_f16(ix->metric, query, ix->raw_vectors + (size_t)cps[i].pos * d, 1, d, &dist);
+      if (has_lower && !(dist >= lower)) continue;
+      if (has_upper && !(dist < upper)) continue;
+      if (dist != dist) continue; /* IS NOT NULL of the flat_knn plan */
+      ref[nr].dist = dist;
+      ref[nr].id = cps[i].id;
+      ref[nr].pos = cps[i].pos;
+      nr++;
+    }
+    qsort(ref, nr, sizeof(cand_t), cand_cmp);
+    cnt = nr < k ? nr : k;
+    for (uint32_t i = 0; i < cnt; i++) {
+      out_dist[i] = ref[i].dist;
+      out_rowid[i] = ref[i].id;
+    }
+    free(ref);
+  }
+  free(cps);
+  free(pp);
+  free(pr);
+  free(pd);
+  free(probes);
+  free(key);
+  return cnt;
+}
+
+typedef struct {
+  const lo_index_f16 *ix;
+  const lo_f16 *queries;
+  uint32_t k, nprobes, refine_factor;
+  int has_lower, has_upper;
+  float lower, upper;
+  float *out_dist;
+  uint64_t *out_rowid;
+  uint32_t *out_count, *probes_out;
+} lo_sb16_ctx;
+static void lo_sb16_body(int64_t qi, void *vctx) {
+  lo_sb16_ctx *c = (lo_sb16_ctx *)vctx;
+  uint32_t stride = c->k * (c->refine_factor ? c->refine_factor : 1);
+  c->out_count[qi] = lo_search_one_f16(c->ix, c->queries + (size_t)qi * c->ix->dim, c->k, c->nprobes, c->refine_factor,
+                                       c->has_lower, c->lower, c->has_upper, c->upper, c->out_dist + (size_t)qi * stride,
+                                       c->out_rowid + (size_t)qi * stride,
+                                       c->probes_out ? c->probes_out + (size_t)qi * c->nprobes : NULL);
+}
+void lo_search_batch_f16(const lo_index_f16 *ix, const lo_f16 *queries, uint32_t Q, uint32_t k, uint32_t nprobes,
+                         uint32_t refine_factor, int has_lower, float lower, int has_upper, float upper, int threads,
+                         float *out_dist, uint64_t *out_rowid, uint32_t *out_count, uint32_t *probes_out) {
+  lo_sb16_ctx c = {ix, queries, k, nprobes, refine_factor, has_lower, has_upper, lower, upper, out_dist, out_rowid, out_count,
+                   probes_out};
+  lo_parallel_for(Q, 4, threads, lo_sb16_body, &c);
 }
 
 /* ------------------------------------------------------------------------------------------------

@@ -99,3 +99,49 @@ def test_gpu_flat_f16_parity(oracle, metric, d):
     assert np.array_equal(one.view(np.uint32), oracle.distance_batch_f16(metric, q[0], v).view(np.uint32))
     od, oi, oc = flat_knn_f16(q, metric, np.zeros((0, d), np.float16), 3)
     assert oc.tolist() == [0] * Q
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+def test_f16_ivf_pq_checker_is_the_generic_path_with_f16_pieces(oracle, metric):
+    """lo_search_batch_f16 against a numpy walk through the same steps built from the f16 primitives that
+    oracle/_ref (the reference's own f16.c) pins: find_partitions by distance_batch_f16, residual rounded to f16,
+    table = distance_batch_f16 per sub-vector, f32 code sums in ascending m, (distance, row id) order."""
+    from lance_b200.synth import IvfPqData
+    rng = np.random.default_rng(31)
+    d, nlist, M, n = 64, 5, 16, 700
+    dsub = d // M
+    cents = rng.normal(size=(nlist, d)).astype(np.float16)
+    cb = rng.normal(size=(M, 256, dsub)).astype(np.float16)
+    sizes = np.array([100, 0, 250, 50, 300])
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    codes = np.concatenate([rng.integers(0, 256, size=(M, s), dtype=np.uint8).ravel() for s in sizes])
+    rids = rng.permutation(n * 3)[:n].astype(np.uint64)
+    data = IvfPqData(metric, d, nlist, M, cents.astype(np.float32), cb.astype(np.float32), offs, codes, rids, None)
+    q = rng.normal(size=(6, d)).astype(np.float16)
+    k, nprobes = 7, 3
+    od, oi, oc, pr = oracle.OracleIndexF16(data).search(q, k, nprobes)
+    for j in range(len(q)):
+        key = oracle.normalize_f16(q[j]) if metric == "cosine" else q[j]
+        cd = oracle.distance_batch_f16("dot" if metric == "dot" else "l2", key, cents)
+        probes = np.lexsort((np.arange(nlist), cd))[:nprobes]
+        assert probes.tolist() == pr[j].tolist()
+        ds, rs = [], []
+        for p in probes.tolist():
+            o, e = int(offs[p]), int(offs[p + 1])
+            if e == o:
+                continue
+            r = key if metric == "dot" else (key.astype(np.float32) - cents[p].astype(np.float32)).astype(np.float16)
+            table = np.stack([oracle.distance_batch_f16("dot" if metric == "dot" else "l2", r[m * dsub:(m + 1) * dsub], cb[m])
+                              for m in range(M)])
+            c = codes[o * M:e * M].reshape(M, e - o)
+            acc = np.zeros(e - o, dtype=np.float32)
+            for m in range(M):
+                acc = (acc + table[m][c[m]]).astype(np.float32)
+            ds.append(acc)
+            rs.append(rids[o:e])
+        ds, rs = np.concatenate(ds), np.concatenate(rs)
+        order = np.lexsort((rs, ds))[:k]
+        n_ = int(oc[j])
+        assert n_ == len(order) and oi[j, :n_].tolist() == rs[order].tolist()
+        assert np.array_equal(od[j, :n_].view(np.uint32), ds[order].view(np.uint32))
