@@ -316,7 +316,11 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
       return set_err(LB200_EUNSUPPORTED, "Float16 IVF_PQ: %zu ADC tables in one batch exceed the table scratch", pre_units);
     use_pre = true;
   }
-  if (use_pre) { add(pre_units * ix->M * 1024); add(pre_units * 4); }
+  // per-pair tables stored as one interleaved image per query group (scan3.cuh lut_fetch_image): a few more table
+  // slots (the last group of a partition may be partly filled), positions in the pair list as unit numbers
+  const bool pre_image = use_pre && !pre_by_query && !ix->f16 && sc.minb == 1 && !getenv("LB200_NO_LUT_IMAGE");
+  const size_t pre_slots = pre_image ? pre_units + (size_t)nlist * (sc.ql - 1) : pre_units;
+  if (use_pre) { add(pre_slots * ix->M * 1024); add(pre_units * 4); }
   // Tables that leave room for one CTA per SM only (M >= 48): with the tables pre-built the residual
   // staging area is not needed, which makes room for the candidate buffers of 16 warps instead of 8.
   if (use_pre && sc.minb == 1 && !getenv("LB200_NO_WIDE")) {
@@ -356,7 +360,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   uint64_t* t_mrow = mslice ? cx.arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
   uint64_t* t_mpos = mslice ? cx.arena.take<uint64_t>((size_t)Q * mslices * kprime) : nullptr;
   uint32_t* t_mcnt = mslice ? cx.arena.take<uint32_t>((size_t)Q * mslices) : nullptr;
-  float* d_lut = use_pre ? cx.arena.take<float>(pre_units * ix->M * 256) : nullptr;
+  float* d_lut = use_pre ? cx.arena.take<float>(pre_slots * ix->M * 256) : nullptr;
   uint32_t* d_lut_max = use_pre ? cx.arena.take<uint32_t>(pre_units) : nullptr;
 
   const bool prof = ix->profiling;
@@ -459,15 +463,18 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
                                                                                  d_lut_max);
       else if (ix->dsub == 8)
         lut_prepass_kernel<8><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
-                                                 (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max);
+                                                 (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max,
+                                                 pre_image ? d_pair_list : nullptr, d_pair_off, (uint32_t)sc.ql);
       else
         lut_prepass_kernel<16><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
-                                                  (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max);
+                                                  (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max,
+                                                  pre_image ? d_pair_list : nullptr, d_pair_off, (uint32_t)sc.ql);
       CK(cudaGetLastError());
       launches++;
       sp.lut_src = d_lut;
       sp.lut_max = d_lut_max;
       sp.lut_by_query = pre_by_query;
+      sp.lut_image = pre_image;
     }
     // pooled bootstrap when most work items are cold: a shard (few of a query's probes are local), few
     // probes per query, or per-pair outputs (no cross-item bound at all)

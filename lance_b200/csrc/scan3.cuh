@@ -65,6 +65,8 @@ struct Scan3Params {
   const float* lut_src;           // ADC tables built by lut_prepass_kernel: [unit][M/16][256][16] f32, or null
   const uint32_t* lut_max;        // [unit] 0, or the largest |entry| bit pattern if some entry is >= 2^118
   int32_t lut_by_query;           // unit = query index (dot: no residual) instead of pair id
+  int32_t lut_image;              // tables of a query group are stored as ONE interleaved image (= the shared-memory
+                                  // table of its work items), group (part, g) at lut_image_base(); lut_max by pair-list position
   uint32_t* qthr;                 // [Q] ordered keys: per-query global threshold, or null
   uint32_t* const* peers;         // [n_peers] the same table on the peer GPUs (NVLink peer memory), or null
   uint32_t n_peers;
@@ -150,6 +152,11 @@ __device__ __forceinline__ float l2_once_packed(const f32x2_t* X, const f32x2_t*
 // residual = q - centroid (v2.rs:285-301), entries by lut_elem (pq/distance.rs:17-85).
 // grid.x = (M/16) * LUTPRE_SPLIT: 16 sub-vectors x a slice of the 256 codes; grid.y = unit tiles.
 // Output layout per unit: [M/16][256][16] f32 == the scan kernel's table order for one query.
+// first table slot of query group g of partition `part` in image mode: partition p's groups start at
+// pair_off[p] + p * (ql - 1), which leaves room for its last, partly filled group
+__host__ __device__ __forceinline__ uint64_t lut_image_base(uint32_t pair_off_p, uint32_t part, uint32_t g, uint32_t ql) {
+  return (uint64_t)pair_off_p + (uint64_t)part * (ql - 1) + (uint64_t)g * ql;
+}
 constexpr uint32_t LUTPRE_UNITS = 64;
 constexpr int LUTPRE_CPT = 2;                              // codes per thread
 constexpr uint32_t LUTPRE_SPLIT = 256 / (16 * LUTPRE_CPT);  // blocks per 16-sub-vector chunk
@@ -158,26 +165,44 @@ __global__ void __launch_bounds__(256)
 lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ centroids,
                    const float* __restrict__ codebook, const uint32_t* __restrict__ probes /*[Q][P]; null: by query*/,
                    const uint64_t* __restrict__ part_off, uint32_t n_units, uint32_t P, uint32_t dim, uint32_t M,
-                   float* __restrict__ out, uint32_t* __restrict__ out_max /*[n_units], zeroed*/) {
+                   float* __restrict__ out, uint32_t* __restrict__ out_max /*[n_units], zeroed*/,
+                   const uint32_t* __restrict__ pair_list /*image mode: unit = position in the pair list; else null*/,
+                   const uint32_t* __restrict__ pair_off, uint32_t ql) {
   constexpr int PITCH = DSUB + 4;  // floats; 8 lanes of an LDS.128 phase land on 8 distinct bank groups
   constexpr int UB = 16;           // units staged at a time
   __shared__ __align__(16) float xs[UB][16 * PITCH];
   __shared__ uint32_t spart[LUTPRE_UNITS];  // partition of each unit of the tile; 0xffffffff: no table needed
+  __shared__ uint32_t squery[LUTPRE_UNITS]; // its query
+  __shared__ uint64_t sobase[LUTPRE_UNITS]; // where its table starts in `out` (floats)
   const uint32_t ch = blockIdx.x / LUTPRE_SPLIT, quarter = blockIdx.x % LUTPRE_SPLIT;
   const uint32_t t = threadIdx.x, slot = t & 15, cq = t >> 4;
   const uint32_t m = ch * 16 + slot;
   const bool residual = probes != nullptr;
   const uint32_t u0 = blockIdx.y * LUTPRE_UNITS, u1 = min(n_units, u0 + LUTPRE_UNITS);
+  // image mode: the tables of the (up to ql) queries of a group are interleaved -- entry e of slot s at
+  // (e * ql + s) -- which is the layout the scan kernel's shared-memory table has, so it fetches a group's tables
+  // with one bulk copy (lut_fetch_image) instead of 4-byte gathers.
+  const uint32_t qs = pair_list ? ql : 1u;
   if (t < LUTPRE_UNITS) {
-    uint32_t part = 0xffffffffu;
+    uint32_t part = 0xffffffffu, query = 0;
+    uint64_t obase = (uint64_t)(u0 + t) * M * 256;
     if (u0 + t < u1) {
       part = 0;
+      query = u0 + t;
       if (residual) {  // a shard holds all nlist partitions, most of them empty: no items, no table
-        part = probes[u0 + t];
+        const uint32_t pair = pair_list ? pair_list[u0 + t] : u0 + t;
+        part = probes[pair];
+        query = pair / P;
+        if (pair_list) {
+          const uint32_t local = u0 + t - pair_off[part];
+          obase = lut_image_base(pair_off[part], part, local / ql, ql) * M * 256 + local % ql;
+        }
         if (part_off[part + 1] == part_off[part]) part = 0xffffffffu;
       }
     }
     spart[t] = part;
+    squery[t] = query;
+    sobase[t] = obase;
   }
   float y[LUTPRE_CPT][DSUB];
 #pragma unroll
@@ -201,7 +226,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
       float v = 0.0f;
       if (part != 0xffffffffu) {
         const uint32_t e = ch * 16 * DSUB + rem;
-        v = __ldg(queries + (size_t)(residual ? u / P : u) * dim + e);
+        v = __ldg(queries + (size_t)squery[u - u0] * dim + e);
         if (residual) v = __fsub_rn(v, __ldg(centroids + (size_t)part * dim + e));
       }
       xs[ui][(rem / DSUB) * PITCH + rem % DSUB] = v;
@@ -216,7 +241,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
         const float4 v = *reinterpret_cast<const float4*>(&xs[ui][slot * PITCH + 4 * j]);
         x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
       }
-      float* o = out + (size_t)(ub + ui) * M * 256 + (size_t)ch * 4096 + slot;
+      float* o = out + sobase[ub + ui - u0] + ((size_t)ch * 4096 + slot) * qs;
       uint32_t mb = 0;
       f32x2_t X[DSUB / 2];
 #pragma unroll
@@ -232,7 +257,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
         } else {
           v = lut_elem<DSUB>(false, x, y[i], DSUB);
         }
-        o[(quarter * (16 * LUTPRE_CPT) + cq + 16 * i) * 16] = v;
+        o[(size_t)(quarter * (16 * LUTPRE_CPT) + cq + 16 * i) * 16 * qs] = v;
         mb = max(mb, __float_as_uint(v) & 0x7fffffffu);
       }
       // only magnitudes that rule out the exact-FMA row switch (>= 2^118) are recorded: (almost) never
@@ -263,6 +288,32 @@ static __device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const floa
   asm volatile("cp.async.commit_group;" ::: "memory");
   const uint32_t mb = lut_max[unit];
   asm volatile("cp.async.wait_group 0;" ::: "memory");
+  return mb;
+}
+
+// Image mode: the group's interleaved tables are one contiguous block -> bulk copies (TMA 1-D) issued by one thread,
+// completion on an mbarrier every thread waits on.  No LSU instructions, no registers.
+static __device__ __noinline__ uint32_t lut_fetch_image(unsigned char* lut, const float* __restrict__ src, uint32_t bytes,
+                                                        const uint32_t* __restrict__ lut_max, uint32_t pbase, uint32_t nq,
+                                                        uint64_t* bar, const uint32_t* phase_s) {
+  const uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
+  const uint32_t phase = *phase_s;   // flipped by thread 0 after the barrier that follows this call
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(lut);
+    for (uint32_t o = 0; o < bytes; o += 32768u) {
+      const uint32_t n = min(32768u, bytes - o);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst + o), "l"(reinterpret_cast<const unsigned char*>(src) + o), "r"(n), "r"(bar_a) : "memory");
+    }
+  }
+  uint32_t mb = 0;
+  if (threadIdx.x < nq) mb = lut_max[pbase + threadIdx.x];
+  uint32_t ok;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar_a), "r"(phase) : "memory");
+  } while (!ok);
   return mb;
 }
 
@@ -592,8 +643,15 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   uint4* sdesc = reinterpret_cast<uint4*>(sitem + 4);      // its descriptor (partition, query group, chunk)
   ItemCtx* ictx = reinterpret_cast<ItemCtx*>(sitem + 8);   // 16-byte aligned
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
+  __shared__ __align__(8) uint64_t lut_bar;   // completion of the bulk table fetch (image mode)
+  __shared__ uint32_t lut_phase;              // its parity (kept out of the registers: the row loop is at the 128 cap)
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (MINB == 1 && p.lut_image && tid == 0) {
+    lut_phase = 0;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&lut_bar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   const uint32_t d = lane % D;
   const uint32_t M = p.M, dsub = p.dsub, dim = p.dim, kprime = p.kprime, capw = p.capw, L = p.L;
   const uint32_t units = L * C16 + 1;
@@ -691,7 +749,10 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     // thread -> (slot = tid%16, code = tid/16 + k*NT/16): a quarter/half warp writes consecutive
     // slots of one code row -> conflict-free wide stores.
     uint32_t maxbits = 0;
-    if (p.lut_src) {
+    if (MINB == 1 && p.lut_image) {  // (one-CTA-per-SM instantiations only: the others sit at the register cap)
+      maxbits = lut_fetch_image(lut, p.lut_src + lut_image_base(p.part_pair_off[part], part, g, QL) * M * 256,
+                                C16 * CB, p.lut_max, pbase, nq, &lut_bar, &lut_phase);
+    } else if (p.lut_src) {
       maxbits = lut_fetch<QL>(lut, p.lut_src, p.lut_max, (size_t)M * 256, p.lut_by_query ? sqidx : spair, nq, C16 * 4096u);
     } else {
       const uint32_t slot = tid & 15;
@@ -762,6 +823,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     // exact-FMA switch only if no partial sum of <=256 entries can overflow: |T| < 2^118
     const bool unsafe = __syncthreads_or(maxbits >= 0x7a800000u) != 0;
     if (tid == 0) {  // everyone has read sitem / sdesc (two barriers ago): hand over the next item
+      if (MINB == 1 && p.lut_image) lut_phase ^= 1u;
       sitem[0] = nxt;
       if (nxt < total_items)
         asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sdesc)),
