@@ -181,6 +181,7 @@ struct lb200_index {
   bool f16 = false;                    // Float16 handle (api_f16pq.inl): centroids / codebook are exact widenings
   __half* d_raw16 = nullptr;           // its raw vectors for the refine step
   uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
+  uint32_t* d_size_order = nullptr;    // partitions in descending size: order of the scan's item queue (worklist.cuh)
   uint8_t* d_codes = nullptr;          // tile16 layout (variants 1/2), or null
   uint8_t* d_codes3 = nullptr;         // skew-stream layout (variant 3), or null
   uint8_t* d_codes4 = nullptr;         // 4-bit PQ: concat over p of [M/2][n_p], rows sorted by row id
@@ -320,6 +321,11 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   ix->dsub = dim / M;
   ix->N = N;
   ix->h_part_off.assign(part_offsets, part_offsets + nlist + 1);
+  std::vector<uint32_t> size_order(nlist);
+  for (uint32_t p = 0; p < nlist; p++) size_order[p] = p;
+  std::stable_sort(size_order.begin(), size_order.end(), [&](uint32_t a, uint32_t b) {
+    return part_offsets[a + 1] - part_offsets[a] > part_offsets[b + 1] - part_offsets[b];
+  });
   {
     uint32_t ne = 0;
     for (uint32_t p = 0; p < nlist; p++) ne += part_offsets[p + 1] > part_offsets[p];
@@ -358,6 +364,10 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   CKF(cudaMalloc(&ix->d_centroids, cent_b));
   CKF(cudaMalloc(&ix->d_codebook, cb_b));
   CKF(cudaMalloc(&ix->d_part_off, (nlist + 1) * 8));
+  size_order.resize(2 * (size_t)nlist);  // [nlist] order, then [nlist] its inverse (rank of a partition in the queue)
+  for (uint32_t i = 0; i < nlist; i++) size_order[nlist + size_order[i]] = i;
+  CKF(cudaMalloc(&ix->d_size_order, (size_t)nlist * 8));
+  CKF(cudaMemcpy(ix->d_size_order, size_order.data(), (size_t)nlist * 8, cudaMemcpyHostToDevice));
   CKF(cudaMalloc(&ix->d_tile_off, (nlist + 1) * 8));
   CKF(cudaMalloc(&ix->d_row_ids, std::max<uint64_t>(N, 1) * 8));
   // Device code layouts.  Variant 3 (skew streams) serves every M that is a multiple of 16; the
@@ -443,6 +453,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   cudaFree(ix->d_raw);
   cudaFree(ix->d_raw16);
   cudaFree(ix->d_part_off);
+  cudaFree(ix->d_size_order);
   cudaFree(ix->d_tile_off);
   cudaFree(ix->d_row_ids);
   cudaFree(ix->d_codes);

@@ -279,6 +279,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   add((size_t)nlist * 4 * 2);       // cnt (cold, other)
   add((size_t)Q * 4);               // first partition per query
   add(npairs * 4);                  // rank
+  add((size_t)nlist * 4);           // queue offsets (size-ordered item queue)
   add((size_t)(nlist + 1) * 4 * 2); // pair_off, item_off
   add(npairs * 4);                  // pair_list
   add(nslots * 16);                 // item descriptors (items <= pairs * chunks)
@@ -340,6 +341,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   uint32_t* d_cnt2 = d_cnt + nlist;
   uint32_t* d_minp = cx.arena.take<uint32_t>(Q);
   uint32_t* d_rank = cx.arena.take<uint32_t>(npairs);
+  uint32_t* d_qoff = cx.arena.take<uint32_t>(nlist);
   uint32_t* d_pair_off = cx.arena.take<uint32_t>(nlist + 1);
   uint32_t* d_item_off = cx.arena.take<uint32_t>(nlist + 1);
   uint32_t* d_pair_list = cx.arena.take<uint32_t>(npairs);
@@ -385,6 +387,13 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   }
   if (prof) CK(cudaEventRecord(cx.ev[1], st));
   // ---- work list ------------------------------------------------------------------------
+  // Item queue in descending partition size (longest first) when a CTA draws few items: the ragged end of the queue is
+  // then a visible part of the scan (partition shards: 1/G of the items per GPU; cfg 4 at N = 8: +3.3 %).  With
+  // hundreds of items per CTA the id-ordered queue is the faster one (cfg 4 at N = 1: -1 %, cfg 1: -4 %; same-box A/B
+  // profiles/r02_ai, r02_aj).
+  bool lpt = ix->d_size_order != nullptr &&
+             (double)Q * P / sc.ql < 64.0 * ix->sm_count * std::max(1, sc.minb);
+  if (const char* e = getenv("LB200_LPT")) lpt = ix->d_size_order != nullptr && atoi(e) != 0;
   CK(cudaMemsetAsync(d_scnt, 0, nslots * 4, st));
   const uint32_t* total_items_p = d_item_off + nlist;
   if (a.pw) {  // built on the host and uploaded with the queries (small search_partitions calls)
@@ -400,7 +409,8 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   if (getenv("LB200_NO_COLDPACK"))
     CK(cudaMemsetAsync(d_minp, 0xff, (size_t)Q * 4, st));
   else
-    first_part_kernel<<<(Q + 255) / 256, 256, 0, st>>>(probes, Q, P, ix->d_part_off, d_minp);
+    first_part_kernel<<<(Q + 255) / 256, 256, 0, st>>>(probes, Q, P, ix->d_part_off, d_minp,
+                                                       lpt ? ix->d_size_order + nlist : nullptr);
   count_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, (uint32_t)npairs, P, d_minp, d_cnt,
                                                                       d_cnt2, d_rank);
   offsets_kernel<<<1, 1024, 0, st>>>(d_cnt, d_cnt2, ix->d_part_off, nlist, (uint32_t)sc.ql, chunk_vecs, ix->M,
@@ -408,7 +418,13 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   scatter_pairs_kernel<<<(uint32_t)((npairs + 255) / 256), 256, 0, st>>>(probes, d_rank, d_pair_off, d_cnt,
                                                                         (uint32_t)npairs, d_pair_list);
   if (sc.variant == 3) {
-    expand_items_kernel<<<(nlist * 32 + 255) / 256, 256, 0, st>>>(d_item_off, ix->d_part_off, nlist, chunk_vecs, d_item_desc);
+    const uint32_t* qoff = nullptr;
+    if (lpt) {
+      queue_offsets_kernel<<<1, 1024, 0, st>>>(d_item_off, ix->d_size_order, nlist, d_qoff);
+      qoff = d_qoff;
+      launches++;
+    }
+    expand_items_kernel<<<(nlist * 32 + 255) / 256, 256, 0, st>>>(d_item_off, ix->d_part_off, nlist, chunk_vecs, d_item_desc, qoff);
     launches++;
   }
   CK(cudaGetLastError());

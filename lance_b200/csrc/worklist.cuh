@@ -68,14 +68,19 @@ __global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
 // (no running bound yet); step 1/3 pack the cold pairs of a partition into the same work items so
 // that few items pay the cold start (with G shards a query has only P/G pairs per shard: without
 // the packing 1-(1-G/P)^QL of all items would hold a cold query).
+// `queue_rank` (or null: the partition id itself) = position of a partition in the order of the item queue.
 __global__ void first_part_kernel(const uint32_t* __restrict__ probes, uint32_t Q, uint32_t P,
-                                  const uint64_t* __restrict__ part_off, uint32_t* __restrict__ minp) {
+                                  const uint64_t* __restrict__ part_off, uint32_t* __restrict__ minp,
+                                  const uint32_t* __restrict__ queue_rank) {
   uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= Q) return;
-  uint32_t m = 0xffffffffu;
+  uint32_t m = 0xffffffffu, mr = 0xffffffffu;
   for (uint32_t r = 0; r < P; r++) {
     uint32_t p = probes[(size_t)q * P + r];
-    if (part_off[p + 1] > part_off[p]) m = min(m, p);
+    if (part_off[p + 1] > part_off[p]) {
+      const uint32_t rk = queue_rank ? queue_rank[p] : p;
+      if (rk < mr) { mr = rk; m = p; }
+    }
   }
   minp[q] = m;
 }
@@ -161,17 +166,51 @@ offsets_kernel(const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ cn
 // Step 2b: one descriptor per work item -- (partition, query group, chunk) -- so that the scan kernel takes an
 // item with ONE load (prefetched while the previous item runs) instead of a binary search over item_off.
 // One warp per partition.
+// `queue_off` (or null: item_off) says where a partition's items sit in the QUEUE the scan CTAs draw from.
 __global__ void expand_items_kernel(const uint32_t* __restrict__ item_off, const uint64_t* __restrict__ part_off,
-                                    uint32_t nlist, uint32_t chunk_vecs, uint4* __restrict__ desc) {
+                                    uint32_t nlist, uint32_t chunk_vecs, uint4* __restrict__ desc,
+                                    const uint32_t* __restrict__ queue_off) {
   const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (p >= nlist) return;
   const uint32_t i0 = item_off[p], i1 = item_off[p + 1];
   if (i1 == i0) return;
   const uint64_t n = part_off[p + 1] - part_off[p];
   const uint32_t nch = (uint32_t)((n + chunk_vecs - 1) / chunk_vecs);
-  for (uint32_t it = i0 + lane; it < i1; it += 32) {
-    const uint32_t local = it - i0;
-    desc[it] = make_uint4(p, local / nch, local % nch, 0u);
+  const uint32_t q0 = queue_off ? queue_off[p] : i0;
+  for (uint32_t local = lane; local < i1 - i0; local += 32) desc[q0 + local] = make_uint4(p, local / nch, local % nch, 0u);
+}
+
+// Longest items first: the queue holds the partitions in descending size (`order`, fixed at index creation), so the
+// last items a CTA draws are the short ones and the CTAs finish together.  With 1/8 of the items per GPU (partition
+// shards) the ragged end of a partition-id-ordered queue was ~10 % of the scan.  queue_off[p] = items of the
+// partitions before p in that order.  One block.
+__global__ void __launch_bounds__(1024)
+queue_offsets_kernel(const uint32_t* __restrict__ item_off, const uint32_t* __restrict__ order, uint32_t nlist,
+                     uint32_t* __restrict__ queue_off) {
+  __shared__ uint32_t s_part[1024];
+  __shared__ uint32_t s_carry;
+  const uint32_t t = threadIdx.x;
+  if (t == 0) s_carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < nlist; base += 1024) {
+    const uint32_t i = base + t;
+    uint32_t c = 0, p = 0;
+    if (i < nlist) {
+      p = order[i];
+      c = item_off[p + 1] - item_off[p];
+    }
+    s_part[t] = c;
+    __syncthreads();
+    for (uint32_t o = 1; o < 1024; o <<= 1) {  // inclusive scan
+      const uint32_t v = t >= o ? s_part[t - o] : 0;
+      __syncthreads();
+      s_part[t] += v;
+      __syncthreads();
+    }
+    if (i < nlist) queue_off[p] = s_carry + s_part[t] - c;
+    __syncthreads();
+    if (t == 1023) s_carry += s_part[1023];
+    __syncthreads();
   }
 }
 
