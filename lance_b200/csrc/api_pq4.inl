@@ -36,6 +36,13 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
   add(npairs * kprime * 4); add(npairs * kprime * 8); add(npairs * kprime * 8); add(npairs * kprime * 8); add(npairs * 4);
   add((size_t)Q * kprime * 4); add((size_t)Q * kprime * 8); add((size_t)Q * kprime * 8); add((size_t)Q * 4);
   add((size_t)Q * kprime * 4);
+  // grouped IVF_FLAT L2 scan (several queries share a partition's rows): work list of one query tile
+  const bool grouped = flat && ix->metric != LB200_DOT && ix->metric != LB200_COSINE && !getenv("LB200_FLAT_SIMPLE") &&
+                       !getenv("LB200_FLAT_PAIRWISE");
+  if (grouped) {
+    add((size_t)nlist * 8); add((size_t)tileQ * 4); add(tpairs * 4); add((size_t)(nlist + 1) * 8); add(tpairs * 4);
+    add(tpairs * 16); add(64);
+  }
   int rc = cx.arena.reserve(need);
   if (rc) return rc;
   cx.arena.reset();
@@ -54,6 +61,19 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
   uint64_t* d_mpos = cx.arena.take<uint64_t>((size_t)Q * kprime);
   uint32_t* d_mcnt = cx.arena.take<uint32_t>(Q);
   float* d_exact = cx.arena.take<float>((size_t)Q * kprime);
+  uint32_t *g_cnt = nullptr, *g_minp = nullptr, *g_rank = nullptr, *g_pair_off = nullptr, *g_item_off = nullptr, *g_pair_list = nullptr;
+  uint4* g_desc = nullptr;
+  unsigned long long* g_stats = nullptr;
+  if (grouped) {
+    g_cnt = cx.arena.take<uint32_t>((size_t)nlist * 2);
+    g_minp = cx.arena.take<uint32_t>(tileQ);
+    g_rank = cx.arena.take<uint32_t>(tpairs);
+    g_pair_off = cx.arena.take<uint32_t>(nlist + 1);
+    g_item_off = cx.arena.take<uint32_t>(nlist + 1);
+    g_pair_list = cx.arena.take<uint32_t>(tpairs);
+    g_desc = cx.arena.take<uint4>(tpairs);
+    g_stats = cx.arena.take<unsigned long long>(8);
+  }
 
   uint32_t launches = 0;
   lb200_stats stats = {};
@@ -97,7 +117,34 @@ static int search4_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, c
     if (flat) {
       const size_t fs = (size_t)dim * 4;
       if (fs > 48 * 1024) CK(cudaFuncSetAttribute(scanflat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs));
-      if (ix->metric == LB200_L2 && !getenv("LB200_FLAT_SIMPLE")) {
+      if (grouped) {
+        // work list of the tile: pairs grouped by partition, items = (partition, group of FLATG_QL queries)
+        CK(cudaMemsetAsync(g_cnt, 0, (size_t)nlist * 8, st));
+        CK(cudaMemsetAsync(g_minp, 0xff, (size_t)qn * 4, st));   // no cold packing here
+        count_pairs_kernel<<<(uint32_t)((pn + 255) / 256), 256, 0, st>>>(probes + p0, (uint32_t)pn, P, g_minp, g_cnt, g_cnt + nlist, g_rank);
+        offsets_kernel<<<1, 1024, 0, st>>>(g_cnt, g_cnt + nlist, ix->d_part_off, nlist, (uint32_t)FLATG_QL,
+                                           (uint32_t)std::max<uint64_t>(ix->max_part, 1), dim * 4, g_pair_off, g_item_off, g_stats);
+        scatter_pairs_kernel<<<(uint32_t)((pn + 255) / 256), 256, 0, st>>>(probes + p0, g_rank, g_pair_off, g_cnt, (uint32_t)pn, g_pair_list);
+        expand_items_kernel<<<(nlist * 32 + 255) / 256, 256, 0, st>>>(g_item_off, ix->d_part_off, nlist,
+                                                                      (uint32_t)std::max<uint64_t>(ix->max_part, 1), g_desc, nullptr);
+        flat_empty_pairs_kernel<<<(uint32_t)pn, 128, 0, st>>>(probes + p0, (uint32_t)pn, ix->d_part_off, d_dist, stride);
+        const int nch = dim % 16 == 0 && (dim == 64 || dim == 128 || dim == 256) ? (int)(dim / 16) : 0;
+        const size_t gs = ((size_t)16 * FLATG_QL * 16 * 17 + (nch ? 0 : (size_t)FLATG_QL * dim)) * 4;
+        const uint32_t gg = (uint32_t)std::min<size_t>(pn, (size_t)ix->sm_count * 3);
+#define LB200_FLATG(N)                                                                                                     \
+  do {                                                                                                                     \
+    CK(cudaFuncSetAttribute(scanflat_l2_group_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gs));           \
+    scanflat_l2_group_kernel<N><<<gg, 256, gs, st>>>(keys + (size_t)q0 * dim, P, dim, ix->d_part_off, ix->d_raw, g_desc,   \
+                                                     g_item_off + nlist, g_pair_list, g_pair_off, d_dist, stride, d_stats, \
+                                                     a.d_bitmask);                                                         \
+  } while (0)
+        if (nch == 4) LB200_FLATG(4);
+        else if (nch == 8) LB200_FLATG(8);
+        else if (nch == 16) LB200_FLATG(16);
+        else LB200_FLATG(0);
+#undef LB200_FLATG
+        launches += 5;
+      } else if (ix->metric == LB200_L2 && !getenv("LB200_FLAT_SIMPLE")) {
         if (fs > 48 * 1024) CK(cudaFuncSetAttribute(scanflat_l2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs));
         scanflat_l2_kernel<<<(uint32_t)pn, 256, fs, st>>>(keys + (size_t)q0 * dim, probes + p0, P, dim, ix->d_part_off,
                                                            ix->d_raw, d_dist, stride, d_stats, a.d_bitmask);

@@ -49,7 +49,7 @@ flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t 
                    int has_lower, float lower, int has_upper, float upper, float* __restrict__ out_dist,
                    uint64_t* __restrict__ out_idx, uint32_t* __restrict__ out_cnt) {
   extern __shared__ unsigned long long sl[];  // [kpow2] result list
-  __shared__ uint32_t hist[4096];
+  __shared__ uint32_t hist[8 * 256];
   __shared__ uint32_t s_prefix, s_mask, s_kk, s_less, s_fill, s_tiebase, s_wsum[8];
   // block = (query, segment of the row): a row is cut into nseg segments so that a small query tile
   // still fills the GPU; the per-segment lists are merged afterwards (merge_lists_kernel)
@@ -70,34 +70,67 @@ flat_select_kernel(const float* __restrict__ dist, size_t dist_stride, uint64_t 
     s_less = 0;
   }
   __syncthreads();
-  // total admissible count decides whether a k-th element exists
-  const int shifts[3] = {20, 8, 0};
-  const int widths[3] = {12, 12, 8};
+  // Radix select of the k-th smallest admissible key, 8 bits per pass.  The top bits of a row's distances are nearly
+  // all alike, so equal digits are first counted in registers (runs) and then added to a per-warp histogram: the
+  // first version (12-bit digits, one shared histogram, thread 0 walking 4096 bins) spent its time in same-address
+  // atomics and in that serial walk (cfg1_flat: 1.6 ms of select per 2.6 ms of scan).
   bool have_kth = true;
-  for (int lvl = 0; lvl < 3 && have_kth; lvl++) {
-    for (uint32_t i = threadIdx.x; i < 4096; i += 256) hist[i] = 0;
+  const uint32_t lane_ = threadIdx.x & 31, w_ = threadIdx.x >> 5;
+  uint32_t(*whist)[256] = reinterpret_cast<uint32_t(*)[256]>(hist);   // [8 warps][256]
+#pragma unroll 1
+  for (int shift = 24; shift >= 0 && have_kth; shift -= 8) {
+    for (uint32_t i = threadIdx.x; i < 8 * 256; i += 256) hist[i] = 0;
     __syncthreads();
     const uint32_t prefix = s_prefix, mask = s_mask;
+    uint32_t run_d = 0xffffffffu, run_c = 0;
     for (uint64_t i = threadIdx.x; i < n; i += 256) {
-      float v = drow[i];
+      const float v = drow[i];
       if (!admissible(v)) continue;
-      uint32_t key = ordered_key(v);
-      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shifts[lvl]) & ((1u << widths[lvl]) - 1u)], 1u);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t kk = s_kk, cum = 0, b = 0, nb = 1u << widths[lvl];
-      for (; b < nb; b++) {
-        if (cum + hist[b] >= kk) break;
-        cum += hist[b];
+      const uint32_t key = ordered_key(v);
+      if ((key & mask) != prefix) continue;
+      const uint32_t dg = (key >> shift) & 255u;
+      if (dg == run_d) run_c++;
+      else {
+        if (run_c) atomicAdd(&whist[w_][run_d], run_c);
+        run_d = dg;
+        run_c = 1;
       }
-      if (b == nb) {
-        s_kk = 0xffffffffu;  // fewer than k admissible rows: take everything
-      } else {
-        s_less += cum;
-        s_kk = kk - cum;
-        s_prefix = prefix | (b << shifts[lvl]);
-        s_mask = mask | (((1u << widths[lvl]) - 1u) << shifts[lvl]);
+    }
+    if (run_c) atomicAdd(&whist[w_][run_d], run_c);
+    __syncthreads();
+    uint32_t tot = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) tot += whist[j][threadIdx.x];
+    __syncthreads();
+    hist[threadIdx.x] = tot;
+    __syncthreads();
+    if (w_ == 0) {  // lane owns bins 8 lane .. 8 lane + 7
+      uint32_t c8[8], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 8; j++) { c8[j] = hist[lane_ * 8 + j]; sum += c8[j]; }
+      uint32_t incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane_ >= (uint32_t)o) incl += v;
+      }
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      const uint32_t kk = s_kk;
+      uint32_t before = incl - sum;
+      __syncwarp();
+      if (total < kk) {
+        if (lane_ == 0) s_kk = 0xffffffffu;  // fewer than k admissible rows: take everything
+      } else if (before < kk && kk <= incl) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          if (before < kk && kk <= before + c8[j]) {
+            s_less += before;
+            s_kk = kk - before;
+            s_prefix = prefix | ((lane_ * 8 + j) << shift);
+            s_mask = mask | (255u << shift);
+          }
+          before += c8[j];
+        }
       }
     }
     __syncthreads();

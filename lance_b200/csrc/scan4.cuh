@@ -569,6 +569,156 @@ scanflat_l2_kernel(const float* __restrict__ keys, const uint32_t* __restrict__ 
   }
 }
 
+// L2, several queries per CTA: a work item = (partition, group of up to 4 queries probing it) from the work list of
+// the 8-bit path (worklist.cuh), so a partition's rows are read once per query GROUP instead of once per pair (r01:
+// one CTA per pair, 0.46 of the roofline with every row crossing L2 once per query).  Arithmetic per (query, row) is
+// l2_scalar::<f32,f32,16> as above: thread l of a half-warp owns lane sum l; the 16 lane sums of 16 rows are then
+// transposed through shared memory so that thread l adds the sums of row l in lane order (one LDS + FADD per
+// value instead of 16 shuffles per row) and the half-warp writes 16 consecutive distances.
+// NCH = dim / 16 when the keys fit registers (dim 64 / 128 / 256), else 0: keys from shared memory, any dim.
+constexpr int FLATG_QL = 4;
+template <int NCH>
+__global__ void __launch_bounds__(256)
+scanflat_l2_group_kernel(const float* __restrict__ keys, uint32_t P, uint32_t dim, const uint64_t* __restrict__ part_off,
+                         const float* __restrict__ raw, const uint4* __restrict__ item_desc,
+                         const uint32_t* __restrict__ item_total, const uint32_t* __restrict__ pair_list,
+                         const uint32_t* __restrict__ pair_off, float* __restrict__ out, size_t out_stride,
+                         unsigned long long* __restrict__ stats, const uint64_t* const* __restrict__ bitmask) {
+  constexpr int QL = FLATG_QL;
+  extern __shared__ float fg_smem[];
+  float* part_sums = fg_smem;                      // [16 half-warps][QL][16 rows][17]
+  float* skeys = fg_smem + 16 * QL * 16 * 17;      // [QL][dim] (NCH == 0 only)
+  __shared__ uint32_t s_pair[QL];
+  const uint32_t tid = threadIdx.x, hw = tid >> 4, l = tid & 15;
+  const uint32_t nchunk = NCH > 0 ? (uint32_t)NCH : dim >> 4, rem0 = nchunk << 4;
+  float* my = part_sums + (size_t)hw * QL * 16 * 17;
+  const uint32_t total = *item_total;
+  for (uint32_t item = blockIdx.x; item < total; item += gridDim.x) {
+    const uint4 de = item_desc[item];
+    const uint32_t part = de.x, g = de.y;
+    const uint32_t pbase = pair_off[part] + g * QL;
+    const uint32_t nq = min((uint32_t)QL, pair_off[part + 1] - pbase);
+    __syncthreads();   // the previous item's readers of s_pair / skeys are done
+    if (tid < QL) s_pair[tid] = tid < nq ? pair_list[pbase + tid] : 0u;
+    __syncthreads();
+    float xq[QL][NCH > 0 ? NCH : 1];
+    if (NCH > 0) {
+#pragma unroll
+      for (int q = 0; q < QL; q++)
+#pragma unroll
+        for (int c = 0; c < NCH; c++) xq[q][c] = (uint32_t)q < nq ? keys[(size_t)(s_pair[q] / P) * dim + c * 16 + l] : 0.0f;
+    } else {
+      for (uint32_t i = tid; i < QL * dim; i += 256) {
+        const uint32_t q = i / dim;
+        skeys[i] = q < nq ? keys[(size_t)(s_pair[q] / P) * dim + (i - q * dim)] : 0.0f;
+      }
+      __syncthreads();
+    }
+    const uint64_t off = part_off[part], n = part_off[part + 1] - off;
+    const uint64_t* bm = bitmask ? bitmask[part] : nullptr;
+    for (uint64_t base = 0; base < n; base += 256) {          // uniform trip count over the CTA
+      const uint64_t r0 = base + hw * 16;
+      if (NCH > 0) {
+        // RW rows per step: all their loads are issued before the first is used (the kernel is latency-bound on the
+        // row reads: r02 ncu of the 1-row version, 30 of 35 stall cycles per issue on the loads)
+        constexpr int RW = 4;
+#pragma unroll 1
+        for (uint32_t j = 0; j < 16; j += RW) {
+          float yv[RW][NCH > 0 ? NCH : 1];
+#pragma unroll
+          for (int k = 0; k < RW; k++) {
+            const uint64_t r = r0 + j + k;
+            const float* y = raw + (off + (r < n ? r : 0)) * dim + l;
+#pragma unroll
+            for (int c = 0; c < NCH; c++) yv[k][c] = __ldg(y + c * 16);
+          }
+#pragma unroll
+          for (int k = 0; k < RW; k++) {
+            float a[QL];
+#pragma unroll
+            for (int q = 0; q < QL; q++) a[q] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < NCH; c++)
+#pragma unroll
+              for (int q = 0; q < QL; q++) {
+                const float d = __fsub_rn(xq[q][c], yv[k][c]);
+                a[q] = __fadd_rn(a[q], __fmul_rn(d, d));
+              }
+#pragma unroll
+            for (int q = 0; q < QL; q++) my[(q * 16 + j + k) * 17 + l] = a[q];
+          }
+        }
+      } else {
+#pragma unroll 2
+        for (uint32_t j = 0; j < 16; j++) {
+          const uint64_t r = r0 + j;
+          float a[QL];
+#pragma unroll
+          for (int q = 0; q < QL; q++) a[q] = 0.0f;
+          if (r < n) {
+            const float* y = raw + (off + r) * dim + l;
+#pragma unroll 8
+            for (uint32_t c = 0; c < nchunk; c++) {
+              const float yv = __ldg(y + c * 16);
+#pragma unroll
+              for (int q = 0; q < QL; q++) {
+                const float d = __fsub_rn(skeys[q * dim + c * 16 + l], yv);
+                a[q] = __fadd_rn(a[q], __fmul_rn(d, d));
+              }
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < QL; q++) my[(q * 16 + j) * 17 + l] = a[q];
+        }
+      }
+      __syncwarp();
+      // thread l finishes row r0 + l of every query: remainder first (l2.rs:73-83), then the lanes in order
+      const uint64_t r = r0 + l;
+      if (r < n) {
+        const bool allowed = !bm || ((bm[r >> 6] >> (r & 63)) & 1);
+#pragma unroll
+        for (int q = 0; q < QL; q++) {
+          if ((uint32_t)q >= nq) break;
+          float v = __int_as_float(0x7fc00000);
+          if (allowed) {
+            float sr = 0.0f;
+            if (NCH == 0) {
+              const float* y = raw + (off + r) * dim;
+              for (uint32_t i = rem0; i < dim; i++) {
+                const float d = __fsub_rn(skeys[q * dim + i], y[i]);
+                sr = __fadd_rn(sr, __fmul_rn(d, d));
+              }
+            }
+            float t = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 16; i++) t = __fadd_rn(t, my[(q * 16 + l) * 17 + i]);
+            v = __fadd_rn(sr, t);
+          }
+          out[(size_t)s_pair[q] * out_stride + r] = v;
+        }
+      }
+      __syncwarp();
+    }
+    // padding of the scratch rows (flat_select reads out_stride entries)
+    for (uint32_t q = 0; q < nq; q++)
+      for (uint64_t i = n + tid; i < out_stride; i += 256) out[(size_t)s_pair[q] * out_stride + i] = __int_as_float(0x7fc00000);
+    if (stats && tid == 0) {
+      atomicAdd(&stats[0], (unsigned long long)n * dim * 4 * nq);
+      atomicAdd(&stats[1], (unsigned long long)nq);
+    }
+  }
+}
+
+// pairs that probe an EMPTY partition have no work item: their scratch rows are all padding
+__global__ void flat_empty_pairs_kernel(const uint32_t* __restrict__ probes, uint32_t npairs, const uint64_t* __restrict__ part_off,
+                                        float* __restrict__ out, size_t out_stride) {
+  const uint32_t e = blockIdx.x;
+  if (e >= npairs) return;
+  const uint32_t p = probes[e];
+  if (part_off[p + 1] != part_off[p]) return;
+  for (uint64_t i = threadIdx.x; i < out_stride; i += blockDim.x) out[(size_t)e * out_stride + i] = __int_as_float(0x7fc00000);
+}
+
 // local index of a selected row -> row id and position in the index (for the merge and the refine)
 __global__ void gather4_kernel(const uint32_t* __restrict__ probes, const uint64_t* __restrict__ part_off,
                                const uint64_t* __restrict__ row_ids, const uint64_t* __restrict__ sel_idx,

@@ -8,6 +8,6 @@ python - <<PY
 import csv
 rows = [r for r in csv.reader(open("gpurun_out/${T}_launches_$W.csv")) if len(r) > 10 and r[0].isdigit()]
 names = [(r[4].split('(')[0][-44:], float(r[-1])) for r in rows]
-idx = max(i for i, (n, _) in enumerate(names) if 'scan3_kernel' in n or 'scan4' in n or 'scanflat' in n)
+idx = max(i for i, (n, _) in enumerate(names) if "scan3_kernel" in n or "scan4" in n or "scanflat" in n)
 for n, v in names[max(0, idx - 12): idx + 6]: print(f"{n:46s} {v/1e6:8.3f} ms")
 PY
