@@ -480,11 +480,11 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
       else if (ix->dsub == 8)
         lut_prepass_kernel<8><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
                                                  (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max,
-                                                 pre_image ? d_pair_list : nullptr, d_pair_off, (uint32_t)sc.ql);
+                                                 pre_image ? d_pair_list : nullptr, d_pair_off, (uint32_t)sc.ql, 0x8000000080000000ull);
       else
         lut_prepass_kernel<16><<<g, 256, 0, st>>>(keys, ix->d_centroids, ix->d_codebook, pr, ix->d_part_off,
                                                   (uint32_t)pre_units, P, dim, ix->M, d_lut, d_lut_max,
-                                                  pre_image ? d_pair_list : nullptr, d_pair_off, (uint32_t)sc.ql);
+                                                  pre_image ? d_pair_list : nullptr, d_pair_off, (uint32_t)sc.ql, 0x8000000080000000ull);
       CK(cudaGetLastError());
       launches++;
       sp.lut_src = d_lut;

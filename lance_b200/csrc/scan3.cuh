@@ -143,6 +143,38 @@ __device__ __forceinline__ float l2_once_packed(const f32x2_t* X, const f32x2_t*
 }
 
 // ---------------------------------------------------------------------------------------------
+// The same trees with the products formed by fma.rn.f32x2(d, d, -0.0): x * x + (-0) rounds once, exactly like
+// mul.rn (the sum of a product and -0 is the product, +0 stays +0), and a packed FMA feeding a packed ADD cannot be
+// contracted any further -- so the first tree level runs packed too instead of unpacking every product (the
+// contraction problem described above).  `nz` = two packed -0.0f that ptxas cannot see through (a kernel parameter):
+// with a visible constant it would turn the fma back into a mul and contract it into the add.
+__device__ __forceinline__ f32x2_t fma2(f32x2_t a, f32x2_t b, f32x2_t c) {
+  f32x2_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+template <int DSUB>
+__device__ __forceinline__ float l2_once_packed_nz(const f32x2_t* X, const f32x2_t* Y, f32x2_t nz) {
+  f32x2_t P[DSUB / 2];
+#pragma unroll
+  for (int i = 0; i < DSUB / 2; i++) {
+    const f32x2_t d = sub2(X[i], Y[i]);
+    P[i] = fma2(d, d, nz);
+  }
+  float lo, hi;
+  if (DSUB == 16) {
+    // reduce_sum16: y8[i] = sq[i] + sq[i + 8]  ->  (y8[2i], y8[2i+1]) = P[i] + P[i + 4]
+    const f32x2_t y01 = add2(P[0], P[4]), y23 = add2(P[1], P[5]), y45 = add2(P[2], P[6]), y67 = add2(P[3], P[7]);
+    const f32x2_t a01 = add2(y01, y45);   // reduce_sum8: (a0, a1) = (y0 + y4, y1 + y5)
+    const f32x2_t a23 = add2(y23, y67);   //              (a2, a3)
+    upk2(add2(a01, a23), lo, hi);         // (a0 + a2, a1 + a3)
+  } else {
+    const f32x2_t a01 = add2(P[0], P[2]), a23 = add2(P[1], P[3]);   // a[i] = sq[i] + sq[i + 4]
+    upk2(add2(a01, a23), lo, hi);
+  }
+  return __fadd_rn(lo, hi);
+}
+
 // ADC tables as a pre-pass (A3 + A4 out of the scan kernel).  The scan kernel builds its tables per
 // work item, re-reading the whole codebook (M*256*dsub*4 bytes) for QL queries; when tables are
 // expensive relative to the rows they serve (small partitions, many sub-vectors) or do not depend
@@ -158,7 +190,7 @@ __host__ __device__ __forceinline__ uint64_t lut_image_base(uint32_t pair_off_p,
   return (uint64_t)pair_off_p + (uint64_t)part * (ql - 1) + (uint64_t)g * ql;
 }
 constexpr uint32_t LUTPRE_UNITS = 64;
-constexpr int LUTPRE_CPT = 2;                              // codes per thread
+constexpr int LUTPRE_CPT = 4;                              // codes per thread
 constexpr uint32_t LUTPRE_SPLIT = 256 / (16 * LUTPRE_CPT);  // blocks per 16-sub-vector chunk
 template <int DSUB>
 __global__ void __launch_bounds__(256)
@@ -167,7 +199,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
                    const uint64_t* __restrict__ part_off, uint32_t n_units, uint32_t P, uint32_t dim, uint32_t M,
                    float* __restrict__ out, uint32_t* __restrict__ out_max /*[n_units], zeroed*/,
                    const uint32_t* __restrict__ pair_list /*image mode: unit = position in the pair list; else null*/,
-                   const uint32_t* __restrict__ pair_off, uint32_t ql) {
+                   const uint32_t* __restrict__ pair_off, uint32_t ql, unsigned long long negzero2 /*0x8000000080000000*/) {
   constexpr int PITCH = DSUB + 4;  // floats; 8 lanes of an LDS.128 phase land on 8 distinct bank groups
   constexpr int UB = 16;           // units staged at a time
   __shared__ __align__(16) float xs[UB][16 * PITCH];
@@ -253,7 +285,7 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
           f32x2_t Y[DSUB / 2];
 #pragma unroll
           for (int j = 0; j < DSUB / 2; j++) Y[j] = pk2(y[i][2 * j], y[i][2 * j + 1]);
-          v = l2_once_packed<DSUB>(X, Y);
+          v = l2_once_packed_nz<DSUB>(X, Y, negzero2);
         } else {
           v = lut_elem<DSUB>(false, x, y[i], DSUB);
         }
