@@ -68,7 +68,8 @@ enum {
  * 4-bit and IVF_FLAT handles take every search entry point, prefilter bitmasks and the shard contract (merged k' list
  * + exact distances, d_out_exact) included.  With a prefilter a 4-bit handle computes each allowed row from the
  * UNQUANTISED f32 table (PQDistCalculator::distance, pq/storage.rs:602-617), as FlatIndex::search does
- * (flat/index.rs:106-122).  The peer-memory exchange of lb200_shard_* / lb200_group_* is built on 8-bit handles. */
+ * (flat/index.rs:106-122).  lb200_shard_* / lb200_group_* take all three handle kinds (the cross-GPU pruning bounds are
+ * an 8-bit-scan feature; 4-bit and IVF_FLAT shards exchange probe lists and candidate lists only). */
 int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist,
                            const float* centroids, uint32_t num_sub_vectors, uint32_t num_bits,
                            const float* codebook, const uint64_t* part_offsets,

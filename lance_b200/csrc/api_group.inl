@@ -124,7 +124,6 @@ static void shard_comm_free(lb200_index* ix) {
 extern "C" int32_t lb200_shard_export(lb200_index* ix, uint32_t max_queries, uint32_t max_nprobes, uint32_t max_kprime,
                                       void* blob_out_128, uint64_t* dev_ptrs_out_2) {
   if (!ix || !max_queries || !max_nprobes || !max_kprime) return set_err(LB200_EINVAL, "null index or zero capacity");
-  if (ix->bits != 8) return set_err(LB200_EUNSUPPORTED, "shard mode is supported on 8-bit PQ handles only");
   if (max_kprime > 512) return set_err(LB200_EUNSUPPORTED, "k*refine_factor=%u > 512", max_kprime);
   CK(cudaSetDevice(ix->device));
   lb200_peer_thresholds_detach(ix);
@@ -491,7 +490,9 @@ extern "C" int32_t lb200_group_create(const int32_t* device_ids, uint32_t G, int
   if (!out) return set_err(LB200_EINVAL, "out is null");
   *out = nullptr;
   if (!device_ids || !G || G > SHARD_MAX) return set_err(LB200_EINVAL, "G=%u out of range [1,%u]", G, SHARD_MAX);
-  if (num_bits != 8) return set_err(LB200_EUNSUPPORTED, "groups are supported for 8-bit PQ only");
+  if (num_bits != 8 && num_bits != 4 && num_bits != 32) return set_err(LB200_EUNSUPPORTED, "num_bits=%u", num_bits);
+  // bytes of one row's codes: 8-bit PQ M, 4-bit PQ M / 2, IVF_FLAT (num_bits 32) none -- its rows are the raw vectors
+  const size_t cbytes = num_bits == 8 ? M : num_bits == 4 ? M / 2 : 0;
   if (!nlist || !part_offsets || !M || !dim) return set_err(LB200_EINVAL, "bad index arguments");
   lb200_group* g = nullptr;
   try {
@@ -543,13 +544,13 @@ extern "C" int32_t lb200_group_create(const int32_t* device_ids, uint32_t G, int
       std::vector<uint64_t> offs(nlist + 1, 0);
       for (uint32_t p = 0; p < nlist; p++) offs[p + 1] = offs[p] + (g->owner[p] == r ? part_offsets[p + 1] - part_offsets[p] : 0);
       const uint64_t n = offs[nlist];
-      std::vector<uint8_t> sc(n * M);
+      std::vector<uint8_t> sc(n * cbytes);
       std::vector<uint64_t> sr(n);
       std::vector<float> sv(raw_vectors_or_null ? n * dim : 0);
       for (uint32_t p = 0; p < nlist; p++) {
         if (g->owner[p] != r) continue;
         const uint64_t o = part_offsets[p], np = part_offsets[p + 1] - o;
-        memcpy(sc.data() + offs[p] * M, codes + o * M, np * M);
+        if (cbytes) memcpy(sc.data() + offs[p] * cbytes, codes + o * cbytes, np * cbytes);
         memcpy(sr.data() + offs[p], row_ids + o, np * 8);
         if (raw_vectors_or_null) memcpy(sv.data() + offs[p] * dim, raw_vectors_or_null + o * dim, np * dim * 4);
       }

@@ -310,7 +310,8 @@ class IvfPqGroup:
         raw = None if data.raw_vectors is None else _f32(data.raw_vectors)
         h = C.c_void_p()
         check(L.lb200_group_create(devs, C.c_uint32(G), C.c_int32(DistanceType.code(data.metric)), C.c_uint32(self.dim),
-                                   C.c_uint32(int(data.nlist)), _p(cents), C.c_uint32(int(data.M)), C.c_uint32(8), _p(cb),
+                                   C.c_uint32(int(data.nlist)), _p(cents), C.c_uint32(int(data.M)),
+                                   C.c_uint32(int(getattr(data, "num_bits", 8))), _p(cb),
                                    _p(offs), _p(codes), _p(rids), _p(raw), _p(po), C.c_uint32(max_queries),
                                    C.c_uint32(max_nprobes), C.c_uint32(max_kprime), C.byref(h)))
         self._h = h

@@ -77,3 +77,43 @@ def test_group_search_equals_single_index(oracle, metric, refine, G):
     with pytest.raises(LanceB200Error, match="exceeds the exported capacity"):
         grp.search(Query(key=np.zeros((65, 64), np.float32), k=10, nprobes=7))
     grp.close()
+
+
+@pytest.mark.parametrize("kind,metric,refine,G", [("pq4", "l2", 0, 2), ("pq4", "cosine", 2, 3), ("flat", "l2", 0, 3), ("flat", "dot", 2, 2)])
+def test_group_search_on_4bit_and_ivf_flat_handles(oracle, kind, metric, refine, G):
+    """The peer-memory exchange with 4-bit PQ and IVF_FLAT shards (shard contract of csrc/api_pq4.inl): one
+    lb200_group_search call == the single-index search, bit for bit."""
+    from lance_b200 import IvfPqGroup, Query
+    from lance_b200.synth import IvfPqData
+    rng = np.random.default_rng(17)
+    d, sizes = 32, [300, 0, 77, 512, 1, 950, 64, 200]
+    nlist, N = len(sizes), sum(sizes)
+    offs = np.zeros(nlist + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    cents = rng.normal(size=(nlist, d)).astype(np.float32)
+    raw = (cents[np.repeat(np.arange(nlist), sizes)] + 0.3 * rng.normal(size=(N, d))).astype(np.float32)
+    rids = rng.permutation(N * 2)[:N].astype(np.uint64)
+    if kind == "pq4":
+        M = 8
+        cb = rng.normal(size=(M, 16, d // M)).astype(np.float32)
+        codes = np.concatenate([rng.integers(0, 256, size=(M // 2, s), dtype=np.uint8).ravel() for s in sizes])
+        data = IvfPqData(metric, d, nlist, M, cents, cb, offs, codes, rids, raw, 4)
+        want = lambda x, k, P, rf: oracle.OracleIndex(data).search(x[None, :], k, P, rf or 0)
+    else:
+        data = IvfPqData(metric, d, nlist, 1, cents, np.zeros((1, 256, d), np.float32), offs, np.zeros(0, np.uint8), rids, raw, 32)
+        want = None
+    q = np.concatenate([raw[::397], rng.normal(size=(3, d)).astype(np.float32)])
+    k, P = 10, 5
+    grp = IvfPqGroup(data, [0] * G, max_queries=32, max_nprobes=8, max_kprime=40)
+    for batch in range(2):
+        gd, gi, gc = grp.search(Query(key=q, k=k, nprobes=P, refine_factor=refine or None))
+        for j in range(len(q)):
+            if kind == "pq4":
+                rd, ri, rc, _ = want(q[j], k, P, refine)
+                rd, ri = rd[0, :min(int(rc[0]), k)], ri[0, :min(int(rc[0]), k)]
+            else:
+                rd, ri = oracle.ivf_flat_search(data, q[j], k, P, refine or None)
+            n = int(gc[j])
+            assert n == len(ri) and gi[j, :n].tolist() == ri.tolist(), (kind, metric, batch, j)
+            assert _bits(gd[j, :n]).tolist() == _bits(rd).tolist()
+    grp.close()
