@@ -842,6 +842,28 @@ def main():
         keys = _normalize(queries[:nq], device_id=local) if metric == "cosine" else queries[:nq]
         gp = ix.find_partitions(keys, nprobes)
         line["parity"] = parity_block(ref, (h_od.numpy(), h_oi.numpy().view(np.uint64), h_oc.numpy()), k, gpu_probes=gp)
+    if world == 1 and not args.no_cpu_baseline and _BITS == 32:
+        # IVF_FLAT: the oracle's per-query restatement (oracle.ivf_flat_search: find_partitions + flat kNN per probed
+        # partition, Python loop over the partitions, C distance kernels), a small sample on one thread
+        import oracle
+        nq = min(64, Q)
+        rd = np.full((nq, k), np.inf, dtype=np.float32)
+        ri = np.full((nq, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+        rc = np.zeros(nq, dtype=np.uint32)
+        rp = np.zeros((nq, min(nprobes, nlist)), dtype=np.uint32)
+        t0 = time.perf_counter()
+        for j in range(nq):
+            d_, r_ = oracle.ivf_flat_search(data, queries[j], k, nprobes, refine or None)
+            rd[j, :len(d_)], ri[j, :len(r_)], rc[j] = d_, r_, len(r_)
+        cdt = time.perf_counter() - t0
+        for j in range(nq):
+            key = oracle.normalize(queries[j]) if metric == "cosine" else queries[j]
+            rp[j] = oracle.find_partitions(data.centroids, key, nprobes, metric)[0]
+        line["cpu_baseline"] = {"value": nq / cdt, "unit": "queries/s", "cores": 1, "kind": "port",
+                                "sample": f"first {nq} queries of the same batch, {cdt:.1f} s, one thread (oracle.ivf_flat_search: "
+                                          "Python loop over the probed partitions around the C distance kernels)"}
+        gp = ix.find_partitions(queries[:nq], nprobes)
+        line["parity"] = parity_block((rd, ri, rc, rp), (h_od.numpy(), h_oi.numpy().view(np.uint64), h_oc.numpy()), k, gpu_probes=gp)
     if world == 1 and _BITS == 8 and not args.no_recall and not args.no_cpu_baseline and args.workload != "tiny":
         ix.close()   # free the benchmark index first
         rb = recall_block(wl, local)
