@@ -256,6 +256,8 @@ def run_flat(args):
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     dev = torch.device("cuda", 0)
     N, d, k, Q = 1_000_000, 128, 10, args.queries or 256
+    fmetric = args.flat_metric          # "also run cosine and dot for coverage" (benchmarks/flat/benchmark.py:68)
+    fcode = {"l2": 0, "cosine": 1, "dot": 2}[fmetric]
     rng = np.random.default_rng(1234)
     vecs = np.clip(np.rint(rng.normal(64, 32, size=(N, d))), 0, 218).astype(np.float32)  # SIFT-like integers
     queries = np.clip(np.rint(rng.normal(64, 32, size=(Q, d))), 0, 218).astype(np.float32)
@@ -274,12 +276,12 @@ def run_flat(args):
     h_oc = torch.empty((Q,), dtype=torch.int32).pin_memory()
 
     def step():
-        check(L.lb200_column_flat_topk_device(col, C.c_int32(0), C.c_void_p(d_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
+        check(L.lb200_column_flat_topk_device(col, C.c_int32(fcode), C.c_void_p(d_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
                                               C.c_void_p(od.data_ptr()), C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()),
                                               C.c_void_p(stream.cuda_stream)))
 
     def e2e_step():  # host queries in, host results out, through the C ABI (H2D + D2H inside)
-        check(L.lb200_column_flat_topk(col, C.c_int32(0), C.c_void_p(h_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
+        check(L.lb200_column_flat_topk(col, C.c_int32(fcode), C.c_void_p(h_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
                                        C.c_void_p(h_od.data_ptr()), C.c_void_p(h_oi.data_ptr()), C.c_void_p(h_oc.data_ptr())))
 
     for _ in range(max(args.warmup, 3)):
@@ -339,7 +341,8 @@ def run_flat(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32 (results); bf16 tensor-core candidate filter + exact f32 re-score",
             "data": "synthetic",
-            "config": {"workload": f"flat brute-force L2 kNN 1Mx128 f32, k=10, {Q} queries per step (BASELINE configs[1])",
+            "config": {"workload": f"flat brute-force {fmetric.upper()} kNN 1Mx128 f32, k=10, {Q} queries per step (BASELINE configs[1]"
+                                   + ("" if fmetric == "l2" else "; metric varied as the reference's flat benchmark does") + ")",
                        "l2_policy": "inputs larger than L2 (256 MB of bf16 rows + 512 MB of f32 rows)",
                        "path": "lb200_column_flat_topk_device (resident column)",
                        "filter": {"used_tc": bool(tc.value), "fell_back": bool(fb.value), "candidates_per_query": cand.value / Q},
@@ -358,7 +361,7 @@ def run_flat(args):
         cores = oracle.max_threads()
         nq = min(32, Q)
         t0 = time.perf_counter()
-        fres = oracle.flat_knn("l2", queries[:nq], vecs, k, threads=cores)
+        fres = oracle.flat_knn(fmetric, queries[:nq], vecs, k, threads=cores)
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": nq / dt, "unit": "queries/s", "cores": cores, "kind": "port",
                                 "sample": f"first {nq} queries, {dt:.1f} s, oracle port on {cores} threads"}
@@ -577,6 +580,7 @@ def main():
     ap.add_argument("--scan-variant", type=int, default=0)
     ap.add_argument("--queries", type=int, default=0,
                     help="override the workload's queries per step (batch-size sweep of BASELINE configs[4])")
+    ap.add_argument("--flat-metric", default="l2", choices=["l2", "cosine", "dot"], help="metric of --workload cfg2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-recall", action="store_true", help="skip the real-built-index recall@10 block")
     ap.add_argument("--shard-of", type=int, default=0,

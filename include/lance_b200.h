@@ -285,12 +285,13 @@ int32_t lb200_flat_topk_device(int32_t device_id, int32_t metric, uint32_t dim,
 /* A vector column kept RESIDENT on the device for flat kNN (compute_distance + SortExec(fetch = k), flat.rs:28-86,
  * scanner.rs:2066-2136; KNNVectorDistanceExec reads the column batch by batch, io/exec/knn.rs:156-183): the rows are
  * uploaded once instead of once per lb200_flat_topk call.  lb200_column_flat_topk[_device] == lb200_flat_topk with the
- * column's rows and validity, results bit-identical.  For L2 on columns of >= 65 536 rows with dim % 64 == 0, dim <= 256
+ * column's rows and validity, results bit-identical.  For L2, cosine and dot on columns of >= 65 536 rows with dim % 64 == 0, dim <= 256
  * and no validity bitmap / bounds the call runs a tensor-core CANDIDATE FILTER first (tcgen05.mma on bf16 copies,
  * operands by TMA, accumulators in TMEM; csrc/flat_tc.cuh): it keeps, per query, every row whose approximate distance is
  * within a proved error bound of an exact upper bound of the k-th distance, and only those rows are scored by the exact
  * fp32 kernels -- same results by construction (csrc/api_column.inl states the bound); if a candidate buffer overflows
- * the exact path answers.  Calls on one column serialise.  lb200_column_last_call reports what the last call did. */
+ * the exact path answers (and the column's next call gets larger buffers).  Cosine keeps one more bf16 copy of the
+ * rows (unit length), made on the first cosine call.  Calls on one column serialise.  lb200_column_last_call reports what the last call did. */
 typedef struct lb200_column lb200_column;
 int32_t lb200_column_create(int32_t device_id, uint32_t dim, const float* vectors, const uint8_t* validity_or_null,
                             uint64_t n, lb200_column** out);

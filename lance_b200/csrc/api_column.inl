@@ -25,6 +25,12 @@ struct lb200_column {
   float* d_v = nullptr;
   uint8_t* d_valid = nullptr;
   __nv_bfloat16* d_vb = nullptr;
+  __nv_bfloat16* d_vb_unit = nullptr;   // cosine: unit-length rows in bf16, built on the first cosine call
+  CUtensorMap map_v_unit;
+  // the sample in the filter's own formats: thresholds come from upper bounds computed by the tensor-core kernel
+  __nv_bfloat16 *d_sb = nullptr, *d_sb_unit = nullptr;
+  float2* d_snorm = nullptr;            // (|y|^2 (1 + e2), |y|) of the sample rows
+  CUtensorMap map_s, map_s_unit;
   float2* d_norm = nullptr;
   float* d_sample = nullptr;
   uint32_t ns = 0;
@@ -37,6 +43,7 @@ struct lb200_column {
   cudaStream_t stream = nullptr;
   int sm_count = 148;
   // last call
+  uint32_t cap_boost = 1;
   uint32_t last_tc = 0, last_fallback = 0;
   uint64_t last_candidates = 0;
 };
@@ -82,6 +89,19 @@ static void ftc_coeffs(uint32_t dim, float* e1, float* e2) {
   *e1 = (float)(2.0 * cc * 1.02 + 1.0 / 2097152.0);
   *e2 = (float)((((3.0 * dim + 12.0) / 16777216.0) + 1.0 / 4194304.0) * 1.02 + 1.0 / 2097152.0);
 }
+// dot: exact R = fl(1 - fl_dot(q, y)), |R - (1 - q.y)| <= (d + 2) u |q||y| + u (u = 2^-24); approx 1 - P with
+// |P - q.y| <= cc |q||y|  =>  E = e1 |q||y| + e0,  e1 = 1.02 (cc + (d + 2) u) + 2^-21 (roundings of the test), e0 = 2^-22
+static void ftc_coeffs_dot(uint32_t dim, float* e1, float* e0) {
+  const double cc = 0.00390625 * (1.0 + 1.0 / 1024.0) + (double)dim / 2097152.0;
+  *e1 = (float)(1.02 * (cc + (dim + 2.0) / 16777216.0) + 1.0 / 2097152.0);
+  *e0 = (float)(1.0 / 4194304.0);
+}
+// cosine: exact R = cosine_fast, |R - (1 - cos)| <= (2 d + 7) u; approx 1 - P' / |q| on rows normalised before the bf16
+// rounding, |P' / |q| - cos| <= cc + (d + 7) u  =>  E = 1.02 (cc + (3 d + 14) u) + 2^-20, independent of the norms
+static void ftc_coeffs_cos(uint32_t dim, float* e) {
+  const double cc = 0.00390625 * (1.0 + 1.0 / 1024.0) + (double)dim / 2097152.0;
+  *e = (float)(1.02 * (cc + (3.0 * dim + 14.0) / 16777216.0) + 1.0 / 1048576.0);
+}
 
 static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q, uint32_t k, bool has_lower, float lower, bool has_upper,
                        float upper, float* d_od, uint64_t* d_oi, uint32_t* d_oc, cudaStream_t st) {
@@ -105,12 +125,30 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   const uint32_t dim = c->dim;
   // expected candidates per query ~ k n / ns (rows below the sample's k-th distance); 4x head-room
   const uint64_t expect = c->ns ? (uint64_t)k * n / c->ns : ~0ull;
+  // thresholds: exact k-th distance over the sample for L2 (the slab kernel makes that 0.1 ms), k-th smallest UPPER
+  // bound from the tensor-core kernel for cosine / dot (their exact kernels would cost 2 ms on the sample); the looser
+  // threshold keeps about twice the rows, hence the larger candidate buffers.  c->cap_boost doubles after an overflow.
+  const bool tc_thr = getenv("LB200_FLAT_TC_THR") ? atoi(getenv("LB200_FLAT_TC_THR")) != 0 : metric != LB200_L2;
+  const uint64_t want_cap = ((tc_thr ? 8 : 4) * expect + 256) * c->cap_boost;
   uint32_t cap = 1024;
-  while (cap < 4 * expect + 256 && cap < 16384) cap <<= 1;
-  const bool use_tc = c->tc_ok && metric == LB200_L2 && !has_lower && !has_upper && k <= c->ns && 4 * expect + 256 <= 16384 && Q > 0 &&
-                      !getenv("LB200_FLAT_NO_TC");
+  while (cap < want_cap && cap < 16384) cap <<= 1;
+  const bool use_tc = c->tc_ok && (metric == LB200_L2 || metric == LB200_COSINE || metric == LB200_DOT) && !has_lower && !has_upper &&
+                      k <= c->ns && (tc_thr ? 8 : 4) * expect + 256 <= 16384 && Q > 0 && !getenv("LB200_FLAT_NO_TC");
   if (!use_tc)
     return flat_topk_device_impl(metric, dim, d_q, Q, c->d_v, c->d_valid, n, k, has_lower, lower, has_upper, upper, d_od, d_oi, d_oc, st);
+  if (metric == LB200_COSINE && !c->d_vb_unit) {   // first cosine call: the unit-length bf16 copy (c->mu is held)
+    cudaError_t e = cudaMalloc(&c->d_vb_unit, (size_t)n * dim * 2);
+    if (e != cudaSuccess) return set_err(LB200_ENOMEM, "cosine copy of the column: %s", cudaGetErrorString(e));
+    to_bf16_unit_kernel<<<(uint32_t)((n * 32 + 255) / 256), 256, 0, st>>>(c->d_v, n, dim, c->d_vb_unit);
+    CK(cudaGetLastError());
+    int rcm = make_tile_map(&c->map_v_unit, c->d_vb_unit, n, dim);
+    if (rcm) return rcm;
+    e = cudaMalloc(&c->d_sb_unit, (size_t)c->ns * dim * 2);
+    if (e != cudaSuccess) return set_err(LB200_ENOMEM, "cosine copy of the sample: %s", cudaGetErrorString(e));
+    to_bf16_unit_kernel<<<(uint32_t)(((uint64_t)c->ns * 32 + 255) / 256), 256, 0, st>>>(c->d_sample, c->ns, dim, c->d_sb_unit);
+    CK(cudaGetLastError());
+    if ((rcm = make_tile_map(&c->map_s_unit, c->d_sb_unit, c->ns, dim))) return rcm;
+  }
   const uint32_t Qpad = (Q + FTC_M - 1) / FTC_M * FTC_M;
   const uint32_t ns = c->ns;
   size_t need = 0;
@@ -130,31 +168,53 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   uint32_t* d_flag = c->scratch.take<uint32_t>(16);
   float* d_sd = c->scratch.take<float>((size_t)Q * ns);
   uint32_t* d_raw = c->scratch.take<uint32_t>(Q);
-  // (1) thresholds: exact distances of every query to the sample rows, k-th smallest per query
-  if ((rc = flat_dist_launch(metric, d_q, Q, c->d_sample, nullptr, ns, dim, d_sd, ns, st))) return rc;
-  static_assert(COL_SAMPLE == 256 * 64, "ftc_kth_kernel<64> holds the sample in 64 registers per thread");
-  ftc_kth_kernel<64><<<Qpad, 256, 0, st>>>(d_sd, ns, Q, k, d_thr, d_cnt);
-  // (2) queries -> bf16 + norms (padding rows zero)
+  // (1) queries -> bf16 + norms (padding rows zero)
   CK(cudaMemsetAsync(d_qb, 0, (size_t)Qpad * dim * 2, st));
   CK(cudaMemsetAsync(d_qn, 0, (size_t)Qpad * 8, st));
   CK(cudaMemsetAsync(d_flag, 0, 64, st));
   to_bf16_norm_kernel<<<(uint32_t)(((uint64_t)Q * 32 + 255) / 256), 256, 0, st>>>(d_q, Q, Q, dim, 1.0f, d_qb, d_qn, d_flag);  // a non-finite query -> exact path
   CK(cudaGetLastError());
-  // (3) tensor-core filter
   CUtensorMap map_q;
   if ((rc = make_tile_map(&map_q, d_qb, Qpad, dim))) return rc;
   FlatTcParams p = {};
-  p.row_norm = c->d_norm; p.q_norm = d_qn; p.q_thr = d_thr; p.cand = d_cand; p.cand_cnt = d_cnt; p.cap = cap;
-  p.n = (uint32_t)n; p.ntiles = (uint32_t)((n + FTC_N - 1) / FTC_N); p.kb = dim / FTC_KBLK;
+  p.q_norm = d_qn; p.q_thr = d_thr; p.cand = d_cand; p.cand_cnt = d_cnt; p.cap = cap; p.kb = dim / FTC_KBLK;
   const size_t blk = (size_t)p.kb * FTC_TILE_BYTES;
   p.stages = (uint32_t)std::min<size_t>(8, (200 * 1024 - blk) / blk);
-  ftc_coeffs(dim, &p.e1, &p.e2);
   const size_t smem = 1024 + blk + (size_t)p.stages * blk + 256 + 8 * 64 * sizeof(float2);
-  CK(cudaFuncSetAttribute(flat_tc_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const uint32_t qblocks = Qpad / FTC_M;
-  dim3 grid(std::max(1u, std::min(p.ntiles, (uint32_t)c->sm_count / std::min(qblocks, (uint32_t)c->sm_count))), qblocks);
-  flat_tc_filter_kernel<<<grid, FTC_THREADS, smem, st>>>(map_q, c->map_v, p);
-  CK(cudaGetLastError());
+  if (metric == LB200_L2) ftc_coeffs(dim, &p.e1, &p.e2);
+  else if (metric == LB200_DOT) ftc_coeffs_dot(dim, &p.e1, &p.e2);
+  else ftc_coeffs_cos(dim, &p.e1);
+#define LB200_FTC_LAUNCH(MET, DUMPF, MAPV)                                                                                  \
+  do {                                                                                                                      \
+    CK(cudaFuncSetAttribute(flat_tc_filter_kernel<MET, DUMPF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+    flat_tc_filter_kernel<MET, DUMPF><<<grid, FTC_THREADS, smem, st>>>(map_q, MAPV, p);                                     \
+  } while (0)
+  // (2) thresholds T_q >= the true k-th distance: the k-th smallest over the sample of
+  //     (a) an UPPER bound of each exact distance, approx + E, from the tensor-core kernel itself (default), or
+  //     (b) the exact distances (L2; LB200_FLAT_TC_THR=0 forces it for cosine / dot, which then spend 2 ms here)
+  if (tc_thr) {
+    p.row_norm = c->d_snorm; p.n = ns; p.ntiles = ns / FTC_N; p.dump = d_sd; p.nq = Q;
+    dim3 grid(std::max(1u, std::min(p.ntiles, (uint32_t)c->sm_count / std::min(qblocks, (uint32_t)c->sm_count))), qblocks);
+    if (metric == LB200_L2) LB200_FTC_LAUNCH(0, true, c->map_s);
+    else if (metric == LB200_DOT) LB200_FTC_LAUNCH(2, true, c->map_s);
+    else LB200_FTC_LAUNCH(1, true, c->map_s_unit);
+    CK(cudaGetLastError());
+  } else if ((rc = flat_dist_launch(metric, d_q, Q, c->d_sample, nullptr, ns, dim, d_sd, ns, st))) {
+    return rc;
+  }
+  static_assert(COL_SAMPLE == 256 * 64 && COL_SAMPLE % FTC_N == 0, "ftc_kth_kernel<64> holds the sample in 64 registers per thread");
+  ftc_kth_kernel<64><<<Qpad, 256, 0, st>>>(d_sd, ns, Q, k, d_thr, d_cnt);
+  // (3) tensor-core filter over the whole column
+  {
+    p.row_norm = c->d_norm; p.n = (uint32_t)n; p.ntiles = (uint32_t)((n + FTC_N - 1) / FTC_N); p.dump = nullptr; p.nq = Q;
+    dim3 grid(std::max(1u, std::min(p.ntiles, (uint32_t)c->sm_count / std::min(qblocks, (uint32_t)c->sm_count))), qblocks);
+    if (metric == LB200_L2) LB200_FTC_LAUNCH(0, false, c->map_v);
+    else if (metric == LB200_DOT) LB200_FTC_LAUNCH(2, false, c->map_v);
+    else LB200_FTC_LAUNCH(1, false, c->map_v_unit);
+    CK(cudaGetLastError());
+  }
+#undef LB200_FTC_LAUNCH
   // (4) exact re-score of the kept rows, top k by (distance, row index)
   ftc_clamp_kernel<<<(Q + 255) / 256, 256, 0, st>>>(d_cnt, Q, cap, d_raw, d_flag);
   std::vector<uint32_t> h_cnt(Q);
@@ -162,7 +222,12 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   CK(cudaMemcpyAsync(h_cnt.data(), d_raw, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(&h_flag, d_flag, 4, cudaMemcpyDeviceToHost, st));
   dim3 rgrid(std::max(1u, std::min(cap / 16, (uint32_t)(8 * c->sm_count + Q - 1) / Q)), Q);
-  ftc_rescore_l2_kernel<<<rgrid, 256, 0, st>>>(d_q, c->d_v, dim, d_cand, d_cnt, cap, d_exact, d_pos);
+  if (metric == LB200_L2) {
+    ftc_rescore_l2_kernel<<<rgrid, 256, 0, st>>>(d_q, c->d_v, dim, d_cand, d_cnt, cap, d_exact, d_pos);
+  } else {   // cosine / dot: the generic exact kernel of the refine step (cosine_fast, dot_distance; dist.cuh)
+    ftc_widen_kernel<<<(uint32_t)(((uint64_t)Q * cap + 255) / 256), 256, 0, st>>>(d_cand, d_cnt, Q, cap, d_pos);
+    refine_distance_kernel<<<(uint32_t)(((size_t)Q * cap + 127) / 128), 128, 0, st>>>(metric, d_q, c->d_v, dim, d_pos, d_cnt, Q, cap, d_exact);
+  }
   ftc_prune_kernel<<<Q, 256, 0, st>>>(d_exact, d_pos, d_cnt, cap, k);
   CK(cudaGetLastError());
   rc = launch_merge(d_exact, d_pos, nullptr, nullptr, d_cnt, Q, 1, cap, cap, cap, 1, 1, k, k, d_od, d_oi, nullptr, nullptr, d_oc, st);
@@ -172,6 +237,7 @@ static int column_topk(lb200_column* c, int metric, const float* d_q, uint32_t Q
   c->last_tc = 1;
   if (h_flag) {  // some query kept more rows than the buffer holds: the exact path answers the whole batch
     c->last_fallback = 1;
+    if (c->cap_boost < 8) c->cap_boost *= 2;   // and the next call gets larger buffers
     return flat_topk_device_impl(metric, dim, d_q, Q, c->d_v, c->d_valid, n, k, false, 0.f, false, 0.f, d_od, d_oi, d_oc, st);
   }
   return 0;
@@ -186,6 +252,10 @@ extern "C" void lb200_column_destroy(lb200_column* c) {
   cudaFree(c->d_v);
   cudaFree(c->d_valid);
   cudaFree(c->d_vb);
+  cudaFree(c->d_vb_unit);
+  cudaFree(c->d_sb);
+  cudaFree(c->d_sb_unit);
+  cudaFree(c->d_snorm);
   cudaFree(c->d_norm);
   cudaFree(c->d_sample);
   c->scratch.release();
@@ -240,6 +310,12 @@ extern "C" int32_t lb200_column_create(int32_t device_id, uint32_t dim, const fl
     to_bf16_norm_kernel<<<(uint32_t)((n_pad * 32 + 255) / 256), 256, 0, c->stream>>>(c->d_v, n, n_pad, dim, 1.0f - e2, c->d_vb, c->d_norm, d_bad);
     gather_rows_kernel<<<(uint32_t)(((uint64_t)c->ns * dim + 255) / 256), 256, 0, c->stream>>>(c->d_v, n / c->ns, c->ns, dim, c->d_sample);
     CKC(cudaGetLastError());
+    CKC(cudaMalloc(&c->d_sb, (size_t)c->ns * dim * 2));
+    CKC(cudaMalloc(&c->d_snorm, (size_t)c->ns * 8));
+    to_bf16_norm_kernel<<<(uint32_t)(((uint64_t)c->ns * 32 + 255) / 256), 256, 0, c->stream>>>(c->d_sample, c->ns, c->ns, dim, 1.0f + e2, c->d_sb,
+                                                                                           c->d_snorm, d_bad);
+    CKC(cudaGetLastError());
+    if ((rc = make_tile_map(&c->map_s, c->d_sb, c->ns, dim))) return fail(rc);
     cudaError_t eb = cudaMemcpyAsync(&h_bad, d_bad, 4, cudaMemcpyDeviceToHost, c->stream);
     if (eb == cudaSuccess) eb = cudaStreamSynchronize(c->stream);
     cudaFree(d_bad);

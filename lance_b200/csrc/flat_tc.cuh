@@ -78,8 +78,16 @@ struct FlatTcParams {
   uint32_t kb;              // dim / 64
   uint32_t stages;          // B pipeline depth
   float e1, e2;             // error bound coefficients, each + 2^-21 (see the epilogue)
+  float* dump;              // DUMP mode: [nq][n] upper bounds of the exact distances (approx + E), instead of candidates
+  uint32_t nq;              // DUMP mode: real queries (rows of `dump`)
 };
 
+// MET: 0 L2, 1 cosine (map_v = rows normalised to unit length before the bf16 rounding), 2 dot.
+// DUMP: no filtering -- every (query, row) gets approx + E, an UPPER bound of its exact distance, written to p.dump.
+// Run over the column's sample it yields the thresholds without any exact distance: the k-th smallest upper bound
+// over a subset of the rows is >= the k-th smallest exact distance over all rows.  (row_norm then holds
+// (|y|^2 (1 + e2), |y|) for L2.)
+template <int MET, bool DUMP>
 __global__ void __launch_bounds__(FTC_THREADS, 1)
 flat_tc_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_v, const FlatTcParams p) {
   extern __shared__ __align__(1024) unsigned char ftc_smem_raw[];
@@ -163,13 +171,19 @@ flat_tc_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
     const uint32_t qi = qblk * FTC_M + lq;
     const float2 qn = p.q_norm[qi];
     const float thr = p.q_thr[qi];
+    // dot:     keep iff  -P - e1 |q||y| <= T - 1 + e0            (distance 1 - q.y, E = e1 |q||y| + e0; e0 in p.e2)
+    // cosine:  keep iff  -P' <= (T - 1 + E) |q|                  (rows pre-normalised: P' ~ q.y / |y|; E in p.e1)
+    // each right-hand side gets 2^-21 (|T| + 1) (|q| for cosine) of slack for its own roundings
     const float ne1q = -(p.e1 * qn.y);
-    const float cq = thr == __int_as_float(0xff800000)
-                         ? thr : fmaf(p.e2, qn.x, thr - qn.x) + 4.76837158203125e-07f * (fabsf(thr) + qn.x);
+    float cq;
+    if (thr == __int_as_float(0xff800000)) cq = thr;
+    else if (MET == 0) cq = fmaf(p.e2, qn.x, thr - qn.x) + 4.76837158203125e-07f * (fabsf(thr) + qn.x);
+    else if (MET == 2) cq = (thr - 1.0f) + p.e2 + 4.76837158203125e-07f * (fabsf(thr) + 1.0f);
+    else cq = ((thr - 1.0f) + p.e1 + 4.76837158203125e-07f * (fabsf(thr) + 1.0f)) * qn.y;
     float2* nb = norm_buf + (warp - 4) * 64;
     uint32_t row0 = blockIdx.x * FTC_N + half * 64;
     float2 n0 = make_float2(0.f, 0.f), n1 = n0;
-    if (my_tiles) { n0 = __ldg(p.row_norm + row0 + lane); n1 = __ldg(p.row_norm + row0 + 32 + lane); }
+    if (MET != 1 && my_tiles) { n0 = __ldg(p.row_norm + row0 + lane); n1 = __ldg(p.row_norm + row0 + 32 + lane); }
     for (uint32_t t = 0; t < my_tiles; t++) {
       const uint32_t acc = t & 1, aph = (t >> 1) & 1;
       __syncwarp();
@@ -178,7 +192,7 @@ flat_tc_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
       __syncwarp();
       const uint32_t row_cur = row0;
       row0 += gridDim.x * FTC_N;
-      if (t + 1 < my_tiles) { n0 = __ldg(p.row_norm + row0 + lane); n1 = __ldg(p.row_norm + row0 + 32 + lane); }
+      if (MET != 1 && t + 1 < my_tiles) { n0 = __ldg(p.row_norm + row0 + lane); n1 = __ldg(p.row_norm + row0 + 32 + lane); }
       ftc_mbar_wait(tfull + acc, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
@@ -195,22 +209,54 @@ flat_tc_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_co
               "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
             : "r"(taddr) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const uint32_t nb_addr = ftc_smem(nb + c0);
+        if (DUMP) {
+          // upper bounds: L2  |q|^2 (1 + e2) + |y|^2 (1 + e2) - 2 P + e1 |q||y|;  dot  1 - P + e1 |q||y| + e0;
+          // cosine  1 - P' / |q| + E
+          if (qi < p.nq) {
+            float* drow = p.dump + (size_t)qi * p.n + row_cur + c0;
+            const float inv_q = MET == 1 ? __fdiv_rn(1.0f, qn.y) : 0.0f;
+            const float base = MET == 0 ? fmaf(p.e2, qn.x, qn.x) : MET == 2 ? 1.0f + p.e2 : 1.0f + p.e1;
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+              float2 yn = make_float2(0.f, 0.f);
+              if (MET != 1) asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(yn.x), "=f"(yn.y) : "r"(nb_addr + j * 8));
+              const float P = __uint_as_float(v[j]);
+              float ub;
+              if (MET == 0) ub = fmaf(-ne1q, yn.y, fmaf(-2.0f, P, yn.x)) + base;
+              else if (MET == 2) ub = fmaf(-ne1q, yn.y, -P) + base;
+              else ub = fmaf(-P, inv_q, base);
+              if (row_cur + c0 + j < p.n) drow[j] = ub;
+            }
+          }
+          continue;
+        }
         // one bit per row that passes; a few rows of a thousand do, so nearly every WARP has some lane with a bit
         // set in a group of 32 rows -- the test must not branch per row
-        const uint32_t nb_addr = ftc_smem(nb + c0);
         uint32_t mask = 0;
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {   // one LDS.128 (a broadcast) brings the norms of two rows
-          float4 y2;
-          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(y2.x), "=f"(y2.y), "=f"(y2.z), "=f"(y2.w) : "r"(nb_addr + j * 8));
-          const float g0 = fmaf(ne1q, y2.y, fmaf(-2.0f, __uint_as_float(v[j]), y2.x));
-          const float g1 = fmaf(ne1q, y2.w, fmaf(-2.0f, __uint_as_float(v[j + 1]), y2.z));
+          float4 y2 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (MET != 1)
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(y2.x), "=f"(y2.y), "=f"(y2.z), "=f"(y2.w) : "r"(nb_addr + j * 8));
+          float g0, g1;
+          if (MET == 0) {
+            g0 = fmaf(ne1q, y2.y, fmaf(-2.0f, __uint_as_float(v[j]), y2.x));
+            g1 = fmaf(ne1q, y2.w, fmaf(-2.0f, __uint_as_float(v[j + 1]), y2.z));
+          } else if (MET == 2) {
+            g0 = fmaf(ne1q, y2.y, -__uint_as_float(v[j]));
+            g1 = fmaf(ne1q, y2.w, -__uint_as_float(v[j + 1]));
+          } else {
+            g0 = -__uint_as_float(v[j]);
+            g1 = -__uint_as_float(v[j + 1]);
+          }
           mask |= g0 <= cq ? 1u << j : 0u;
           mask |= g1 <= cq ? 2u << j : 0u;
         }
         while (mask) {
           const uint32_t j = __ffs(mask) - 1;
           mask &= mask - 1;
+          if (MET != 0 && row_cur + c0 + j >= p.n) continue;   // zero-filled rows past the end (L2: excluded by their +inf norm)
           const uint32_t pos = atomicAdd(p.cand_cnt + qi, 1u);
           if (pos < p.cap) p.cand[(size_t)qi * p.cap + pos] = row_cur + c0 + j;
         }
@@ -249,6 +295,32 @@ __global__ void to_bf16_norm_kernel(const float* __restrict__ x, uint64_t n, uin
     norms[r] = make_float2(s * scale, sqrtf(s));
     if (!(s < __int_as_float(0x7f800000))) atomicExch(nonfinite, 1u);
   }
+}
+
+// cosine: f32 rows -> unit-length rows rounded to bf16 (y / |y| per element; a zero row becomes NaN and can never pass
+// the filter, like its NaN cosine distance can never be returned).  One warp per row.
+__global__ void to_bf16_unit_kernel(const float* __restrict__ x, uint64_t n, uint32_t dim, __nv_bfloat16* __restrict__ xb) {
+  const uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t lane = threadIdx.x & 31;
+  if (r >= n) return;
+  float s = 0.0f;
+  for (uint32_t j = lane; j < dim; j += 32) {
+    const float v = x[r * dim + j];
+    s = fmaf(v, v, s);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float ny = sqrtf(s);
+  for (uint32_t j = lane; j < dim; j += 32) xb[r * dim + j] = __float2bfloat16_rn(__fdiv_rn(x[r * dim + j], ny));
+}
+
+// kept rows as the u64 positions the generic exact kernels take (cosine / dot re-score); ~0 past the count
+__global__ void ftc_widen_kernel(const uint32_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t Q, uint32_t cap,
+                                 uint64_t* __restrict__ pos) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (uint64_t)Q * cap) return;
+  const uint32_t q = (uint32_t)(i / cap), j = (uint32_t)(i - (uint64_t)q * cap);
+  pos[i] = j < min(cnt[q], cap) ? (uint64_t)cand[i] : ~0ull;
 }
 
 // rows [i * stride] of x, i < ns -> contiguous sample

@@ -79,9 +79,6 @@ def test_column_cases_the_filter_does_not_serve():
     v = _sift(rng, n, d)
     q = _sift(rng, Q, d)
     col = VectorColumn(v)
-    for metric in ("cosine", "dot"):
-        _same(col.flat_knn(q, metric, 10), flat_knn(q, metric, v, 10))
-        assert not col.last_call()["used_tc"]
     base = flat_knn(q, "l2", v, 50)[0]
     lo, hi = float(np.median(base)), float(base.max())
     _same(col.flat_knn(q, "l2", 10, lower_bound=lo, upper_bound=hi), flat_knn(q, "l2", v, 10, lower_bound=lo, upper_bound=hi))
@@ -120,4 +117,30 @@ def test_column_with_non_finite_values_uses_the_exact_path():
     _same(col.flat_knn(q, "l2", 10), flat_knn(q, "l2", v, 10))
     st = col.last_call()
     assert st["used_tc"] and not st["fell_back"]
+    col.close()
+
+
+@pytest.mark.parametrize("metric", ["cosine", "dot"])
+@pytest.mark.parametrize("d,n,Q,k", [(128, 100_003, 9, 10), (64, 150_000, 130, 100), (256, 70_000, 128, 1), (192, 262_144, 33, 10)])
+def test_column_filter_cosine_and_dot(metric, d, n, Q, k):
+    """The same bound-and-verify scheme for the other two metrics of compute_distance (flat.rs:28-86; the reference's flat
+    benchmark runs all three): dot on the raw bf16 rows with E = e1 |q||y| + e0, cosine on rows normalised before the
+    bf16 rounding with a constant E; exact re-score by the refine step's kernels.  Indices, distance bits and counts must
+    equal the exact path's, including duplicates (ties) and a zero row (NaN cosine distance: never returned)."""
+    from lance_b200 import VectorColumn, flat_knn
+    rng = np.random.default_rng(d + Q + len(metric))
+    v = (rng.normal(size=(n, d)) * rng.uniform(0.5, 2.0, size=(n, 1))).astype(np.float32)
+    v[1000:1050] = v[5]
+    v[77] = 0.0
+    q = np.concatenate([v[rng.integers(0, n, Q // 2 + 1)] + 0.1 * rng.normal(size=(Q // 2 + 1, d)).astype(np.float32),
+                        rng.normal(size=(Q, d)).astype(np.float32)])[:Q]
+    q[0] = v[5]
+    col = VectorColumn(v)
+    got = col.flat_knn(q, metric, k)
+    st = col.last_call()
+    assert st["used_tc"] and not st["fell_back"], st
+    assert st["candidates"] >= Q * k
+    _same(got, flat_knn(q, metric, v, k))
+    _same(col.flat_knn(q[:3], "l2", k), flat_knn(q[:3], "l2", v, k))     # the L2 form on the same column afterwards
+    _same(col.flat_knn(q[::-1].copy(), metric, k), flat_knn(q[::-1].copy(), metric, v, k))
     col.close()
