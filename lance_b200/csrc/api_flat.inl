@@ -28,6 +28,15 @@ static int flat_dist_launch(int metric, const float* d_q, uint32_t Q, const floa
     CK(cudaGetLastError());
     return 0;
   }
+  // dot, d % 64 == 0, no nulls: the slab kernel of the dot coarse step (dot_distance in the same f32x16 order)
+  if (metric == LB200_DOT && dim % 64 == 0 && !d_valid && ssm2 <= (size_t)optin && Q >= 4 && n < (1ull << 32) &&
+      !getenv("LB200_COARSE_SIMPLE")) {
+    CK(cudaFuncSetAttribute(coarse_dist_dot_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm2));
+    dim3 g2((uint32_t)((n + 127) / 128), (Q + CD_QB - 1) / CD_QB);
+    coarse_dist_dot_slab_kernel<<<g2, 512, ssm2, st>>>(d_q, d_v, Q, (uint32_t)n, dim, d_out, out_stride);
+    CK(cudaGetLastError());
+    return 0;
+  }
   if (metric == LB200_L2 && dim % 16 == 0 && dim >= 32 && tsm <= (size_t)optin && Q >= 8 && !getenv("LB200_COARSE_SIMPLE")) {
     CK(cudaFuncSetAttribute(coarse_dist_l2_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
     dim3 g2((uint32_t)((n + 127) / 128), (Q + CQ_QB - 1) / CQ_QB);
