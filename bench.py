@@ -254,67 +254,124 @@ def run_flat(args):
     from lance_b200 import _lib
     from lance_b200._lib import check
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
-    dev = torch.device("cuda", 0)
+    import torch.distributed as dist
+    from lance_b200.index import merge_topk_device
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
     N, d, k, Q = 1_000_000, 128, 10, args.queries or 256
     fmetric = args.flat_metric          # "also run cosine and dot for coverage" (benchmarks/flat/benchmark.py:68)
     fcode = {"l2": 0, "cosine": 1, "dot": 2}[fmetric]
     rng = np.random.default_rng(1234)
     vecs = np.clip(np.rint(rng.normal(64, 32, size=(N, d))), 0, 218).astype(np.float32)  # SIFT-like integers
     queries = np.clip(np.rint(rng.normal(64, 32, size=(Q, d))), 0, 218).astype(np.float32)
+    # multi-GPU ("flat kNN shards by rows the same way"): rank r keeps rows [lo, hi) resident, every rank
+    # scores the whole query batch against its rows, one NCCL all_gather of the [Q][k] lists, merge on rank 0
+    lo, hi = rank * N // world, (rank + 1) * N // world
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     L = _lib.lib()
     col = C.c_void_p()
-    check(L.lb200_column_create(C.c_int32(0), C.c_uint32(d), vecs.ctypes.data_as(C.c_void_p), None, C.c_uint64(N), C.byref(col)))
+    mine = np.ascontiguousarray(vecs[lo:hi])
+    check(L.lb200_column_create(C.c_int32(local), C.c_uint32(d), mine.ctypes.data_as(C.c_void_p), None, C.c_uint64(hi - lo), C.byref(col)))
     d_q = torch.from_numpy(queries).to(dev)
     od = torch.empty((Q, k), dtype=torch.float32, device=dev)
     oi = torch.empty((Q, k), dtype=torch.int64, device=dev)
     oc = torch.empty((Q,), dtype=torch.int32, device=dev)
+    if world > 1:
+        g_d = torch.empty((world, Q, k), dtype=torch.float32, device=dev)
+        g_i = torch.empty((world, Q, k), dtype=torch.int64, device=dev)
+        g_c = torch.empty((world, Q), dtype=torch.int32, device=dev)
+        l_d, l_i, l_c = torch.empty_like(od), torch.empty_like(oi), torch.empty_like(oc)
     h_q = torch.from_numpy(queries).pin_memory()
     h_od = torch.empty((Q, k), dtype=torch.float32).pin_memory()
     h_oi = torch.empty((Q, k), dtype=torch.int64).pin_memory()
     h_oc = torch.empty((Q,), dtype=torch.int32).pin_memory()
 
     def step():
+        if world == 1:
+            check(L.lb200_column_flat_topk_device(col, C.c_int32(fcode), C.c_void_p(d_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
+                                                  C.c_void_p(od.data_ptr()), C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()),
+                                                  C.c_void_p(stream.cuda_stream)))
+            return
         check(L.lb200_column_flat_topk_device(col, C.c_int32(fcode), C.c_void_p(d_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
-                                              C.c_void_p(od.data_ptr()), C.c_void_p(oi.data_ptr()), C.c_void_p(oc.data_ptr()),
+                                              C.c_void_p(l_d.data_ptr()), C.c_void_p(l_i.data_ptr()), C.c_void_p(l_c.data_ptr()),
                                               C.c_void_p(stream.cuda_stream)))
+        l_i.add_(lo)                                       # local row index -> row index in the whole column
+        dist.all_gather_into_tensor(g_d.view(-1), l_d.view(-1))
+        dist.all_gather_into_tensor(g_i.view(-1), l_i.view(-1))
+        dist.all_gather_into_tensor(g_c.view(-1), l_c.view(-1))
+        if rank == 0:
+            merge_topk_device(local, g_d.data_ptr(), g_i.data_ptr(), None, g_c.data_ptr(), world, Q, k, k, k,
+                              od.data_ptr(), oi.data_ptr(), oc.data_ptr(), stream=stream.cuda_stream)
 
-    def e2e_step():  # host queries in, host results out, through the C ABI (H2D + D2H inside)
-        check(L.lb200_column_flat_topk(col, C.c_int32(fcode), C.c_void_p(h_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
-                                       C.c_void_p(h_od.data_ptr()), C.c_void_p(h_oi.data_ptr()), C.c_void_p(h_oc.data_ptr())))
+    def e2e_step():  # host queries in, host results out (H2D + D2H inside the timed region)
+        if world == 1:
+            check(L.lb200_column_flat_topk(col, C.c_int32(fcode), C.c_void_p(h_q.data_ptr()), C.c_uint32(Q), C.c_uint32(k), None, None,
+                                           C.c_void_p(h_od.data_ptr()), C.c_void_p(h_oi.data_ptr()), C.c_void_p(h_oc.data_ptr())))
+            return
+        d_q.copy_(h_q, non_blocking=True)
+        step()
+        if rank == 0:
+            h_od.copy_(od, non_blocking=True); h_oi.copy_(oi, non_blocking=True); h_oc.copy_(oc, non_blocking=True)
+        stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
 
     for _ in range(max(args.warmup, 3)):
         step()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(0)
+    barrier()
+    sampler = ClockSampler(local)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(args.steps):
         step()
     e1.record(stream)
-    torch.cuda.synchronize()
+    barrier()
     ms = e0.elapsed_time(e1)
+    if world > 1:
+        tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        ms = float(tmax.item())
     clocks = sampler.stop()
-    if not clocks.get("samples"):   # a 10 ms timed region is shorter than nvidia-smi's sampling period: sample a repeat of it
-        sampler = ClockSampler(0)
+    need_repeat = not clocks.get("samples")
+    if world > 1:                   # the same decision on every rank: the repeat holds collectives
+        flag = torch.tensor([1 if need_repeat else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+        need_repeat = bool(flag.item())
+    if need_repeat:   # a 10 ms timed region is shorter than nvidia-smi's sampling period: sample a repeat of it
+        sampler = ClockSampler(local)
         sampler.start()
-        t0 = time.perf_counter()
-        while time.perf_counter() - t0 < 1.5:
-            for _ in range(20):
-                step()
-            torch.cuda.synchronize()
+        for _ in range(30 if world > 1 else 1):            # (the same count on every rank: step() holds collectives)
+            t0 = time.perf_counter()
+            while world == 1 and time.perf_counter() - t0 < 1.5:
+                for _ in range(20):
+                    step()
+                torch.cuda.synchronize()
+            if world > 1:
+                for _ in range(100):
+                    step()
+                torch.cuda.synchronize()
         clocks = sampler.stop()
         clocks["note"] = "sampled over a 1.5 s repeat of the same steps right after the timed region (which is too short to sample)"
     tc, cand, fb = C.c_uint32(0), C.c_uint64(0), C.c_uint32(0)
     check(L.lb200_column_last_call(col, C.byref(tc), C.byref(cand), C.byref(fb)))
     for _ in range(2):
         e2e_step()
+    barrier()
     t0 = time.perf_counter()
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(e2e_steps):
         e2e_step()
+    barrier()
     ms_e2e = (time.perf_counter() - t0) * 1e3
     # the exact path alone on the same column, for the line's own A/B
     os.environ["LB200_FLAT_NO_TC"] = "1"
@@ -337,14 +394,15 @@ def run_flat(args):
     # the filter kernel streams the bf16 rows once per 128-query block: its algorithmic bytes
     qblocks = (Q + 127) // 128
     bytes_step = N * d * 2 * qblocks
-    line = {"metric": "flat kNN queries/sec (batched)", "value": qps, "unit": "queries/s", "n_gpus": 1,
+    line = {"metric": "flat kNN queries/sec (batched)", "value": qps, "unit": "queries/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32 (results); bf16 tensor-core candidate filter + exact f32 re-score",
             "data": "synthetic",
             "config": {"workload": f"flat brute-force {fmetric.upper()} kNN 1Mx128 f32, k=10, {Q} queries per step (BASELINE configs[1]"
                                    + ("" if fmetric == "l2" else "; metric varied as the reference's flat benchmark does") + ")",
                        "l2_policy": "inputs larger than L2 (256 MB of bf16 rows + 512 MB of f32 rows)",
-                       "path": "lb200_column_flat_topk_device (resident column)",
+                       "path": "lb200_column_flat_topk_device (resident column)" + ("" if world == 1 else
+                               f"; rows sharded over {world} GPUs, NCCL all_gather of the [Q][k] lists, lb200_merge_topk_device on rank 0"),
                        "filter": {"used_tc": bool(tc.value), "fell_back": bool(fb.value), "candidates_per_query": cand.value / Q},
                        "exact_path_ms_per_step": ms_exact},
             "roofline": {"bound": "hbm", "achieved": bytes_step / (step_ms * 1e-3) / 1e9, "peak": peak_hbm, "unit": "GB/s",
@@ -353,9 +411,14 @@ def run_flat(args):
                          "note": "bytes = N*d*2 (bf16 rows) per 128-query block of the filter kernel; flops = Q*N*d*2 on tcgen05"},
             "e2e": {"value": Q * e2e_steps / (ms_e2e * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": int(queries.nbytes),
                     "d2h_bytes_per_step": Q * k * 12 + Q * 4, "ms_per_step": ms_e2e / e2e_steps,
-                    "path": "lb200_column_flat_topk (host-pointer C ABI on the resident column; queries H2D, results D2H inside)"},
+                    "path": "lb200_column_flat_topk (host-pointer C ABI on the resident column; queries H2D, results D2H inside)"
+                            if world == 1 else "pinned H2D of the queries on every rank + the sharded step + D2H of the merged result on rank 0"},
             "gpu_launches": 8 * args.steps,  # sample distances, k-th select, query bf16, filter, clamp, exact re-score, prune, merge
             "clocks": clocks}
+    if rank != 0:
+        L.lb200_column_destroy(col)
+        dist.destroy_process_group()
+        return
     if not args.no_cpu_baseline:
         import oracle
         cores = oracle.max_threads()
@@ -370,6 +433,8 @@ def run_flat(args):
                                       (od.cpu().numpy(), oi.cpu().numpy().view(np.uint64), oc.cpu().numpy()), k)
     print(json.dumps(line), flush=True)
     L.lb200_column_destroy(col)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def clustered_lowrank(N, d, seed, dev, nblobs=4096, rank=16, chunk=2_000_000):
@@ -580,6 +645,7 @@ def main():
     ap.add_argument("--scan-variant", type=int, default=0)
     ap.add_argument("--queries", type=int, default=0,
                     help="override the workload's queries per step (batch-size sweep of BASELINE configs[4])")
+    ap.add_argument("--nprobes", type=int, default=0, help="override the workload's nprobes (SURVEY 8: cfg 3 is run at 1, 20 and 102)")
     ap.add_argument("--flat-metric", default="l2", choices=["l2", "cosine", "dot"], help="metric of --workload cfg2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-recall", action="store_true", help="skip the real-built-index recall@10 block")
@@ -599,6 +665,8 @@ def main():
     if args.queries:
         wl = wl[:8] + (args.queries, wl[9].replace("%d queries" % wl[8], "%d queries" % args.queries)
                        .replace("10k queries", "%d queries" % args.queries))
+    if args.nprobes:
+        wl = wl[:5] + (args.nprobes,) + wl[6:9] + (wl[9] + f" [nprobes overridden: {args.nprobes}]",)
     if args.mode == "dropin":
         if args.impl == "reference" or _BITS != 8:
             print(json.dumps({"impl": args.impl, "unavailable": "--mode dropin runs both arms itself (8-bit IVF_PQ only)"}))
