@@ -374,7 +374,7 @@ uint64_t lb200_noalloc_scratch_bytes(void);
  * cosine keys (rust/lance-linalg/src/kernels.rs:118-121), refine on the Float16 rows.  centroids [nlist][dim],
  * codebook [M][256][dim/M], raw vectors and keys are IEEE binary16 bit patterns; codes are 8-bit, layout as
  * lb200_index_create.  Distances are f32 in the order of the reference's scalar f16 fallbacks (csrc/f16pq.cuh).
- * Limits: num_sub_vectors % 16 == 0; the handle takes lb200_search_f16 only (the f32 entry points answer
+ * Limits: num_sub_vectors % 16 == 0; the handle takes the *_f16 entry points only (the f32 search entry points answer
  * LB200_EINVAL); stats / destroy as for any handle.  No bf16 form: the reference's find_partitions and PQ storage
  * dispatch on Float16 / Float32 / Float64 only. */
 int32_t lb200_index_create_f16(int32_t device_id, int32_t metric, uint32_t dim, uint32_t nlist, const uint16_t* centroids,
@@ -384,6 +384,14 @@ int32_t lb200_index_create_f16(int32_t device_id, int32_t metric, uint32_t dim, 
 int32_t lb200_search_f16(lb200_index* ix, const uint16_t* queries, uint32_t Q, uint32_t nprobes, uint32_t k,
                          uint32_t refine_factor, const float* lower_or_null, const float* upper_or_null,
                          float* out_dist, uint64_t* out_rowid, uint32_t* out_count);
+/* The two calls the exec nodes make (find_partitions once per query, search_in_partition per probed partition), Float16
+ * keys used as given (already normalised for a cosine index), arguments as lb200_find_partitions / lb200_search_partitions
+ * (no prefilter form yet). */
+int32_t lb200_find_partitions_f16(lb200_index* ix, const uint16_t* queries, uint32_t Q, uint32_t nprobes,
+                                  uint32_t* out_part_ids, float* out_part_dists_or_null);
+int32_t lb200_search_partitions_f16(lb200_index* ix, const uint16_t* queries, uint32_t Q, const uint32_t* part_ids, uint32_t P,
+                                    uint32_t k_prime, const float* lower_or_null, const float* upper_or_null, float* out_dist,
+                                    uint64_t* out_rowid, uint32_t* out_count);
 
 /* The same two entry points for Float16 columns (the reference's f16 path:
  * `impl L2/Dot/Cosine/Normalize for f16`, rust/lance-linalg/src/distance/{l2.rs:136-166, dot.rs:100-137,

@@ -27,7 +27,7 @@ EXPORTS = [
     "lb200_column_last_call",
     "lb200_flat_topk_device_noalloc", "lb200_noalloc_scratch_bytes",
     "lb200_prefilter_create", "lb200_prefilter_destroy", "lb200_search_partitions_filtered",
-    "lb200_index_create_f16", "lb200_search_f16",
+    "lb200_index_create_f16", "lb200_search_f16", "lb200_find_partitions_f16", "lb200_search_partitions_f16",
 ]
 
 

@@ -122,3 +122,89 @@ extern "C" int32_t lb200_search_f16(lb200_index* ix, const uint16_t* queries, ui
   }
   return 0;
 }
+
+// VectorIndex::find_partitions for Float16 keys (kmeans_find_partitions::<f16>): keys used as given -- the exec node
+// has normalised them for a cosine index (knn.rs:366-369), in f16 arithmetic.
+extern "C" int32_t lb200_find_partitions_f16(lb200_index* ix, const uint16_t* queries, uint32_t Q, uint32_t nprobes,
+                                             uint32_t* out_part_ids, float* out_part_dists_or_null) {
+  int rc = check_queries(ix, queries, Q);
+  if (rc) return rc;
+  if (!ix->f16) return set_err(LB200_EINVAL, "lb200_find_partitions_f16 needs a handle made by lb200_index_create_f16");
+  if (!out_part_ids) return set_err(LB200_EINVAL, "null output");
+  const uint32_t P = std::min(nprobes, ix->nlist);
+  if (!Q || !P) return 0;
+  CtxLease ls;
+  if ((rc = ls.acquire(ix, nullptr))) return rc;
+  CallCtx& cx = *ls.cx;
+  cudaStream_t st = ls.st;
+  const uint32_t dim = ix->dim;
+  const size_t np = (size_t)Q * P * 4;
+  const size_t need = Arena::pad((size_t)Q * dim * 2) + 2 * Arena::pad((size_t)Q * dim * 4) + Arena::pad((size_t)Q * ix->nlist * 4) +
+                      2 * Arena::pad(np) + 4096;
+  if ((rc = cx.arena.reserve(need))) return rc;
+  cx.arena.reset();
+  __half* d_q16 = cx.arena.take<__half>((size_t)Q * dim);
+  float* d_orig = cx.arena.take<float>((size_t)Q * dim);
+  float* d_key = cx.arena.take<float>((size_t)Q * dim);
+  float* d_D = cx.arena.take<float>((size_t)Q * ix->nlist);
+  uint32_t* d_p = cx.arena.take<uint32_t>((size_t)Q * P);
+  float* d_pd = cx.arena.take<float>((size_t)Q * P);
+  uint32_t launches = 0;
+  CK(cudaMemcpyAsync(d_q16, queries, (size_t)Q * dim * 2, cudaMemcpyHostToDevice, st));
+  f16_keys_kernel<<<(Q + 127) / 128, 128, 0, st>>>(d_q16, Q, dim, 0, d_orig, d_key);
+  CK(cudaGetLastError());
+  if ((rc = coarse_device(ix, d_key, Q, P, d_D, d_p, d_pd, st, &launches))) return rc;
+  CK(cudaMemcpyAsync(out_part_ids, d_p, np, cudaMemcpyDeviceToHost, st));
+  if (out_part_dists_or_null) CK(cudaMemcpyAsync(out_part_dists_or_null, d_pd, np, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// VectorIndex::search_in_partition for explicit (query, partition) pairs on a Float16 handle: keys used as given,
+// one list of up to k' rows per pair (out [Q][P][k'], counts [Q][P]); [lower, upper) as lb200_search_partitions.
+extern "C" int32_t lb200_search_partitions_f16(lb200_index* ix, const uint16_t* queries, uint32_t Q, const uint32_t* part_ids,
+                                               uint32_t P, uint32_t k_prime, const float* lower_or_null, const float* upper_or_null,
+                                               float* out_dist, uint64_t* out_rowid, uint32_t* out_count) {
+  int rc = check_queries(ix, queries, Q);
+  if (rc) return rc;
+  if (!ix->f16) return set_err(LB200_EINVAL, "lb200_search_partitions_f16 needs a handle made by lb200_index_create_f16");
+  if (Q && P && (!part_ids || !out_dist || !out_rowid || !out_count)) return set_err(LB200_EINVAL, "null argument");
+  if (k_prime == 0) return set_err(LB200_EINVAL, "k must be > 0");
+  if (!Q || !P) return 0;
+  const size_t npairs = (size_t)Q * P;
+  if (npairs >= (1ull << 31)) return set_err(LB200_EUNSUPPORTED, "Q*P too large");
+  for (size_t i = 0; i < npairs; i++)
+    if (part_ids[i] >= ix->nlist) return set_err(LB200_EINVAL, "partition centroid %u does not exist", part_ids[i]);
+  CtxLease ls;
+  if ((rc = ls.acquire(ix, nullptr))) return rc;
+  CallCtx& cx = *ls.cx;
+  cudaStream_t st = ls.st;
+  const uint32_t dim = ix->dim;
+  const size_t b_q16 = Arena::pad((size_t)Q * dim * 2), b_f32 = Arena::pad((size_t)Q * dim * 4), b_p = Arena::pad(npairs * 4),
+               no = npairs * k_prime;
+  const size_t o_orig = b_q16, o_key = o_orig + b_f32, o_p = o_key + b_f32, o_od = o_p + b_p, o_or = o_od + Arena::pad(no * 4),
+               o_oc = o_or + Arena::pad(no * 8), total = o_oc + Arena::pad(npairs * 4);
+  if ((rc = cx.stage.reserve(total))) return rc;
+  char* b = cx.stage.base;
+  CK(cudaMemcpyAsync(b, queries, (size_t)Q * dim * 2, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(b + o_p, part_ids, npairs * 4, cudaMemcpyHostToDevice, st));
+  f16_keys_kernel<<<(Q + 127) / 128, 128, 0, st>>>(reinterpret_cast<const __half*>(b), Q, dim, 0, reinterpret_cast<float*>(b + o_orig),
+                                                  reinterpret_cast<float*>(b + o_key));
+  CK(cudaGetLastError());
+  SearchArgs a = {};
+  a.d_queries = reinterpret_cast<const float*>(b + o_orig);
+  a.d_keys_override = reinterpret_cast<const float*>(b + o_key);
+  a.Q = Q; a.d_part_ids = reinterpret_cast<const uint32_t*>(b + o_p); a.P = P; a.k = k_prime; a.refine_factor = 0;
+  a.normalize = false; a.per_pair_output = true;
+  a.has_lower = lower_or_null != nullptr; a.has_upper = upper_or_null != nullptr;
+  a.lower = lower_or_null ? *lower_or_null : 0.f; a.upper = upper_or_null ? *upper_or_null : 0.f;
+  a.d_out_dist = reinterpret_cast<float*>(b + o_od);
+  a.d_out_rowid = reinterpret_cast<uint64_t*>(b + o_or);
+  a.d_out_count = reinterpret_cast<uint32_t*>(b + o_oc);
+  if ((rc = search_pipeline(ix, cx, a, st))) return rc;
+  CK(cudaMemcpyAsync(out_dist, b + o_od, no * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_rowid, b + o_or, no * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_count, b + o_oc, npairs * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}

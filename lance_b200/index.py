@@ -374,6 +374,27 @@ class IvfPqIndexF16:
                                        _fptr(query.lower_bound), _fptr(query.upper_bound), _p(od), _p(oi), _p(oc)))
         return od, oi, oc
 
+    def find_partitions(self, keys, nprobes, return_distances=False):
+        """VectorIndex::find_partitions for float16 keys (used as given)."""
+        q = np.atleast_2d(np.ascontiguousarray(keys, dtype=np.float16))
+        P = min(int(nprobes), self.nlist)
+        ids = np.empty((q.shape[0], P), dtype=np.uint32)
+        ds = np.empty((q.shape[0], P), dtype=np.float32) if return_distances else None
+        check(self._L.lb200_find_partitions_f16(self._h, _p(q), C.c_uint32(q.shape[0]), C.c_uint32(nprobes), _p(ids), _p(ds)))
+        return (ids, ds) if return_distances else ids
+
+    def search_in_partition(self, part_ids, keys, k, lower_bound=None, upper_bound=None):
+        """VectorIndex::search_in_partition for explicit (query, partition) pairs: (dist, row ids) [Q][P][k], count [Q][P]."""
+        q = np.atleast_2d(np.ascontiguousarray(keys, dtype=np.float16))
+        parts = np.ascontiguousarray(part_ids, dtype=np.uint32).reshape(q.shape[0], -1)
+        Q, P = parts.shape
+        od = np.full((Q, P, k), np.inf, dtype=np.float32)
+        oi = np.full((Q, P, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+        oc = np.zeros((Q, P), dtype=np.uint32)
+        check(self._L.lb200_search_partitions_f16(self._h, _p(q), C.c_uint32(Q), _p(parts), C.c_uint32(P), C.c_uint32(k),
+                                                  _fptr(lower_bound), _fptr(upper_bound), _p(od), _p(oi), _p(oc)))
+        return od, oi, oc
+
     def close(self):
         if getattr(self, "_h", None):
             self._L.lb200_index_destroy(self._h)

@@ -451,6 +451,25 @@ class OracleIndexF16:
         self.ix = _IndexF16(METRICS[data.metric], data.dim, data.nlist, data.M, k[0].ctypes.data, k[1].ctypes.data,
                             k[2].ctypes.data, k[3].ctypes.data, k[4].ctypes.data, None if k[5] is None else k[5].ctypes.data)
 
+    def find_partitions(self, key, nprobes):
+        key = _f16(key)
+        P = min(nprobes, self.data.nlist)
+        ids = np.empty(max(P, 1), dtype=np.uint32)
+        ds = np.empty(max(P, 1), dtype=np.float32)
+        m = METRICS[self.data.metric]
+        n = lib().lo_find_partitions_f16(self._keep[0].ctypes.data_as(C.c_void_p), C.c_uint32(self.data.nlist), C.c_uint32(self.data.dim),
+                                         _p(key), C.c_uint32(nprobes), C.c_int(DOT if m == DOT else L2), _p(ids), _p(ds))
+        return ids[:n], ds[:n]
+
+    def search_in_partition(self, part, key, kprime, lower=None, upper=None):
+        key = _f16(key)
+        od = np.empty(max(kprime, 1), dtype=np.float32)
+        oi = np.empty(max(kprime, 1), dtype=np.uint64)
+        n = lib().lo_search_in_partition_f16(C.byref(self.ix), C.c_uint32(part), _p(key), C.c_uint32(kprime),
+                                             C.c_int(lower is not None), C.c_float(lower or 0.0), C.c_int(upper is not None),
+                                             C.c_float(upper or 0.0), None, _p(od), _p(oi), None)
+        return od[:n], oi[:n]
+
     def search(self, queries, k, nprobes, refine_factor=0, lower=None, upper=None, threads=0):
         queries = _f16(queries)
         Q = queries.shape[0]

@@ -79,3 +79,31 @@ def test_f16_handle_rejects_f32_entry_points_and_bad_shapes(oracle):
                     np.zeros(800 * 8, np.uint8), data.row_ids, None)
     with pytest.raises(LanceB200Error, match="num_sub_vectors"):
         IvfPqIndexF16(bad)
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+def test_f16_find_partitions_and_search_in_partition(oracle, metric):
+    """The two calls the exec nodes make, on a Float16 handle: keys as given (normalised by the caller for cosine)."""
+    from lance_b200 import IvfPqIndexF16
+    data, vecs = _f16_index(metric, 128, 10, 16, 4000, seed=41)
+    rng = np.random.default_rng(42)
+    q = (vecs[rng.integers(0, len(vecs), 7)] + 0.05 * rng.normal(size=(7, 128))).astype(np.float16)
+    keys = np.stack([oracle.normalize_f16(x) for x in q]) if metric == "cosine" else q
+    ix, ox = IvfPqIndexF16(data), oracle.OracleIndexF16(data)
+    try:
+        ids, ds = ix.find_partitions(keys, 4, return_distances=True)
+        for j in range(len(q)):
+            ri, rd = ox.find_partitions(keys[j], 4)
+            assert ids[j].tolist() == ri.tolist()
+            assert _bits(ds[j]).tolist() == _bits(rd).tolist()
+        parts = np.stack([np.roll(np.arange(10, dtype=np.uint32), j)[:3] for j in range(len(q))])
+        for lo, hi in ((None, None), (None, float(np.median(ds)))):
+            od, oi, oc = ix.search_in_partition(parts, keys, 15, lower_bound=lo, upper_bound=hi)
+            for j in range(len(q)):
+                for c in range(3):
+                    rd, rr = ox.search_in_partition(int(parts[j, c]), keys[j], 15, lo, hi)
+                    n = int(oc[j, c])
+                    assert n == len(rr) and oi[j, c, :n].tolist() == rr.tolist(), (metric, j, c)
+                    assert _bits(od[j, c, :n]).tolist() == _bits(rd).tolist()
+    finally:
+        ix.close()
