@@ -291,7 +291,9 @@ int32_t lb200_flat_topk_device(int32_t device_id, int32_t metric, uint32_t dim,
  * within a proved error bound of an exact upper bound of the k-th distance, and only those rows are scored by the exact
  * fp32 kernels -- same results by construction (csrc/api_column.inl states the bound); if a candidate buffer overflows
  * the exact path answers (and the column's next call gets larger buffers).  Cosine keeps one more bf16 copy of the
- * rows (unit length), made on the first cosine call.  Calls on one column serialise.  lb200_column_last_call reports what the last call did. */
+ * rows (unit length), made on the first cosine call.  Calls on one column serialise.  The _device form enqueues on
+ * `stream` (NULL: the column's own) and RETURNS AFTER THE STREAM HAS DRAINED: it reads the candidate counts back to decide
+ * about the fall-back, so it is not an asynchronous call.  lb200_column_last_call reports what the last call did. */
 typedef struct lb200_column lb200_column;
 int32_t lb200_column_create(int32_t device_id, uint32_t dim, const float* vectors, const uint8_t* validity_or_null,
                             uint64_t n, lb200_column** out);
