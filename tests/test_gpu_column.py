@@ -144,3 +144,18 @@ def test_column_filter_cosine_and_dot(metric, d, n, Q, k):
     _same(col.flat_knn(q[:3], "l2", k), flat_knn(q[:3], "l2", v, k))     # the L2 form on the same column afterwards
     _same(col.flat_knn(q[::-1].copy(), metric, k), flat_knn(q[::-1].copy(), metric, v, k))
     col.close()
+
+
+def test_column_large_query_batches_are_chunked():
+    """More than 2048 queries per call: the column answers in chunks (bounded scratch); statistics add up."""
+    from lance_b200 import VectorColumn, flat_knn
+    rng = np.random.default_rng(77)
+    d, n, Q, k = 64, 70_000, 2100, 5
+    v = _sift(rng, n, d)
+    q = _sift(rng, Q, d)
+    col = VectorColumn(v)
+    got = col.flat_knn(q, "l2", k)
+    st = col.last_call()
+    assert st["used_tc"] and not st["fell_back"] and st["candidates"] >= Q * k
+    _same(got, flat_knn(q, "l2", v, k))
+    col.close()
