@@ -85,6 +85,20 @@ __global__ void first_part_kernel(const uint32_t* __restrict__ probes, uint32_t 
   minp[q] = m;
 }
 
+// Seeding launch (api_search.inl): the pair a query's first bound comes from = its NEAREST probed partition that holds
+// rows here (probe lists are in ascending centroid distance).  No such partition -> the first probe (empty: no item).
+__global__ void seed_probes_kernel(const uint32_t* __restrict__ probes, uint32_t Q, uint32_t P,
+                                   const uint64_t* __restrict__ part_off, uint32_t* __restrict__ seed) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= Q) return;
+  uint32_t best = probes[(size_t)q * P];
+  for (uint32_t r = 0; r < P; r++) {
+    const uint32_t p = probes[(size_t)q * P + r];
+    if (part_off[p + 1] > part_off[p]) { best = p; break; }
+  }
+  seed[q] = best;
+}
+
 // Step 1: histogram of probed partitions (cold pairs and the others counted apart);
 // rank[e] = arrival order of pair e in its class, bit 31 = cold.
 __global__ void count_pairs_kernel(const uint32_t* __restrict__ probes, uint32_t npairs, uint32_t P,
