@@ -177,6 +177,7 @@ struct lb200_index {
   uint32_t dim = 0, nlist = 0, M = 0, dsub = 0;
   uint64_t N = 0, ntiles = 0, max_part = 0;
   double avg_np = 0;  // mean rows per NON-EMPTY partition
+  uint32_t nonempty = 0;  // partitions that hold rows
   float *d_centroids = nullptr, *d_codebook = nullptr, *d_raw = nullptr;
   bool f16 = false;                    // Float16 handle (api_f16pq.inl): centroids / codebook are exact widenings
   __half* d_raw16 = nullptr;           // its raw vectors for the refine step
@@ -330,6 +331,7 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
     uint32_t ne = 0;
     for (uint32_t p = 0; p < nlist; p++) ne += part_offsets[p + 1] > part_offsets[p];
     ix->avg_np = (double)N / std::max(1u, ne);
+    ix->nonempty = ne;
   }
   std::vector<uint64_t> tile_off(nlist + 1);
   uint64_t t = 0;

@@ -408,8 +408,9 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   // then a visible part of the scan (partition shards: 1/G of the items per GPU; cfg 4 at N = 8: +3.3 %).  With
   // hundreds of items per CTA the id-ordered queue is the faster one (cfg 4 at N = 1: -1 %, cfg 1: -4 %; same-box A/B
   // profiles/r02_ai, r02_aj).
+  // (a shard holds rows in a fraction of the partitions only: that fraction of the pairs becomes work items)
   bool lpt = ix->d_size_order != nullptr &&
-             (double)Q * P / sc.ql < 64.0 * ix->sm_count * std::max(1, sc.minb);
+             (double)Q * P / sc.ql * ((double)ix->nonempty / std::max(1u, nlist)) < 64.0 * ix->sm_count * std::max(1, sc.minb);
   if (const char* e = getenv("LB200_LPT")) lpt = ix->d_size_order != nullptr && atoi(e) != 0;
   CK(cudaMemsetAsync(d_scnt, 0, nslots * 4, st));
   const uint32_t* total_items_p = d_item_off + nlist;
@@ -516,7 +517,9 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
     // shard of 8 (profiles/r02_bj_*: LB200_KEEP_QTHR).  So the first 2048 rows of each query's NEAREST probed partition
     // are scanned first, by the same kernel on a one-pair-per-query work list; its finalize publishes the k'-th best
     // of those rows (a valid bound: k' real rows at or below it; to the peer shards too).  Outputs are thrown away --
-    // the main launch scans those rows again.  Only with in-kernel tables (the pre-pass builds per-pair tables once).
+    // the main launch scans those rows again.  Only with in-kernel tables: per-pair pre-pass tables (cfg 3) sit in slots
+    // that follow the main work list, and with per-query tables (cfg 5, dot) the extra launch cost more than it saved
+    // (same-box A/B: 8.39 vs 7.98 ms).
     bool seed = sp.qthr != nullptr && !use_pre && !a.pw && !a.d_bitmask && P >= 8 && npairs >= 4096 && kprime <= 64;
     if (const char* e = getenv("LB200_SEED")) seed = seed && atoi(e) != 0;
     if (seed) {
@@ -524,7 +527,8 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
       CK(cudaMemsetAsync(s_minp, 0xff, (size_t)Q * 4, st));
       CK(cudaMemsetAsync(s_stats, 0, 32, st));
       CK(cudaMemsetAsync(s_ocnt, 0, (size_t)Q * 4, st));
-      seed_probes_kernel<<<(Q + 255) / 256, 256, 0, st>>>(probes, Q, P, ix->d_part_off, s_probe);
+      const int first_only = a.shard_mode && sp.n_peers > 0 && !getenv("LB200_SEED_ALL");
+      seed_probes_kernel<<<(Q + 255) / 256, 256, 0, st>>>(probes, Q, P, ix->d_part_off, s_probe, first_only);
       count_pairs_kernel<<<(Q + 255) / 256, 256, 0, st>>>(s_probe, Q, 1, s_minp, s_cnt, s_cnt + nlist, s_rank);
       const uint32_t whole = (uint32_t)std::max<uint64_t>(16, (ix->max_part + 15) / 16 * 16);   // one item per query group
       offsets_kernel<<<1, 1024, 0, st>>>(s_cnt, s_cnt + nlist, ix->d_part_off, nlist, (uint32_t)sc.ql, whole, ix->M, s_pair_off,
@@ -536,7 +540,9 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
       ss.P = 1;                                   // pair id == query
       ss.pair_list = s_pair_list; ss.part_pair_off = s_pair_off; ss.item_off = s_item_off; ss.item_counter = s_counter;
       ss.item_desc = s_desc;
-      ss.chunk_vecs = 2048; ss.max_chunks = 1;    // chunk 0 only: rows [0, 2048) of the partition
+      uint32_t seed_rows = 2048;
+      if (const char* e = getenv("LB200_SEED_ROWS")) seed_rows = std::max(1024u, (uint32_t)atoi(e) / 1024u * 1024u);
+      ss.chunk_vecs = seed_rows; ss.max_chunks = 1;    // chunk 0 only: rows [0, seed_rows) of the partition
       ss.no_boot = 0; ss.boot2 = 1;
       ss.lut_src = nullptr; ss.lut_max = nullptr; ss.lut_image = 0;
       ss.out_dist = s_odist; ss.out_pos = s_opos; ss.out_rowid = s_orow; ss.out_count = s_ocnt;

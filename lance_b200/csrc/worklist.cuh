@@ -87,12 +87,14 @@ __global__ void first_part_kernel(const uint32_t* __restrict__ probes, uint32_t 
 
 // Seeding launch (api_search.inl): the pair a query's first bound comes from = its NEAREST probed partition that holds
 // rows here (probe lists are in ascending centroid distance).  No such partition -> the first probe (empty: no item).
+// first_only (partition shards): only the query's globally nearest partition counts -- the shard that holds it seeds the
+// query and the bound reaches the other shards through the peer tables, instead of every shard seeding every query.
 __global__ void seed_probes_kernel(const uint32_t* __restrict__ probes, uint32_t Q, uint32_t P,
-                                   const uint64_t* __restrict__ part_off, uint32_t* __restrict__ seed) {
+                                   const uint64_t* __restrict__ part_off, uint32_t* __restrict__ seed, int first_only) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= Q) return;
   uint32_t best = probes[(size_t)q * P];
-  for (uint32_t r = 0; r < P; r++) {
+  for (uint32_t r = 0; r < (first_only ? 1u : P); r++) {
     const uint32_t p = probes[(size_t)q * P + r];
     if (part_off[p + 1] > part_off[p]) { best = p; break; }
   }

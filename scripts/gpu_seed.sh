@@ -20,7 +20,8 @@ PY
 }
 EXTRA=""
 run seed_cfg4 LB200_SEED=1
-run noseed_cfg4 LB200_SEED=0
+if [ $N -gt 1 ]; then run seedall_cfg4 LB200_SEED=1 LB200_SEED_ALL=1; fi
+if [ $N -eq 1 ]; then run noseed_cfg4 LB200_SEED=0; fi
 if [ $N -eq 1 ]; then
   EXTRA="--workload cfg1"; run seed_cfg1 LB200_SEED=1; run noseed_cfg1 LB200_SEED=0
 fi
