@@ -425,11 +425,15 @@ coarse_dist_l2_slab_kernel(const float* __restrict__ queries, const float* __res
   fetch(0);
   stash(tile);
   __syncthreads();
-  float acc[4][16];
+  // lane accumulators in packed pairs (lanes 2j, 2j+1): sub, square and add run as FADD2 / FFMA2 / FADD2 -- each half is
+  // the scalar IEEE operation (the square is fma(d, d, -0) == mul.rn, see dist.cuh), half the issue slots of the
+  // scalar form (this kernel is fp32-issue bound: r01 ncu)
+  f32x2_t acc2[4][8];
 #pragma unroll
   for (int k = 0; k < 4; k++)
 #pragma unroll
-    for (int i = 0; i < 16; i++) acc[k][i] = 0.0f;
+    for (int i = 0; i < 8; i++) acc2[k][i] = 0ull;
+  const f32x2_t nz = g_negzero2;
   const float* xq = sq + (size_t)qg * 4 * d;
 #pragma unroll 1
   for (uint32_t s = 0; s < nslab; s++) {
@@ -442,21 +446,24 @@ coarse_dist_l2_slab_kernel(const float* __restrict__ queries, const float* __res
         float y[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) y[r] = buf[(size_t)(16 * ch + 4 * i4 + r) * CQ_PITCH + ct];
+        const f32x2_t y01 = pk2(y[0], y[1]), y23 = pk2(y[2], y[3]);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
           const float4 xv = *reinterpret_cast<const float4*>(xq + (size_t)k * d + s * 64 + 16 * ch + 4 * i4);
-          const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-          for (int r = 0; r < 4; r++) {
-            const float df = __fsub_rn(xs[r], y[r]);
-            acc[k][4 * i4 + r] = __fadd_rn(acc[k][4 * i4 + r], __fmul_rn(df, df));
-          }
+          const f32x2_t d01 = sub2(pk2(xv.x, xv.y), y01), d23 = sub2(pk2(xv.z, xv.w), y23);
+          acc2[k][2 * i4] = add2(acc2[k][2 * i4], fma2(d01, d01, nz));
+          acc2[k][2 * i4 + 1] = add2(acc2[k][2 * i4 + 1], fma2(d23, d23, nz));
         }
       }
     }
     if (s + 1 < nslab) stash(tile + ((s + 1) & 1) * CD_SLAB);
     __syncthreads();
   }
+  float acc[4][16];
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+#pragma unroll
+    for (int i = 0; i < 8; i++) upk2(acc2[k][i], acc[k][2 * i], acc[k][2 * i + 1]);
   const uint32_t c = c0 + ct;
 #pragma unroll
   for (int k = 0; k < 4; k++) {

@@ -208,4 +208,41 @@ __device__ __forceinline__ float exact_distance(int metric, const float* x, floa
   return cosine_fast(x, x_norm, y, d);
 }
 
+// Packed FP32 (Blackwell FADD2/FMUL2, PTX .f32x2): two IEEE round-to-nearest operations per
+// instruction, bit-identical per half to the scalar ops.  ptxas 12.9 CONTRACTS a mul.rn.f32x2 that
+// feeds an add.rn.f32x2 into one FFMA2 (single rounding) although both carry .rn, so products are
+// always unpacked and summed first with scalar __fadd_rn; only sub, mul and add-of-sums are packed.
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t pk2(float a, float b) {
+  f32x2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ f32x2_t add2(f32x2_t a, f32x2_t b) {
+  f32x2_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2_t sub2(f32x2_t a, f32x2_t b) {
+  f32x2_t r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2_t mul2(f32x2_t a, f32x2_t b) {
+  f32x2_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2_t fma2(f32x2_t a, f32x2_t b, f32x2_t c) {
+  f32x2_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// two packed -0.0f that the compiler cannot see through (fma2(d, d, -0) == mul.rn exactly, and cannot be contracted into
+// a following add2; a literal -0 would be folded back into a mul): read through the constant bank at run time
+static __constant__ unsigned long long g_negzero2 = 0x8000000080000000ull;
+
 }  // namespace lb200

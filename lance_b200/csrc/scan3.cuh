@@ -85,34 +85,7 @@ struct Scan3Params {
 
 constexpr uint32_t KEY_PINF = 0xff800000u;  // ordered_key(+inf)
 
-// Packed FP32 (Blackwell FADD2/FMUL2, PTX .f32x2): two IEEE round-to-nearest operations per
-// instruction, bit-identical per half to the scalar ops.  ptxas 12.9 CONTRACTS a mul.rn.f32x2 that
-// feeds an add.rn.f32x2 into one FFMA2 (single rounding) although both carry .rn, so products are
-// always unpacked and summed first with scalar __fadd_rn; only sub, mul and add-of-sums are packed.
-typedef unsigned long long f32x2_t;
-__device__ __forceinline__ f32x2_t pk2(float a, float b) {
-  f32x2_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ void upk2(f32x2_t v, float& a, float& b) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
-}
-__device__ __forceinline__ f32x2_t add2(f32x2_t a, f32x2_t b) {
-  f32x2_t r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ f32x2_t sub2(f32x2_t a, f32x2_t b) {
-  f32x2_t r;
-  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ f32x2_t mul2(f32x2_t a, f32x2_t b) {
-  f32x2_t r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
+// (packed FP32 helpers -- f32x2_t, pk2, upk2, add2, sub2, mul2, fma2 -- live in dist.cuh)
 // l2_once<f32x8,8> / l2_once<f32x16,16> (l2.rs:207-216) with the reduce_sum trees of simd/f32.rs,
 // on packed pairs X[i] = (x[2i], x[2i+1]).  Same operations, same order per value as dist.cuh.
 template <int DSUB>
@@ -148,11 +121,6 @@ __device__ __forceinline__ float l2_once_packed(const f32x2_t* X, const f32x2_t*
 // contracted any further -- so the first tree level runs packed too instead of unpacking every product (the
 // contraction problem described above).  `nz` = two packed -0.0f that ptxas cannot see through (a kernel parameter):
 // with a visible constant it would turn the fma back into a mul and contract it into the add.
-__device__ __forceinline__ f32x2_t fma2(f32x2_t a, f32x2_t b, f32x2_t c) {
-  f32x2_t r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
 template <int DSUB>
 __device__ __forceinline__ float l2_once_packed_nz(const f32x2_t* X, const f32x2_t* Y, f32x2_t nz) {
   f32x2_t P[DSUB / 2];
