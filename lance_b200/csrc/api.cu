@@ -179,6 +179,7 @@ struct lb200_index {
   double avg_np = 0;  // mean rows per NON-EMPTY partition
   uint32_t nonempty = 0;  // partitions that hold rows
   float *d_centroids = nullptr, *d_codebook = nullptr, *d_raw = nullptr;
+  float* d_codebook_img = nullptr;     // lane-order image of the codebook for the in-kernel table build (scan3.cuh cb_image_f4)
   bool f16 = false;                    // Float16 handle (api_f16pq.inl): centroids / codebook are exact widenings
   __half* d_raw16 = nullptr;           // its raw vectors for the refine step
   uint64_t *d_part_off = nullptr, *d_tile_off = nullptr, *d_row_ids = nullptr;
@@ -413,6 +414,12 @@ extern "C" int32_t lb200_index_create(int32_t device_id, int32_t metric, uint32_
   }
   CKF(cudaMemcpyAsync(ix->d_centroids, centroids, cent_b, cudaMemcpyHostToDevice, ix->stream));
   CKF(cudaMemcpyAsync(ix->d_codebook, codebook, cb_b, cudaMemcpyHostToDevice, ix->stream));
+  if (M % 16 == 0 && (ix->dsub == 8 || ix->dsub == 16)) {
+    CKF(cudaMalloc(&ix->d_codebook_img, cb_b));
+    const uint32_t n4 = M * 256 * (ix->dsub / 4);
+    cb_image_kernel<<<(n4 + 255) / 256, 256, 0, ix->stream>>>(ix->d_codebook, M, ix->dsub, reinterpret_cast<float4*>(ix->d_codebook_img));
+    CKF(cudaGetLastError());
+  }
   CKF(cudaMemcpyAsync(ix->d_part_off, part_offsets, (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
   CKF(cudaMemcpyAsync(ix->d_tile_off, tile_off.data(), (nlist + 1) * 8, cudaMemcpyHostToDevice, ix->stream));
   if (N) {
@@ -452,6 +459,7 @@ extern "C" void lb200_index_destroy(lb200_index* ix) {
   shard_comm_free(ix);
   cudaFree(ix->d_centroids);
   cudaFree(ix->d_codebook);
+  cudaFree(ix->d_codebook_img);
   cudaFree(ix->d_raw);
   cudaFree(ix->d_raw16);
   cudaFree(ix->d_part_off);

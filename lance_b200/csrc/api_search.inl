@@ -452,7 +452,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
   if (sc.variant == 3) {
     Scan3Params sp = {};
     sp.codes = ix->d_codes3; sp.sb_off = ix->d_sb_off; sp.part_off = ix->d_part_off; sp.row_ids = ix->d_row_ids;
-    sp.centroids = ix->d_centroids; sp.codebook = ix->d_codebook;
+    sp.centroids = ix->d_centroids; sp.codebook = sc.dsub_t ? ix->d_codebook_img : ix->d_codebook;  // in-kernel build: DSUB > 0 reads the image
     sp.dim = dim; sp.M = ix->M; sp.dsub = ix->dsub; sp.nlist = nlist; sp.L = ix->skew_L;
     sp.residual = ix->metric != LB200_DOT;
     sp.queries = keys; sp.Q = Q; sp.P = P; sp.kprime = kprime;

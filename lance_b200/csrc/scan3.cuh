@@ -37,6 +37,10 @@
 #define LB200_CODE_LOAD 0
 #endif
 
+#ifndef LB200_CB_DEPTH
+#define LB200_CB_DEPTH 1
+#endif
+
 namespace lb200 {
 
 struct Scan3Params {
@@ -46,7 +50,7 @@ struct Scan3Params {
   const uint64_t* part_off;       // [nlist+1] first row of each partition
   const uint64_t* row_ids;        // [N]
   const float* centroids;         // [nlist][dim]
-  const float* codebook;          // [M][256][dsub]
+  const float* codebook;          // DSUB == 0 instantiations: [M][256][dsub]; DSUB > 0: the lane-order image (cb_image_f4)
   uint32_t dim, M, dsub, nlist;
   uint32_t L;                     // rows per lane per superblock
   int32_t residual;               // 1: L2/cosine, 0: dot
@@ -141,6 +145,22 @@ __device__ __forceinline__ float l2_once_packed_nz(const f32x2_t* X, const f32x2
     upk2(add2(a01, a23), lo, hi);
   }
   return __fadd_rn(lo, hi);
+}
+
+// Codebook image for the in-kernel table build.  A build thread is (slot = tid % 16 -> sub-vector, code = tid / 16 + step):
+// in the [M][256][dsub] array the 32 lanes of one load instruction sit 32 bytes or 8 KB apart -- 32 cache lines per
+// instruction, and the build's loads alone cost the LSU pipe as many wavefronts as the whole row loop of a 4k-row
+// partition (r02_bt ncu, cfg 1: the build was 36 % of the kernel's warp time).  The image stores, per 16-sub-vector
+// chunk and per PAIR of codes, the i-th float4 of the 32 (code parity, slot) rows side by side: one load instruction
+// = 512 contiguous bytes.  Offset in float4 units; built once per handle by cb_image_kernel.
+__host__ __device__ __forceinline__ size_t cb_image_f4(uint32_t ch, uint32_t code, uint32_t slot, uint32_t i, uint32_t dsub4) {
+  return (((size_t)ch * 128 + (code >> 1)) * dsub4 + i) * 32 + (code & 1u) * 16 + slot;
+}
+static __global__ void cb_image_kernel(const float* __restrict__ codebook, uint32_t M, uint32_t dsub, float4* __restrict__ image) {
+  const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x, dsub4 = dsub / 4;
+  if (e >= M * 256 * dsub4) return;
+  const uint32_t i = e % dsub4, row = e / dsub4, code = row & 255u, m = row >> 8;
+  image[cb_image_f4(m >> 4, code, m & 15u, i, dsub4)] = reinterpret_cast<const float4*>(codebook)[e];
 }
 
 // ADC tables as a pre-pass (A3 + A4 out of the scan kernel).  The scan kernel builds its tables per
@@ -768,25 +788,32 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
         }
         // the codebook rows come from L2 (128 KB+ per item, more than L1 keeps): the next row is loaded while the
         // current one is worked on (r02 ncu: 5.6 % of the kernel's warp time sat on the first use of this load)
-        float4 nx[DSUB > 0 ? DSUB / 4 : 1];
+        constexpr int CBD = LB200_CB_DEPTH;                       // loads in flight per thread (code steps ahead)
+        constexpr uint32_t CBSTEP = (NT / 32) * (DSUB > 0 ? DSUB / 4 : 1) * 32;  // float4s between code steps
+        float4 nx[CBD][DSUB > 0 ? DSUB / 4 : 1];
+        // lane-order image: this warp's 32 (code parity, slot) rows of one load are 512 contiguous bytes
+        const float4* cb4 = reinterpret_cast<const float4*>(p.codebook) + cb_image_f4(ch, tid >> 4, slot, 0, DSUB > 0 ? DSUB / 4 : 1);
         if (DSUB > 0) {
 #pragma unroll
-          for (int i = 0; i < DSUB / 4; i++)
-            nx[i] = __ldg(reinterpret_cast<const float4*>(p.codebook + ((size_t)m * 256 + (tid >> 4)) * DSUB) + i);
+          for (int d = 0; d < CBD; d++)
+#pragma unroll
+            for (int i = 0; i < DSUB / 4; i++) nx[d][i] = __ldg(cb4 + d * CBSTEP + i * 32);
         }
 #pragma unroll 1
-        for (uint32_t code = tid >> 4; code < 256; code += NT / 16) {
+        for (uint32_t code0 = tid >> 4; code0 < 256; code0 += CBD * (NT / 16)) {
+#pragma unroll
+        for (int d = 0; d < CBD; d++) {
+          const uint32_t code = code0 + d * (NT / 16);
           const float* y = p.codebook + ((size_t)m * 256 + code) * dsub;
           float yr[DSUB > 0 ? DSUB : 1];
           if (DSUB > 0) {
 #pragma unroll
             for (int i = 0; i < DSUB / 4; i++) {
-              yr[4 * i] = nx[i].x; yr[4 * i + 1] = nx[i].y; yr[4 * i + 2] = nx[i].z; yr[4 * i + 3] = nx[i].w;
+              yr[4 * i] = nx[d][i].x; yr[4 * i + 1] = nx[d][i].y; yr[4 * i + 2] = nx[d][i].z; yr[4 * i + 3] = nx[d][i].w;
             }
-            if (code + NT / 16 < 256) {
+            if (code + CBD * (NT / 16) < 256) {
 #pragma unroll
-              for (int i = 0; i < DSUB / 4; i++)
-                nx[i] = __ldg(reinterpret_cast<const float4*>(y + (size_t)(NT / 16) * DSUB) + i);
+              for (int i = 0; i < DSUB / 4; i++) nx[d][i] = __ldg(cb4 + (d + CBD) * CBSTEP + i * 32);
             }
           }
           float val[QL];
@@ -817,6 +844,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
             *reinterpret_cast<float4*>(dst) = make_float4(val[0], val[1], val[2], val[3]);
           else
             *reinterpret_cast<float2*>(dst) = make_float2(val[0], val[1]);
+        }
+        cb4 += CBD * CBSTEP;
         }
       }
     }
