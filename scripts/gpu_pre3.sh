@@ -1,0 +1,16 @@
+#!/bin/bash
+# pre-pass staging change: parity tests + cfg3 / cfg5 lines
+T=${1:-r2bw}
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests/test_gpu_parity.py tests/test_gpu_f16_ivfpq.py -x -q > gpurun_out/${T}_tests.log 2>&1; echo "exit $?" >> gpurun_out/${T}_tests.log; tail -3 gpurun_out/${T}_tests.log
+for W in cfg3 cfg5; do
+  timeout 600 python bench.py --workload $W --steps 10 --warmup 3 --no-cpu-baseline --no-recall > gpurun_out/${T}_bench_$W.json 2> gpurun_out/${T}_bench_$W.err
+  python - <<PY
+import json
+try:
+    d = json.loads(open("gpurun_out/${T}_bench_$W.json").read().strip().splitlines()[-1])
+    print("$W", round(d["value"]), "q/s  ms/step", round(d["ms_per_step"], 3), "scan_ms", round(d["roofline"]["scan_ms_per_launch"], 3), "frac", round(d["roofline"]["frac"], 3), "crc", d.get("result_crc32"))
+except Exception as e:
+    print("parse fail", e); print(open("gpurun_out/${T}_bench_$W.err").read()[-1500:])
+PY
+done
