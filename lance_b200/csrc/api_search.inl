@@ -320,7 +320,7 @@ static int search_pipeline(lb200_index* ix, CallCtx& cx, const SearchArgs& a, cu
       return set_err(LB200_EUNSUPPORTED, "Float16 IVF_PQ: %zu ADC tables in one batch exceed the table scratch", pre_units);
     use_pre = true;
   }
-  // per-pair tables stored as one interleaved image per query group (scan3.cuh lut_fetch_image): a few more table
+  // per-pair tables stored as one interleaved image per query group (scan3.cuh lut_image_issue / lut_image_wait): a few more table
   // slots (the last group of a partition may be partly filled), positions in the pair list as unit numbers
   const bool pre_image = use_pre && !pre_by_query && !ix->f16 && sc.minb == 1 && !getenv("LB200_NO_LUT_IMAGE");
   const size_t pre_slots = pre_image ? pre_units + (size_t)nlist * (sc.ql - 1) : pre_units;
