@@ -310,11 +310,11 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
 // bandwidth- not latency-bound.  Returns the largest |entry| bit pattern of the item's tables (from
 // the pre-pass) for the exact-FMA row switch test.  Out of line: runs once per item.
 template <int QL>
-static __device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const float* __restrict__ src,
-                                           const uint32_t* __restrict__ lut_max, size_t unit_stride,
-                                           const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent) {
+static __device__ __noinline__ void lut_fetch_issue(unsigned char* lut, const float* __restrict__ src, size_t unit_stride,
+                                                    const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent,
+                                                    uint32_t w /*rank among the issuing warps*/, uint32_t nwarp) {
   constexpr uint32_t EPW = 32 / QL;
-  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const uint32_t lane = threadIdx.x & 31;
   const uint32_t unit = units[min(lane % QL, nq - 1)];  // unused slots replicate a valid table (never read back)
   const float* s = src + (size_t)unit * unit_stride + lane / QL;
   const uint32_t dst = (uint32_t)__cvta_generic_to_shared(lut) + lane * 4;
@@ -322,9 +322,19 @@ static __device__ __noinline__ uint32_t lut_fetch(unsigned char* lut, const floa
   for (uint32_t e = w * EPW; e < nent; e += nwarp * EPW)
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + e * (4 * QL)), "l"(s + e) : "memory");
   asm volatile("cp.async.commit_group;" ::: "memory");
-  const uint32_t mb = lut_max[unit];
+}
+template <int QL>
+static __device__ __noinline__ uint32_t lut_fetch_wait(const uint32_t* __restrict__ lut_max, const uint32_t* units, uint32_t nq) {
+  const uint32_t mb = lut_max[units[min((threadIdx.x & 31) % QL, nq - 1)]];
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   return mb;
+}
+template <int QL>
+static __device__ __forceinline__ uint32_t lut_fetch(unsigned char* lut, const float* __restrict__ src,
+                                                     const uint32_t* __restrict__ lut_max, size_t unit_stride,
+                                                     const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent) {
+  lut_fetch_issue<QL>(lut, src, unit_stride, units, nq, nent, threadIdx.x >> 5, blockDim.x >> 5);
+  return lut_fetch_wait<QL>(lut_max, units, nq);
 }
 
 // Image mode: the group's interleaved tables are one contiguous block -> bulk copies (TMA 1-D) issued by one thread,
@@ -685,6 +695,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   const uint32_t sthrf_saddr = (uint32_t)__cvta_generic_to_shared(sthrf);
   __shared__ __align__(8) uint64_t lut_bar;   // completion of the bulk table fetch (image mode)
   __shared__ uint32_t lut_phase;              // its parity (kept out of the registers: the row loop is at the 128 cap)
+  __shared__ uint32_t sunit_n[4];             // wide CTAs, pre-built tables: the NEXT item's table units, its query count,
+  __shared__ uint32_t snq_n, spref;           // and whether the item now starting had its tables fetched ahead
 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   if (MINB == 1 && p.lut_image && tid == 0) {
@@ -727,6 +739,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
   // top of an item and its result is first used after the table build; the descriptor then travels global ->
   // shared with cp.async during the row scan.
   if (tid == 0) {
+    spref = 0;
     const uint32_t it = atomicAdd(p.item_counter, 1u);
     sitem[0] = it;
     if (it < total_items) {
@@ -797,7 +810,10 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     if (MINB == 1 && p.lut_image) {  // (one-CTA-per-SM instantiations only: the others sit at the register cap)
       maxbits = lut_image_wait(p.lut_max, pbase, nq, &lut_bar, &lut_phase);  // issued at the end of the previous item
     } else if (p.lut_src) {
-      maxbits = lut_fetch<QL>(lut, p.lut_src, p.lut_max, (size_t)M * 256, p.lut_by_query ? sqidx : spair, nq, C16 * 4096u);
+      if (NW == 16 && spref)  // issued by the idle warps at the end of the previous item (below)
+        maxbits = lut_fetch_wait<QL>(p.lut_max, p.lut_by_query ? sqidx : spair, nq);
+      else
+        maxbits = lut_fetch<QL>(lut, p.lut_src, p.lut_max, (size_t)M * 256, p.lut_by_query ? sqidx : spair, nq, C16 * 4096u);
     } else {
       const uint32_t slot = tid & 15;
 #pragma unroll 1
@@ -1012,6 +1028,33 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
     if (MINB == 1 && p.lut_image && tid == NT - 32 && sitem[0] < total_items) {
       const uint4 dn = *sdesc;
       lut_image_issue(lut, p.lut_src + lut_image_base(p.part_pair_off[dn.x], dn.x, dn.y, QL) * M * 256, C16 * CB, &lut_bar);
+    }
+    // wide CTAs with pre-built tables that are gathered per query (lut_fetch): the end-of-item select keeps nq <= QL
+    // warps busy and the rest waited for it, then everyone issued the next item's 4-byte copies (r02_bt ncu, cfg 5:
+    // 16 % of the warp time behind the select, 17 % of the instructions in the fetch).  The warps without a query
+    // now work out the next item's units and issue its fetch while the select runs.
+    if constexpr (NW == 16 && BOOT) {
+      if (p.lut_src && !p.lut_image) {
+        const bool have = sitem[0] < total_items;
+        if (tid == 0) spref = have ? 1u : 0u;
+        if (have && w >= QL) {
+          const uint32_t i = tid - QL * 32;
+          if (i < QL) {
+            const uint4 dn = *sdesc;
+            const uint32_t pb = p.part_pair_off[dn.x] + dn.y * QL;
+            const uint32_t nqn = min((uint32_t)QL, p.part_pair_off[dn.x + 1] - pb);
+            uint32_t u = 0;
+            if (i < nqn) {
+              u = p.pair_list[pb + i];
+              if (p.lut_by_query) u /= p.P;
+            }
+            sunit_n[i] = u;
+            if (i == 0) snq_n = nqn;
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"((NW - QL) * 32) : "memory");
+          lut_fetch_issue<QL>(lut, p.lut_src, (size_t)M * 256, sunit_n, snq_n, C16 * 4096u, w - QL, NW - QL);
+        }
+      }
     }
 
     if constexpr (BOOT) {
