@@ -37,6 +37,9 @@
 #define LB200_CODE_LOAD 0
 #endif
 
+#ifndef LB200_FINALIZE_SMALL
+#define LB200_FINALIZE_SMALL 1
+#endif
 #ifndef LB200_CB_DEPTH
 #define LB200_CB_DEPTH 1
 #endif
@@ -642,11 +645,77 @@ static __device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
   __syncthreads();
 }
 
+// End of an item for one query, small candidate counts (n <= 128, the usual case once the bounds are warm): the
+// candidates go from the NW per-warp segments straight into registers (4 per lane, located through a prefix scan of
+// the segment counts), every candidate is ranked against every other by (key, row id, position) with shuffles, and
+// the first k' are written to their rank.  Same order as warp_select_k + warp_sort_emit (select.cuh), without the
+// segment-by-segment gather (16 dependent shared-memory round trips) and the 32-step bisection over shared memory
+// (r02_bt ncu, cfg 5: the select was 16 % of the warp time with nq of 16 warps busy).  Returns false when n > 128.
+static __device__ __noinline__ bool finalize_small(const ItemCtx* c, uint32_t qq, uint32_t lane) {
+  const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime;
+  const uint32_t cn = lane < NW ? c->ccnt[qq * NW + lane] : 0u;
+  uint32_t inc = cn;  // inclusive prefix over the segments
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(FULL, inc, o);
+    if (lane >= (uint32_t)o) inc += v;
+  }
+  const uint32_t n = __shfl_sync(FULL, inc, 31);
+  if (n > 128) return false;
+  const uint32_t* dk = c->ckey + (size_t)qq * NW * capw;
+  const uint32_t* dp = c->cpos + (size_t)qq * NW * capw;
+  uint32_t seg[4], base[4];
+#pragma unroll
+  for (int r = 0; r < 4; r++) seg[r] = base[r] = 0;
+  for (uint32_t l = 0; l < NW; l++) {  // segment of element idx = number of segments that end at or before it
+    const uint32_t e = __shfl_sync(FULL, inc, l);
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+      if (e <= lane + 32u * r) { seg[r] = l + 1; base[r] = e; }
+  }
+  uint32_t key[4], pos[4], rank[4];
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+    const uint32_t idx = lane + 32u * r;
+    key[r] = 0xffffffffu; pos[r] = 0; rank[r] = 0;
+    if (idx < n) {
+      key[r] = dk[(size_t)seg[r] * capw + idx - base[r]];
+      pos[r] = dp[(size_t)seg[r] * capw + idx - base[r]];
+    }
+  }
+#pragma unroll
+  for (int rj = 0; rj < 4; rj++) {
+    const uint32_t nj = n > 32u * rj ? min(32u, n - 32u * rj) : 0u;
+    for (uint32_t jl = 0; jl < nj; jl++) {
+      const uint32_t kj = __shfl_sync(FULL, key[rj], jl), pj = __shfl_sync(FULL, pos[rj], jl);
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        if (kj < key[r]) rank[r]++;
+        else if (kj == key[r] && !(rj == r && jl == lane) && lane + 32u * r < n && cand_less(kj, pj, key[r], pos[r], c->prow)) rank[r]++;
+      }
+    }
+  }
+  const uint32_t nout = min(n, kprime);
+  const size_t slot = (size_t)c->spair[qq] * c->max_chunks + c->chunk;
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+    if (lane + 32u * r < n && rank[r] < nout) {
+      c->out_dist[slot * kprime + rank[r]] = key_to_float(key[r]);
+      c->out_pos[slot * kprime + rank[r]] = c->row_base + pos[r];
+      c->out_rowid[slot * kprime + rank[r]] = c->prow[pos[r]];
+      if (n >= kprime && rank[r] == kprime - 1 && c->qthr) publish_bound(c, c->sqidx[qq], key[r]);  // the k'-th best
+    }
+  }
+  if (lane == 0) c->out_count[slot] = nout;
+  return true;
+}
+
 // End of an item: one warp per query gathers the warps' buffers, selects k', emits sorted.
 static __device__ __noinline__ void finalize_fn(const ItemCtx* c) {
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime;
   for (uint32_t qq = w; qq < c->nq; qq += NW) {
+    if (LB200_FINALIZE_SMALL && finalize_small(c, qq, lane)) continue;
     uint32_t* dk = c->ckey + (size_t)qq * NW * capw;
     uint32_t* dp = c->cpos + (size_t)qq * NW * capw;
     uint32_t n = gather_segments(dk, dp, c->ccnt + qq * NW, NW, capw, lane);

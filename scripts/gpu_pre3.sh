@@ -2,7 +2,7 @@
 # pre-pass staging change: parity tests + cfg3 / cfg5 lines
 T=${1:-r2bw}
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_gpu_parity.py tests/test_gpu_f16_ivfpq.py -x -q > gpurun_out/${T}_tests.log 2>&1; echo "exit $?" >> gpurun_out/${T}_tests.log; tail -3 gpurun_out/${T}_tests.log
+timeout 1200 python -m pytest tests/test_gpu_parity.py tests/test_gpu_f16_ivfpq.py tests/test_gpu_group.py tests/test_gpu_dropin.py tests/test_gpu_scanner.py -x -q > gpurun_out/${T}_tests.log 2>&1; echo "exit $?" >> gpurun_out/${T}_tests.log; tail -3 gpurun_out/${T}_tests.log
 for W in cfg3 cfg5; do
   timeout 600 python bench.py --workload $W --steps 10 --warmup 3 --no-cpu-baseline --no-recall > gpurun_out/${T}_bench_$W.json 2> gpurun_out/${T}_bench_$W.err
   python - <<PY
