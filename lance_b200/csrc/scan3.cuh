@@ -40,6 +40,9 @@
 #ifndef LB200_FINALIZE_SMALL
 #define LB200_FINALIZE_SMALL 1
 #endif
+#ifndef LB200_FINALIZE_SMALL_INLINE
+#define LB200_FINALIZE_SMALL_INLINE 0   // the call-free (BOOT = false) text: A/B'd separately, see DESIGN 4.2
+#endif
 #ifndef LB200_CB_DEPTH
 #define LB200_CB_DEPTH 1
 #endif
@@ -651,9 +654,14 @@ static __device__ __noinline__ void bootstrap_fn(const ItemCtx* c) {
 // the first k' are written to their rank.  Same order as warp_select_k + warp_sort_emit (select.cuh), without the
 // segment-by-segment gather (16 dependent shared-memory round trips) and the 32-step bisection over shared memory
 // (r02_bt ncu, cfg 5: the select was 16 % of the warp time with nq of 16 warps busy).  Returns false when n > 128.
-static __device__ __noinline__ bool finalize_small(const ItemCtx* c, uint32_t qq, uint32_t lane) {
-  const uint32_t NW = c->nw, capw = c->capw, kprime = c->kprime;
-  const uint32_t cn = lane < NW ? c->ccnt[qq * NW + lane] : 0u;
+// Returns bit 63: handled, bit 62: the query has k' candidates and bits 0-31 hold the k'-th best key (the bound to
+// publish), bits 32-47: rows written.
+static __device__ __noinline__ uint64_t rank_emit_small(const uint32_t* dk, const uint32_t* dp, const uint32_t* cnt, uint32_t NW,
+                                                        uint32_t capw, uint32_t kprime, const uint64_t* __restrict__ prow,
+                                                        uint64_t row_base, float* __restrict__ out_dist,
+                                                        uint64_t* __restrict__ out_pos, uint64_t* __restrict__ out_rowid,
+                                                        uint32_t lane) {
+  const uint32_t cn = lane < NW ? cnt[lane] : 0u;
   uint32_t inc = cn;  // inclusive prefix over the segments
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -661,9 +669,7 @@ static __device__ __noinline__ bool finalize_small(const ItemCtx* c, uint32_t qq
     if (lane >= (uint32_t)o) inc += v;
   }
   const uint32_t n = __shfl_sync(FULL, inc, 31);
-  if (n > 128) return false;
-  const uint32_t* dk = c->ckey + (size_t)qq * NW * capw;
-  const uint32_t* dp = c->cpos + (size_t)qq * NW * capw;
+  if (n > 128) return 0ull;
   uint32_t seg[4], base[4];
 #pragma unroll
   for (int r = 0; r < 4; r++) seg[r] = base[r] = 0;
@@ -691,22 +697,38 @@ static __device__ __noinline__ bool finalize_small(const ItemCtx* c, uint32_t qq
 #pragma unroll
       for (int r = 0; r < 4; r++) {
         if (kj < key[r]) rank[r]++;
-        else if (kj == key[r] && !(rj == r && jl == lane) && lane + 32u * r < n && cand_less(kj, pj, key[r], pos[r], c->prow)) rank[r]++;
+        else if (kj == key[r] && !(rj == r && jl == lane) && lane + 32u * r < n && cand_less(kj, pj, key[r], pos[r], prow)) rank[r]++;
       }
     }
   }
   const uint32_t nout = min(n, kprime);
-  const size_t slot = (size_t)c->spair[qq] * c->max_chunks + c->chunk;
+  uint32_t myT = 0;
+  bool mine = false;
 #pragma unroll
   for (int r = 0; r < 4; r++) {
     if (lane + 32u * r < n && rank[r] < nout) {
-      c->out_dist[slot * kprime + rank[r]] = key_to_float(key[r]);
-      c->out_pos[slot * kprime + rank[r]] = c->row_base + pos[r];
-      c->out_rowid[slot * kprime + rank[r]] = c->prow[pos[r]];
-      if (n >= kprime && rank[r] == kprime - 1 && c->qthr) publish_bound(c, c->sqidx[qq], key[r]);  // the k'-th best
+      out_dist[rank[r]] = key_to_float(key[r]);
+      out_pos[rank[r]] = row_base + pos[r];
+      out_rowid[rank[r]] = prow[pos[r]];
+      if (rank[r] == kprime - 1) { myT = key[r]; mine = true; }  // the k'-th best
     }
   }
-  if (lane == 0) c->out_count[slot] = nout;
+  const uint32_t who = __ballot_sync(FULL, mine);
+  uint64_t ret = (1ull << 63) | ((uint64_t)nout << 32);
+  if (who) ret |= (1ull << 62) | __shfl_sync(FULL, myT, __ffs(who) - 1);
+  return ret;
+}
+static __device__ __forceinline__ bool finalize_small(const ItemCtx* c, uint32_t qq, uint32_t lane) {
+  const size_t slot = (size_t)c->spair[qq] * c->max_chunks + c->chunk;
+  const uint64_t r = rank_emit_small(c->ckey + (size_t)qq * c->nw * c->capw, c->cpos + (size_t)qq * c->nw * c->capw,
+                                     c->ccnt + qq * c->nw, c->nw, c->capw, c->kprime, c->prow, c->row_base,
+                                     c->out_dist + slot * c->kprime, c->out_pos + slot * c->kprime,
+                                     c->out_rowid + slot * c->kprime, lane);
+  if (!(r >> 63)) return false;
+  if (lane == 0) {
+    if (((r >> 62) & 1ull) && c->qthr) publish_bound(c, c->sqidx[qq], (uint32_t)r);
+    c->out_count[slot] = (uint32_t)(r >> 32) & 0xffffu;
+  }
   return true;
 }
 
@@ -1134,6 +1156,18 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       for (uint32_t qq = w; qq < nq; qq += NW) {
         uint32_t* dk = ckey + (size_t)qq * NW * capw;
         uint32_t* dp = cpos + (size_t)qq * NW * capw;
+        if (LB200_FINALIZE_SMALL_INLINE) {
+          const size_t slot = (size_t)spair[qq] * p.max_chunks + c;
+          const uint64_t r = rank_emit_small(dk, dp, ccnt + qq * NW, NW, capw, kprime, prow, row_base, p.out_dist + slot * kprime,
+                                             p.out_pos + slot * kprime, p.out_rowid + slot * kprime, lane);
+          if (r >> 63) {
+            if (lane == 0) {
+              if (((r >> 62) & 1ull) && p.qthr) atomicMin(p.qthr + sqidx[qq], (uint32_t)r);
+              p.out_count[slot] = (uint32_t)(r >> 32) & 0xffffu;
+            }
+            continue;
+          }
+        }
         uint32_t n = ccnt[qq * NW];
 #pragma unroll 1
         for (uint32_t w2 = 1; w2 < NW; w2++) {
