@@ -315,18 +315,34 @@ lut_prepass_kernel(const float* __restrict__ queries, const float* __restrict__ 
 // registers, so every thread keeps its whole share of the table in flight at once -- the copy is
 // bandwidth- not latency-bound.  Returns the largest |entry| bit pattern of the item's tables (from
 // the pre-pass) for the exact-FMA row switch test.  Out of line: runs once per item.
-template <int QL>
+// NWARP (the number of issuing warps) is a template parameter so that the copies of an unrolled block differ by
+// compile-time offsets: one LDGSTS per copy plus two pointer bumps per eight (the first version, with a run-time
+// stride and a bound check per copy, spent 14 instructions per 4-byte copy: r02_cb ncu, 18 % of cfg 5's instructions).
+template <int QL, int NWARP>
 static __device__ __noinline__ void lut_fetch_issue(unsigned char* lut, const float* __restrict__ src, size_t unit_stride,
                                                     const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent,
-                                                    uint32_t w /*rank among the issuing warps*/, uint32_t nwarp) {
-  constexpr uint32_t EPW = 32 / QL;
+                                                    uint32_t w /*rank among the issuing warps*/) {
+  constexpr uint32_t EPW = 32 / QL, STEP = NWARP * EPW;  // entries per warp instruction / per round of the issuing warps
   const uint32_t lane = threadIdx.x & 31;
   const uint32_t unit = units[min(lane % QL, nq - 1)];  // unused slots replicate a valid table (never read back)
-  const float* s = src + (size_t)unit * unit_stride + lane / QL;
-  const uint32_t dst = (uint32_t)__cvta_generic_to_shared(lut) + lane * 4;
-#pragma unroll 8
-  for (uint32_t e = w * EPW; e < nent; e += nwarp * EPW)
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + e * (4 * QL)), "l"(s + e) : "memory");
+  const float* s = src + (size_t)unit * unit_stride + lane / QL + w * EPW;
+  uint32_t dst = (uint32_t)__cvta_generic_to_shared(lut) + lane * 4 + w * EPW * (4 * QL);
+  uint32_t nit = nent > w * EPW ? (nent - w * EPW + STEP - 1) / STEP : 0u;
+#pragma unroll 1
+  for (; nit >= 8; nit -= 8) {
+#define LB200_CP4(K) \
+    asm volatile("cp.async.ca.shared.global [%0 + %2], [%1 + %3], 4;" ::"r"(dst), "l"(s), "n"((K) * STEP * 4 * QL), "n"((K) * STEP * 4) : "memory")
+    LB200_CP4(0); LB200_CP4(1); LB200_CP4(2); LB200_CP4(3); LB200_CP4(4); LB200_CP4(5); LB200_CP4(6); LB200_CP4(7);
+#undef LB200_CP4
+    dst += 8 * STEP * 4 * QL;
+    s += 8 * STEP;
+  }
+#pragma unroll 1
+  for (; nit; nit--) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(s) : "memory");
+    dst += STEP * 4 * QL;
+    s += STEP;
+  }
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
 template <int QL>
@@ -335,11 +351,11 @@ static __device__ __noinline__ uint32_t lut_fetch_wait(const uint32_t* __restric
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   return mb;
 }
-template <int QL>
+template <int QL, int NWARP>
 static __device__ __forceinline__ uint32_t lut_fetch(unsigned char* lut, const float* __restrict__ src,
                                                      const uint32_t* __restrict__ lut_max, size_t unit_stride,
                                                      const uint32_t* units /*shared [QL]*/, uint32_t nq, uint32_t nent) {
-  lut_fetch_issue<QL>(lut, src, unit_stride, units, nq, nent, threadIdx.x >> 5, blockDim.x >> 5);
+  lut_fetch_issue<QL, NWARP>(lut, src, unit_stride, units, nq, nent, threadIdx.x >> 5);
   return lut_fetch_wait<QL>(lut_max, units, nq);
 }
 
@@ -904,7 +920,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
       if (NW == 16 && spref)  // issued by the idle warps at the end of the previous item (below)
         maxbits = lut_fetch_wait<QL>(p.lut_max, p.lut_by_query ? sqidx : spair, nq);
       else
-        maxbits = lut_fetch<QL>(lut, p.lut_src, p.lut_max, (size_t)M * 256, p.lut_by_query ? sqidx : spair, nq, C16 * 4096u);
+        maxbits = lut_fetch<QL, NW>(lut, p.lut_src, p.lut_max, (size_t)M * 256, p.lut_by_query ? sqidx : spair, nq, C16 * 4096u);
     } else {
       const uint32_t slot = tid & 15;
 #pragma unroll 1
@@ -1143,7 +1159,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) scan3_kernel(const Scan3Params 
             if (i == 0) snq_n = nqn;
           }
           asm volatile("bar.sync 1, %0;" ::"n"((NW - QL) * 32) : "memory");
-          lut_fetch_issue<QL>(lut, p.lut_src, (size_t)M * 256, sunit_n, snq_n, C16 * 4096u, w - QL, NW - QL);
+          lut_fetch_issue<QL, NW - QL>(lut, p.lut_src, (size_t)M * 256, sunit_n, snq_n, C16 * 4096u, w - QL);
         }
       }
     }
