@@ -634,3 +634,24 @@ def test_baseline_config_shapes_bit_identical(oracle, name, N, d, nlist, M, metr
             assert oc[qi, j] == n and oi[qi, j, :n].tolist() == pr.tolist()
             assert _bits(od[qi, j, :n]).tolist() == _bits(pd).tolist()
     ix.close()
+
+
+# ---- partition counts that are not a multiple of the prefix kernels' block (1024 threads x a run per thread), with
+# empty partitions in the runs: offsets_kernel / queue_offsets_kernel (both queue orders) against the oracle ----------
+@pytest.mark.parametrize("nlist,lpt", [(1500, "0"), (1500, "1"), (2049, "1"), (1023, "0")])
+def test_ragged_partition_counts_through_worklist_kernels(oracle, nlist, lpt, monkeypatch):
+    from lance_b200 import IvfPqIndex, Query
+    monkeypatch.setenv("LB200_LPT", lpt)
+    rng = np.random.default_rng(nlist)
+    sizes = rng.integers(0, 90, size=nlist)
+    sizes[rng.integers(0, nlist, size=nlist // 7)] = 0            # empty partitions inside the threads' runs
+    sizes[[0, nlist - 1]] = [37, 0]
+    data = _ragged_index("l2", 32, nlist, 16, sizes, seed=nlist + 1)
+    q = queries_near_centroids(data, 48, seed=nlist + 2)
+    ix = IvfPqIndex(data)
+    o = oracle.OracleIndex(data)
+    for nprobes, k in [(40, 10), (nlist, 5)]:
+        gd, gi, gc = ix.search(Query(key=q, k=k, nprobes=nprobes))
+        rd, ri, rc, _ = o.search(q, k=k, nprobes=nprobes, refine_factor=0)
+        _assert_same(gd, gi, gc, rd[:, :k], ri[:, :k], np.minimum(rc, k), f"nlist={nlist} lpt={lpt} nprobes={nprobes}")
+    ix.close()
