@@ -27,6 +27,10 @@
 //  * Candidates are filtered against a running k'-th-best threshold that is shared by the warps
 //    of the CTA and -- for merged searches -- by all work items of the same query (global
 //    atomicMin), so that after a query's first partition almost nothing reaches the buffers.
+//  * Life of a work item in a CTA: take the descriptor (fetched during the previous item) -> tables (built here from
+//    the lane-order codebook image, or copied from the pre-pass: bulk copies of a group image / 4-byte gathers of
+//    per-query tables, in the wide CTAs both ISSUED during the previous item's select) -> row loop -> barrier ->
+//    next item's table fetch starts -> one warp per query selects k' (in registers for <= 128 candidates) and emits.
 #pragma once
 #include "scan.cuh"
 
@@ -41,7 +45,7 @@
 #define LB200_FINALIZE_SMALL 1
 #endif
 #ifndef LB200_FINALIZE_SMALL_INLINE
-#define LB200_FINALIZE_SMALL_INLINE 0   // the call-free (BOOT = false) text: A/B'd separately, see DESIGN 4.2
+#define LB200_FINALIZE_SMALL_INLINE 0   // the call-free (BOOT = false) text: as a call 2-4 % slower there
 #endif
 #ifndef LB200_CB_DEPTH
 #define LB200_CB_DEPTH 1
